@@ -1,0 +1,720 @@
+// C ABI of libtaco_b200.so (include/taco_b200.h): handle, weight ingestion / packing, and the
+// host-side orchestration of the sm_100a kernels.  No torch types, no CPU compute fallback.
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <string>
+#include <vector>
+
+#include "taco_internal.h"
+
+namespace {
+
+struct Weight {
+    std::vector<float> host;
+    std::vector<int64_t> shape;
+    float* dev = nullptr;
+};
+
+struct Buf {
+    void* p = nullptr;
+    size_t bytes = 0;
+};
+
+const char* ENC_CONV = "encoder_convolutions/conv_layer_%d_encoder_convolutions";
+const char* POST_CONV = "postnet_convolutions/conv_layer_%d_postnet_convolutions";
+const char* ENC_FW = "encoder_LSTM/bidirectional_rnn/fw/encoder_fw_lstm";
+const char* ENC_BW = "encoder_LSTM/bidirectional_rnn/bw/encoder_bw_lstm";
+const char* REF_CONV = "ref_encoder/conv2d_%d";
+const char* REF_GRU = "ref_encoder/rnn/gru_cell";
+const char* REF_DENSE = "ref_encoder/dense";
+const char* MHA = "Multihead-attention";
+const char* PRENET = "decoder/decoder_prenet/dense_%d";
+const char* DEC_LSTM1 = "decoder/decoder_LSTM/multi_rnn_cell/cell_0/decoder_LSTM_1";
+const char* DEC_LSTM2 = "decoder/decoder_LSTM/multi_rnn_cell/cell_1/decoder_LSTM_2";
+const char* LSA = "decoder/Location_Sensitive_Attention";
+const char* MEMORY_LAYER = "decoder/memory_layer";
+const char* FRAME_PROJ = "decoder/linear_transform_projection/projection_linear_transform_projection";
+const char* STOP_PROJ = "decoder/stop_token_projection/projection_stop_token_projection";
+const char* POST_PROJ = "postnet_projection/projection_postnet_projection";
+
+std::string fmt(const char* f, int a) {
+    char buf[256];
+    snprintf(buf, sizeof buf, f, a);
+    return buf;
+}
+
+}  // namespace
+
+struct TacoHandle {
+    TacoHParams hp;
+    int device = 0;
+    std::string err;
+    std::map<std::string, Weight> w;
+    std::map<std::string, Buf> ws;
+    std::vector<void*> owned;
+    bool finalized = false;
+    int precision = TACO_PRECISION_FP32;
+    int64_t launches = 0;
+    int n_sm = 0;
+    // folded BN scale/shift
+    float *enc_scale[8] = {}, *enc_shift[8] = {};
+    float *post_scale[8] = {}, *post_shift[8] = {};
+    float *ref_scale[8] = {}, *ref_shift[8] = {};
+    // packed resident shards
+    float* dec_blob[2] = {};     // U = 2 (GN 128), U = 4 (GN 64)
+    float* bilstm_blob[2] = {};  // same two configs, [2 dir][GN][256*4U]
+    // decoder running state
+    int dec_t = 0, dec_B = 0, dec_T = 0, dec_RBP = 0, dec_GB = 0;
+};
+
+namespace {
+
+#define CK(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess) {                                                                   \
+            h->err = std::string(#call) + ": " + cudaGetErrorString(e_);                           \
+            return TACO_ERR_CUDA;                                                                  \
+        }                                                                                          \
+    } while (0)
+
+#define FAIL(code, msg)  \
+    do {                 \
+        h->err = (msg);  \
+        return (code);   \
+    } while (0)
+
+int get_ws(TacoHandle* h, const std::string& name, size_t bytes, void** out) {
+    Buf& b = h->ws[name];
+    if (b.bytes < bytes) {
+        if (b.p) {
+            CK(cudaDeviceSynchronize());
+            CK(cudaFree(b.p));
+            b.p = nullptr;
+            b.bytes = 0;
+        }
+        size_t want = bytes + bytes / 8 + 256;
+        CK(cudaMalloc(&b.p, want));
+        b.bytes = want;
+    }
+    *out = b.p;
+    return TACO_OK;
+}
+
+#define WS(ptr, type, name, count)                                              \
+    type* ptr;                                                                  \
+    {                                                                           \
+        void* v_;                                                               \
+        int rc_ = get_ws(h, name, (size_t)(count) * sizeof(type), &v_);         \
+        if (rc_ != TACO_OK) return rc_;                                         \
+        ptr = reinterpret_cast<type*>(v_);                                      \
+    }
+
+const Weight* find_w(TacoHandle* h, const std::string& name) {
+    auto it = h->w.find(name);
+    return it == h->w.end() ? nullptr : &it->second;
+}
+
+int upload(TacoHandle* h, const std::vector<float>& v, float** out) {
+    void* d;
+    CK(cudaMalloc(&d, v.size() * sizeof(float)));
+    CK(cudaMemcpy(d, v.data(), v.size() * sizeof(float), cudaMemcpyHostToDevice));
+    h->owned.push_back(d);
+    *out = reinterpret_cast<float*>(d);
+    return TACO_OK;
+}
+
+// BN(inference) + conv bias folded:  y = conv*scale + shift
+int fold_bn(TacoHandle* h, const std::string& scope, const char* conv, float eps, float** scale, float** shift) {
+    const Weight* bias = find_w(h, scope + "/" + conv + "/bias");
+    const Weight* g = find_w(h, scope + "/batch_normalization/gamma");
+    const Weight* b = find_w(h, scope + "/batch_normalization/beta");
+    const Weight* mu = find_w(h, scope + "/batch_normalization/moving_mean");
+    const Weight* var = find_w(h, scope + "/batch_normalization/moving_variance");
+    if (!bias || !g || !b || !mu || !var) FAIL(TACO_ERR_MISSING_WEIGHT, "missing BN/bias variables under " + scope);
+    size_t c = g->host.size();
+    std::vector<float> sc(c), sh(c);
+    for (size_t i = 0; i < c; ++i) {
+        float s = g->host[i] / sqrtf(var->host[i] + eps);
+        sc[i] = s;
+        sh[i] = b->host[i] + (bias->host[i] - mu->host[i]) * s;
+    }
+    int rc = upload(h, sc, scale);
+    if (rc) return rc;
+    return upload(h, sh, shift);
+}
+
+int need(TacoHandle* h, const std::string& name, std::initializer_list<int64_t> shape, const Weight** out) {
+    const Weight* w = find_w(h, name);
+    if (!w) FAIL(TACO_ERR_MISSING_WEIGHT, "missing variable " + name);
+    if (w->shape.size() != shape.size()) FAIL(TACO_ERR_INVALID, "rank mismatch for " + name);
+    size_t i = 0;
+    for (int64_t s : shape) {
+        if (w->shape[i++] != s) FAIL(TACO_ERR_INVALID, "shape mismatch for " + name);
+    }
+    *out = w;
+    return TACO_OK;
+}
+
+int pack_decoder_blobs(TacoHandle* h) {
+    const Weight *k1, *b1, *k2, *b2, *kp1, *bp1, *kp2, *bp2, *kq, *kf, *bf, *kst, *bst;
+    int rc;
+#define NEED(var, name, ...)                              \
+    if ((rc = need(h, name, {__VA_ARGS__}, &var))) return rc;
+    NEED(k1, std::string(DEC_LSTM1) + "/kernel", 1280, 1024)
+    NEED(b1, std::string(DEC_LSTM1) + "/bias", 1024)
+    NEED(k2, std::string(DEC_LSTM2) + "/kernel", 512, 1024)
+    NEED(b2, std::string(DEC_LSTM2) + "/bias", 1024)
+    NEED(kp1, fmt(PRENET, 1) + "/kernel", 80, 256)
+    NEED(bp1, fmt(PRENET, 1) + "/bias", 256)
+    NEED(kp2, fmt(PRENET, 2) + "/kernel", 256, 256)
+    NEED(bp2, fmt(PRENET, 2) + "/bias", 256)
+    NEED(kq, std::string(LSA) + "/query_layer/kernel", 256, 128)
+    NEED(kf, std::string(FRAME_PROJ) + "/kernel", 1024, 160)
+    NEED(bf, std::string(FRAME_PROJ) + "/bias", 160)
+    NEED(kst, std::string(STOP_PROJ) + "/kernel", 1024, 2)
+    NEED(bst, std::string(STOP_PROJ) + "/bias", 2)
+    for (int cfg = 0; cfg < 2; ++cfg) {
+        const int U = cfg == 0 ? 2 : 4, GN = 256 / U, NCL = 4 * U;
+        const int PCN = 256 / GN, QCN = 128 / GN;
+        const int bf_ = taco_decoder_blob_floats(U);
+        std::vector<float> blob((size_t)GN * bf_, 0.f);
+        for (int nt = 0; nt < GN; ++nt) {
+            float* p = blob.data() + (size_t)nt * bf_;
+            float* W1 = p;
+            float* W2 = W1 + 1280 * NCL;
+            float* Wp1 = W2 + 512 * NCL;
+            float* Wp2 = Wp1 + 80 * 4;
+            float* Wq = Wp2 + 256 * 4;
+            float* Wo = Wq + 256 * 4;
+            float* bias = Wo + 1024 * 4;
+            for (int g = 0; g < 4; ++g)
+                for (int ul = 0; ul < U; ++ul) {
+                    int col = g * 256 + nt * U + ul, lc = g * U + ul;
+                    for (int k = 0; k < 1280; ++k) W1[k * NCL + lc] = k1->host[(size_t)k * 1024 + col];
+                    for (int k = 0; k < 512; ++k) W2[k * NCL + lc] = k2->host[(size_t)k * 1024 + col];
+                    bias[lc] = b1->host[col];
+                    bias[NCL + lc] = b2->host[col];
+                }
+            for (int j = 0; j < PCN; ++j) {
+                int col = nt * PCN + j;
+                for (int k = 0; k < 80; ++k) Wp1[k * 4 + j] = kp1->host[(size_t)k * 256 + col];
+                for (int k = 0; k < 256; ++k) Wp2[k * 4 + j] = kp2->host[(size_t)k * 256 + col];
+                bias[2 * NCL + j] = bp1->host[col];
+                bias[2 * NCL + 4 + j] = bp2->host[col];
+            }
+            for (int j = 0; j < QCN; ++j) {
+                int col = nt * QCN + j;
+                for (int k = 0; k < 256; ++k) Wq[k * 4 + j] = kq->host[(size_t)k * 128 + col];
+            }
+            for (int j = 0; j < 4; ++j) {
+                int col = nt * 4 + j;
+                if (col < 160) {
+                    for (int k = 0; k < 1024; ++k) Wo[k * 4 + j] = kf->host[(size_t)k * 160 + col];
+                    bias[2 * NCL + 8 + j] = bf->host[col];
+                } else if (col < 162) {
+                    for (int k = 0; k < 1024; ++k) Wo[k * 4 + j] = kst->host[(size_t)k * 2 + (col - 160)];
+                    bias[2 * NCL + 8 + j] = bst->host[col - 160];
+                }
+            }
+        }
+        if ((rc = upload(h, blob, &h->dec_blob[cfg]))) return rc;
+    }
+    // BiLSTM recurrent shards (rows 512..767 of the [768,1024] kernels)
+    const Weight *kfw, *kbw, *bfw, *bbw;
+    NEED(kfw, std::string(ENC_FW) + "/kernel", 768, 1024)
+    NEED(kbw, std::string(ENC_BW) + "/kernel", 768, 1024)
+    NEED(bfw, std::string(ENC_FW) + "/bias", 1024)
+    NEED(bbw, std::string(ENC_BW) + "/bias", 1024)
+    for (int cfg = 0; cfg < 2; ++cfg) {
+        const int U = cfg == 0 ? 2 : 4, GN = 256 / U, NCL = 4 * U;
+        const int bf_ = taco_bilstm_blob_floats(U);
+        std::vector<float> blob((size_t)2 * GN * bf_, 0.f);
+        for (int d = 0; d < 2; ++d) {
+            const Weight* kk = d == 0 ? kfw : kbw;
+            for (int nt = 0; nt < GN; ++nt) {
+                float* p = blob.data() + ((size_t)d * GN + nt) * bf_;
+                for (int g = 0; g < 4; ++g)
+                    for (int ul = 0; ul < U; ++ul) {
+                        int col = g * 256 + nt * U + ul, lc = g * U + ul;
+                        for (int k = 0; k < 256; ++k) p[k * NCL + lc] = kk->host[(size_t)(512 + k) * 1024 + col];
+                    }
+            }
+        }
+        if ((rc = upload(h, blob, &h->bilstm_blob[cfg]))) return rc;
+    }
+#undef NEED
+    return TACO_OK;
+}
+
+const float* dev_w(TacoHandle* h, const std::string& name) {
+    const Weight* w = find_w(h, name);
+    return w ? w->dev : nullptr;
+}
+
+__global__ void clip_copy_kernel(const float* __restrict__ in, float* __restrict__ out, int B, int F, int F_stride, int C,
+                                 float lo, float hi, int clip) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    size_t n = (size_t)B * F * C;
+    if (i >= n) return;
+    size_t c = i % C, f = (i / C) % F, b = i / ((size_t)C * F);
+    float v = in[(b * F_stride + f) * C + c];
+    out[i] = clip ? fminf(fmaxf(v, lo), hi) : v;
+}
+
+// XT layout [GB][K][RBP] -> row-major [B][K]
+__global__ void untranspose_xt_kernel(const float* __restrict__ xt, float* __restrict__ out, int B, int K, int RBP) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= B * K) return;
+    int b = i / K, k = i % K;
+    out[i] = xt[((size_t)(b / RBP) * K + k) * RBP + (b % RBP)];
+}
+
+int conv(TacoHandle* h, const float* x, long long x_stride, long long x_bstride, const float* w, const float* scale,
+         const float* shift, float* y, long long y_stride, long long y_bstride, const float* residual, int B, int T, int Cin,
+         int Cout, int k, int act, bool clip, float lo, float hi, cudaStream_t st) {
+    ConvParams p;
+    memset(&p, 0, sizeof p);
+    p.x = x; p.x_stride = x_stride; p.x_bstride = x_bstride;
+    p.w = w; p.scale = scale; p.shift = shift;
+    p.y = y; p.y_stride = y_stride; p.y_bstride = y_bstride;
+    p.residual = residual;
+    p.B = B; p.T = T; p.Cin = Cin; p.Cout = Cout; p.k = k; p.act = act;
+    p.clip = clip ? 1 : 0; p.clip_lo = lo; p.clip_hi = hi;
+    CK(taco_launch_conv1d_f32(p, st));
+    h->launches++;
+    return TACO_OK;
+}
+
+bool hp_supported(const TacoHParams& hp, std::string* why) {
+#define REQ(cond)                                  \
+    if (!(cond)) {                                 \
+        *why = "unsupported hparams: " #cond;      \
+        return false;                              \
+    }
+    REQ(hp.embedding_dim == 512)
+    REQ(hp.conv_channels == 512)
+    REQ(hp.enc_lstm_hidden_size == 256)
+    REQ(hp.style_embed_depth == 256)
+    REQ(hp.use_gst == 1)
+    REQ(hp.num_heads * (hp.style_embed_depth / hp.num_heads) == hp.style_embed_depth)
+    REQ(hp.reference_depth == 128)
+    REQ(hp.n_reference_filters >= 1 && hp.n_reference_filters <= 8)
+    REQ(hp.attention_dim == 128)
+    REQ(hp.attention_filters == 32)
+    REQ(hp.attention_kernel == 31)
+    REQ(hp.prenet_layers[0] == 256 && hp.prenet_layers[1] == 256)
+    REQ(hp.decoder_lstm_units == 256)
+    REQ(hp.num_mels == 80)
+    REQ(hp.outputs_per_step == 2)
+    REQ(hp.conv_num_layers >= 1 && hp.conv_num_layers <= 8)
+    REQ(hp.postnet_num_layers >= 1 && hp.postnet_num_layers <= 8)
+    REQ((hp.postnet_channels + hp.style_embed_depth) % 16 == 0)
+    REQ(hp.conv_kernel_size % 2 == 1 && hp.postnet_kernel_size % 2 == 1)
+#undef REQ
+    return true;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* taco_version(void) { return "taco_b200 0.1 sm_100a"; }
+
+int taco_create(const TacoHParams* hp, int device, TacoHandle** out) {
+    if (!hp || !out) return TACO_ERR_INVALID;
+    *out = nullptr;
+    TacoHandle* h = new TacoHandle();
+    h->hp = *hp;
+    h->device = device;
+    *out = h;  // returned even on failure so the caller can read taco_last_error
+    std::string why;
+    if (!hp_supported(*hp, &why)) FAIL(TACO_ERR_UNSUPPORTED, why);
+    CK(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, device));
+    h->n_sm = prop.multiProcessorCount;
+    if (prop.major < 10) FAIL(TACO_ERR_UNSUPPORTED, "sm_100a device required (no fallback path)");
+    if (!prop.cooperativeLaunch) FAIL(TACO_ERR_UNSUPPORTED, "cooperative launch unsupported");
+    if (h->n_sm < 128) FAIL(TACO_ERR_UNSUPPORTED, "persistent decoder needs >= 128 SMs");
+    return TACO_OK;
+}
+
+void taco_destroy(TacoHandle* h) {
+    if (!h) return;
+    cudaSetDevice(h->device);
+    cudaDeviceSynchronize();
+    for (auto& kv : h->w)
+        if (kv.second.dev) cudaFree(kv.second.dev);
+    for (auto& kv : h->ws)
+        if (kv.second.p) cudaFree(kv.second.p);
+    for (void* p : h->owned) cudaFree(p);
+    delete h;
+}
+
+const char* taco_last_error(const TacoHandle* h) { return h ? h->err.c_str() : "null handle"; }
+
+int64_t taco_launch_count(const TacoHandle* h) { return h ? h->launches : 0; }
+
+int taco_set_precision(TacoHandle* h, int precision) {
+    if (!h) return TACO_ERR_INVALID;
+    if (precision != TACO_PRECISION_FP32 && precision != TACO_PRECISION_BF16_CONV) FAIL(TACO_ERR_INVALID, "bad precision");
+    if (precision == TACO_PRECISION_BF16_CONV) FAIL(TACO_ERR_UNSUPPORTED, "tcgen05 conv path not built into this library");
+    h->precision = precision;
+    return TACO_OK;
+}
+
+int taco_set_weight(TacoHandle* h, const char* name, const void* data, const int64_t* shape, int rank, int dtype) {
+    if (!h || !name || !data || rank < 0 || rank > 4) return TACO_ERR_INVALID;
+    if (dtype != TACO_DTYPE_F32) FAIL(TACO_ERR_UNSUPPORTED, "only fp32 weights are accepted");
+    CK(cudaSetDevice(h->device));
+    size_t n = 1;
+    for (int i = 0; i < rank; ++i) n *= (size_t)shape[i];
+    Weight& w = h->w[name];
+    w.shape.assign(shape, shape + rank);
+    w.host.resize(n);
+    CK(cudaMemcpy(w.host.data(), data, n * sizeof(float), cudaMemcpyDefault));
+    if (w.dev) {
+        CK(cudaFree(w.dev));
+        w.dev = nullptr;
+    }
+    CK(cudaMalloc(&w.dev, (n + 4) * sizeof(float)));
+    CK(cudaMemcpy(w.dev, w.host.data(), n * sizeof(float), cudaMemcpyHostToDevice));
+    h->finalized = false;
+    return TACO_OK;
+}
+
+int taco_finalize_weights(TacoHandle* h) {
+    if (!h) return TACO_ERR_INVALID;
+    CK(cudaSetDevice(h->device));
+    for (void* p : h->owned) cudaFree(p);
+    h->owned.clear();
+    const float eps = 1e-3f;  // tf.layers.batch_normalization default
+    int rc;
+    for (int i = 0; i < h->hp.conv_num_layers; ++i)
+        if ((rc = fold_bn(h, fmt(ENC_CONV, i + 1), "conv1d", eps, &h->enc_scale[i], &h->enc_shift[i]))) return rc;
+    for (int i = 0; i < h->hp.postnet_num_layers; ++i)
+        if ((rc = fold_bn(h, fmt(POST_CONV, i + 1), "conv1d", eps, &h->post_scale[i], &h->post_shift[i]))) return rc;
+    for (int i = 0; i < h->hp.n_reference_filters; ++i)
+        if ((rc = fold_bn(h, fmt(REF_CONV, i), "conv2d", eps, &h->ref_scale[i], &h->ref_shift[i]))) return rc;
+    if ((rc = pack_decoder_blobs(h))) return rc;
+    const char* required[] = {"inputs_embedding", "style_tokens"};
+    for (const char* r : required)
+        if (!find_w(h, r)) FAIL(TACO_ERR_MISSING_WEIGHT, std::string("missing variable ") + r);
+    std::string req2[] = {std::string(MEMORY_LAYER) + "/kernel", std::string(LSA) + "/location_features_convolution/kernel",
+                          std::string(LSA) + "/location_features_convolution/bias", std::string(LSA) + "/location_features_layer/kernel",
+                          std::string(LSA) + "/attention_variable", std::string(LSA) + "/attention_bias",
+                          std::string(POST_PROJ) + "/kernel", std::string(POST_PROJ) + "/bias",
+                          std::string(REF_GRU) + "/gates/kernel", std::string(REF_GRU) + "/gates/bias",
+                          std::string(REF_GRU) + "/candidate/kernel", std::string(REF_GRU) + "/candidate/bias",
+                          std::string(REF_DENSE) + "/kernel", std::string(REF_DENSE) + "/bias",
+                          std::string(MHA) + "/conv1d/kernel", std::string(MHA) + "/conv1d/bias",
+                          std::string(MHA) + "/conv1d_1/kernel", std::string(MHA) + "/conv1d_1/bias",
+                          std::string(MHA) + "/attention_v", std::string(MHA) + "/attention_g", std::string(MHA) + "/attention_b"};
+    for (const std::string& r : req2)
+        if (!find_w(h, r)) FAIL(TACO_ERR_MISSING_WEIGHT, "missing variable " + r);
+    for (int i = 0; i < h->hp.conv_num_layers; ++i)
+        if (!find_w(h, fmt(ENC_CONV, i + 1) + "/conv1d/kernel")) FAIL(TACO_ERR_MISSING_WEIGHT, "missing encoder conv kernel");
+    for (int i = 0; i < h->hp.postnet_num_layers; ++i)
+        if (!find_w(h, fmt(POST_CONV, i + 1) + "/conv1d/kernel")) FAIL(TACO_ERR_MISSING_WEIGHT, "missing postnet conv kernel");
+    for (int i = 0; i < h->hp.n_reference_filters; ++i)
+        if (!find_w(h, fmt(REF_CONV, i) + "/conv2d/kernel")) FAIL(TACO_ERR_MISSING_WEIGHT, "missing reference conv2d kernel");
+    h->finalized = true;
+    return TACO_OK;
+}
+
+int taco_encode(TacoHandle* h, const int32_t* ids, const int32_t* lens, int B, int T, const float* ref_mel, int Tm,
+                const float* gst_weights, float* memory_out, void* stream) {
+    if (!h) return TACO_ERR_INVALID;
+    if (!h->finalized) FAIL(TACO_ERR_STATE, "taco_finalize_weights has not been called");
+    if (!ids || !lens || !memory_out || B < 1 || T < 1) FAIL(TACO_ERR_INVALID, "taco_encode: bad arguments");
+    if (!ref_mel && !gst_weights) FAIL(TACO_ERR_INVALID, "taco_encode: neither reference mel nor GST weights given");
+    if (B > 64) FAIL(TACO_ERR_UNSUPPORTED, "taco_encode: B > 64 per call (shard the batch on the host)");
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    CK(cudaSetDevice(h->device));
+    const TacoHParams& hp = h->hp;
+    const int E = hp.embedding_dim, C = hp.conv_channels, H = hp.enc_lstm_hidden_size, SD = hp.style_embed_depth;
+    const int MD = 2 * H + SD;
+    const size_t M = (size_t)B * T;
+    WS(bufA, float, "enc_a", M * 512)
+    WS(bufB, float, "enc_b", M * 512)
+    WS(xw, float, "enc_xw", 2 * M * 1024)
+    CK(taco_launch_embedding(ids, dev_w(h, "inputs_embedding"), bufA, (int)M, E, hp.n_symbols, st));
+    h->launches++;
+    float *cur = bufA, *nxt = bufB;
+    int cin = E, rc;
+    for (int i = 0; i < hp.conv_num_layers; ++i) {
+        rc = conv(h, cur, cin, (long long)T * cin, dev_w(h, fmt(ENC_CONV, i + 1) + "/conv1d/kernel"), h->enc_scale[i],
+                  h->enc_shift[i], nxt, C, (long long)T * C, nullptr, B, T, cin, C, hp.conv_kernel_size, ACT_RELU, false, 0, 0, st);
+        if (rc) return rc;
+        std::swap(cur, nxt);
+        cin = C;
+    }
+    // hoisted input projection of both LSTM directions: xw[d] = conv_out . W[0:512] + bias
+    for (int d = 0; d < 2; ++d) {
+        const char* scope = d == 0 ? ENC_FW : ENC_BW;
+        rc = conv(h, cur, C, (long long)T * C, dev_w(h, std::string(scope) + "/kernel"), nullptr,
+                  dev_w(h, std::string(scope) + "/bias"), xw + (size_t)d * M * 1024, 1024, (long long)T * 1024, nullptr, B, T, C,
+                  4 * H, 1, ACT_NONE, false, 0, 0, st);
+        if (rc) return rc;
+    }
+    CK(cudaMemsetAsync(memory_out, 0, M * MD * sizeof(float), st));
+    {
+        BiLstmParams p;
+        memset(&p, 0, sizeof p);
+        p.B = B; p.T = T;
+        p.RBP = B <= 4 ? 4 : (B <= 8 ? 8 : (B <= 16 ? 16 : 32));
+        p.GB = (B + p.RBP - 1) / p.RBP;
+        const int cfg = p.GB == 1 ? 0 : 1;
+        p.U = cfg == 0 ? 2 : 4;
+        p.GN = 256 / p.U;
+        p.blobs = h->bilstm_blob[cfg];
+        p.blob_floats = taco_bilstm_blob_floats(p.U);
+        p.xw = xw;
+        p.lens = lens;
+        const size_t hT_floats = (size_t)2 * 2 * p.GB * 256 * p.RBP;
+        WS(hT, float, "enc_hT", hT_floats)
+        WS(bar, unsigned, "enc_bar", 4)
+        CK(cudaMemsetAsync(hT, 0, hT_floats * sizeof(float), st));
+        CK(cudaMemsetAsync(bar, 0, 4 * sizeof(unsigned), st));
+        p.hT = hT;
+        p.out = memory_out;
+        p.out_stride = MD;
+        p.zoneout = hp.zoneout_rate;
+        p.barrier = bar;
+        CK(taco_launch_bilstm(p, st));
+        h->launches++;
+    }
+    // style embedding
+    WS(style, float, "enc_style", (size_t)B * SD)
+    const int heads = hp.num_heads, tokd = SD / heads;
+    if (ref_mel) {
+        if (Tm < 1) FAIL(TACO_ERR_INVALID, "taco_encode: reference mel length");
+        int Hh = Tm, Ww = hp.num_mels, cin2 = 1;
+        size_t maxel = 0;
+        {
+            int hh = Hh, ww = Ww;
+            for (int i = 0; i < hp.n_reference_filters; ++i) {
+                hh = (hh + 1) / 2; ww = (ww + 1) / 2;
+                size_t el = (size_t)B * hh * ww * hp.reference_filters[i];
+                if (el > maxel) maxel = el;
+            }
+        }
+        WS(rA, float, "ref_a", maxel)
+        WS(rB, float, "ref_b", maxel)
+        const float* src = ref_mel;
+        float *dst = rA, *other = rB;
+        for (int i = 0; i < hp.n_reference_filters; ++i) {
+            int cout = hp.reference_filters[i];
+            CK(taco_launch_conv2d_s2(src, dev_w(h, fmt(REF_CONV, i) + "/conv2d/kernel"), h->ref_scale[i], h->ref_shift[i], dst, B,
+                                     Hh, Ww, cin2, cout, st));
+            h->launches++;
+            Hh = (Hh + 1) / 2; Ww = (Ww + 1) / 2; cin2 = cout;
+            src = dst;
+            std::swap(dst, other);
+        }
+        WS(refo, float, "ref_out", (size_t)B * 128)
+        const int In = Ww * cin2;
+        const Weight* gk = find_w(h, std::string(REF_GRU) + "/gates/kernel");
+        if ((int64_t)gk->shape[0] != In + 128) FAIL(TACO_ERR_INVALID, "reference GRU kernel does not match conv stack output width");
+        CK(taco_launch_ref_gru(src, B, Hh, In, dev_w(h, std::string(REF_GRU) + "/gates/kernel"),
+                               dev_w(h, std::string(REF_GRU) + "/gates/bias"), dev_w(h, std::string(REF_GRU) + "/candidate/kernel"),
+                               dev_w(h, std::string(REF_GRU) + "/candidate/bias"), dev_w(h, std::string(REF_DENSE) + "/kernel"),
+                               dev_w(h, std::string(REF_DENSE) + "/bias"), refo, st));
+        h->launches++;
+        CK(taco_launch_gst_attention(refo, dev_w(h, "style_tokens"), dev_w(h, std::string(MHA) + "/conv1d/kernel"),
+                                     dev_w(h, std::string(MHA) + "/conv1d/bias"), dev_w(h, std::string(MHA) + "/conv1d_1/kernel"),
+                                     dev_w(h, std::string(MHA) + "/conv1d_1/bias"), dev_w(h, std::string(MHA) + "/attention_v"),
+                                     dev_w(h, std::string(MHA) + "/attention_g"), dev_w(h, std::string(MHA) + "/attention_b"), style, B,
+                                     hp.num_gst, tokd, heads, hp.style_att_dim, st));
+        h->launches++;
+        CK(taco_launch_style_fill(memory_out, style, B, T, SD, MD, SD, st));
+    } else {
+        CK(taco_launch_style_random(gst_weights, dev_w(h, "style_tokens"), style, heads, hp.num_gst, tokd, st));
+        h->launches++;
+        CK(taco_launch_style_fill(memory_out, style, B, T, SD, MD, 0, st));
+    }
+    h->launches++;
+    return TACO_OK;
+}
+
+int taco_decode(TacoHandle* h, int mode, const float* memory, const int32_t* lens, int B, int T, const float* mel_targets,
+                int F_tgt, int S_max, const uint8_t* prenet_masks, uint64_t philox_seed, int reset_state, int logits_only,
+                float* frames, float* stop, float* align_hist, int32_t* steps_out, void* stream) {
+    if (!h) return TACO_ERR_INVALID;
+    if (!h->finalized) FAIL(TACO_ERR_STATE, "taco_finalize_weights has not been called");
+    if (!memory || !lens || !frames || !stop || !align_hist || !steps_out || B < 1 || T < 1 || S_max < 1)
+        FAIL(TACO_ERR_INVALID, "taco_decode: bad arguments");
+    if (mode != TACO_MODE_FREE && mode != TACO_MODE_TEACHER) FAIL(TACO_ERR_INVALID, "taco_decode: bad mode");
+    if (mode == TACO_MODE_TEACHER && (!mel_targets || F_tgt < 1)) FAIL(TACO_ERR_INVALID, "taco_decode: teacher mode needs mel targets");
+    if (B > 64) FAIL(TACO_ERR_UNSUPPORTED, "taco_decode: B > 64 per call (shard the batch on the host)");
+    if (T > 1024) FAIL(TACO_ERR_UNSUPPORTED, "taco_decode: T > 1024");
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    CK(cudaSetDevice(h->device));
+    const TacoHParams& hp = h->hp;
+
+    DecParams p;
+    memset(&p, 0, sizeof p);
+    p.B = B; p.T = T;
+    p.RBP = B <= 4 ? 4 : (B <= 8 ? 8 : (B <= 16 ? 16 : 32));
+    p.GB = (B + p.RBP - 1) / p.RBP;
+    const int cfg = p.GB == 1 ? 0 : 1;
+    p.U = cfg == 0 ? 2 : 4;
+    p.GN = 256 / p.U;
+    const int nCta = p.GB * p.GN;
+    static const int ns_opts[] = {96, 64, 48, 32, 24, 16, 12, 8, 6, 4, 3, 2, 1};
+    p.NS = 1;
+    for (int ns : ns_opts)
+        if (B * ns <= nCta) { p.NS = ns; break; }
+    p.S_max = S_max; p.S_cap = S_max; p.mode = mode;
+    p.stop_at_any = hp.stop_at_any; p.cumulative = hp.cumulative_weights; p.smoothing = hp.smoothing;
+    p.stop_sigmoid = logits_only ? 0 : 1;
+    p.zoneout = hp.zoneout_rate;
+    p.keep_scale = 1.0f / (1.0f - hp.dropout_rate);
+    p.blobs = h->dec_blob[cfg];
+    p.blob_floats = taco_decoder_blob_floats(p.U);
+    p.Wl = dev_w(h, std::string(LSA) + "/location_features_layer/kernel");
+    p.conv_w = dev_w(h, std::string(LSA) + "/location_features_convolution/kernel");
+    p.conv_b = dev_w(h, std::string(LSA) + "/location_features_convolution/bias");
+    p.v_a = dev_w(h, std::string(LSA) + "/attention_variable");
+    p.b_a = dev_w(h, std::string(LSA) + "/attention_bias");
+
+    if (!reset_state && (h->dec_B != B || h->dec_T != T)) FAIL(TACO_ERR_STATE, "taco_decode: continuing with a different batch shape");
+    // lengths: mask_encoder False => every row attends over all T positions (Attention.py:150)
+    WS(lens_eff, int32_t, "dec_lens", B)
+    if (hp.mask_encoder) {
+        CK(cudaMemcpyAsync(lens_eff, lens, B * sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
+    } else {
+        std::vector<int32_t> full(B, T);
+        CK(cudaMemcpyAsync(lens_eff, full.data(), B * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+        CK(cudaStreamSynchronize(st));
+    }
+    p.lens = lens_eff;
+    // keys = memory_layer(values), computed once per utterance batch (Attention.py:153-158)
+    WS(keys, float, "dec_keys", (size_t)B * T * 128)
+    if (reset_state) {
+        int rc = conv(h, memory, 768, (long long)T * 768, dev_w(h, std::string(MEMORY_LAYER) + "/kernel"), nullptr, nullptr, keys, 128,
+                      (long long)T * 128, nullptr, B, T, 768, 128, 1, ACT_NONE, false, 0, 0, st);
+        if (rc) return rc;
+    }
+    p.values = memory;
+    p.keys = keys;
+    // exchange buffers: one allocation, zeroed on reset
+    const size_t R = p.RBP, GBs = p.GB;
+    const size_t n_x = GBs * 80 * R, n_256 = GBs * 256 * R, n_768 = GBs * 768 * R;
+    const size_t n_q = (size_t)B * 128, n_cum = (size_t)B * T, n_c = (size_t)B * 256;
+    const size_t total = n_x + 2 * n_256 /*p1,p2*/ + n_768 + 2 * n_256 /*h1z*/ + n_256 + 2 * n_256 /*h2z*/ + n_256 + n_q + n_cum + 2 * n_c;
+    WS(ex, float, "dec_exchange", total + 64)
+    WS(pre, float, "dec_pre", (size_t)B * T * 128)
+    if (reset_state) {
+        CK(cudaMemsetAsync(ex, 0, (total + 64) * sizeof(float), st));
+        h->dec_t = 0;
+    }
+    float* c = ex;
+    p.xT = c; c += n_x;
+    p.p1T = c; c += n_256;
+    p.p2T = c; c += n_256;
+    p.ctxT = c; c += n_768;
+    p.h1zT = c; c += 2 * n_256;
+    p.h1rawT = c; c += n_256;
+    p.h2zT = c; c += 2 * n_256;
+    p.h2rawT = c; c += n_256;
+    p.q = c; c += n_q;
+    p.cum = c; c += n_cum;
+    p.c1 = c; c += n_c;
+    p.c2 = c; c += n_c;
+    p.pre = pre;
+    p.t0 = h->dec_t;
+    p.targets = mel_targets;
+    p.F_tgt = F_tgt;
+    p.masks = prenet_masks;
+    p.seed = philox_seed;
+    p.frames = frames; p.stop = stop; p.hist = align_hist; p.steps_out = steps_out;
+    WS(cnt, int, "dec_stop_count", (size_t)S_max + 8)
+    CK(cudaMemsetAsync(cnt, 0, ((size_t)S_max + 8) * sizeof(int), st));
+    p.stop_count = cnt;
+    p.barrier = reinterpret_cast<unsigned*>(cnt + S_max + 4);
+    CK(taco_launch_decoder(p, st));
+    h->launches++;
+    h->dec_t += S_max;  // exact for S_max == 1 (cell stepping) and for runs to completion
+    h->dec_B = B; h->dec_T = T; h->dec_RBP = p.RBP; h->dec_GB = p.GB;
+    return TACO_OK;
+}
+
+int taco_transpose_alignments(TacoHandle* h, const float* align_hist, int S, int B, int T, float* out, void* stream) {
+    if (!h) return TACO_ERR_INVALID;
+    if (!align_hist || !out || S < 1 || B < 1 || T < 1) FAIL(TACO_ERR_INVALID, "taco_transpose_alignments: bad arguments");
+    CK(cudaSetDevice(h->device));
+    CK(taco_launch_transpose_alignments(align_hist, out, S, B, T, reinterpret_cast<cudaStream_t>(stream)));
+    h->launches++;
+    return TACO_OK;
+}
+
+int taco_postnet(TacoHandle* h, const float* frames, int B, int F, int F_stride, float* decoder_output, float* mel_outputs,
+                 void* stream) {
+    if (!h) return TACO_ERR_INVALID;
+    if (!h->finalized) FAIL(TACO_ERR_STATE, "taco_finalize_weights has not been called");
+    if (!frames || !decoder_output || !mel_outputs || B < 1 || F < 1 || F_stride < F) FAIL(TACO_ERR_INVALID, "taco_postnet: bad arguments");
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    CK(cudaSetDevice(h->device));
+    const TacoHParams& hp = h->hp;
+    const int M = hp.num_mels, PC = hp.postnet_channels + hp.style_embed_depth;
+    const float hi = hp.max_abs_value;
+    const float lo = (hp.symmetric_mels ? -hp.max_abs_value : 0.f) - hp.lower_bound_decay;
+    {
+        size_t n = (size_t)B * F * M;
+        clip_copy_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(frames, decoder_output, B, F, F_stride, M, lo, hi, hp.clip_outputs);
+        CK(cudaGetLastError());
+        h->launches++;
+    }
+    WS(pa, float, "post_a", (size_t)B * F * PC)
+    WS(pb, float, "post_b", (size_t)B * F * PC)
+    const float* cur = decoder_output;
+    float *dst = pa, *other = pb;
+    int cin = M, rc;
+    for (int i = 0; i < hp.postnet_num_layers; ++i) {
+        int act = i < hp.postnet_num_layers - 1 ? ACT_TANH : ACT_NONE;
+        rc = conv(h, cur, cin, (long long)F * cin, dev_w(h, fmt(POST_CONV, i + 1) + "/conv1d/kernel"), h->post_scale[i], h->post_shift[i],
+                  dst, PC, (long long)F * PC, nullptr, B, F, cin, PC, hp.postnet_kernel_size, act, false, 0, 0, st);
+        if (rc) return rc;
+        cur = dst;
+        std::swap(dst, other);
+        cin = PC;
+    }
+    return conv(h, cur, PC, (long long)F * PC, dev_w(h, std::string(POST_PROJ) + "/kernel"), nullptr,
+                dev_w(h, std::string(POST_PROJ) + "/bias"), mel_outputs, M, (long long)F * M, decoder_output, B, F, PC, M, 1, ACT_NONE,
+                hp.clip_outputs != 0, lo, hi, st);
+}
+
+int taco_get_decoder_state(TacoHandle* h, int B, int T, float* c1, float* h1, float* c2, float* h2, float* attention,
+                           float* alignments, void* stream) {
+    if (!h) return TACO_ERR_INVALID;
+    if (h->dec_B != B || h->dec_T != T) FAIL(TACO_ERR_STATE, "taco_get_decoder_state: no decoder state of that shape");
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    CK(cudaSetDevice(h->device));
+    auto it = h->ws.find("dec_exchange");
+    if (it == h->ws.end()) FAIL(TACO_ERR_STATE, "no decoder state");
+    float* ex = reinterpret_cast<float*>(it->second.p);
+    const size_t R = h->dec_RBP, GBs = h->dec_GB;
+    const size_t n_x = GBs * 80 * R, n_256 = GBs * 256 * R, n_768 = GBs * 768 * R;
+    const size_t n_q = (size_t)B * 128, n_cum = (size_t)B * T, n_c = (size_t)B * 256;
+    float* ctxT = ex + n_x + 2 * n_256;
+    float* h1zT = ctxT + n_768;
+    float* h2zT = h1zT + 3 * n_256;
+    float* cum = h2zT + 3 * n_256 + n_q;
+    float* c1s = cum + n_cum;
+    float* c2s = c1s + n_c;
+    const int par = h->dec_t & 1;  // buffer the NEXT step will read
+    const int nb = (B * 768 + 255) / 256;
+    if (c1) CK(cudaMemcpyAsync(c1, c1s, n_c * sizeof(float), cudaMemcpyDeviceToDevice, st));
+    if (c2) CK(cudaMemcpyAsync(c2, c2s, n_c * sizeof(float), cudaMemcpyDeviceToDevice, st));
+    if (alignments) CK(cudaMemcpyAsync(alignments, cum, n_cum * sizeof(float), cudaMemcpyDeviceToDevice, st));
+    if (h1) untranspose_xt_kernel<<<nb, 256, 0, st>>>(h1zT + par * n_256, h1, B, 256, (int)R);
+    if (h2) untranspose_xt_kernel<<<nb, 256, 0, st>>>(h2zT + par * n_256, h2, B, 256, (int)R);
+    if (attention) untranspose_xt_kernel<<<nb, 256, 0, st>>>(ctxT, attention, B, 768, (int)R);
+    CK(cudaGetLastError());
+    return TACO_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,103 @@
+// Internal declarations shared by the .cu translation units of libtaco_b200.so.
+#pragma once
+#include <cuda_runtime.h>
+#include <stddef.h>
+#include <stdint.h>
+
+#include "../../include/taco_b200.h"
+
+// ---------------------------------------------------------------------------------------------
+// decoder.cu
+// ---------------------------------------------------------------------------------------------
+struct DecParams {
+    int B, T, RBP, GB, GN, U, NS;
+    int S_max, S_cap, t0, mode;
+    int stop_at_any, cumulative, smoothing, stop_sigmoid;
+    float zoneout, keep_scale;
+    // resident weights
+    const float* blobs;  // [GN][blob_floats]
+    int blob_floats;
+    const float *Wl, *conv_w, *conv_b, *v_a, *b_a;
+    // encoder memory
+    const float *values, *keys;
+    const int* lens;
+    // exchange buffers (XT layout [GB][K][RBP] unless noted)
+    float *xT, *p1T, *p2T, *ctxT, *h1zT, *h1rawT, *h2zT, *h2rawT;
+    float *q;    // [B][128]
+    float *pre;  // [B][T][128]
+    float *cum;  // [B][T]
+    float *c1, *c2;  // [B][256]
+    // inputs
+    const float* targets;
+    int F_tgt;
+    const uint8_t* masks;
+    uint64_t seed;
+    // outputs
+    float *frames, *stop, *hist;
+    int* steps_out;
+    int* stop_count;  // [S_max], zeroed
+    unsigned* barrier;
+};
+
+int taco_decoder_blob_floats(int U);
+size_t taco_decoder_smem_bytes(int U);
+cudaError_t taco_launch_decoder(const DecParams& p, cudaStream_t stream);
+cudaError_t taco_launch_transpose_alignments(const float* hist, float* out, int S, int B, int T, cudaStream_t stream);
+
+// ---------------------------------------------------------------------------------------------
+// conv.cu : conv1d('same') / dense as implicit GEMM, fused scale/shift + activation epilogue
+// ---------------------------------------------------------------------------------------------
+enum { ACT_NONE = 0, ACT_RELU = 1, ACT_TANH = 2 };
+
+struct ConvParams {
+    const float* x;       // [B][T][Cin]; row stride x_stride (floats) between t, batch stride x_bstride
+    long long x_stride, x_bstride;
+    const float* w;       // [k][Cin][Cout]
+    const float* scale;   // [Cout] or null (=1)
+    const float* shift;   // [Cout] or null (=0)
+    float* y;             // [B][T][Cout]; row stride y_stride, batch stride y_bstride
+    long long y_stride, y_bstride;
+    const float* residual;  // optional [B][T][Cout] dense, added before clip
+    int B, T, Cin, Cout, k, act;
+    int clip;             // clamp to [clip_lo, clip_hi] after residual
+    float clip_lo, clip_hi;
+    float in_clip_lo, in_clip_hi;
+    int in_clip;          // clamp the INPUT while loading (decoder_output clip, Tacotron.py:282-284)
+};
+cudaError_t taco_launch_conv1d_f32(const ConvParams& p, cudaStream_t stream);
+
+// ---------------------------------------------------------------------------------------------
+// encoder.cu
+// ---------------------------------------------------------------------------------------------
+cudaError_t taco_launch_embedding(const int32_t* ids, const float* table, float* out, int n_tok, int dim, int n_symbols,
+                                  cudaStream_t stream);
+struct BiLstmParams {
+    int B, T, RBP, GB, GN, U;  // GN unit tiles per direction; grid = 2 * GB * GN
+    const float* blobs;        // [2][GN][256*4U + 4U]  recurrent kernel shard [256][4U] + zero pad
+    int blob_floats;
+    const float* xw;           // [2][B*T][1024] input projection (+bias), gate order i,j,f,o
+    const int* lens;
+    float* hT;                 // [2 dir][2 parity][GB][256][RBP]
+    float* out;                // [B][T][out_stride]; fw at +0, bw at +256
+    int out_stride;
+    float zoneout;
+    unsigned* barrier;         // [2] one counter per direction
+};
+int taco_bilstm_blob_floats(int U);
+cudaError_t taco_launch_bilstm(const BiLstmParams& p, cudaStream_t stream);
+cudaError_t taco_launch_style_fill(float* memory, const float* style, int B, int T, int style_dim, int mem_dim,
+                                   int style_bstride, cudaStream_t stream);
+
+// ---------------------------------------------------------------------------------------------
+// refenc.cu : reference encoder (conv2d s2 + BN + ReLU stack, GRU, dense tanh) and GST attention
+// ---------------------------------------------------------------------------------------------
+cudaError_t taco_launch_conv2d_s2(const float* x, const float* w, const float* scale, const float* shift, float* y, int B,
+                                  int H, int W, int Cin, int Cout, cudaStream_t stream);
+cudaError_t taco_launch_ref_gru(const float* x, int B, int Tp, int In, const float* Wg, const float* bg, const float* Wc,
+                                const float* bc, const float* Wd, const float* bd, float* ref_out, cudaStream_t stream);
+cudaError_t taco_launch_gst_attention(const float* ref, const float* tokens, const float* Wq, const float* bq,
+                                      const float* Wk, const float* bk, const float* v, const float* g, const float* b,
+                                      float* style, int B, int n_tok, int tok_dim, int heads, int units,
+                                      cudaStream_t stream);
+cudaError_t taco_launch_style_random(const float* gst_weights, const float* tokens, float* style, int heads, int n_tok,
+                                     int tok_dim, cudaStream_t stream);

@@ -1,0 +1,171 @@
+"""Parity of the CUDA path (through the C ABI) against the CPU oracle on identical random-init
+weights and seeded synthetic inputs.  fp32 kernels: tolerances are absolute, stated per test."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import philox
+from oracle.tacotron_oracle import TacotronOracle, output_lengths
+from tacotron_prosody_multi_gpu_b200 import synthetic, weights
+from tacotron_prosody_multi_gpu_b200.hparams import default_hparams
+
+pytestmark = pytest.mark.gpu
+
+ATOL_F32 = 2e-4      # teacher-forced fp32 kernels vs fp32 oracle (rtol 1e-4 / atol 1e-5 per op;
+                     # accumulated over <= 40 recurrent steps)
+ATOL_ALIGN = 2e-5
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    from tacotron_prosody_multi_gpu_b200.engine import TacoEngine
+    hp = default_hparams()
+    w = weights.set_stop_bias(weights.init_weights(hp, perturb=0.05), -10.0)
+    eng = TacoEngine(hp, w)
+    return hp, w, eng, TacotronOracle(hp, w)
+
+
+def _t(a):
+    return a.detach().cpu().numpy()
+
+
+def test_encoder_parity(ctx):
+    hp, w, eng, orc = ctx
+    ids, lens = synthetic.token_batch(hp, [20, 11, 16, 7, 20])
+    gw = synthetic.gst_random_weights(hp)
+    ref = orc.encode(ids, lens, gst_weights=gw).numpy()
+    mem = eng.encode(torch.from_numpy(ids), torch.from_numpy(lens), gst_weights=gw)
+    np.testing.assert_allclose(_t(mem), ref, atol=1e-4)
+    assert float(mem[1, 11:, :512].abs().max()) == 0.0       # zero LSTM output beyond length
+
+
+def test_reference_encoder_gst_parity(ctx):
+    hp, w, eng, orc = ctx
+    ids, lens = synthetic.token_batch(hp, [9, 6])
+    rm = synthetic.reference_mel(hp, 2, 150)
+    ref = orc.encode(ids, lens, reference_mel=rm).numpy()
+    mem = eng.encode(torch.from_numpy(ids), torch.from_numpy(lens), reference_mel=torch.from_numpy(rm))
+    np.testing.assert_allclose(_t(mem)[:, :, 512:], ref[:, :, 512:], atol=5e-5)
+    np.testing.assert_allclose(_t(mem), ref, atol=1e-4)
+
+
+@pytest.mark.parametrize("lengths", [[13], [20, 11, 16], [9] * 6 + [14] * 5, [10, 25] * 10, [12, 30, 7, 22] * 16])
+def test_decoder_teacher_forced_parity(ctx, lengths):
+    """Covers every batch-tile configuration: RBP 4 / 4 / 16 / 32 (U=2) and B=64 (GB=2, U=4)."""
+    hp, w, eng, orc = ctx
+    B = len(lengths)
+    ids, lens = synthetic.token_batch(hp, lengths)
+    T = ids.shape[1]
+    rng = np.random.default_rng(B)
+    memory = (rng.standard_normal((B, T, 768)) * 0.5).astype(np.float32)
+    mel, _, _ = synthetic.mel_targets(hp, lens, frames_per_token=1, max_frames=24)
+    S = mel.shape[1] // 2
+    masks = philox.prenet_masks(11, S, B)
+    with torch.no_grad():
+        ref = orc.decode(torch.from_numpy(memory), lens, mel_targets=mel, prenet_masks=masks)
+    d = eng.decode(torch.from_numpy(memory).cuda(), torch.from_numpy(lens), mel_targets=torch.from_numpy(mel),
+                   prenet_masks=masks)
+    assert d["steps"] == ref["steps"] == S
+    np.testing.assert_allclose(_t(d["frames"]), ref["frames_raw"].numpy(), atol=ATOL_F32)
+    np.testing.assert_allclose(_t(d["stop"]), ref["stop"].numpy(), atol=ATOL_F32)
+    al = _t(eng.alignments(d["align_hist"], S))
+    np.testing.assert_allclose(al, ref["alignments"].numpy(), atol=ATOL_ALIGN)
+    for b, n in enumerate(lens):
+        assert al[b, n:].max(initial=0.0) == 0.0              # exact zeros beyond length (-inf mask)
+    np.testing.assert_allclose(al.sum(1), 1.0, atol=1e-5)
+    st = eng.decoder_state(B, T)
+    fs = ref["final_state"]
+    np.testing.assert_allclose(_t(st["c1"]), fs.c1.numpy(), atol=ATOL_F32)
+    np.testing.assert_allclose(_t(st["h2"]), fs.h2.numpy(), atol=ATOL_F32)
+    np.testing.assert_allclose(_t(st["attention"]), fs.attention.numpy(), atol=ATOL_F32)
+    np.testing.assert_allclose(_t(st["alignments"]), fs.alignments.numpy(), atol=1e-4)
+
+
+def test_philox_in_kernel_equals_explicit_masks(ctx):
+    hp, w, eng, orc = ctx
+    ids, lens = synthetic.token_batch(hp, [10, 8, 12])
+    rng = np.random.default_rng(5)
+    memory = torch.from_numpy((rng.standard_normal((3, 12, 768)) * 0.5).astype(np.float32)).cuda()
+    S = 7
+    a = eng.decode(memory, torch.from_numpy(lens), max_iters=S, philox_seed=0x1234567890)
+    b = eng.decode(memory, torch.from_numpy(lens), max_iters=S, prenet_masks=philox.prenet_masks(0x1234567890, S, 3))
+    assert a["steps"] == b["steps"] == S
+    assert torch.equal(a["frames"], b["frames"]) and torch.equal(a["align_hist"], b["align_hist"])
+
+
+def test_free_running_stop_step_bit_exact(ctx):
+    """Batch-global stop (Helpers.py:51-52): S == first step where any stop prob > 0.5, +1."""
+    hp, _, _, _ = ctx
+    from tacotron_prosody_multi_gpu_b200.engine import TacoEngine
+    base = weights.init_weights(hp, perturb=0.05)
+    ids, lens = synthetic.token_batch(hp, [14, 9, 12, 11])
+    gw = synthetic.gst_random_weights(hp)
+    found = False
+    for bias in (-0.6, -0.45, -0.3, -0.8):
+        w = weights.scale_stop_projection(base, 8.0, bias)
+        orc = TacotronOracle(hp, w)
+        ref = orc.forward(ids, lens, gst_weights=gw, max_iters=40, philox_seed=99)
+        logits = torch.logit(ref["stop"].double().clamp(1e-9, 1 - 1e-9))
+        S = ref["steps"]
+        margin = float(logits[:, : 2 * (S - 1)].abs().min()) if S > 1 else 1.0
+        margin = min(margin, float(logits[:, 2 * (S - 1):].max().abs()))
+        if 3 <= S < 40 and margin >= 0.02:
+            found = True
+            break
+    assert found, "no stop-parity configuration with a safe logit margin"
+    eng = TacoEngine(hp, w)
+    out = eng.forward(torch.from_numpy(ids), torch.from_numpy(lens), gst_weights=gw, max_iters=40, philox_seed=99)
+    assert out["steps"] == S                                               # bit-exact stop step
+    assert out["mel_outputs"].shape == (4, 2 * S, 80) and out["alignments"].shape == (4, 14, S)
+    np.testing.assert_allclose(_t(out["mel_outputs"]), ref["mel_outputs"].numpy(), atol=5e-4)
+    assert output_lengths(_t(out["stop"])) == output_lengths(ref["stop"].numpy())   # bit-exact output lengths
+    eng.close()
+
+
+def test_postnet_parity(ctx):
+    hp, w, eng, orc = ctx
+    rng = np.random.default_rng(3)
+    frames = (rng.standard_normal((3, 38, 80)) * 3.0).astype(np.float32)      # exercises the clip
+    with torch.no_grad():
+        dec_ref = torch.clamp(torch.from_numpy(frames), -4.1, 4.0)
+        mel_ref = orc.postnet(dec_ref).numpy()
+    dec, mel = eng.postnet(torch.from_numpy(frames).cuda(), 38)
+    assert torch.equal(dec.cpu(), dec_ref)
+    np.testing.assert_allclose(_t(mel), mel_ref, atol=2e-4)
+    # F < F_stride: only the first F frames are consumed
+    dec2, mel2 = eng.postnet(torch.from_numpy(frames).cuda(), 20)
+    with torch.no_grad():
+        mel_ref2 = orc.postnet(dec_ref[:, :20]).numpy()
+    np.testing.assert_allclose(_t(mel2), mel_ref2, atol=2e-4)
+
+
+def test_full_forward_c1_like(ctx):
+    """C1-shaped (B=8 teacher-forced / GTA) at a size the oracle finishes in seconds."""
+    hp, w, eng, orc = ctx
+    ids, lens = synthetic.token_batch(hp, synthetic.SENTENCE_LENGTHS[:8])
+    mel, _, _ = synthetic.mel_targets(hp, lens, frames_per_token=1)
+    gw = synthetic.gst_random_weights(hp)
+    ref = orc.forward(ids, lens, mel_targets=mel, gst_weights=gw, philox_seed=hp.tacotron_random_seed)
+    out = eng.forward(torch.from_numpy(ids), torch.from_numpy(lens), mel_targets=torch.from_numpy(mel), gst_weights=gw,
+                      philox_seed=hp.tacotron_random_seed)
+    assert out["steps"] == ref["steps"] == mel.shape[1] // 2
+    np.testing.assert_allclose(_t(out["encoder_outputs"]), ref["encoder_outputs"].numpy(), atol=2e-4)
+    np.testing.assert_allclose(_t(out["decoder_output"]), ref["decoder_output"].numpy(), atol=5e-4)
+    np.testing.assert_allclose(_t(out["mel_outputs"]), ref["mel_outputs"].numpy(), atol=1e-3)
+    np.testing.assert_allclose(_t(out["alignments"]), ref["alignments"].numpy(), atol=5e-5)
+    np.testing.assert_allclose(_t(out["stop"]), ref["stop"].numpy(), atol=5e-4)
+
+
+def test_cell_stepping_matches_one_launch(ctx):
+    """taco_decode(reset_state=0, S_max=1) == `cell(inputs, state)` stepping (Decoder.py:246-292)."""
+    hp, w, eng, orc = ctx
+    ids, lens = synthetic.token_batch(hp, [10, 8])
+    rng = np.random.default_rng(8)
+    memory = torch.from_numpy((rng.standard_normal((2, 10, 768)) * 0.5).astype(np.float32)).cuda()
+    S = 5
+    whole = eng.decode(memory, torch.from_numpy(lens), max_iters=S, philox_seed=3)
+    frames = []
+    for t in range(S):
+        d = eng.decode(memory, torch.from_numpy(lens), max_iters=1, philox_seed=3, reset_state=(t == 0))
+        frames.append(d["frames"].clone())
+    assert torch.equal(torch.cat(frames, 1), whole["frames"])
