@@ -131,6 +131,12 @@ int taco_postnet(TacoHandle* h, const float* frames, int B, int F, int F_stride,
 /* Number of kernels launched by this handle since creation (bench.py's gpu_launches). */
 int64_t taco_launch_count(const TacoHandle* h);
 
+/* Device time of the most recent run of a stage, from CUDA events recorded on the caller's stream
+ * around it (blocks until the stage has finished).  TACO_STAGE_DECODER_KERNEL brackets only the
+ * persistent decoder kernel launch -- the figure bench.py's roofline uses. */
+enum { TACO_STAGE_ENCODE = 0, TACO_STAGE_DECODER_KERNEL = 1, TACO_STAGE_POSTNET = 2, TACO_N_STAGES = 3 };
+int taco_stage_ms(TacoHandle* h, int stage, float* ms_out);
+
 /* Decoder recurrent state kept in the handle (TacotronDecoderCellState, Decoder.py:419-438):
  * copies c1,h1,c2,h2 [B,256], attention [B,768], alignments (cumulative) [B,T] out to / in from
  * caller DEVICE buffers.  Any pointer may be NULL to skip that field. */

@@ -13,6 +13,7 @@ TACO_MODE_FREE = 0
 TACO_MODE_TEACHER = 1
 TACO_PRECISION_FP32 = 0
 TACO_PRECISION_BF16_CONV = 1
+TACO_STAGE_ENCODE, TACO_STAGE_DECODER_KERNEL, TACO_STAGE_POSTNET = 0, 1, 2
 
 ERROR_NAMES = {-1: "TACO_ERR_INVALID", -2: "TACO_ERR_UNSUPPORTED", -3: "TACO_ERR_CUDA",
                -4: "TACO_ERR_MISSING_WEIGHT", -5: "TACO_ERR_STATE"}
@@ -22,6 +23,7 @@ EXPORTED_SYMBOLS = [
     "taco_create", "taco_destroy", "taco_last_error", "taco_version", "taco_set_weight",
     "taco_finalize_weights", "taco_set_precision", "taco_encode", "taco_decode",
     "taco_transpose_alignments", "taco_postnet", "taco_launch_count", "taco_get_decoder_state",
+    "taco_stage_ms",
 ]
 
 
@@ -86,6 +88,8 @@ def lib():
     L.taco_launch_count.restype = i64
     L.taco_get_decoder_state.argtypes = [vp, i32, i32, vp, vp, vp, vp, vp, vp, vp]
     L.taco_get_decoder_state.restype = i32
+    L.taco_stage_ms.argtypes = [vp, i32, C.POINTER(C.c_float)]
+    L.taco_stage_ms.restype = i32
     _lib = L
     return L
 

@@ -66,6 +66,9 @@ struct TacoHandle {
     float* bilstm_blob[2] = {};  // same two configs, [2 dir][GN][256*4U]
     // decoder running state
     int dec_t = 0, dec_B = 0, dec_T = 0, dec_RBP = 0, dec_GB = 0;
+    // CUDA events bracketing each stage on the caller's stream (taco_stage_ms)
+    cudaEvent_t ev[TACO_N_STAGES][2] = {};
+    bool ev_valid[TACO_N_STAGES] = {};
 };
 
 namespace {
@@ -338,6 +341,8 @@ int taco_create(const TacoHParams* hp, int device, TacoHandle** out) {
     if (prop.major < 10) FAIL(TACO_ERR_UNSUPPORTED, "sm_100a device required (no fallback path)");
     if (!prop.cooperativeLaunch) FAIL(TACO_ERR_UNSUPPORTED, "cooperative launch unsupported");
     if (h->n_sm < 128) FAIL(TACO_ERR_UNSUPPORTED, "persistent decoder needs >= 128 SMs");
+    for (int i = 0; i < TACO_N_STAGES; ++i)
+        for (int j = 0; j < 2; ++j) CK(cudaEventCreate(&h->ev[i][j]));
     return TACO_OK;
 }
 
@@ -350,6 +355,9 @@ void taco_destroy(TacoHandle* h) {
     for (auto& kv : h->ws)
         if (kv.second.p) cudaFree(kv.second.p);
     for (void* p : h->owned) cudaFree(p);
+    for (int i = 0; i < TACO_N_STAGES; ++i)
+        for (int j = 0; j < 2; ++j)
+            if (h->ev[i][j]) cudaEventDestroy(h->ev[i][j]);
     delete h;
 }
 
@@ -437,6 +445,7 @@ int taco_encode(TacoHandle* h, const int32_t* ids, const int32_t* lens, int B, i
     const int E = hp.embedding_dim, C = hp.conv_channels, H = hp.enc_lstm_hidden_size, SD = hp.style_embed_depth;
     const int MD = 2 * H + SD;
     const size_t M = (size_t)B * T;
+    CK(cudaEventRecord(h->ev[TACO_STAGE_ENCODE][0], st));
     WS(bufA, float, "enc_a", M * 512)
     WS(bufB, float, "enc_b", M * 512)
     WS(xw, float, "enc_xw", 2 * M * 1024)
@@ -536,6 +545,8 @@ int taco_encode(TacoHandle* h, const int32_t* ids, const int32_t* lens, int B, i
         CK(taco_launch_style_fill(memory_out, style, B, T, SD, MD, 0, st));
     }
     h->launches++;
+    CK(cudaEventRecord(h->ev[TACO_STAGE_ENCODE][1], st));
+    h->ev_valid[TACO_STAGE_ENCODE] = true;
     return TACO_OK;
 }
 
@@ -635,7 +646,10 @@ int taco_decode(TacoHandle* h, int mode, const float* memory, const int32_t* len
     CK(cudaMemsetAsync(cnt, 0, ((size_t)S_max + 8) * sizeof(int), st));
     p.stop_count = cnt;
     p.barrier = reinterpret_cast<unsigned*>(cnt + S_max + 4);
+    CK(cudaEventRecord(h->ev[TACO_STAGE_DECODER_KERNEL][0], st));
     CK(taco_launch_decoder(p, st));
+    CK(cudaEventRecord(h->ev[TACO_STAGE_DECODER_KERNEL][1], st));
+    h->ev_valid[TACO_STAGE_DECODER_KERNEL] = true;
     h->launches++;
     h->dec_t += S_max;  // exact for S_max == 1 (cell stepping) and for runs to completion
     h->dec_B = B; h->dec_T = T; h->dec_RBP = p.RBP; h->dec_GB = p.GB;
@@ -662,6 +676,7 @@ int taco_postnet(TacoHandle* h, const float* frames, int B, int F, int F_stride,
     const int M = hp.num_mels, PC = hp.postnet_channels + hp.style_embed_depth;
     const float hi = hp.max_abs_value;
     const float lo = (hp.symmetric_mels ? -hp.max_abs_value : 0.f) - hp.lower_bound_decay;
+    CK(cudaEventRecord(h->ev[TACO_STAGE_POSTNET][0], st));
     {
         size_t n = (size_t)B * F * M;
         clip_copy_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(frames, decoder_output, B, F, F_stride, M, lo, hi, hp.clip_outputs);
@@ -682,9 +697,22 @@ int taco_postnet(TacoHandle* h, const float* frames, int B, int F, int F_stride,
         std::swap(dst, other);
         cin = PC;
     }
-    return conv(h, cur, PC, (long long)F * PC, dev_w(h, std::string(POST_PROJ) + "/kernel"), nullptr,
-                dev_w(h, std::string(POST_PROJ) + "/bias"), mel_outputs, M, (long long)F * M, decoder_output, B, F, PC, M, 1, ACT_NONE,
-                hp.clip_outputs != 0, lo, hi, st);
+    rc = conv(h, cur, PC, (long long)F * PC, dev_w(h, std::string(POST_PROJ) + "/kernel"), nullptr,
+              dev_w(h, std::string(POST_PROJ) + "/bias"), mel_outputs, M, (long long)F * M, decoder_output, B, F, PC, M, 1, ACT_NONE,
+              hp.clip_outputs != 0, lo, hi, st);
+    if (rc) return rc;
+    CK(cudaEventRecord(h->ev[TACO_STAGE_POSTNET][1], st));
+    h->ev_valid[TACO_STAGE_POSTNET] = true;
+    return TACO_OK;
+}
+
+int taco_stage_ms(TacoHandle* h, int stage, float* ms_out) {
+    if (!h || !ms_out || stage < 0 || stage >= TACO_N_STAGES) return TACO_ERR_INVALID;
+    if (!h->ev_valid[stage]) FAIL(TACO_ERR_STATE, "taco_stage_ms: stage has not run");
+    CK(cudaSetDevice(h->device));
+    CK(cudaEventSynchronize(h->ev[stage][1]));
+    CK(cudaEventElapsedTime(ms_out, h->ev[stage][0], h->ev[stage][1]));
+    return TACO_OK;
 }
 
 int taco_get_decoder_state(TacoHandle* h, int B, int T, float* c1, float* h1, float* c2, float* h2, float* attention,

@@ -82,6 +82,12 @@ class TacoEngine(object):
     def launch_count(self):
         return int(self.L.taco_launch_count(self._h))
 
+    def stage_ms(self, stage):
+        """Device milliseconds of the last run of a stage (CUDA events inside the library)."""
+        ms = C.c_float()
+        self._check(self.L.taco_stage_ms(self._h, int(stage), C.byref(ms)), "taco_stage_ms")
+        return float(ms.value)
+
     # ------------------------------------------------------------------ path stages
     def encode(self, ids, lens, reference_mel=None, gst_weights=None):
         """-> memory [B, T, 768] (= ``encoder_outputs``, Tacotron.py:224)."""
@@ -186,3 +192,51 @@ class TacoEngine(object):
         dec, mel = self.postnet(d["frames"], S * r)
         return dict(encoder_outputs=memory, decoder_output=dec, mel_outputs=mel, stop=d["stop"][:, : S * r],
                     alignments=self.alignments(d["align_hist"], S), steps=S, frames_raw=d["frames"][:, : S * r])
+
+    # ------------------------------------------------------------------ host-buffer entry (the e2e path)
+    def _pinned(self, key, shape, dtype):
+        cache = self.__dict__.setdefault("_pin_cache", {})
+        t = cache.get(key)
+        n = int(np.prod(shape)) if len(shape) else 1
+        if t is None or t.dtype != dtype or t.numel() < n:
+            t = torch.empty(max(n, 1), dtype=dtype, pin_memory=True)
+            cache[key] = t
+        return t[:n].view(*shape)
+
+    def _h2d(self, key, arr, dtype):
+        a = np.ascontiguousarray(arr)
+        p = self._pinned(key, a.shape, dtype)
+        p.copy_(torch.from_numpy(a).to(dtype))
+        return p.to(self.device, non_blocking=True), p.numel() * p.element_size()
+
+    def forward_host(self, ids, lens, mel_targets=None, reference_mel=None, gst_weights=None, max_iters=None,
+                     prenet_masks=None, philox_seed=0, fetch=("mel_outputs", "alignments", "stop")):
+        """``forward`` on HOST numpy arrays: inputs staged through pinned memory and copied host->device,
+        the tensors the reference's ``session.run`` fetches (Tacotron_synthesizer.py:110: mel_outputs,
+        alignments, stop tokens) copied device->host into pinned buffers.  Returns numpy views + byte counts."""
+        h2d = 0
+        ids_d, n = self._h2d("ids", ids, torch.int32); h2d += n
+        lens_d, n = self._h2d("lens", lens, torch.int32); h2d += n
+        tgt_d = ref_d = gw_d = None
+        if mel_targets is not None:
+            tgt_d, n = self._h2d("tgt", mel_targets, torch.float32); h2d += n
+        if reference_mel is not None:
+            ref_d, n = self._h2d("ref", reference_mel, torch.float32); h2d += n
+        elif gst_weights is not None:
+            gw_d, n = self._h2d("gw", gst_weights, torch.float32); h2d += n
+        if prenet_masks is not None:
+            prenet_masks, n = self._h2d("masks", prenet_masks, torch.uint8); h2d += n
+        out = self.forward(ids_d, lens_d, tgt_d, ref_d, gw_d, max_iters, prenet_masks, philox_seed)
+        res = {"steps": out["steps"]}
+        d2h = 4  # the int32 step count read back by forward()
+        for k in fetch:
+            t = out[k].contiguous()
+            p = self._pinned("out_" + k, tuple(t.shape), t.dtype)
+            p.copy_(t, non_blocking=True)
+            d2h += t.numel() * t.element_size()
+            res[k] = p
+        torch.cuda.current_stream(self.device).synchronize()
+        for k in fetch:
+            res[k] = res[k].numpy()
+        res["h2d_bytes"], res["d2h_bytes"] = h2d, d2h
+        return res

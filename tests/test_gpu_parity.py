@@ -16,6 +16,27 @@ ATOL_F32 = 2e-4      # teacher-forced fp32 kernels vs fp32 oracle (SURVEY §8c: 
 ATOL_ALIGN = 2e-5
 
 
+def pick_stop_bias(hp, base, ids, lens, gw, max_iters, philox_seed, scale=8.0):
+    """Stop-parity config: the stop bias only shifts the logits (free-running feedback does
+    not read them), so run the oracle once without stopping, then place the bias in the widest gap
+    between the running max of the pre-stop logits and the logit that crosses.  Returns
+    (weights, S, |logit| margin on every decision up to and including the stop step)."""
+    w0 = weights.scale_stop_projection(base, scale, -30.0)
+    ref = TacotronOracle(hp, w0).forward(ids, lens, gst_weights=gw, max_iters=max_iters, philox_seed=philox_seed)
+    assert ref["steps"] == max_iters
+    logit = torch.logit(ref["stop"].double().clamp(1e-300, 1.0)) + 30.0        # [B, 2S]
+    m = logit.reshape(logit.shape[0], max_iters, -1).amax(dim=(0, 2)).numpy()    # per-step max over batch, r
+    best = None
+    run = m[0]
+    for s in range(1, max_iters - 1):
+        if s >= 3 and m[s] > run and (best is None or m[s] - run > best[0]):
+            best = (m[s] - run, s, -(m[s] + run) / 2.0)
+        run = max(run, m[s])
+    assert best is not None
+    gap, s, bias = best
+    return weights.scale_stop_projection(base, scale, float(bias)), s + 1, gap / 2.0
+
+
 @pytest.fixture(scope="module")
 def ctx():
     from tacotron_prosody_multi_gpu_b200.engine import TacoEngine
@@ -100,19 +121,10 @@ def test_free_running_stop_step_bit_exact(ctx):
     base = weights.init_weights(hp, perturb=0.05)
     ids, lens = synthetic.token_batch(hp, [14, 9, 12, 11])
     gw = synthetic.gst_random_weights(hp)
-    found = False
-    for bias in (-0.6, -0.45, -0.3, -0.8):
-        w = weights.scale_stop_projection(base, 8.0, bias)
-        orc = TacotronOracle(hp, w)
-        ref = orc.forward(ids, lens, gst_weights=gw, max_iters=40, philox_seed=99)
-        logits = torch.logit(ref["stop"].double().clamp(1e-9, 1 - 1e-9))
-        S = ref["steps"]
-        margin = float(logits[:, : 2 * (S - 1)].abs().min()) if S > 1 else 1.0
-        margin = min(margin, float(logits[:, 2 * (S - 1):].max().abs()))
-        if 3 <= S < 40 and margin >= 0.02:
-            found = True
-            break
-    assert found, "no stop-parity configuration with a safe logit margin"
+    w, S, margin = pick_stop_bias(hp, base, ids, lens, gw, max_iters=40, philox_seed=99)
+    assert 3 <= S < 40 and margin >= 0.01, (S, margin)
+    ref = TacotronOracle(hp, w).forward(ids, lens, gst_weights=gw, max_iters=40, philox_seed=99)
+    assert ref["steps"] == S
     eng = TacoEngine(hp, w)
     out = eng.forward(torch.from_numpy(ids), torch.from_numpy(lens), gst_weights=gw, max_iters=40, philox_seed=99)
     assert out["steps"] == S                                               # bit-exact stop step
