@@ -198,7 +198,7 @@ def run_b200(args):
 
     hp = default_hparams()
     w = weights.set_stop_bias(weights.init_weights(hp, perturb=0.05), -10.0)
-    eng = TacoEngine(hp, w, device=local_rank)
+    eng = TacoEngine(hp, w, device=local_rank, precision=args.precision)
     ids, lens, gw = workload(hp, rank)
     B, T = ids.shape
     S = args.decoder_steps
@@ -284,7 +284,10 @@ def run_b200(args):
     line = {
         "metric": METRIC, "value": world * frames_per_step * args.steps / (ms_total * 1e-3), "unit": UNIT,
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_total / args.steps,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "bf16" if args.precision == "bf16" else "f32", "data": "synthetic",
+        "precision": ("bf16 operands + fp32 accumulation (tcgen05) in the postnet contractions; decoder, attention, "
+                      "softmax, recurrent state and all outputs fp32") if args.precision == "bf16" else "fp32 everywhere",
         "config": {"workload": "C2 free-running inference, B=64/GPU, sentences.txt token lengths x4 (T=111), "
                                "S=%d decoder steps (max_iters, stop bias -10), r=2, random-init seed 45454" % S,
                    "batch_per_gpu": B, "T": T, "decoder_steps": S, "frames_counted": "all B*2S frames (no stop fires)",
@@ -323,6 +326,8 @@ def main():
     ap.add_argument("--ref-steps", type=int, default=0, help="--impl reference: decoder steps per pass (0 = auto)")
     ap.add_argument("--ref-budget-s", type=float, default=240.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"],
+                    help="bf16: tensor-core (tcgen05) contractions with bf16 operands, fp32 accumulate; fp32: SIMT everywhere")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "b200":
         args.warmup = 3

@@ -62,6 +62,11 @@ struct TacoHandle {
     float *post_scale[8] = {}, *post_shift[8] = {};
     float *ref_scale[8] = {}, *ref_shift[8] = {};
     // packed resident shards
+    // tensor-core operands: bf16 K-major [Cout][taps*Cin_pad] (conv_tc.cu)
+    void* post_wt[8] = {};
+    int post_cin_pad[8] = {};
+    void* post_proj_wt = nullptr;
+    void* enc_wt[8] = {};
     float* dec_blob[2] = {};     // U = 2 (GN 128), U = 4 (GN 64)
     float* bilstm_blob[2] = {};  // same two configs, [2 dir][GN][256*4U]
     // decoder running state
@@ -125,6 +130,30 @@ int upload(TacoHandle* h, const std::vector<float>& v, float** out) {
     CK(cudaMemcpy(d, v.data(), v.size() * sizeof(float), cudaMemcpyHostToDevice));
     h->owned.push_back(d);
     *out = reinterpret_cast<float*>(d);
+    return TACO_OK;
+}
+
+uint16_t f32_to_bf16_rne(float f) {
+    uint32_t u;
+    memcpy(&u, &f, 4);
+    if ((u & 0x7FFFFFFFu) > 0x7F800000u) return (uint16_t)((u >> 16) | 0x40);  // NaN
+    u += 0x7FFFu + ((u >> 16) & 1u);
+    return (uint16_t)(u >> 16);
+}
+
+// TF conv1d kernel [k][Cin][Cout] fp32 -> K-major bf16 [Cout][k*Cin_pad] (zero-padded channels)
+int pack_conv_bf16(TacoHandle* h, const Weight* w, int k, int cin, int cin_pad, int cout, void** out) {
+    std::vector<uint16_t> t((size_t)cout * k * cin_pad, 0);
+    for (int tap = 0; tap < k; ++tap)
+        for (int ci = 0; ci < cin; ++ci) {
+            const float* src = w->host.data() + ((size_t)tap * cin + ci) * cout;
+            for (int co = 0; co < cout; ++co) t[(size_t)co * k * cin_pad + (size_t)tap * cin_pad + ci] = f32_to_bf16_rne(src[co]);
+        }
+    void* d;
+    CK(cudaMalloc(&d, t.size() * 2));
+    CK(cudaMemcpy(d, t.data(), t.size() * 2, cudaMemcpyHostToDevice));
+    h->owned.push_back(d);
+    *out = d;
     return TACO_OK;
 }
 
@@ -368,7 +397,10 @@ int64_t taco_launch_count(const TacoHandle* h) { return h ? h->launches : 0; }
 int taco_set_precision(TacoHandle* h, int precision) {
     if (!h) return TACO_ERR_INVALID;
     if (precision != TACO_PRECISION_FP32 && precision != TACO_PRECISION_BF16_CONV) FAIL(TACO_ERR_INVALID, "bad precision");
-    if (precision == TACO_PRECISION_BF16_CONV) FAIL(TACO_ERR_UNSUPPORTED, "tcgen05 conv path not built into this library");
+    if (precision == TACO_PRECISION_BF16_CONV) {
+        const int PC = h->hp.postnet_channels + h->hp.style_embed_depth;
+        if (PC % 256 != 0 || h->hp.num_mels != 80) FAIL(TACO_ERR_UNSUPPORTED, "tcgen05 postnet needs a channel width multiple of 256 and 80 mels");
+    }
     h->precision = precision;
     return TACO_OK;
 }
@@ -428,6 +460,29 @@ int taco_finalize_weights(TacoHandle* h) {
         if (!find_w(h, fmt(POST_CONV, i + 1) + "/conv1d/kernel")) FAIL(TACO_ERR_MISSING_WEIGHT, "missing postnet conv kernel");
     for (int i = 0; i < h->hp.n_reference_filters; ++i)
         if (!find_w(h, fmt(REF_CONV, i) + "/conv2d/kernel")) FAIL(TACO_ERR_MISSING_WEIGHT, "missing reference conv2d kernel");
+    {
+        const TacoHParams& hp = h->hp;
+        const int PC = hp.postnet_channels + hp.style_embed_depth;
+        int cin = hp.num_mels;
+        for (int i = 0; i < hp.postnet_num_layers; ++i) {
+            const Weight* w = find_w(h, fmt(POST_CONV, i + 1) + "/conv1d/kernel");
+            const int cpad = (cin + 63) / 64 * 64;
+            if ((int64_t)w->shape[0] != hp.postnet_kernel_size || (int64_t)w->shape[1] != cin || (int64_t)w->shape[2] != PC)
+                FAIL(TACO_ERR_INVALID, "postnet conv kernel shape");
+            h->post_cin_pad[i] = cpad;
+            if ((rc = pack_conv_bf16(h, w, hp.postnet_kernel_size, cin, cpad, PC, &h->post_wt[i]))) return rc;
+            cin = PC;
+        }
+        const Weight* wp = find_w(h, std::string(POST_PROJ) + "/kernel");
+        if ((int64_t)wp->shape[0] != PC || (int64_t)wp->shape[1] != hp.num_mels) FAIL(TACO_ERR_INVALID, "postnet projection shape");
+        if ((rc = pack_conv_bf16(h, wp, 1, PC, PC, hp.num_mels, &h->post_proj_wt))) return rc;
+        cin = hp.embedding_dim;
+        for (int i = 0; i < hp.conv_num_layers; ++i) {
+            const Weight* w = find_w(h, fmt(ENC_CONV, i + 1) + "/conv1d/kernel");
+            if ((rc = pack_conv_bf16(h, w, hp.conv_kernel_size, cin, cin, hp.conv_channels, &h->enc_wt[i]))) return rc;
+            cin = hp.conv_channels;
+        }
+    }
     h->finalized = true;
     return TACO_OK;
 }
@@ -677,6 +732,41 @@ int taco_postnet(TacoHandle* h, const float* frames, int B, int F, int F_stride,
     const float hi = hp.max_abs_value;
     const float lo = (hp.symmetric_mels ? -hp.max_abs_value : 0.f) - hp.lower_bound_decay;
     CK(cudaEventRecord(h->ev[TACO_STAGE_POSTNET][0], st));
+    if (h->precision == TACO_PRECISION_BF16_CONV) {
+        // tcgen05 path: bf16 operands, fp32 accumulation; activations stay bf16 between layers
+        const int C0 = h->post_cin_pad[0];
+        const size_t wide = (size_t)(PC > C0 ? PC : C0);
+        WS(ta, uint16_t, "post_tc_a", (size_t)B * F * wide)
+        WS(tb, uint16_t, "post_tc_b", (size_t)B * F * wide)
+        CK(taco_launch_prep_bf16(frames, decoder_output, ta, B, F, (long long)F_stride * M, M, C0, lo, hi, hp.clip_outputs, st));
+        h->launches++;
+        uint16_t *cur = ta, *nxt = tb;
+        for (int i = 0; i < hp.postnet_num_layers; ++i) {
+            ConvTcParams c;
+            memset(&c, 0, sizeof c);
+            c.x = cur; c.wt = h->post_wt[i];
+            c.B = B; c.F = F; c.Cin = h->post_cin_pad[i]; c.taps = hp.postnet_kernel_size; c.Cout = PC;
+            c.scale = h->post_scale[i]; c.shift = h->post_shift[i];
+            c.act = i < hp.postnet_num_layers - 1 ? ACT_TANH : ACT_NONE;
+            c.y_bf16 = nxt; c.y_stride = PC;
+            CK(taco_launch_conv_tc(c, h->n_sm, st));
+            h->launches++;
+            std::swap(cur, nxt);
+        }
+        ConvTcParams c;
+        memset(&c, 0, sizeof c);
+        c.x = cur; c.wt = h->post_proj_wt;
+        c.B = B; c.F = F; c.Cin = PC; c.taps = 1; c.Cout = M;
+        c.shift = dev_w(h, std::string(POST_PROJ) + "/bias");
+        c.act = ACT_NONE;
+        c.y_f32 = mel_outputs; c.out_f32_only = 1; c.residual = decoder_output;
+        c.clip = hp.clip_outputs != 0; c.clip_lo = lo; c.clip_hi = hi;
+        CK(taco_launch_conv_tc(c, h->n_sm, st));
+        h->launches++;
+        CK(cudaEventRecord(h->ev[TACO_STAGE_POSTNET][1], st));
+        h->ev_valid[TACO_STAGE_POSTNET] = true;
+        return TACO_OK;
+    }
     {
         size_t n = (size_t)B * F * M;
         clip_copy_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(frames, decoder_output, B, F, F_stride, M, lo, hi, hp.clip_outputs);

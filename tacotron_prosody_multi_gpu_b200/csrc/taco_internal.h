@@ -67,6 +67,28 @@ struct ConvParams {
 cudaError_t taco_launch_conv1d_f32(const ConvParams& p, cudaStream_t stream);
 
 // ---------------------------------------------------------------------------------------------
+// conv_tc.cu : tcgen05 / TMEM / TMA implicit-GEMM conv1d('same') / dense, bf16 operands
+// ---------------------------------------------------------------------------------------------
+struct ConvTcParams {
+    const void* x;        // bf16 [B][F][Cin], Cin multiple of 64 (channel-padded)
+    const void* wt;       // bf16 [Cout][taps*Cin]  (K-major, pre-transposed at load time)
+    int B, F, Cin, taps, Cout;
+    const float* scale;   // [Cout] or null
+    const float* shift;   // [Cout] or null
+    int act;
+    void* y_bf16;         // bf16 [B][F][y_stride] (ignored when out_f32_only)
+    int y_stride;
+    float* y_f32;         // optional fp32 copy [B][F][Cout]; the only output when out_f32_only
+    int out_f32_only;     // dense + residual + clip epilogue, Cout in {80, 128}
+    const float* residual;
+    int clip;
+    float clip_lo, clip_hi;
+};
+cudaError_t taco_launch_conv_tc(const ConvTcParams& p, int n_sm, cudaStream_t stream);
+cudaError_t taco_launch_prep_bf16(const float* in, float* out32, void* out16, int B, int F, long long in_bstride, int C,
+                                  int Cpad, float lo, float hi, int clip, cudaStream_t stream);
+
+// ---------------------------------------------------------------------------------------------
 // encoder.cu
 // ---------------------------------------------------------------------------------------------
 cudaError_t taco_launch_embedding(const int32_t* ids, const float* table, float* out, int n_tok, int dim, int n_symbols,

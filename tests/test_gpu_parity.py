@@ -181,3 +181,34 @@ def test_cell_stepping_matches_one_launch(ctx):
         d = eng.decode(memory, torch.from_numpy(lens), max_iters=1, philox_seed=3, reset_state=(t == 0))
         frames.append(d["frames"].clone())
     assert torch.equal(torch.cat(frames, 1), whole["frames"])
+
+
+# ------------------------------------------------------------------ tcgen05 (bf16 operand) conv path
+ATOL_TC_MIRROR = 1.2e-2  # tcgen05 kernels vs the oracle with the SAME bf16 operand rounding (conv_bf16=True):
+                        # differences are fp32 accumulation order + bf16 re-rounding of near-tie activations
+ATOL_TC_FP32 = 6e-2     # vs the fp32 oracle: bf16 operand rounding through 6 stacked contractions (K = 3840)
+
+
+@pytest.mark.parametrize("B,F", [(3, 38), (2, 300), (5, 128)])
+def test_postnet_tcgen05_parity(ctx, B, F):
+    hp, w, _, orc = ctx
+    from tacotron_prosody_multi_gpu_b200.engine import TacoEngine
+    eng = TacoEngine(hp, w, precision="bf16")
+    rng = np.random.default_rng(3 + F)
+    frames = (rng.standard_normal((B, F + 6, 80)) * 3.0).astype(np.float32)
+    with torch.no_grad():
+        dec_ref = torch.clamp(torch.from_numpy(frames[:, :F]), -4.1, 4.0)
+        mel_mirror = TacotronOracle(hp, w, conv_bf16=True).postnet(dec_ref).numpy()
+        mel_fp32 = orc.postnet(dec_ref).numpy()
+    dec, mel = eng.postnet(torch.from_numpy(frames).cuda(), F)
+    assert torch.equal(dec.cpu(), dec_ref)
+    e_mirror = float(np.abs(_t(mel) - mel_mirror).max())
+    e_fp32 = float(np.abs(_t(mel) - mel_fp32).max())
+    e_round = float(np.abs(mel_mirror - mel_fp32).max())
+    print("tcgen05 postnet B=%d F=%d: |gpu-mirror|=%.2e |gpu-fp32|=%.2e |mirror-fp32|=%.2e rms(gpu-mirror)=%.2e" % (
+        B, F, e_mirror, e_fp32, e_round, float(np.sqrt(np.mean((_t(mel) - mel_mirror) ** 2)))))
+    np.testing.assert_allclose(_t(mel), mel_mirror, atol=ATOL_TC_MIRROR)
+    np.testing.assert_allclose(_t(mel), mel_fp32, atol=ATOL_TC_FP32)
+    # the kernel is closer to the bf16-rounding oracle than that oracle is to the fp32 one
+    assert e_mirror < e_round
+    eng.close()
