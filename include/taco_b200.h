@@ -34,7 +34,7 @@ enum {
 
 enum { TACO_MODE_FREE = 0, TACO_MODE_TEACHER = 1 };
 enum { TACO_DTYPE_F32 = 0 };
-enum { TACO_PRECISION_FP32 = 0, TACO_PRECISION_BF16_CONV = 1 };
+enum { TACO_PRECISION_FP32 = 0, TACO_PRECISION_BF16_CONV = 1, TACO_PRECISION_BF16 = 2 };
 
 /* Subset of Utils/Hyperparams.py:4-239 that shapes the path (network dims :43-63, GST :7-14,
  * run params :157-172).  Field names follow the reference. */
@@ -90,7 +90,10 @@ int taco_set_weight(TacoHandle* h, const char* name, const void* data, const int
 /* Folds BN, packs the per-CTA resident decoder shards; errors if a variable is missing. */
 int taco_finalize_weights(TacoHandle* h);
 /* TACO_PRECISION_FP32: fp32 SIMT everywhere.  TACO_PRECISION_BF16_CONV: encoder-conv / postnet
- * contractions on tcgen05 tensor cores with bf16 operands, fp32 accumulation. */
+ * contractions on tcgen05 tensor cores with bf16 operands, fp32 accumulation.
+ * TACO_PRECISION_BF16: additionally the decoder step's contractions (prenet, LSTM gates, query,
+ * frame/stop projection) run on tensor cores with bf16 operands and the attention values are
+ * streamed as bf16 (dataflow persistent kernel); recurrent state, softmax, outputs stay fp32. */
 int taco_set_precision(TacoHandle* h, int precision);
 
 /* Embedding -> EncoderConvolution -> EncoderLSTM -> (reference encoder -> GST | random-weight
@@ -136,6 +139,11 @@ int64_t taco_launch_count(const TacoHandle* h);
  * persistent decoder kernel launch -- the figure bench.py's roofline uses. */
 enum { TACO_STAGE_ENCODE = 0, TACO_STAGE_DECODER_KERNEL = 1, TACO_STAGE_POSTNET = 2, TACO_N_STAGES = 3 };
 int taco_stage_ms(TacoHandle* h, int stage, float* ms_out);
+
+/* Diagnostics: copies a named internal workspace buffer to HOST memory (synchronises the device).
+ * Used by the profiling scripts (e.g. "dec2_timing": per-CTA per-stage nanoseconds of the dataflow
+ * decoder when the environment variable TACO_DEC2_TIMING is set). */
+int taco_debug_read_workspace(TacoHandle* h, const char* name, void* host_dst, size_t bytes);
 
 /* Decoder recurrent state kept in the handle (TacotronDecoderCellState, Decoder.py:419-438):
  * copies c1,h1,c2,h2 [B,256], attention [B,768], alignments (cumulative) [B,T] out to / in from

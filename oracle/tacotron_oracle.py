@@ -55,12 +55,16 @@ def _round_bf16(x):
 class TacotronOracle(object):
     """Module-for-module restatement of ``Tacotron.initialize`` (Tacotron.py:46-349)."""
 
-    def __init__(self, hp, weights, dtype=torch.float32, conv_bf16=False):
+    def __init__(self, hp, weights, dtype=torch.float32, conv_bf16=False, dec_bf16=False):
         """``conv_bf16``: round conv/dense GEMM operands of the encoder-conv / postnet stacks to
-        bf16 (fp32 accumulate), mirroring the tensor-core kernels' operand precision."""
+        bf16 (fp32 accumulate), mirroring the tensor-core kernels' operand precision.
+        ``dec_bf16``: same for the decoder step's contractions (prenet, both LSTM layers, query
+        layer, frame/stop projection) and the attention values of the context reduction; recurrent
+        state, gate non-linearities, energies, softmax and cumulative alignments stay fp32."""
         self.hp = hp
         self.dtype = dtype
         self.conv_bf16 = conv_bf16
+        self.dec_bf16 = dec_bf16
         self.w = {k: torch.from_numpy(np.asarray(v, np.float32)).to(dtype) for k, v in weights.items()}
 
     # ------------------------------------------------------------------ primitives
@@ -103,19 +107,28 @@ class TacotronOracle(object):
             y = y * drop_mask.to(y.dtype) / keep
         return y
 
+    def _dmm(self, x, w):
+        """Decoder contraction; operands rounded to bf16 in the ``dec_bf16`` mirror mode."""
+        if self.dec_bf16:
+            return _round_bf16(x) @ _round_bf16(w)
+        return x @ w
+
     @staticmethod
-    def lstm_cell(x, c, h, kernel, bias):
+    def lstm_cell(x, c, h, kernel, bias, round_ops=False):
         """tf.nn.rnn_cell.LSTMCell (Encoder.py:104; App. A.1): gates i,j,f,o; forget_bias 1.0."""
-        z = torch.cat([x, h], dim=1) @ kernel + bias
+        xh = torch.cat([x, h], dim=1)
+        if round_ops:
+            xh, kernel = _round_bf16(xh), _round_bf16(kernel)
+        z = xh @ kernel + bias
         i, j, f, o = torch.chunk(z, 4, dim=1)
         new_c = torch.sigmoid(f + 1.0) * c + torch.sigmoid(i) * torch.tanh(j)
         new_h = torch.sigmoid(o) * torch.tanh(new_c)
         return new_c, new_h
 
-    def zoneout_lstm(self, x, c, h, kernel, bias, is_training=False, masks=None):
+    def zoneout_lstm(self, x, c, h, kernel, bias, is_training=False, masks=None, round_ops=False):
         """ZoneoutLSTMCell.__call__ (Encoder.py:118-142; App. A.2): output = RAW new_h, state zoned."""
         z = self.hp.zoneout_rate
-        new_c, new_h = self.lstm_cell(x, c, h, kernel, bias)
+        new_c, new_h = self.lstm_cell(x, c, h, kernel, bias, round_ops)
         if is_training:
             mc, mh = masks  # Bernoulli(1-z) keep masks; (1-z)*dropout(d, 1-z) == mask*d (Encoder.py:135-136)
             zc = c + mc.to(c.dtype) * (new_c - c)
@@ -270,7 +283,7 @@ class TacotronOracle(object):
 
     def attention_step(self, query, cum, values, keys, mask):
         """LocationSensitiveAttention.__call__ + _compute_attention (Attention.py:169-210,345-366,369-401)."""
-        q = query @ self.w[W_LSA + "/query_layer/kernel"]                                     # [B, A]
+        q = self._dmm(query, self.w[W_LSA + "/query_layer/kernel"])                           # [B, A]
         f = self._conv1d_same(cum.unsqueeze(2), self.w[W_LSA + "/location_features_convolution/kernel"],
                               self.w[W_LSA + "/location_features_convolution/bias"])          # [B, T, 32]
         loc = f @ self.w[W_LSA + "/location_features_layer/kernel"]                           # [B, T, A]
@@ -285,7 +298,8 @@ class TacotronOracle(object):
             energy = torch.where(mask, energy, torch.full_like(energy, -math.inf))
             align = torch.softmax(energy, dim=-1)
         next_cum = align + cum if self.hp.cumulative_weights else align
-        context = torch.bmm(align.unsqueeze(1), values).squeeze(1)                            # [B, 768]
+        vals = _round_bf16(values) if self.dec_bf16 else values
+        context = torch.bmm(align.unsqueeze(1), vals).squeeze(1)                              # [B, 768]
         return context, align, next_cum
 
     # ------------------------------------------------------------------ decoder
@@ -293,7 +307,7 @@ class TacotronOracle(object):
         """Prenet.__call__ (Decoder.py:342-352): dense+ReLU+dropout(0.5, ALWAYS on). keep_masks: [B, L, units]."""
         keep = 1.0 - self.hp.dropout_rate
         for i in range(len(self.hp.prenet_layers)):
-            x = torch.relu(x @ self.w[(W_PRENET % (i + 1)) + "/kernel"] + self.w[(W_PRENET % (i + 1)) + "/bias"])
+            x = torch.relu(self._dmm(x, self.w[(W_PRENET % (i + 1)) + "/kernel"]) + self.w[(W_PRENET % (i + 1)) + "/bias"])
             x = x * keep_masks[:, i].to(x.dtype) / keep
         return x
 
@@ -313,12 +327,12 @@ class TacotronOracle(object):
         m1 = m2 = None
         if is_training:
             m1, m2 = zo_masks
-        h1raw, c1, h1 = self.zoneout_lstm(lstm_in, state.c1, state.h1, k1, b1, is_training, m1)
-        h2raw, c2, h2 = self.zoneout_lstm(h1raw, state.c2, state.h2, k2, b2, is_training, m2)
+        h1raw, c1, h1 = self.zoneout_lstm(lstm_in, state.c1, state.h1, k1, b1, is_training, m1, self.dec_bf16)
+        h2raw, c2, h2 = self.zoneout_lstm(h1raw, state.c2, state.h2, k2, b2, is_training, m2, self.dec_bf16)
         context, align, cum = self.attention_step(h2raw, state.alignments, values, keys, mask)
         proj_in = torch.cat([h2raw, context], dim=-1)
-        frames = proj_in @ self.w[W_FRAME + "/kernel"] + self.w[W_FRAME + "/bias"]
-        stop_logits = proj_in @ self.w[W_STOP + "/kernel"] + self.w[W_STOP + "/bias"]
+        frames = self._dmm(proj_in, self.w[W_FRAME + "/kernel"]) + self.w[W_FRAME + "/bias"]
+        stop_logits = self._dmm(proj_in, self.w[W_STOP + "/kernel"]) + self.w[W_STOP + "/bias"]
         nxt = DecoderState(c1, h1, c2, h2, context, cum, state.time + 1)
         return frames, stop_logits, align, nxt
 

@@ -13,6 +13,7 @@ TACO_MODE_FREE = 0
 TACO_MODE_TEACHER = 1
 TACO_PRECISION_FP32 = 0
 TACO_PRECISION_BF16_CONV = 1
+TACO_PRECISION_BF16 = 2
 TACO_STAGE_ENCODE, TACO_STAGE_DECODER_KERNEL, TACO_STAGE_POSTNET = 0, 1, 2
 
 ERROR_NAMES = {-1: "TACO_ERR_INVALID", -2: "TACO_ERR_UNSUPPORTED", -3: "TACO_ERR_CUDA",
@@ -23,7 +24,7 @@ EXPORTED_SYMBOLS = [
     "taco_create", "taco_destroy", "taco_last_error", "taco_version", "taco_set_weight",
     "taco_finalize_weights", "taco_set_precision", "taco_encode", "taco_decode",
     "taco_transpose_alignments", "taco_postnet", "taco_launch_count", "taco_get_decoder_state",
-    "taco_stage_ms",
+    "taco_stage_ms", "taco_debug_read_workspace",
 ]
 
 
@@ -90,6 +91,8 @@ def lib():
     L.taco_get_decoder_state.restype = i32
     L.taco_stage_ms.argtypes = [vp, i32, C.POINTER(C.c_float)]
     L.taco_stage_ms.restype = i32
+    L.taco_debug_read_workspace.argtypes = [vp, C.c_char_p, vp, C.c_size_t]
+    L.taco_debug_read_workspace.restype = i32
     _lib = L
     return L
 

@@ -1,6 +1,7 @@
 // C ABI of libtaco_b200.so (include/taco_b200.h): handle, weight ingestion / packing, and the
 // host-side orchestration of the sm_100a kernels.  No torch types, no CPU compute fallback.
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <string>
@@ -68,6 +69,10 @@ struct TacoHandle {
     void* post_proj_wt = nullptr;
     void* enc_wt[8] = {};
     float* dec_blob[2] = {};     // U = 2 (GN 128), U = 4 (GN 64)
+    // dataflow decoder (decoder2.cu): fragment-major bf16 shards and fused location kernel
+    uint32_t *dec2_blob = nullptr, *dec2_wq = nullptr, *dec2_ghi = nullptr, *dec2_glo = nullptr;
+    float* dec2_bconst = nullptr;
+    int dec_kind = 0;            // which decoder kernel owns the running state (1 = decoder.cu, 2 = decoder2.cu)
     float* bilstm_blob[2] = {};  // same two configs, [2 dir][GN][256*4U]
     // decoder running state
     int dec_t = 0, dec_B = 0, dec_T = 0, dec_RBP = 0, dec_GB = 0;
@@ -280,6 +285,124 @@ int pack_decoder_blobs(TacoHandle* h) {
     return TACO_OK;
 }
 
+int upload_words(TacoHandle* h, const std::vector<uint32_t>& v, uint32_t** out) {
+    void* d;
+    CK(cudaMalloc(&d, v.size() * sizeof(uint32_t)));
+    CK(cudaMemcpy(d, v.data(), v.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+    h->owned.push_back(d);
+    *out = reinterpret_cast<uint32_t*>(d);
+    return TACO_OK;
+}
+
+inline uint32_t pack2(float lo, float hi) { return (uint32_t)f32_to_bf16_rne(lo) | ((uint32_t)f32_to_bf16_rne(hi) << 16); }
+inline float bf16_round(float f) {
+    uint32_t u = (uint32_t)f32_to_bf16_rne(f) << 16;
+    float r;
+    memcpy(&r, &u, 4);
+    return r;
+}
+
+// Shards for decoder2.cu: per CTA c (units 2c, 2c+1) the mma.sync m16n8k16 B-fragments of its 8 gate
+// columns / 2 prenet / 2 projection columns: word [ks][lane=4g+t][j] = bf16 pair
+// (W[16ks + 2t + 8j][n=g], W[16ks + 2t + 8j + 1][g]).
+int pack_decoder2(TacoHandle* h) {
+    const Weight *k1, *b1, *k2, *b2, *kp1, *bp1, *kp2, *bp2, *kq, *kf, *bf, *kst, *bst, *cw, *cb, *wl, *ba;
+    int rc;
+#define NEED(var, name, ...) \
+    if ((rc = need(h, name, {__VA_ARGS__}, &var))) return rc;
+    NEED(k1, std::string(DEC_LSTM1) + "/kernel", 1280, 1024)
+    NEED(b1, std::string(DEC_LSTM1) + "/bias", 1024)
+    NEED(k2, std::string(DEC_LSTM2) + "/kernel", 512, 1024)
+    NEED(b2, std::string(DEC_LSTM2) + "/bias", 1024)
+    NEED(kp1, fmt(PRENET, 1) + "/kernel", 80, 256)
+    NEED(bp1, fmt(PRENET, 1) + "/bias", 256)
+    NEED(kp2, fmt(PRENET, 2) + "/kernel", 256, 256)
+    NEED(bp2, fmt(PRENET, 2) + "/bias", 256)
+    NEED(kq, std::string(LSA) + "/query_layer/kernel", 256, 128)
+    NEED(kf, std::string(FRAME_PROJ) + "/kernel", 1024, 160)
+    NEED(bf, std::string(FRAME_PROJ) + "/bias", 160)
+    NEED(kst, std::string(STOP_PROJ) + "/kernel", 1024, 2)
+    NEED(bst, std::string(STOP_PROJ) + "/bias", 2)
+    NEED(cw, std::string(LSA) + "/location_features_convolution/kernel", 31, 1, 32)
+    NEED(cb, std::string(LSA) + "/location_features_convolution/bias", 32)
+    NEED(wl, std::string(LSA) + "/location_features_layer/kernel", 32, 128)
+    NEED(ba, std::string(LSA) + "/attention_bias", 128)
+#undef NEED
+    const int BW = TACO_DEC2_BLOB_WORDS;
+    std::vector<uint32_t> blob((size_t)TACO_DEC2_CTAS * BW, 0u);
+    // generic fragment packer: get(k, n) -> weight
+    auto pack_frag = [](uint32_t* dst, int KS, auto get) {
+        for (int ks = 0; ks < KS; ++ks)
+            for (int lane = 0; lane < 32; ++lane) {
+                const int g = lane >> 2, t = lane & 3;
+                for (int j = 0; j < 2; ++j) {
+                    const int k = ks * 16 + 2 * t + 8 * j;
+                    dst[(ks * 32 + lane) * 2 + j] = pack2(get(k, g), get(k + 1, g));
+                }
+            }
+    };
+    for (int c = 0; c < TACO_DEC2_CTAS; ++c) {
+        uint32_t* p = blob.data() + (size_t)c * BW;
+        auto gate_col = [c](int n) { return (n >> 1) * 256 + 2 * c + (n & 1); };  // n = gate*2 + unit
+        pack_frag(p, 80, [&](int k, int n) { return k1->host[(size_t)k * 1024 + gate_col(n)]; });
+        pack_frag(p + 80 * 64, 32, [&](int k, int n) { return k2->host[(size_t)k * 1024 + gate_col(n)]; });
+        pack_frag(p + 112 * 64, 5, [&](int k, int n) { return n < 2 ? kp1->host[(size_t)k * 256 + 2 * c + n] : 0.f; });
+        pack_frag(p + 117 * 64, 16, [&](int k, int n) { return n < 2 ? kp2->host[(size_t)k * 256 + 2 * c + n] : 0.f; });
+        pack_frag(p + 133 * 64, 64, [&](int k, int n) {
+            const int oc = 2 * c + n;
+            if (n >= 2 || oc >= 162) return 0.f;
+            return oc < 160 ? kf->host[(size_t)k * 160 + oc] : kst->host[(size_t)k * 2 + (oc - 160)];
+        });
+        float* bias = reinterpret_cast<float*>(p + 197 * 64);
+        for (int n = 0; n < 8; ++n) {
+            bias[n] = b1->host[gate_col(n)];
+            bias[8 + n] = b2->host[gate_col(n)];
+        }
+        for (int n = 0; n < 2; ++n) {
+            bias[16 + n] = bp1->host[2 * c + n];
+            bias[18 + n] = bp2->host[2 * c + n];
+            const int oc = 2 * c + n;
+            bias[20 + n] = oc < 160 ? bf->host[oc] : (oc < 162 ? bst->host[oc - 160] : 0.f);
+        }
+    }
+    if ((rc = upload_words(h, blob, &h->dec2_blob))) return rc;
+    std::vector<uint32_t> wq((size_t)256 * 64);
+    for (int k = 0; k < 256; ++k)
+        for (int j = 0; j < 64; ++j) wq[(size_t)k * 64 + j] = pack2(kq->host[(size_t)k * 128 + 2 * j], kq->host[(size_t)k * 128 + 2 * j + 1]);
+    if ((rc = upload_words(h, wq, &h->dec2_wq))) return rc;
+    // G[k][d] = sum_c conv[k][c] Wl[c][d] (k < 31; row 31 = 0), hi/lo bf16 split, B-fragment-major [ks][nt][lane][2]
+    std::vector<double> G((size_t)32 * 128, 0.0);
+    for (int k = 0; k < 31; ++k)
+        for (int d = 0; d < 128; ++d) {
+            double a = 0;
+            for (int c = 0; c < 32; ++c) a += (double)cw->host[(size_t)k * 32 + c] * (double)wl->host[(size_t)c * 128 + d];
+            G[(size_t)k * 128 + d] = a;
+        }
+    std::vector<uint32_t> ghi((size_t)2 * 16 * 64), glo((size_t)2 * 16 * 64);
+    for (int ks = 0; ks < 2; ++ks)
+        for (int nt = 0; nt < 16; ++nt)
+            for (int lane = 0; lane < 32; ++lane) {
+                const int g = lane >> 2, t = lane & 3;
+                for (int j = 0; j < 2; ++j) {
+                    const int k = ks * 16 + 2 * t + 8 * j, d = nt * 8 + g;
+                    const float a0 = (float)G[(size_t)k * 128 + d], a1 = (float)G[(size_t)(k + 1) * 128 + d];
+                    const float h0 = bf16_round(a0), h1 = bf16_round(a1);
+                    const size_t idx = ((size_t)(ks * 16 + nt) * 32 + lane) * 2 + j;
+                    ghi[idx] = pack2(h0, h1);
+                    glo[idx] = pack2((float)(G[(size_t)k * 128 + d] - h0), (float)(G[(size_t)(k + 1) * 128 + d] - h1));
+                }
+            }
+    if ((rc = upload_words(h, ghi, &h->dec2_ghi))) return rc;
+    if ((rc = upload_words(h, glo, &h->dec2_glo))) return rc;
+    std::vector<float> bconst(128);
+    for (int d = 0; d < 128; ++d) {
+        double a = ba->host[d];
+        for (int c = 0; c < 32; ++c) a += (double)cb->host[c] * (double)wl->host[(size_t)c * 128 + d];
+        bconst[d] = (float)a;
+    }
+    return upload(h, bconst, &h->dec2_bconst);
+}
+
 const float* dev_w(TacoHandle* h, const std::string& name) {
     const Weight* w = find_w(h, name);
     return w ? w->dev : nullptr;
@@ -316,6 +439,110 @@ int conv(TacoHandle* h, const float* x, long long x_stride, long long x_bstride,
     p.clip = clip ? 1 : 0; p.clip_lo = lo; p.clip_hi = hi;
     CK(taco_launch_conv1d_f32(p, st));
     h->launches++;
+    return TACO_OK;
+}
+
+// taco_decode through the dataflow kernel (decoder2.cu) -- TACO_PRECISION_BF16
+int decode_v2(TacoHandle* h, int mode, const float* memory, const int32_t* lens, int B, int T, const float* mel_targets,
+              int F_tgt, int S_max, const uint8_t* prenet_masks, uint64_t philox_seed, int reset_state, int logits_only,
+              float* frames, float* stop, float* align_hist, int32_t* steps_out, cudaStream_t st) {
+    const TacoHParams& hp = h->hp;
+    Dec2Params p;
+    memset(&p, 0, sizeof p);
+    p.B = B; p.T = T;
+    p.MT = B <= 16 ? 1 : (B <= 32 ? 2 : 4);
+    p.KG = 16 / p.MT;
+    static const int ns_opts[] = {96, 48, 32, 24, 16, 12, 8, 6, 4, 3, 2, 1};
+    p.NS = 1;
+    for (int ns : ns_opts)
+        if (B * ns <= TACO_DEC2_CTAS) { p.NS = ns; break; }
+    p.S_max = S_max; p.S_cap = S_max; p.mode = mode;
+    p.stop_at_any = hp.stop_at_any; p.cumulative = hp.cumulative_weights; p.smoothing = hp.smoothing;
+    p.stop_sigmoid = logits_only ? 0 : 1;
+    p.zoneout = hp.zoneout_rate;
+    p.keep_scale = 1.0f / (1.0f - hp.dropout_rate);
+    p.blobs = h->dec2_blob; p.wq = h->dec2_wq; p.g_hi = h->dec2_ghi; p.g_lo = h->dec2_glo;
+    p.va = dev_w(h, std::string(LSA) + "/attention_variable");
+    p.bconst = h->dec2_bconst;
+    if (!reset_state && (h->dec_kind != 2 || h->dec_B != B || h->dec_T != T))
+        FAIL(TACO_ERR_STATE, "taco_decode: continuing with a different batch shape or precision");
+    WS(lens_eff, int32_t, "dec_lens", B)
+    if (hp.mask_encoder) {
+        CK(cudaMemcpyAsync(lens_eff, lens, B * sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
+    } else {
+        std::vector<int32_t> full(B, T);
+        CK(cudaMemcpyAsync(lens_eff, full.data(), B * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+        CK(cudaStreamSynchronize(st));
+    }
+    p.lens = lens_eff;
+    WS(keys, float, "dec_keys", (size_t)B * T * 128)
+    WS(vals, uint16_t, "dec2_values", (size_t)B * T * 768)
+    if (reset_state) {
+        int rc = conv(h, memory, 768, (long long)T * 768, dev_w(h, std::string(MEMORY_LAYER) + "/kernel"), nullptr, nullptr, keys, 128,
+                      (long long)T * 128, nullptr, B, T, 768, 128, 1, ACT_NONE, false, 0, 0, st);
+        if (rc) return rc;
+        CK(taco_launch_f32_to_bf16(memory, vals, (size_t)B * T * 768, st));
+        h->launches++;
+    }
+    p.keys = keys;
+    p.values = vals;
+    // rings
+    const size_t unit = (size_t)p.MT * 128 * 4;  // words per k-step, 4 slots
+    const size_t n_x = unit * 5, n_h = unit * 16, n_c = unit * 48;
+    WS(rings, uint32_t, "dec2_rings", n_x + 6 * n_h + n_c)
+    uint32_t* r = rings;
+    p.ring_x = r; r += n_x;
+    p.ring_p1 = r; r += n_h;
+    p.ring_p2 = r; r += n_h;
+    p.ring_h1raw = r; r += n_h;
+    p.ring_h1z = r; r += n_h;
+    p.ring_h2raw = r; r += n_h;
+    p.ring_h2z = r; r += n_h;
+    p.ring_ctx = r;
+    // recurrent state (fp32 row-major): c1 h1z c2 h2z [B][256], ctx [B][768], x [B][80], cum [B][T]
+    const size_t n_state = (size_t)B * (4 * 256 + 768 + 80 + T);
+    WS(state, float, "dec2_state", n_state)
+    if (reset_state) {
+        CK(cudaMemsetAsync(state, 0, n_state * sizeof(float), st));
+        h->dec_t = 0;
+    }
+    float* s = state;
+    p.c1 = s; s += (size_t)B * 256;
+    p.h1z = s; s += (size_t)B * 256;
+    p.c2 = s; s += (size_t)B * 256;
+    p.h2z = s; s += (size_t)B * 256;
+    p.ctx_state = s; s += (size_t)B * 768;
+    p.x_state = s; s += (size_t)B * 80;
+    p.cum = s;
+    int pre_in_smem = 0;
+    taco_decoder2_smem_bytes(T, &pre_in_smem);
+    p.pre_in_smem = pre_in_smem;
+    if (!pre_in_smem) {
+        WS(pre, float, "dec2_pre", (size_t)TACO_DEC2_CTAS * T * 128)
+        p.pre_scratch = pre;
+    }
+    p.t0 = h->dec_t;
+    p.targets = mel_targets; p.F_tgt = F_tgt;
+    p.masks = prenet_masks; p.seed = philox_seed;
+    p.frames = frames; p.stop = stop; p.hist = align_hist; p.steps_out = steps_out;
+    WS(flags, int, "dec2_flags", (size_t)S_max + 8)
+    CK(cudaMemsetAsync(flags, 0, ((size_t)S_max + 8) * sizeof(int), st));
+    p.flags = flags;
+    p.abort_flag = flags + S_max + 4;
+    if (getenv("TACO_DEC2_DBG")) p.dbg = atoi(getenv("TACO_DEC2_DBG"));
+    if (getenv("TACO_DEC2_TIMING")) {
+        WS(timing, long long, "dec2_timing", (size_t)TACO_DEC2_CTAS * 16)
+        p.timing = timing;
+    }
+    CK(taco_launch_decoder2_init(p, st));
+    h->launches++;
+    CK(cudaEventRecord(h->ev[TACO_STAGE_DECODER_KERNEL][0], st));
+    CK(taco_launch_decoder2(p, st));
+    CK(cudaEventRecord(h->ev[TACO_STAGE_DECODER_KERNEL][1], st));
+    h->ev_valid[TACO_STAGE_DECODER_KERNEL] = true;
+    h->launches++;
+    h->dec_t += S_max;
+    h->dec_B = B; h->dec_T = T; h->dec_kind = 2;
     return TACO_OK;
 }
 
@@ -396,8 +623,9 @@ int64_t taco_launch_count(const TacoHandle* h) { return h ? h->launches : 0; }
 
 int taco_set_precision(TacoHandle* h, int precision) {
     if (!h) return TACO_ERR_INVALID;
-    if (precision != TACO_PRECISION_FP32 && precision != TACO_PRECISION_BF16_CONV) FAIL(TACO_ERR_INVALID, "bad precision");
-    if (precision == TACO_PRECISION_BF16_CONV) {
+    if (precision != TACO_PRECISION_FP32 && precision != TACO_PRECISION_BF16_CONV && precision != TACO_PRECISION_BF16)
+        FAIL(TACO_ERR_INVALID, "bad precision");
+    if (precision != TACO_PRECISION_FP32) {
         const int PC = h->hp.postnet_channels + h->hp.style_embed_depth;
         if (PC % 256 != 0 || h->hp.num_mels != 80) FAIL(TACO_ERR_UNSUPPORTED, "tcgen05 postnet needs a channel width multiple of 256 and 80 mels");
     }
@@ -439,6 +667,7 @@ int taco_finalize_weights(TacoHandle* h) {
     for (int i = 0; i < h->hp.n_reference_filters; ++i)
         if ((rc = fold_bn(h, fmt(REF_CONV, i), "conv2d", eps, &h->ref_scale[i], &h->ref_shift[i]))) return rc;
     if ((rc = pack_decoder_blobs(h))) return rc;
+    if ((rc = pack_decoder2(h))) return rc;
     const char* required[] = {"inputs_embedding", "style_tokens"};
     for (const char* r : required)
         if (!find_w(h, r)) FAIL(TACO_ERR_MISSING_WEIGHT, std::string("missing variable ") + r);
@@ -619,6 +848,9 @@ int taco_decode(TacoHandle* h, int mode, const float* memory, const int32_t* len
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     CK(cudaSetDevice(h->device));
     const TacoHParams& hp = h->hp;
+    if (h->precision == TACO_PRECISION_BF16 && T <= TACO_DEC2_TMAX)
+        return decode_v2(h, mode, memory, lens, B, T, mel_targets, F_tgt, S_max, prenet_masks, philox_seed, reset_state, logits_only,
+                         frames, stop, align_hist, steps_out, st);
 
     DecParams p;
     memset(&p, 0, sizeof p);
@@ -646,7 +878,8 @@ int taco_decode(TacoHandle* h, int mode, const float* memory, const int32_t* len
     p.v_a = dev_w(h, std::string(LSA) + "/attention_variable");
     p.b_a = dev_w(h, std::string(LSA) + "/attention_bias");
 
-    if (!reset_state && (h->dec_B != B || h->dec_T != T)) FAIL(TACO_ERR_STATE, "taco_decode: continuing with a different batch shape");
+    if (!reset_state && (h->dec_kind != 1 || h->dec_B != B || h->dec_T != T))
+        FAIL(TACO_ERR_STATE, "taco_decode: continuing with a different batch shape or precision");
     // lengths: mask_encoder False => every row attends over all T positions (Attention.py:150)
     WS(lens_eff, int32_t, "dec_lens", B)
     if (hp.mask_encoder) {
@@ -707,7 +940,7 @@ int taco_decode(TacoHandle* h, int mode, const float* memory, const int32_t* len
     h->ev_valid[TACO_STAGE_DECODER_KERNEL] = true;
     h->launches++;
     h->dec_t += S_max;  // exact for S_max == 1 (cell stepping) and for runs to completion
-    h->dec_B = B; h->dec_T = T; h->dec_RBP = p.RBP; h->dec_GB = p.GB;
+    h->dec_B = B; h->dec_T = T; h->dec_RBP = p.RBP; h->dec_GB = p.GB; h->dec_kind = 1;
     return TACO_OK;
 }
 
@@ -732,7 +965,7 @@ int taco_postnet(TacoHandle* h, const float* frames, int B, int F, int F_stride,
     const float hi = hp.max_abs_value;
     const float lo = (hp.symmetric_mels ? -hp.max_abs_value : 0.f) - hp.lower_bound_decay;
     CK(cudaEventRecord(h->ev[TACO_STAGE_POSTNET][0], st));
-    if (h->precision == TACO_PRECISION_BF16_CONV) {
+    if (h->precision != TACO_PRECISION_FP32) {
         // tcgen05 path: bf16 operands, fp32 accumulation; activations stay bf16 between layers
         const int C0 = h->post_cin_pad[0];
         const size_t wide = (size_t)(PC > C0 ? PC : C0);
@@ -796,6 +1029,16 @@ int taco_postnet(TacoHandle* h, const float* frames, int B, int F, int F_stride,
     return TACO_OK;
 }
 
+int taco_debug_read_workspace(TacoHandle* h, const char* name, void* host_dst, size_t bytes) {
+    if (!h || !name || !host_dst) return TACO_ERR_INVALID;
+    auto it = h->ws.find(name);
+    if (it == h->ws.end() || it->second.bytes < bytes) FAIL(TACO_ERR_STATE, std::string("no such workspace: ") + name);
+    CK(cudaSetDevice(h->device));
+    CK(cudaDeviceSynchronize());
+    CK(cudaMemcpy(host_dst, it->second.p, bytes, cudaMemcpyDeviceToHost));
+    return TACO_OK;
+}
+
 int taco_stage_ms(TacoHandle* h, int stage, float* ms_out) {
     if (!h || !ms_out || stage < 0 || stage >= TACO_N_STAGES) return TACO_ERR_INVALID;
     if (!h->ev_valid[stage]) FAIL(TACO_ERR_STATE, "taco_stage_ms: stage has not run");
@@ -811,6 +1054,20 @@ int taco_get_decoder_state(TacoHandle* h, int B, int T, float* c1, float* h1, fl
     if (h->dec_B != B || h->dec_T != T) FAIL(TACO_ERR_STATE, "taco_get_decoder_state: no decoder state of that shape");
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     CK(cudaSetDevice(h->device));
+    if (h->dec_kind == 2) {
+        auto it2 = h->ws.find("dec2_state");
+        if (it2 == h->ws.end()) FAIL(TACO_ERR_STATE, "no decoder state");
+        const float* s = reinterpret_cast<const float*>(it2->second.p);
+        const size_t nb = (size_t)B * 256 * sizeof(float);
+        if (c1) CK(cudaMemcpyAsync(c1, s, nb, cudaMemcpyDeviceToDevice, st));
+        if (h1) CK(cudaMemcpyAsync(h1, s + (size_t)B * 256, nb, cudaMemcpyDeviceToDevice, st));
+        if (c2) CK(cudaMemcpyAsync(c2, s + (size_t)B * 512, nb, cudaMemcpyDeviceToDevice, st));
+        if (h2) CK(cudaMemcpyAsync(h2, s + (size_t)B * 768, nb, cudaMemcpyDeviceToDevice, st));
+        if (attention) CK(cudaMemcpyAsync(attention, s + (size_t)B * 1024, (size_t)B * 768 * sizeof(float), cudaMemcpyDeviceToDevice, st));
+        if (alignments)
+            CK(cudaMemcpyAsync(alignments, s + (size_t)B * (1024 + 768 + 80), (size_t)B * T * sizeof(float), cudaMemcpyDeviceToDevice, st));
+        return TACO_OK;
+    }
     auto it = h->ws.find("dec_exchange");
     if (it == h->ws.end()) FAIL(TACO_ERR_STATE, "no decoder state");
     float* ex = reinterpret_cast<float*>(it->second.p);

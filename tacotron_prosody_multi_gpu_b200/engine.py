@@ -74,7 +74,8 @@ class TacoEngine(object):
         self._check(self.L.taco_finalize_weights(self._h), "taco_finalize_weights")
 
     def set_precision(self, precision):
-        code = {"fp32": _lib.TACO_PRECISION_FP32, "bf16": _lib.TACO_PRECISION_BF16_CONV}[precision]
+        code = {"fp32": _lib.TACO_PRECISION_FP32, "bf16_conv": _lib.TACO_PRECISION_BF16_CONV,
+                "bf16": _lib.TACO_PRECISION_BF16}[precision]
         self._check(self.L.taco_set_precision(self._h, code), "taco_set_precision")
         self.precision = precision
 
@@ -148,6 +149,8 @@ class TacoEngine(object):
         out = dict(frames=frames, stop=stop, align_hist=hist, S_max=S_max, steps=steps)
         if sync:
             out["steps"] = int(steps.item())
+            if out["steps"] < 0:
+                raise _lib.TacoError("taco_decode: the persistent decoder kernel aborted (an exchange poll timed out)")
         return out
 
     def alignments(self, align_hist, S):

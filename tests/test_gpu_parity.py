@@ -212,3 +212,107 @@ def test_postnet_tcgen05_parity(ctx, B, F):
     # the kernel is closer to the bf16-rounding oracle than that oracle is to the fp32 one
     assert e_mirror < e_round
     eng.close()
+
+
+# ------------------------------------------------------------------ dataflow decoder (bf16 tensor-core contractions)
+# Tolerances of TACO_PRECISION_BF16 against the oracle that rounds the SAME operands to bf16 (dec_bf16=True):
+# remaining differences are fp32 accumulation order, tanh.approx in the energies (|err| <= 2^-10.99 per PTX ISA),
+# the hi/lo-split fused location contraction (~2^-16 relative) and bf16 re-rounding of near-tie activations.
+ATOL_D2_FRAMES = 3e-2
+ATOL_D2_ALIGN = 5e-3
+# ... and against the plain fp32 oracle (bf16 operand rounding through <= 24 recurrent steps)
+ATOL_D2_FRAMES_FP32 = 1e-1
+ATOL_D2_ALIGN_FP32 = 2e-2
+
+
+@pytest.fixture(scope="module")
+def ctx2():
+    from tacotron_prosody_multi_gpu_b200.engine import TacoEngine
+    hp = default_hparams()
+    w = weights.set_stop_bias(weights.init_weights(hp, perturb=0.05), -10.0)
+    eng = TacoEngine(hp, w, precision="bf16")
+    return hp, w, eng, TacotronOracle(hp, w, conv_bf16=True, dec_bf16=True), TacotronOracle(hp, w)
+
+
+@pytest.mark.parametrize("lengths", [[13], [20, 11, 16], [9] * 6 + [14] * 5, [10, 25] * 10, [12, 30, 7, 22] * 16])
+def test_decoder2_teacher_forced_parity(ctx2, lengths):
+    """Covers MT = 1 / 1 / 1 / 2 / 4 M-tiles and NS = 96 / 32 / 8 / 6 / 2 context slices."""
+    hp, w, eng, mir, orc = ctx2
+    B = len(lengths)
+    ids, lens = synthetic.token_batch(hp, lengths)
+    T = ids.shape[1]
+    rng = np.random.default_rng(B)
+    memory = (rng.standard_normal((B, T, 768)) * 0.5).astype(np.float32)
+    mel, _, _ = synthetic.mel_targets(hp, lens, frames_per_token=1, max_frames=24)
+    S = mel.shape[1] // 2
+    masks = philox.prenet_masks(11, S, B)
+    with torch.no_grad():
+        ref = mir.decode(torch.from_numpy(memory), lens, mel_targets=mel, prenet_masks=masks)
+        ref32 = orc.decode(torch.from_numpy(memory), lens, mel_targets=mel, prenet_masks=masks)
+    d = eng.decode(torch.from_numpy(memory).cuda(), torch.from_numpy(lens), mel_targets=torch.from_numpy(mel),
+                   prenet_masks=masks)
+    assert d["steps"] == ref["steps"] == S
+    al = _t(eng.alignments(d["align_hist"], S))
+    print("decoder2 B=%d: |frames-mirror|=%.2e |frames-fp32|=%.2e |mirror-fp32|=%.2e |align-mirror|=%.2e" % (
+        B, np.abs(_t(d["frames"]) - ref["frames_raw"].numpy()).max(), np.abs(_t(d["frames"]) - ref32["frames_raw"].numpy()).max(),
+        np.abs(ref["frames_raw"].numpy() - ref32["frames_raw"].numpy()).max(), np.abs(al - ref["alignments"].numpy()).max()))
+    np.testing.assert_allclose(_t(d["frames"]), ref["frames_raw"].numpy(), atol=ATOL_D2_FRAMES)
+    np.testing.assert_allclose(_t(d["stop"]), ref["stop"].numpy(), atol=ATOL_D2_FRAMES)
+    np.testing.assert_allclose(al, ref["alignments"].numpy(), atol=ATOL_D2_ALIGN)
+    np.testing.assert_allclose(_t(d["frames"]), ref32["frames_raw"].numpy(), atol=ATOL_D2_FRAMES_FP32)
+    np.testing.assert_allclose(al, ref32["alignments"].numpy(), atol=ATOL_D2_ALIGN_FP32)
+    for b, n in enumerate(lens):
+        assert al[b, n:].max(initial=0.0) == 0.0              # exact zeros beyond length (-inf mask)
+    np.testing.assert_allclose(al.sum(1), 1.0, atol=1e-5)
+    st = eng.decoder_state(B, T)
+    fs = ref["final_state"]
+    np.testing.assert_allclose(_t(st["c1"]), fs.c1.numpy(), atol=ATOL_D2_FRAMES)
+    np.testing.assert_allclose(_t(st["h2"]), fs.h2.numpy(), atol=ATOL_D2_FRAMES)
+    np.testing.assert_allclose(_t(st["attention"]), fs.attention.numpy(), atol=ATOL_D2_FRAMES)
+    np.testing.assert_allclose(_t(st["alignments"]), fs.alignments.numpy(), atol=5e-2)
+
+
+def test_decoder2_philox_equals_explicit_masks(ctx2):
+    hp, w, eng, _, _ = ctx2
+    ids, lens = synthetic.token_batch(hp, [10, 8, 12])
+    rng = np.random.default_rng(5)
+    memory = torch.from_numpy((rng.standard_normal((3, 12, 768)) * 0.5).astype(np.float32)).cuda()
+    S = 7
+    a = eng.decode(memory, torch.from_numpy(lens), max_iters=S, philox_seed=0x1234567890)
+    b = eng.decode(memory, torch.from_numpy(lens), max_iters=S, prenet_masks=philox.prenet_masks(0x1234567890, S, 3))
+    assert a["steps"] == b["steps"] == S
+    assert torch.equal(a["frames"], b["frames"]) and torch.equal(a["align_hist"], b["align_hist"])
+
+
+def test_decoder2_cell_stepping_matches_one_launch(ctx2):
+    hp, w, eng, _, _ = ctx2
+    ids, lens = synthetic.token_batch(hp, [10, 8])
+    rng = np.random.default_rng(8)
+    memory = torch.from_numpy((rng.standard_normal((2, 10, 768)) * 0.5).astype(np.float32)).cuda()
+    S = 5
+    whole = eng.decode(memory, torch.from_numpy(lens), max_iters=S, philox_seed=3)
+    frames = []
+    for t in range(S):
+        d = eng.decode(memory, torch.from_numpy(lens), max_iters=1, philox_seed=3, reset_state=(t == 0))
+        frames.append(d["frames"].clone())
+    assert torch.equal(torch.cat(frames, 1), whole["frames"])
+
+
+def test_decoder2_free_running_stop_step_bit_exact(ctx2):
+    """Batch-global stop: S and output lengths equal the bf16-mirroring oracle's exactly."""
+    hp, _, _, _, _ = ctx2
+    from tacotron_prosody_multi_gpu_b200.engine import TacoEngine
+    base = weights.init_weights(hp, perturb=0.05)
+    ids, lens = synthetic.token_batch(hp, [14, 9, 12, 11])
+    gw = synthetic.gst_random_weights(hp)
+    w, S, margin = pick_stop_bias(hp, base, ids, lens, gw, max_iters=40, philox_seed=99)
+    mir = TacotronOracle(hp, w, conv_bf16=True, dec_bf16=True)
+    ref = mir.forward(ids, lens, gst_weights=gw, max_iters=40, philox_seed=99)
+    eng = TacoEngine(hp, w, precision="bf16")
+    out = eng.forward(torch.from_numpy(ids), torch.from_numpy(lens), gst_weights=gw, max_iters=40, philox_seed=99)
+    print("decoder2 free-run: S gpu=%d mirror=%d fp32-oracle=%d margin=%.3f" % (out["steps"], ref["steps"], S, margin))
+    assert out["steps"] == ref["steps"]
+    assert out["mel_outputs"].shape == (4, 2 * ref["steps"], 80)
+    np.testing.assert_allclose(_t(out["mel_outputs"]), ref["mel_outputs"].numpy(), atol=5e-2)
+    assert output_lengths(_t(out["stop"])) == output_lengths(ref["stop"].numpy())
+    eng.close()
