@@ -1,0 +1,56 @@
+"""Attention modules (TacotronModel/modules/Attention.py) as descriptors of fused stages.
+
+``LocationSensitiveAttention`` (Attention.py:96-210, scores :369-401, context :345-366): keys =
+memory . W_mem are computed once per utterance batch; every decoder step the persistent kernel
+evaluates  e[t] = v_a . tanh(keys[t] + q + loc(cum)[t] + b_a), a masked softmax over t < length,
+cum += a, context = a . values -- with the location conv (k31, 32 filters) and its 32 -> 128
+projection folded into one Toeplitz contraction.  ``MultiheadAttention`` (Attention.py:214-341) is the
+GST style-token attention, executed inside ``taco_encode``.
+"""
+from .Encoder import FusedStageError
+
+
+class LocationSensitiveAttention(object):
+    def __init__(self, num_units, memory, hparams, mask_encoder=True, memory_sequence_length=None,
+                 smoothing=False, cumulate_weights=True, name='LocationSensitiveAttention'):
+        if num_units != hparams.attention_dim:
+            raise ValueError("num_units must equal hparams.attention_dim (%d)" % hparams.attention_dim)
+        self.num_units = num_units
+        self.values = memory                     # [B, T, 768] device tensor (zeroed beyond length by the encoder)
+        self.hparams = hparams
+        self.mask_encoder = mask_encoder
+        self.memory_sequence_length = memory_sequence_length if mask_encoder else None
+        self.smoothing = smoothing
+        self._cumulate = cumulate_weights
+        self.synthesis_constraint = False
+        self.name = name
+        self.batch_size = memory.shape[0]
+        self.alignments_size = memory.shape[1]
+
+    state_size = property(lambda self: self.alignments_size)
+
+    def initial_alignments(self, batch_size, dtype=None):
+        import torch
+        return torch.zeros(batch_size, self.alignments_size, device=self.values.device)
+
+    initial_state = initial_alignments
+
+    def __call__(self, query, state):
+        raise FusedStageError("LocationSensitiveAttention.__call__ is fused into the persistent decoder kernel: "
+                              "call TacotronDecoderCell(...)(inputs, state) or dynamic decoding via Tacotron.initialize")
+
+
+class MultiheadAttention(object):
+    def __init__(self, query, value, num_heads=4, attention_type='mlp_attention', num_units=None, normalize=True):
+        self.query = query
+        self.value = value
+        self.num_heads = num_heads
+        self.attention_type = attention_type
+        self.num_units = num_units or query.shape[-1]
+        self.normalize = normalize
+        if attention_type != 'mlp_attention':
+            raise FusedStageError("only mlp_attention (the reference default, Hyperparams.py:12) is on the B200 path")
+
+    def multi_head_attention(self):
+        raise FusedStageError("GST multi-head attention runs inside taco_encode (gst_attention_kernel): "
+                              "pass reference_mel to EncoderCell / Tacotron.initialize")

@@ -1,0 +1,154 @@
+"""``Tacotron(hparams).initialize(...)`` of the reference (TacotronModel/modules/Tacotron.py:37-349)
+over the B200 C-ABI extension.
+
+The reference builds one TF graph "tower" per GPU inside a single process and evaluates it later with
+``session.run``; this class executes eagerly: ``initialize`` splits the packed inputs per tower with
+``split_infos`` exactly as Tacotron.py:92-130 does, runs each tower through
+encoder -> persistent decoder -> postnet on the process's GPU (one process per GPU is the scaling
+model, see sharding.py), and leaves the results in the reference's attributes, as lists with one entry
+per tower: ``tower_decoder_output`` / ``tower_mel_outputs`` [B,F,80], ``tower_alignments`` [B,T,S],
+``tower_stop_token_prediction`` [B,F] (Tacotron.py:314-317) and ``encoder_outputs`` [B,T,768] (:224).
+
+Modes: inference (free running, TacoTestHelper) and GTA / evaluation
+(teacher-forced forward, TacoTrainingHelper with ratio 1.0).  ``is_training=True`` (dropout, batch
+statistics, Bernoulli zoneout, losses, optimizer) is SURVEY 8f row f1 and raises.
+"""
+import numpy as np
+
+from ...Utils.Helpers import TacoTestHelper, TacoTrainingHelper
+from ...Utils.Utils import split_func
+from . import Attention, Decoder, Encoder, Postnet
+from .Encoder import FusedStageError
+
+
+def reference_encoder(inputs, hparams, is_training=True, activation='relu'):
+    """Tacotron.py:12-29 (6 x conv2d 3x3 s2 + BN + ReLU -> GRU(128) -> Dense tanh).  Executed inside
+    ``taco_encode`` when a reference mel is given; kept here as the named entry of the reference."""
+    raise FusedStageError("reference_encoder runs inside taco_encode: pass reference_mel to Tacotron.initialize")
+
+
+class Tacotron(object):
+    def __init__(self, hparams):
+        self.hparams = hparams
+        self.tower_decoder_output = []
+        self.tower_alignments = []
+        self.tower_stop_token_prediction = []
+        self.tower_mel_outputs = []
+        self.tower_linear_outputs = []
+        self.tower_ref_output = []
+
+    def initialize(self, inputs, input_lengths, mel_targets=None, stop_token_targets=None, linear_targets=None,
+                   targets_lengths=None, GTA=False, global_step=None, is_training=False, is_evaluating=False,
+                   split_infos=None, reference_mel=None, gst_weights=None, max_iters=None, prenet_masks=None,
+                   philox_seed=None):
+        """Arguments up to ``reference_mel`` are the reference's (Tacotron.py:46-48), NumPy arrays or
+        tensors in place of placeholders.  Extra, optional: ``gst_weights`` [heads, tokens] (the
+        injected stand-in for the ``tf.random_uniform`` style weights of Tacotron.py:216-222 when no
+        reference mel is given), ``max_iters`` (default hparams.max_iters), ``prenet_masks`` /
+        ``philox_seed`` (the always-on prenet dropout, Decoder.py:350-351)."""
+        hp = self.hparams
+        # ---- argument checks, Tacotron.py:65-77 ----
+        if mel_targets is None and stop_token_targets is not None:
+            raise ValueError('no mel targets were provided but token_targets were given')
+        if mel_targets is not None and stop_token_targets is None and not GTA:
+            raise ValueError('Mel targets are provided without corresponding token_targets')
+        if not GTA and hp.predict_linear == True and linear_targets is None and is_training:  # noqa: E712
+            raise ValueError('Model is set to use post processing to predict linear spectrograms in training but no linear targets given!')
+        if GTA and linear_targets is not None:
+            raise ValueError('Linear spectrogram prediction is not supported in GTA mode!')
+        if is_training and hp.mask_decoder and targets_lengths is None:
+            raise RuntimeError('Model set to mask paddings but no targets lengths provided for the mask!')
+        if is_training and is_evaluating:
+            raise RuntimeError('Model can not be in training and evaluation modes at the same time!')
+        if is_training:
+            raise FusedStageError("is_training=True (losses, backward, optimizer, dropout / batch statistics) is SURVEY 8f row f1; "
+                                  "the teacher-forced forward pass is available with GTA=True or is_evaluating=True")
+
+        import torch
+        from ... import runtime
+        from ...synthetic import gst_random_weights
+        eng = runtime.engine(hp)
+        G = hp.tacotron_num_gpus
+        inputs = np.asarray(inputs.cpu() if hasattr(inputs, "cpu") else inputs)
+        input_lengths = np.asarray(input_lengths.cpu() if hasattr(input_lengths, "cpu") else input_lengths).astype(np.int32).reshape(-1)
+        if split_infos is None:
+            if G != 1:
+                raise ValueError("split_infos is required when tacotron_num_gpus > 1")
+            split_infos = np.asarray([[inputs.shape[1], 0 if mel_targets is None else np.shape(mel_targets)[1], 0, 0]], np.int32)
+        split_infos = np.asarray(split_infos, np.int32)
+        if split_infos.shape[0] != G:
+            raise ValueError("split_infos has %d rows for %d towers" % (split_infos.shape[0], G))
+        # ---- tower split, Tacotron.py:92-130 (split_func on the host; per-device batch = inputs.shape[0]) ----
+        batch_size = inputs.shape[0]
+        if input_lengths.shape[0] != batch_size * G:
+            raise ValueError("input_lengths has %d entries, expected %d towers x %d" % (input_lengths.shape[0], G, batch_size))
+        tower_input_lengths = np.split(input_lengths, G)
+        p_inputs = split_func(inputs, split_infos[:, 0])
+        p_mel = None
+        if mel_targets is not None:
+            mel_np = np.asarray(mel_targets.cpu() if hasattr(mel_targets, "cpu") else mel_targets, np.float32)
+            p_mel = split_func(mel_np, split_infos[:, 1])
+        self.tower_inputs = [np.ascontiguousarray(p_inputs[i].reshape(batch_size, -1)) for i in range(G)]
+        self.tower_input_lengths = tower_input_lengths
+        self.tower_mel_targets = [] if p_mel is None else [np.ascontiguousarray(p_mel[i].reshape(batch_size, -1, hp.num_mels)) for i in range(G)]
+        self.tower_targets_lengths = None if targets_lengths is None else np.split(np.asarray(targets_lengths), G)
+        self.tower_stop_token_targets = []
+        self.tower_linear_targets = []
+        if reference_mel is not None:
+            reference_mel = torch.as_tensor(np.asarray(reference_mel, np.float32))
+        elif gst_weights is None:
+            gst_weights = gst_random_weights(hp)
+        seed = hp.tacotron_random_seed if philox_seed is None else philox_seed
+
+        self.tower_decoder_output, self.tower_alignments = [], []
+        self.tower_stop_token_prediction, self.tower_mel_outputs = [], []
+        tower_encoder_outputs = []
+        self.tower_steps = []
+        for i in range(G):
+            ids = torch.from_numpy(self.tower_inputs[i].astype(np.int32))
+            lens = torch.from_numpy(tower_input_lengths[i].astype(np.int32))
+            # -- encoder (Tacotron.py:179-224) --
+            enc = Encoder.EncoderCell(Encoder.EncoderConvolution(is_training, hparams=hp, scope='encoder_convolutions'),
+                                      Encoder.EncoderLSTM(is_training, size=hp.enc_lstm_hidden_size, zoneout=hp.zoneout_rate,
+                                                          scope='encoder_LSTM'))
+            enc(ids, lens, reference_mel=reference_mel, gst_weights=gst_weights)
+            encoder_outputs = enc.memory
+            # -- decoder (Tacotron.py:229-284) --
+            prenet = Decoder.Prenet(is_training, layers_sizes=hp.prenet_layers, drop_rate=hp.dropout_rate, scope='decoder_prenet')
+            attention_mechanism = Attention.LocationSensitiveAttention(
+                num_units=hp.attention_dim, memory=encoder_outputs, hparams=hp, mask_encoder=hp.mask_encoder,
+                memory_sequence_length=lens, smoothing=hp.smoothing, cumulate_weights=hp.cumulative_weights)
+            decoder_lstm = Decoder.DecoderRNN(is_training=is_training, layers=2, size=hp.decoder_lstm_units,
+                                              zoneout=hp.zoneout_rate, scope='decoder_LSTM')
+            frame_projection = Decoder.FrameProjection(shape=hp.num_mels * hp.outputs_per_step, scope='linear_transform_projection')
+            stop_projection = Decoder.StopProjection(is_training, shape=hp.outputs_per_step, scope='stop_token_projection')
+            decoder_cell = Decoder.TacotronDecoderCell(prenet, attention_mechanism, decoder_lstm, frame_projection, stop_projection)
+            if is_evaluating or GTA:
+                tgt = torch.from_numpy(self.tower_mel_targets[i])
+                helper = TacoTrainingHelper(batch_size, tgt, hp, GTA, is_evaluating, global_step)
+            else:
+                helper = TacoTestHelper(batch_size, hp)
+            decoder_init_state = decoder_cell.zero_state(batch_size=batch_size)
+            iters = hp.max_iters if max_iters is None else max_iters
+            d = Decoder.CustomDecoder(decoder_cell, helper, decoder_init_state).decode(
+                max_iters=None if (is_evaluating or GTA) else iters, prenet_masks=prenet_masks, philox_seed=seed)
+            S = d["steps"]
+            F = S * hp.outputs_per_step
+            # -- postnet + projection + residual + clip (Tacotron.py:280-309) --
+            decoder_output, mel_outputs = Postnet.Postnet(is_training, hparams=hp, scope='postnet_convolutions')(d["frames"][:, :F])
+            tower_encoder_outputs.append(encoder_outputs)
+            self.tower_decoder_output.append(decoder_output)
+            self.tower_alignments.append(eng.alignments(d["align_hist"], S))    # [B, T, S] (Tacotron.py:312)
+            self.tower_stop_token_prediction.append(d["stop"][:, :F])
+            self.tower_mel_outputs.append(mel_outputs)
+            self.tower_steps.append(S)
+        self.encoder_outputs = tower_encoder_outputs[-1]   # the reference keeps the last tower's (Tacotron.py:224)
+        self.tower_encoder_outputs = tower_encoder_outputs
+        self.all_vars = sorted(runtime.weights(hp).keys())
+        return self
+
+    def add_loss(self):
+        raise FusedStageError("add_loss (Tacotron.py:351-446) is SURVEY 8f row f1")
+
+    def add_optimizer(self, global_step):
+        raise FusedStageError("add_optimizer (Tacotron.py:448-540) is SURVEY 8f row f1")

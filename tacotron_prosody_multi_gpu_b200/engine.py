@@ -113,7 +113,7 @@ class TacoEngine(object):
         return memory
 
     def decode(self, memory, lens, mel_targets=None, max_iters=None, prenet_masks=None, philox_seed=0,
-               reset_state=True, logits_only=False, sync=True):
+               reset_state=True, logits_only=False, sync=True, single_step_at=None):
         """One persistent-kernel launch for all decoder steps.
 
         Returns dict(frames [B, 2*S_max, 80] raw, stop [B, 2*S_max], align_hist [S_max, B, T],
@@ -130,6 +130,9 @@ class TacoEngine(object):
             S_max = F_tgt // r
             if max_iters is not None:
                 S_max = min(S_max, max_iters)
+            if single_step_at is not None:  # `cell(inputs, state)`: step t reads targets[:, r*t - 1]
+                assert F_tgt >= r * single_step_at
+                S_max = 1
             mode = _lib.TACO_MODE_TEACHER
         else:
             S_max = self.hp.max_iters if max_iters is None else max_iters

@@ -206,6 +206,8 @@ def default_hparams():
         lower_bound_decay=0.1,
         tacotron_clip_gradients=True,
         base_dir="",
+        join_output_audio=True,
+        sentences=[],
     )
 
 

@@ -1,0 +1,135 @@
+"""The reference-facing classes driving the C-ABI extension on a real GPU: Tacotron.initialize (inference / GTA,
+1 and 2 towers with split_infos), Synthesizer.synthesize output contract, cell stepping, sharded synthesis."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle.tacotron_oracle import TacotronOracle
+from tacotron_prosody_multi_gpu_b200 import runtime, sharding, synthetic, weights
+from tacotron_prosody_multi_gpu_b200.hparams import default_hparams
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def rt():
+    hp = default_hparams()
+    w = weights.set_stop_bias(weights.init_weights(hp, perturb=0.05), -10.0)
+    runtime.set_precision("fp32")
+    runtime.set_weights(w)
+    yield hp, w
+    runtime.close()
+
+
+def test_tacotron_initialize_inference_two_towers(rt):
+    from tacotron_prosody_multi_gpu_b200.TacotronModel.modules.Tacotron import Tacotron
+    from tacotron_prosody_multi_gpu_b200.Utils.Tacotron_feeder import _prepare_inputs
+    hp, w = rt
+    hp2 = hp.copy()
+    hp2.tacotron_num_gpus = 2
+    idsA, lensA = synthetic.token_batch(hp, [9, 12], seed=1)
+    idsB, lensB = synthetic.token_batch(hp, [7, 5], seed=2)
+    packed = np.concatenate([idsA, idsB], axis=1)                     # per-device blocks along the TIME axis
+    split_infos = np.asarray([[idsA.shape[1], 0, 0, 0], [idsB.shape[1], 0, 0, 0]], np.int32)
+    gw = synthetic.gst_random_weights(hp)
+    m = Tacotron(hp2).initialize(packed, np.concatenate([lensA, lensB]), split_infos=split_infos, gst_weights=gw, max_iters=6, philox_seed=5)
+    assert len(m.tower_mel_outputs) == 2 and m.tower_steps == [6, 6]
+    orc = TacotronOracle(hp, w)
+    for i, (ids, lens) in enumerate(((idsA, lensA), (idsB, lensB))):
+        ref = orc.forward(ids, lens, gst_weights=gw, max_iters=6, philox_seed=5)
+        assert tuple(m.tower_mel_outputs[i].shape) == (2, 12, 80)
+        assert tuple(m.tower_alignments[i].shape) == (2, ids.shape[1], 6)
+        assert tuple(m.tower_stop_token_prediction[i].shape) == (2, 12)
+        np.testing.assert_allclose(m.tower_mel_outputs[i].cpu().numpy(), ref["mel_outputs"].numpy(), atol=1e-3)
+        np.testing.assert_allclose(m.tower_decoder_output[i].cpu().numpy(), ref["decoder_output"].numpy(), atol=5e-4)
+        np.testing.assert_allclose(m.tower_alignments[i].cpu().numpy(), ref["alignments"].numpy(), atol=1e-4)
+    assert tuple(m.encoder_outputs.shape) == (2, idsB.shape[1], 768)
+
+
+def test_tacotron_initialize_gta_teacher_forced(rt):
+    from tacotron_prosody_multi_gpu_b200.TacotronModel.modules.Tacotron import Tacotron
+    hp, w = rt
+    ids, lens = synthetic.token_batch(hp, [8, 11, 6], seed=3)
+    mel, _, _ = synthetic.mel_targets(hp, lens, frames_per_token=1, max_frames=16)
+    gw = synthetic.gst_random_weights(hp)
+    m = Tacotron(hp).initialize(ids, lens, mel_targets=mel, GTA=True, gst_weights=gw, philox_seed=9)
+    ref = TacotronOracle(hp, w).forward(ids, lens, mel_targets=mel, gst_weights=gw, philox_seed=9)
+    assert m.tower_steps[0] == mel.shape[1] // 2 == ref["steps"]
+    np.testing.assert_allclose(m.tower_mel_outputs[0].cpu().numpy(), ref["mel_outputs"].numpy(), atol=1e-3)
+    np.testing.assert_allclose(m.tower_stop_token_prediction[0].cpu().numpy(), ref["stop"].numpy(), atol=5e-4)
+
+
+def test_cell_stepping_through_class_api(rt):
+    """TacotronDecoderCell.__call__(inputs, state) chained by CustomDecoder.step == one dynamic_decode launch."""
+    from tacotron_prosody_multi_gpu_b200.TacotronModel.modules import Attention, Decoder
+    from tacotron_prosody_multi_gpu_b200.Utils.Helpers import TacoTestHelper
+    hp, w = rt
+    eng = runtime.engine(hp)
+    ids, lens = synthetic.token_batch(hp, [10, 8])
+    memory = torch.from_numpy((np.random.default_rng(8).standard_normal((2, 10, 768)) * 0.5).astype(np.float32)).cuda()
+    am = Attention.LocationSensitiveAttention(hp.attention_dim, memory, hp, memory_sequence_length=torch.from_numpy(lens))
+    cell = Decoder.TacotronDecoderCell(Decoder.Prenet(False, hp.prenet_layers), am, Decoder.DecoderRNN(False, 2, 256, hp.zoneout_rate),
+                                       Decoder.FrameProjection(160), Decoder.StopProjection(False, 2))
+    S = 4
+    whole = eng.decode(memory, torch.from_numpy(lens), max_iters=S, philox_seed=0)
+    dec = Decoder.CustomDecoder(cell, TacoTestHelper(2, hp), cell.zero_state(2))
+    finished, inputs, state = dec.initialize()
+    frames = []
+    for t in range(S):
+        out, state, inputs, fin = dec.step(t, inputs, state)
+        frames.append(out.rnn_output.reshape(2, 2, 80))
+        assert state.time == t + 1 and len(state.alignment_history) == t + 1
+    np.testing.assert_allclose(torch.cat(frames, 1).cpu().numpy(), whole["frames"].cpu().numpy(), atol=1e-5)
+    np.testing.assert_allclose(torch.stack(state.alignment_history).cpu().numpy(), whole["align_hist"].cpu().numpy(), atol=1e-6)
+    with pytest.raises(NotImplementedError):
+        cell(inputs, state.replace(time=2))      # a stale state cannot be continued
+
+
+def test_synthesizer_output_contract(rt, tmp_path):
+    from tacotron_prosody_multi_gpu_b200.Utils.Tacotron_synthesizer import Synthesizer
+    hp, w = rt
+    hp2 = hp.copy()
+    hp2.tacotron_num_gpus = 2
+    # stop parity config: scaled stop projection so that the batch-global stop fires mid-sequence
+    w2 = weights.scale_stop_projection(weights.init_weights(hp, perturb=0.05), 8.0, 0.0)
+    ck = str(tmp_path / "taco.npz")
+    weights.save(ck, w2)
+    synth = Synthesizer().load(ck, hp2, GTA=False)
+    seqs = [synthetic.token_batch(hp, [n], seed=n)[0][0] for n in (9, 13, 7)]   # 3 texts -> padded to 4 (2 towers x 2)
+    out_dir = tmp_path / "inference"
+    out_dir.mkdir()
+    gw = synthetic.gst_random_weights(hp)
+    paths, speakers = synth.synthesize(seqs, ["a", "b", "c"], str(out_dir), None, None, gst_weights=gw, max_iters=30)
+    assert len(paths) == 4 and speakers == ['<no_g>'] * 4 and os.path.basename(paths[0]) == "speech-mel-a.npy"
+    orc = TacotronOracle(hp, w2)
+    from tacotron_prosody_multi_gpu_b200.Utils.Tacotron_feeder import _get_output_lengths, _prepare_inputs
+    for g in range(2):
+        tower = (seqs + [seqs[-1]])[2 * g: 2 * g + 2]
+        ids, _ = _prepare_inputs(tower)
+        ref = orc.forward(ids.astype(np.int32), np.asarray([len(s) for s in tower], np.int32), gst_weights=gw, max_iters=30,
+                          philox_seed=hp.tacotron_random_seed)
+        keep = _get_output_lengths(ref["stop"].numpy())
+        for j in range(2):
+            mel = np.load(paths[2 * g + j])
+            assert mel.dtype == np.float32 and mel.shape == (keep[j], 80)          # bit-exact output lengths
+            np.testing.assert_allclose(mel, np.clip(ref["mel_outputs"].numpy()[j, :keep[j]], -4, 4), atol=2e-3)
+    runtime.set_weights(w)
+
+
+def test_sharded_synthesis_equals_unsharded(rt):
+    hp, w = rt
+    eng = runtime.engine(hp)
+    seqs = [synthetic.token_batch(hp, [n], seed=100 + n)[0][0] for n in (5, 9, 7, 12, 6, 10, 8, 11, 4)]
+    gw = synthetic.gst_random_weights(hp)
+    one = sharding.synthesize_batches(eng, hp, seqs, 0, 1, batch_size=2, gst_weights=gw, max_iters=5)
+    assert sorted(one) == list(range(9))
+    merged = {}
+    for r in range(4):
+        part = sharding.synthesize_batches(eng, hp, seqs, r, 4, batch_size=2, gst_weights=gw, max_iters=5)
+        assert not (set(part) & set(merged))
+        merged.update(part)
+    assert sorted(merged) == list(range(9))
+    for i in range(9):
+        assert np.array_equal(one[i]["mel"], merged[i]["mel"])      # same batch composition -> bit-identical
