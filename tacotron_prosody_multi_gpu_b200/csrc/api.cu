@@ -72,6 +72,10 @@ struct TacoHandle {
     // dataflow decoder (decoder2.cu): fragment-major bf16 shards and fused location kernel
     uint32_t *dec2_blob = nullptr, *dec2_wq = nullptr, *dec2_ghi = nullptr, *dec2_glo = nullptr;
     float* dec2_bconst = nullptr;
+    // cluster decoder (decoder3.cu): per-rank resident A-fragment tiles + L2-streamed tiles
+    uint32_t* dec3_res = nullptr;
+    uint32_t* dec3_stream = nullptr;
+    int dec3_max_clusters = -1;  // cudaOccupancyMaxActiveClusters of decoder3_kernel (queried once)
     int dec_kind = 0;            // which decoder kernel owns the running state (1 = decoder.cu, 2 = decoder2.cu)
     float* bilstm_blob[2] = {};  // same two configs, [2 dir][GN][256*4U]
     // decoder running state
@@ -403,6 +407,89 @@ int pack_decoder2(TacoHandle* h) {
     return upload(h, bconst, &h->dec2_bconst);
 }
 
+
+// Shards for decoder3.cu: per cluster rank c (units 16c..16c+15) the mma.sync m16n8k16 A-fragments (weights^T:
+// rows = output columns, cols = k) of its tiles: word [lane = 4g+t][reg] = bf16 pair
+// (W[k0 + 2t + 8(reg>>1)][m = g + 8(reg&1)], W[k0 + 2t + 8(reg>>1) + 1][m]).
+int pack_decoder3(TacoHandle* h) {
+    const Weight *k1, *b1, *k2, *b2, *kp1, *bp1, *kp2, *bp2, *kq, *kf, *bf, *kst, *bst;
+    int rc;
+#define NEED(var, name, ...) \
+    if ((rc = need(h, name, {__VA_ARGS__}, &var))) return rc;
+    NEED(k1, std::string(DEC_LSTM1) + "/kernel", 1280, 1024)
+    NEED(b1, std::string(DEC_LSTM1) + "/bias", 1024)
+    NEED(k2, std::string(DEC_LSTM2) + "/kernel", 512, 1024)
+    NEED(b2, std::string(DEC_LSTM2) + "/bias", 1024)
+    NEED(kp1, fmt(PRENET, 1) + "/kernel", 80, 256)
+    NEED(bp1, fmt(PRENET, 1) + "/bias", 256)
+    NEED(kp2, fmt(PRENET, 2) + "/kernel", 256, 256)
+    NEED(bp2, fmt(PRENET, 2) + "/bias", 256)
+    NEED(kq, std::string(LSA) + "/query_layer/kernel", 256, 128)
+    NEED(kf, std::string(FRAME_PROJ) + "/kernel", 1024, 160)
+    NEED(bf, std::string(FRAME_PROJ) + "/bias", 160)
+    NEED(kst, std::string(STOP_PROJ) + "/kernel", 1024, 2)
+    NEED(bst, std::string(STOP_PROJ) + "/bias", 2)
+#undef NEED
+    auto pack_tile = [](uint32_t* dst, auto get) {   // get(k in 0..15, m in 0..15)
+        for (int lane = 0; lane < 32; ++lane) {
+            const int g = lane >> 2, t = lane & 3;
+            for (int reg = 0; reg < 4; ++reg) {
+                const int m = g + 8 * (reg & 1), k = 2 * t + 8 * (reg >> 1);
+                dst[lane * 4 + reg] = pack2(get(k, m), get(k + 1, m));
+            }
+        }
+    };
+    const int RW = TACO_DEC3_RES_WORDS, SW = TACO_DEC3_STREAM_TILES * 128;
+    std::vector<uint32_t> res((size_t)16 * RW, 0u), str((size_t)16 * SW, 0u);
+    for (int c = 0; c < 16; ++c) {
+        uint32_t* p = res.data() + (size_t)c * RW;
+        for (int ks = 0; ks < 64; ++ks)   // frame / stop projection of [LSTM output ; context] (Decoder.py:273-279)
+            pack_tile(p + ks * 128, [&](int k, int m) {
+                const int kk = ks * 16 + k;
+                if (c < 10) return kf->host[(size_t)kk * 160 + 16 * c + m];
+                if (c == 10 && m < 2) return kst->host[(size_t)kk * 2 + m];
+                return 0.f;
+            });
+        p += 64 * 128;
+        for (int ks = 0; ks < 5; ++ks) pack_tile(p + ks * 128, [&](int k, int m) { return kp1->host[(size_t)(ks * 16 + k) * 256 + 16 * c + m]; });
+        p += 5 * 128;
+        for (int ks = 0; ks < 16; ++ks) pack_tile(p + ks * 128, [&](int k, int m) { return kp2->host[(size_t)(ks * 16 + k) * 256 + 16 * c + m]; });
+        p += 16 * 128;
+        for (int mt = 0; mt < 4; ++mt)
+            for (int ks = 0; ks < 16; ++ks)
+                pack_tile(p + (mt * 16 + ks) * 128, [&](int k, int m) { return k1->host[(size_t)(ks * 16 + k) * 1024 + mt * 256 + 16 * c + m]; });
+        p += 64 * 128;
+        for (int mt = 0; mt < 4; ++mt)
+            for (int ks = 0; ks < 16; ++ks)
+                pack_tile(p + (mt * 16 + ks) * 128, [&](int k, int m) { return k2->host[(size_t)(ks * 16 + k) * 1024 + mt * 256 + 16 * c + m]; });
+        p += 64 * 128;
+        for (int mt = 0; mt < 8; ++mt) pack_tile(p + mt * 128, [&](int k, int m) { return kq->host[(size_t)(16 * c + k) * 128 + mt * 16 + m]; });
+        p += 8 * 128;
+        float* bias = reinterpret_cast<float*>(p);
+        for (int gt = 0; gt < 4; ++gt)
+            for (int u = 0; u < 16; ++u) {
+                bias[gt * 16 + u] = b1->host[gt * 256 + 16 * c + u];
+                bias[64 + gt * 16 + u] = b2->host[gt * 256 + 16 * c + u];
+            }
+        for (int u = 0; u < 16; ++u) {
+            bias[128 + u] = bp1->host[16 * c + u];
+            bias[144 + u] = bp2->host[16 * c + u];
+            bias[160 + u] = c < 10 ? bf->host[16 * c + u] : ((c == 10 && u < 2) ? bst->host[u] : 0.f);
+        }
+        uint32_t* q = str.data() + (size_t)c * SW;
+        for (int mt = 0; mt < 4; ++mt) {
+            for (int ks = 0; ks < 48; ++ks)   // LSTM-1 kernel rows of the context [256, 1024)
+                pack_tile(q + (mt * 48 + ks) * 128, [&](int k, int m) { return k1->host[(size_t)(256 + ks * 16 + k) * 1024 + mt * 256 + 16 * c + m]; });
+            for (int ks = 0; ks < 16; ++ks) {  // LSTM-1 rows of h1 [1024, 1280); LSTM-2 rows of h2 [256, 512)
+                pack_tile(q + (192 + mt * 16 + ks) * 128, [&](int k, int m) { return k1->host[(size_t)(1024 + ks * 16 + k) * 1024 + mt * 256 + 16 * c + m]; });
+                pack_tile(q + (256 + mt * 16 + ks) * 128, [&](int k, int m) { return k2->host[(size_t)(256 + ks * 16 + k) * 1024 + mt * 256 + 16 * c + m]; });
+            }
+        }
+    }
+    if ((rc = upload_words(h, res, &h->dec3_res))) return rc;
+    return upload_words(h, str, &h->dec3_stream);
+}
+
 const float* dev_w(TacoHandle* h, const std::string& name) {
     const Weight* w = find_w(h, name);
     return w ? w->dev : nullptr;
@@ -424,6 +511,14 @@ __global__ void untranspose_xt_kernel(const float* __restrict__ xt, float* __res
     if (i >= B * K) return;
     int b = i / K, k = i % K;
     out[i] = xt[((size_t)(b / RBP) * K + k) * RBP + (b % RBP)];
+}
+
+// teacher-forced continuation (`cell(inputs, state)`): x(t0) = targets[:, r*t0 - 1] into the XT exchange block
+__global__ void load_xt_from_targets_kernel(const float* __restrict__ targets, int F_tgt, int fidx, float* __restrict__ xt, int B, int RBP) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= B * 80) return;
+    const int b = i / 80, k = i % 80;
+    xt[((size_t)(b / RBP) * 80 + k) * RBP + (b % RBP)] = fidx < F_tgt ? targets[((size_t)b * F_tgt + fidx) * 80 + k] : 0.f;
 }
 
 int conv(TacoHandle* h, const float* x, long long x_stride, long long x_bstride, const float* w, const float* scale,
@@ -543,6 +638,98 @@ int decode_v2(TacoHandle* h, int mode, const float* memory, const int32_t* lens,
     h->launches++;
     h->dec_t += S_max;
     h->dec_B = B; h->dec_T = T; h->dec_kind = 2;
+    return TACO_OK;
+}
+
+// taco_decode through the cluster kernel (decoder3.cu) -- TACO_PRECISION_BF16 when 16-CTA clusters can be scheduled
+int decode_v3(TacoHandle* h, int mode, const float* memory, const int32_t* lens, int B, int T, const float* mel_targets,
+              int F_tgt, int S_max, const uint8_t* prenet_masks, uint64_t philox_seed, int reset_state, int logits_only,
+              float* frames, float* stop, float* align_hist, int32_t* steps_out, cudaStream_t st) {
+    const TacoHParams& hp = h->hp;
+    Dec3Params p;
+    memset(&p, 0, sizeof p);
+    p.B = B; p.T = T;
+    // batch rows are split over clusters; <= 8 rows per cluster keeps one n-tile, more clusters shorten every exchange
+    int ncl = (B + 7) / 8;
+    if (getenv("TACO_DEC3_NCL")) ncl = atoi(getenv("TACO_DEC3_NCL"));
+    if (ncl > h->dec3_max_clusters) ncl = h->dec3_max_clusters;
+    if (ncl < (B + 15) / 16) FAIL(TACO_ERR_UNSUPPORTED, "taco_decode: batch needs more co-resident 16-CTA clusters than this device schedules");
+    if (ncl < 1) ncl = 1;
+    p.R = (B + ncl - 1) / ncl;
+    p.NCL = (B + p.R - 1) / p.R;
+    p.S_max = S_max; p.S_cap = S_max; p.mode = mode;
+    p.stop_at_any = hp.stop_at_any; p.cumulative = hp.cumulative_weights; p.smoothing = hp.smoothing;
+    p.stop_sigmoid = logits_only ? 0 : 1;
+    p.pre_reg = T <= 128 ? 1 : 0;
+    p.zoneout = hp.zoneout_rate;
+    p.keep_scale = 1.0f / (1.0f - hp.dropout_rate);
+    p.res_blobs = h->dec3_res;
+    p.stream_blobs = reinterpret_cast<const uint4*>(h->dec3_stream);
+    p.g_hi = h->dec2_ghi; p.g_lo = h->dec2_glo;
+    p.va = dev_w(h, std::string(LSA) + "/attention_variable");
+    p.bconst = h->dec2_bconst;
+    if (!reset_state && (h->dec_kind != 3 || h->dec_B != B || h->dec_T != T))
+        FAIL(TACO_ERR_STATE, "taco_decode: continuing with a different batch shape or precision");
+    WS(lens_eff, int32_t, "dec_lens", B)
+    if (hp.mask_encoder) {
+        CK(cudaMemcpyAsync(lens_eff, lens, B * sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
+    } else {
+        std::vector<int32_t> full(B, T);
+        CK(cudaMemcpyAsync(lens_eff, full.data(), B * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+        CK(cudaStreamSynchronize(st));
+    }
+    p.lens = lens_eff;
+    WS(keys, float, "dec_keys", (size_t)B * T * 128)
+    WS(vals, uint16_t, "dec2_values", (size_t)B * T * 768)
+    if (reset_state) {
+        int rc = conv(h, memory, 768, (long long)T * 768, dev_w(h, std::string(MEMORY_LAYER) + "/kernel"), nullptr, nullptr, keys, 128,
+                      (long long)T * 128, nullptr, B, T, 768, 128, 1, ACT_NONE, false, 0, 0, st);
+        if (rc) return rc;
+        CK(taco_launch_f32_to_bf16(memory, vals, (size_t)B * T * 768, st));
+        h->launches++;
+    }
+    p.keys = keys;
+    p.values = vals;
+    // recurrent state (fp32 row-major): c1 h1z c2 h2z [B][256], ctx [B][768], x [B][80], cum [B][T]
+    const size_t n_state = (size_t)B * (4 * 256 + 768 + 80 + T);
+    WS(state, float, "dec2_state", n_state)
+    if (reset_state) {
+        CK(cudaMemsetAsync(state, 0, n_state * sizeof(float), st));
+        h->dec_t = 0;
+    }
+    float* s = state;
+    p.c1 = s; s += (size_t)B * 256;
+    p.h1z = s; s += (size_t)B * 256;
+    p.c2 = s; s += (size_t)B * 256;
+    p.h2z = s; s += (size_t)B * 256;
+    p.ctx_state = s; s += (size_t)B * 768;
+    p.x_state = s; s += (size_t)B * 80;
+    p.cum = s;
+    if (!p.pre_reg) {
+        WS(pre, float, "dec3_pre", (size_t)B * T * 128)
+        p.pre_scratch = pre;
+    }
+    p.t0 = h->dec_t;
+    p.targets = mel_targets; p.F_tgt = F_tgt;
+    p.masks = prenet_masks; p.seed = philox_seed;
+    p.frames = frames; p.stop = stop; p.hist = align_hist; p.steps_out = steps_out;
+    const size_t n_flags = (size_t)S_max * p.NCL + 8;
+    WS(flags, int, "dec3_flags", n_flags)
+    CK(cudaMemsetAsync(flags, 0, n_flags * sizeof(int), st));
+    p.flags = flags;
+    p.abort_flag = flags + (size_t)S_max * p.NCL + 4;
+    if (getenv("TACO_DEC2_TIMING")) {
+        WS(timing, long long, "dec2_timing", (size_t)TACO_DEC3_CLUSTER * TACO_DEC3_MAX_CLUSTERS * 16)
+        CK(cudaMemsetAsync(timing, 0, (size_t)TACO_DEC3_CLUSTER * TACO_DEC3_MAX_CLUSTERS * 16 * sizeof(long long), st));
+        p.timing = timing;
+    }
+    CK(cudaEventRecord(h->ev[TACO_STAGE_DECODER_KERNEL][0], st));
+    CK(taco_launch_decoder3(p, st));
+    CK(cudaEventRecord(h->ev[TACO_STAGE_DECODER_KERNEL][1], st));
+    h->ev_valid[TACO_STAGE_DECODER_KERNEL] = true;
+    h->launches++;
+    h->dec_t += S_max;
+    h->dec_B = B; h->dec_T = T; h->dec_kind = 3;
     return TACO_OK;
 }
 
@@ -668,6 +855,7 @@ int taco_finalize_weights(TacoHandle* h) {
         if ((rc = fold_bn(h, fmt(REF_CONV, i), "conv2d", eps, &h->ref_scale[i], &h->ref_shift[i]))) return rc;
     if ((rc = pack_decoder_blobs(h))) return rc;
     if ((rc = pack_decoder2(h))) return rc;
+    if ((rc = pack_decoder3(h))) return rc;
     const char* required[] = {"inputs_embedding", "style_tokens"};
     for (const char* r : required)
         if (!find_w(h, r)) FAIL(TACO_ERR_MISSING_WEIGHT, std::string("missing variable ") + r);
@@ -848,6 +1036,18 @@ int taco_decode(TacoHandle* h, int mode, const float* memory, const int32_t* len
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     CK(cudaSetDevice(h->device));
     const TacoHParams& hp = h->hp;
+    if (h->precision == TACO_PRECISION_BF16 && h->dec3_max_clusters < 0) {
+        int n = 0;
+        if (taco_decoder3_max_clusters(&n) != cudaSuccess) {
+            cudaGetLastError();
+            n = 0;
+        }
+        h->dec3_max_clusters = n > TACO_DEC3_MAX_CLUSTERS ? TACO_DEC3_MAX_CLUSTERS : n;
+    }
+    const char* force = getenv("TACO_DECODER");   // "2": dataflow kernel through L2 (decoder2.cu), kept for comparison
+    if (h->precision == TACO_PRECISION_BF16 && T <= TACO_DEC3_TMAX && h->dec3_max_clusters * 16 >= B && !(force && force[0] == '2'))
+        return decode_v3(h, mode, memory, lens, B, T, mel_targets, F_tgt, S_max, prenet_masks, philox_seed, reset_state, logits_only,
+                         frames, stop, align_hist, steps_out, st);
     if (h->precision == TACO_PRECISION_BF16 && T <= TACO_DEC2_TMAX)
         return decode_v2(h, mode, memory, lens, B, T, mel_targets, F_tgt, S_max, prenet_masks, philox_seed, reset_state, logits_only,
                          frames, stop, align_hist, steps_out, st);
@@ -930,6 +1130,11 @@ int taco_decode(TacoHandle* h, int mode, const float* memory, const int32_t* len
     p.masks = prenet_masks;
     p.seed = philox_seed;
     p.frames = frames; p.stop = stop; p.hist = align_hist; p.steps_out = steps_out;
+    if (mode == TACO_MODE_TEACHER && !reset_state && p.t0 > 0) {
+        load_xt_from_targets_kernel<<<(B * 80 + 255) / 256, 256, 0, st>>>(mel_targets, F_tgt, p.t0 * hp.outputs_per_step - 1, p.xT, B, p.RBP);
+        CK(cudaGetLastError());
+        h->launches++;
+    }
     WS(cnt, int, "dec_stop_count", (size_t)S_max + 8)
     CK(cudaMemsetAsync(cnt, 0, ((size_t)S_max + 8) * sizeof(int), st));
     p.stop_count = cnt;
@@ -1054,7 +1259,7 @@ int taco_get_decoder_state(TacoHandle* h, int B, int T, float* c1, float* h1, fl
     if (h->dec_B != B || h->dec_T != T) FAIL(TACO_ERR_STATE, "taco_get_decoder_state: no decoder state of that shape");
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     CK(cudaSetDevice(h->device));
-    if (h->dec_kind == 2) {
+    if (h->dec_kind == 2 || h->dec_kind == 3) {
         auto it2 = h->ws.find("dec2_state");
         if (it2 == h->ws.end()) FAIL(TACO_ERR_STATE, "no decoder state");
         const float* s = reinterpret_cast<const float*>(it2->second.p);

@@ -1,0 +1,291 @@
+// Persistent CLUSTER decoder kernel (sm_100a): thread-block clusters of 16 CTAs, exchanges through
+// distributed shared memory, bf16 mma.sync contractions, fp32 state.
+//
+// Computes TacotronDecoderCell.__call__ for every decoder step (reference Decoder.py:246-292;
+// CustomDecoder.step / helpers, Decoder.py:117-146, Utils/Helpers.py:36-59,115-128;
+// LocationSensitiveAttention, Attention.py:169-210,345-401) like decoder2.cu, but decomposed by what
+// the measurements in tools/microbench_hop.cu say bounds a step on B200:
+//   one L2 hop (st.relaxed.gpu -> polled ld.relaxed.gpu)   0.45 us,  128-CTA all-gather through L2 1.6-2.2 us
+//   one DSMEM hop (st.shared::cluster -> local smem poll)   0.19 us,  16-CTA all-gather through DSMEM 0.5 us
+// so the batch is split over CLUSTERS (rows r0..r0+R-1 per cluster, no inter-cluster traffic except the
+// batch-global stop bit) and inside a cluster every activation vector is exchanged through DSMEM:
+//
+//  * CTA rank c of a cluster owns units 16c..16c+15 of every layer (64 LSTM gate columns, 16 prenet
+//    columns, 16 projection columns) for ALL rows of the cluster, and the attention of cluster row c.
+//  * mma.sync.m16n8k16: A = weight tile [16 output columns x 16 k] (fragment-major in shared memory for
+//    the phases on the critical path, streamed fragment-major from L2 for the contributions that only
+//    depend on step s-1), B = activations [16 k x 8 rows] read from the CTA's own shared memory.
+//  * "Data is the flag": a producer multicasts its bf16 pairs straight into every peer's activation
+//    buffer (st.shared::cluster.v4); buffers are pre-filled with the sentinel 0xFFFFFFFF (two bf16 NaNs);
+//    consumers poll their LOCAL shared memory while loading the B fragments and re-arm the buffer after
+//    use.  No fences, no mbarriers, no grid barrier.
+//  * query projection without a resident Wq: q = h2raw.Wq is K-split -- CTA c contracts its own 16 units
+//    (one k-step) for all rows and sends each row's partial [128] to the CTA that owns the row's attention.
+//  * batch-global stop (Helpers.py:51-52) across clusters: one flag word per (step, cluster) in global
+//    memory, consumed two steps late (speculative steps are discarded), so no step waits on L2.
+#include <cooperative_groups.h>
+#include <cuda_bf16.h>
+
+#include "common.cuh"
+#include "taco_internal.h"
+
+namespace cg = cooperative_groups;
+
+namespace {
+
+constexpr int CS = TACO_DEC3_CLUSTER;  // 16 CTAs per cluster
+constexpr int NT = TACO_THREADS;       // 512 threads = 16 warps
+constexpr int MEL = 80, PRE = 256, DEC = 256, MEM = 768, ATT = 128;
+constexpr uint32_t SENT = 0xFFFFFFFFu;
+constexpr int T_MAX3 = TACO_DEC3_TMAX;  // 512
+constexpr int PRE_REG_T = 128;          // T <= 128: location pre-activations live in registers
+constexpr int KS_X = 5, KS_H = 16, KS_CTX = 48;
+constexpr int TILE_W = 128;             // words of one A tile (32 lanes x uint4) and of one B k-step block (2 n-tiles x 32 lanes x uint2)
+
+// ---- shared-memory map (32-bit word offsets) ----
+constexpr int SO_WO = 0;                          // [64 ks] frame/stop projection tiles (ks 0..15: h2raw, 16..63: context)
+constexpr int SO_WP1 = SO_WO + 64 * TILE_W;       // [5]
+constexpr int SO_WP2 = SO_WP1 + 5 * TILE_W;       // [16]
+constexpr int SO_W1P = SO_WP2 + 16 * TILE_W;      // [4 mt][16 ks]  LSTM-1, prenet-output rows
+constexpr int SO_W2H = SO_W1P + 64 * TILE_W;      // [4 mt][16 ks]  LSTM-2, h1raw rows
+constexpr int SO_WQ = SO_W2H + 64 * TILE_W;       // [8 mt]         query kernel rows of this CTA's 16 units
+constexpr int SO_BIAS = SO_WQ + 8 * TILE_W;       // b1[64] b2[64] bp1[16] bp2[16] bo[16]
+constexpr int RES_WORDS = SO_BIAS + 176;          // resident blob words per rank
+constexpr int SO_X = RES_WORDS;                   // activation buffers (B-fragment order, one 128-word block per k-step)
+constexpr int SO_P1 = SO_X + KS_X * TILE_W;
+constexpr int SO_P2 = SO_P1 + KS_H * TILE_W;
+constexpr int SO_H1R = SO_P2 + KS_H * TILE_W;
+constexpr int SO_H1Z = SO_H1R + KS_H * TILE_W;
+constexpr int SO_H2R = SO_H1Z + KS_H * TILE_W;
+constexpr int SO_H2Z = SO_H2R + KS_H * TILE_W;
+constexpr int SO_CTX = SO_H2Z + KS_H * TILE_W;
+constexpr int SO_RED = SO_CTX + KS_CTX * TILE_W;  // 4352 floats: K-split partials; aliased as attention scratch
+constexpr int RED_WORDS = 16 * 16 * 17;
+constexpr int SO_QRECV = SO_RED + RED_WORDS;      // [16 src][128] fp32 query partials of this CTA's attention row
+constexpr int SO_STG_R = SO_QRECV + 16 * ATT;     // staging: raw block, zoned block, context row
+constexpr int SO_STG_Z = SO_STG_R + TILE_W;
+constexpr int SO_STG_C = SO_STG_Z + TILE_W;       // [48 ks][8 words]
+constexpr int SO_ES = SO_STG_C + KS_CTX * 8;      // [T_MAX3]
+constexpr int SO_CPAD = SO_ES + T_MAX3;           // [T_MAX3 + 48]  cpad[i] = cum[i - 15]
+constexpr int PW3 = (T_MAX3 + 48) / 2;
+constexpr int SO_P = SO_CPAD + T_MAX3 + 48;       // 4 x [PW3] pair arrays P0hi, P1hi, P0lo, P1lo
+constexpr int SO_QS = SO_P + 4 * PW3;             // [128]
+constexpr int SO_VA = SO_QS + ATT;
+constexpr int SO_BC = SO_VA + ATT;
+constexpr int SO_FLAG = SO_BC + ATT;              // [8]
+constexpr int SO_TACC = SO_FLAG + 8;              // 16 x int64 stage timers
+constexpr int SMEM3_WORDS = SO_TACC + 32;
+static_assert(RES_WORDS == TACO_DEC3_RES_WORDS, "resident blob size");
+static_assert(SMEM3_WORDS * 4 <= 227 * 1024, "shared memory budget");
+static_assert(SO_X % 4 == 0 && SO_RED % 4 == 0 && SO_QRECV % 4 == 0 && SO_STG_R % 4 == 0 && SO_STG_C % 4 == 0 && SO_ES % 4 == 0 &&
+              SO_QS % 4 == 0 && SO_TACC % 2 == 0, "smem alignment");
+
+extern __shared__ __align__(16) uint32_t smem3[];
+#define SMU(off) (smem3 + (off))
+#define SMF(off) (reinterpret_cast<float*>(smem3 + (off)))
+
+struct Guard3 {
+    int* abort_flag;
+    bool dead;
+};
+
+__device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ uint32_t mapa_rank(uint32_t addr, uint32_t rank) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ void st_remote_v4(uint32_t addr, const uint4& v) {
+    asm volatile("st.shared::cluster.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+__device__ __forceinline__ uint2 lds_poll_v2(const uint32_t* p) {
+    uint2 v;
+    asm volatile("ld.volatile.shared.v2.u32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(smem_addr(p)) : "memory");
+    return v;
+}
+__device__ __forceinline__ uint4 lds_poll_v4(const uint32_t* p) {
+    uint4 v;
+    asm volatile("ld.volatile.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(smem_addr(p)) : "memory");
+    return v;
+}
+__device__ __forceinline__ uint32_t ldg_relaxed(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void stg_relaxed(uint32_t* p, uint32_t v) {
+    asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint4 ldg_stream_v4(const uint4* p) {
+    uint4 v;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+    return v;
+}
+
+// bounded spin: a poll that never completes (a bug, not a data condition) raises the abort flag instead of
+// hanging the GPU; once raised every poll in every CTA falls through.
+__device__ __forceinline__ bool spin_check3(Guard3& g, int& spins) {
+    if (((++spins) & 1023) == 0) {
+        if (*reinterpret_cast<volatile int*>(g.abort_flag) != 0) g.dead = true;
+        if (spins > (1 << 24)) {
+            atomicExch(g.abort_flag, 1);
+            g.dead = true;
+        }
+    }
+    return g.dead;
+}
+
+__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
+    __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
+    return *reinterpret_cast<uint32_t*>(&h);
+}
+__device__ __forceinline__ float bf_lo(uint32_t w) { return __uint_as_float(w << 16); }
+__device__ __forceinline__ float bf_hi(uint32_t w) { return __uint_as_float(w & 0xFFFF0000u); }
+
+__device__ __forceinline__ void mma16816(float (&c)[4], const uint4& a, const uint2& b) {
+    asm volatile(
+        "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+        : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+        : "r"(a.x), "r"(a.y), "r"(a.z), "r"(a.w), "r"(b.x), "r"(b.y));
+}
+
+__device__ __forceinline__ float tanh_apx(float x) {
+    float y;
+    asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+__device__ __forceinline__ float sigmoid_f(float x) { return __fdividef(1.0f, 1.0f + __expf(-x)); }
+__device__ __forceinline__ float tanh_f(float x) { return 1.0f - __fdividef(2.0f, __expf(2.0f * x) + 1.0f); }
+
+// word offset, inside a 128-word B block, of the bf16 pair (row r, k-pair j = 0..7 of the k-step)
+__device__ __forceinline__ int bword(int r, int j) { return ((r >> 3) << 6) + ((((r & 7) << 2) | (j & 3)) << 1) + (j >> 2); }
+
+// B fragment of (k-step block, n-tile j) for this lane, polling while a producer has not written it yet
+__device__ __forceinline__ uint2 load_b(const uint32_t* blk, int j, int lane, Guard3& g) {
+    const uint32_t* p = blk + (j << 6) + (lane << 1);
+    uint2 b = lds_poll_v2(p);
+    int spins = 0;
+    while (!g.dead && __any_sync(0xffffffffu, b.x == SENT || b.y == SENT)) {
+        if (spin_check3(g, spins)) break;
+        b = lds_poll_v2(p);
+    }
+    g.dead = __any_sync(0xffffffffu, g.dead);
+    return b;
+}
+
+// acc[j] += A(tile) . B(block ks, n-tile j) over this warp's k-steps ks = k0, k0 + kstride, ... < KS
+// A tiles: a_tiles + (ks * a_ks_stride) words, fragment-major in shared memory.
+template <int NTL>
+__device__ __forceinline__ void gemm_smem(float (&acc)[2][4], const uint32_t* a_tiles, int a_ks_stride, const uint32_t* bbuf, int KS,
+                                          int k0, int kstride, int lane, Guard3& g) {
+    for (int ks = k0; ks < KS; ks += kstride) {
+        const uint4 a = *reinterpret_cast<const uint4*>(a_tiles + ks * a_ks_stride + (lane << 2));
+#pragma unroll
+        for (int j = 0; j < NTL; ++j) {
+            const uint2 b = load_b(bbuf + ks * TILE_W, j, lane, g);
+            mma16816(acc[j], a, b);
+        }
+    }
+}
+
+// same with the A tiles streamed from global memory (L2-resident, fragment-major): tiles at a_glob + ks * a_ks_stride (uint4 units)
+template <int NTL, int CH>
+__device__ __forceinline__ void gemm_stream(float (&acc)[2][4], const uint4* a_glob, int a_ks_stride, const uint32_t* bbuf, int KS, int k0,
+                                            int kstride, int lane, Guard3& g) {
+    for (int ksb = k0; ksb < KS; ksb += CH * kstride) {
+        uint4 a[CH];
+#pragma unroll
+        for (int i = 0; i < CH; ++i) {
+            const int ks = ksb + i * kstride;
+            if (ks < KS) a[i] = ldg_stream_v4(a_glob + (size_t)ks * a_ks_stride + lane);
+        }
+#pragma unroll
+        for (int i = 0; i < CH; ++i) {
+            const int ks = ksb + i * kstride;
+            if (ks < KS) {
+#pragma unroll
+                for (int j = 0; j < NTL; ++j) {
+                    const uint2 b = load_b(bbuf + ks * TILE_W, j, lane, g);
+                    mma16816(acc[j], a[i], b);
+                }
+            }
+        }
+    }
+}
+
+// partial accumulators of warp (mt, kg) -> red[((kg * MTN + mt) * 16 + m) * 17 + n]
+__device__ __forceinline__ void store_red3(float* red, const float (&acc)[2][4], int slot, int lane, int ntl) {
+    const int gq = lane >> 2, tq = lane & 3;
+    float* r0 = red + (slot * 16 + gq) * 17 + 2 * tq;
+    for (int j = 0; j < ntl; ++j) {
+        r0[8 * j] = acc[j][0];
+        r0[8 * j + 1] = acc[j][1];
+        r0[8 * 17 + 8 * j] = acc[j][2];
+        r0[8 * 17 + 8 * j + 1] = acc[j][3];
+    }
+}
+
+// re-arm a consumed activation buffer: valid rows -> sentinel, padding rows -> 0 (they have no producer)
+__device__ __forceinline__ void rearm(uint32_t* buf, int KS, int R, int tid) {
+    for (int i = tid; i < KS * TILE_W; i += NT) {
+        const int w = i & (TILE_W - 1);
+        const int row = ((w >> 6) << 3) + ((w & 63) >> 3);
+        buf[i] = row < R ? SENT : 0u;
+    }
+}
+
+// multicast one staged 128-word block (B-fragment order, k-step = this CTA's rank) to every CTA of the cluster
+__device__ __forceinline__ void multicast_block(const uint32_t* stage, uint32_t* dst_buf, int rank, int R, int tid) {
+    const int dst = tid >> 5, v = tid & 31;
+    const int row = ((v >> 4) << 3) + ((v & 15) >> 1);
+    if (row < R) {
+        const uint4 val = *reinterpret_cast<const uint4*>(stage + (v << 2));
+        st_remote_v4(mapa_rank(smem_addr(dst_buf + rank * TILE_W + (v << 2)), dst), val);
+    }
+}
+
+__device__ __forceinline__ bool keep_bit3(const Dec3Params& p, int step, int b, int layer, int unit) {
+    if (p.masks) return p.masks[(((size_t)(step - p.t0) * p.B + b) * 2 + layer) * PRE + unit] != 0;
+    return philox_keep(p.seed, (uint32_t)step, (uint32_t)b, (uint32_t)layer, (uint32_t)unit);
+}
+
+}  // namespace
+
+#include "decoder3_kernel.inl"
+
+size_t taco_decoder3_smem_bytes() { return (size_t)SMEM3_WORDS * 4; }
+
+cudaError_t taco_decoder3_max_clusters(int* out) {
+    cudaError_t e = cudaFuncSetAttribute(decoder3_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(decoder3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)taco_decoder3_smem_bytes());
+    if (e != cudaSuccess) return e;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(CS * 8);
+    cfg.blockDim = dim3(NT);
+    cfg.dynamicSmemBytes = taco_decoder3_smem_bytes();
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = CS;
+    at[0].val.clusterDim.y = 1;
+    at[0].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    return cudaOccupancyMaxActiveClusters(out, decoder3_kernel, &cfg);
+}
+
+cudaError_t taco_launch_decoder3(const Dec3Params& p, cudaStream_t stream) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(CS * p.NCL);
+    cfg.blockDim = dim3(NT);
+    cfg.dynamicSmemBytes = taco_decoder3_smem_bytes();
+    cfg.stream = stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = CS;
+    at[0].val.clusterDim.y = 1;
+    at[0].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, decoder3_kernel, p);
+}

@@ -1,0 +1,250 @@
+// Attention helpers of decoder3.cu (kept in a separate file only for size).
+namespace {
+
+// pair arrays of the hi/lo bf16 split of the zero-padded cumulative alignments (Toeplitz A operand)
+__device__ __forceinline__ void att3_build_pairs(int T, int tid) {
+    const float* cpad = SMF(SO_CPAD);
+    uint32_t* P = SMU(SO_P);
+    const int n = (T + 46) / 2 + 1;
+    for (int i = tid; i < n && i < PW3; i += NT) {
+        const float c0 = cpad[2 * i], c1 = cpad[2 * i + 1], c2 = (2 * i + 2 < T_MAX3 + 48) ? cpad[2 * i + 2] : 0.f;
+        const float h0 = __bfloat162float(__float2bfloat16_rn(c0));
+        const float h1 = __bfloat162float(__float2bfloat16_rn(c1));
+        const float h2 = __bfloat162float(__float2bfloat16_rn(c2));
+        P[i] = pack_bf16x2(h0, h1);
+        P[PW3 + i] = pack_bf16x2(h1, h2);
+        P[2 * PW3 + i] = pack_bf16x2(c0 - h0, c1 - h1);
+        P[3 * PW3 + i] = pack_bf16x2(c1 - h1, c2 - h2);
+    }
+}
+
+// One 16-row tile of the location term: acc[t][d] = sum_k cum[t + k - 15] G[k][d], d = 8*warp + 2*tq (+1), rows t0+gq, t0+gq+8
+// (Attention.py:193-197 fused: conv1d(k=31, 32 filters) then Dense(128, no bias)); hi/lo bf16 split, 3 MMAs per k-step.
+__device__ __forceinline__ void att3_loc_tile(float (&acc)[4], int t0, int lane, const uint2 (&ghi)[2], const uint2 (&glo)[2]) {
+    const int gq = lane >> 2, tq = lane & 3;
+    const uint32_t* P0h = SMU(SO_P);
+    const uint32_t* P1h = SMU(SO_P + PW3);
+    const uint32_t* P0l = SMU(SO_P + 2 * PW3);
+    const uint32_t* P1l = SMU(SO_P + 3 * PW3);
+    const int ta = t0 + gq, tb = ta + 8;
+    acc[0] = acc[1] = acc[2] = acc[3] = 0.f;
+#pragma unroll
+    for (int ks = 0; ks < 2; ++ks) {
+        uint4 ah, al;
+        // element (row, k) = cpad[t0 + row + k]; pair (k, k+1) at index i = t0 + row + k: even -> P0[i/2], odd -> P1[(i-1)/2]
+        const int ia = ta + ks * 16 + 2 * tq, ib = tb + ks * 16 + 2 * tq;
+        const bool oa = ia & 1, ob = ib & 1;
+        ah.x = oa ? P1h[ia >> 1] : P0h[ia >> 1];
+        ah.y = ob ? P1h[ib >> 1] : P0h[ib >> 1];
+        ah.z = oa ? P1h[(ia + 8) >> 1] : P0h[(ia + 8) >> 1];
+        ah.w = ob ? P1h[(ib + 8) >> 1] : P0h[(ib + 8) >> 1];
+        al.x = oa ? P1l[ia >> 1] : P0l[ia >> 1];
+        al.y = ob ? P1l[ib >> 1] : P0l[ib >> 1];
+        al.z = oa ? P1l[(ia + 8) >> 1] : P0l[(ia + 8) >> 1];
+        al.w = ob ? P1l[(ib + 8) >> 1] : P0l[(ib + 8) >> 1];
+        mma16816(acc, ah, ghi[ks]);
+        mma16816(acc, ah, glo[ks]);
+        mma16816(acc, al, ghi[ks]);
+    }
+}
+
+// pre[t][d] = keys[b][t][d] + b_a[d] + conv_bias.Wl[d] + location term, for all t < len of row b.
+// T <= PRE_REG_T: kept in registers preR[tile][4] (thread = rows 16*tile + gq (+8), columns 8*warp + 2*tq (+1));
+// otherwise written to the row's global scratch [T][128].
+__device__ __forceinline__ void att3_location(const Dec3Params& p, float (&preR)[8][4], float* pre_scr, int b, int len, int warp, int lane) {
+    const int gq = lane >> 2, tq = lane & 3;
+    uint2 ghi[2], glo[2];
+#pragma unroll
+    for (int ks = 0; ks < 2; ++ks) {
+        ghi[ks] = __ldg(reinterpret_cast<const uint2*>(p.g_hi) + (ks * 16 + warp) * 32 + lane);
+        glo[ks] = __ldg(reinterpret_cast<const uint2*>(p.g_lo) + (ks * 16 + warp) * 32 + lane);
+    }
+    const int d0 = warp * 8 + 2 * tq;
+    const float bc0 = SMF(SO_BC)[d0], bc1 = SMF(SO_BC)[d0 + 1];
+    if (p.pre_reg) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int t0 = 16 * i;
+            if (t0 < len) {
+                const int ta = t0 + gq, tb = ta + 8;
+                float2 ka = make_float2(0.f, 0.f), kb = make_float2(0.f, 0.f);
+                if (ta < len) ka = __ldg(reinterpret_cast<const float2*>(p.keys + ((size_t)b * p.T + ta) * ATT + d0));
+                if (tb < len) kb = __ldg(reinterpret_cast<const float2*>(p.keys + ((size_t)b * p.T + tb) * ATT + d0));
+                float acc[4];
+                att3_loc_tile(acc, t0, lane, ghi, glo);
+                preR[i][0] = acc[0] + ka.x + bc0;
+                preR[i][1] = acc[1] + ka.y + bc1;
+                preR[i][2] = acc[2] + kb.x + bc0;
+                preR[i][3] = acc[3] + kb.y + bc1;
+            }
+        }
+    } else {
+        for (int t0 = 0; t0 < len; t0 += 16) {
+            const int ta = t0 + gq, tb = ta + 8;
+            float2 ka = make_float2(0.f, 0.f), kb = make_float2(0.f, 0.f);
+            if (ta < len) ka = __ldg(reinterpret_cast<const float2*>(p.keys + ((size_t)b * p.T + ta) * ATT + d0));
+            if (tb < len) kb = __ldg(reinterpret_cast<const float2*>(p.keys + ((size_t)b * p.T + tb) * ATT + d0));
+            float acc[4];
+            att3_loc_tile(acc, t0, lane, ghi, glo);
+            if (ta < len) *reinterpret_cast<float2*>(pre_scr + (size_t)ta * ATT + d0) = make_float2(acc[0] + ka.x + bc0, acc[1] + ka.y + bc1);
+            if (tb < len) *reinterpret_cast<float2*>(pre_scr + (size_t)tb * ATT + d0) = make_float2(acc[2] + kb.x + bc0, acc[3] + kb.y + bc1);
+        }
+    }
+}
+
+// One attention step of cluster row `rank` (global row b): q from the 16 partials, energies, masked softmax, cumulate,
+// alignment history, context (bf16 values, fp32 accumulate), multicast of the context row, next step's location term.
+__device__ __forceinline__ void att3_step(const Dec3Params& p, float (&preR)[8][4], float* pre_scr, int b, int len, int rank, int s,
+                                          int tid, int warp, int lane, Guard3& g, long long* tacc, long long& tprev, bool timing) {
+    float* scr = SMF(SO_RED);
+    // E1: q[d] = sum over the 16 source CTAs of their K-slice partial (query_layer, Attention.py:187-189)
+    if (tid < ATT) {
+        float q = 0.f;
+#pragma unroll 4
+        for (int src = 0; src < CS; ++src) {
+            const uint32_t* a = SMU(SO_QRECV) + src * ATT + tid;
+            uint32_t w = *reinterpret_cast<const volatile uint32_t*>(a);
+            int spins = 0;
+            while (w == SENT && !spin_check3(g, spins)) w = *reinterpret_cast<const volatile uint32_t*>(a);
+            q += __uint_as_float(w);
+        }
+        SMF(SO_QS)[tid] = g.dead ? 0.f : q;
+    }
+    __syncthreads();
+    for (int i = tid; i < CS * ATT; i += NT) SMU(SO_QRECV)[i] = SENT;  // re-arm for the next step
+    // E2: energies e[t] = sum_d v_a[d] tanh(pre[t][d] + q[d])   (Attention.py:401)
+    if (p.pre_reg) {
+        const int gq = lane >> 2, tq = lane & 3, d0 = warp * 8 + 2 * tq;
+        const float q0 = SMF(SO_QS)[d0], q1 = SMF(SO_QS)[d0 + 1], v0 = SMF(SO_VA)[d0], v1 = SMF(SO_VA)[d0 + 1];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            if (16 * i < len) {
+                float ea = v0 * tanh_apx(preR[i][0] + q0) + v1 * tanh_apx(preR[i][1] + q1);
+                float eb = v0 * tanh_apx(preR[i][2] + q0) + v1 * tanh_apx(preR[i][3] + q1);
+                ea += __shfl_xor_sync(0xffffffffu, ea, 1);
+                eb += __shfl_xor_sync(0xffffffffu, eb, 1);
+                ea += __shfl_xor_sync(0xffffffffu, ea, 2);
+                eb += __shfl_xor_sync(0xffffffffu, eb, 2);
+                if (tq == 0) {
+                    scr[warp * PRE_REG_T + 16 * i + gq] = ea;
+                    scr[warp * PRE_REG_T + 16 * i + gq + 8] = eb;
+                }
+            }
+        }
+        __syncthreads();
+        if (tid < len) {
+            float e = 0.f;
+#pragma unroll
+            for (int w = 0; w < 16; ++w) e += scr[w * PRE_REG_T + tid];
+            SMF(SO_ES)[tid] = e;
+        }
+    } else {
+        const int tl = lane & 7, qd = lane >> 3;
+        const float4* q4 = reinterpret_cast<const float4*>(SMF(SO_QS) + qd * 32);
+        const float4* v4 = reinterpret_cast<const float4*>(SMF(SO_VA) + qd * 32);
+        for (int tb = 0; tb < len; tb += 128) {
+            const int t = tb + warp * 8 + tl;
+            float e = 0.f;
+            if (t < len) {
+                const float4* p4 = reinterpret_cast<const float4*>(pre_scr + (size_t)t * ATT + qd * 32);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const float4 x = p4[i], qq = q4[i], vv = v4[i];
+                    e = fmaf(vv.x, tanh_apx(x.x + qq.x), e);
+                    e = fmaf(vv.y, tanh_apx(x.y + qq.y), e);
+                    e = fmaf(vv.z, tanh_apx(x.z + qq.z), e);
+                    e = fmaf(vv.w, tanh_apx(x.w + qq.w), e);
+                }
+            }
+            e += __shfl_xor_sync(0xffffffffu, e, 8);
+            e += __shfl_xor_sync(0xffffffffu, e, 16);
+            if (qd == 0 && t < len) SMF(SO_ES)[t] = e;
+        }
+    }
+    __syncthreads();
+    // E3: masked softmax over t < len (exact zeros beyond: -inf mask), Attention.py:203-206
+    if (warp == 0) {
+        float m = -INFINITY;
+        if (!p.smoothing) {
+            for (int t = lane; t < len; t += 32) m = fmaxf(m, SMF(SO_ES)[t]);
+            m = warp_max(m);
+        }
+        float sum = 0.f;
+        for (int t = lane; t < len; t += 32) {
+            const float v = p.smoothing ? sigmoidf_(SMF(SO_ES)[t]) : expf(SMF(SO_ES)[t] - m);
+            SMF(SO_ES)[t] = v;
+            sum += v;
+        }
+        sum = warp_sum(sum);
+        const float inv = 1.0f / sum;
+        for (int t = lane; t < len; t += 32) SMF(SO_ES)[t] *= inv;
+    }
+    __syncthreads();
+    // E4: cumulate + alignment history
+    for (int t = tid; t < p.T; t += NT) {
+        const float a = t < len ? SMF(SO_ES)[t] : 0.f;
+        SMF(SO_CPAD)[15 + t] = p.cumulative ? SMF(SO_CPAD)[15 + t] + a : a;
+        p.hist[((size_t)s * p.B + b) * p.T + t] = a;
+    }
+    // E5: context = sum_t a[t] values[b][t][:]   (_compute_attention, Attention.py:345-366)
+    {
+        constexpr int D8 = MEM / 8, TG = 5;
+        const int d8 = tid % D8, tg = tid / D8;
+        float c[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        if (tg < TG) {
+            const uint4* vp = reinterpret_cast<const uint4*>(p.values + (size_t)b * p.T * MEM) + d8;
+#pragma unroll 4
+            for (int t = tg; t < len; t += TG) {
+                const uint4 v = ldg_stream_v4(vp + (size_t)t * D8);
+                const float a = SMF(SO_ES)[t];
+                c[0] = fmaf(a, bf_lo(v.x), c[0]);
+                c[1] = fmaf(a, bf_hi(v.x), c[1]);
+                c[2] = fmaf(a, bf_lo(v.y), c[2]);
+                c[3] = fmaf(a, bf_hi(v.y), c[3]);
+                c[4] = fmaf(a, bf_lo(v.z), c[4]);
+                c[5] = fmaf(a, bf_hi(v.z), c[5]);
+                c[6] = fmaf(a, bf_lo(v.w), c[6]);
+                c[7] = fmaf(a, bf_hi(v.w), c[7]);
+            }
+            float4* dst = reinterpret_cast<float4*>(scr + (size_t)tg * MEM + d8 * 8);
+            dst[0] = make_float4(c[0], c[1], c[2], c[3]);
+            dst[1] = make_float4(c[4], c[5], c[6], c[7]);
+        }
+        __syncthreads();
+        if (tid < MEM / 2) {
+            float x0 = 0.f, x1 = 0.f;
+#pragma unroll
+            for (int q = 0; q < TG; ++q) {
+                const float2 v = *reinterpret_cast<const float2*>(scr + (size_t)q * MEM + 2 * tid);
+                x0 += v.x;
+                x1 += v.y;
+            }
+            const int ks = tid >> 3, j = tid & 7;
+            SMU(SO_STG_C)[ks * 8 + ((j & 3) << 1) + (j >> 2)] = pack_bf16x2(x0, x1);
+            *reinterpret_cast<float2*>(p.ctx_state + (size_t)b * MEM + 2 * tid) = make_float2(x0, x1);
+        }
+        __syncthreads();
+        // multicast this row's 48 x 32-byte chunks into every CTA's context buffer
+        for (int i = tid; i < CS * KS_CTX * 2; i += NT) {
+            const int dst = i / (KS_CTX * 2), v = i - dst * (KS_CTX * 2);
+            const int ks = v >> 1, half = v & 1;
+            const uint4 val = *reinterpret_cast<const uint4*>(SMU(SO_STG_C) + ks * 8 + half * 4);
+            st_remote_v4(mapa_rank(smem_addr(SMU(SO_CTX) + ks * TILE_W + ((rank >> 3) << 6) + ((rank & 7) << 3) + half * 4), dst), val);
+        }
+    }
+    if (timing) {
+        long long now_;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now_));
+        tacc[8] += now_ - tprev;
+        tprev = now_;
+    }
+}
+
+// E6 (off the critical path, after the projection): location pre-activations of the NEXT step from the new cumulative alignments
+__device__ __forceinline__ void att3_next(const Dec3Params& p, float (&preR)[8][4], float* pre_scr, int b, int len, int tid, int warp, int lane) {
+    att3_build_pairs(p.T, tid);
+    __syncthreads();
+    att3_location(p, preR, pre_scr, b, len, warp, lane);
+}
+
+}  // namespace

@@ -1,0 +1,422 @@
+// Body of decoder3.cu (kept in a separate file only for size).  See decoder3.cu for the design.
+#include "decoder3_attention.inl"
+
+namespace {
+
+#define D3_STAMP(i)                                                     \
+    if (timing) {                                                       \
+        long long now_;                                                 \
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now_));        \
+        tacc[i] += now_ - tprev;                                        \
+        tprev = now_;                                                   \
+    }
+
+// fill one activation buffer from a row-major fp32 state array [B][width] (rows row0 .. row0+R-1 of this cluster)
+__device__ __forceinline__ void fill_from_state(uint32_t* buf, const float* state, int width, int row0, int R, int tid) {
+    const int pairs = width >> 1;
+    for (int i = tid; i < R * pairs; i += NT) {
+        const int r = i / pairs, pi = i - r * pairs;
+        const int col = 2 * pi;
+        const float2 v = *reinterpret_cast<const float2*>(state + (size_t)(row0 + r) * width + col);
+        buf[(col >> 4) * TILE_W + bword(r, (col & 15) >> 1)] = pack_bf16x2(v.x, v.y);
+    }
+}
+
+__global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__ Dec3Params p) {
+    cg::cluster_group cluster = cg::this_cluster();
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int rank = (int)cluster.block_rank();
+    const int cid = blockIdx.x / CS;
+    const int row0 = cid * p.R;
+    const int R = min(p.R, p.B - row0);
+    Guard3 g{p.abort_flag, false};
+    const bool free_run = p.mode == TACO_MODE_FREE;
+    const float zo = p.zoneout;
+
+    // ---- one-time loads: resident weight tiles of this rank, attention vectors, activation buffers ----
+    {
+        const uint4* src = reinterpret_cast<const uint4*>(p.res_blobs + (size_t)rank * RES_WORDS);
+        uint4* dst = reinterpret_cast<uint4*>(SMU(0));
+        for (int i = tid; i < RES_WORDS / 4; i += NT) dst[i] = src[i];
+        if (tid < ATT) {
+            SMF(SO_VA)[tid] = p.va[tid];
+            SMF(SO_BC)[tid] = p.bconst[tid];
+        }
+        for (int i = tid; i < T_MAX3 + 48; i += NT) SMF(SO_CPAD)[i] = 0.f;
+        if (tid < 8 + 32) SMU(SO_FLAG)[tid] = 0;
+        rearm(SMU(SO_X), KS_X + 6 * KS_H + KS_CTX, R, tid);   // all activation buffers are contiguous
+        for (int i = tid; i < CS * ATT; i += NT) SMU(SO_QRECV)[i] = SENT;
+    }
+    __syncthreads();
+    // recurrent state of step t0-1 (zeros after reset): context, zoned h1 / h2, next decoder input
+    fill_from_state(SMU(SO_CTX), p.ctx_state, MEM, row0, R, tid);
+    fill_from_state(SMU(SO_H1Z), p.h1z, DEC, row0, R, tid);
+    fill_from_state(SMU(SO_H2Z), p.h2z, DEC, row0, R, tid);
+    if (free_run) fill_from_state(SMU(SO_X), p.x_state, MEL, row0, R, tid);
+
+    // epilogue threads: (unit eu = tid & 15 of this CTA's 16 units, cluster row er = tid >> 4); fp32 recurrent state in registers
+    const int eu = tid & 15, er = tid >> 4;
+    const bool ept = tid < 256;
+    const bool evalid = ept && er < R;
+    const int eb = row0 + er;
+    float c1s = 0.f, h1s = 0.f, c2s = 0.f, h2s = 0.f;
+    if (evalid) {
+        c1s = p.c1[(size_t)eb * DEC + 16 * rank + eu];
+        h1s = p.h1z[(size_t)eb * DEC + 16 * rank + eu];
+        c2s = p.c2[(size_t)eb * DEC + 16 * rank + eu];
+        h2s = p.h2z[(size_t)eb * DEC + 16 * rank + eu];
+    }
+    // attention work item: cluster row `rank`
+    const bool att = rank < R;
+    const int ab = row0 + (att ? rank : 0);
+    const int alen = att ? p.lens[ab] : 0;
+    float* pre_scr = p.pre_scratch ? p.pre_scratch + (size_t)ab * p.T * ATT : nullptr;
+    float preR[8][4];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) preR[i][0] = preR[i][1] = preR[i][2] = preR[i][3] = 0.f;
+    __syncthreads();
+    if (att) {
+        for (int t = tid; t < p.T; t += NT) SMF(SO_CPAD)[15 + t] = p.cum[(size_t)ab * p.T + t];
+        __syncthreads();
+        att3_build_pairs(p.T, tid);
+        __syncthreads();
+        att3_location(p, preR, pre_scr, ab, alen, warp, lane);
+    }
+    // every CTA of the cluster has armed its buffers before any peer may write into them
+    cluster.sync();
+
+    const int mt = warp & 3, kg = warp >> 2;   // 4-m-tile phases: (gate tile, k group)
+    const uint4* stream = p.stream_blobs + (size_t)rank * (320 * 32);
+    const uint4* sW1C = stream + (size_t)(mt * KS_CTX) * 32;
+    const uint4* sW1H = stream + (size_t)(192 + mt * KS_H) * 32;
+    const uint4* sW2Z = stream + (size_t)(256 + mt * KS_H) * 32;
+    const float* bias = SMF(SO_BIAS);   // b1[64] b2[64] bp1[16] bp2[16] bo[16]
+    float* red = SMF(SO_RED);
+
+    // contributions of step t0-1's context / zoned states to the gates of step t0
+    float acc1[2][4] = {}, acc2[2][4] = {}, accO[2][4] = {};
+    gemm_stream<2, 4>(acc1, sW1C, 32, SMU(SO_CTX), KS_CTX, kg, 4, lane, g);
+    gemm_stream<2, 4>(acc1, sW1H, 32, SMU(SO_H1Z), KS_H, kg, 4, lane, g);
+    gemm_stream<2, 4>(acc2, sW2Z, 32, SMU(SO_H2Z), KS_H, kg, 4, lane, g);
+    __syncthreads();
+    rearm(SMU(SO_H1Z), KS_H, R, tid);
+    rearm(SMU(SO_H2Z), KS_H, R, tid);
+    rearm(SMU(SO_CTX), KS_CTX, R, tid);
+    __syncthreads();
+
+    long long* tacc = reinterpret_cast<long long*>(smem3 + SO_TACC);
+    long long tprev = 0;
+    const bool timing = p.timing != nullptr && tid == 0;
+    if (timing) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tprev));
+    // stop flags of step s-2, loaded one step before they are consumed (free running; thread 0)
+    uint32_t fl[TACO_DEC3_MAX_CLUSTERS];
+#pragma unroll
+    for (int i = 0; i < TACO_DEC3_MAX_CLUSTERS; ++i) fl[i] = 1u;
+    int s_done = 0;
+    bool stopped = false;
+
+    for (int s = 0; s < p.S_max; ++s) {
+        const int step = p.t0 + s;
+        // ---- batch-global stop (Helpers.py:51-52), evaluated three steps late; speculative steps are discarded ----
+        if (free_run && tid == 0) {
+            if (s >= 3) {
+                bool any = false, all = true;
+#pragma unroll
+                for (int i = 0; i < TACO_DEC3_MAX_CLUSTERS; ++i) {
+                    if (i < p.NCL) {
+                        uint32_t v = fl[i];
+                        int spins = 0;
+                        while (v == 0u && !spin_check3(g, spins)) v = ldg_relaxed(reinterpret_cast<const uint32_t*>(p.flags) + (size_t)(s - 3) * p.NCL + i);
+                        any = any || (v & 2u);
+                        all = all && (v & 2u);
+                    }
+                }
+                SMU(SO_FLAG)[0] = ((p.stop_at_any ? any : all) || g.dead) ? 2u : 1u;
+            }
+            if (s >= 2) {
+#pragma unroll
+                for (int i = 0; i < TACO_DEC3_MAX_CLUSTERS; ++i)
+                    if (i < p.NCL) fl[i] = ldg_relaxed(reinterpret_cast<const uint32_t*>(p.flags) + (size_t)(s - 2) * p.NCL + i);
+            }
+        }
+        // ================= P1: prenet dense_1 (Decoder.py:346-351) =================
+        {
+            float acc[2][4] = {};
+            if (warp < KS_X) {
+                if (free_run) {
+                    gemm_smem<2>(acc, SMU(SO_WP1), TILE_W, SMU(SO_X), KS_X, warp, 16, lane, g);
+                } else {
+                    // TacoTrainingHelper.next_inputs (Helpers.py:121-124, ratio 1.0): x(step) = targets[:, r*step - 1]
+                    const int fidx = step * 2 - 1;
+                    const int gq = lane >> 2, tq = lane & 3;
+                    const uint4 a = *reinterpret_cast<const uint4*>(SMU(SO_WP1) + warp * TILE_W + (lane << 2));
+#pragma unroll
+                    for (int j = 0; j < 2; ++j) {
+                        uint2 bfrag = make_uint2(0u, 0u);
+                        const int r = 8 * j + gq;
+                        if (fidx >= 0 && fidx < p.F_tgt && r < R) {
+                            const float* src = p.targets + ((size_t)(row0 + r) * p.F_tgt + fidx) * MEL + warp * 16 + 2 * tq;
+                            const float2 v0 = __ldg(reinterpret_cast<const float2*>(src));
+                            const float2 v1 = __ldg(reinterpret_cast<const float2*>(src + 8));
+                            bfrag.x = pack_bf16x2(v0.x, v0.y);
+                            bfrag.y = pack_bf16x2(v1.x, v1.y);
+                        }
+                        mma16816(acc[j], a, bfrag);
+                    }
+                }
+                store_red3(red, acc, warp, lane, 2);
+            }
+            D3_STAMP(0)
+            __syncthreads();
+            if (free_run && s >= 3 && SMU(SO_FLAG)[0] == 2u) {
+                stopped = true;
+                break;   // CTA- and cluster-uniform: every CTA reads the same flag words
+            }
+            if (ept) {
+                float z = bias[128 + eu];
+#pragma unroll
+                for (int k = 0; k < KS_X; ++k) z += red[(k * 16 + eu) * 17 + er];
+                z = fmaxf(z, 0.f);
+                z = (evalid && keep_bit3(p, step, eb, 0, 16 * rank + eu)) ? z * p.keep_scale : 0.f;
+                const float zn = __shfl_down_sync(0xffffffffu, z, 1);
+                if (!(eu & 1)) SMU(SO_STG_R)[bword(er, eu >> 1)] = pack_bf16x2(z, zn);
+            }
+            if (free_run) rearm(SMU(SO_X), KS_X, R, tid);
+            if (s > 0) {   // buffers whose last readers ran before this phase's barrier
+                rearm(SMU(SO_CTX), KS_CTX, R, tid);
+                rearm(SMU(SO_H2R), KS_H, R, tid);
+                rearm(SMU(SO_H2Z), KS_H, R, tid);
+            }
+            __syncthreads();
+            multicast_block(SMU(SO_STG_R), SMU(SO_P1), rank, R, tid);
+            D3_STAMP(1)
+        }
+        // ================= P2: prenet dense_2 =================
+        {
+            float acc[2][4] = {};
+            gemm_smem<2>(acc, SMU(SO_WP2), TILE_W, SMU(SO_P1), KS_H, warp, 16, lane, g);
+            store_red3(red, acc, warp, lane, 2);
+            D3_STAMP(2)
+            __syncthreads();
+            if (ept) {
+                float z = bias[144 + eu];
+#pragma unroll
+                for (int k = 0; k < 16; ++k) z += red[(k * 16 + eu) * 17 + er];
+                z = fmaxf(z, 0.f);
+                z = (evalid && keep_bit3(p, step, eb, 1, 16 * rank + eu)) ? z * p.keep_scale : 0.f;
+                const float zn = __shfl_down_sync(0xffffffffu, z, 1);
+                if (!(eu & 1)) SMU(SO_STG_R)[bword(er, eu >> 1)] = pack_bf16x2(z, zn);
+            }
+            rearm(SMU(SO_P1), KS_H, R, tid);
+            __syncthreads();
+            multicast_block(SMU(SO_STG_R), SMU(SO_P2), rank, R, tid);
+            D3_STAMP(3)
+        }
+        // ================= L1: decoder LSTM layer 1 (Decoder.py:256; Encoder.py:118-142) =================
+        {
+            gemm_smem<2>(acc1, SMU(SO_W1P) + mt * KS_H * TILE_W, TILE_W, SMU(SO_P2), KS_H, kg, 4, lane, g);
+            store_red3(red, acc1, kg * 4 + mt, lane, 2);
+#pragma unroll
+            for (int j = 0; j < 2; ++j) acc1[j][0] = acc1[j][1] = acc1[j][2] = acc1[j][3] = 0.f;
+            D3_STAMP(4)
+            __syncthreads();
+            if (ept) {
+                float z[4];
+#pragma unroll
+                for (int gt = 0; gt < 4; ++gt) {
+                    z[gt] = bias[gt * 16 + eu];
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) z[gt] += red[((k * 4 + gt) * 16 + eu) * 17 + er];
+                }
+                // gate order i, j, f, o; forget bias 1.0
+                const float c_new = sigmoid_f(z[2] + 1.0f) * c1s + sigmoid_f(z[0]) * tanh_f(z[1]);
+                float h_new = sigmoid_f(z[3]) * tanh_f(c_new);
+                if (evalid) {
+                    c1s = (1.f - zo) * c_new + zo * c1s;
+                    h1s = (1.f - zo) * h_new + zo * h1s;
+                } else {
+                    h_new = 0.f;
+                }
+                const float hn1 = __shfl_down_sync(0xffffffffu, h_new, 1);
+                const float hz1 = __shfl_down_sync(0xffffffffu, h1s, 1);
+                if (!(eu & 1)) {
+                    SMU(SO_STG_R)[bword(er, eu >> 1)] = pack_bf16x2(h_new, hn1);
+                    SMU(SO_STG_Z)[bword(er, eu >> 1)] = pack_bf16x2(h1s, hz1);
+                }
+            }
+            rearm(SMU(SO_P2), KS_H, R, tid);
+            __syncthreads();
+            multicast_block(SMU(SO_STG_R), SMU(SO_H1R), rank, R, tid);
+            multicast_block(SMU(SO_STG_Z), SMU(SO_H1Z), rank, R, tid);
+            D3_STAMP(5)
+        }
+        // ================= L2: decoder LSTM layer 2 =================
+        {
+            gemm_smem<2>(acc2, SMU(SO_W2H) + mt * KS_H * TILE_W, TILE_W, SMU(SO_H1R), KS_H, kg, 4, lane, g);
+            // zoned h1 of this step -> gates of the next step (weights streamed from L2)
+            gemm_stream<2, 4>(acc1, sW1H, 32, SMU(SO_H1Z), KS_H, kg, 4, lane, g);
+            store_red3(red, acc2, kg * 4 + mt, lane, 2);
+#pragma unroll
+            for (int j = 0; j < 2; ++j) acc2[j][0] = acc2[j][1] = acc2[j][2] = acc2[j][3] = 0.f;
+            D3_STAMP(6)
+            __syncthreads();
+            if (ept) {
+                float z[4];
+#pragma unroll
+                for (int gt = 0; gt < 4; ++gt) {
+                    z[gt] = bias[64 + gt * 16 + eu];
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) z[gt] += red[((k * 4 + gt) * 16 + eu) * 17 + er];
+                }
+                const float c_new = sigmoid_f(z[2] + 1.0f) * c2s + sigmoid_f(z[0]) * tanh_f(z[1]);
+                float h_new = sigmoid_f(z[3]) * tanh_f(c_new);
+                if (evalid) {
+                    c2s = (1.f - zo) * c_new + zo * c2s;
+                    h2s = (1.f - zo) * h_new + zo * h2s;
+                } else {
+                    h_new = 0.f;
+                }
+                const float hn1 = __shfl_down_sync(0xffffffffu, h_new, 1);
+                const float hz1 = __shfl_down_sync(0xffffffffu, h2s, 1);
+                if (!(eu & 1)) {
+                    SMU(SO_STG_R)[bword(er, eu >> 1)] = pack_bf16x2(h_new, hn1);
+                    SMU(SO_STG_Z)[bword(er, eu >> 1)] = pack_bf16x2(h2s, hz1);
+                }
+            }
+            rearm(SMU(SO_H1R), KS_H, R, tid);
+            rearm(SMU(SO_H1Z), KS_H, R, tid);
+            __syncthreads();
+            // K-slice of the query projection: qpart[row][d] = sum_{u in my 16 units} h2raw[row][u] Wq[u][d]
+            if (warp < 8) {
+                float accq[2][4] = {};
+                const uint4 a = *reinterpret_cast<const uint4*>(SMU(SO_WQ) + warp * TILE_W + (lane << 2));
+                const int gq = lane >> 2, tq = lane & 3;
+#pragma unroll
+                for (int j = 0; j < 2; ++j) {
+                    const uint2 bfrag = *reinterpret_cast<const uint2*>(SMU(SO_STG_R) + (j << 6) + (lane << 1));
+                    mma16816(accq[j], a, bfrag);
+                    float* q0 = red + (8 * j + 2 * tq) * ATT + warp * 16 + gq;   // [row][d]
+                    q0[0] = accq[j][0];
+                    q0[ATT] = accq[j][1];
+                    q0[8] = accq[j][2];
+                    q0[ATT + 8] = accq[j][3];
+                }
+            }
+            __syncthreads();
+            {
+                const int row = tid >> 5, v = tid & 31;
+                if (row < R) {
+                    const uint4 val = *reinterpret_cast<const uint4*>(red + row * ATT + (v << 2));
+                    st_remote_v4(mapa_rank(smem_addr(SMU(SO_QRECV) + rank * ATT + (v << 2)), row), val);
+                }
+            }
+            multicast_block(SMU(SO_STG_R), SMU(SO_H2R), rank, R, tid);
+            multicast_block(SMU(SO_STG_Z), SMU(SO_H2Z), rank, R, tid);
+            D3_STAMP(7)
+        }
+        // ---- h2-dependent halves of the next LSTM-2 gates and of the projection (their operands arrive with the query partials) ----
+        gemm_stream<2, 4>(acc2, sW2Z, 32, SMU(SO_H2Z), KS_H, kg, 4, lane, g);
+#pragma unroll
+        for (int j = 0; j < 2; ++j) accO[j][0] = accO[j][1] = accO[j][2] = accO[j][3] = 0.f;
+        if (rank <= 10) gemm_smem<2>(accO, SMU(SO_WO), TILE_W, SMU(SO_H2R), KS_H, warp, 16, lane, g);
+        D3_STAMP(9)
+        // ================= ATT: location-sensitive attention of cluster row `rank` =================
+        if (att) att3_step(p, preR, pre_scr, ab, alen, rank, s, tid, warp, lane, g, tacc, tprev, timing);
+        D3_STAMP(10)
+        // ================= PROJ: frame + stop projection, outputs, feedback (Decoder.py:273-279; Helpers.py:36-59) =================
+        if (rank <= 10) {
+            gemm_smem<2>(accO, SMU(SO_WO) + KS_H * TILE_W, TILE_W, SMU(SO_CTX), KS_CTX, warp, 16, lane, g);
+            __syncthreads();   // attention scratch (aliases red) is no longer read
+            store_red3(red, accO, warp, lane, 2);
+            D3_STAMP(11)
+            __syncthreads();
+            bool fin = false;
+            if (ept) {
+                float y = bias[160 + eu];
+#pragma unroll
+                for (int k = 0; k < 16; ++k) y += red[(k * 16 + eu) * 17 + er];
+                if (rank < 10) {
+                    const int col = 16 * rank + eu;   // 0..159: frame col / 80, mel col % 80
+                    if (evalid) p.frames[((size_t)eb * p.S_cap * 2 + (size_t)s * 2 + (col >= MEL ? 1 : 0)) * MEL + (col >= MEL ? col - MEL : col)] = y;
+                    if (rank >= 5) {
+                        // TacoTestHelper.next_inputs: next input = last frame of this step (Helpers.py:56)
+                        const float x = evalid ? y : 0.f;
+                        if (evalid) p.x_state[(size_t)eb * MEL + col - MEL] = x;
+                        const float xn = __shfl_down_sync(0xffffffffu, x, 1);
+                        if (!(eu & 1)) SMU(SO_STG_R)[bword(er, eu >> 1)] = pack_bf16x2(x, xn);
+                    }
+                } else if (eu < 2) {
+                    const float sg = sigmoidf_(y);
+                    if (evalid) {
+                        p.stop[(size_t)eb * p.S_cap * 2 + (size_t)s * 2 + eu] = p.stop_sigmoid ? sg : y;
+                        fin = sg > 0.5f;   // tf.round(sigmoid) == 1 <=> sigmoid > 0.5 (half-to-even; Helpers.py:40)
+                    }
+                }
+            }
+            if (rank == 10) {
+                if (free_run) {
+                    const int cnt = __syncthreads_count(fin ? 1 : 0);
+                    if (tid == 0) stg_relaxed(reinterpret_cast<uint32_t*>(p.flags) + (size_t)s * p.NCL + cid, (p.stop_at_any ? cnt > 0 : cnt == 2 * R) ? 2u : 1u);
+                }
+            } else if (rank >= 5 && free_run) {
+                __syncthreads();
+                const int dst = tid >> 5, v = tid & 31;
+                const int row = ((v >> 4) << 3) + ((v & 15) >> 1);
+                if (row < R) {
+                    const uint4 val = *reinterpret_cast<const uint4*>(SMU(SO_STG_R) + (v << 2));
+                    st_remote_v4(mapa_rank(smem_addr(SMU(SO_X) + (rank - 5) * TILE_W + (v << 2)), dst), val);
+                }
+            }
+        }
+        D3_STAMP(12)
+        // ---- shadow of the feedback exchange: context-dependent part of the next LSTM-1 gates ----
+        gemm_stream<2, 4>(acc1, sW1C, 32, SMU(SO_CTX), KS_CTX, kg, 4, lane, g);
+        D3_STAMP(13)
+        if (att) att3_next(p, preR, pre_scr, ab, alen, tid, warp, lane);
+        D3_STAMP(14)
+        __syncthreads();   // red / staging readers of this step are done before the next step's writers
+        s_done = s + 1;
+    }
+
+    if (timing)
+        for (int i = 0; i < 16; ++i) p.timing[(size_t)blockIdx.x * 16 + i] = tacc[i];
+    // ---- write back the recurrent state + step count ----
+    if (evalid) {
+        p.c1[(size_t)eb * DEC + 16 * rank + eu] = c1s;
+        p.h1z[(size_t)eb * DEC + 16 * rank + eu] = h1s;
+        p.c2[(size_t)eb * DEC + 16 * rank + eu] = c2s;
+        p.h2z[(size_t)eb * DEC + 16 * rank + eu] = h2s;
+    }
+    if (att)
+        for (int t = tid; t < p.T; t += NT) p.cum[(size_t)ab * p.T + t] = SMF(SO_CPAD)[15 + t];
+    if (blockIdx.x == 0 && tid == 0) {
+        int steps = s_done;
+        if (free_run) {
+            // the stop bits of the last (up to) three executed steps have not been consumed yet
+            const int first = stopped ? s_done - 3 : max(0, s_done - 3);
+            steps = stopped ? s_done - 3 + 1 : s_done;
+            if (!stopped) {
+                for (int st = first; st < s_done; ++st) {
+                    bool any = false, all = true;
+                    for (int i = 0; i < p.NCL; ++i) {
+                        uint32_t v = 0u;
+                        int spins = 0;
+                        while ((v = ldg_relaxed(reinterpret_cast<const uint32_t*>(p.flags) + (size_t)st * p.NCL + i)) == 0u && !spin_check3(g, spins)) {
+                        }
+                        any = any || (v & 2u);
+                        all = all && (v & 2u);
+                    }
+                    if (p.stop_at_any ? any : all) {
+                        steps = st + 1;
+                        break;
+                    }
+                }
+            }
+        }
+        *p.steps_out = (g.dead || *reinterpret_cast<volatile int*>(p.abort_flag) != 0) ? -1 : steps;
+    }
+    // no CTA may exit while a peer can still write into its shared memory
+    cluster.sync();
+}
+
+}  // namespace

@@ -88,6 +88,47 @@ cudaError_t taco_launch_decoder2(const Dec2Params& p, cudaStream_t stream);
 cudaError_t taco_launch_f32_to_bf16(const float* in, void* out, size_t n, cudaStream_t stream);
 
 // ---------------------------------------------------------------------------------------------
+// decoder3.cu : cluster persistent decoder (16-CTA clusters, DSMEM exchanges, bf16 mma.sync contractions)
+// ---------------------------------------------------------------------------------------------
+#define TACO_DEC3_CLUSTER 16
+#define TACO_DEC3_MAX_CLUSTERS 8
+#define TACO_DEC3_TMAX 512
+#define TACO_DEC3_RES_WORDS (221 * 128 + 176)
+#define TACO_DEC3_STREAM_TILES 320
+struct Dec3Params {
+    int B, T, NCL, R;       // NCL clusters; cluster i owns batch rows [i*R, min(B, i*R + R))
+    int S_max, S_cap, t0, mode;
+    int stop_at_any, cumulative, smoothing, stop_sigmoid;
+    int pre_reg;            // T <= 128: location pre-activations live in registers (else pre_scratch)
+    float zoneout, keep_scale;
+    const uint32_t* res_blobs;   // [16 ranks][TACO_DEC3_RES_WORDS] A-fragment tiles resident in shared memory + fp32 biases
+    const uint4* stream_blobs;   // [16 ranks][320 tiles][32 lanes] A-fragment tiles streamed from L2: W1c [4][48], W1h [4][16], W2z [4][16]
+    const uint32_t *g_hi, *g_lo; // G = conv31 . Wl, B-fragment-major [2 ks][16 nt][32 lanes][2], hi / lo bf16 split
+    const float *va, *bconst;    // [128] attention_variable; attention_bias + conv_bias . Wl
+    const uint16_t* values;      // bf16 [B][T][768]
+    const float* keys;           // fp32 [B][T][128]
+    const int* lens;
+    // recurrent state, fp32 row-major (TacotronDecoderCellState, Decoder.py:419-438)
+    float *c1, *h1z, *c2, *h2z;  // [B][256]
+    float* ctx_state;            // [B][768]
+    float* cum;                  // [B][T]
+    float* x_state;              // [B][80] next decoder input (free-running)
+    float* pre_scratch;          // [B][T][128] when !pre_reg, else null
+    const float* targets;
+    int F_tgt;
+    const uint8_t* masks;
+    uint64_t seed;
+    float *frames, *stop, *hist;
+    int* steps_out;
+    int* flags;       // [S_max][NCL]: 0 not ready, 1 continue, 2 stop (free-running)
+    int* abort_flag;
+    long long* timing;  // optional [grid][16] per-CTA stage nanoseconds (thread 0), or null
+};
+size_t taco_decoder3_smem_bytes();
+cudaError_t taco_decoder3_max_clusters(int* out);
+cudaError_t taco_launch_decoder3(const Dec3Params& p, cudaStream_t stream);
+
+// ---------------------------------------------------------------------------------------------
 // conv.cu : conv1d('same') / dense as implicit GEMM, fused scale/shift + activation epilogue
 // ---------------------------------------------------------------------------------------------
 enum { ACT_NONE = 0, ACT_RELU = 1, ACT_TANH = 2 };
