@@ -705,10 +705,9 @@ int decode_v3(TacoHandle* h, int mode, const float* memory, const int32_t* lens,
     p.ctx_state = s; s += (size_t)B * 768;
     p.x_state = s; s += (size_t)B * 80;
     p.cum = s;
-    if (!p.pre_reg) {
-        WS(pre, float, "dec3_pre", (size_t)B * T * 128)
-        p.pre_scratch = pre;
-    }
+    WS(pre, float, "dec3_pre", (size_t)B * T * 128)
+    p.pre_scratch = pre;
+    p.cont = reset_state ? 0 : 1;
     p.t0 = h->dec_t;
     p.targets = mel_targets; p.F_tgt = F_tgt;
     p.masks = prenet_masks; p.seed = philox_seed;
@@ -719,8 +718,8 @@ int decode_v3(TacoHandle* h, int mode, const float* memory, const int32_t* lens,
     p.flags = flags;
     p.abort_flag = flags + (size_t)S_max * p.NCL + 4;
     if (getenv("TACO_DEC2_TIMING")) {
-        WS(timing, long long, "dec2_timing", (size_t)TACO_DEC3_CLUSTER * TACO_DEC3_MAX_CLUSTERS * 16)
-        CK(cudaMemsetAsync(timing, 0, (size_t)TACO_DEC3_CLUSTER * TACO_DEC3_MAX_CLUSTERS * 16 * sizeof(long long), st));
+        WS(timing, long long, "dec2_timing", (size_t)TACO_DEC3_CLUSTER * TACO_DEC3_MAX_CLUSTERS * 24)
+        CK(cudaMemsetAsync(timing, 0, (size_t)TACO_DEC3_CLUSTER * TACO_DEC3_MAX_CLUSTERS * 24 * sizeof(long long), st));
         p.timing = timing;
     }
     CK(cudaEventRecord(h->ev[TACO_STAGE_DECODER_KERNEL][0], st));

@@ -73,8 +73,8 @@ constexpr int SO_QS = SO_P + 4 * PW3;             // [128]
 constexpr int SO_VA = SO_QS + ATT;
 constexpr int SO_BC = SO_VA + ATT;
 constexpr int SO_FLAG = SO_BC + ATT;              // [8]
-constexpr int SO_TACC = SO_FLAG + 8;              // 16 x int64 stage timers
-constexpr int SMEM3_WORDS = SO_TACC + 32;
+constexpr int SO_TACC = SO_FLAG + 8;              // 24 x int64 stage timers
+constexpr int SMEM3_WORDS = SO_TACC + 48;
 static_assert(RES_WORDS == TACO_DEC3_RES_WORDS, "resident blob size");
 static_assert(SMEM3_WORDS * 4 <= 227 * 1024, "shared memory budget");
 static_assert(SO_X % 4 == 0 && SO_RED % 4 == 0 && SO_QRECV % 4 == 0 && SO_STG_R % 4 == 0 && SO_STG_C % 4 == 0 && SO_ES % 4 == 0 &&

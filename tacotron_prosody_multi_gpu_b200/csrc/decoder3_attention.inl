@@ -2,12 +2,20 @@
 namespace {
 
 // pair arrays of the hi/lo bf16 split of the zero-padded cumulative alignments (Toeplitz A operand)
-__device__ __forceinline__ void att3_build_pairs(int T, int tid) {
+// from_es: the sequence is the NEW alignments a[t] (SO_ES, valid for t < len) instead of the cumulative ones (SO_CPAD)
+__device__ __forceinline__ void att3_build_pairs(int T, int tid, bool from_es = false, int len = 0) {
     const float* cpad = SMF(SO_CPAD);
+    const float* es = SMF(SO_ES);
     uint32_t* P = SMU(SO_P);
     const int n = (T + 46) / 2 + 1;
+    auto val = [&](int i) -> float {
+        if (i >= T_MAX3 + 48) return 0.f;
+        if (!from_es) return cpad[i];
+        const int t = i - 15;
+        return (t >= 0 && t < len) ? es[t] : 0.f;
+    };
     for (int i = tid; i < n && i < PW3; i += NT) {
-        const float c0 = cpad[2 * i], c1 = cpad[2 * i + 1], c2 = (2 * i + 2 < T_MAX3 + 48) ? cpad[2 * i + 2] : 0.f;
+        const float c0 = val(2 * i), c1 = val(2 * i + 1), c2 = val(2 * i + 2);
         const float h0 = __bfloat162float(__float2bfloat16_rn(c0));
         const float h1 = __bfloat162float(__float2bfloat16_rn(c1));
         const float h2 = __bfloat162float(__float2bfloat16_rn(c2));
@@ -51,7 +59,10 @@ __device__ __forceinline__ void att3_loc_tile(float (&acc)[4], int t0, int lane,
 // pre[t][d] = keys[b][t][d] + b_a[d] + conv_bias.Wl[d] + location term, for all t < len of row b.
 // T <= PRE_REG_T: kept in registers preR[tile][4] (thread = rows 16*tile + gq (+8), columns 8*warp + 2*tq (+1));
 // otherwise written to the row's global scratch [T][128].
-__device__ __forceinline__ void att3_location(const Dec3Params& p, float (&preR)[8][4], float* pre_scr, int b, int len, int warp, int lane) {
+// incremental: the pair arrays hold the NEW alignments and the (linear) location term is accumulated: pre += T(a).G
+// -- no key reload from L2 (cumulative attention only).
+__device__ __forceinline__ void att3_location(const Dec3Params& p, float (&preR)[8][4], float* pre_scr, int b, int len, int warp, int lane,
+                                              bool incremental = false) {
     const int gq = lane >> 2, tq = lane & 3;
     uint2 ghi[2], glo[2];
 #pragma unroll
@@ -61,6 +72,38 @@ __device__ __forceinline__ void att3_location(const Dec3Params& p, float (&preR)
     }
     const int d0 = warp * 8 + 2 * tq;
     const float bc0 = SMF(SO_BC)[d0], bc1 = SMF(SO_BC)[d0 + 1];
+    if (incremental) {
+        if (p.pre_reg) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                if (16 * i < len) {
+                    float acc[4];
+                    att3_loc_tile(acc, 16 * i, lane, ghi, glo);
+                    preR[i][0] += acc[0];
+                    preR[i][1] += acc[1];
+                    preR[i][2] += acc[2];
+                    preR[i][3] += acc[3];
+                }
+            }
+        } else {
+            for (int t0 = 0; t0 < len; t0 += 16) {
+                const int ta = t0 + gq, tb = ta + 8;
+                float acc[4];
+                att3_loc_tile(acc, t0, lane, ghi, glo);
+                if (ta < len) {
+                    float2* d = reinterpret_cast<float2*>(pre_scr + (size_t)ta * ATT + d0);
+                    const float2 o = *d;
+                    *d = make_float2(o.x + acc[0], o.y + acc[1]);
+                }
+                if (tb < len) {
+                    float2* d = reinterpret_cast<float2*>(pre_scr + (size_t)tb * ATT + d0);
+                    const float2 o = *d;
+                    *d = make_float2(o.x + acc[2], o.y + acc[3]);
+                }
+            }
+        }
+        return;
+    }
     if (p.pre_reg) {
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
@@ -97,20 +140,32 @@ __device__ __forceinline__ void att3_location(const Dec3Params& p, float (&preR)
 __device__ __forceinline__ void att3_step(const Dec3Params& p, float (&preR)[8][4], float* pre_scr, int b, int len, int rank, int s,
                                           int tid, int warp, int lane, Guard3& g, long long* tacc, long long& tprev, bool timing) {
     float* scr = SMF(SO_RED);
+#define A3_STAMP(i)                                                     \
+    if (timing) {                                                       \
+        long long now_;                                                 \
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now_));        \
+        tacc[i] += now_ - tprev;                                        \
+        tprev = now_;                                                   \
+    }
     // E1: q[d] = sum over the 16 source CTAs of their K-slice partial (query_layer, Attention.py:187-189)
-    if (tid < ATT) {
+    {
+        // 4 threads per d, 4 sources each
+        const int d = tid >> 2, part = tid & 3;
         float q = 0.f;
-#pragma unroll 4
-        for (int src = 0; src < CS; ++src) {
-            const uint32_t* a = SMU(SO_QRECV) + src * ATT + tid;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const uint32_t* a = SMU(SO_QRECV) + (part * 4 + i) * ATT + d;
             uint32_t w = *reinterpret_cast<const volatile uint32_t*>(a);
             int spins = 0;
             while (w == SENT && !spin_check3(g, spins)) w = *reinterpret_cast<const volatile uint32_t*>(a);
             q += __uint_as_float(w);
         }
-        SMF(SO_QS)[tid] = g.dead ? 0.f : q;
+        q += __shfl_xor_sync(0xffffffffu, q, 1);
+        q += __shfl_xor_sync(0xffffffffu, q, 2);
+        if (part == 0) SMF(SO_QS)[d] = g.dead ? 0.f : q;
     }
     __syncthreads();
+    A3_STAMP(8)
     for (int i = tid; i < CS * ATT; i += NT) SMU(SO_QRECV)[i] = SENT;  // re-arm for the next step
     // E2: energies e[t] = sum_d v_a[d] tanh(pre[t][d] + q[d])   (Attention.py:401)
     if (p.pre_reg) {
@@ -162,6 +217,7 @@ __device__ __forceinline__ void att3_step(const Dec3Params& p, float (&preR)[8][
         }
     }
     __syncthreads();
+    A3_STAMP(16)
     // E3: masked softmax over t < len (exact zeros beyond: -inf mask), Attention.py:203-206
     if (warp == 0) {
         float m = -INFINITY;
@@ -171,7 +227,7 @@ __device__ __forceinline__ void att3_step(const Dec3Params& p, float (&preR)[8][
         }
         float sum = 0.f;
         for (int t = lane; t < len; t += 32) {
-            const float v = p.smoothing ? sigmoidf_(SMF(SO_ES)[t]) : expf(SMF(SO_ES)[t] - m);
+            const float v = p.smoothing ? sigmoidf_(SMF(SO_ES)[t]) : __expf(SMF(SO_ES)[t] - m);
             SMF(SO_ES)[t] = v;
             sum += v;
         }
@@ -180,6 +236,7 @@ __device__ __forceinline__ void att3_step(const Dec3Params& p, float (&preR)[8][
         for (int t = lane; t < len; t += 32) SMF(SO_ES)[t] *= inv;
     }
     __syncthreads();
+    A3_STAMP(10)
     // E4: cumulate + alignment history
     for (int t = tid; t < p.T; t += NT) {
         const float a = t < len ? SMF(SO_ES)[t] : 0.f;
@@ -193,7 +250,7 @@ __device__ __forceinline__ void att3_step(const Dec3Params& p, float (&preR)[8][
         float c[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
         if (tg < TG) {
             const uint4* vp = reinterpret_cast<const uint4*>(p.values + (size_t)b * p.T * MEM) + d8;
-#pragma unroll 4
+#pragma unroll 8
             for (int t = tg; t < len; t += TG) {
                 const uint4 v = ldg_stream_v4(vp + (size_t)t * D8);
                 const float a = SMF(SO_ES)[t];
@@ -224,6 +281,7 @@ __device__ __forceinline__ void att3_step(const Dec3Params& p, float (&preR)[8][
             *reinterpret_cast<float2*>(p.ctx_state + (size_t)b * MEM + 2 * tid) = make_float2(x0, x1);
         }
         __syncthreads();
+        A3_STAMP(17)
         // multicast this row's 48 x 32-byte chunks into every CTA's context buffer
         for (int i = tid; i < CS * KS_CTX * 2; i += NT) {
             const int dst = i / (KS_CTX * 2), v = i - dst * (KS_CTX * 2);
@@ -232,19 +290,14 @@ __device__ __forceinline__ void att3_step(const Dec3Params& p, float (&preR)[8][
             st_remote_v4(mapa_rank(smem_addr(SMU(SO_CTX) + ks * TILE_W + ((rank >> 3) << 6) + ((rank & 7) << 3) + half * 4), dst), val);
         }
     }
-    if (timing) {
-        long long now_;
-        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now_));
-        tacc[8] += now_ - tprev;
-        tprev = now_;
-    }
+    A3_STAMP(15)
 }
 
 // E6 (off the critical path, after the projection): location pre-activations of the NEXT step from the new cumulative alignments
 __device__ __forceinline__ void att3_next(const Dec3Params& p, float (&preR)[8][4], float* pre_scr, int b, int len, int tid, int warp, int lane) {
-    att3_build_pairs(p.T, tid);
+    att3_build_pairs(p.T, tid, p.cumulative != 0, len);
     __syncthreads();
-    att3_location(p, preR, pre_scr, b, len, warp, lane);
+    att3_location(p, preR, pre_scr, b, len, warp, lane, p.cumulative != 0);
 }
 
 }  // namespace

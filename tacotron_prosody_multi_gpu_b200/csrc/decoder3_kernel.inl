@@ -43,7 +43,7 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
             SMF(SO_BC)[tid] = p.bconst[tid];
         }
         for (int i = tid; i < T_MAX3 + 48; i += NT) SMF(SO_CPAD)[i] = 0.f;
-        if (tid < 8 + 32) SMU(SO_FLAG)[tid] = 0;
+        if (tid < 8 + 48) SMU(SO_FLAG)[tid] = 0;
         rearm(SMU(SO_X), KS_X + 6 * KS_H + KS_CTX, R, tid);   // all activation buffers are contiguous
         for (int i = tid; i < CS * ATT; i += NT) SMU(SO_QRECV)[i] = SENT;
     }
@@ -70,7 +70,7 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
     const bool att = rank < R;
     const int ab = row0 + (att ? rank : 0);
     const int alen = att ? p.lens[ab] : 0;
-    float* pre_scr = p.pre_scratch ? p.pre_scratch + (size_t)ab * p.T * ATT : nullptr;
+    float* pre_scr = p.pre_scratch + (size_t)ab * p.T * ATT;   // [T][128]: working copy when !pre_reg, saved state otherwise
     float preR[8][4];
 #pragma unroll
     for (int i = 0; i < 8; ++i) preR[i][0] = preR[i][1] = preR[i][2] = preR[i][3] = 0.f;
@@ -80,7 +80,27 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
         __syncthreads();
         att3_build_pairs(p.T, tid);
         __syncthreads();
-        att3_location(p, preR, pre_scr, ab, alen, warp, lane);
+        if (!p.cont || !p.cumulative) {
+            att3_location(p, preR, pre_scr, ab, alen, warp, lane);
+        } else if (p.pre_reg) {
+            // continuation launch: the accumulated pre-activations were saved by the previous launch (keeps cell stepping
+            // bit-identical to one multi-step launch)
+            const int gq = lane >> 2, tq = lane & 3, d0 = warp * 8 + 2 * tq;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const int ta = 16 * i + gq, tb = ta + 8;
+                if (ta < alen) {
+                    const float2 v = *reinterpret_cast<const float2*>(pre_scr + (size_t)ta * ATT + d0);
+                    preR[i][0] = v.x;
+                    preR[i][1] = v.y;
+                }
+                if (tb < alen) {
+                    const float2 v = *reinterpret_cast<const float2*>(pre_scr + (size_t)tb * ATT + d0);
+                    preR[i][2] = v.x;
+                    preR[i][3] = v.y;
+                }
+            }
+        }
     }
     // every CTA of the cluster has armed its buffers before any peer may write into them
     cluster.sync();
@@ -139,6 +159,9 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
                     if (i < p.NCL) fl[i] = ldg_relaxed(reinterpret_cast<const uint32_t*>(p.flags) + (size_t)(s - 2) * p.NCL + i);
             }
         }
+        // prenet dropout bits of this step (always on, Decoder.py:350-351): computed while the feedback frame is in flight
+        const bool keep0 = evalid && keep_bit3(p, step, eb, 0, 16 * rank + eu);
+        const bool keep1 = evalid && keep_bit3(p, step, eb, 1, 16 * rank + eu);
         // ================= P1: prenet dense_1 (Decoder.py:346-351) =================
         {
             float acc[2][4] = {};
@@ -177,7 +200,7 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
 #pragma unroll
                 for (int k = 0; k < KS_X; ++k) z += red[(k * 16 + eu) * 17 + er];
                 z = fmaxf(z, 0.f);
-                z = (evalid && keep_bit3(p, step, eb, 0, 16 * rank + eu)) ? z * p.keep_scale : 0.f;
+                z = keep0 ? z * p.keep_scale : 0.f;
                 const float zn = __shfl_down_sync(0xffffffffu, z, 1);
                 if (!(eu & 1)) SMU(SO_STG_R)[bword(er, eu >> 1)] = pack_bf16x2(z, zn);
             }
@@ -203,7 +226,7 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
 #pragma unroll
                 for (int k = 0; k < 16; ++k) z += red[(k * 16 + eu) * 17 + er];
                 z = fmaxf(z, 0.f);
-                z = (evalid && keep_bit3(p, step, eb, 1, 16 * rank + eu)) ? z * p.keep_scale : 0.f;
+                z = keep1 ? z * p.keep_scale : 0.f;
                 const float zn = __shfl_down_sync(0xffffffffu, z, 1);
                 if (!(eu & 1)) SMU(SO_STG_R)[bword(er, eu >> 1)] = pack_bf16x2(z, zn);
             }
@@ -379,7 +402,7 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
     }
 
     if (timing)
-        for (int i = 0; i < 16; ++i) p.timing[(size_t)blockIdx.x * 16 + i] = tacc[i];
+        for (int i = 0; i < 24; ++i) p.timing[(size_t)blockIdx.x * 24 + i] = tacc[i];
     // ---- write back the recurrent state + step count ----
     if (evalid) {
         p.c1[(size_t)eb * DEC + 16 * rank + eu] = c1s;
@@ -387,8 +410,18 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
         p.c2[(size_t)eb * DEC + 16 * rank + eu] = c2s;
         p.h2z[(size_t)eb * DEC + 16 * rank + eu] = h2s;
     }
-    if (att)
+    if (att) {
         for (int t = tid; t < p.T; t += NT) p.cum[(size_t)ab * p.T + t] = SMF(SO_CPAD)[15 + t];
+        if (p.pre_reg) {
+            const int gq = lane >> 2, tq = lane & 3, d0 = warp * 8 + 2 * tq;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const int ta = 16 * i + gq, tb = ta + 8;
+                if (ta < alen) *reinterpret_cast<float2*>(pre_scr + (size_t)ta * ATT + d0) = make_float2(preR[i][0], preR[i][1]);
+                if (tb < alen) *reinterpret_cast<float2*>(pre_scr + (size_t)tb * ATT + d0) = make_float2(preR[i][2], preR[i][3]);
+            }
+        }
+    }
     if (blockIdx.x == 0 && tid == 0) {
         int steps = s_done;
         if (free_run) {

@@ -99,7 +99,8 @@ struct Dec3Params {
     int B, T, NCL, R;       // NCL clusters; cluster i owns batch rows [i*R, min(B, i*R + R))
     int S_max, S_cap, t0, mode;
     int stop_at_any, cumulative, smoothing, stop_sigmoid;
-    int pre_reg;            // T <= 128: location pre-activations live in registers (else pre_scratch)
+    int pre_reg;            // T <= 128: location pre-activations live in registers (else in pre_scratch)
+    int cont;               // continuation launch (reset_state == 0): pre-activations are loaded from pre_scratch
     float zoneout, keep_scale;
     const uint32_t* res_blobs;   // [16 ranks][TACO_DEC3_RES_WORDS] A-fragment tiles resident in shared memory + fp32 biases
     const uint4* stream_blobs;   // [16 ranks][320 tiles][32 lanes] A-fragment tiles streamed from L2: W1c [4][48], W1h [4][16], W2z [4][16]
@@ -113,7 +114,7 @@ struct Dec3Params {
     float* ctx_state;            // [B][768]
     float* cum;                  // [B][T]
     float* x_state;              // [B][80] next decoder input (free-running)
-    float* pre_scratch;          // [B][T][128] when !pre_reg, else null
+    float* pre_scratch;          // [B][T][128] location pre-activations: working copy (!pre_reg) / state saved between launches
     const float* targets;
     int F_tgt;
     const uint8_t* masks;
