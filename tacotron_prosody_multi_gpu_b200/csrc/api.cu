@@ -455,14 +455,10 @@ int pack_decoder3(TacoHandle* h) {
         p += 5 * 128;
         for (int ks = 0; ks < 16; ++ks) pack_tile(p + ks * 128, [&](int k, int m) { return kp2->host[(size_t)(ks * 16 + k) * 256 + 16 * c + m]; });
         p += 16 * 128;
-        for (int mt = 0; mt < 4; ++mt)
-            for (int ks = 0; ks < 16; ++ks)
-                pack_tile(p + (mt * 16 + ks) * 128, [&](int k, int m) { return k1->host[(size_t)(ks * 16 + k) * 1024 + mt * 256 + 16 * c + m]; });
-        p += 64 * 128;
-        for (int mt = 0; mt < 4; ++mt)
-            for (int ks = 0; ks < 16; ++ks)
-                pack_tile(p + (mt * 16 + ks) * 128, [&](int k, int m) { return k2->host[(size_t)(ks * 16 + k) * 1024 + mt * 256 + 16 * c + m]; });
-        p += 64 * 128;
+        for (int mt = 0; mt < 4; ++mt)   // resident: first 32 k-steps of the LSTM-1 context rows [256, 256 + 512)
+            for (int ks = 0; ks < 32; ++ks)
+                pack_tile(p + (mt * 32 + ks) * 128, [&](int k, int m) { return k1->host[(size_t)(256 + ks * 16 + k) * 1024 + mt * 256 + 16 * c + m]; });
+        p += 128 * 128;
         for (int mt = 0; mt < 8; ++mt) pack_tile(p + mt * 128, [&](int k, int m) { return kq->host[(size_t)(16 * c + k) * 128 + mt * 16 + m]; });
         p += 8 * 128;
         float* bias = reinterpret_cast<float*>(p);
@@ -477,14 +473,17 @@ int pack_decoder3(TacoHandle* h) {
             bias[160 + u] = c < 10 ? bf->host[16 * c + u] : ((c == 10 && u < 2) ? bst->host[u] : 0.f);
         }
         uint32_t* q = str.data() + (size_t)c * SW;
-        for (int mt = 0; mt < 4; ++mt) {
-            for (int ks = 0; ks < 48; ++ks)   // LSTM-1 kernel rows of the context [256, 1024)
-                pack_tile(q + (mt * 48 + ks) * 128, [&](int k, int m) { return k1->host[(size_t)(256 + ks * 16 + k) * 1024 + mt * 256 + 16 * c + m]; });
-            for (int ks = 0; ks < 16; ++ks) {  // LSTM-1 rows of h1 [1024, 1280); LSTM-2 rows of h2 [256, 512)
-                pack_tile(q + (192 + mt * 16 + ks) * 128, [&](int k, int m) { return k1->host[(size_t)(1024 + ks * 16 + k) * 1024 + mt * 256 + 16 * c + m]; });
-                pack_tile(q + (256 + mt * 16 + ks) * 128, [&](int k, int m) { return k2->host[(size_t)(256 + ks * 16 + k) * 1024 + mt * 256 + 16 * c + m]; });
+        // streamed sets [4 mt][16 ks]: 0 LSTM-1 prenet rows [0,256); 1 LSTM-2 h1 rows [0,256); 2 LSTM-1 h1 rows [1024,1280);
+        // 3 LSTM-2 h2 rows [256,512); 4 LSTM-1 context rows [768,1024) (context k-steps 32..47)
+        for (int mt = 0; mt < 4; ++mt)
+            for (int ks = 0; ks < 16; ++ks) {
+                auto col = [&](int m) { return mt * 256 + 16 * c + m; };
+                pack_tile(q + (0 + mt * 16 + ks) * 128, [&](int k, int m) { return k1->host[(size_t)(ks * 16 + k) * 1024 + col(m)]; });
+                pack_tile(q + (64 + mt * 16 + ks) * 128, [&](int k, int m) { return k2->host[(size_t)(ks * 16 + k) * 1024 + col(m)]; });
+                pack_tile(q + (128 + mt * 16 + ks) * 128, [&](int k, int m) { return k1->host[(size_t)(1024 + ks * 16 + k) * 1024 + col(m)]; });
+                pack_tile(q + (192 + mt * 16 + ks) * 128, [&](int k, int m) { return k2->host[(size_t)(256 + ks * 16 + k) * 1024 + col(m)]; });
+                pack_tile(q + (256 + mt * 16 + ks) * 128, [&](int k, int m) { return k1->host[(size_t)(768 + ks * 16 + k) * 1024 + col(m)]; });
             }
-        }
     }
     if ((rc = upload_words(h, res, &h->dec3_res))) return rc;
     return upload_words(h, str, &h->dec3_stream);

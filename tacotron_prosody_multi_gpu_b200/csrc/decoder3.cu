@@ -46,9 +46,9 @@ constexpr int TILE_W = 128;             // words of one A tile (32 lanes x uint4
 constexpr int SO_WO = 0;                          // [64 ks] frame/stop projection tiles (ks 0..15: h2raw, 16..63: context)
 constexpr int SO_WP1 = SO_WO + 64 * TILE_W;       // [5]
 constexpr int SO_WP2 = SO_WP1 + 5 * TILE_W;       // [16]
-constexpr int SO_W1P = SO_WP2 + 16 * TILE_W;      // [4 mt][16 ks]  LSTM-1, prenet-output rows
-constexpr int SO_W2H = SO_W1P + 64 * TILE_W;      // [4 mt][16 ks]  LSTM-2, h1raw rows
-constexpr int SO_WQ = SO_W2H + 64 * TILE_W;       // [8 mt]         query kernel rows of this CTA's 16 units
+constexpr int W1C_RES = 32;                       // k-steps of the LSTM-1 context rows kept in shared memory (of 48)
+constexpr int SO_W1C = SO_WP2 + 16 * TILE_W;      // [4 mt][32 ks]  LSTM-1, context rows [256, 256 + 512)
+constexpr int SO_WQ = SO_W1C + 4 * W1C_RES * TILE_W;  // [8 mt]     query kernel rows of this CTA's 16 units
 constexpr int SO_BIAS = SO_WQ + 8 * TILE_W;       // b1[64] b2[64] bp1[16] bp2[16] bo[16]
 constexpr int RES_WORDS = SO_BIAS + 176;          // resident blob words per rank
 constexpr int SO_X = RES_WORDS;                   // activation buffers (B-fragment order, one 128-word block per k-step)
@@ -72,8 +72,8 @@ constexpr int SO_P = SO_CPAD + T_MAX3 + 48;       // 4 x [PW3] pair arrays P0hi,
 constexpr int SO_QS = SO_P + 4 * PW3;             // [128]
 constexpr int SO_VA = SO_QS + ATT;
 constexpr int SO_BC = SO_VA + ATT;
-constexpr int SO_FLAG = SO_BC + ATT;              // [8]
-constexpr int SO_TACC = SO_FLAG + 8;              // 24 x int64 stage timers
+constexpr int SO_FLAG = SO_BC + ATT;              // [16]: 0 = stop decision, 8.. = prefetched stop words of the clusters
+constexpr int SO_TACC = SO_FLAG + 16;              // 24 x int64 stage timers
 constexpr int SMEM3_WORDS = SO_TACC + 48;
 static_assert(RES_WORDS == TACO_DEC3_RES_WORDS, "resident blob size");
 static_assert(SMEM3_WORDS * 4 <= 227 * 1024, "shared memory budget");
@@ -121,6 +121,11 @@ __device__ __forceinline__ uint4 ldg_stream_v4(const uint4* p) {
     asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
     return v;
 }
+
+__device__ __forceinline__ void cp_async_4(uint32_t* smem_dst, const void* gsrc) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_addr(smem_dst)), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
 // bounded spin: a poll that never completes (a bug, not a data condition) raises the abort flag instead of
 // hanging the GPU; once raised every poll in every CTA falls through.
@@ -173,64 +178,144 @@ __device__ __forceinline__ uint2 load_b(const uint32_t* blk, int j, int lane, Gu
     return b;
 }
 
-// acc[j] += A(tile) . B(block ks, n-tile j) over this warp's k-steps ks = k0, k0 + kstride, ... < KS
-// A tiles: a_tiles + (ks * a_ks_stride) words, fragment-major in shared memory.
-template <int NTL>
-__device__ __forceinline__ void gemm_smem(float (&acc)[2][4], const uint32_t* a_tiles, int a_ks_stride, const uint32_t* bbuf, int KS,
-                                          int k0, int kstride, int lane, Guard3& g) {
-    for (int ks = k0; ks < KS; ks += kstride) {
-        const uint4 a = *reinterpret_cast<const uint4*>(a_tiles + ks * a_ks_stride + (lane << 2));
-#pragma unroll
-        for (int j = 0; j < NTL; ++j) {
-            const uint2 b = load_b(bbuf + ks * TILE_W, j, lane, g);
-            mma16816(acc[j], a, b);
-        }
-    }
-}
+// ---------------------------------------------------------------------------------------------
+// The loop body of the kernel is executed by 16 warps that are almost always waiting on a dependency; what it must not
+// do is miss the 32 KB instruction cache every step.  Everything that repeats is therefore ONE out-of-line routine with
+// its operands passed and returned in registers (by-value structs).
+// ---------------------------------------------------------------------------------------------
+struct AccV {
+    float v[2][4];
+    int dead;
+};
+struct A4 {
+    uint4 a[4];
+};
 
-// same with the A tiles streamed from global memory (L2-resident, fragment-major): tiles at a_glob + ks * a_ks_stride (uint4 units)
-template <int NTL, int CH>
-__device__ __forceinline__ void gemm_stream(float (&acc)[2][4], const uint4* a_glob, int a_ks_stride, const uint32_t* bbuf, int KS, int k0,
-                                            int kstride, int lane, Guard3& g) {
-    for (int ksb = k0; ksb < KS; ksb += CH * kstride) {
-        uint4 a[CH];
+// Just-in-time weight tiles: the 4 A tiles (k-steps kg, kg+4, kg+8, kg+12 of a 16-k-step set) this warp needs in a later
+// phase are requested from L2 BEFORE the wait that precedes that phase, so their latency hides behind the exchange.
+__device__ __forceinline__ void prefetch4(uint4 (&a)[4], const uint4* set_mt, int kg, int lane) {
 #pragma unroll
-        for (int i = 0; i < CH; ++i) {
-            const int ks = ksb + i * kstride;
-            if (ks < KS) a[i] = ldg_stream_v4(a_glob + (size_t)ks * a_ks_stride + lane);
-        }
+    for (int i = 0; i < 4; ++i) a[i] = ldg_stream_v4(set_mt + (size_t)(kg + 4 * i) * 32 + lane);
+}
+// the 8 B fragments (4 k-steps x 2 n-tiles) of blocks ks0, ks0 + kstride, ...: all loads in flight together, ONE vote per round
+__device__ __forceinline__ void load_b4(uint2 (&b)[4][2], const uint32_t* bbuf, int ks0, int kstride, int nks, int lane, Guard3& g) {
+    int spins = 0;
+    while (true) {
+        bool bad = false;
 #pragma unroll
-        for (int i = 0; i < CH; ++i) {
-            const int ks = ksb + i * kstride;
-            if (ks < KS) {
+        for (int i = 0; i < 4; ++i) {
+            if (i < nks) {
 #pragma unroll
-                for (int j = 0; j < NTL; ++j) {
-                    const uint2 b = load_b(bbuf + ks * TILE_W, j, lane, g);
-                    mma16816(acc[j], a[i], b);
+                for (int j = 0; j < 2; ++j) {
+                    b[i][j] = lds_poll_v2(bbuf + (ks0 + i * kstride) * TILE_W + (j << 6) + (lane << 1));
+                    bad = bad || b[i][j].x == SENT || b[i][j].y == SENT;
                 }
             }
         }
+        if (!__any_sync(0xffffffffu, bad)) break;
+        if (g.dead || spin_check3(g, spins)) break;
     }
+    g.dead = __any_sync(0xffffffffu, g.dead);
+}
+// acc[j] += A(regs i) . B(block kg + 4 i, n-tile j)
+__device__ __forceinline__ AccV gemm_regs_core(AccV acc, A4 a, const uint32_t* bbuf, int kg, int lane, int* abort_flag) {
+    Guard3 g{abort_flag, acc.dead != 0};
+    uint2 b[4][2];
+    load_b4(b, bbuf, kg, 4, 4, lane, g);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+#pragma unroll
+        for (int j = 0; j < 2; ++j) mma16816(acc.v[j], a.a[i], b[i][j]);
+    }
+    acc.dead = g.dead;
+    return acc;
+}
+// resident tiles, k-steps k0, k0 + kstride, ... < KS in chunks of 4
+__device__ __forceinline__ AccV gemm_smem4_core(AccV acc, const uint32_t* a_tiles, const uint32_t* bbuf, int KS, int k0, int kstride, int lane,
+                                              int* abort_flag) {
+    Guard3 g{abort_flag, acc.dead != 0};
+    for (int ksb = k0; ksb < KS; ksb += 4 * kstride) {
+        const int nks = min(4, (KS - ksb + kstride - 1) / kstride);
+        uint4 a[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+            if (i < nks) a[i] = *reinterpret_cast<const uint4*>(a_tiles + (ksb + i * kstride) * TILE_W + (lane << 2));
+        uint2 b[4][2];
+        load_b4(b, bbuf, ksb, kstride, nks, lane, g);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            if (i < nks) {
+#pragma unroll
+                for (int j = 0; j < 2; ++j) mma16816(acc.v[j], a[i], b[i][j]);
+            }
+        }
+    }
+    acc.dead = g.dead;
+    return acc;
+}
+__device__ __forceinline__ void gemm_regs(float (&acc)[2][4], const uint4 (&a)[4], const uint32_t* bbuf, int kg, int lane, Guard3& g) {
+    AccV x;
+    A4 t;
+#pragma unroll
+    for (int j = 0; j < 2; ++j)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) x.v[j][i] = acc[j][i];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) t.a[i] = a[i];
+    x.dead = g.dead;
+    x = gemm_regs_core(x, t, bbuf, kg, lane, g.abort_flag);
+#pragma unroll
+    for (int j = 0; j < 2; ++j)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) acc[j][i] = x.v[j][i];
+    g.dead = x.dead != 0;
+}
+__device__ __forceinline__ void gemm_smem4(float (&acc)[2][4], const uint32_t* a_tiles, const uint32_t* bbuf, int KS, int k0, int kstride,
+                                           int lane, Guard3& g) {
+    AccV x;
+#pragma unroll
+    for (int j = 0; j < 2; ++j)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) x.v[j][i] = acc[j][i];
+    x.dead = g.dead;
+    x = gemm_smem4_core(x, a_tiles, bbuf, KS, k0, kstride, lane, g.abort_flag);
+#pragma unroll
+    for (int j = 0; j < 2; ++j)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) acc[j][i] = x.v[j][i];
+    g.dead = x.dead != 0;
 }
 
 // partial accumulators of warp (mt, kg) -> red[((kg * MTN + mt) * 16 + m) * 17 + n]
-__device__ __forceinline__ void store_red3(float* red, const float (&acc)[2][4], int slot, int lane, int ntl) {
+__device__ __forceinline__ void store_red3_core(float* red, AccV acc, int slot, int lane) {
     const int gq = lane >> 2, tq = lane & 3;
     float* r0 = red + (slot * 16 + gq) * 17 + 2 * tq;
-    for (int j = 0; j < ntl; ++j) {
-        r0[8 * j] = acc[j][0];
-        r0[8 * j + 1] = acc[j][1];
-        r0[8 * 17 + 8 * j] = acc[j][2];
-        r0[8 * 17 + 8 * j + 1] = acc[j][3];
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+        r0[8 * j] = acc.v[j][0];
+        r0[8 * j + 1] = acc.v[j][1];
+        r0[8 * 17 + 8 * j] = acc.v[j][2];
+        r0[8 * 17 + 8 * j + 1] = acc.v[j][3];
     }
+}
+__device__ __forceinline__ void store_red3(float* red, const float (&acc)[2][4], int slot, int lane, int) {
+    AccV x;
+#pragma unroll
+    for (int j = 0; j < 2; ++j)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) x.v[j][i] = acc[j][i];
+    x.dead = 0;
+    store_red3_core(red, x, slot, lane);
 }
 
 // re-arm a consumed activation buffer: valid rows -> sentinel, padding rows -> 0 (they have no producer)
 __device__ __forceinline__ void rearm(uint32_t* buf, int KS, int R, int tid) {
-    for (int i = tid; i < KS * TILE_W; i += NT) {
-        const int w = i & (TILE_W - 1);
-        const int row = ((w >> 6) << 3) + ((w & 63) >> 3);
-        buf[i] = row < R ? SENT : 0u;
+    uint4* b4 = reinterpret_cast<uint4*>(buf);
+    for (int i = tid; i < KS * (TILE_W / 4); i += NT) {
+        const int v = i & 31;   // uint4 index inside the block: 4 words = 2 lanes of one row
+        const int row = ((v >> 4) << 3) + ((v & 15) >> 1);
+        const uint32_t x = row < R ? SENT : 0u;
+        b4[i] = make_uint4(x, x, x, x);
     }
 }
 
@@ -244,9 +329,26 @@ __device__ __forceinline__ void multicast_block(const uint32_t* stage, uint32_t*
     }
 }
 
+// Philox4x32-10 as in common.cuh (same counter / key layout, restated in oracle/philox.py), rolled and out of line
+__device__ __forceinline__ bool philox_keep3(uint64_t seed, uint32_t step, uint32_t row, uint32_t layer, uint32_t unit) {
+    const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
+    uint4 c = make_uint4(step, row, layer, unit >> 7);
+    uint2 k = make_uint2((uint32_t)seed, (uint32_t)(seed >> 32));
+#pragma unroll 1
+    for (int i = 0; i < 10; ++i) {
+        const uint32_t hi0 = __umulhi(M0, c.x), lo0 = M0 * c.x;
+        const uint32_t hi1 = __umulhi(M1, c.z), lo1 = M1 * c.z;
+        c = make_uint4(hi1 ^ c.y ^ k.x, lo1, hi0 ^ c.w ^ k.y, lo0);
+        k.x += W0;
+        k.y += W1;
+    }
+    const uint32_t bit = unit & 127u;
+    const uint32_t w = (bit >> 5) == 0 ? c.x : ((bit >> 5) == 1 ? c.y : ((bit >> 5) == 2 ? c.z : c.w));
+    return (w >> (bit & 31u)) & 1u;
+}
 __device__ __forceinline__ bool keep_bit3(const Dec3Params& p, int step, int b, int layer, int unit) {
     if (p.masks) return p.masks[(((size_t)(step - p.t0) * p.B + b) * 2 + layer) * PRE + unit] != 0;
-    return philox_keep(p.seed, (uint32_t)step, (uint32_t)b, (uint32_t)layer, (uint32_t)unit);
+    return philox_keep3(p.seed, (uint32_t)step, (uint32_t)b, (uint32_t)layer, (uint32_t)unit);
 }
 
 }  // namespace

@@ -28,14 +28,17 @@ __device__ __forceinline__ void att3_build_pairs(int T, int tid, bool from_es = 
 
 // One 16-row tile of the location term: acc[t][d] = sum_k cum[t + k - 15] G[k][d], d = 8*warp + 2*tq (+1), rows t0+gq, t0+gq+8
 // (Attention.py:193-197 fused: conv1d(k=31, 32 filters) then Dense(128, no bias)); hi/lo bf16 split, 3 MMAs per k-step.
-__device__ __forceinline__ void att3_loc_tile(float (&acc)[4], int t0, int lane, const uint2 (&ghi)[2], const uint2 (&glo)[2]) {
+struct G4 {
+    uint2 hi[2], lo[2];
+};
+__device__ __forceinline__ float4 att3_loc_tile_core(int t0, int lane, G4 gm) {
     const int gq = lane >> 2, tq = lane & 3;
     const uint32_t* P0h = SMU(SO_P);
     const uint32_t* P1h = SMU(SO_P + PW3);
     const uint32_t* P0l = SMU(SO_P + 2 * PW3);
     const uint32_t* P1l = SMU(SO_P + 3 * PW3);
     const int ta = t0 + gq, tb = ta + 8;
-    acc[0] = acc[1] = acc[2] = acc[3] = 0.f;
+    float acc[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
     for (int ks = 0; ks < 2; ++ks) {
         uint4 ah, al;
@@ -50,10 +53,17 @@ __device__ __forceinline__ void att3_loc_tile(float (&acc)[4], int t0, int lane,
         al.y = ob ? P1l[ib >> 1] : P0l[ib >> 1];
         al.z = oa ? P1l[(ia + 8) >> 1] : P0l[(ia + 8) >> 1];
         al.w = ob ? P1l[(ib + 8) >> 1] : P0l[(ib + 8) >> 1];
-        mma16816(acc, ah, ghi[ks]);
-        mma16816(acc, ah, glo[ks]);
-        mma16816(acc, al, ghi[ks]);
+        mma16816(acc, ah, gm.hi[ks]);
+        mma16816(acc, ah, gm.lo[ks]);
+        mma16816(acc, al, gm.hi[ks]);
     }
+    return make_float4(acc[0], acc[1], acc[2], acc[3]);
+}
+__device__ __forceinline__ void att3_loc_tile(float (&acc)[4], int t0, int lane, const uint2 (&ghi)[2], const uint2 (&glo)[2]) {
+    G4 gm;
+    gm.hi[0] = ghi[0]; gm.hi[1] = ghi[1]; gm.lo[0] = glo[0]; gm.lo[1] = glo[1];
+    const float4 r = att3_loc_tile_core(t0, lane, gm);
+    acc[0] = r.x; acc[1] = r.y; acc[2] = r.z; acc[3] = r.w;
 }
 
 // pre[t][d] = keys[b][t][d] + b_a[d] + conv_bias.Wl[d] + location term, for all t < len of row b.
@@ -141,10 +151,10 @@ __device__ __forceinline__ void att3_step(const Dec3Params& p, float (&preR)[8][
                                           int tid, int warp, int lane, Guard3& g, long long* tacc, long long& tprev, bool timing) {
     float* scr = SMF(SO_RED);
 #define A3_STAMP(i)                                                     \
-    if (timing) {                                                       \
+    if (timing) { /* whole warp 0, uniform: a divergent stamp would push the following collectives onto their slow path */ \
         long long now_;                                                 \
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now_));        \
-        tacc[i] += now_ - tprev;                                        \
+        if (lane == 0) tacc[i] += now_ - tprev;                         \
         tprev = now_;                                                   \
     }
     // E1: q[d] = sum over the 16 source CTAs of their K-slice partial (query_layer, Attention.py:187-189)
@@ -220,20 +230,52 @@ __device__ __forceinline__ void att3_step(const Dec3Params& p, float (&preR)[8][
     A3_STAMP(16)
     // E3: masked softmax over t < len (exact zeros beyond: -inf mask), Attention.py:203-206
     if (warp == 0) {
-        float m = -INFINITY;
-        if (!p.smoothing) {
-            for (int t = lane; t < len; t += 32) m = fmaxf(m, SMF(SO_ES)[t]);
-            m = warp_max(m);
+        if (len <= 128) {
+            // whole row in registers: 4 positions per lane
+            float e[4];
+            float m = -INFINITY;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int t = lane + 32 * i;
+                e[i] = t < len ? SMF(SO_ES)[t] : -INFINITY;
+                m = fmaxf(m, e[i]);
+            }
+            A3_STAMP(18)
+            m = p.smoothing ? 0.f : warp_max(m);
+            A3_STAMP(19)
+            float sum = 0.f;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int t = lane + 32 * i;
+                e[i] = t < len ? (p.smoothing ? sigmoidf_(e[i]) : __expf(e[i] - m)) : 0.f;
+                sum += e[i];
+            }
+            A3_STAMP(20)
+            sum = warp_sum(sum);
+            A3_STAMP(21)
+            const float inv = __fdividef(1.0f, sum);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int t = lane + 32 * i;
+                if (t < len) SMF(SO_ES)[t] = e[i] * inv;
+            }
+            A3_STAMP(22)
+        } else {
+            float m = -INFINITY;
+            if (!p.smoothing) {
+                for (int t = lane; t < len; t += 32) m = fmaxf(m, SMF(SO_ES)[t]);
+                m = warp_max(m);
+            }
+            float sum = 0.f;
+            for (int t = lane; t < len; t += 32) {
+                const float v = p.smoothing ? sigmoidf_(SMF(SO_ES)[t]) : __expf(SMF(SO_ES)[t] - m);
+                SMF(SO_ES)[t] = v;
+                sum += v;
+            }
+            sum = warp_sum(sum);
+            const float inv = 1.0f / sum;
+            for (int t = lane; t < len; t += 32) SMF(SO_ES)[t] *= inv;
         }
-        float sum = 0.f;
-        for (int t = lane; t < len; t += 32) {
-            const float v = p.smoothing ? sigmoidf_(SMF(SO_ES)[t]) : __expf(SMF(SO_ES)[t] - m);
-            SMF(SO_ES)[t] = v;
-            sum += v;
-        }
-        sum = warp_sum(sum);
-        const float inv = 1.0f / sum;
-        for (int t = lane; t < len; t += 32) SMF(SO_ES)[t] *= inv;
     }
     __syncthreads();
     A3_STAMP(10)
@@ -250,7 +292,7 @@ __device__ __forceinline__ void att3_step(const Dec3Params& p, float (&preR)[8][
         float c[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
         if (tg < TG) {
             const uint4* vp = reinterpret_cast<const uint4*>(p.values + (size_t)b * p.T * MEM) + d8;
-#pragma unroll 8
+#pragma unroll 4
             for (int t = tg; t < len; t += TG) {
                 const uint4 v = ldg_stream_v4(vp + (size_t)t * D8);
                 const float a = SMF(SO_ES)[t];

@@ -4,10 +4,10 @@
 namespace {
 
 #define D3_STAMP(i)                                                     \
-    if (timing) {                                                       \
+    if (timing) { /* whole warp 0, uniform: a divergent stamp would push the following collectives onto their slow path */ \
         long long now_;                                                 \
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now_));        \
-        tacc[i] += now_ - tprev;                                        \
+        if (lane == 0) tacc[i] += now_ - tprev;                         \
         tprev = now_;                                                   \
     }
 
@@ -43,7 +43,7 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
             SMF(SO_BC)[tid] = p.bconst[tid];
         }
         for (int i = tid; i < T_MAX3 + 48; i += NT) SMF(SO_CPAD)[i] = 0.f;
-        if (tid < 8 + 48) SMU(SO_FLAG)[tid] = 0;
+        if (tid < 16 + 48) SMU(SO_FLAG)[tid] = 0;
         rearm(SMU(SO_X), KS_X + 6 * KS_H + KS_CTX, R, tid);   // all activation buffers are contiguous
         for (int i = tid; i < CS * ATT; i += NT) SMU(SO_QRECV)[i] = SENT;
     }
@@ -107,17 +107,28 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
 
     const int mt = warp & 3, kg = warp >> 2;   // 4-m-tile phases: (gate tile, k group)
     const uint4* stream = p.stream_blobs + (size_t)rank * (320 * 32);
-    const uint4* sW1C = stream + (size_t)(mt * KS_CTX) * 32;
-    const uint4* sW1H = stream + (size_t)(192 + mt * KS_H) * 32;
-    const uint4* sW2Z = stream + (size_t)(256 + mt * KS_H) * 32;
+    // streamed sets of 64 tiles [4 mt][16 ks]: LSTM-1 prenet rows, LSTM-2 h1 rows, LSTM-1 h1z rows, LSTM-2 h2z rows, LSTM-1 context k-steps 32..47
+    const uint4* sW1P = stream + (size_t)(0 + mt * KS_H) * 32;
+    const uint4* sW2H = stream + (size_t)(64 + mt * KS_H) * 32;
+    const uint4* sW1H = stream + (size_t)(128 + mt * KS_H) * 32;
+    const uint4* sW2Z = stream + (size_t)(192 + mt * KS_H) * 32;
+    const uint4* sW1C = stream + (size_t)(256 + mt * KS_H) * 32;
+    const uint32_t* rW1C = SMU(SO_W1C) + mt * W1C_RES * TILE_W;
     const float* bias = SMF(SO_BIAS);   // b1[64] b2[64] bp1[16] bp2[16] bo[16]
     float* red = SMF(SO_RED);
 
     // contributions of step t0-1's context / zoned states to the gates of step t0
-    float acc1[2][4] = {}, acc2[2][4] = {}, accO[2][4] = {};
-    gemm_stream<2, 4>(acc1, sW1C, 32, SMU(SO_CTX), KS_CTX, kg, 4, lane, g);
-    gemm_stream<2, 4>(acc1, sW1H, 32, SMU(SO_H1Z), KS_H, kg, 4, lane, g);
-    gemm_stream<2, 4>(acc2, sW2Z, 32, SMU(SO_H2Z), KS_H, kg, 4, lane, g);
+    float acc1[2][4] = {}, acc2[2][4] = {};
+    {
+        uint4 t0[4], t1[4], t2[4];
+        prefetch4(t0, sW1C, kg, lane);
+        prefetch4(t1, sW1H, kg, lane);
+        prefetch4(t2, sW2Z, kg, lane);
+        gemm_smem4(acc1, rW1C, SMU(SO_CTX), W1C_RES, kg, 4, lane, g);
+        gemm_regs(acc1, t0, SMU(SO_CTX) + W1C_RES * TILE_W, kg, lane, g);
+        gemm_regs(acc1, t1, SMU(SO_H1Z), kg, lane, g);
+        gemm_regs(acc2, t2, SMU(SO_H2Z), kg, lane, g);
+    }
     __syncthreads();
     rearm(SMU(SO_H1Z), KS_H, R, tid);
     rearm(SMU(SO_H2Z), KS_H, R, tid);
@@ -126,12 +137,8 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
 
     long long* tacc = reinterpret_cast<long long*>(smem3 + SO_TACC);
     long long tprev = 0;
-    const bool timing = p.timing != nullptr && tid == 0;
+    const bool timing = p.timing != nullptr && warp == 0;
     if (timing) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tprev));
-    // stop flags of step s-2, loaded one step before they are consumed (free running; thread 0)
-    uint32_t fl[TACO_DEC3_MAX_CLUSTERS];
-#pragma unroll
-    for (int i = 0; i < TACO_DEC3_MAX_CLUSTERS; ++i) fl[i] = 1u;
     int s_done = 0;
     bool stopped = false;
 
@@ -140,25 +147,22 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
         // ---- batch-global stop (Helpers.py:51-52), evaluated three steps late; speculative steps are discarded ----
         if (free_run && tid == 0) {
             if (s >= 3) {
+                cp_async_wait_all();   // words of step s-3, requested one step ago
                 bool any = false, all = true;
-#pragma unroll
-                for (int i = 0; i < TACO_DEC3_MAX_CLUSTERS; ++i) {
-                    if (i < p.NCL) {
-                        uint32_t v = fl[i];
-                        int spins = 0;
-                        while (v == 0u && !spin_check3(g, spins)) v = ldg_relaxed(reinterpret_cast<const uint32_t*>(p.flags) + (size_t)(s - 3) * p.NCL + i);
-                        any = any || (v & 2u);
-                        all = all && (v & 2u);
-                    }
+                for (int i = 0; i < p.NCL; ++i) {
+                    uint32_t v = *reinterpret_cast<volatile uint32_t*>(SMU(SO_FLAG) + 8 + i);
+                    int spins = 0;
+                    while (v == 0u && !spin_check3(g, spins)) v = ldg_relaxed(reinterpret_cast<const uint32_t*>(p.flags) + (size_t)(s - 3) * p.NCL + i);
+                    any = any || (v & 2u);
+                    all = all && (v & 2u);
                 }
                 SMU(SO_FLAG)[0] = ((p.stop_at_any ? any : all) || g.dead) ? 2u : 1u;
             }
-            if (s >= 2) {
-#pragma unroll
-                for (int i = 0; i < TACO_DEC3_MAX_CLUSTERS; ++i)
-                    if (i < p.NCL) fl[i] = ldg_relaxed(reinterpret_cast<const uint32_t*>(p.flags) + (size_t)(s - 2) * p.NCL + i);
-            }
+            if (s >= 2)
+                for (int i = 0; i < p.NCL; ++i) cp_async_4(SMU(SO_FLAG) + 8 + i, p.flags + (size_t)(s - 2) * p.NCL + i);
         }
+        uint4 aW1P[4];
+        prefetch4(aW1P, sW1P, kg, lane);   // used two exchanges later (L1)
         // prenet dropout bits of this step (always on, Decoder.py:350-351): computed while the feedback frame is in flight
         const bool keep0 = evalid && keep_bit3(p, step, eb, 0, 16 * rank + eu);
         const bool keep1 = evalid && keep_bit3(p, step, eb, 1, 16 * rank + eu);
@@ -167,7 +171,7 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
             float acc[2][4] = {};
             if (warp < KS_X) {
                 if (free_run) {
-                    gemm_smem<2>(acc, SMU(SO_WP1), TILE_W, SMU(SO_X), KS_X, warp, 16, lane, g);
+                    gemm_smem4(acc, SMU(SO_WP1), SMU(SO_X), KS_X, warp, 16, lane, g);
                 } else {
                     // TacoTrainingHelper.next_inputs (Helpers.py:121-124, ratio 1.0): x(step) = targets[:, r*step - 1]
                     const int fidx = step * 2 - 1;
@@ -207,8 +211,7 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
             if (free_run) rearm(SMU(SO_X), KS_X, R, tid);
             if (s > 0) {   // buffers whose last readers ran before this phase's barrier
                 rearm(SMU(SO_CTX), KS_CTX, R, tid);
-                rearm(SMU(SO_H2R), KS_H, R, tid);
-                rearm(SMU(SO_H2Z), KS_H, R, tid);
+                rearm(SMU(SO_H1Z), 3 * KS_H, R, tid);   // H1Z, H2R, H2Z are contiguous
             }
             __syncthreads();
             multicast_block(SMU(SO_STG_R), SMU(SO_P1), rank, R, tid);
@@ -217,7 +220,7 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
         // ================= P2: prenet dense_2 =================
         {
             float acc[2][4] = {};
-            gemm_smem<2>(acc, SMU(SO_WP2), TILE_W, SMU(SO_P1), KS_H, warp, 16, lane, g);
+            gemm_smem4(acc, SMU(SO_WP2), SMU(SO_P1), KS_H, warp, 16, lane, g);
             store_red3(red, acc, warp, lane, 2);
             D3_STAMP(2)
             __syncthreads();
@@ -237,7 +240,9 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
         }
         // ================= L1: decoder LSTM layer 1 (Decoder.py:256; Encoder.py:118-142) =================
         {
-            gemm_smem<2>(acc1, SMU(SO_W1P) + mt * KS_H * TILE_W, TILE_W, SMU(SO_P2), KS_H, kg, 4, lane, g);
+            gemm_regs(acc1, aW1P, SMU(SO_P2), kg, lane, g);
+            uint4 aW2H[4];
+            prefetch4(aW2H, sW2H, kg, lane);   // in flight during the LSTM-1 epilogue and the h1 exchange
             store_red3(red, acc1, kg * 4 + mt, lane, 2);
 #pragma unroll
             for (int j = 0; j < 2; ++j) acc1[j][0] = acc1[j][1] = acc1[j][2] = acc1[j][3] = 0.f;
@@ -272,12 +277,12 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
             multicast_block(SMU(SO_STG_R), SMU(SO_H1R), rank, R, tid);
             multicast_block(SMU(SO_STG_Z), SMU(SO_H1Z), rank, R, tid);
             D3_STAMP(5)
-        }
         // ================= L2: decoder LSTM layer 2 =================
+            gemm_regs(acc2, aW2H, SMU(SO_H1R), kg, lane, g);
+        }
+        uint4 aW1H[4];
+        prefetch4(aW1H, sW1H, kg, lane);   // in flight during the LSTM-2 epilogue and the query exchange
         {
-            gemm_smem<2>(acc2, SMU(SO_W2H) + mt * KS_H * TILE_W, TILE_W, SMU(SO_H1R), KS_H, kg, 4, lane, g);
-            // zoned h1 of this step -> gates of the next step (weights streamed from L2)
-            gemm_stream<2, 4>(acc1, sW1H, 32, SMU(SO_H1Z), KS_H, kg, 4, lane, g);
             store_red3(red, acc2, kg * 4 + mt, lane, 2);
 #pragma unroll
             for (int j = 0; j < 2; ++j) acc2[j][0] = acc2[j][1] = acc2[j][2] = acc2[j][3] = 0.f;
@@ -307,7 +312,6 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
                 }
             }
             rearm(SMU(SO_H1R), KS_H, R, tid);
-            rearm(SMU(SO_H1Z), KS_H, R, tid);
             __syncthreads();
             // K-slice of the query projection: qpart[row][d] = sum_{u in my 16 units} h2raw[row][u] Wq[u][d]
             if (warp < 8) {
@@ -338,17 +342,21 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
             D3_STAMP(7)
         }
         // ---- h2-dependent halves of the next LSTM-2 gates and of the projection (their operands arrive with the query partials) ----
-        gemm_stream<2, 4>(acc2, sW2Z, 32, SMU(SO_H2Z), KS_H, kg, 4, lane, g);
-#pragma unroll
-        for (int j = 0; j < 2; ++j) accO[j][0] = accO[j][1] = accO[j][2] = accO[j][3] = 0.f;
-        if (rank <= 10) gemm_smem<2>(accO, SMU(SO_WO), TILE_W, SMU(SO_H2R), KS_H, warp, 16, lane, g);
+        uint4 aW2Z[4];
+        prefetch4(aW2Z, sW2Z, kg, lane);
+        gemm_regs(acc1, aW1H, SMU(SO_H1Z), kg, lane, g);   // zoned h1 of this step -> LSTM-1 gates of the next step
+        gemm_regs(acc2, aW2Z, SMU(SO_H2Z), kg, lane, g);   // zoned h2 of this step -> LSTM-2 gates of the next step
         D3_STAMP(9)
         // ================= ATT: location-sensitive attention of cluster row `rank` =================
         if (att) att3_step(p, preR, pre_scr, ab, alen, rank, s, tid, warp, lane, g, tacc, tprev, timing);
+        uint4 aW1C[4];
+        prefetch4(aW1C, sW1C, kg, lane);   // in flight while the projection waits for the slowest context row
         D3_STAMP(10)
         // ================= PROJ: frame + stop projection, outputs, feedback (Decoder.py:273-279; Helpers.py:36-59) =================
         if (rank <= 10) {
-            gemm_smem<2>(accO, SMU(SO_WO) + KS_H * TILE_W, TILE_W, SMU(SO_CTX), KS_CTX, warp, 16, lane, g);
+            float accO[2][4] = {};
+            gemm_smem4(accO, SMU(SO_WO), SMU(SO_H2R), KS_H, warp, 16, lane, g);
+            gemm_smem4(accO, SMU(SO_WO) + KS_H * TILE_W, SMU(SO_CTX), KS_CTX, warp, 16, lane, g);
             __syncthreads();   // attention scratch (aliases red) is no longer read
             store_red3(red, accO, warp, lane, 2);
             D3_STAMP(11)
@@ -393,7 +401,8 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
         }
         D3_STAMP(12)
         // ---- shadow of the feedback exchange: context-dependent part of the next LSTM-1 gates ----
-        gemm_stream<2, 4>(acc1, sW1C, 32, SMU(SO_CTX), KS_CTX, kg, 4, lane, g);
+        gemm_smem4(acc1, rW1C, SMU(SO_CTX), W1C_RES, kg, 4, lane, g);
+        gemm_regs(acc1, aW1C, SMU(SO_CTX) + W1C_RES * TILE_W, kg, lane, g);
         D3_STAMP(13)
         if (att) att3_next(p, preR, pre_scr, ab, alen, tid, warp, lane);
         D3_STAMP(14)
@@ -401,7 +410,7 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
         s_done = s + 1;
     }
 
-    if (timing)
+    if (timing && lane == 0)
         for (int i = 0; i < 24; ++i) p.timing[(size_t)blockIdx.x * 24 + i] = tacc[i];
     // ---- write back the recurrent state + step count ----
     if (evalid) {
