@@ -707,6 +707,7 @@ int decode_v3(TacoHandle* h, int mode, const float* memory, const int32_t* lens,
     WS(pre, float, "dec3_pre", (size_t)B * T * 128)
     p.pre_scratch = pre;
     p.cont = reset_state ? 0 : 1;
+    if (getenv("TACO_DEC3_DBG")) p.dbg = atoi(getenv("TACO_DEC3_DBG"));
     p.t0 = h->dec_t;
     p.targets = mel_targets; p.F_tgt = F_tgt;
     p.masks = prenet_masks; p.seed = philox_seed;

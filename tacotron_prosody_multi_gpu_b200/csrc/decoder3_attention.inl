@@ -292,7 +292,7 @@ __device__ __forceinline__ void att3_step(const Dec3Params& p, float (&preR)[8][
         float c[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
         if (tg < TG) {
             const uint4* vp = reinterpret_cast<const uint4*>(p.values + (size_t)b * p.T * MEM) + d8;
-#pragma unroll 4
+#pragma unroll 8
             for (int t = tg; t < len; t += TG) {
                 const uint4 v = ldg_stream_v4(vp + (size_t)t * D8);
                 const float a = SMF(SO_ES)[t];
@@ -326,7 +326,8 @@ __device__ __forceinline__ void att3_step(const Dec3Params& p, float (&preR)[8][
         A3_STAMP(17)
         // multicast this row's 48 x 32-byte chunks into every CTA's context buffer
         for (int i = tid; i < CS * KS_CTX * 2; i += NT) {
-            const int dst = i / (KS_CTX * 2), v = i - dst * (KS_CTX * 2);
+            const int slot = i / (KS_CTX * 2), v = i - slot * (KS_CTX * 2);
+            const int dst = slot < 5 ? slot + 5 : (slot < 10 ? slot - 5 : slot);   // feedback-frame producers (ranks 5..9) first
             const int ks = v >> 1, half = v & 1;
             const uint4 val = *reinterpret_cast<const uint4*>(SMU(SO_STG_C) + ks * 8 + half * 4);
             st_remote_v4(mapa_rank(smem_addr(SMU(SO_CTX) + ks * TILE_W + ((rank >> 3) << 6) + ((rank & 7) << 3) + half * 4), dst), val);

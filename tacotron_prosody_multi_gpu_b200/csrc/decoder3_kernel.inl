@@ -3,6 +3,8 @@
 
 namespace {
 
+constexpr int STOP_LAG = 8;
+
 #define D3_STAMP(i)                                                     \
     if (timing) { /* whole warp 0, uniform: a divergent stamp would push the following collectives onto their slow path */ \
         long long now_;                                                 \
@@ -144,22 +146,20 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
 
     for (int s = 0; s < p.S_max; ++s) {
         const int step = p.t0 + s;
-        // ---- batch-global stop (Helpers.py:51-52), evaluated three steps late; speculative steps are discarded ----
-        if (free_run && tid == 0) {
-            if (s >= 3) {
-                cp_async_wait_all();   // words of step s-3, requested one step ago
-                bool any = false, all = true;
-                for (int i = 0; i < p.NCL; ++i) {
-                    uint32_t v = *reinterpret_cast<volatile uint32_t*>(SMU(SO_FLAG) + 8 + i);
-                    int spins = 0;
-                    while (v == 0u && !spin_check3(g, spins)) v = ldg_relaxed(reinterpret_cast<const uint32_t*>(p.flags) + (size_t)(s - 3) * p.NCL + i);
-                    any = any || (v & 2u);
-                    all = all && (v & 2u);
-                }
-                SMU(SO_FLAG)[0] = ((p.stop_at_any ? any : all) || g.dead) ? 2u : 1u;
+        // ---- batch-global stop (Helpers.py:51-52), evaluated STOP_LAG steps late so that clusters never wait for each other; speculative steps are discarded ----
+        // Warp 15 is idle during P1 (warps 0..4 contract the 5 k-steps of the frame): lane i handles the word of cluster i.
+        if (free_run && warp == 15 && !(p.dbg & 1)) {
+            if (s >= STOP_LAG) {
+                cp_async_wait_all();   // words of step s - STOP_LAG, requested one step ago
+                uint32_t v = lane < p.NCL ? *reinterpret_cast<volatile uint32_t*>(SMU(SO_FLAG) + 8 + lane) : 1u;
+                int spins = 0;
+                while (v == 0u && !spin_check3(g, spins)) v = ldg_relaxed(reinterpret_cast<const uint32_t*>(p.flags) + (size_t)(s - STOP_LAG) * p.NCL + lane);
+                const unsigned stopm = __ballot_sync(0xffffffffu, (v & 2u) != 0u);
+                const unsigned deadm = __ballot_sync(0xffffffffu, g.dead);
+                const unsigned full = (1u << p.NCL) - 1u;
+                if (lane == 0) SMU(SO_FLAG)[0] = ((p.stop_at_any ? stopm != 0u : (stopm & full) == full) || deadm != 0u) ? 2u : 1u;
             }
-            if (s >= 2)
-                for (int i = 0; i < p.NCL; ++i) cp_async_4(SMU(SO_FLAG) + 8 + i, p.flags + (size_t)(s - 2) * p.NCL + i);
+            if (s >= STOP_LAG - 1 && lane < p.NCL) cp_async_4(SMU(SO_FLAG) + 8 + lane, p.flags + (size_t)(s - (STOP_LAG - 1)) * p.NCL + lane);
         }
         uint4 aW1P[4];
         prefetch4(aW1P, sW1P, kg, lane);   // used two exchanges later (L1)
@@ -195,7 +195,7 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
             }
             D3_STAMP(0)
             __syncthreads();
-            if (free_run && s >= 3 && SMU(SO_FLAG)[0] == 2u) {
+            if (free_run && s >= STOP_LAG && SMU(SO_FLAG)[0] == 2u) {
                 stopped = true;
                 break;   // CTA- and cluster-uniform: every CTA reads the same flag words
             }
@@ -348,7 +348,13 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
         gemm_regs(acc2, aW2Z, SMU(SO_H2Z), kg, lane, g);   // zoned h2 of this step -> LSTM-2 gates of the next step
         D3_STAMP(9)
         // ================= ATT: location-sensitive attention of cluster row `rank` =================
-        if (att) att3_step(p, preR, pre_scr, ab, alen, rank, s, tid, warp, lane, g, tacc, tprev, timing);
+        if (att) {
+            att3_step(p, preR, pre_scr, ab, alen, rank, s, tid, warp, lane, g, tacc, tprev, timing);
+            // next step's location term: off the critical path of every CTA but the one that owns the slowest row
+            __syncthreads();
+            att3_next(p, preR, pre_scr, ab, alen, tid, warp, lane);
+            D3_STAMP(14)
+        }
         uint4 aW1C[4];
         prefetch4(aW1C, sW1C, kg, lane);   // in flight while the projection waits for the slowest context row
         D3_STAMP(10)
@@ -404,8 +410,6 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
         gemm_smem4(acc1, rW1C, SMU(SO_CTX), W1C_RES, kg, 4, lane, g);
         gemm_regs(acc1, aW1C, SMU(SO_CTX) + W1C_RES * TILE_W, kg, lane, g);
         D3_STAMP(13)
-        if (att) att3_next(p, preR, pre_scr, ab, alen, tid, warp, lane);
-        D3_STAMP(14)
         __syncthreads();   // red / staging readers of this step are done before the next step's writers
         s_done = s + 1;
     }
@@ -434,9 +438,9 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
     if (blockIdx.x == 0 && tid == 0) {
         int steps = s_done;
         if (free_run) {
-            // the stop bits of the last (up to) three executed steps have not been consumed yet
-            const int first = stopped ? s_done - 3 : max(0, s_done - 3);
-            steps = stopped ? s_done - 3 + 1 : s_done;
+            // the stop bits of the last (up to) STOP_LAG executed steps have not been consumed yet
+            const int first = max(0, s_done - STOP_LAG);
+            steps = stopped ? s_done - STOP_LAG + 1 : s_done;
             if (!stopped) {
                 for (int st = first; st < s_done; ++st) {
                     bool any = false, all = true;

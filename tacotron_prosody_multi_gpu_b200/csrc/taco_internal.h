@@ -100,6 +100,7 @@ struct Dec3Params {
     int S_max, S_cap, t0, mode;
     int stop_at_any, cumulative, smoothing, stop_sigmoid;
     int pre_reg;            // T <= 128: location pre-activations live in registers (else in pre_scratch)
+    int dbg;                // experiment bitmask (TACO_DEC3_DBG): 1 = never consume the stop flags
     int cont;               // continuation launch (reset_state == 0): pre-activations are loaded from pre_scratch
     float zoneout, keep_scale;
     const uint32_t* res_blobs;   // [16 ranks][TACO_DEC3_RES_WORDS] A-fragment tiles resident in shared memory + fp32 biases
