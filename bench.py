@@ -286,15 +286,15 @@ def run_b200(args):
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_total / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "bf16" if args.precision == "bf16" else "f32", "data": "synthetic",
-        "precision": ("bf16 operands + fp32 accumulation (tcgen05) in the postnet contractions; decoder, attention, "
-                      "softmax, recurrent state and all outputs fp32") if args.precision == "bf16" else "fp32 everywhere",
+        "precision": ("bf16 operands + fp32 accumulation in every contraction (tcgen05 in the postnet, mma.sync in the decoder step); "
+                      "attention values streamed as bf16; recurrent state, softmax, location term and all outputs fp32") if args.precision == "bf16" else "fp32 everywhere",
         "config": {"workload": "C2 free-running inference, B=64/GPU, sentences.txt token lengths x4 (T=111), "
                                "S=%d decoder steps (max_iters, stop bias -10), r=2, random-init seed 45454" % S,
                    "batch_per_gpu": B, "T": T, "decoder_steps": S, "frames_counted": "all B*2S frames (no stop fires)",
                    "l2": "512 MB flush write between timed steps", "parallelism": "independent batches per GPU, no collective"},
         "decoder_step_us": 1e6 * dec_s / S,
         "stages_ms": stage,
-        "roofline": {"bound": "hbm", "kernel": "decoder_persistent_kernel", "achieved": achieved, "peak": peak,
+        "roofline": {"bound": "hbm", "kernel": "decoder3_kernel (cluster persistent decoder)" if args.precision == "bf16" else "decoder_persistent_kernel", "achieved": achieved, "peak": peak,
                      "peak_source": peak_src + " (burst copy bandwidth)", "unit": "GB/s", "frac": achieved / peak,
                      "algorithmic_bytes_per_launch": step_bytes * S, "launch_ms": dec_s * 1e3, "traffic": None},
         "e2e": {"value": world * frames_per_step * args.steps / (e2e_ms * 1e-3), "unit": UNIT,

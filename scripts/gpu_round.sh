@@ -2,16 +2,16 @@
 # One GPU visit: parity tests, bench (both arms), ncu launch list, ncu full capture of the decoder kernel.
 # Usage (under gpurun): bash scripts/gpu_round.sh <tag> [kernel-regex]
 TAG=${1:-rXX}
-KREGEX=${2:-decoder2_kernel}
+KREGEX=${2:-decoder3_kernel}
 O=gpurun_out
 mkdir -p $O
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm --format=csv > $O/${TAG}_smi.txt 2>&1
 nproc >> $O/${TAG}_smi.txt
-timeout 900 python -m pytest tests -m gpu -x -q > $O/${TAG}_pytest.log 2>&1; echo "pytest rc=$?" | tee -a $O/${TAG}_pytest.log
+timeout 900 python -m pytest tests -m gpu -q > $O/${TAG}_pytest.log 2>&1; echo "pytest rc=$?" | tee -a $O/${TAG}_pytest.log
 timeout 120 python __graft_entry__.py smoke > $O/${TAG}_smoke.log 2>&1; echo "smoke rc=$?" | tee -a $O/${TAG}_smoke.log
 timeout 600 python bench.py --steps 5 --warmup 3 > $O/${TAG}_bench.json 2> $O/${TAG}_bench.err; echo "bench rc=$?"
 tail -c 3000 $O/${TAG}_bench.json
-timeout 200 python scripts/dec2_timing.py 64 200 > $O/${TAG}_dec2_timing.txt 2>&1; cat $O/${TAG}_dec2_timing.txt
+timeout 200 python scripts/dec3_timing.py 64 200 > $O/${TAG}_dec3_timing.txt 2>&1; cat $O/${TAG}_dec3_timing.txt | cut -c1-400
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/${TAG}_launches.csv \
     python bench.py --steps 2 --warmup 3 --no-cpu-baseline > $O/${TAG}_ncu_launch.log 2>&1; echo "ncu launches rc=$?"
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:${KREGEX} -s 1 -c 1 -o $O/${TAG}_decoder_full -f \

@@ -96,11 +96,27 @@ def test_synthesizer_output_contract(rt, tmp_path):
     w2 = weights.scale_stop_projection(weights.init_weights(hp, perturb=0.05), 8.0, 0.0)
     ck = str(tmp_path / "taco.npz")
     weights.save(ck, w2)
-    synth = Synthesizer().load(ck, hp2, GTA=False)
     seqs = [synthetic.token_batch(hp, [n], seed=n)[0][0] for n in (9, 13, 7)]   # 3 texts -> padded to 4 (2 towers x 2)
+    gw = synthetic.gst_random_weights(hp)
+    from tacotron_prosody_multi_gpu_b200.Utils.Tacotron_feeder import _prepare_inputs as _pi
+    orc0 = TacotronOracle(hp, w2)
+    refs = None
+    for seed in range(20):   # stop-parity config: every rounded stop decision of both towers has a margin
+        cand = []
+        for g in range(2):
+            tower = (seqs + [seqs[-1]])[2 * g: 2 * g + 2]
+            ids, _ = _pi(tower)
+            cand.append(orc0.forward(ids.astype(np.int32), np.asarray([len(x) for x in tower], np.int32), gst_weights=gw, max_iters=30,
+                                     philox_seed=seed))
+        margin = min(float(np.abs(c["stop"].numpy() - 0.5).min()) for c in cand)
+        if margin > 1.5e-3 and all(c["steps"] < 30 for c in cand):   # fp32 kernels reproduce the stop tokens to ~1e-5
+            refs = cand
+            hp2.tacotron_random_seed = seed
+            break
+    assert refs is not None, "no dropout seed with a stop margin found"
+    synth = Synthesizer().load(ck, hp2, GTA=False)
     out_dir = tmp_path / "inference"
     out_dir.mkdir()
-    gw = synthetic.gst_random_weights(hp)
     paths, speakers = synth.synthesize(seqs, ["a", "b", "c"], str(out_dir), None, None, gst_weights=gw, max_iters=30)
     assert len(paths) == 4 and speakers == ['<no_g>'] * 4 and os.path.basename(paths[0]) == "speech-mel-a.npy"
     orc = TacotronOracle(hp, w2)
@@ -108,8 +124,7 @@ def test_synthesizer_output_contract(rt, tmp_path):
     for g in range(2):
         tower = (seqs + [seqs[-1]])[2 * g: 2 * g + 2]
         ids, _ = _prepare_inputs(tower)
-        ref = orc.forward(ids.astype(np.int32), np.asarray([len(s) for s in tower], np.int32), gst_weights=gw, max_iters=30,
-                          philox_seed=hp.tacotron_random_seed)
+        ref = refs[g]
         keep = _get_output_lengths(ref["stop"].numpy())
         for j in range(2):
             mel = np.load(paths[2 * g + j])
