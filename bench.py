@@ -50,6 +50,18 @@ def load_peaks():
     return 6650.0, "fallback"
 
 
+def load_traffic(kernel):
+    """DRAM bytes per launch of the dominant kernel from the committed ncu --set full capture."""
+    p = os.path.join(ROOT, "profiles", "decoder_traffic.json")
+    try:
+        d = json.load(open(p))
+        if d.get("kernel") and d["kernel"] in kernel:
+            return int(d["dram_bytes_per_launch"])
+    except (OSError, ValueError, KeyError):
+        pass
+    return None
+
+
 def workload(hp, rank=0, batch=B_PER_GPU):
     from tacotron_prosody_multi_gpu_b200 import synthetic
     lengths = synthetic.cycle_lengths(batch)
@@ -58,12 +70,13 @@ def workload(hp, rank=0, batch=B_PER_GPU):
     return ids, lens, gw
 
 
-def decoder_step_bytes(lens, T, B):
+def decoder_step_bytes(lens, T, B, key_bytes=4, value_bytes=4):
     """Algorithmic bytes of ONE decoder step (SURVEY 8d / DESIGN.md): keys+values of the valid
-    positions read once (fp32), cumulative alignments read+write and alignment history write
+    positions read once AT THEIR STORED ELEMENT SIZE (fp32 keys; values fp32, or bf16 in the
+    bf16 precision mode), cumulative alignments read+write and alignment history write
     (3 x 4 bytes per padded position), frame + stop outputs."""
     valid = int(np.sum(lens))
-    return valid * (128 + 768) * 4 + 12 * B * T + B * (160 + 2) * 4
+    return valid * (128 * key_bytes + 768 * value_bytes) + 12 * B * T + B * (160 + 2) * 4
 
 
 class ClockSampler(object):
@@ -278,7 +291,7 @@ def run_b200(args):
         return 0
 
     peak, peak_src = load_peaks()
-    step_bytes = decoder_step_bytes(lens, T, B)
+    step_bytes = decoder_step_bytes(lens, T, B, 4, 2 if args.precision == "bf16" else 4)
     dec_s = float(np.mean(dec_ms)) * 1e-3
     achieved = step_bytes * S / dec_s / 1e9
     line = {
@@ -296,7 +309,8 @@ def run_b200(args):
         "stages_ms": stage,
         "roofline": {"bound": "hbm", "kernel": "decoder3_kernel (cluster persistent decoder)" if args.precision == "bf16" else "decoder_persistent_kernel", "achieved": achieved, "peak": peak,
                      "peak_source": peak_src + " (burst copy bandwidth)", "unit": "GB/s", "frac": achieved / peak,
-                     "algorithmic_bytes_per_launch": step_bytes * S, "launch_ms": dec_s * 1e3, "traffic": None},
+                     "algorithmic_bytes_per_launch": step_bytes * S, "launch_ms": dec_s * 1e3,
+                     "traffic": load_traffic("decoder3_kernel" if args.precision == "bf16" else "decoder_persistent_kernel")},
         "e2e": {"value": world * frames_per_step * args.steps / (e2e_ms * 1e-3), "unit": UNIT,
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms / args.steps},
         "gpu_launches": int(launches),

@@ -126,6 +126,12 @@ def test_synthesizer_output_contract(rt, tmp_path):
         ids, _ = _prepare_inputs(tower)
         ref = refs[g]
         keep = _get_output_lengths(ref["stop"].numpy())
+        got = np.stack(synth.last_stop_tokens[2 * g: 2 * g + 2])
+        print("tower %d: seed %d steps oracle=%d gpu F=%d  max|stop diff| over common frames = %.3e" % (
+            g, hp2.tacotron_random_seed, ref["steps"], got.shape[1],
+            np.abs(got[:, :min(got.shape[1], 2 * ref["steps"])] - ref["stop"].numpy()[:, :min(got.shape[1], 2 * ref["steps"])]).max()))
+        print(" oracle stop", np.round(ref["stop"].numpy(), 4).tolist())
+        print(" gpu    stop", np.round(got, 4).tolist())
         for j in range(2):
             mel = np.load(paths[2 * g + j])
             assert mel.dtype == np.float32 and mel.shape == (keep[j], 80)          # bit-exact output lengths

@@ -316,3 +316,70 @@ def test_decoder2_free_running_stop_step_bit_exact(ctx2):
     np.testing.assert_allclose(_t(out["mel_outputs"]), ref["mel_outputs"].numpy(), atol=5e-2)
     assert output_lengths(_t(out["stop"])) == output_lengths(ref["stop"].numpy())
     eng.close()
+
+
+# ------------------------------------------------------------------ full-size configurations of BASELINE.json
+def test_c2_batch64_T111_teacher_forced_parity(ctx2):
+    """C2 shape (B=64, the sentences.txt lengths x4, T=111) on the cluster decoder, teacher-forced so the
+    oracle finishes in seconds; covers the 7/8-cluster row split and the in-register `pre` path (T <= 128)."""
+    hp, w, eng, mir, orc = ctx2
+    lengths = synthetic.cycle_lengths(64)
+    ids, lens = synthetic.token_batch(hp, lengths)
+    B, T = ids.shape
+    assert (B, T) == (64, 111)
+    rng = np.random.default_rng(64)
+    memory = (rng.standard_normal((B, T, 768)) * 0.5).astype(np.float32)
+    mel, _, _ = synthetic.mel_targets(hp, lens, frames_per_token=1, max_frames=32)
+    S = mel.shape[1] // 2
+    with torch.no_grad():
+        ref = mir.decode(torch.from_numpy(memory), lens, mel_targets=mel, philox_seed=21)
+    d = eng.decode(torch.from_numpy(memory).cuda(), torch.from_numpy(lens), mel_targets=torch.from_numpy(mel), philox_seed=21)
+    assert d["steps"] == ref["steps"] == S
+    al = _t(eng.alignments(d["align_hist"], S))
+    np.testing.assert_allclose(_t(d["frames"]), ref["frames_raw"].numpy(), atol=ATOL_D2_FRAMES)
+    np.testing.assert_allclose(al, ref["alignments"].numpy(), atol=ATOL_D2_ALIGN)
+    for b, n in enumerate(lens):
+        assert al[b, n:].max(initial=0.0) == 0.0
+    np.testing.assert_allclose(al.sum(1), 1.0, atol=1e-5)
+
+
+def test_c5_long_form_reference_encoder(ctx2):
+    """C5: B=16, T=300 tokens, prosody reference encoder on a [16, 2000, 80] reference mel, S=1000 decoder
+    steps.  (i) the first 48 steps teacher-forced against the bf16-mirroring oracle (T > 128: the `pre`
+    scratch path of the cluster decoder); (ii) the full 1000 free-running steps through size-independent
+    properties: S == max_iters, alignment rows are distributions over the valid positions and exactly 0
+    beyond the length, outputs finite and inside the clip range, frames(t) of a second identical launch
+    are bit-identical (Philox dropout is keyed by (seed, step, row), not by launch)."""
+    hp, w, eng, mir, orc = ctx2
+    lengths = [300, 287, 300, 251, 199, 300, 123, 64, 300, 18, 277, 300, 150, 290, 300, 42]
+    ids, lens = synthetic.token_batch(hp, lengths)
+    B, T = ids.shape
+    rm = synthetic.reference_mel(hp, B, 2000)
+    with torch.no_grad():
+        enc_ref = mir.encode(ids, lens, reference_mel=rm)
+    mem = eng.encode(torch.from_numpy(ids), torch.from_numpy(lens), reference_mel=torch.from_numpy(rm))
+    np.testing.assert_allclose(_t(mem)[:, :, 512:], enc_ref.numpy()[:, :, 512:], atol=2e-3)   # style embedding
+    np.testing.assert_allclose(_t(mem), enc_ref.numpy(), atol=ATOL_TC_FP32)
+    # (i) teacher-forced prefix from the ORACLE's memory so the decoder is compared on identical inputs
+    mel, _, _ = synthetic.mel_targets(hp, lens, frames_per_token=1, max_frames=96)
+    S = mel.shape[1] // 2
+    with torch.no_grad():
+        ref = mir.decode(enc_ref, lens, mel_targets=mel, philox_seed=5)
+    d = eng.decode(enc_ref.cuda(), torch.from_numpy(lens), mel_targets=torch.from_numpy(mel), philox_seed=5)
+    assert d["steps"] == ref["steps"] == S
+    al = _t(eng.alignments(d["align_hist"], S))
+    np.testing.assert_allclose(_t(d["frames"]), ref["frames_raw"].numpy(), atol=ATOL_D2_FRAMES)
+    np.testing.assert_allclose(al, ref["alignments"].numpy(), atol=ATOL_D2_ALIGN)
+    # (ii) the whole long-form pass
+    out = eng.forward(torch.from_numpy(ids), torch.from_numpy(lens), reference_mel=torch.from_numpy(rm), max_iters=1000, philox_seed=5)
+    assert out["steps"] == 1000
+    assert out["mel_outputs"].shape == (B, 2000, 80) and out["alignments"].shape == (B, T, 1000)
+    al = _t(out["alignments"])
+    assert np.isfinite(al).all() and np.isfinite(_t(out["mel_outputs"])).all()
+    np.testing.assert_allclose(al.sum(1), 1.0, atol=2e-5)
+    for b, n in enumerate(lens):
+        assert al[b, n:].max(initial=0.0) == 0.0
+    mo = _t(out["mel_outputs"])
+    assert mo.min() >= -4.1 - 1e-6 and mo.max() <= 4.0 + 1e-6
+    out2 = eng.forward(torch.from_numpy(ids), torch.from_numpy(lens), reference_mel=torch.from_numpy(rm), max_iters=1000, philox_seed=5)
+    assert torch.equal(out["frames_raw"], out2["frames_raw"])
