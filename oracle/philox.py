@@ -61,3 +61,25 @@ def prenet_masks(seed, steps, batch, units=256, layers=2, step0=0):
         for l in range(layers):
             out[s, :, l, :] = prenet_keep_mask(seed, step0 + s, batch, units, l)
     return out
+
+
+TRAIN_TAG = 0x54524E31  # "TRN1": 4th counter word of the training-mode mask streams
+
+
+def keep_threshold(p):
+    """uint32 threshold t with keep <=> word < t  (P[keep] = t / 2^32)."""
+    return min(int(p * 4294967296.0), 0xFFFFFFFF)
+
+
+def keep_mask(seed, stream, n, p, offset=0):
+    """Training-mode Bernoulli(p) keep bits (encoder / postnet dropout, zoneout masks; the reference
+    draws them from TF's stateful RNG, Encoder.py:135-136,167): element ``idx`` of mask stream
+    ``stream`` uses word ``idx & 3`` of Philox4x32-10(counter=(idx >> 2, stream, idx >> 34, TRAIN_TAG),
+    key=seed).  Returns uint8 [n] for idx in [offset, offset + n)."""
+    idx = np.arange(offset, offset + n, dtype=np.uint64)
+    blk = idx >> np.uint64(2)
+    o = philox4x32_10(blk & _MASK, np.uint64(stream), blk >> np.uint64(32), np.uint64(TRAIN_TAG),
+                      seed & 0xFFFFFFFF, (seed >> 32) & 0xFFFFFFFF)
+    lane = (idx & np.uint64(3)).astype(np.int64)
+    word = np.where(lane == 0, o[0], np.where(lane == 1, o[1], np.where(lane == 2, o[2], o[3])))
+    return (word < np.uint32(keep_threshold(p))).astype(np.uint8)
