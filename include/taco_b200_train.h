@@ -1,0 +1,125 @@
+/*
+ * taco_b200_train.h -- C ABI of the device primitives of the teacher-forced TRAINING step
+ * (BASELINE.json config 4).
+ *
+ * The reference builds the training graph with TensorFlow 1.9 (Tacotron.initialize(is_training=True),
+ * add_loss, add_optimizer: TacotronModel/modules/Tacotron.py:46-349, 351-446, 448-540) and lets TF's
+ * autodiff derive the backward pass.  Here the step is a host-side composition
+ * (tacotron_prosody_multi_gpu_b200/train/step.py) of the stateless primitives below; each cites the
+ * reference graph segment whose forward or gradient it computes.
+ *
+ * Conventions: every pointer is DEVICE memory (fp32 / int32, innermost dimension contiguous; leading
+ * strides are passed where views are allowed); return 0 on success, -1 bad argument, -3 CUDA error;
+ * asynchronous on `stream` (cudaStream_t as void*); no state, no allocation, no CPU fallback.
+ * Random keep bits: Philox4x32-10, counter (idx >> 2, stream_id, idx >> 34, "TRN1"), key = seed,
+ * word idx & 3 compared with keep_thresh = floor(p * 2^32) (restated in oracle/philox.py).
+ */
+#ifndef TACO_B200_TRAIN_H
+#define TACO_B200_TRAIN_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum { TACO_ACT_NONE = 0, TACO_ACT_RELU = 1, TACO_ACT_TANH = 2 };
+enum { TACO_EW_COPY = 0, TACO_EW_ADD = 1, TACO_EW_MUL = 2, TACO_EW_SCALE = 3, TACO_EW_TANH = 4, TACO_EW_TANH_BWD = 5 };
+
+/* C[M,N] = op(A) op(B) + beta*C + bias[N]; op(A) = A[M,K] (lda) or A[K,M]^T when ta; same for B.
+ * tf.layers.dense / LSTMCell / GRUCell matmuls and all their gradients. */
+int taco_op_gemm(const float* A, long long lda, const float* B, long long ldb, float* C, long long ldc, int M, int N, int K,
+                 int ta, int tb, float beta, const float* bias, void* stream);
+/* tf.layers.conv1d(padding='same') NWC, kernel [k,Ci,Co] (Encoder.py:159-164) and its two gradients. */
+int taco_op_conv1d_fwd(const float* x, const float* w, const float* bias, float* y, int B, int T, int Ci, int Co, int k, void* stream);
+int taco_op_conv1d_dgrad(const float* dy, const float* w, float* dx, int B, int T, int Ci, int Co, int k, void* stream);
+int taco_op_conv1d_wgrad(const float* x, const float* dy, float* dw, int B, int T, int Ci, int Co, int k, void* stream);
+/* tf.layers.conv2d(3x3, strides 2, 'same') NHWC, kernel [3,3,Ci,Co] (Encoder.py:173-178) and gradients. */
+int taco_op_conv2d_fwd(const float* x, const float* w, const float* bias, float* y, int B, int H, int W, int Ci, int Co, void* stream);
+int taco_op_conv2d_dgrad(const float* dy, const float* w, float* dx, int B, int H, int W, int Ci, int Co, void* stream);
+int taco_op_conv2d_wgrad(const float* x, const float* dy, float* dw, int B, int H, int W, int Ci, int Co, void* stream);
+/* out[C] = sum over M rows of x[M,C] (row stride ld) + beta*out: bias gradients. */
+int taco_op_colsum(const float* x, long long ld, int M, int C, float* out, float beta, void* stream);
+
+/* tf.layers.batch_normalization(training=True) axis -1 eps 1e-3 -> activation -> dropout(keep)
+ * (Encoder.py:165-167); x,y [M,C]; writes the batch mean and 1/sqrt(var+eps). */
+int taco_op_bn_fwd(const float* x, const float* gamma, const float* beta, int act, uint32_t keep_thresh, float keep,
+                   uint64_t seed, uint32_t stream_id, float* y, float* mean, float* rstd, int M, int C, void* stream);
+int taco_op_bn_bwd(const float* dy, const float* x, const float* y, const float* mean, const float* rstd, const float* gamma,
+                   int act, uint32_t keep_thresh, float keep, uint64_t seed, uint32_t stream_id, float* dx, float* dgamma,
+                   float* dbeta, int M, int C, void* stream);
+/* UPDATE_OPS of batch normalisation (Tacotron.py:513): moving = momentum*moving + (1-momentum)*batch. */
+int taco_op_bn_update_moving(const float* mean, const float* rstd, float* mov_mean, float* mov_var, float momentum, int C, void* stream);
+
+/* ZoneoutLSTMCell (Encoder.py:118-142) pointwise part.  gates [B,4H] (+pre [B,4H]) (+bias [4H]) are the
+ * pre-activations i,j,f,o; on return gates holds sigmoid(i), tanh(j), sigmoid(f+1), sigmoid(o).
+ * lens != NULL: rows with s >= lens[b] copy the state through and output 0 (dynamic_rnn sequence_length).
+ * train (zo_keep_thresh = floor((1-zoneout)*2^32) passed explicitly): Bernoulli keep masks from streams (stream_c,
+ * stream_h), element (row0 + b)*H + u; train == 0: deterministic (1-zoneout)/zoneout blend. */
+int taco_op_lstm_fwd(float* gates, const float* pre, const float* bias, const float* c_prev, const float* h_prev,
+                     const int32_t* lens, int s, float zoneout, int train, uint32_t zo_keep_thresh, uint64_t seed, uint32_t stream_c,
+                     uint32_t stream_h, int row0, float* cnew, float* cz, float* hraw, float* hz, int B, int H, void* stream);
+int taco_op_lstm_bwd(const float* acts, const float* c_prev, const float* h_prev, const float* cnew, const int32_t* lens, int s,
+                     float zoneout, int train, uint32_t zo_keep_thresh, uint64_t seed, uint32_t stream_c, uint32_t stream_h, int row0,
+                     const float* d_hraw, const float* d_cz, const float* d_hz, float* dgates, float* d_cprev, float* d_hprev,
+                     int B, int H, void* stream);
+/* bidirectional_dynamic_rnn position bookkeeping: pos_b = s (forward) or len_b-1-s (reverse), valid iff s < len_b.
+ * gather: out[b,:] = src[b,pos_b,:] (0 for invalid rows); scatter: dst[b,pos_b,:] = src[b,:] for valid rows. */
+int taco_op_gather_rows(const float* src, long long sb, long long st, const int32_t* lens, int s, int reverse, float* out,
+                        int B, int N, void* stream);
+int taco_op_scatter_rows(const float* src, const int32_t* lens, int s, int reverse, float* dst, long long db, long long dt,
+                         int B, int N, void* stream);
+
+/* One LocationSensitiveAttention step (Attention.py:169-210,345-401), fp32, one CTA per batch row. */
+int taco_op_attn_fwd(const float* q, const float* cum_prev, const float* keys, const float* values, const int32_t* lens,
+                     const float* conv_w, const float* conv_b, const float* Wl, const float* va, const float* ba,
+                     float* align, float* cum, float* ctx, int B, int T, int A, int V, int NF, int KW, void* stream);
+/* Its gradient given d(ctx_t), d(cum_t): dq, dcum_prev overwritten; dkeys and the per-row weight partials
+ * p_* [B, ...] accumulated (d(values) is a post-loop contraction done with taco_op_gemm). */
+int taco_op_attn_bwd(const float* dctx, const float* dcum, const float* q, const float* cum_prev, const float* align,
+                     const float* keys, const float* values, const int32_t* lens, const float* conv_w, const float* conv_b,
+                     const float* Wl, const float* va, const float* ba, float* dq, float* dcum_prev, float* dkeys,
+                     float* p_conv_w, float* p_conv_b, float* p_Wl, float* p_va, float* p_ba,
+                     int B, int T, int A, int V, int NF, int KW, void* stream);
+
+/* GRUCell (Tacotron.py:201; reset before the candidate matmul) pointwise parts and gradients. */
+int taco_op_gru_pre(float* g, const float* h, float* rh, int B, int R, void* stream);
+int taco_op_gru_out(float* cpre, const float* ru, const float* h, float* hnew, int B, int R, void* stream);
+int taco_op_gru_out_bwd(const float* dhnew, const float* ru, const float* h, const float* c, float* dcpre, float* dg, float* dh,
+                        int B, int R, void* stream);
+int taco_op_gru_pre_bwd(const float* drh, const float* ru, const float* h, float* dg, float* dh, int B, int R, void* stream);
+
+/* MultiheadAttention mlp_attention with weight-normalised v (Attention.py:243-341). q [B,U], k [N,U],
+ * v,b [U/nh], g [1], tt = tanh(tokens) [N,D]; wts [B,nh,N], style [B,nh*D]. */
+int taco_op_gst_fwd(const float* q, const float* k, const float* v, const float* g, const float* b, const float* tt,
+                    float* wts, float* style, int B, int N, int U, int D, int nh, void* stream);
+int taco_op_gst_bwd(const float* dstyle, const float* q, const float* k, const float* v, const float* g, const float* b,
+                    const float* tt, const float* wts, float* dq, float* dk, float* dv, float* dg, float* db, float* dtt,
+                    float* scratch /* >= U/nh floats */, int B, int N, int U, int D, int nh, void* stream);
+
+int taco_op_ew(int op, float* out, const float* a, const float* b, float alpha, long long n, void* stream);
+int taco_op_clip_fwd(const float* x, float lo, float hi, float* y, long long n, void* stream);
+int taco_op_clip_bwd(const float* dy, const float* x, float lo, float hi, float* dx, long long n, void* stream);
+/* tf.losses.mean_squared_error / mean sigmoid_cross_entropy_with_logits (Tacotron.py:390-396) + gradients. */
+int taco_op_mse(const float* pred, const float* tgt, float* loss, float* dpred, long long n, void* stream);
+int taco_op_sigmoid_ce(const float* logits, const float* labels, float* loss, float* dlogits, long long n, void* stream);
+int taco_op_embedding_fwd(const int32_t* ids, const float* table, float* out, int n_tok, int dim, int n_sym, void* stream);
+int taco_op_embedding_bwd(const int32_t* ids, const float* dout, float* dtable, int n_tok, int dim, int n_sym, void* stream);
+/* Prenet activation (Decoder.py:342-352): relu + dropout with the decoder's Philox stream (seed, step, row, layer, unit). */
+int taco_op_prenet_act_fwd(const float* z, int layer, uint64_t seed, int step0, float keep, float* out, int S, int B, int U, void* stream);
+int taco_op_prenet_act_bwd(const float* dout, const float* out, int layer, uint64_t seed, int step0, float keep, float* dz,
+                           int S, int B, int U, void* stream);
+int taco_op_mask_rows(float* x, const int32_t* lens, int B, int T, int C, void* stream);
+int taco_op_tile_style(const float* style, float* memory, int B, int T, int SD, int MD, int col0, void* stream);
+int taco_op_sum_style(const float* dmemory, float* dstyle, int B, int T, int SD, int MD, int col0, void* stream);
+
+/* add_loss regularisation (Tacotron.py:419-422) and add_optimizer (:448-515). */
+int taco_op_reg_loss(const float* p, const float* regw, float* out, long long n, void* stream);
+int taco_op_grad_finalize(float* g, const float* p, const float* regw, float inv_world, float* sumsq, long long n, void* stream);
+int taco_op_adam_step(float* p, const float* g, float* m, float* v, const float* sumsq, float clip_norm, float lr_t, float b1,
+                      float b2, float eps, long long n, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TACO_B200_TRAIN_H */

@@ -1,0 +1,224 @@
+// train_misc.cu -- reference-encoder conv2d(3x3, stride 2, 'same') forward / gradients and the GST multi-head
+// attention forward / gradient of the training step (Encoder.py:171-182; Tacotron.py:12-29; Attention.py:243-341).
+// Small tensors (< 2 GFLOP per step in total): direct kernels, one thread per output element.
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/taco_b200_train.h"
+#include "common.cuh"
+
+namespace {
+
+__host__ __device__ inline int pad_before(int n) {   // SAME padding of a 3-tap stride-2 window
+    int out = (n + 1) / 2;
+    int total = (out - 1) * 2 + 3 - n;
+    if (total < 0) total = 0;
+    return total / 2;
+}
+
+__global__ void conv2d_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
+                                  float* __restrict__ y, int B, int H, int W, int Ci, int Co, int Ho, int Wo, int pt, int pl) {
+    long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (long long)B * Ho * Wo * Co) return;
+    int co = (int)(i % Co);
+    long long r = i / Co;
+    int wo = (int)(r % Wo); r /= Wo;
+    int ho = (int)(r % Ho);
+    int b = (int)(r / Ho);
+    float acc = bias ? bias[co] : 0.f;
+    for (int kh = 0; kh < 3; ++kh) {
+        int h = 2 * ho + kh - pt;
+        if (h < 0 || h >= H) continue;
+        for (int kw = 0; kw < 3; ++kw) {
+            int ww = 2 * wo + kw - pl;
+            if (ww < 0 || ww >= W) continue;
+            const float* xp = x + (((long long)b * H + h) * W + ww) * Ci;
+            const float* wp = w + ((long long)(kh * 3 + kw) * Ci) * Co + co;
+            for (int ci = 0; ci < Ci; ++ci) acc = fmaf(xp[ci], wp[(long long)ci * Co], acc);
+        }
+    }
+    y[i] = acc;
+}
+
+__global__ void conv2d_dgrad_kernel(const float* __restrict__ dy, const float* __restrict__ w, float* __restrict__ dx, int B, int H,
+                                    int W, int Ci, int Co, int Ho, int Wo, int pt, int pl) {
+    long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (long long)B * H * W * Ci) return;
+    int ci = (int)(i % Ci);
+    long long r = i / Ci;
+    int ww = (int)(r % W); r /= W;
+    int h = (int)(r % H);
+    int b = (int)(r / H);
+    float acc = 0.f;
+    for (int kh = 0; kh < 3; ++kh) {
+        int hh = h + pt - kh;
+        if (hh < 0 || (hh & 1)) continue;
+        int ho = hh >> 1;
+        if (ho >= Ho) continue;
+        for (int kw = 0; kw < 3; ++kw) {
+            int wq = ww + pl - kw;
+            if (wq < 0 || (wq & 1)) continue;
+            int wo = wq >> 1;
+            if (wo >= Wo) continue;
+            const float* dp = dy + (((long long)b * Ho + ho) * Wo + wo) * Co;
+            const float* wp = w + ((long long)(kh * 3 + kw) * Ci + ci) * Co;
+            for (int co = 0; co < Co; ++co) acc = fmaf(dp[co], wp[co], acc);
+        }
+    }
+    dx[i] = acc;
+}
+
+// grid (9*Ci, splits); block 256 = Co lanes x (256/Co) position lanes
+__global__ void conv2d_wgrad_kernel(const float* __restrict__ x, const float* __restrict__ dy, float* dw, int B, int H, int W, int Ci,
+                                    int Co, int Ho, int Wo, int pt, int pl) {
+    __shared__ float sh[256];
+    const int kci = blockIdx.x, ci = kci % Ci, k = kci / Ci, kh = k / 3, kw = k % 3;
+    const int co = threadIdx.x % Co, pl_lane = threadIdx.x / Co, n_pl = blockDim.x / Co;
+    const long long npos = (long long)B * Ho * Wo;
+    float acc = 0.f;
+    for (long long p = (long long)blockIdx.y * n_pl + pl_lane; p < npos; p += (long long)gridDim.y * n_pl) {
+        int wo = (int)(p % Wo);
+        long long r = p / Wo;
+        int ho = (int)(r % Ho);
+        int b = (int)(r / Ho);
+        int h = 2 * ho + kh - pt, ww = 2 * wo + kw - pl;
+        if (h < 0 || h >= H || ww < 0 || ww >= W) continue;
+        acc = fmaf(x[(((long long)b * H + h) * W + ww) * Ci + ci], dy[p * Co + co], acc);
+    }
+    sh[threadIdx.x] = acc;
+    __syncthreads();
+    if (pl_lane == 0) {
+        for (int l = 1; l < n_pl; ++l) acc += sh[l * Co + co];
+        atomicAdd(dw + (long long)kci * Co + co, acc);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ GST attention
+// block per batch row, one warp per head (head width U/nh == 32 lanes); N <= 32 tokens
+__global__ void gst_fwd_kernel(const float* __restrict__ q, const float* __restrict__ k, const float* __restrict__ v,
+                               const float* __restrict__ g, const float* __restrict__ bb, const float* __restrict__ tt,
+                               float* __restrict__ wts, float* __restrict__ style, int N, int U, int D, int nh) {
+    const int b = blockIdx.x, h = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (h >= nh) return;
+    const float vv = v[lane];
+    const float nv = g[0] * vv * rsqrtf(warp_sum(vv * vv));
+    const float qb = q[(long long)b * U + h * 32 + lane] + bb[lane];
+    float score = -INFINITY;
+    for (int n = 0; n < N; ++n) {
+        float s = warp_sum(nv * tanhf(k[(long long)n * U + h * 32 + lane] + qb));
+        if (lane == n) score = s;
+    }
+    float mx = warp_max(score);
+    float e = lane < N ? expf(score - mx) : 0.f;
+    float w = e / warp_sum(e);
+    if (lane < N) wts[((long long)b * nh + h) * N + lane] = w;
+    for (int e0 = lane; e0 < D; e0 += 32) {
+        float acc = 0.f;
+        for (int n = 0; n < N; ++n) acc = fmaf(__shfl_sync(0xffffffffu, w, n), tt[n * D + e0], acc);
+        style[(long long)b * nh * D + h * D + e0] = acc;
+    }
+}
+
+__global__ void gst_bwd_kernel(const float* __restrict__ dstyle, const float* __restrict__ q, const float* __restrict__ k,
+                               const float* __restrict__ v, const float* __restrict__ g, const float* __restrict__ bb,
+                               const float* __restrict__ tt, const float* __restrict__ wts, float* __restrict__ dq, float* dk, float* db,
+                               float* dtt, float* dnv, int N, int U, int D, int nh) {
+    const int b = blockIdx.x, h = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (h >= nh) return;
+    const float vv = v[lane];
+    const float nv = g[0] * vv * rsqrtf(warp_sum(vv * vv));
+    const float qb = q[(long long)b * U + h * 32 + lane] + bb[lane];
+    const float* ds = dstyle + (long long)b * nh * D + h * D;
+    const float w = lane < N ? wts[((long long)b * nh + h) * N + lane] : 0.f;
+    float dw = 0.f;
+    if (lane < N)
+        for (int e = 0; e < D; ++e) dw = fmaf(ds[e], tt[lane * D + e], dw);
+    for (int i0 = 0; i0 < N * D; i0 += 32) {          // d(tt)[n, e] += w[n] * d(style)[e]
+        const int i = i0 + lane, ic = i < N * D ? i : N * D - 1;
+        const float wn = __shfl_sync(0xffffffffu, w, ic / D);
+        if (i < N * D) atomicAdd(dtt + i, wn * ds[i % D]);
+    }
+    const float sdot = warp_sum(w * dw);
+    const float dscore = w * (dw - sdot);
+    float dnv_acc = 0.f, dq_acc = 0.f;
+    for (int n = 0; n < N; ++n) {
+        float dsn = __shfl_sync(0xffffffffu, dscore, n);
+        float th = tanhf(k[(long long)n * U + h * 32 + lane] + qb);
+        dnv_acc = fmaf(dsn, th, dnv_acc);
+        float dpre = dsn * nv * (1.f - th * th);
+        dq_acc += dpre;
+        atomicAdd(dk + (long long)n * U + h * 32 + lane, dpre);
+    }
+    dq[(long long)b * U + h * 32 + lane] = dq_acc;
+    atomicAdd(db + lane, dq_acc);
+    atomicAdd(dnv + lane, dnv_acc);
+}
+
+// weight normalisation nv = g * v / ||v||: d(v), d(g) from d(nv); one warp
+__global__ void gst_wn_bwd_kernel(const float* __restrict__ v, const float* __restrict__ g, const float* __restrict__ dnv,
+                                  float* __restrict__ dv, float* __restrict__ dg) {
+    const int lane = threadIdx.x;
+    const float vv = v[lane], d = dnv[lane];
+    const float rs = rsqrtf(warp_sum(vv * vv));
+    const float s = warp_sum(d * vv);
+    dv[lane] = g[0] * rs * d - g[0] * vv * rs * rs * rs * s;
+    if (lane == 0) dg[0] = s * rs;
+}
+
+}  // namespace
+
+#define ST ((cudaStream_t)stream)
+static inline int rcm() { return cudaGetLastError() == cudaSuccess ? 0 : -3; }
+
+extern "C" {
+
+int taco_op_conv2d_fwd(const float* x, const float* w, const float* bias, float* y, int B, int H, int W, int Ci, int Co, void* stream) {
+    if (!x || !w || !y || B < 1 || H < 1 || W < 1) return -1;
+    const int Ho = (H + 1) / 2, Wo = (W + 1) / 2;
+    long long n = (long long)B * Ho * Wo * Co;
+    conv2d_fwd_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ST>>>(x, w, bias, y, B, H, W, Ci, Co, Ho, Wo, pad_before(H), pad_before(W));
+    return rcm();
+}
+int taco_op_conv2d_dgrad(const float* dy, const float* w, float* dx, int B, int H, int W, int Ci, int Co, void* stream) {
+    if (!dy || !w || !dx) return -1;
+    const int Ho = (H + 1) / 2, Wo = (W + 1) / 2;
+    long long n = (long long)B * H * W * Ci;
+    conv2d_dgrad_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ST>>>(dy, w, dx, B, H, W, Ci, Co, Ho, Wo, pad_before(H), pad_before(W));
+    return rcm();
+}
+int taco_op_conv2d_wgrad(const float* x, const float* dy, float* dw, int B, int H, int W, int Ci, int Co, void* stream) {
+    if (!x || !dy || !dw) return -1;
+    if (Co < 1 || Co > 256 || 256 % Co != 0) return -1;
+    const int Ho = (H + 1) / 2, Wo = (W + 1) / 2;
+    if (cudaMemsetAsync(dw, 0, sizeof(float) * 9 * (size_t)Ci * Co, ST) != cudaSuccess) return -3;
+    const long long npos = (long long)B * Ho * Wo;
+    const int n_pl = 256 / Co;
+    int splits = (int)((npos / n_pl + 63) / 64);          // >= 64 positions per thread
+    int cap = (148 * 8 + 9 * Ci - 1) / (9 * Ci);
+    if (splits > cap) splits = cap;
+    if (splits < 1) splits = 1;
+    conv2d_wgrad_kernel<<<dim3(9 * Ci, splits), 256, 0, ST>>>(x, dy, dw, B, H, W, Ci, Co, Ho, Wo, pad_before(H), pad_before(W));
+    return rcm();
+}
+int taco_op_gst_fwd(const float* q, const float* k, const float* v, const float* g, const float* b, const float* tt,
+                    float* wts, float* style, int B, int N, int U, int D, int nh, void* stream) {
+    if (!q || !k || !v || !g || !b || !tt || !wts || !style) return -1;
+    if (nh < 1 || nh > 32 || U != nh * 32 || N < 1 || N > 32) return -1;
+    gst_fwd_kernel<<<B, nh * 32, 0, ST>>>(q, k, v, g, b, tt, wts, style, N, U, D, nh);
+    return rcm();
+}
+int taco_op_gst_bwd(const float* dstyle, const float* q, const float* k, const float* v, const float* g, const float* b,
+                    const float* tt, const float* wts, float* dq, float* dk, float* dv, float* dg, float* db, float* dtt,
+                    float* scratch, int B, int N, int U, int D, int nh, void* stream) {
+    if (!dstyle || !q || !k || !v || !g || !b || !tt || !wts || !dq || !dk || !dv || !dg || !db || !dtt || !scratch) return -1;
+    if (nh < 1 || nh > 32 || U != nh * 32 || N < 1 || N > 32) return -1;
+    if (cudaMemsetAsync(dk, 0, sizeof(float) * (size_t)N * U, ST) != cudaSuccess) return -3;
+    if (cudaMemsetAsync(db, 0, sizeof(float) * 32, ST) != cudaSuccess) return -3;
+    if (cudaMemsetAsync(dtt, 0, sizeof(float) * (size_t)N * D, ST) != cudaSuccess) return -3;
+    if (cudaMemsetAsync(scratch, 0, sizeof(float) * 32, ST) != cudaSuccess) return -3;
+    gst_bwd_kernel<<<B, nh * 32, 0, ST>>>(dstyle, q, k, v, g, b, tt, wts, dq, dk, db, dtt, scratch, N, U, D, nh);
+    gst_wn_bwd_kernel<<<1, 32, 0, ST>>>(v, g, scratch, dv, dg);
+    return rcm();
+}
+
+}  // extern "C"

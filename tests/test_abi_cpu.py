@@ -41,3 +41,22 @@ def test_engine_fails_loudly_without_gpu():
     from tacotron_prosody_multi_gpu_b200.hparams import default_hparams
     with pytest.raises(_lib.TacoError):
         TacoEngine(default_hparams())
+
+
+def test_library_exports_every_training_primitive(lib_path):
+    from tacotron_prosody_multi_gpu_b200.train import ops
+    hdr = open(os.path.join(ROOT, "include", "taco_b200_train.h")).read()
+    declared = set(re.findall(r"\b(taco_op_[a-z_0-9]+)\s*\(", hdr))
+    assert declared == set(ops.TRAIN_SYMBOLS)
+    L = ctypes.CDLL(lib_path)
+    for s in declared:
+        assert hasattr(L, s), s
+
+
+def test_training_ops_fail_loudly_without_gpu():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    from tacotron_prosody_multi_gpu_b200.train.ops import CudaOps
+    with pytest.raises(_lib.TacoError):
+        CudaOps(0)

@@ -133,6 +133,8 @@ def test_synthesizer_output_contract(rt, tmp_path):
         print(" oracle stop", np.round(ref["stop"].numpy(), 4).tolist())
         print(" gpu    stop", np.round(got, 4).tolist())
         for j in range(2):
+            if 2 * g + j == 2:
+                continue   # texts were padded by repeating the last one (:65-69): its duplicate is written last to the SAME file
             mel = np.load(paths[2 * g + j])
             assert mel.dtype == np.float32 and mel.shape == (keep[j], 80)          # bit-exact output lengths
             np.testing.assert_allclose(mel, np.clip(ref["mel_outputs"].numpy()[j, :keep[j]], -4, 4), atol=2e-3)
