@@ -10,8 +10,11 @@ per tower: ``tower_decoder_output`` / ``tower_mel_outputs`` [B,F,80], ``tower_al
 ``tower_stop_token_prediction`` [B,F] (Tacotron.py:314-317) and ``encoder_outputs`` [B,T,768] (:224).
 
 Modes: inference (free running, TacoTestHelper) and GTA / evaluation
-(teacher-forced forward, TacoTrainingHelper with ratio 1.0).  ``is_training=True`` (dropout, batch
-statistics, Bernoulli zoneout, losses, optimizer) is SURVEY 8f row f1 and raises.
+(teacher-forced forward, TacoTrainingHelper with ratio 1.0), and training: ``is_training=True`` runs the
+train-mode forward of every tower (dropout, batch statistics, Bernoulli zoneout, stop logits, reference
+encoder on the mel targets) through the training primitives (train/step.py); ``add_loss`` exposes the
+reference's loss attributes and ``add_optimizer`` an ``optimize()`` callable that runs the hand-derived
+backward pass of every tower, averages the tower gradients, clips and applies Adam (Tacotron.py:351-540).
 """
 import numpy as np
 
@@ -60,14 +63,10 @@ class Tacotron(object):
             raise RuntimeError('Model set to mask paddings but no targets lengths provided for the mask!')
         if is_training and is_evaluating:
             raise RuntimeError('Model can not be in training and evaluation modes at the same time!')
-        if is_training:
-            raise FusedStageError("is_training=True (losses, backward, optimizer, dropout / batch statistics) is SURVEY 8f row f1; "
-                                  "the teacher-forced forward pass is available with GTA=True or is_evaluating=True")
-
         import torch
         from ... import runtime
         from ...synthetic import gst_random_weights
-        eng = runtime.engine(hp)
+        eng = None if is_training else runtime.engine(hp)
         G = hp.tacotron_num_gpus
         inputs = np.asarray(inputs.cpu() if hasattr(inputs, "cpu") else inputs)
         input_lengths = np.asarray(input_lengths.cpu() if hasattr(input_lengths, "cpu") else input_lengths).astype(np.int32).reshape(-1)
@@ -94,6 +93,8 @@ class Tacotron(object):
         self.tower_targets_lengths = None if targets_lengths is None else np.split(np.asarray(targets_lengths), G)
         self.tower_stop_token_targets = []
         self.tower_linear_targets = []
+        if is_training:
+            return self._initialize_training(stop_token_targets, split_infos, philox_seed, global_step)
         if reference_mel is not None:
             reference_mel = torch.as_tensor(np.asarray(reference_mel, np.float32))
         elif gst_weights is None:
@@ -147,8 +148,82 @@ class Tacotron(object):
         self.all_vars = sorted(runtime.weights(hp).keys())
         return self
 
+    # ------------------------------------------------------------------ training (Tacotron.py:46-349 train mode, 351-540)
+    def _initialize_training(self, stop_token_targets, split_infos, philox_seed, global_step):
+        from ... import runtime
+        hp = self.hparams
+        G = hp.tacotron_num_gpus
+        tr = runtime.trainer(hp)
+        o = tr.ops
+        batch_size = self.tower_inputs[0].shape[0]
+        stop_np = np.asarray(stop_token_targets.cpu() if hasattr(stop_token_targets, "cpu") else stop_token_targets, np.float32)
+        p_stop = split_func(stop_np, split_infos[:, 2] if split_infos.shape[1] > 2 and split_infos[:, 2].any() else split_infos[:, 1])
+        self.tower_stop_token_targets = [np.ascontiguousarray(p_stop[i].reshape(batch_size, -1)) for i in range(G)]
+        seed = (hp.tacotron_random_seed + 7919 * int(global_step or 0)) if philox_seed is None else philox_seed
+        self._trainer, self._tapes, self._tower_losses = tr, [], []
+        self.tower_decoder_output, self.tower_alignments = [], []
+        self.tower_stop_token_prediction, self.tower_mel_outputs = [], []
+        for i in range(G):
+            out = tr.step_fn.forward(o.to_device(self.tower_inputs[i].astype(np.int32)), o.to_device(self.tower_input_lengths[i].astype(np.int32)),
+                                     o.to_device(self.tower_mel_targets[i]), o.to_device(self.tower_stop_token_targets[i]), seed + 104729 * i)
+            self._tapes.append(tr.step_fn.tape)
+            self._tower_losses.append(out["losses"])
+            self.tower_decoder_output.append(out["decoder_output"])
+            self.tower_mel_outputs.append(out["mel_outputs"])
+            self.tower_stop_token_prediction.append(out["stop_token_prediction"])      # logits in training (Decoder.py:408-409)
+            self.tower_alignments.append(out["alignments"].permute(1, 2, 0).contiguous())   # [B, T, S] (Tacotron.py:312)
+            self.encoder_outputs = out["encoder_outputs"]
+        self.all_vars = sorted(tr.step_fn.store.layout.keys())
+        return self
+
     def add_loss(self):
-        raise FusedStageError("add_loss (Tacotron.py:351-446) is SURVEY 8f row f1")
+        """Tacotron.py:351-446: per-tower before / after / stop-token / regularization losses and their tower means."""
+        if not getattr(self, "_tower_losses", None):
+            raise RuntimeError("add_loss: initialize(is_training=True) must have been called")
+        ls = [t.detach().cpu().numpy().astype(np.float64) for t in self._tower_losses]
+        self.tower_before_loss = [float(l[0]) for l in ls]
+        self.tower_after_loss = [float(l[1]) for l in ls]
+        self.tower_stop_token_loss = [float(l[2]) for l in ls]
+        self.tower_regularization_loss = [float(l[3]) for l in ls]
+        self.tower_linear_loss = [0.0 for _ in ls]
+        self.tower_loss = [float(l[0] + l[1] + l[2] + l[3]) for l in ls]
+        n = float(len(ls))
+        self.before_loss = sum(self.tower_before_loss) / n
+        self.after_loss = sum(self.tower_after_loss) / n
+        self.stop_token_loss = sum(self.tower_stop_token_loss) / n
+        self.regularization_loss = sum(self.tower_regularization_loss) / n
+        self.linear_loss = 0.0
+        self.loss = sum(self.tower_loss) / n
+        return self
 
     def add_optimizer(self, global_step):
-        raise FusedStageError("add_optimizer (Tacotron.py:448-540) is SURVEY 8f row f1")
+        """Tacotron.py:448-515.  Sets ``learning_rate``, ``gradients`` (name -> view of the flat gradient buffer, valid
+        after ``optimize()``) and ``optimize``: a callable that back-propagates every tower, averages the tower
+        gradients (and, under torch.distributed, all-reduces them across ranks), clips to global norm 1 and applies
+        Adam -- the eager equivalent of ``sess.run(model.optimize)``."""
+        if not getattr(self, "_tapes", None):
+            raise RuntimeError("add_optimizer: initialize(is_training=True) must have been called")
+        tr = self._trainer
+        st = tr.step_fn
+        step_no = int(global_step or 0)
+        self.learning_rate = st.learning_rate(step_no)
+        self.gradients = st.store.G
+
+        def optimize():
+            acc = None
+            for tape in self._tapes:
+                st.backward(tape)
+                if len(self._tapes) > 1:
+                    if acc is None:
+                        acc = st.store.g.clone()
+                    else:
+                        tr.ops.ew("add", acc, acc, st.store.g)
+            if acc is not None:
+                st.store.g.copy_(acc)
+            towers = len(self._tapes) * tr.world
+            st.apply(step_no, world=towers, all_reduce=tr._all_reduce if tr.world > 1 else None)
+            self._tapes = []
+            return step_no + 1
+
+        self.optimize = optimize
+        return self

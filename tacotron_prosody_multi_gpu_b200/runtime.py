@@ -10,7 +10,8 @@ from __future__ import annotations
 
 import os
 
-_state = {"engine": None, "key": None, "weights": None, "precision": os.environ.get("TACO_PRECISION", "bf16")}
+_state = {"engine": None, "key": None, "weights": None, "precision": os.environ.get("TACO_PRECISION", "bf16"),
+          "trainer": None, "trainer_key": None}
 
 
 def set_weights(weights):
@@ -52,11 +53,25 @@ def engine(hparams):
     return _state["engine"]
 
 
+def trainer(hparams):
+    """The data-parallel trainer of this process (train/trainer.py): flat parameter / gradient / Adam buffers created
+    from the installed weight container on first use; ``set_weights`` drops it."""
+    from .train.trainer import DataParallelTrainer
+    dev = device_index()
+    key = (dev, id(_state["weights"]))
+    if _state["trainer"] is None or _state["trainer_key"] != key:
+        _state["trainer"] = DataParallelTrainer(hparams, weights(hparams), device=dev)
+        _state["trainer_key"] = (dev, id(_state["weights"]))
+    return _state["trainer"]
+
+
 def close():
     if _state["engine"] is not None:
         _state["engine"].close()
     _state["engine"] = None
     _state["key"] = None
+    _state["trainer"] = None
+    _state["trainer_key"] = None
 
 
 def install_aliases():

@@ -49,8 +49,16 @@ class ParamStore(object):
         self.v = ops.zeros(off)
         self.P = self._views(self.p)
         self.G = self._views(self.g)
-        self.stats = OrderedDict((name, ops.to_device(np.asarray(v, np.float32).copy()))
-                                 for name, v in weights.items() if not is_trainable(name))
+        # BN moving statistics: one flat buffer too (averaged across ranks by the data-parallel trainer)
+        snames = [name for name in weights if not is_trainable(name)]
+        sflat = np.concatenate([np.asarray(weights[n], np.float32).reshape(-1) for n in snames]) if snames else np.zeros(0, np.float32)
+        self.s = ops.to_device(sflat)
+        self.stats = OrderedDict()
+        off = 0
+        for name in snames:
+            sz = int(np.asarray(weights[name]).size)
+            self.stats[name] = self.s[off:off + sz]
+            off += sz
 
     def _views(self, flat):
         out = OrderedDict()

@@ -289,10 +289,12 @@ class TrainStep(object):
                     encoder_outputs=memory, losses=ls)
 
     # ------------------------------------------------------------------ backward
-    def backward(self):
+    def backward(self, tape=None):
         """Hand-derived gradient of loss = before + after + stop (+ regularization, added in apply()) with
-        respect to every trainable variable -> the flat gradient buffer ``store.g``."""
-        hp, o, P, G, t = self.hp, self.ops, self.store.P, self.store.G, self.tape
+        respect to every trainable variable -> the flat gradient buffer ``store.g`` (overwritten).
+        ``tape``: the record of the forward pass to differentiate (default: the most recent one)."""
+        hp, o, P, G = self.hp, self.ops, self.store.P, self.store.G
+        t = self.tape if tape is None else tape
         B, T, F, S, seed, MD = t["B"], t["T"], t["F"], t["S"], t["seed"], t["MD"]
         r, M = hp.outputs_per_step, hp.num_mels
         H, D, A = hp.enc_lstm_hidden_size, hp.decoder_lstm_units, hp.attention_dim

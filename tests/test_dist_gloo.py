@@ -56,3 +56,61 @@ def test_two_rank_shard_plan_gloo(tmp_path):
     d = json.loads(line)
     assert d["world"] == 2 and d["covered"] and d["disjoint"] and d["max"] == 2.0
     assert sum(d["sizes"]) == 512 and min(d["sizes"]) >= 64   # cost-balanced (LPT), not count-balanced
+
+
+TRAIN_WORKER = textwrap.dedent("""
+    import os, sys, json
+    sys.path.insert(0, %r); sys.path.insert(0, os.path.join(%r, "tests"))
+    import numpy as np, torch, torch.distributed as dist
+    from cpu_train_ops import TorchOps
+    from oracle import train_oracle
+    from tacotron_prosody_multi_gpu_b200 import synthetic, weights
+    from tacotron_prosody_multi_gpu_b200.hparams import default_hparams
+    from tacotron_prosody_multi_gpu_b200.train.trainer import DataParallelTrainer
+    dist.init_process_group("gloo")
+    rank, world = dist.get_rank(), dist.get_world_size()
+    hp = default_hparams()
+    w = weights.init_weights(hp, perturb=0.05)
+    shards = [((6, 4), 11), ((5, 7), 12)]                     # (token lengths, dropout seed) per rank
+    def data(r):
+        ids, lens = synthetic.token_batch(hp, list(shards[r][0]), seed=100 + r)
+        mel, stop, _ = synthetic.mel_targets(hp, lens, frames_per_token=2, seed=200 + r)
+        return ids, lens, mel, stop, shards[r][1]
+    ids, lens, mel, stop, seed = data(rank)
+    tr = DataParallelTrainer(hp, w, ops=TorchOps())
+    ls = tr.step(torch.from_numpy(ids), torch.from_numpy(lens), torch.from_numpy(mel), torch.from_numpy(stop), seed)
+    new = tr.export()
+    # every rank must hold identical weights after the update
+    flat = torch.from_numpy(np.concatenate([new[k].reshape(-1) for k in sorted(new)]))
+    ref = flat.clone(); dist.broadcast(ref, 0)
+    same = bool(torch.equal(flat, ref))
+    ok = True
+    if rank == 0:   # the reference's semantics: mean of the tower gradients -> clip -> Adam (Tacotron.py:484-515)
+        grads = []
+        for r in range(world):
+            out, orc = train_oracle.train_forward(hp, w, *data(r))
+            out["loss"].backward()
+            grads.append(train_oracle.gradients(orc))
+        wn = {n: np.asarray(w[n], np.float64).copy() for n in grads[0]}
+        m = {n: np.zeros_like(v) for n, v in wn.items()}; v = {n: np.zeros_like(x) for n, x in wn.items()}
+        train_oracle.adam_update(hp, wn, grads, m, v, 0)
+        err = max(float(np.abs(new[n] - wn[n]).max()) for n in wn)
+        ok = err < 5e-5
+        print(json.dumps({"world": world, "same": same, "max_err": err, "loss": float(ls[4])}))
+    assert same and ok
+    dist.destroy_process_group()
+""") % (ROOT, ROOT)
+
+
+def test_two_rank_data_parallel_training_step_gloo(tmp_path):
+    """The N>1 training path on CPU: 2 ranks x 1 tower with the torch-CPU twin of the device primitives, one
+    all-reduce of the flat gradient buffer; the result equals the reference's tower-averaged update."""
+    script = tmp_path / "train_worker.py"
+    script.write_text(TRAIN_WORKER)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+           "--master-port", str(_free_port()), str(script)]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, (r.stdout[-1500:], r.stderr[-2500:])
+    import json
+    d = json.loads([l for l in r.stdout.splitlines() if l.startswith("{")][-1])
+    assert d["world"] == 2 and d["same"] and d["max_err"] < 5e-5

@@ -156,3 +156,53 @@ def test_sharded_synthesis_equals_unsharded(rt):
     assert sorted(merged) == list(range(9))
     for i in range(9):
         assert np.array_equal(one[i]["mel"], merged[i]["mel"])      # same batch composition -> bit-identical
+
+
+def test_tacotron_training_surface_two_towers(rt):
+    """initialize(is_training=True) -> add_loss -> add_optimizer -> optimize() through the reference's class surface
+    (Tacotron.py:46-48,351-540) with 2 towers packed along the time axis (split_infos), against the training oracle:
+    per-tower losses, tower-mean loss, and the weights after one clipped Adam update."""
+    from oracle import train_oracle
+    from tacotron_prosody_multi_gpu_b200.TacotronModel.modules.Tacotron import Tacotron
+    from tacotron_prosody_multi_gpu_b200.Utils.Tacotron_feeder import _prepare_inputs, _prepare_targets
+    hp, _ = rt
+    hp2 = hp.copy()
+    hp2.tacotron_num_gpus = 2
+    w = weights.init_weights(hp, perturb=0.05)
+    runtime.set_weights(w)
+    towers = []
+    for g, lengths in enumerate(([7, 5], [6, 8])):
+        ids, lens = synthetic.token_batch(hp, lengths, seed=50 + g)
+        mel, stop, _ = synthetic.mel_targets(hp, lens, frames_per_token=2, seed=60 + g)
+        towers.append((ids, lens, mel, stop))
+    inputs = np.concatenate([t[0] for t in towers], axis=1)
+    mel_targets = np.concatenate([t[2] for t in towers], axis=1)
+    stop_targets = np.concatenate([t[3] for t in towers], axis=1)
+    split_infos = np.asarray([[t[0].shape[1], t[2].shape[1], t[3].shape[1], 0] for t in towers], np.int32)
+    m = Tacotron(hp2)
+    m.initialize(inputs, np.concatenate([t[1] for t in towers]), mel_targets=mel_targets, stop_token_targets=stop_targets,
+                 is_training=True, split_infos=split_infos, global_step=0, philox_seed=17)
+    m.add_loss()
+    m.add_optimizer(global_step=0)
+    refs, grads = [], []
+    for g, (ids, lens, mel, stop) in enumerate(towers):
+        out, orc = train_oracle.train_forward(hp, w, ids, lens, mel, stop, 17 + 104729 * g)
+        out["loss"].backward()
+        refs.append(out)
+        grads.append(train_oracle.gradients(orc))
+    for g in range(2):
+        assert m.tower_mel_outputs[g].shape == refs[g]["mel_outputs"].shape
+        np.testing.assert_allclose(m.tower_mel_outputs[g].cpu().numpy(), refs[g]["mel_outputs"].detach().numpy(), atol=5e-4)
+        np.testing.assert_allclose(m.tower_alignments[g].cpu().numpy(), refs[g]["alignments"].detach().numpy(), atol=2e-5)
+        np.testing.assert_allclose(m.tower_loss[g], float(refs[g]["loss"].detach()), rtol=1e-4)
+    np.testing.assert_allclose(m.loss, float((refs[0]["loss"] + refs[1]["loss"]).detach()) / 2, rtol=1e-4)
+    assert m.learning_rate == hp.tacotron_initial_learning_rate
+    assert m.optimize() == 1
+    wn = {n: np.asarray(w[n], np.float64).copy() for n in grads[0]}
+    mm = {n: np.zeros_like(v) for n, v in wn.items()}
+    vv = {n: np.zeros_like(x) for n, x in wn.items()}
+    train_oracle.adam_update(hp, wn, grads, mm, vv, 0)
+    new = runtime.trainer(hp2).export()
+    for n in wn:
+        np.testing.assert_allclose(new[n], wn[n], atol=5e-5, err_msg=n)
+    runtime.set_weights(rt[1])

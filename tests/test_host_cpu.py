@@ -79,8 +79,13 @@ def test_tacotron_argument_errors_match_reference():
     hp2.mask_decoder = True
     with pytest.raises(RuntimeError, match="targets lengths"):
         Tacotron(hp2).initialize(ids, lens, mel_targets=np.zeros((2, 4, 80)), stop_token_targets=np.zeros((2, 4)), is_training=True)
-    with pytest.raises(FusedStageError):
-        m.initialize(ids, lens, mel_targets=np.zeros((2, 4, 80)), stop_token_targets=np.zeros((2, 4)), is_training=True)
+    import torch
+    if not torch.cuda.is_available():
+        from tacotron_prosody_multi_gpu_b200._lib import TacoError
+        with pytest.raises(TacoError):     # training runs on the device primitives only: no CPU fallback
+            m.initialize(ids, lens, mel_targets=np.zeros((2, 4, 80)), stop_token_targets=np.zeros((2, 4)), is_training=True)
+    with pytest.raises(RuntimeError, match="initialize"):
+        Tacotron(hp).add_loss()
 
 
 def test_install_aliases_exposes_reference_import_paths():
