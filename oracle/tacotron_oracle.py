@@ -57,9 +57,10 @@ class TacotronOracle(object):
 
     def __init__(self, hp, weights, dtype=torch.float32, conv_bf16=False, dec_bf16=False):
         """``conv_bf16``: round conv/dense GEMM operands of the encoder-conv / postnet stacks to
-        bf16 (fp32 accumulate), mirroring the tensor-core kernels' operand precision.
+        bf16 (fp32 accumulate), mirroring the tensor-core kernels' operand precision (this includes the
+        hoisted input projection of the encoder LSTMs; their recurrent contraction stays fp32).
         ``dec_bf16``: same for the decoder step's contractions (prenet, both LSTM layers, query
-        layer, frame/stop projection) and the attention values of the context reduction; recurrent
+        layer, frame/stop projection), the memory-layer keys and the attention values of the context reduction; recurrent
         state, gate non-linearities, energies, softmax and cumulative alignments stay fp32."""
         self.hp = hp
         self.dtype = dtype
@@ -114,21 +115,27 @@ class TacotronOracle(object):
         return x @ w
 
     @staticmethod
-    def lstm_cell(x, c, h, kernel, bias, round_ops=False):
-        """tf.nn.rnn_cell.LSTMCell (Encoder.py:104; App. A.1): gates i,j,f,o; forget_bias 1.0."""
-        xh = torch.cat([x, h], dim=1)
-        if round_ops:
-            xh, kernel = _round_bf16(xh), _round_bf16(kernel)
-        z = xh @ kernel + bias
+    def lstm_cell(x, c, h, kernel, bias, round_ops=False, round_input_only=False):
+        """tf.nn.rnn_cell.LSTMCell (Encoder.py:104; App. A.1): gates i,j,f,o; forget_bias 1.0.
+        ``round_input_only``: bf16 operands for the INPUT projection only (the encoder's hoisted x . W[0:in]
+        runs on the tensor cores in the bf16 modes; the recurrent h . W[in:] stays fp32)."""
+        if round_input_only:
+            n = x.shape[1]
+            z = _round_bf16(x) @ _round_bf16(kernel[:n]) + h @ kernel[n:] + bias
+        else:
+            xh = torch.cat([x, h], dim=1)
+            if round_ops:
+                xh, kernel = _round_bf16(xh), _round_bf16(kernel)
+            z = xh @ kernel + bias
         i, j, f, o = torch.chunk(z, 4, dim=1)
         new_c = torch.sigmoid(f + 1.0) * c + torch.sigmoid(i) * torch.tanh(j)
         new_h = torch.sigmoid(o) * torch.tanh(new_c)
         return new_c, new_h
 
-    def zoneout_lstm(self, x, c, h, kernel, bias, is_training=False, masks=None, round_ops=False):
+    def zoneout_lstm(self, x, c, h, kernel, bias, is_training=False, masks=None, round_ops=False, round_input_only=False):
         """ZoneoutLSTMCell.__call__ (Encoder.py:118-142; App. A.2): output = RAW new_h, state zoned."""
         z = self.hp.zoneout_rate
-        new_c, new_h = self.lstm_cell(x, c, h, kernel, bias, round_ops)
+        new_c, new_h = self.lstm_cell(x, c, h, kernel, bias, round_ops, round_input_only)
         if is_training:
             mc, mh = masks  # Bernoulli(1-z) keep masks; (1-z)*dropout(d, 1-z) == mask*d (Encoder.py:135-136)
             zc = c + mc.to(c.dtype) * (new_c - c)
@@ -167,7 +174,7 @@ class TacotronOracle(object):
                               torch.zeros_like(lengths))
             xt = x[rows, pos]
             m = None if masks is None else (masks[0][s], masks[1][s])
-            raw_h, zc, zh = self.zoneout_lstm(xt, c, h, kernel, bias, is_training, m)
+            raw_h, zc, zh = self.zoneout_lstm(xt, c, h, kernel, bias, is_training, m, round_input_only=self.conv_bf16)
             v = valid[:, None]
             c = torch.where(v, zc, c)
             h = torch.where(v, zh, h)
@@ -278,7 +285,7 @@ class TacotronOracle(object):
         else:
             values = memory
             mask = torch.ones_like(mask)
-        keys = values @ self.w[W_MEMORY + "/kernel"]
+        keys = self._dmm(values, self.w[W_MEMORY + "/kernel"])   # bf16 operands in the dec_bf16 mirror mode
         return values, keys, mask
 
     def attention_step(self, query, cum, values, keys, mask):

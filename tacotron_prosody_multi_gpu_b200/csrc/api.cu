@@ -68,6 +68,8 @@ struct TacoHandle {
     int post_cin_pad[8] = {};
     void* post_proj_wt = nullptr;
     void* enc_wt[8] = {};
+    void* enc_xw_wt[2] = {};   // LSTM input projection kernel[0:C] of fw / bw, bf16 K-major
+    void* keys_wt = nullptr;    // memory_layer kernel, bf16 K-major [128][768]
     float* dec_blob[2] = {};     // U = 2 (GN 128), U = 4 (GN 64)
     // dataflow decoder (decoder2.cu): fragment-major bf16 shards and fused location kernel
     uint32_t *dec2_blob = nullptr, *dec2_wq = nullptr, *dec2_ghi = nullptr, *dec2_glo = nullptr;
@@ -536,6 +538,19 @@ int conv(TacoHandle* h, const float* x, long long x_stride, long long x_bstride,
     return TACO_OK;
 }
 
+// keys = memory_layer(values) (Attention.py:153-158) for the bf16 decoders: tcgen05 dense, bf16 operands, fp32 out
+int keys_tc(TacoHandle* h, const void* vals_bf16, float* keys, int B, int T, cudaStream_t st) {
+    ConvTcParams c;
+    memset(&c, 0, sizeof c);
+    c.x = vals_bf16; c.wt = h->keys_wt;
+    c.B = B; c.F = T; c.Cin = 768; c.taps = 1; c.Cout = 128;
+    c.act = ACT_NONE;
+    c.y_f32 = keys; c.out_f32_only = 1;
+    CK(taco_launch_conv_tc(c, h->n_sm, st));
+    h->launches++;
+    return TACO_OK;
+}
+
 // taco_decode through the dataflow kernel (decoder2.cu) -- TACO_PRECISION_BF16
 int decode_v2(TacoHandle* h, int mode, const float* memory, const int32_t* lens, int B, int T, const float* mel_targets,
               int F_tgt, int S_max, const uint8_t* prenet_masks, uint64_t philox_seed, int reset_state, int logits_only,
@@ -572,11 +587,11 @@ int decode_v2(TacoHandle* h, int mode, const float* memory, const int32_t* lens,
     WS(keys, float, "dec_keys", (size_t)B * T * 128)
     WS(vals, uint16_t, "dec2_values", (size_t)B * T * 768)
     if (reset_state) {
-        int rc = conv(h, memory, 768, (long long)T * 768, dev_w(h, std::string(MEMORY_LAYER) + "/kernel"), nullptr, nullptr, keys, 128,
-                      (long long)T * 128, nullptr, B, T, 768, 128, 1, ACT_NONE, false, 0, 0, st);
-        if (rc) return rc;
+        // values as bf16 (the per-step stream), keys = values . W_mem on tcgen05 from the same bf16 copy
         CK(taco_launch_f32_to_bf16(memory, vals, (size_t)B * T * 768, st));
         h->launches++;
+        int rc = keys_tc(h, vals, keys, B, T, st);
+        if (rc) return rc;
     }
     p.keys = keys;
     p.values = vals;
@@ -681,11 +696,11 @@ int decode_v3(TacoHandle* h, int mode, const float* memory, const int32_t* lens,
     WS(keys, float, "dec_keys", (size_t)B * T * 128)
     WS(vals, uint16_t, "dec2_values", (size_t)B * T * 768)
     if (reset_state) {
-        int rc = conv(h, memory, 768, (long long)T * 768, dev_w(h, std::string(MEMORY_LAYER) + "/kernel"), nullptr, nullptr, keys, 128,
-                      (long long)T * 128, nullptr, B, T, 768, 128, 1, ACT_NONE, false, 0, 0, st);
-        if (rc) return rc;
+        // values as bf16 (the per-step stream), keys = values . W_mem on tcgen05 from the same bf16 copy
         CK(taco_launch_f32_to_bf16(memory, vals, (size_t)B * T * 768, st));
         h->launches++;
+        int rc = keys_tc(h, vals, keys, B, T, st);
+        if (rc) return rc;
     }
     p.keys = keys;
     p.values = vals;
@@ -898,6 +913,12 @@ int taco_finalize_weights(TacoHandle* h) {
             if ((rc = pack_conv_bf16(h, w, hp.conv_kernel_size, cin, cin, hp.conv_channels, &h->enc_wt[i]))) return rc;
             cin = hp.conv_channels;
         }
+        for (int d = 0; d < 2; ++d) {
+            const Weight* w = find_w(h, std::string(d == 0 ? ENC_FW : ENC_BW) + "/kernel");
+            if ((rc = pack_conv_bf16(h, w, 1, hp.conv_channels, hp.conv_channels, 4 * hp.enc_lstm_hidden_size, &h->enc_xw_wt[d]))) return rc;
+        }
+        const Weight* wm = find_w(h, std::string(MEMORY_LAYER) + "/kernel");
+        if ((rc = pack_conv_bf16(h, wm, 1, (int)wm->shape[0], (int)wm->shape[0], hp.attention_dim, &h->keys_wt))) return rc;
     }
     h->finalized = true;
     return TACO_OK;
@@ -924,7 +945,43 @@ int taco_encode(TacoHandle* h, const int32_t* ids, const int32_t* lens, int B, i
     h->launches++;
     float *cur = bufA, *nxt = bufB;
     int cin = E, rc;
-    for (int i = 0; i < hp.conv_num_layers; ++i) {
+    const bool enc_tc = h->precision != TACO_PRECISION_FP32 && E % 64 == 0 && C % 256 == 0 && (4 * H) % 256 == 0;
+    if (enc_tc) {
+        // bf16-operand tcgen05 path: conv stack (BN folded, ReLU) bf16 -> bf16, then both LSTM input projections
+        // (+bias) with an fp32 copy for the recurrent kernel
+        const size_t wide = (size_t)(4 * H > C ? 4 * H : C);
+        WS(ta, uint16_t, "enc_tc_a", M * wide)
+        WS(tb, uint16_t, "enc_tc_b", M * wide)
+        CK(taco_launch_f32_to_bf16(bufA, ta, M * (size_t)E, st));
+        h->launches++;
+        uint16_t *c16 = ta, *n16 = tb;
+        for (int i = 0; i < hp.conv_num_layers; ++i) {
+            ConvTcParams c;
+            memset(&c, 0, sizeof c);
+            c.x = c16; c.wt = h->enc_wt[i];
+            c.B = B; c.F = T; c.Cin = cin; c.taps = hp.conv_kernel_size; c.Cout = C;
+            c.scale = h->enc_scale[i]; c.shift = h->enc_shift[i];
+            c.act = ACT_RELU;
+            c.y_bf16 = n16; c.y_stride = C;
+            CK(taco_launch_conv_tc(c, h->n_sm, st));
+            h->launches++;
+            std::swap(c16, n16);
+            cin = C;
+        }
+        for (int d = 0; d < 2; ++d) {
+            ConvTcParams c;
+            memset(&c, 0, sizeof c);
+            c.x = c16; c.wt = h->enc_xw_wt[d];
+            c.B = B; c.F = T; c.Cin = C; c.taps = 1; c.Cout = 4 * H;
+            c.shift = dev_w(h, std::string(d == 0 ? ENC_FW : ENC_BW) + "/bias");
+            c.act = ACT_NONE;
+            c.y_bf16 = n16; c.y_stride = 4 * H;          // bf16 copy is scratch; the BiLSTM reads the fp32 copy
+            c.y_f32 = xw + (size_t)d * M * 1024;
+            CK(taco_launch_conv_tc(c, h->n_sm, st));
+            h->launches++;
+        }
+    }
+    for (int i = 0; i < hp.conv_num_layers && !enc_tc; ++i) {
         rc = conv(h, cur, cin, (long long)T * cin, dev_w(h, fmt(ENC_CONV, i + 1) + "/conv1d/kernel"), h->enc_scale[i],
                   h->enc_shift[i], nxt, C, (long long)T * C, nullptr, B, T, cin, C, hp.conv_kernel_size, ACT_RELU, false, 0, 0, st);
         if (rc) return rc;
@@ -932,7 +989,7 @@ int taco_encode(TacoHandle* h, const int32_t* ids, const int32_t* lens, int B, i
         cin = C;
     }
     // hoisted input projection of both LSTM directions: xw[d] = conv_out . W[0:512] + bias
-    for (int d = 0; d < 2; ++d) {
+    for (int d = 0; d < 2 && !enc_tc; ++d) {
         const char* scope = d == 0 ? ENC_FW : ENC_BW;
         rc = conv(h, cur, C, (long long)T * C, dev_w(h, std::string(scope) + "/kernel"), nullptr,
                   dev_w(h, std::string(scope) + "/bias"), xw + (size_t)d * M * 1024, 1024, (long long)T * 1024, nullptr, B, T, C,
