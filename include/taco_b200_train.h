@@ -26,6 +26,12 @@ extern "C" {
 enum { TACO_ACT_NONE = 0, TACO_ACT_RELU = 1, TACO_ACT_TANH = 2 };
 enum { TACO_EW_COPY = 0, TACO_EW_ADD = 1, TACO_EW_MUL = 2, TACO_EW_SCALE = 3, TACO_EW_TANH = 4, TACO_EW_TANH_BWD = 5 };
 
+/* Process-wide operand precision of the THROUGHPUT-bound contractions (conv1d fwd / dgrad / wgrad, the GEMMs over all
+ * S*B rows): TACO_TRAIN_FP32 = fp32 SIMT FMA (parity mode, default); TACO_TRAIN_BF16 = operands rounded to bf16,
+ * mma.sync tensor cores, fp32 accumulation.  The per-step recurrent contractions always run in fp32. */
+enum { TACO_TRAIN_FP32 = 0, TACO_TRAIN_BF16 = 1 };
+int taco_op_set_precision(int precision);
+
 /* C[M,N] = op(A) op(B) + beta*C + bias[N]; op(A) = A[M,K] (lda) or A[K,M]^T when ta; same for B.
  * tf.layers.dense / LSTMCell / GRUCell matmuls and all their gradients. */
 int taco_op_gemm(const float* A, long long lda, const float* B, long long ldb, float* C, long long ldc, int M, int N, int K,
@@ -118,6 +124,53 @@ int taco_op_reg_loss(const float* p, const float* regw, float* out, long long n,
 int taco_op_grad_finalize(float* g, const float* p, const float* regw, float inv_world, float* sumsq, long long n, void* stream);
 int taco_op_adam_step(float* p, const float* g, float* m, float* v, const float* sumsq, float clip_norm, float lr_t, float b1,
                       float b2, float eps, long long n, void* stream);
+
+/* ---- whole time loops, launched from C (no host-language overhead per step) ------------------------------------
+ * The same per-step primitives as above, sequenced for all S decoder steps / all T encoder positions. */
+typedef struct TacoDecLoop {
+    int32_t B, T, S, D, MD, A, U2, NF, KW;   /* batch, tokens, steps, LSTM units 256, memory width 768, attention dim 128,
+                                                prenet width 256, location filters 32, location kernel 31 */
+    float zoneout;
+    uint32_t zo_keep_thresh;
+    uint64_t seed;
+    uint32_t stream1, stream2;               /* Philox streams of the cell masks of LSTM 1 / 2 (hidden masks: +1) */
+    const float *W1, *W2, *b2, *Wq;          /* [U2+MD+D,4D], [2D,4D], [4D], [D,A] */
+    const float *conv_w, *conv_b, *Wl, *va, *ba;
+    const float *keys, *values;              /* [B,T,A], [B,T,MD] */
+    const int32_t* lens;
+    const float* G1x;                        /* [S,B,4D] prenet term of the LSTM-1 gates (+bias), hoisted */
+    float *acts1, *acts2;                    /* [S,B,4D] saved gate activations */
+    float *c1new, *c2new, *h1raw, *h2raw;    /* [S,B,D] */
+    float *c1z, *h1z, *c2z, *h2z;            /* [S+1,B,D] zoned state, slot 0 = zero state */
+    float *ctx, *cum;                        /* [S+1,B,MD], [S+1,B,T] */
+    float *align, *q;                        /* [S,B,T], [S,B,A] */
+    /* backward only */
+    float *dH2, *dCtx;                       /* [S,B,D], [S,B,MD]: in = gradients from the projections, out = totals */
+    float *dG1, *dG2, *dQ;                   /* [S,B,4D], [S,B,4D], [S,B,A] out */
+    float* dkeys;                            /* [B,T,A] accumulated (caller zeroes) */
+    float *p_conv_w, *p_conv_b, *p_Wl, *p_va, *p_ba;   /* per-row partials of the attention weight gradients (caller zeroes) */
+    float* work;                             /* scratch, >= B*(9*D + MD + 2*T) floats */
+} TacoDecLoop;
+int taco_op_decoder_loop_fwd(const TacoDecLoop* p, void* stream);
+int taco_op_decoder_loop_bwd(const TacoDecLoop* p, void* stream);
+
+typedef struct TacoLstmLoop {
+    int32_t B, T, H, C, reverse;             /* one direction of the encoder BiLSTM; C = input width */
+    float zoneout;
+    uint32_t zo_keep_thresh;
+    uint64_t seed;
+    uint32_t stream_c, stream_h;
+    const float* K;                          /* [C+H, 4H] */
+    const int32_t* lens;
+    const float* xw;                         /* [B,T,4H] hoisted input projection (+bias) */
+    float *acts, *cnew, *cz, *hz;            /* [T,B,4H], [T,B,H], [T+1,B,H], [T+1,B,H] */
+    float* out;                              /* fwd: raw h scattered to out[b,pos,:H]; bwd: d(out) gathered from it */
+    long long out_sb, out_st;                /* batch / time strides of `out` (a column block of [B,T,2H] or [B,T,MD]) */
+    float *dxw, *dg;                         /* bwd: [B,T,4H] (caller zeroes), [T,B,4H] */
+    float* work;                             /* scratch, >= B*9*H floats */
+} TacoLstmLoop;
+int taco_op_lstm_loop_fwd(const TacoLstmLoop* p, void* stream);
+int taco_op_lstm_loop_bwd(const TacoLstmLoop* p, void* stream);
 
 #ifdef __cplusplus
 }

@@ -34,6 +34,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=2)
     ap.add_argument("--batch", type=int, default=32)
     ap.add_argument("--max-frames", type=int, default=1000)
+    ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"],
+                    help="bf16: large contractions on mma.sync tensor cores (bf16 operands, fp32 accumulate); fp32: SIMT parity mode")
     ap.add_argument("--cpu-sample", type=int, default=1, help="1: time the oracle on a bounded sample (N=1 only)")
     args = ap.parse_args()
     import torch
@@ -51,6 +53,7 @@ def main():
     hp = default_hparams()
     w = weights.init_weights(hp)
     tr = DataParallelTrainer(hp, w, device=local)
+    tr.ops.set_precision(args.precision)
     ids, lens, mel, stop = workload(hp, args.batch, args.max_frames, rank)
     o = tr.ops
     d_ids, d_lens, d_mel, d_stop = o.to_device(ids), o.to_device(lens), o.to_device(mel), o.to_device(stop)
@@ -99,7 +102,9 @@ def main():
         k = args.steps
         line = {"metric": "train_steps_per_sec_b%d_per_gpu" % args.batch, "value": k / (total_ms * 1e-3), "unit": "steps/s",
                 "mel_frames_per_sec": world * B * F * k / (total_ms * 1e-3), "n_gpus": world, "steps": k, "warmup": args.warmup,
-                "ms_per_step": total_ms / k, "host_wall_ms_per_step": 1e3 * wall / k, "scaling": "weak", "dtype": "f32",
+                "ms_per_step": total_ms / k, "host_wall_ms_per_step": 1e3 * wall / k, "scaling": "weak", "dtype": "bf16" if args.precision == "bf16" else "f32",
+                "precision": "bf16 operands + fp32 accumulation in the conv / all-rows contractions (mma.sync); recurrent per-step contractions, "
+                             "state, normalisation, losses, optimizer fp32" if args.precision == "bf16" else "fp32 everywhere",
                 "data": "synthetic", "config": {"workload": "C4 teacher-forced training step fwd+bwd+clip+Adam, B=%d/GPU, T=%d, F=%d (S=%d decoder steps), "
                                                 "random-init seed 45454, one all-reduce of %d fp32 gradients per step" % (B, T, F, F // 2, st.store.n)},
                 "phases_ms": {kk: v / k for kk, v in phases.items()}, "gpu_launches": launches,

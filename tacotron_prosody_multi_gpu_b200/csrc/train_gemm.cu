@@ -8,6 +8,7 @@
 // Tiles: BM x BN x BK with a TM x TN register micro-tile per thread, shared-memory double buffering.
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <cstdint>
 
 #include "../../include/taco_b200_train.h"
 
@@ -55,7 +56,8 @@ struct AConvWgrad {
 
 template <int BM, int BN, int BK, int TM, int TN, class AL, class BL>
 __global__ void __launch_bounds__((BM / TM) * (BN / TN))
-gemm_kernel(AL A, BL Bm, float* __restrict__ C, long long ldc, int M, int N, int K, float beta, const float* __restrict__ bias) {
+gemm_kernel(AL A, BL Bm, float* __restrict__ C, long long ldc, int M, int N, int K, float beta, const float* __restrict__ bias,
+            int kchunk /* K range per blockIdx.z; gridDim.z > 1 => split-K with atomic accumulation into C */) {
     constexpr int NT = (BM / TM) * (BN / TN);
     __shared__ float As[2][BK][BM + 4];
     __shared__ float Bs[2][BK][BN + 4];
@@ -106,13 +108,15 @@ gemm_kernel(AL A, BL Bm, float* __restrict__ C, long long ldc, int M, int N, int
             if (e < BK * BN) Bs[buf][kk][nn] = rb[i];
         }
     };
-    const int nk = (K + BK - 1) / BK;
-    gload(0);
+    const int kbeg = blockIdx.z * kchunk;
+    if (gridDim.z > 1) K = min(K, kbeg + kchunk);
+    const int nk = (K - kbeg + BK - 1) / BK;
+    gload(kbeg);
     sstore(0);
     __syncthreads();
     for (int it = 0; it < nk; ++it) {
         const int buf = it & 1;
-        if (it + 1 < nk) gload((it + 1) * BK);
+        if (it + 1 < nk) gload(kbeg + (it + 1) * BK);
 #pragma unroll
         for (int kk = 0; kk < BK; ++kk) {
             float a[TM], b[TN];
@@ -137,27 +141,399 @@ gemm_kernel(AL A, BL Bm, float* __restrict__ C, long long ldc, int M, int N, int
             int n = n0 + tx * TN + j;
             if (n >= N) continue;
             float v = acc[i][j];
-            if (bias) v += bias[n];
             float* c = C + (long long)m * ldc + n;
+            if (gridDim.z > 1) {             // split-K: C was zeroed (beta 0) or holds the addend (beta 1)
+                if (bias && blockIdx.z == 0) v += bias[n];
+                atomicAdd(c, v);
+                continue;
+            }
+            if (bias) v += bias[n];
             if (beta != 0.f) v += beta * *c;
             *c = v;
         }
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// bf16 tensor-core variant (TACO_TRAIN_BF16): same loader functors, operands rounded to bf16 while staged into
+// shared memory, mma.sync.m16n8k16 with fp32 accumulation.  128x128x32 tiles, 8 warps (2 x 4, warp tile 64x32),
+// ldmatrix fragment loads from k-contiguous [row][40-half] tiles (80-byte rows: conflict-free), split-K over
+// blockIdx.z with atomic accumulation for the weight-gradient shapes (few output tiles, K = S*B rows).
+// ---------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ unsigned short f2bf(float f) {   // round-to-nearest-even (finite inputs)
+    uint32_t u = __float_as_uint(f);
+    u += 0x7FFFu + ((u >> 16) & 1u);
+    return (unsigned short)(u >> 16);
+}
+
+template <class AL, class BL>
+__global__ void __launch_bounds__(256)
+gemm_mma_kernel(AL A, BL Bm, float* __restrict__ C, long long ldc, int M, int N, int K, float beta, const float* __restrict__ bias,
+                int kchunk) {
+    constexpr int BM = 128, BN = 128, BK = 32, LD = 40, NT = 256;
+    __shared__ __align__(16) unsigned short As[2][BM][LD];
+    __shared__ __align__(16) unsigned short Bs[2][BN][LD];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int wm = warp >> 2, wn = warp & 3;
+    const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
+    float acc[4][4][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+#pragma unroll
+            for (int r = 0; r < 4; ++r) acc[i][j][r] = 0.f;
+    constexpr int PER = BM * BK / NT;   // 16 elements of A and of B per thread per k-tile
+    float ra[PER], rb[PER];
+    auto gload = [&](int k0) {
+#pragma unroll
+        for (int i = 0; i < PER; ++i) {
+            int e = tid + i * NT, mm, kk;
+            if (A.k_contig) { kk = e % BK; mm = e / BK; } else { mm = e % BM; kk = e / BM; }
+            ra[i] = (m0 + mm < M && k0 + kk < K) ? A(m0 + mm, k0 + kk) : 0.f;
+        }
+#pragma unroll
+        for (int i = 0; i < PER; ++i) {
+            int e = tid + i * NT, nn, kk;
+            if (Bm.n_contig) { nn = e % BN; kk = e / BN; } else { kk = e % BK; nn = e / BK; }
+            rb[i] = (n0 + nn < N && k0 + kk < K) ? Bm(k0 + kk, n0 + nn) : 0.f;
+        }
+    };
+    auto sstore = [&](int buf) {
+#pragma unroll
+        for (int i = 0; i < PER; ++i) {
+            int e = tid + i * NT, mm, kk;
+            if (A.k_contig) { kk = e % BK; mm = e / BK; } else { mm = e % BM; kk = e / BM; }
+            As[buf][mm][kk] = f2bf(ra[i]);
+        }
+#pragma unroll
+        for (int i = 0; i < PER; ++i) {
+            int e = tid + i * NT, nn, kk;
+            if (Bm.n_contig) { nn = e % BN; kk = e / BN; } else { kk = e % BK; nn = e / BK; }
+            Bs[buf][nn][kk] = f2bf(rb[i]);
+        }
+    };
+    const int kbeg = blockIdx.z * kchunk;
+    if (gridDim.z > 1) K = min(K, kbeg + kchunk);
+    const int nk = (K - kbeg + BK - 1) / BK;
+    if (nk > 0) {
+        gload(kbeg);
+        sstore(0);
+    }
+    __syncthreads();
+    for (int it = 0; it < nk; ++it) {
+        const int buf = it & 1;
+        if (it + 1 < nk) gload(kbeg + (it + 1) * BK);
+#pragma unroll
+        for (int ks = 0; ks < BK; ks += 16) {
+            uint32_t af[4][4], bfr[4][2];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const uint32_t addr = smem_u32(&As[buf][wm * 64 + i * 16 + (lane & 15)][ks + (lane >> 4) * 8]);
+                asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+                             : "=r"(af[i][0]), "=r"(af[i][1]), "=r"(af[i][2]), "=r"(af[i][3]) : "r"(addr));
+            }
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {   // two n-tiles per ldmatrix.x4
+                const int id = lane >> 3;
+                const uint32_t addr = smem_u32(&Bs[buf][wn * 32 + j * 16 + (id >> 1) * 8 + (lane & 7)][ks + (id & 1) * 8]);
+                asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+                             : "=r"(bfr[2 * j][0]), "=r"(bfr[2 * j][1]), "=r"(bfr[2 * j + 1][0]), "=r"(bfr[2 * j + 1][1]) : "r"(addr));
+            }
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                                 : "+f"(acc[i][j][0]), "+f"(acc[i][j][1]), "+f"(acc[i][j][2]), "+f"(acc[i][j][3])
+                                 : "r"(af[i][0]), "r"(af[i][1]), "r"(af[i][2]), "r"(af[i][3]), "r"(bfr[j][0]), "r"(bfr[j][1]));
+        }
+        if (it + 1 < nk) sstore(buf ^ 1);
+        __syncthreads();
+    }
+    const int g = lane >> 2, tq = lane & 3;
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+                const int m = m0 + wm * 64 + i * 16 + g + (r >> 1) * 8;
+                const int n = n0 + wn * 32 + j * 8 + tq * 2 + (r & 1);
+                if (m >= M || n >= N) continue;
+                float v = acc[i][j][r];
+                float* c = C + (long long)m * ldc + n;
+                if (gridDim.z > 1) {
+                    if (bias && blockIdx.z == 0) v += bias[n];
+                    atomicAdd(c, v);
+                    continue;
+                }
+                if (bias) v += bias[n];
+                if (beta != 0.f) v += beta * *c;
+                *c = v;
+            }
+}
+
+int g_train_precision = 0;   // TACO_TRAIN_FP32 / TACO_TRAIN_BF16 (taco_op_set_precision)
+
+template <class AL, class BL>
+int launch_gemm_mma(AL A, BL Bm, float* C, long long ldc, int M, int N, int K, float beta, const float* bias, cudaStream_t st) {
+    dim3 grid((N + 127) / 128, (M + 127) / 128, 1);
+    int kchunk = K;
+    const int ctas = grid.x * grid.y;
+    if ((beta == 0.f || beta == 1.f) && ctas < 148 && K >= 1024) {
+        int splits = (296 + ctas - 1) / ctas;
+        if (splits > K / 256) splits = K / 256;
+        if (splits > 1) {
+            kchunk = ((K + splits - 1) / splits + 31) / 32 * 32;
+            grid.z = (K + kchunk - 1) / kchunk;
+            if (grid.z > 1 && beta == 0.f &&
+                cudaMemset2DAsync(C, (size_t)ldc * sizeof(float), 0, (size_t)N * sizeof(float), (size_t)M, st) != cudaSuccess)
+                return -3;
+        }
+    }
+    gemm_mma_kernel<AL, BL><<<grid, 256, 0, st>>>(A, Bm, C, ldc, M, N, K, beta, bias, kchunk);
+    return cudaGetLastError() == cudaSuccess ? 0 : -3;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Vectorised bf16 tensor-core kernel: operands are fetched as 8-element segments along their CONTIGUOUS axis
+// (two 16-byte loads, index arithmetic once per segment) and staged in shared memory in their natural
+// orientation; fragments of an operand whose contiguous axis is m / n (not k) are read with ldmatrix.trans.
+// Requires every contiguous extent to be a multiple of 8 (dispatch falls back to gemm_mma_kernel otherwise).
+// ---------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void ld8(const float* p, float v[8]) {
+    if ((reinterpret_cast<uintptr_t>(p) & 15) == 0) {
+        float4 a = *reinterpret_cast<const float4*>(p), b = *reinterpret_cast<const float4*>(p + 4);
+        v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+    } else {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) v[i] = p[i];
+    }
+}
+__device__ __forceinline__ void zero8(float v[8]) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) v[i] = 0.f;
+}
+// A operands: load8(m, k, v) -- K_CONTIG: v[i] = A(m, k+i);  else: v[i] = A(m+i, k).   (in-range m, k guaranteed)
+struct VAPlainK { static constexpr bool K_CONTIG = true; const float* p; long long ld;
+    __device__ __forceinline__ void load8(int m, int k, float v[8]) const { ld8(p + (long long)m * ld + k, v); } };
+struct VAPlainM { static constexpr bool K_CONTIG = false; const float* p; long long ld;      // stored [K][M]
+    __device__ __forceinline__ void load8(int m, int k, float v[8]) const { ld8(p + (long long)k * ld + m, v); } };
+struct VAConvFwd { static constexpr bool K_CONTIG = true; const float* x; int T, Ci, left;
+    __device__ __forceinline__ void load8(int m, int k, float v[8]) const {
+        int b = m / T, t = m - b * T, j = k / Ci, ci = k - j * Ci, tt = t + j - left;
+        if (tt < 0 || tt >= T) { zero8(v); return; }
+        ld8(x + ((long long)b * T + tt) * Ci + ci, v);
+    } };
+struct VAConvDgrad { static constexpr bool K_CONTIG = true; const float* dy; int T, Co, left;
+    __device__ __forceinline__ void load8(int m, int k, float v[8]) const {
+        int b = m / T, t = m - b * T, j = k / Co, co = k - j * Co, tt = t - j + left;
+        if (tt < 0 || tt >= T) { zero8(v); return; }
+        ld8(dy + ((long long)b * T + tt) * Co + co, v);
+    } };
+struct VAConvWgrad { static constexpr bool K_CONTIG = false; const float* x; int T, Ci, left;   // m = (j, ci), k = (b, t)
+    __device__ __forceinline__ void load8(int m, int k, float v[8]) const {
+        int j = m / Ci, ci = m - j * Ci, b = k / T, t = k - b * T, tt = t + j - left;
+        if (tt < 0 || tt >= T) { zero8(v); return; }
+        ld8(x + ((long long)b * T + tt) * Ci + ci, v);
+    } };
+// B operands: load8(k, n, v) -- K_CONTIG: v[i] = B(k+i, n);  else: v[i] = B(k, n+i)
+struct VBPlainN { static constexpr bool K_CONTIG = false; const float* p; long long ld;     // stored [K][N]
+    __device__ __forceinline__ void load8(int k, int n, float v[8]) const { ld8(p + (long long)k * ld + n, v); } };
+struct VBPlainK { static constexpr bool K_CONTIG = true; const float* p; long long ld;      // stored [N][K]
+    __device__ __forceinline__ void load8(int k, int n, float v[8]) const { ld8(p + (long long)n * ld + k, v); } };
+struct VBConvDgrad { static constexpr bool K_CONTIG = true; const float* w; int Ci, Co;      // k = (j, co), n = ci
+    __device__ __forceinline__ void load8(int k, int n, float v[8]) const {
+        int j = k / Co, co = k - j * Co;
+        ld8(w + ((long long)j * Ci + n) * Co + co, v);
+    } };
+
+__device__ __forceinline__ uint4 pack8(const float v[8]) {
+    return make_uint4((uint32_t)f2bf(v[0]) | ((uint32_t)f2bf(v[1]) << 16), (uint32_t)f2bf(v[2]) | ((uint32_t)f2bf(v[3]) << 16),
+                      (uint32_t)f2bf(v[4]) | ((uint32_t)f2bf(v[5]) << 16), (uint32_t)f2bf(v[6]) | ((uint32_t)f2bf(v[7]) << 16));
+}
+
+template <class AL, class BL>
+__global__ void __launch_bounds__(256)
+gemm_mma2_kernel(AL A, BL Bm, float* __restrict__ C, long long ldc, int M, int N, int K, float beta, const float* __restrict__ bias,
+                 int kchunk) {
+    constexpr int BM = 128, BN = 128, BK = 32;
+    constexpr int LDK = BK + 8;     // halves per row of a k-contiguous tile  [rows][LDK]   (80 B rows)
+    constexpr int LDT = BM + 8;     // halves per row of a transposed tile    [BK][LDT]     (272 B rows)
+    constexpr int TILE = BM * LDK > BK * LDT ? BM * LDK : BK * LDT;
+    __shared__ __align__(16) unsigned short As[2][TILE];
+    __shared__ __align__(16) unsigned short Bs[2][TILE];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int wm = warp >> 2, wn = warp & 3;
+    const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
+    float acc[4][4][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+#pragma unroll
+            for (int r = 0; r < 4; ++r) acc[i][j][r] = 0.f;
+    // segment ownership: k-contiguous tile: row = tid>>2 (+64), k offset 8*(tid&3); transposed tile: k row = tid>>4 (+16), offset 8*(tid&15)
+    float ra[2][8], rb[2][8];
+    auto gload = [&](int k0) {
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            if (AL::K_CONTIG) {
+                const int m = m0 + (tid >> 2) + 64 * h, k = k0 + 8 * (tid & 3);
+                if (m < M && k < K) A.load8(m, k, ra[h]); else zero8(ra[h]);
+            } else {
+                const int k = k0 + (tid >> 4) + 16 * h, m = m0 + 8 * (tid & 15);
+                if (m < M && k < K) A.load8(m, k, ra[h]); else zero8(ra[h]);
+            }
+            if (BL::K_CONTIG) {
+                const int n = n0 + (tid >> 2) + 64 * h, k = k0 + 8 * (tid & 3);
+                if (n < N && k < K) Bm.load8(k, n, rb[h]); else zero8(rb[h]);
+            } else {
+                const int k = k0 + (tid >> 4) + 16 * h, n = n0 + 8 * (tid & 15);
+                if (n < N && k < K) Bm.load8(k, n, rb[h]); else zero8(rb[h]);
+            }
+        }
+    };
+    auto sstore = [&](int buf) {
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            if (AL::K_CONTIG) *reinterpret_cast<uint4*>(&As[buf][((tid >> 2) + 64 * h) * LDK + 8 * (tid & 3)]) = pack8(ra[h]);
+            else *reinterpret_cast<uint4*>(&As[buf][((tid >> 4) + 16 * h) * LDT + 8 * (tid & 15)]) = pack8(ra[h]);
+            if (BL::K_CONTIG) *reinterpret_cast<uint4*>(&Bs[buf][((tid >> 2) + 64 * h) * LDK + 8 * (tid & 3)]) = pack8(rb[h]);
+            else *reinterpret_cast<uint4*>(&Bs[buf][((tid >> 4) + 16 * h) * LDT + 8 * (tid & 15)]) = pack8(rb[h]);
+        }
+    };
+    const int kbeg = blockIdx.z * kchunk;
+    if (gridDim.z > 1) K = min(K, kbeg + kchunk);
+    const int nk = (K - kbeg + BK - 1) / BK;
+    if (nk > 0) {
+        gload(kbeg);
+        sstore(0);
+    }
+    __syncthreads();
+    const int id = lane >> 3, l7 = lane & 7;
+    for (int it = 0; it < nk; ++it) {
+        const int buf = it & 1;
+        if (it + 1 < nk) gload(kbeg + (it + 1) * BK);
+#pragma unroll
+        for (int ks = 0; ks < BK; ks += 16) {
+            uint32_t af[4][4], bfr[4][2];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int mb = wm * 64 + i * 16;
+                if (AL::K_CONTIG) {
+                    const uint32_t addr = smem_u32(&As[buf][(mb + (lane & 15)) * LDK + ks + (lane >> 4) * 8]);
+                    asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+                                 : "=r"(af[i][0]), "=r"(af[i][1]), "=r"(af[i][2]), "=r"(af[i][3]) : "r"(addr));
+                } else {   // stored [k][m]: matrices (m lo,k lo) (m hi,k lo) (m lo,k hi) (m hi,k hi), transposed on load
+                    const uint32_t addr = smem_u32(&As[buf][(ks + (id >> 1) * 8 + l7) * LDT + mb + (id & 1) * 8]);
+                    asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+                                 : "=r"(af[i][0]), "=r"(af[i][1]), "=r"(af[i][2]), "=r"(af[i][3]) : "r"(addr));
+                }
+            }
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {   // two n-tiles per ldmatrix.x4: (nt0,k lo) (nt0,k hi) (nt1,k lo) (nt1,k hi)
+                const int nb = wn * 32 + j * 16;
+                if (BL::K_CONTIG) {
+                    const uint32_t addr = smem_u32(&Bs[buf][(nb + (id >> 1) * 8 + l7) * LDK + ks + (id & 1) * 8]);
+                    asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+                                 : "=r"(bfr[2 * j][0]), "=r"(bfr[2 * j][1]), "=r"(bfr[2 * j + 1][0]), "=r"(bfr[2 * j + 1][1]) : "r"(addr));
+                } else {   // stored [k][n]
+                    const uint32_t addr = smem_u32(&Bs[buf][(ks + (id & 1) * 8 + l7) * LDT + nb + (id >> 1) * 8]);
+                    asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+                                 : "=r"(bfr[2 * j][0]), "=r"(bfr[2 * j][1]), "=r"(bfr[2 * j + 1][0]), "=r"(bfr[2 * j + 1][1]) : "r"(addr));
+                }
+            }
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                                 : "+f"(acc[i][j][0]), "+f"(acc[i][j][1]), "+f"(acc[i][j][2]), "+f"(acc[i][j][3])
+                                 : "r"(af[i][0]), "r"(af[i][1]), "r"(af[i][2]), "r"(af[i][3]), "r"(bfr[j][0]), "r"(bfr[j][1]));
+        }
+        if (it + 1 < nk) sstore(buf ^ 1);
+        __syncthreads();
+    }
+    const int g = lane >> 2, tq = lane & 3;
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+                const int m = m0 + wm * 64 + i * 16 + g + (r >> 1) * 8;
+                const int n = n0 + wn * 32 + j * 8 + tq * 2 + (r & 1);
+                if (m >= M || n >= N) continue;
+                float v = acc[i][j][r];
+                float* c = C + (long long)m * ldc + n;
+                if (gridDim.z > 1) {
+                    if (bias && blockIdx.z == 0) v += bias[n];
+                    atomicAdd(c, v);
+                    continue;
+                }
+                if (bias) v += bias[n];
+                if (beta != 0.f) v += beta * *c;
+                *c = v;
+            }
+}
+
+template <class AL, class BL>
+int launch_gemm_mma2(AL A, BL Bm, float* C, long long ldc, int M, int N, int K, float beta, const float* bias, cudaStream_t st) {
+    dim3 grid((N + 127) / 128, (M + 127) / 128, 1);
+    int kchunk = K;
+    const int ctas = grid.x * grid.y;
+    if ((beta == 0.f || beta == 1.f) && ctas < 148 && K >= 1024) {
+        int splits = (296 + ctas - 1) / ctas;
+        if (splits > K / 256) splits = K / 256;
+        if (splits > 1) {
+            kchunk = ((K + splits - 1) / splits + 31) / 32 * 32;
+            grid.z = (K + kchunk - 1) / kchunk;
+            if (grid.z > 1 && beta == 0.f &&
+                cudaMemset2DAsync(C, (size_t)ldc * sizeof(float), 0, (size_t)N * sizeof(float), (size_t)M, st) != cudaSuccess)
+                return -3;
+        }
+    }
+    gemm_mma2_kernel<AL, BL><<<grid, 256, 0, st>>>(A, Bm, C, ldc, M, N, K, beta, bias, kchunk);
+    return cudaGetLastError() == cudaSuccess ? 0 : -3;
+}
+inline bool use_mma(int M, int N, int K) {
+    return g_train_precision == TACO_TRAIN_BF16 && (long long)M * N >= 64LL * 64 * 64 && (long long)M * N * K >= (1LL << 24);
+}
+
 template <class AL, class BL>
 int launch_gemm(AL A, BL Bm, float* C, long long ldc, int M, int N, int K, float beta, const float* bias, cudaStream_t st) {
     if (M <= 0 || N <= 0) return 0;
     const long long work = (long long)M * N;
+    // bf16 tensor cores for the throughput-bound contractions; the skinny per-step ones stay fp32 (latency-bound)
+    if (g_train_precision == TACO_TRAIN_BF16 && work >= 64LL * 64 * 64 && (long long)M * N * K >= (1LL << 24))
+        return launch_gemm_mma(A, Bm, C, ldc, M, N, K, beta, bias, st);
     if (work >= 128LL * 128 * 96) {          // enough 128x128 tiles to fill the 148 SMs
         dim3 grid((N + 127) / 128, (M + 127) / 128);
-        gemm_kernel<128, 128, 8, 8, 8, AL, BL><<<grid, 256, 0, st>>>(A, Bm, C, ldc, M, N, K, beta, bias);
+        gemm_kernel<128, 128, 8, 8, 8, AL, BL><<<grid, 256, 0, st>>>(A, Bm, C, ldc, M, N, K, beta, bias, K);
     } else if (work >= 64LL * 64 * 64) {
         dim3 grid((N + 63) / 64, (M + 63) / 64);
-        gemm_kernel<64, 64, 16, 4, 4, AL, BL><<<grid, 256, 0, st>>>(A, Bm, C, ldc, M, N, K, beta, bias);
+        gemm_kernel<64, 64, 16, 4, 4, AL, BL><<<grid, 256, 0, st>>>(A, Bm, C, ldc, M, N, K, beta, bias, K);
     } else {
-        dim3 grid((N + 31) / 32, (M + 31) / 32);
-        gemm_kernel<32, 32, 32, 2, 2, AL, BL><<<grid, 256, 0, st>>>(A, Bm, C, ldc, M, N, K, beta, bias);
+        // skinny per-step contractions (M = batch): latency-bound on the K loop -> split K over up to 8 CTAs
+        dim3 grid((N + 31) / 32, (M + 31) / 32, 1);
+        int kchunk = K;
+        const int ctas = grid.x * grid.y;
+        if ((beta == 0.f || beta == 1.f) && K >= 256 && ctas < 148) {
+            int splits = (296 + ctas - 1) / ctas;
+            if (splits > 8) splits = 8;
+            if (splits > K / 128) splits = K / 128;
+            if (splits > 1) {
+                kchunk = ((K + splits - 1) / splits + 31) / 32 * 32;
+                grid.z = (K + kchunk - 1) / kchunk;
+                if (grid.z > 1 && beta == 0.f &&
+                    cudaMemset2DAsync(C, (size_t)ldc * sizeof(float), 0, (size_t)N * sizeof(float), (size_t)M, st) != cudaSuccess)
+                    return -3;
+            }
+        }
+        gemm_kernel<32, 32, 32, 2, 2, AL, BL><<<grid, 256, 0, st>>>(A, Bm, C, ldc, M, N, K, beta, bias, kchunk);
     }
     return cudaGetLastError() == cudaSuccess ? 0 : -3;
 }
@@ -166,9 +542,22 @@ int launch_gemm(AL A, BL Bm, float* C, long long ldc, int M, int N, int K, float
 
 extern "C" {
 
+int taco_op_set_precision(int precision) {
+    if (precision != TACO_TRAIN_FP32 && precision != TACO_TRAIN_BF16) return -1;
+    g_train_precision = precision;
+    return 0;
+}
+
 int taco_op_gemm(const float* A, long long lda, const float* B, long long ldb, float* C, long long ldc, int M, int N, int K,
                  int ta, int tb, float beta, const float* bias, void* stream) {
     if (!A || !B || !C || K < 0) return -1;
+    if (use_mma(M, N, K) && K % 8 == 0 && M % 8 == 0 && N % 8 == 0 && lda % 4 == 0 && ldb % 4 == 0) {
+        cudaStream_t st = (cudaStream_t)stream;
+        if (!ta && !tb) return launch_gemm_mma2(VAPlainK{A, lda}, VBPlainN{B, ldb}, C, ldc, M, N, K, beta, bias, st);
+        if (ta && !tb) return launch_gemm_mma2(VAPlainM{A, lda}, VBPlainN{B, ldb}, C, ldc, M, N, K, beta, bias, st);
+        if (!ta && tb) return launch_gemm_mma2(VAPlainK{A, lda}, VBPlainK{B, ldb}, C, ldc, M, N, K, beta, bias, st);
+        return launch_gemm_mma2(VAPlainM{A, lda}, VBPlainK{B, ldb}, C, ldc, M, N, K, beta, bias, st);
+    }
     APlain a{A, ta ? 1 : lda, ta ? lda : 1, ta ? 0 : 1};
     BPlain b{B, tb ? 1 : ldb, tb ? ldb : 1, tb ? 0 : 1};
     return launch_gemm(a, b, C, ldc, M, N, K, beta, bias, (cudaStream_t)stream);
@@ -176,6 +565,8 @@ int taco_op_gemm(const float* A, long long lda, const float* B, long long ldb, f
 
 int taco_op_conv1d_fwd(const float* x, const float* w, const float* bias, float* y, int B, int T, int Ci, int Co, int k, void* stream) {
     if (!x || !w || !y) return -1;
+    if (use_mma(B * T, Co, k * Ci) && Ci % 8 == 0 && Co % 8 == 0)
+        return launch_gemm_mma2(VAConvFwd{x, T, Ci, (k - 1) / 2}, VBPlainN{w, Co}, y, Co, B * T, Co, k * Ci, 0.f, bias, (cudaStream_t)stream);
     AConvFwd a{x, T, Ci, (k - 1) / 2, 1};
     BPlain b{w, Co, 1, 1};
     return launch_gemm(a, b, y, Co, B * T, Co, k * Ci, 0.f, bias, (cudaStream_t)stream);
@@ -183,6 +574,9 @@ int taco_op_conv1d_fwd(const float* x, const float* w, const float* bias, float*
 
 int taco_op_conv1d_dgrad(const float* dy, const float* w, float* dx, int B, int T, int Ci, int Co, int k, void* stream) {
     if (!dy || !w || !dx) return -1;
+    if (use_mma(B * T, Ci, k * Co) && Ci % 8 == 0 && Co % 8 == 0)
+        return launch_gemm_mma2(VAConvDgrad{dy, T, Co, (k - 1) / 2}, VBConvDgrad{w, Ci, Co}, dx, Ci, B * T, Ci, k * Co, 0.f, nullptr,
+                                (cudaStream_t)stream);
     AConvDgrad a{dy, T, Co, (k - 1) / 2, 1};
     BConvDgrad b{w, Ci, Co, 0};
     return launch_gemm(a, b, dx, Ci, B * T, Ci, k * Co, 0.f, nullptr, (cudaStream_t)stream);
@@ -190,6 +584,9 @@ int taco_op_conv1d_dgrad(const float* dy, const float* w, float* dx, int B, int 
 
 int taco_op_conv1d_wgrad(const float* x, const float* dy, float* dw, int B, int T, int Ci, int Co, int k, void* stream) {
     if (!x || !dy || !dw) return -1;
+    if (use_mma(k * Ci, Co, B * T) && Ci % 8 == 0 && Co % 8 == 0 && (B * T) % 8 == 0)
+        return launch_gemm_mma2(VAConvWgrad{x, T, Ci, (k - 1) / 2}, VBPlainN{dy, Co}, dw, Co, k * Ci, Co, B * T, 0.f, nullptr,
+                                (cudaStream_t)stream);
     AConvWgrad a{x, T, Ci, (k - 1) / 2, 0};
     BPlain b{dy, Co, 1, 1};
     return launch_gemm(a, b, dw, Co, k * Ci, Co, B * T, 0.f, nullptr, (cudaStream_t)stream);

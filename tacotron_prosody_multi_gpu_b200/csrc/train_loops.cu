@@ -1,0 +1,124 @@
+// train_loops.cu -- the time loops of the training step sequenced from C: all S decoder steps (forward and
+// BPTT) and all T positions of one encoder-LSTM direction.  Same primitives and the same order as the host
+// composition in train/step.py (which stays the readable restatement and is what the CPU tests check); moving the
+// loops here removes ~10 000 host-language launches per step.
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/taco_b200_train.h"
+
+#define OK(x) do { int rc_ = (x); if (rc_) return rc_; } while (0)
+
+extern "C" {
+
+int taco_op_decoder_loop_fwd(const TacoDecLoop* p, void* st) {
+    if (!p || !p->W1 || !p->W2 || !p->G1x || !p->acts1 || !p->acts2 || !p->ctx || !p->cum) return -1;
+    const int B = p->B, T = p->T, S = p->S, D = p->D, MD = p->MD, A = p->A, U2 = p->U2, G = 4 * p->D;
+    const float* W1c = p->W1 + (size_t)U2 * G;          // rows of the context
+    const float* W1h = p->W1 + (size_t)(U2 + MD) * G;   // rows of h1
+    const float* W2h = p->W2 + (size_t)D * G;
+    for (int s = 0; s < S; ++s) {
+        const size_t oD = (size_t)s * B * D, oG = (size_t)s * B * G, nD = oD + (size_t)B * D;
+        float* a1 = p->acts1 + oG;
+        float* a2 = p->acts2 + oG;
+        OK(taco_op_gemm(p->ctx + (size_t)s * B * MD, MD, W1c, G, a1, G, B, G, MD, 0, 0, 0.f, nullptr, st));
+        OK(taco_op_gemm(p->h1z + oD, D, W1h, G, a1, G, B, G, D, 0, 0, 1.f, nullptr, st));
+        OK(taco_op_lstm_fwd(a1, p->G1x + oG, nullptr, p->c1z + oD, p->h1z + oD, nullptr, 0, p->zoneout, 1, p->zo_keep_thresh, p->seed,
+                            p->stream1, p->stream1 + 1, s * B, p->c1new + oD, p->c1z + nD, p->h1raw + oD, p->h1z + nD, B, D, st));
+        OK(taco_op_gemm(p->h1raw + oD, D, p->W2, G, a2, G, B, G, D, 0, 0, 0.f, nullptr, st));
+        OK(taco_op_gemm(p->h2z + oD, D, W2h, G, a2, G, B, G, D, 0, 0, 1.f, nullptr, st));
+        OK(taco_op_lstm_fwd(a2, nullptr, p->b2, p->c2z + oD, p->h2z + oD, nullptr, 0, p->zoneout, 1, p->zo_keep_thresh, p->seed,
+                            p->stream2, p->stream2 + 1, s * B, p->c2new + oD, p->c2z + nD, p->h2raw + oD, p->h2z + nD, B, D, st));
+        float* q = p->q + (size_t)s * B * A;
+        OK(taco_op_gemm(p->h2raw + oD, D, p->Wq, A, q, A, B, A, D, 0, 0, 0.f, nullptr, st));
+        OK(taco_op_attn_fwd(q, p->cum + (size_t)s * B * T, p->keys, p->values, p->lens, p->conv_w, p->conv_b, p->Wl, p->va, p->ba,
+                            p->align + (size_t)s * B * T, p->cum + (size_t)(s + 1) * B * T, p->ctx + (size_t)(s + 1) * B * MD, B, T, A, MD,
+                            p->NF, p->KW, st));
+    }
+    return 0;
+}
+
+int taco_op_decoder_loop_bwd(const TacoDecLoop* p, void* st) {
+    if (!p || !p->dH2 || !p->dCtx || !p->dG1 || !p->dG2 || !p->dQ || !p->dkeys || !p->work) return -1;
+    const int B = p->B, T = p->T, S = p->S, D = p->D, MD = p->MD, A = p->A, U2 = p->U2, G = 4 * p->D;
+    const float* W1c = p->W1 + (size_t)U2 * G;
+    const float* W1h = p->W1 + (size_t)(U2 + MD) * G;
+    const float* W2h = p->W2 + (size_t)D * G;
+    const size_t BD = (size_t)B * D;
+    float* w = p->work;
+    if (cudaMemsetAsync(w, 0, sizeof(float) * ((size_t)B * (9 * D + MD + 2 * T)), (cudaStream_t)st) != cudaSuccess) return -3;
+    float *dc1 = w, *dh1z = w + BD, *dc2 = w + 2 * BD, *dh2z = w + 3 * BD;
+    float *dc1n = w + 4 * BD, *dh1zn = w + 5 * BD, *dc2n = w + 6 * BD, *dh2zn = w + 7 * BD;
+    float* dh1raw = w + 8 * BD;
+    float* dctx_carry = w + 9 * BD;
+    float* dcum = dctx_carry + (size_t)B * MD;
+    float* dcum_n = dcum + (size_t)B * T;
+    for (int s = S - 1; s >= 0; --s) {
+        const size_t oD = (size_t)s * B * D, oG = (size_t)s * B * G;
+        float* dctx = p->dCtx + (size_t)s * B * MD;
+        OK(taco_op_ew(TACO_EW_ADD, dctx, dctx, dctx_carry, 1.f, (long long)B * MD, st));
+        float* dq = p->dQ + (size_t)s * B * A;
+        OK(taco_op_attn_bwd(dctx, dcum, p->q + (size_t)s * B * A, p->cum + (size_t)s * B * T, p->align + (size_t)s * B * T, p->keys,
+                            p->values, p->lens, p->conv_w, p->conv_b, p->Wl, p->va, p->ba, dq, dcum_n, p->dkeys, p->p_conv_w,
+                            p->p_conv_b, p->p_Wl, p->p_va, p->p_ba, B, T, A, MD, p->NF, p->KW, st));
+        { float* t_ = dcum; dcum = dcum_n; dcum_n = t_; }
+        float* dh2 = p->dH2 + oD;
+        OK(taco_op_gemm(dq, A, p->Wq, A, dh2, D, B, D, A, 0, 1, 1.f, nullptr, st));
+        OK(taco_op_lstm_bwd(p->acts2 + oG, p->c2z + oD, p->h2z + oD, p->c2new + oD, nullptr, 0, p->zoneout, 1, p->zo_keep_thresh, p->seed,
+                            p->stream2, p->stream2 + 1, s * B, dh2, dc2, dh2z, p->dG2 + oG, dc2n, dh2zn, B, D, st));
+        OK(taco_op_gemm(p->dG2 + oG, G, p->W2, G, dh1raw, D, B, D, G, 0, 1, 0.f, nullptr, st));
+        OK(taco_op_gemm(p->dG2 + oG, G, W2h, G, dh2zn, D, B, D, G, 0, 1, 1.f, nullptr, st));
+        OK(taco_op_lstm_bwd(p->acts1 + oG, p->c1z + oD, p->h1z + oD, p->c1new + oD, nullptr, 0, p->zoneout, 1, p->zo_keep_thresh, p->seed,
+                            p->stream1, p->stream1 + 1, s * B, dh1raw, dc1, dh1z, p->dG1 + oG, dc1n, dh1zn, B, D, st));
+        OK(taco_op_gemm(p->dG1 + oG, G, W1c, G, dctx_carry, MD, B, MD, G, 0, 1, 0.f, nullptr, st));
+        OK(taco_op_gemm(p->dG1 + oG, G, W1h, G, dh1zn, D, B, D, G, 0, 1, 1.f, nullptr, st));
+        float* t_;
+        t_ = dc1; dc1 = dc1n; dc1n = t_;
+        t_ = dh1z; dh1z = dh1zn; dh1zn = t_;
+        t_ = dc2; dc2 = dc2n; dc2n = t_;
+        t_ = dh2z; dh2z = dh2zn; dh2zn = t_;
+    }
+    return 0;
+}
+
+int taco_op_lstm_loop_fwd(const TacoLstmLoop* p, void* st) {
+    if (!p || !p->K || !p->lens || !p->xw || !p->acts || !p->cnew || !p->cz || !p->hz || !p->out || !p->work) return -1;
+    const int B = p->B, T = p->T, H = p->H, G = 4 * p->H;
+    const float* Kh = p->K + (size_t)p->C * G;
+    float* pre = p->work;
+    float* hraw = p->work + (size_t)B * G;
+    for (int s = 0; s < T; ++s) {
+        const size_t oH = (size_t)s * B * H, nH = oH + (size_t)B * H;
+        float* a = p->acts + (size_t)s * B * G;
+        OK(taco_op_gather_rows(p->xw, (long long)T * G, G, p->lens, s, p->reverse, pre, B, G, st));
+        OK(taco_op_gemm(p->hz + oH, H, Kh, G, a, G, B, G, H, 0, 0, 0.f, nullptr, st));
+        OK(taco_op_lstm_fwd(a, pre, nullptr, p->cz + oH, p->hz + oH, p->lens, s, p->zoneout, 1, p->zo_keep_thresh, p->seed, p->stream_c,
+                            p->stream_h, s * B, p->cnew + oH, p->cz + nH, hraw, p->hz + nH, B, H, st));
+        OK(taco_op_scatter_rows(hraw, p->lens, s, p->reverse, p->out, p->out_sb, p->out_st, B, H, st));
+    }
+    return 0;
+}
+
+int taco_op_lstm_loop_bwd(const TacoLstmLoop* p, void* st) {
+    if (!p || !p->K || !p->lens || !p->acts || !p->cnew || !p->cz || !p->hz || !p->out || !p->dxw || !p->dg || !p->work) return -1;
+    const int B = p->B, T = p->T, H = p->H, G = 4 * p->H;
+    const float* Kh = p->K + (size_t)p->C * G;
+    const size_t BH = (size_t)B * H;
+    if (cudaMemsetAsync(p->work, 0, sizeof(float) * 5 * BH, (cudaStream_t)st) != cudaSuccess) return -3;
+    float *dc = p->work, *dh = p->work + BH, *dcn = p->work + 2 * BH, *dhn = p->work + 3 * BH, *d_hraw = p->work + 4 * BH;
+    for (int s = T - 1; s >= 0; --s) {
+        const size_t oH = (size_t)s * B * H;
+        float* dg = p->dg + (size_t)s * B * G;
+        OK(taco_op_gather_rows(p->out, p->out_sb, p->out_st, p->lens, s, p->reverse, d_hraw, B, H, st));
+        OK(taco_op_lstm_bwd(p->acts + (size_t)s * B * G, p->cz + oH, p->hz + oH, p->cnew + oH, p->lens, s, p->zoneout, 1, p->zo_keep_thresh,
+                            p->seed, p->stream_c, p->stream_h, s * B, d_hraw, dc, dh, dg, dcn, dhn, B, H, st));
+        OK(taco_op_gemm(dg, G, Kh, G, dhn, H, B, H, G, 0, 1, 1.f, nullptr, st));
+        OK(taco_op_scatter_rows(dg, p->lens, s, p->reverse, p->dxw, (long long)T * G, G, B, G, st));
+        float* t_;
+        t_ = dc; dc = dcn; dcn = t_;
+        t_ = dh; dh = dhn; dhn = t_;
+    }
+    return 0;
+}
+
+}  // extern "C"

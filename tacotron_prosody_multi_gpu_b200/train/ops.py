@@ -281,3 +281,79 @@ class CudaOps(object):
     def adam_step(self, p, g, m, v, sumsq, clip_norm, lr_t, b1, b2, eps):
         self._call("taco_op_adam_step", _c(p), _c(g), _c(m), _c(v), _c(sumsq), float(clip_norm), float(lr_t), float(b1), float(b2),
                    float(eps), p.numel())
+
+
+# ---------------------------------------------------------------------- whole time loops sequenced in C (train_loops.cu)
+class TacoDecLoop(C.Structure):
+    _fields_ = ([(n, C.c_int32) for n in ("B", "T", "S", "D", "MD", "A", "U2", "NF", "KW")] +
+                [("zoneout", C.c_float), ("zo_keep_thresh", C.c_uint32), ("seed", C.c_uint64), ("stream1", C.c_uint32),
+                 ("stream2", C.c_uint32)] +
+                [(n, C.c_void_p) for n in ("W1", "W2", "b2", "Wq", "conv_w", "conv_b", "Wl", "va", "ba", "keys", "values", "lens", "G1x",
+                                           "acts1", "acts2", "c1new", "c2new", "h1raw", "h2raw", "c1z", "h1z", "c2z", "h2z", "ctx", "cum",
+                                           "align", "q", "dH2", "dCtx", "dG1", "dG2", "dQ", "dkeys", "p_conv_w", "p_conv_b", "p_Wl",
+                                           "p_va", "p_ba", "work")])
+
+
+class TacoLstmLoop(C.Structure):
+    _fields_ = ([(n, C.c_int32) for n in ("B", "T", "H", "C", "reverse")] +
+                [("zoneout", C.c_float), ("zo_keep_thresh", C.c_uint32), ("seed", C.c_uint64), ("stream_c", C.c_uint32),
+                 ("stream_h", C.c_uint32)] +
+                [(n, C.c_void_p) for n in ("K", "lens", "xw", "acts", "cnew", "cz", "hz", "out")] +
+                [("out_sb", C.c_longlong), ("out_st", C.c_longlong)] +
+                [(n, C.c_void_p) for n in ("dxw", "dg", "work")])
+
+
+LOOP_SYMBOLS = ("taco_op_decoder_loop_fwd", "taco_op_decoder_loop_bwd", "taco_op_lstm_loop_fwd", "taco_op_lstm_loop_bwd")
+
+
+def _fill(struct, ints, ptrs):
+    for k, v in ints.items():
+        setattr(struct, k, v)
+    for k, t in ptrs.items():
+        if t is not None:
+            assert t.is_contiguous() or k == "out", k
+            setattr(struct, k, t.data_ptr())
+    return struct
+
+
+def _loop_call(self, name, struct, n_launch):
+    fn = getattr(self.L, name)
+    fn.argtypes = [C.c_void_p, C.c_void_p]
+    fn.restype = C.c_int
+    rc = fn(C.byref(struct), self._st())
+    self.launches += n_launch
+    if rc != 0:
+        raise _lib.TacoError("%s failed with code %d" % (name, rc))
+
+
+def _decoder_loop(self, bwd, dims, zoneout, seed, stream1, stream2, **t):
+    s = _fill(TacoDecLoop(), dict(dims, zoneout=float(zoneout), zo_keep_thresh=keep_threshold(1.0 - zoneout), seed=seed,
+                                   stream1=stream1, stream2=stream2), t)
+    _loop_call(self, "taco_op_decoder_loop_bwd" if bwd else "taco_op_decoder_loop_fwd", s, dims["S"] * (9 if bwd else 8))
+
+
+def _lstm_loop(self, bwd, dims, zoneout, seed, stream_c, stream_h, out, **t):
+    s = _fill(TacoLstmLoop(), dict(dims, zoneout=float(zoneout), zo_keep_thresh=keep_threshold(1.0 - zoneout), seed=seed,
+                                    stream_c=stream_c, stream_h=stream_h, out_sb=out.stride(0), out_st=out.stride(1)),
+              dict(t, out=out))
+    assert out.stride(2) == 1
+    _loop_call(self, "taco_op_lstm_loop_bwd" if bwd else "taco_op_lstm_loop_fwd", s, dims["T"] * 4)
+
+
+CudaOps.decoder_loop = _decoder_loop
+CudaOps.lstm_loop = _lstm_loop
+TRAIN_SYMBOLS = tuple(_SIGS.keys()) + LOOP_SYMBOLS + ("taco_op_set_precision",)
+
+
+def _set_precision(self, precision):
+    """"fp32": SIMT FMA everywhere (parity mode); "bf16": the throughput-bound contractions (conv fwd / dgrad / wgrad and the
+    GEMMs over all S*B rows) on mma.sync tensor cores with bf16 operands and fp32 accumulation (process-wide)."""
+    code = {"fp32": 0, "bf16": 1}[precision]
+    self.L.taco_op_set_precision.argtypes = [C.c_int]
+    self.L.taco_op_set_precision.restype = C.c_int
+    if self.L.taco_op_set_precision(code) != 0:
+        raise _lib.TacoError("taco_op_set_precision failed")
+    self.precision = precision
+
+
+CudaOps.set_precision = _set_precision

@@ -143,7 +143,11 @@ class TrainStep(object):
             cz, hz = o.zeros(T + 1, B, H), o.zeros(T + 1, B, H)
             pre = o.empty(B, 4 * H)
             sc, sh = STREAM_ENC_LSTM + 2 * d, STREAM_ENC_LSTM + 2 * d + 1
-            for s in range(T):
+            fast = hasattr(o, "lstm_loop")         # the same loop sequenced in C (train_loops.cu)
+            if fast:
+                o.lstm_loop(False, dict(B=B, T=T, H=H, C=C, reverse=int(rev)), zo, seed, sc, sh, enc_out[:, :, d * H:(d + 1) * H],
+                            K=K, lens=lens, xw=xw, acts=acts, cnew=cnew, cz=cz, hz=hz, work=o.empty(B * 9 * H))
+            for s in range(0 if not fast else T, T):
                 o.gather_rows(xw, lens, s, rev, pre)
                 o.gemm(hz[s], K[C:], acts[s])
                 o.lstm_fwd(acts[s], pre, None, cz[s], hz[s], lens, s, zo, True, seed, sc, sh, s * B,
@@ -228,7 +232,14 @@ class TrainStep(object):
         ctx, cum = o.zeros(S + 1, B, MD), o.zeros(S + 1, B, T)
         align, q = o.empty(S, B, T), o.empty(S, B, A)
         s1, s2 = STREAM_DEC_LSTM, STREAM_DEC_LSTM + 2
-        for s in range(S):
+        dims = dict(B=B, T=T, S=S, D=D, MD=MD, A=A, U2=U2, NF=att_w[0].shape[2], KW=att_w[0].shape[0])
+        fast = hasattr(o, "decoder_loop")           # the same loop sequenced in C (train_loops.cu)
+        if fast:
+            o.decoder_loop(False, dims, zo, seed, s1, s2, W1=W1, W2=W2, b2=b2, Wq=Wq, conv_w=att_w[0], conv_b=att_w[1], Wl=att_w[2],
+                           va=att_w[3], ba=att_w[4], keys=keys, values=values, lens=lens_eff, G1x=G1x, acts1=acts1, acts2=acts2,
+                           c1new=c1new, c2new=c2new, h1raw=h1raw, h2raw=h2raw, c1z=c1z, h1z=h1z, c2z=c2z, h2z=h2z, ctx=ctx, cum=cum,
+                           align=align, q=q)
+        for s in range(0 if not fast else S, S):
             o.gemm(ctx[s], W1[U2:U2 + MD], acts1[s])
             o.gemm(h1z[s], W1[U2 + MD:], acts1[s], beta=1.0)
             o.lstm_fwd(acts1[s], G1x[s], None, c1z[s], h1z[s], None, 0, zo, True, seed, s1, s1 + 1, s * B,
@@ -239,7 +250,7 @@ class TrainStep(object):
                        c2new[s], c2z[s + 1], h2raw[s], h2z[s + 1])
             o.gemm(h2raw[s], Wq, q[s])
             o.attn_fwd(q[s], cum[s], keys, values, lens_eff, *att_w, align[s], cum[s + 1], ctx[s + 1])
-        t.update(Xin=Xin, P1=P1, P2=P2, acts1=acts1, acts2=acts2, c1new=c1new, c2new=c2new, h1raw=h1raw, h2raw=h2raw,
+        t.update(dec_dims=dims, G1x=G1x, Xin=Xin, P1=P1, P2=P2, acts1=acts1, acts2=acts2, c1new=c1new, c2new=c2new, h1raw=h1raw, h2raw=h2raw,
                  c1z=c1z, h1z=h1z, c2z=c2z, h2z=h2z, ctx=ctx, cum=cum, align=align, q=q)
         # frame / stop projections on [LSTM_output, context] for all steps at once (Decoder.py:355-410)
         Wf, Ws = P[W.FRAME_PROJ + "/kernel"], P[W.STOP_PROJ + "/kernel"]
@@ -354,7 +365,14 @@ class TrainStep(object):
         dctx_carry = o.zeros(B, MD)
         dcum, dcum_n = o.zeros(B, T), o.empty(B, T)
         s1, s2 = STREAM_DEC_LSTM, STREAM_DEC_LSTM + 2
-        for s in range(S - 1, -1, -1):
+        fast = hasattr(o, "decoder_loop")
+        if fast:
+            o.decoder_loop(True, t["dec_dims"], zo, seed, s1, s2, W1=W1, W2=W2, Wq=Wq, conv_w=att_w[0], conv_b=att_w[1], Wl=att_w[2],
+                           va=att_w[3], ba=att_w[4], keys=keys, values=values, lens=lens_eff, acts1=t["acts1"], acts2=t["acts2"],
+                           c1new=t["c1new"], c2new=t["c2new"], c1z=t["c1z"], h1z=t["h1z"], c2z=t["c2z"], h2z=t["h2z"], cum=t["cum"],
+                           align=t["align"], q=t["q"], dH2=dH2, dCtx=dCtx, dG1=dG1, dG2=dG2, dQ=dQ, dkeys=dkeys, p_conv_w=parts[0],
+                           p_conv_b=parts[1], p_Wl=parts[2], p_va=parts[3], p_ba=parts[4], work=o.empty(B * (9 * D + MD + 2 * T)))
+        for s in range(S - 1 if not fast else -1, -1, -1):
             o.ew("add", dCtx[s], dCtx[s], dctx_carry)                 # total d(ctx_t); kept for d(values)
             o.attn_bwd(dCtx[s], dcum, t["q"][s], t["cum"][s], t["align"][s], keys, values, lens_eff, *att_w,
                        dQ[s], dcum_n, dkeys, *parts)
@@ -460,7 +478,11 @@ class TrainStep(object):
             dg = o.empty(T, B, 4 * H)
             dc, dhz, dcn, dhn = o.zeros(B, H), o.zeros(B, H), o.empty(B, H), o.empty(B, H)
             src = dmemory[:, :, d * H:(d + 1) * H]
-            for s in range(T - 1, -1, -1):
+            fast = hasattr(o, "lstm_loop")
+            if fast:
+                o.lstm_loop(True, dict(B=B, T=T, H=H, C=C, reverse=int(rec["rev"])), zo, seed, rec["sc"], rec["sh"], src, K=K, lens=lens,
+                            acts=rec["acts"], cnew=rec["cnew"], cz=rec["cz"], hz=rec["hz"], dxw=dxw, dg=dg, work=o.empty(B * 9 * H))
+            for s in range(T - 1 if not fast else -1, -1, -1):
                 o.gather_rows(src, lens, s, rec["rev"], d_hraw)
                 o.lstm_bwd(rec["acts"][s], rec["cz"][s], rec["hz"][s], rec["cnew"][s], lens, s, zo, True, seed, rec["sc"], rec["sh"],
                            s * B, d_hraw, dc, dhz, dg[s], dcn, dhn)

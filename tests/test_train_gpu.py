@@ -239,3 +239,73 @@ def test_training_step_matches_oracle_autograd(ops, lengths, fpt):
     new = step.store.export()
     for n in wn:
         np.testing.assert_allclose(new[n], wn[n], atol=5e-5, err_msg=n)
+
+
+# ------------------------------------------------------------------ bf16 tensor-core mode of the large contractions
+def _bf(x):
+    return x.to(torch.bfloat16).to(torch.float32)
+
+
+def test_bf16_mma_contractions_match_bf16_rounded_operands(ops):
+    """TACO_TRAIN_BF16: the result equals an fp32 contraction of the bf16-ROUNDED operands up to accumulation order."""
+    cu, tw = ops
+    cu.set_precision("bf16")
+    try:
+        for (M, N, K, ta, tb, beta, bias) in [(600, 520, 600, 0, 0, 0.0, 1), (1280, 1024, 4099, 1, 0, 0.0, 0), (2000, 1100, 512, 0, 1, 1.0, 1),
+                                              (256, 1024, 16000, 1, 0, 0.0, 0)]:
+            A = R(K, M) if ta else R(M, K)
+            Bm = R(N, K) if tb else R(K, N)
+            C0, b = R(M, N, seed=3), (R(N) if bias else None)
+            Cg = C0.clone().cuda()
+            cu.gemm(A.cuda(), Bm.cuda(), Cg, bool(ta), bool(tb), beta, None if b is None else b.cuda())
+            Cc = C0.clone()
+            tw.gemm(_bf(A), _bf(Bm), Cc, bool(ta), bool(tb), beta, b)
+            np.testing.assert_allclose(Cg.cpu().numpy(), Cc.numpy(), atol=2e-4 * np.sqrt(K), rtol=1e-4)
+        for (B, T, Ci, Co, k) in [(3, 130, 80, 768, 5), (4, 200, 768, 768, 5), (20, 200, 768, 80, 5), (4, 111, 512, 512, 5)]:
+            x, w, dy = R(B, T, Ci), R(k, Ci, Co, scale=0.1), R(B, T, Co)
+            for name, args, mnk in (("conv1d_fwd", [x, w, R(Co), torch.zeros(B, T, Co)], (B * T, Co, k * Ci)),
+                                    ("conv1d_dgrad", [dy, w, torch.zeros(B, T, Ci)], (B * T, Ci, k * Co)),
+                                    ("conv1d_wgrad", [x, dy, torch.zeros(k, Ci, Co)], (k * Ci, Co, B * T))):
+                # the library routes a contraction to the tensor cores only when it is throughput-bound (train_gemm.cu: use_mma)
+                routed = mnk[0] * mnk[1] >= 64 ** 3 and mnk[0] * mnk[1] * mnk[2] >= 2 ** 24
+                ag = [a.clone().cuda() for a in args]
+                ac = [(_bf(a) if (routed and i in (0, 1)) else a.clone()) for i, a in enumerate(args)]
+                getattr(cu, name)(*ag)
+                getattr(tw, name)(*ac)
+                np.testing.assert_allclose(ag[-1].cpu().numpy(), ac[-1].numpy(), atol=3e-3, rtol=1e-3, err_msg=name)
+    finally:
+        cu.set_precision("fp32")
+
+
+def test_training_step_bf16_mode_close_to_fp32_oracle(ops):
+    """bf16 operands in the large contractions: losses within 2 %, every large gradient tensor within 6 % (relative L2; worst are the reference-encoder kernels behind the GRU + GST chain) of
+    autograd through the fp32 oracle; stated tolerance of the mixed-precision mode."""
+    cu, _ = ops
+    hp = default_hparams()
+    w = weights.init_weights(hp, perturb=0.05)
+    ids, lens, mel, stop, seed = _problem(hp, (18, 31, 36, 41), 4, 3)
+    ref, orc = train_oracle.train_forward(hp, w, ids, lens, mel, stop, seed)
+    ref["loss"].backward()
+    ref_grads = train_oracle.gradients(orc)
+    cu.set_precision("bf16")
+    try:
+        step = TrainStep(hp, cu, w)
+        out = step.forward(cu.to_device(ids), cu.to_device(lens), cu.to_device(mel), cu.to_device(stop), seed)
+        step.backward()
+        torch.cuda.synchronize()
+    finally:
+        cu.set_precision("fp32")
+    ls = out["losses"].cpu().numpy()
+    for i, k in enumerate(("before_loss", "after_loss", "stop_token_loss")):
+        np.testing.assert_allclose(ls[i], float(ref[k].detach()), rtol=2e-2)
+    worst = ("", 0.0)
+    for name, g_ref in ref_grads.items():
+        if g_ref.size < 1024 or np.linalg.norm(g_ref) < 1e-4:
+            continue
+        g = step.store.G[name].cpu().numpy().reshape(g_ref.shape).astype(np.float64)
+        if is_regularized(name):
+            g = g + train_oracle.reg_weight(hp) * np.asarray(w[name], np.float64)
+        err = np.linalg.norm(g - g_ref) / np.linalg.norm(g_ref)
+        worst = max(worst, (name, err), key=lambda z: z[1])
+        assert err < 6e-2, "%s: relative L2 error %.3e" % (name, err)
+    print("bf16 mode worst gradient (relative L2):", worst)
