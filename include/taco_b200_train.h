@@ -76,7 +76,8 @@ int taco_op_gather_rows(const float* src, long long sb, long long st, const int3
 int taco_op_scatter_rows(const float* src, const int32_t* lens, int s, int reverse, float* dst, long long db, long long dt,
                          int B, int N, void* stream);
 
-/* One LocationSensitiveAttention step (Attention.py:169-210,345-401), fp32, one CTA per batch row. */
+/* One LocationSensitiveAttention step (Attention.py:169-210,345-401), fp32: energy / softmax / context kernels tiled over
+ * (positions x rows) and (value columns x rows). */
 int taco_op_attn_fwd(const float* q, const float* cum_prev, const float* keys, const float* values, const int32_t* lens,
                      const float* conv_w, const float* conv_b, const float* Wl, const float* va, const float* ba,
                      float* align, float* cum, float* ctx, int B, int T, int A, int V, int NF, int KW, void* stream);
@@ -85,7 +86,7 @@ int taco_op_attn_fwd(const float* q, const float* cum_prev, const float* keys, c
 int taco_op_attn_bwd(const float* dctx, const float* dcum, const float* q, const float* cum_prev, const float* align,
                      const float* keys, const float* values, const int32_t* lens, const float* conv_w, const float* conv_b,
                      const float* Wl, const float* va, const float* ba, float* dq, float* dcum_prev, float* dkeys,
-                     float* p_conv_w, float* p_conv_b, float* p_Wl, float* p_va, float* p_ba,
+                     float* p_conv_w, float* p_conv_b, float* p_Wl, float* p_va, float* p_ba, float* scratch /* >= B*T*NF floats */,
                      int B, int T, int A, int V, int NF, int KW, void* stream);
 
 /* GRUCell (Tacotron.py:201; reset before the candidate matmul) pointwise parts and gradients. */
@@ -149,7 +150,7 @@ typedef struct TacoDecLoop {
     float *dG1, *dG2, *dQ;                   /* [S,B,4D], [S,B,4D], [S,B,A] out */
     float* dkeys;                            /* [B,T,A] accumulated (caller zeroes) */
     float *p_conv_w, *p_conv_b, *p_Wl, *p_va, *p_ba;   /* per-row partials of the attention weight gradients (caller zeroes) */
-    float* work;                             /* scratch, >= B*(9*D + MD + 2*T) floats */
+    float* work;                             /* scratch, >= B*(8*D + 2*T + T*NF) + S*B*D + (S+1)*B*MD floats */
 } TacoDecLoop;
 int taco_op_decoder_loop_fwd(const TacoDecLoop* p, void* stream);
 int taco_op_decoder_loop_bwd(const TacoDecLoop* p, void* stream);

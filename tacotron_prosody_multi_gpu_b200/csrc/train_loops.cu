@@ -17,20 +17,27 @@ int taco_op_decoder_loop_fwd(const TacoDecLoop* p, void* st) {
     const float* W1c = p->W1 + (size_t)U2 * G;          // rows of the context
     const float* W1h = p->W1 + (size_t)(U2 + MD) * G;   // rows of h1
     const float* W2h = p->W2 + (size_t)D * G;
+    // the per-step contractions are split-K with atomic accumulation: zero their outputs once for all steps instead of
+    // one memset per step
+    cudaStream_t cs = (cudaStream_t)st;
+    if (cudaMemsetAsync(p->acts1, 0, sizeof(float) * (size_t)S * B * G, cs) != cudaSuccess ||
+        cudaMemsetAsync(p->acts2, 0, sizeof(float) * (size_t)S * B * G, cs) != cudaSuccess ||
+        cudaMemsetAsync(p->q, 0, sizeof(float) * (size_t)S * B * A, cs) != cudaSuccess)
+        return -3;
     for (int s = 0; s < S; ++s) {
         const size_t oD = (size_t)s * B * D, oG = (size_t)s * B * G, nD = oD + (size_t)B * D;
         float* a1 = p->acts1 + oG;
         float* a2 = p->acts2 + oG;
-        OK(taco_op_gemm(p->ctx + (size_t)s * B * MD, MD, W1c, G, a1, G, B, G, MD, 0, 0, 0.f, nullptr, st));
+        OK(taco_op_gemm(p->ctx + (size_t)s * B * MD, MD, W1c, G, a1, G, B, G, MD, 0, 0, 1.f, nullptr, st));
         OK(taco_op_gemm(p->h1z + oD, D, W1h, G, a1, G, B, G, D, 0, 0, 1.f, nullptr, st));
         OK(taco_op_lstm_fwd(a1, p->G1x + oG, nullptr, p->c1z + oD, p->h1z + oD, nullptr, 0, p->zoneout, 1, p->zo_keep_thresh, p->seed,
                             p->stream1, p->stream1 + 1, s * B, p->c1new + oD, p->c1z + nD, p->h1raw + oD, p->h1z + nD, B, D, st));
-        OK(taco_op_gemm(p->h1raw + oD, D, p->W2, G, a2, G, B, G, D, 0, 0, 0.f, nullptr, st));
+        OK(taco_op_gemm(p->h1raw + oD, D, p->W2, G, a2, G, B, G, D, 0, 0, 1.f, nullptr, st));
         OK(taco_op_gemm(p->h2z + oD, D, W2h, G, a2, G, B, G, D, 0, 0, 1.f, nullptr, st));
         OK(taco_op_lstm_fwd(a2, nullptr, p->b2, p->c2z + oD, p->h2z + oD, nullptr, 0, p->zoneout, 1, p->zo_keep_thresh, p->seed,
                             p->stream2, p->stream2 + 1, s * B, p->c2new + oD, p->c2z + nD, p->h2raw + oD, p->h2z + nD, B, D, st));
         float* q = p->q + (size_t)s * B * A;
-        OK(taco_op_gemm(p->h2raw + oD, D, p->Wq, A, q, A, B, A, D, 0, 0, 0.f, nullptr, st));
+        OK(taco_op_gemm(p->h2raw + oD, D, p->Wq, A, q, A, B, A, D, 0, 0, 1.f, nullptr, st));
         OK(taco_op_attn_fwd(q, p->cum + (size_t)s * B * T, p->keys, p->values, p->lens, p->conv_w, p->conv_b, p->Wl, p->va, p->ba,
                             p->align + (size_t)s * B * T, p->cum + (size_t)(s + 1) * B * T, p->ctx + (size_t)(s + 1) * B * MD, B, T, A, MD,
                             p->NF, p->KW, st));
@@ -46,31 +53,38 @@ int taco_op_decoder_loop_bwd(const TacoDecLoop* p, void* st) {
     const float* W2h = p->W2 + (size_t)D * G;
     const size_t BD = (size_t)B * D;
     float* w = p->work;
-    if (cudaMemsetAsync(w, 0, sizeof(float) * ((size_t)B * (9 * D + MD + 2 * T)), (cudaStream_t)st) != cudaSuccess) return -3;
+    // work layout: 8 state vectors [B,D] | dcum x2 [B,T] | attention scratch [B,T,NF] | per-step d(h1raw) [S,B,D] |
+    // per-step d(ctx) carry [S+1,B,MD]  (per-step slots are zeroed once: their producers accumulate with split-K atomics)
+    const size_t n_work = (size_t)B * (8 * D + 2 * T + (size_t)T * p->NF) + (size_t)S * B * D + (size_t)(S + 1) * B * MD;
+    if (cudaMemsetAsync(w, 0, sizeof(float) * n_work, (cudaStream_t)st) != cudaSuccess) return -3;
     float *dc1 = w, *dh1z = w + BD, *dc2 = w + 2 * BD, *dh2z = w + 3 * BD;
     float *dc1n = w + 4 * BD, *dh1zn = w + 5 * BD, *dc2n = w + 6 * BD, *dh2zn = w + 7 * BD;
-    float* dh1raw = w + 8 * BD;
-    float* dctx_carry = w + 9 * BD;
-    float* dcum = dctx_carry + (size_t)B * MD;
+    float* dcum = w + 8 * BD;
     float* dcum_n = dcum + (size_t)B * T;
+    float* attn_scratch = dcum_n + (size_t)B * T;      // [B][T][NF]
+    float* dh1raw_all = attn_scratch + (size_t)B * T * p->NF;
+    float* dcarry_all = dh1raw_all + (size_t)S * B * D;   // slot s+1 = carry INTO step s (slot S = 0)
     for (int s = S - 1; s >= 0; --s) {
         const size_t oD = (size_t)s * B * D, oG = (size_t)s * B * G;
         float* dctx = p->dCtx + (size_t)s * B * MD;
+        float* dh1raw = dh1raw_all + (size_t)s * B * D;
+        const float* dctx_carry = dcarry_all + (size_t)(s + 1) * B * MD;
+        float* dctx_carry_out = dcarry_all + (size_t)s * B * MD;
         OK(taco_op_ew(TACO_EW_ADD, dctx, dctx, dctx_carry, 1.f, (long long)B * MD, st));
         float* dq = p->dQ + (size_t)s * B * A;
         OK(taco_op_attn_bwd(dctx, dcum, p->q + (size_t)s * B * A, p->cum + (size_t)s * B * T, p->align + (size_t)s * B * T, p->keys,
                             p->values, p->lens, p->conv_w, p->conv_b, p->Wl, p->va, p->ba, dq, dcum_n, p->dkeys, p->p_conv_w,
-                            p->p_conv_b, p->p_Wl, p->p_va, p->p_ba, B, T, A, MD, p->NF, p->KW, st));
+                            p->p_conv_b, p->p_Wl, p->p_va, p->p_ba, attn_scratch, B, T, A, MD, p->NF, p->KW, st));
         { float* t_ = dcum; dcum = dcum_n; dcum_n = t_; }
         float* dh2 = p->dH2 + oD;
         OK(taco_op_gemm(dq, A, p->Wq, A, dh2, D, B, D, A, 0, 1, 1.f, nullptr, st));
         OK(taco_op_lstm_bwd(p->acts2 + oG, p->c2z + oD, p->h2z + oD, p->c2new + oD, nullptr, 0, p->zoneout, 1, p->zo_keep_thresh, p->seed,
                             p->stream2, p->stream2 + 1, s * B, dh2, dc2, dh2z, p->dG2 + oG, dc2n, dh2zn, B, D, st));
-        OK(taco_op_gemm(p->dG2 + oG, G, p->W2, G, dh1raw, D, B, D, G, 0, 1, 0.f, nullptr, st));
+        OK(taco_op_gemm(p->dG2 + oG, G, p->W2, G, dh1raw, D, B, D, G, 0, 1, 1.f, nullptr, st));
         OK(taco_op_gemm(p->dG2 + oG, G, W2h, G, dh2zn, D, B, D, G, 0, 1, 1.f, nullptr, st));
         OK(taco_op_lstm_bwd(p->acts1 + oG, p->c1z + oD, p->h1z + oD, p->c1new + oD, nullptr, 0, p->zoneout, 1, p->zo_keep_thresh, p->seed,
                             p->stream1, p->stream1 + 1, s * B, dh1raw, dc1, dh1z, p->dG1 + oG, dc1n, dh1zn, B, D, st));
-        OK(taco_op_gemm(p->dG1 + oG, G, W1c, G, dctx_carry, MD, B, MD, G, 0, 1, 0.f, nullptr, st));
+        OK(taco_op_gemm(p->dG1 + oG, G, W1c, G, dctx_carry_out, MD, B, MD, G, 0, 1, 1.f, nullptr, st));
         OK(taco_op_gemm(p->dG1 + oG, G, W1h, G, dh1zn, D, B, D, G, 0, 1, 1.f, nullptr, st));
         float* t_;
         t_ = dc1; dc1 = dc1n; dc1n = t_;
@@ -87,11 +101,12 @@ int taco_op_lstm_loop_fwd(const TacoLstmLoop* p, void* st) {
     const float* Kh = p->K + (size_t)p->C * G;
     float* pre = p->work;
     float* hraw = p->work + (size_t)B * G;
+    if (cudaMemsetAsync(p->acts, 0, sizeof(float) * (size_t)T * B * G, (cudaStream_t)st) != cudaSuccess) return -3;
     for (int s = 0; s < T; ++s) {
         const size_t oH = (size_t)s * B * H, nH = oH + (size_t)B * H;
         float* a = p->acts + (size_t)s * B * G;
         OK(taco_op_gather_rows(p->xw, (long long)T * G, G, p->lens, s, p->reverse, pre, B, G, st));
-        OK(taco_op_gemm(p->hz + oH, H, Kh, G, a, G, B, G, H, 0, 0, 0.f, nullptr, st));
+        OK(taco_op_gemm(p->hz + oH, H, Kh, G, a, G, B, G, H, 0, 0, 1.f, nullptr, st));
         OK(taco_op_lstm_fwd(a, pre, nullptr, p->cz + oH, p->hz + oH, p->lens, s, p->zoneout, 1, p->zo_keep_thresh, p->seed, p->stream_c,
                             p->stream_h, s * B, p->cnew + oH, p->cz + nH, hraw, p->hz + nH, B, H, st));
         OK(taco_op_scatter_rows(hraw, p->lens, s, p->reverse, p->out, p->out_sb, p->out_st, B, H, st));

@@ -33,7 +33,7 @@ _SIGS = {
     "taco_op_gather_rows": [_P, _LL, _LL, _P, _I, _I, _P, _I, _I, _P],
     "taco_op_scatter_rows": [_P, _P, _I, _I, _P, _LL, _LL, _I, _I, _P],
     "taco_op_attn_fwd": [_P] * 13 + [_I] * 6 + [_P],
-    "taco_op_attn_bwd": [_P] * 21 + [_I] * 6 + [_P],
+    "taco_op_attn_bwd": [_P] * 22 + [_I] * 6 + [_P],
     "taco_op_gru_pre": [_P, _P, _P, _I, _I, _P],
     "taco_op_gru_out": [_P, _P, _P, _P, _I, _I, _P],
     "taco_op_gru_out_bwd": [_P, _P, _P, _P, _P, _P, _P, _I, _I, _P],
@@ -204,7 +204,7 @@ class CudaOps(object):
         B, T, A = keys.shape
         self._call("taco_op_attn_bwd", _c(dctx), _c(dcum), _c(q), _c(cum_prev), _c(align), _c(keys), _c(values), _c(lens), _c(conv_w),
                    _c(conv_b), _c(Wl), _c(va), _c(ba), _c(dq), _c(dcum_prev), _c(dkeys), _c(p_conv_w), _c(p_conv_b), _c(p_Wl),
-                   _c(p_va), _c(p_ba), B, T, A, values.shape[2], conv_w.shape[2], conv_w.shape[0])
+                   _c(p_va), _c(p_ba), _c(self.empty(B * T * conv_w.shape[2])), B, T, A, values.shape[2], conv_w.shape[2], conv_w.shape[0])
 
     # ------------------------------------------------------------------ GRU / GST
     def gru_pre(self, g, h, rh):

@@ -371,7 +371,7 @@ class TrainStep(object):
                            va=att_w[3], ba=att_w[4], keys=keys, values=values, lens=lens_eff, acts1=t["acts1"], acts2=t["acts2"],
                            c1new=t["c1new"], c2new=t["c2new"], c1z=t["c1z"], h1z=t["h1z"], c2z=t["c2z"], h2z=t["h2z"], cum=t["cum"],
                            align=t["align"], q=t["q"], dH2=dH2, dCtx=dCtx, dG1=dG1, dG2=dG2, dQ=dQ, dkeys=dkeys, p_conv_w=parts[0],
-                           p_conv_b=parts[1], p_Wl=parts[2], p_va=parts[3], p_ba=parts[4], work=o.empty(B * (9 * D + MD + 2 * T)))
+                           p_conv_b=parts[1], p_Wl=parts[2], p_va=parts[3], p_ba=parts[4], work=o.empty(B * (8 * D + 2 * T + T * t["dec_dims"]["NF"]) + S * B * D + (S + 1) * B * MD))
         for s in range(S - 1 if not fast else -1, -1, -1):
             o.ew("add", dCtx[s], dCtx[s], dctx_carry)                 # total d(ctx_t); kept for d(values)
             o.attn_bwd(dCtx[s], dcum, t["q"][s], t["cum"][s], t["align"][s], keys, values, lens_eff, *att_w,
