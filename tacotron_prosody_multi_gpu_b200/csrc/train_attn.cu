@@ -305,7 +305,7 @@ __global__ void __launch_bounds__(256) attn_bwd_pre_kernel(const float* __restri
 }
 
 // location convolution gradients of one row: d(conv_w), d(conv_b) (+= into the row partials), d(cum_{t-1})
-__global__ void __launch_bounds__(256) attn_bwd_conv_kernel(const float* __restrict__ dcum, const float* __restrict__ cum_prev,
+__global__ void __launch_bounds__(512) attn_bwd_conv_kernel(const float* __restrict__ dcum, const float* __restrict__ cum_prev,
                                                             const float* __restrict__ dfl, const int32_t* __restrict__ lens,
                                                             const float* __restrict__ conv_w, float* __restrict__ dcum_prev,
                                                             float* __restrict__ p_conv_w, float* __restrict__ p_conv_b, int T, int KW) {
@@ -333,18 +333,24 @@ __global__ void __launch_bounds__(256) attn_bwd_conv_kernel(const float* __restr
         for (int t = 0; t < len; ++t) a += s_dfl[t * (NF + 1) + tid];
         p_conv_b[(long long)b * NF + tid] += a;
     }
-    for (int tp = tid; tp < T; tp += blockDim.x) {
-        float a = dcum[(long long)b * T + tp];
-        for (int j = 0; j < KW; ++j) {
-            const int t = tp - j + left;       // floc[t] read cum[t + j - left] = cum[tp]
-            if (t >= 0 && t < len) {
-                const float* dfr = s_dfl + t * (NF + 1);
-                const float* cwr = s_cw + j * NF;
+    // d(cum_{t-1})[tp]: 4 adjacent lanes share one position, each takes every 4th tap; combined with two shuffles
+    const int Tq = (T + 63) / 64 * 64;           // keep whole warps in the loop (shuffles)
+    for (int i = tid; i < Tq * 4; i += blockDim.x) {
+        const int tp = i >> 2, jq = i & 3;
+        float a = 0.f;
+        if (tp < T)
+            for (int j = jq; j < KW; j += 4) {
+                const int t = tp - j + left;       // floc[t] read cum[t + j - left] = cum[tp]
+                if (t >= 0 && t < len) {
+                    const float* dfr = s_dfl + t * (NF + 1);
+                    const float* cwr = s_cw + j * NF;
 #pragma unroll 8
-                for (int ff = 0; ff < NF; ++ff) a = fmaf(dfr[ff], cwr[ff], a);
+                    for (int ff = 0; ff < NF; ++ff) a = fmaf(dfr[ff], cwr[ff], a);
+                }
             }
-        }
-        dcum_prev[(long long)b * T + tp] = a;
+        a += __shfl_xor_sync(0xffffffffu, a, 1);
+        a += __shfl_xor_sync(0xffffffffu, a, 2);
+        if (jq == 0 && tp < T) dcum_prev[(long long)b * T + tp] = a + dcum[(long long)b * T + tp];
     }
 }
 
@@ -392,7 +398,7 @@ int taco_op_attn_bwd(const float* dctx, const float* dcum, const float* q, const
     const size_t sm2 = sizeof(float) * ((size_t)T + KW + (size_t)KW * NF + (size_t)T * (NF + 1));
     if (sm2 > 200 * 1024) return -1;
     if (!ensure_smem(attn_bwd_conv_kernel, sm2)) return -3;
-    attn_bwd_conv_kernel<<<B, 256, sm2, st>>>(dcum, cum_prev, dfl, lens, conv_w, dcum_prev, p_conv_w, p_conv_b, T, KW);
+    attn_bwd_conv_kernel<<<B, 512, sm2, st>>>(dcum, cum_prev, dfl, lens, conv_w, dcum_prev, p_conv_w, p_conv_b, T, KW);
     return cudaGetLastError() == cudaSuccess ? 0 : -3;
 }
 

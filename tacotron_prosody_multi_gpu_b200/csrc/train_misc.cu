@@ -62,7 +62,15 @@ __global__ void conv2d_dgrad_kernel(const float* __restrict__ dy, const float* _
             if (wo >= Wo) continue;
             const float* dp = dy + (((long long)b * Ho + ho) * Wo + wo) * Co;
             const float* wp = w + ((long long)(kh * 3 + kw) * Ci + ci) * Co;
-            for (int co = 0; co < Co; ++co) acc = fmaf(dp[co], wp[co], acc);
+            if ((Co & 3) == 0) {                  // 16-byte loads: d(y) is a warp broadcast, the kernel row is private
+                for (int co = 0; co < Co; co += 4) {
+                    const float4 d4 = *reinterpret_cast<const float4*>(dp + co);
+                    const float4 w4 = *reinterpret_cast<const float4*>(wp + co);
+                    acc = fmaf(d4.x, w4.x, acc); acc = fmaf(d4.y, w4.y, acc); acc = fmaf(d4.z, w4.z, acc); acc = fmaf(d4.w, w4.w, acc);
+                }
+            } else {
+                for (int co = 0; co < Co; ++co) acc = fmaf(dp[co], wp[co], acc);
+            }
         }
     }
     dx[i] = acc;
@@ -76,14 +84,16 @@ __global__ void conv2d_wgrad_kernel(const float* __restrict__ x, const float* __
     const int co = threadIdx.x % Co, pl_lane = threadIdx.x / Co, n_pl = blockDim.x / Co;
     const long long npos = (long long)B * Ho * Wo;
     float acc = 0.f;
+#pragma unroll 4
     for (long long p = (long long)blockIdx.y * n_pl + pl_lane; p < npos; p += (long long)gridDim.y * n_pl) {
         int wo = (int)(p % Wo);
         long long r = p / Wo;
         int ho = (int)(r % Ho);
         int b = (int)(r / Ho);
         int h = 2 * ho + kh - pt, ww = 2 * wo + kw - pl;
-        if (h < 0 || h >= H || ww < 0 || ww >= W) continue;
-        acc = fmaf(x[(((long long)b * H + h) * W + ww) * Ci + ci], dy[p * Co + co], acc);
+        const bool ok = h >= 0 && h < H && ww >= 0 && ww < W;      // predicated (no branch): loads of 4 iterations in flight
+        const float xv = ok ? x[(((long long)b * H + h) * W + ww) * Ci + ci] : 0.f;
+        acc = fmaf(xv, dy[p * Co + co], acc);
     }
     sh[threadIdx.x] = acc;
     __syncthreads();
@@ -194,7 +204,7 @@ int taco_op_conv2d_wgrad(const float* x, const float* dy, float* dw, int B, int 
     const long long npos = (long long)B * Ho * Wo;
     const int n_pl = 256 / Co;
     int splits = (int)((npos / n_pl + 63) / 64);          // >= 64 positions per thread
-    int cap = (148 * 8 + 9 * Ci - 1) / (9 * Ci);
+    int cap = (148 * 16 + 9 * Ci - 1) / (9 * Ci);
     if (splits > cap) splits = cap;
     if (splits < 1) splits = 1;
     conv2d_wgrad_kernel<<<dim3(9 * Ci, splits), 256, 0, ST>>>(x, dy, dw, B, H, W, Ci, Co, Ho, Wo, pad_before(H), pad_before(W));
