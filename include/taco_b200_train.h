@@ -36,6 +36,13 @@ int taco_op_set_precision(int precision);
  * tf.layers.dense / LSTMCell / GRUCell matmuls and all their gradients. */
 int taco_op_gemm(const float* A, long long lda, const float* B, long long ldb, float* C, long long ldc, int M, int N, int K,
                  int ta, int tb, float beta, const float* bias, void* stream);
+/* Fused pairs of the per-step (M = batch) contractions, always accumulating into their outputs (split-K, atomics):
+ *   C += [A1 | A2] . B          -- x- and h-part of an LSTM gate contraction in one launch (B = kernel rows [K1+K2, N])
+ *   [C1 | C2] += A . B^T        -- its gradient w.r.t. both inputs in one launch (B = the same kernel rows [N1+N2, K]) */
+int taco_op_gemm_pair_acc(const float* A1, long long lda1, int K1, const float* A2, long long lda2, int K2, const float* B, long long ldb,
+                          float* C, long long ldc, int M, int N, void* stream);
+int taco_op_gemm_nt_split_acc(const float* A, long long lda, const float* B, long long ldb, float* C1, long long ldc1, int N1, float* C2,
+                              long long ldc2, int N2, int M, int K, void* stream);
 /* tf.layers.conv1d(padding='same') NWC, kernel [k,Ci,Co] (Encoder.py:159-164) and its two gradients. */
 int taco_op_conv1d_fwd(const float* x, const float* w, const float* bias, float* y, int B, int T, int Ci, int Co, int k, void* stream);
 int taco_op_conv1d_dgrad(const float* dy, const float* w, float* dx, int B, int T, int Ci, int Co, int k, void* stream);

@@ -18,6 +18,10 @@ struct APlain {   // A(m,k) = A[m*sm + k*sk]
     const float* p; long long sm, sk; int k_contig;
     __device__ __forceinline__ float operator()(int m, int k) const { return p[m * sm + k * sk]; }
 };
+struct APair {    // A(m,k) = k < K1 ? A1[m*ld1 + k] : A2[m*ld2 + k - K1]   (two k-contiguous row blocks side by side)
+    const float *p1, *p2; long long ld1, ld2; int K1, k_contig;
+    __device__ __forceinline__ float operator()(int m, int k) const { return k < K1 ? p1[m * ld1 + k] : p2[m * ld2 + (k - K1)]; }
+};
 struct BPlain {   // B(k,n) = B[k*sk + n*sn]
     const float* p; long long sk, sn; int n_contig;
     __device__ __forceinline__ float operator()(int k, int n) const { return p[k * sk + n * sn]; }
@@ -57,7 +61,8 @@ struct AConvWgrad {
 template <int BM, int BN, int BK, int TM, int TN, class AL, class BL>
 __global__ void __launch_bounds__((BM / TM) * (BN / TN))
 gemm_kernel(AL A, BL Bm, float* __restrict__ C, long long ldc, int M, int N, int K, float beta, const float* __restrict__ bias,
-            int kchunk /* K range per blockIdx.z; gridDim.z > 1 => split-K with atomic accumulation into C */) {
+            int kchunk /* K range per blockIdx.z; gridDim.z > 1 => split-K with atomic accumulation into C */,
+            float* __restrict__ C2 = nullptr, long long ldc2 = 0, int N1 = 0 /* columns >= N1 go to C2[m*ldc2 + n - N1] */) {
     constexpr int NT = (BM / TM) * (BN / TN);
     __shared__ float As[2][BK][BM + 4];
     __shared__ float Bs[2][BK][BN + 4];
@@ -141,7 +146,7 @@ gemm_kernel(AL A, BL Bm, float* __restrict__ C, long long ldc, int M, int N, int
             int n = n0 + tx * TN + j;
             if (n >= N) continue;
             float v = acc[i][j];
-            float* c = C + (long long)m * ldc + n;
+            float* c = (C2 && n >= N1) ? C2 + (long long)m * ldc2 + (n - N1) : C + (long long)m * ldc + n;
             if (gridDim.z > 1) {             // split-K: C was zeroed (beta 0) or holds the addend (beta 1)
                 if (bias && blockIdx.z == 0) v += bias[n];
                 atomicAdd(c, v);
@@ -540,7 +545,39 @@ int launch_gemm(AL A, BL Bm, float* C, long long ldc, int M, int N, int K, float
 
 }  // namespace
 
+// skinny (M = batch) contraction with a two-block A and/or a two-block C, always accumulating (beta = 1), split-K
+template <class AL>
+int launch_skinny_acc(AL A, BPlain Bm, float* C, long long ldc, float* C2, long long ldc2, int N1, int M, int N, int K, cudaStream_t st) {
+    dim3 grid((N + 31) / 32, (M + 31) / 32, 1);
+    int kchunk = K;
+    const int ctas = grid.x * grid.y;
+    if (K >= 256 && ctas < 148) {
+        int splits = (296 + ctas - 1) / ctas;
+        if (splits > 8) splits = 8;
+        if (splits > K / 128) splits = K / 128;
+        if (splits > 1) {
+            kchunk = ((K + splits - 1) / splits + 31) / 32 * 32;
+            grid.z = (K + kchunk - 1) / kchunk;
+        }
+    }
+    gemm_kernel<32, 32, 32, 2, 2, AL, BPlain><<<grid, 256, 0, st>>>(A, Bm, C, ldc, M, N, K, 1.f, nullptr, kchunk, C2, ldc2, N1);
+    return cudaGetLastError() == cudaSuccess ? 0 : -3;
+}
+
 extern "C" {
+
+/* C += [A1 | A2] . B   (A1 [M,K1], A2 [M,K2] row-major, B [K1+K2, N] row-major): the x- and h-part of an LSTM gate contraction */
+int taco_op_gemm_pair_acc(const float* A1, long long lda1, int K1, const float* A2, long long lda2, int K2, const float* B, long long ldb,
+                          float* C, long long ldc, int M, int N, void* stream) {
+    if (!A1 || !A2 || !B || !C || M < 1 || N < 1 || K1 < 1 || K2 < 1) return -1;
+    return launch_skinny_acc(APair{A1, A2, lda1, lda2, K1, 1}, BPlain{B, ldb, 1, 1}, C, ldc, nullptr, 0, 0, M, N, K1 + K2, (cudaStream_t)stream);
+}
+/* [C1 | C2] += A . B^T   (A [M,K], B stored [N1+N2, K] row-major): the gradient of the same contraction w.r.t. its two inputs */
+int taco_op_gemm_nt_split_acc(const float* A, long long lda, const float* B, long long ldb, float* C1, long long ldc1, int N1, float* C2,
+                              long long ldc2, int N2, int M, int K, void* stream) {
+    if (!A || !B || !C1 || !C2 || M < 1 || N1 < 1 || N2 < 1 || K < 1) return -1;
+    return launch_skinny_acc(APlain{A, lda, 1, 1}, BPlain{B, 1, ldb, 0}, C1, ldc1, C2, ldc2, N1, M, N1 + N2, K, (cudaStream_t)stream);
+}
 
 int taco_op_set_precision(int precision) {
     if (precision != TACO_TRAIN_FP32 && precision != TACO_TRAIN_BF16) return -1;

@@ -28,12 +28,10 @@ int taco_op_decoder_loop_fwd(const TacoDecLoop* p, void* st) {
         const size_t oD = (size_t)s * B * D, oG = (size_t)s * B * G, nD = oD + (size_t)B * D;
         float* a1 = p->acts1 + oG;
         float* a2 = p->acts2 + oG;
-        OK(taco_op_gemm(p->ctx + (size_t)s * B * MD, MD, W1c, G, a1, G, B, G, MD, 0, 0, 1.f, nullptr, st));
-        OK(taco_op_gemm(p->h1z + oD, D, W1h, G, a1, G, B, G, D, 0, 0, 1.f, nullptr, st));
+        OK(taco_op_gemm_pair_acc(p->ctx + (size_t)s * B * MD, MD, MD, p->h1z + oD, D, D, W1c, G, a1, G, B, G, st));   // W1c | W1h adjacent rows
         OK(taco_op_lstm_fwd(a1, p->G1x + oG, nullptr, p->c1z + oD, p->h1z + oD, nullptr, 0, p->zoneout, 1, p->zo_keep_thresh, p->seed,
                             p->stream1, p->stream1 + 1, s * B, p->c1new + oD, p->c1z + nD, p->h1raw + oD, p->h1z + nD, B, D, st));
-        OK(taco_op_gemm(p->h1raw + oD, D, p->W2, G, a2, G, B, G, D, 0, 0, 1.f, nullptr, st));
-        OK(taco_op_gemm(p->h2z + oD, D, W2h, G, a2, G, B, G, D, 0, 0, 1.f, nullptr, st));
+        OK(taco_op_gemm_pair_acc(p->h1raw + oD, D, D, p->h2z + oD, D, D, p->W2, G, a2, G, B, G, st));
         OK(taco_op_lstm_fwd(a2, nullptr, p->b2, p->c2z + oD, p->h2z + oD, nullptr, 0, p->zoneout, 1, p->zo_keep_thresh, p->seed,
                             p->stream2, p->stream2 + 1, s * B, p->c2new + oD, p->c2z + nD, p->h2raw + oD, p->h2z + nD, B, D, st));
         float* q = p->q + (size_t)s * B * A;
@@ -80,12 +78,10 @@ int taco_op_decoder_loop_bwd(const TacoDecLoop* p, void* st) {
         OK(taco_op_gemm(dq, A, p->Wq, A, dh2, D, B, D, A, 0, 1, 1.f, nullptr, st));
         OK(taco_op_lstm_bwd(p->acts2 + oG, p->c2z + oD, p->h2z + oD, p->c2new + oD, nullptr, 0, p->zoneout, 1, p->zo_keep_thresh, p->seed,
                             p->stream2, p->stream2 + 1, s * B, dh2, dc2, dh2z, p->dG2 + oG, dc2n, dh2zn, B, D, st));
-        OK(taco_op_gemm(p->dG2 + oG, G, p->W2, G, dh1raw, D, B, D, G, 0, 1, 1.f, nullptr, st));
-        OK(taco_op_gemm(p->dG2 + oG, G, W2h, G, dh2zn, D, B, D, G, 0, 1, 1.f, nullptr, st));
+        OK(taco_op_gemm_nt_split_acc(p->dG2 + oG, G, p->W2, G, dh1raw, D, D, dh2zn, D, D, B, G, st));
         OK(taco_op_lstm_bwd(p->acts1 + oG, p->c1z + oD, p->h1z + oD, p->c1new + oD, nullptr, 0, p->zoneout, 1, p->zo_keep_thresh, p->seed,
                             p->stream1, p->stream1 + 1, s * B, dh1raw, dc1, dh1z, p->dG1 + oG, dc1n, dh1zn, B, D, st));
-        OK(taco_op_gemm(p->dG1 + oG, G, W1c, G, dctx_carry_out, MD, B, MD, G, 0, 1, 1.f, nullptr, st));
-        OK(taco_op_gemm(p->dG1 + oG, G, W1h, G, dh1zn, D, B, D, G, 0, 1, 1.f, nullptr, st));
+        OK(taco_op_gemm_nt_split_acc(p->dG1 + oG, G, W1c, G, dctx_carry_out, MD, MD, dh1zn, D, D, B, G, st));
         float* t_;
         t_ = dc1; dc1 = dc1n; dc1n = t_;
         t_ = dh1z; dh1z = dh1zn; dh1zn = t_;

@@ -82,18 +82,16 @@ __global__ void conv2d_wgrad_kernel(const float* __restrict__ x, const float* __
     __shared__ float sh[256];
     const int kci = blockIdx.x, ci = kci % Ci, k = kci / Ci, kh = k / 3, kw = k % 3;
     const int co = threadIdx.x % Co, pl_lane = threadIdx.x / Co, n_pl = blockDim.x / Co;
-    const long long npos = (long long)B * Ho * Wo;
+    const int npos = B * Ho * Wo;                 // < 2^31 (checked by the launcher): 32-bit index arithmetic
     float acc = 0.f;
 #pragma unroll 4
-    for (long long p = (long long)blockIdx.y * n_pl + pl_lane; p < npos; p += (long long)gridDim.y * n_pl) {
-        int wo = (int)(p % Wo);
-        long long r = p / Wo;
-        int ho = (int)(r % Ho);
-        int b = (int)(r / Ho);
+    for (int p = blockIdx.y * n_pl + pl_lane; p < npos; p += gridDim.y * n_pl) {
+        const int r = p / Wo, wo = p - r * Wo;
+        const int b = r / Ho, ho = r - b * Ho;
         int h = 2 * ho + kh - pt, ww = 2 * wo + kw - pl;
         const bool ok = h >= 0 && h < H && ww >= 0 && ww < W;      // predicated (no branch): loads of 4 iterations in flight
         const float xv = ok ? x[(((long long)b * H + h) * W + ww) * Ci + ci] : 0.f;
-        acc = fmaf(xv, dy[p * Co + co], acc);
+        acc = fmaf(xv, dy[(long long)p * Co + co], acc);
     }
     sh[threadIdx.x] = acc;
     __syncthreads();
@@ -202,6 +200,7 @@ int taco_op_conv2d_wgrad(const float* x, const float* dy, float* dw, int B, int 
     const int Ho = (H + 1) / 2, Wo = (W + 1) / 2;
     if (cudaMemsetAsync(dw, 0, sizeof(float) * 9 * (size_t)Ci * Co, ST) != cudaSuccess) return -3;
     const long long npos = (long long)B * Ho * Wo;
+    if (npos >= (1LL << 31) - 65536) return -1;
     const int n_pl = 256 / Co;
     int splits = (int)((npos / n_pl + 63) / 64);          // >= 64 positions per thread
     int cap = (148 * 16 + 9 * Ci - 1) / (9 * Ci);
