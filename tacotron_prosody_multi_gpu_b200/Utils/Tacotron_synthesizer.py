@@ -6,8 +6,9 @@ the TF-default random init with the reference's seed.  ``synthesize`` keeps the 
 pads the text list to a multiple of ``tacotron_num_gpus`` by repeating the last entry (:65-69), packs
 per-device batches along the time axis with ``split_infos`` (:77-84,99-105), runs the model, trims each
 mel at the first rounded stop token (:112, feeder :92-95), clips to the T2 output range (:131-135) and
-writes ``speech-mel-{basename}.npy`` float32 [len, 80] (:166-167).  Griffin-Lim wavs and matplotlib
-plots (:170-181) are emitted only if librosa / matplotlib are importable.
+writes ``speech-mel-{basename}.npy`` float32 [len, 80] (:166-167).  With ``log_dir`` the Griffin-Lim wav of every
+mel (:170-175) comes from the device path in Utils/AudioProcessing; the matplotlib plots
+(:176-181) are emitted only if the reference's plot helpers are importable.
 """
 import os
 
@@ -15,6 +16,7 @@ import numpy as np
 
 from ..TacotronModel.modules.Tacotron import Tacotron
 from .Infolog import log
+from .AudioProcessing.AudioPreprocess import inv_preemphasis, mel_to_audio_serie, save_wav
 from .Tacotron_feeder import _get_output_lengths, _prepare_inputs, _prepare_targets
 
 
@@ -94,7 +96,11 @@ class Synthesizer(object):
         mels = [np.clip(mel, lo, hi) for mel in mels]
         self.last_alignments, self.last_stop_tokens, self.last_mels = alignments, stop_tokens, mels
         if basenames is None:
-            raise RuntimeError('audio playback (basenames=None, Tacotron_synthesizer.py:137-149) needs the vocoder path (SURVEY 8f row f3)')
+            # Tacotron_synthesizer.py:137-149 writes temp.wav and shells out to a player; the waveform is produced and
+            # saved, playback is left to the caller
+            wav = mel_to_audio_serie(mels[0].T, hparams)
+            save_wav(wav, 'temp.wav', sr=hparams.sample_rate)
+            return
         saved_mels_paths, speaker_ids = [], []
         for i, mel in enumerate(mels):
             speaker_ids.append('<no_g>')
@@ -108,16 +114,20 @@ class Synthesizer(object):
     _warned = False
 
     def _emit_logs(self, mel, alignment, text, basename, log_dir):
+        """:170-181: Griffin-Lim wav (device path, include/taco_b200_audio.h) and, when the reference's matplotlib
+        helpers are importable, the alignment / mel plots."""
+        hp = self.hparams
+        os.makedirs(os.path.join(log_dir, 'wavs'), exist_ok=True)
+        if mel.shape[0] >= 5:   # librosa's reflect padding needs hop * (frames - 1) > n_fft / 2
+            wav = inv_preemphasis(mel_to_audio_serie(mel.T, hp), hp.preemphasis, hp.preemphasize)
+            save_wav(wav, os.path.join(log_dir, 'wavs/speech-wav-{}-mel.wav'.format(basename)), sr=hp.sample_rate)
         try:
-            from Utils.AudioProcessing.AudioPreprocess import inv_preemphasis, mel_to_audio_serie, save_wav  # reference module
-            from Utils.Plot import plot_alignment, plot_spectrogram
+            from Utils.Plot import plot_alignment, plot_spectrogram  # the reference's own module, if on sys.path
         except Exception:
             if not Synthesizer._warned:
-                log('wav / plot emission skipped (Griffin-Lim + matplotlib of the reference are not importable here)')
+                log('plot emission skipped (the reference\'s matplotlib helpers are not importable here)')
                 Synthesizer._warned = True
             return
-        hp = self.hparams
-        wav = inv_preemphasis(mel_to_audio_serie(mel.T, hp), hp.preemphasis, hp.preemphasize)
-        save_wav(wav, os.path.join(log_dir, 'wavs/speech-wav-{}-mel.wav'.format(basename)), sr=hp.sample_rate)
+        os.makedirs(os.path.join(log_dir, 'plots'), exist_ok=True)
         plot_alignment(alignment, os.path.join(log_dir, 'plots/speech-alignment-{}.png'.format(basename)), info=str(text), split_title=True)
         plot_spectrogram(mel, os.path.join(log_dir, 'plots/speech-mel-{}.png'.format(basename)), info=str(text), split_title=True)

@@ -16,7 +16,7 @@ CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(CSRC, "build")
 LIB = os.path.join(HERE, "libtaco_b200.so")
 SOURCES = ["api.cu", "decoder.cu", "decoder2.cu", "decoder3.cu", "conv.cu", "conv_tc.cu", "encoder.cu", "refenc.cu",
-           "train_gemm.cu", "train_ops.cu", "train_attn.cu", "train_misc.cu", "train_loops.cu"]
+           "train_gemm.cu", "train_ops.cu", "train_attn.cu", "train_misc.cu", "train_loops.cu", "griffin_lim.cu"]
 NVCC_FLAGS = ["-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
               "-Xcompiler", "-fPIC", "-Xptxas", "-v"]
 
@@ -41,6 +41,7 @@ def build(force=False, verbose=False):
     headers = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".h", ".cuh", ".inl"))]
     headers.append(os.path.join(os.path.dirname(HERE), "include", "taco_b200.h"))
     headers.append(os.path.join(os.path.dirname(HERE), "include", "taco_b200_train.h"))
+    headers.append(os.path.join(os.path.dirname(HERE), "include", "taco_b200_audio.h"))
     sources = [s for s in SOURCES if os.path.exists(os.path.join(CSRC, s))]
     jobs = []
     for s in sources:

@@ -1,0 +1,568 @@
+// Mel -> waveform (Griffin-Lim) for sm_100a: the C ABI of include/taco_b200_audio.h.
+//
+// Reference: Utils/AudioProcessing/AudioPreprocess.py:152-186 (mel_to_audio_serie) and the librosa stft / istft it calls
+// (center=True reflect padding, periodic Hann of win_size zero-padded to n_fft, window-sum-of-squares normalisation).
+//
+// One Griffin-Lim iteration is ONE kernel.  A CTA owns two adjacent frames of one utterance:
+//   1. gathers the overlap-added, window-sum-normalised signal under its two windows from the previous iteration's
+//      windowed frames (each sample: <= ceil(win/hop) frames, fixed order => deterministic, no atomics),
+//   2. packs frame 0 into the real and frame 1 into the imaginary part of one 2048-point complex FFT held in shared
+//      memory (Stockham autosort, radix 4,4,4,4,4,2, twiddles from a shared table computed in double precision),
+//   3. splits the two Hermitian spectra, replaces the moduli by the target magnitudes (phase kept),
+//   4. packs the two projected spectra into one inverse FFT, windows the two real outputs and writes them as the next
+//      iteration's frames.
+// HBM/L2 traffic per frame and iteration: n_bins magnitudes + ~(1 + hop/win) * 4 * win gathered samples read, win
+// samples written -- the spectra never leave shared memory.
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/taco_b200_audio.h"
+#include "common.cuh"
+
+namespace {
+
+constexpr int N = 2048;          // n_fft
+constexpr int NB = N / 2 + 1;    // bins
+constexpr int GL_THREADS = 256;
+constexpr uint32_t GLIM_TAG = 0x474C494D;
+
+__device__ __forceinline__ float2 cmul(float2 a, float2 b) { return make_float2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x); }
+
+// One Stockham pass of radix R over N points: in -> out.  tw[m] = exp(-2 pi i m / N); INV conjugates it.
+template <int R, bool INV>
+__device__ __forceinline__ void fft_pass(const float2* __restrict__ in, float2* __restrict__ out, const float2* __restrict__ tw, int Ns) {
+    constexpr int T = N / R;
+    const int tstride = N / (Ns * R);
+    for (int j = threadIdx.x; j < T; j += GL_THREADS) {
+        const int k = j & (Ns - 1);
+        float2 v[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            v[r] = in[j + r * T];
+            if (r > 0) {
+                float2 w = tw[(r * k * tstride) & (N - 1)];
+                if (INV) w.y = -w.y;
+                v[r] = cmul(v[r], w);
+            }
+        }
+        const int j0 = (j - k) * R + k;
+        if (R == 4) {
+            const float2 a0 = make_float2(v[0].x + v[2].x, v[0].y + v[2].y);
+            const float2 a1 = make_float2(v[0].x - v[2].x, v[0].y - v[2].y);
+            const float2 a2 = make_float2(v[1].x + v[3].x, v[1].y + v[3].y);
+            const float2 d = make_float2(v[1].x - v[3].x, v[1].y - v[3].y);
+            const float2 a3 = INV ? make_float2(-d.y, d.x) : make_float2(d.y, -d.x);   // * (+i) / (-i)
+            out[j0] = make_float2(a0.x + a2.x, a0.y + a2.y);
+            out[j0 + Ns] = make_float2(a1.x + a3.x, a1.y + a3.y);
+            out[j0 + 2 * Ns] = make_float2(a0.x - a2.x, a0.y - a2.y);
+            out[j0 + 3 * Ns] = make_float2(a1.x - a3.x, a1.y - a3.y);
+        } else {
+            out[j0] = make_float2(v[0].x + v[1].x, v[0].y + v[1].y);
+            out[j0 + Ns] = make_float2(v[0].x - v[1].x, v[0].y - v[1].y);
+        }
+    }
+    __syncthreads();
+}
+
+// 2048-point FFT, a -> a (b is scratch): six passes, the data ends in the buffer it started in.
+template <bool INV>
+__device__ __forceinline__ void fft2048(float2* a, float2* b, const float2* tw) {
+    fft_pass<4, INV>(a, b, tw, 1);
+    fft_pass<4, INV>(b, a, tw, 4);
+    fft_pass<4, INV>(a, b, tw, 16);
+    fft_pass<4, INV>(b, a, tw, 64);
+    fft_pass<4, INV>(a, b, tw, 256);
+    fft_pass<2, INV>(b, a, tw, 1024);
+}
+
+struct GlGeom {
+    int hop, win, lpad;      // lpad = (N - win) / 2: first non-zero tap of the padded window
+    int cover;               // ceil(win / hop): frames over one sample
+};
+
+// Overlap-added, normalised signal sample n (0 <= n < hop * (F - 1)) from the windowed frames yf [F][win]
+// (librosa.istft: y[i*hop : i*hop + n_fft] += w * irfft(S_i); y /= sum w^2 where > tiny; y = y[n_fft/2 : -n_fft/2]).
+__device__ __forceinline__ float ola_sample(const float* __restrict__ yf, const float* __restrict__ w, const GlGeom g, int F, int n) {
+    const int q = n + N / 2 - g.lpad;                       // position relative to frame 0's first tap
+    int i_hi = q / g.hop;
+    if (i_hi > F - 1) i_hi = F - 1;
+    int i_lo = (q - g.win + g.hop) / g.hop;                 // ceil((q - win + 1) / hop) for q - win + 1 >= 0
+    if (q - g.win + 1 <= 0) i_lo = 0;
+    float acc = 0.f, ws = 0.f;
+    for (int i = i_lo; i <= i_hi; ++i) {
+        const int j = q - i * g.hop;
+        const float wj = __ldg(w + j);
+        acc += yf[(size_t)i * g.win + j];
+        ws = fmaf(wj, wj, ws);
+    }
+    return ws > 1.17549435e-38f ? acc / ws : acc;
+}
+
+__device__ __forceinline__ float glim_turns(uint64_t seed, uint32_t utt, uint64_t idx) {
+    const uint64_t blk = idx >> 2;
+    const uint4 o = philox4x32_10(make_uint4((uint32_t)blk, utt, (uint32_t)(blk >> 32), GLIM_TAG),
+                                  make_uint2((uint32_t)seed, (uint32_t)(seed >> 32)));
+    const uint32_t lane = (uint32_t)idx & 3u;
+    const uint32_t word = lane == 0 ? o.x : lane == 1 ? o.y : lane == 2 ? o.z : o.w;
+    return (float)(word >> 8) * (1.0f / 16777216.0f);
+}
+
+}  // namespace
+
+namespace {
+
+enum { GL_FIRST = 0, GL_ITER = 1, GL_MEASURE = 2 };
+
+struct GlArgs {
+    const float* mag;        // [B,F,NB]
+    const float* turns;      // [B,F,NB] or null (GL_FIRST)
+    const float* yf_in;      // [B,F,win] windowed frames of the previous iteration (GL_ITER)
+    const float* sig;        // [B,sig_stride] signal (GL_MEASURE)
+    long long sig_stride;
+    float* yf_out;           // [B,F,win]
+    float* dist_acc;         // [B,2] (GL_MEASURE)
+    const int32_t* n_frames; // [B] or null
+    const float2* tw;        // [N]
+    const float* w;          // [win]
+    GlGeom g;
+    int F;
+    uint64_t seed;
+    int utt0;
+};
+
+template <int MODE>
+__global__ void __launch_bounds__(GL_THREADS) gl_kernel(const GlArgs a) {
+    extern __shared__ float2 gl_smem[];
+    float2* A = gl_smem;
+    float2* Bf = gl_smem + N;
+    float2* tw = gl_smem + 2 * N;
+    const int b = blockIdx.y, t0 = blockIdx.x * 2, tid = threadIdx.x;
+    const int Fb = a.n_frames ? a.n_frames[b] : a.F;
+    if (t0 >= Fb) return;
+    const bool has1 = t0 + 1 < Fb;
+    const GlGeom g = a.g;
+    const float* mag0 = a.mag + ((size_t)b * a.F + t0) * NB;
+    for (int i = tid; i < N; i += GL_THREADS) tw[i] = a.tw[i];
+
+    if (MODE != GL_FIRST) {
+        float* seg = reinterpret_cast<float*>(Bf);
+        const int L = g.hop * (Fb - 1);
+        const float* yf = a.yf_in ? a.yf_in + (size_t)b * a.F * g.win : nullptr;
+        for (int i = tid; i < g.win + g.hop; i += GL_THREADS) {
+            int n = t0 * g.hop + g.lpad + i - N / 2;
+            if (n < 0) n = -n;                       // np.pad(mode='reflect')
+            if (n >= L) n = 2 * (L - 1) - n;
+            n = min(max(n, 0), L - 1);
+            seg[i] = MODE == GL_MEASURE ? a.sig[(size_t)b * a.sig_stride + n] : ola_sample(yf, a.w, g, Fb, n);
+        }
+        __syncthreads();
+        for (int j = tid; j < N; j += GL_THREADS) {
+            const int jj = j - g.lpad;
+            float2 z = make_float2(0.f, 0.f);
+            if (jj >= 0 && jj < g.win) {
+                const float wj = __ldg(a.w + jj);
+                z.x = wj * seg[jj];
+                z.y = has1 ? wj * seg[jj + g.hop] : 0.f;
+            }
+            A[j] = z;
+        }
+        __syncthreads();
+        fft2048<false>(A, Bf, tw);
+    } else {
+        __syncthreads();
+    }
+
+    float err = 0.f, ref = 0.f;
+    for (int k = tid; k <= N / 2; k += GL_THREADS) {
+        const float m0 = mag0[k];
+        const float m1 = has1 ? mag0[NB + k] : 0.f;
+        float2 P0, P1;
+        if (MODE == GL_FIRST) {
+            float u0, u1 = 0.f;
+            if (a.turns) {
+                const float* tr = a.turns + ((size_t)b * a.F + t0) * NB;
+                u0 = tr[k];
+                if (has1) u1 = tr[NB + k];
+            } else {
+                u0 = glim_turns(a.seed, (uint32_t)(b + a.utt0), (uint64_t)k * Fb + t0);
+                if (has1) u1 = glim_turns(a.seed, (uint32_t)(b + a.utt0), (uint64_t)k * Fb + t0 + 1);
+            }
+            float s, c;
+            sincospif(2.f * u0, &s, &c);
+            P0 = make_float2(m0 * c, m0 * s);
+            sincospif(2.f * u1, &s, &c);
+            P1 = make_float2(m1 * c, m1 * s);
+        } else {
+            const float2 Zk = A[k], Zn = A[(N - k) & (N - 1)];
+            const float2 X0 = make_float2(0.5f * (Zk.x + Zn.x), 0.5f * (Zk.y - Zn.y));   // (Z[k] + conj Z[N-k]) / 2
+            const float2 X1 = make_float2(0.5f * (Zk.y + Zn.y), 0.5f * (Zn.x - Zk.x));   // (Z[k] - conj Z[N-k]) / 2i
+            const float r0 = sqrtf(X0.x * X0.x + X0.y * X0.y), r1 = sqrtf(X1.x * X1.x + X1.y * X1.y);
+            if (MODE == GL_MEASURE) {
+                err += (r0 - m0) * (r0 - m0) + (has1 ? (r1 - m1) * (r1 - m1) : 0.f);
+                ref += m0 * m0 + m1 * m1;
+                continue;
+            }
+            const float s0 = r0 > 0.f ? m0 / r0 : 0.f, s1 = r1 > 0.f ? m1 / r1 : 0.f;   // exp(i angle(X)); angle(0) = 0
+            P0 = r0 > 0.f ? make_float2(X0.x * s0, X0.y * s0) : make_float2(m0, 0.f);
+            P1 = r1 > 0.f ? make_float2(X1.x * s1, X1.y * s1) : make_float2(m1, 0.f);
+        }
+        if (k == 0 || k == N / 2) P0.y = P1.y = 0.f;       // irfft ignores the imaginary part of DC / Nyquist
+        Bf[k] = make_float2(P0.x - P1.y, P0.y + P1.x);      // P0 + i P1
+        if (k > 0 && k < N / 2) Bf[N - k] = make_float2(P0.x + P1.y, P1.x - P0.y);   // conj P0 + i conj P1
+    }
+    if (MODE == GL_MEASURE) {
+        __shared__ float red[2][GL_THREADS / 32];
+        for (int o = 16; o; o >>= 1) {
+            err += __shfl_xor_sync(0xffffffffu, err, o);
+            ref += __shfl_xor_sync(0xffffffffu, ref, o);
+        }
+        if ((tid & 31) == 0) { red[0][tid >> 5] = err; red[1][tid >> 5] = ref; }
+        __syncthreads();
+        if (tid == 0) {
+            float e = 0.f, r = 0.f;
+            for (int i = 0; i < GL_THREADS / 32; ++i) { e += red[0][i]; r += red[1][i]; }
+            atomicAdd(a.dist_acc + 2 * b, e);
+            atomicAdd(a.dist_acc + 2 * b + 1, r);
+        }
+        return;
+    }
+    __syncthreads();
+    fft2048<true>(Bf, A, tw);
+    float* out0 = a.yf_out + ((size_t)b * a.F + t0) * g.win;
+    for (int j = tid; j < g.win; j += GL_THREADS) {
+        const float wj = __ldg(a.w + j) * (1.0f / N);
+        const float2 z = Bf[g.lpad + j];
+        out0[j] = wj * z.x;
+        if (has1) out0[g.win + j] = wj * z.y;
+    }
+}
+
+__global__ void gl_dist_final_kernel(const float* acc, float* out, int B) {
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b < B) out[b] = acc[2 * b + 1] > 0.f ? sqrtf(acc[2 * b] / acc[2 * b + 1]) : 0.f;
+}
+
+// final overlap-add of the last iteration's frames into the waveform
+__global__ void gl_ola_kernel(const float* __restrict__ yf, const float* __restrict__ w, GlGeom g, const int32_t* n_frames, int F,
+                              float* __restrict__ audio, long long stride) {
+    const int b = blockIdx.y;
+    const int Fb = n_frames ? n_frames[b] : F;
+    const long long L = (long long)g.hop * (Fb - 1);
+    for (long long n = (long long)blockIdx.x * blockDim.x + threadIdx.x; n < stride; n += (long long)gridDim.x * blockDim.x)
+        audio[b * stride + n] = n < L ? ola_sample(yf + (size_t)b * F * g.win, w, g, Fb, (int)n) : 0.f;
+}
+
+// y[n] = x[n] + k y[n-1] (scipy.signal.lfilter([1], [1, -k])), in place; one CTA per utterance, chunked scan
+__global__ void __launch_bounds__(1024) gl_deemphasis_kernel(float* audio, long long stride, GlGeom g, const int32_t* n_frames, int F, float k) {
+    __shared__ float tail[1024];
+    __shared__ float carry[1024];
+    const int b = blockIdx.x, tid = threadIdx.x;
+    const int Fb = n_frames ? n_frames[b] : F;
+    const int L = g.hop * (Fb - 1);
+    const int C = (L + 1023) / 1024;
+    float* x = audio + b * stride;
+    const int lo = min(tid * C, L), hi = min(lo + C, L);
+    float acc = 0.f;
+    for (int i = lo; i < hi; ++i) { acc = fmaf(k, acc, x[i]); x[i] = acc; }
+    tail[tid] = acc;
+    __syncthreads();
+    if (tid == 0) {
+        float c = 0.f;
+        for (int t = 0; t < 1024; ++t) {
+            carry[t] = c;                                   // true y just before chunk t
+            const int len = min(max(L - t * C, 0), C);
+            c = tail[t] + powf(k, (float)len) * c;
+        }
+    }
+    __syncthreads();
+    float pw = k * carry[tid];
+    for (int i = lo; i < hi; ++i) { x[i] += pw; pw *= k; }
+}
+
+struct MelNormDev { int sn, clip, sym; float m, lo, ref, power; };
+
+// mag[b,t,k] = max(1e-10, sum_m inv[k,m] * 10^((denorm(mel[b,t,m]) + ref) / 20)) ^ power; 8 frames per CTA share the basis reads
+constexpr int MM_FRAMES = 8;
+__global__ void __launch_bounds__(256) gl_mel_to_mag_kernel(const float* __restrict__ mel, const int32_t* n_frames, int F, int n_mels,
+                                                             const float* __restrict__ invT /*[n_mels][NB]*/, MelNormDev nm,
+                                                             float* __restrict__ mag) {
+    extern __shared__ float amp[];   // [MM_FRAMES][n_mels]
+    const int b = blockIdx.y, t0 = blockIdx.x * MM_FRAMES;
+    const int Fb = n_frames ? n_frames[b] : F;
+    for (int i = threadIdx.x; i < MM_FRAMES * n_mels; i += blockDim.x) {
+        const int f = i / n_mels, m = i - f * n_mels, t = t0 + f;
+        float v = 0.f;
+        if (t < Fb) {
+            float d = mel[((size_t)b * F + t) * n_mels + m];
+            if (nm.sn) {
+                if (nm.sym) {
+                    if (nm.clip) d = fminf(fmaxf(d, -nm.m), nm.m);
+                    d = (d + nm.m) * -nm.lo / (2.f * nm.m) + nm.lo;
+                } else {
+                    if (nm.clip) d = fminf(fmaxf(d, 0.f), nm.m);
+                    d = d * -nm.lo / nm.m + nm.lo;
+                }
+            }
+            v = exp10f((d + nm.ref) * 0.05f);
+        }
+        amp[i] = v;
+    }
+    __syncthreads();
+    for (int k = threadIdx.x; k < NB; k += blockDim.x) {
+        float acc[MM_FRAMES];
+#pragma unroll
+        for (int f = 0; f < MM_FRAMES; ++f) acc[f] = 0.f;
+        for (int m = 0; m < n_mels; ++m) {
+            const float bv = __ldg(invT + (size_t)m * NB + k);
+#pragma unroll
+            for (int f = 0; f < MM_FRAMES; ++f) acc[f] = fmaf(bv, amp[f * n_mels + m], acc[f]);
+        }
+#pragma unroll
+        for (int f = 0; f < MM_FRAMES; ++f) {
+            const int t = t0 + f;
+            if (t < F) mag[((size_t)b * F + t) * NB + k] = t < Fb ? powf(fmaxf(acc[f], 1e-10f), nm.power) : 0.f;
+        }
+    }
+}
+
+}  // namespace
+
+struct TacoGl {
+    int device = 0;
+    GlGeom g{};
+    int n_mels = 0;
+    float2* tw = nullptr;      // [N]
+    float* w = nullptr;        // [win]
+    float* invT = nullptr;     // [n_mels][NB]
+    float* yf[2] = {nullptr, nullptr};
+    size_t yf_floats = 0;
+    float* dist_acc = nullptr;
+    size_t dist_cap = 0;
+    std::string err;
+};
+
+namespace {
+
+constexpr size_t GL_SMEM = 3 * N * sizeof(float2);
+
+int gl_fail(TacoGl* g, int code, const char* what, cudaError_t e = cudaSuccess) {
+    if (g) {
+        g->err = what;
+        if (e != cudaSuccess) { g->err += ": "; g->err += cudaGetErrorString(e); }
+    }
+    return code;
+}
+
+#define GL_CUDA(call)                                                        \
+    do {                                                                     \
+        cudaError_t e_ = (call);                                             \
+        if (e_ != cudaSuccess) return gl_fail(g, e_ == cudaErrorMemoryAllocation ? -2 : -3, #call, e_); \
+    } while (0)
+
+int gl_reserve(TacoGl* g, int B, int F) {
+    const size_t need = (size_t)B * F * g->g.win;
+    if (need > g->yf_floats) {
+        for (int i = 0; i < 2; ++i) {
+            if (g->yf[i]) cudaFree(g->yf[i]);
+            g->yf[i] = nullptr;
+        }
+        g->yf_floats = 0;
+        GL_CUDA(cudaMalloc(&g->yf[0], need * sizeof(float)));
+        GL_CUDA(cudaMalloc(&g->yf[1], need * sizeof(float)));
+        g->yf_floats = need;
+    }
+    if ((size_t)B > g->dist_cap) {
+        if (g->dist_acc) cudaFree(g->dist_acc);
+        g->dist_acc = nullptr;
+        g->dist_cap = 0;
+        GL_CUDA(cudaMalloc(&g->dist_acc, (size_t)B * 2 * sizeof(float)));
+        g->dist_cap = B;
+    }
+    return 0;
+}
+
+template <int MODE>
+int gl_launch(TacoGl* g, const GlArgs& a, int B, cudaStream_t st) {
+    static bool attr_done = false;
+    if (!attr_done) {
+        GL_CUDA(cudaFuncSetAttribute(gl_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GL_SMEM));
+        attr_done = true;
+    }
+    dim3 grid((a.F + 1) / 2, B);
+    gl_kernel<MODE><<<grid, GL_THREADS, GL_SMEM, st>>>(a);
+    GL_CUDA(cudaGetLastError());
+    return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+int taco_gl_create(int device, int n_fft, int hop, int win, int n_mels, const float* inv_mel_basis, TacoGl** out) {
+    if (!out) return -1;
+    *out = nullptr;
+    if (n_fft != N || hop < 1 || win < hop || win > N || (win & 1) || n_mels < 1 || n_mels > 512 || !inv_mel_basis) return -1;
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || device < 0 || device >= count) return -3;
+    TacoGl* g = new TacoGl();
+    g->device = device;
+    g->g.hop = hop;
+    g->g.win = win;
+    g->g.lpad = (N - win) / 2;
+    g->g.cover = (win + hop - 1) / hop;
+    g->n_mels = n_mels;
+    std::vector<float2> tw(N);
+    for (int m = 0; m < N; ++m) {
+        const double ang = -2.0 * 3.14159265358979323846 * m / N;
+        tw[m] = make_float2((float)cos(ang), (float)sin(ang));
+    }
+    std::vector<float> w(win);
+    for (int j = 0; j < win; ++j) w[j] = (float)(0.5 - 0.5 * cos(2.0 * 3.14159265358979323846 * j / win));   // periodic Hann
+    std::vector<float> invT((size_t)n_mels * NB);
+    for (int k = 0; k < NB; ++k)
+        for (int m = 0; m < n_mels; ++m) invT[(size_t)m * NB + k] = inv_mel_basis[(size_t)k * n_mels + m];
+    cudaError_t e = cudaSetDevice(device);
+    if (e == cudaSuccess) e = cudaMalloc(&g->tw, N * sizeof(float2));
+    if (e == cudaSuccess) e = cudaMalloc(&g->w, win * sizeof(float));
+    if (e == cudaSuccess) e = cudaMalloc(&g->invT, invT.size() * sizeof(float));
+    if (e == cudaSuccess) e = cudaMemcpy(g->tw, tw.data(), N * sizeof(float2), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(g->w, w.data(), win * sizeof(float), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(g->invT, invT.data(), invT.size() * sizeof(float), cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) {
+        taco_gl_destroy(g);
+        return e == cudaErrorMemoryAllocation ? -2 : -3;
+    }
+    *out = g;
+    return 0;
+}
+
+void taco_gl_destroy(TacoGl* g) {
+    if (!g) return;
+    cudaFree(g->tw);
+    cudaFree(g->w);
+    cudaFree(g->invT);
+    cudaFree(g->yf[0]);
+    cudaFree(g->yf[1]);
+    cudaFree(g->dist_acc);
+    delete g;
+}
+
+const char* taco_gl_last_error(const TacoGl* g) { return g ? g->err.c_str() : "null plan"; }
+
+int taco_gl_mel_to_mag(TacoGl* g, const float* mel_dev, const int32_t* n_frames_dev, int B, int F, const TacoMelNorm* norm,
+                       float* mag_dev, void* stream) {
+    if (!g) return -1;
+    if (!mel_dev || !mag_dev || !norm || B < 1 || F < 1) return gl_fail(g, -1, "taco_gl_mel_to_mag: bad argument");
+    MelNormDev nm{norm->signal_normalization, norm->allow_clipping_in_normalization, norm->symmetric_mels, norm->max_abs_value,
+                  norm->min_level_db, norm->ref_level_db, norm->power};
+    dim3 grid((F + MM_FRAMES - 1) / MM_FRAMES, B);
+    gl_mel_to_mag_kernel<<<grid, 256, MM_FRAMES * g->n_mels * sizeof(float), (cudaStream_t)stream>>>(mel_dev, n_frames_dev, F, g->n_mels,
+                                                                                                  g->invT, nm, mag_dev);
+    GL_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int taco_gl_griffin_lim(TacoGl* g, const float* mag_dev, const float* turns_dev, const int32_t* n_frames_dev, uint64_t seed,
+                        int utterance0, int B, int F, int iters, float preemphasis_k, float* audio_dev, long long audio_stride,
+                        void* stream) {
+    if (!g) return -1;
+    if (!mag_dev || !audio_dev || B < 1 || F < 2 || iters < 0 || audio_stride < (long long)g->g.hop * (F - 1))
+        return gl_fail(g, -1, "taco_gl_griffin_lim: bad argument");
+    if ((long long)g->g.hop * (F - 1) <= N / 2 && !n_frames_dev)
+        return gl_fail(g, -1, "taco_gl_griffin_lim: hop * (frames - 1) must exceed n_fft / 2 (reflect padding)");
+    cudaStream_t st = (cudaStream_t)stream;
+    if (int rc = gl_reserve(g, B, F)) return rc;
+    GlArgs a{};
+    a.mag = mag_dev;
+    a.turns = turns_dev;
+    a.n_frames = n_frames_dev;
+    a.tw = g->tw;
+    a.w = g->w;
+    a.g = g->g;
+    a.F = F;
+    a.seed = seed;
+    a.utt0 = utterance0;
+    a.yf_out = g->yf[0];
+    if (int rc = gl_launch<GL_FIRST>(g, a, B, st)) return rc;
+    int cur = 0;
+    for (int it = 0; it < iters; ++it) {
+        a.yf_in = g->yf[cur];
+        a.yf_out = g->yf[cur ^ 1];
+        if (int rc = gl_launch<GL_ITER>(g, a, B, st)) return rc;
+        cur ^= 1;
+    }
+    const int gx = (int)((audio_stride + 255) / 256 < 4096 ? (audio_stride + 255) / 256 : 4096);
+    gl_ola_kernel<<<dim3(gx, B), 256, 0, st>>>(g->yf[cur], g->w, g->g, n_frames_dev, F, audio_dev, audio_stride);
+    GL_CUDA(cudaGetLastError());
+    if (preemphasis_k != 0.f) {
+        gl_deemphasis_kernel<<<B, 1024, 0, st>>>(audio_dev, audio_stride, g->g, n_frames_dev, F, preemphasis_k);
+        GL_CUDA(cudaGetLastError());
+    }
+    return 0;
+}
+
+int taco_gl_spectral_distance(TacoGl* g, const float* audio_dev, long long audio_stride, const float* mag_dev,
+                              const int32_t* n_frames_dev, int B, int F, float* out_dev, void* stream) {
+    if (!g) return -1;
+    if (!audio_dev || !mag_dev || !out_dev || B < 1 || F < 2) return gl_fail(g, -1, "taco_gl_spectral_distance: bad argument");
+    cudaStream_t st = (cudaStream_t)stream;
+    if (int rc = gl_reserve(g, B, F)) return rc;
+    GL_CUDA(cudaMemsetAsync(g->dist_acc, 0, (size_t)B * 2 * sizeof(float), st));
+    GlArgs a{};
+    a.mag = mag_dev;
+    a.sig = audio_dev;
+    a.sig_stride = audio_stride;
+    a.dist_acc = g->dist_acc;
+    a.n_frames = n_frames_dev;
+    a.tw = g->tw;
+    a.w = g->w;
+    a.g = g->g;
+    a.F = F;
+    if (int rc = gl_launch<GL_MEASURE>(g, a, B, st)) return rc;
+    gl_dist_final_kernel<<<(B + 127) / 128, 128, 0, st>>>(g->dist_acc, out_dev, B);
+    GL_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int taco_mel_to_audio(TacoGl* g, const float* mel_host, const int32_t* n_frames_host, int B, int F, const TacoMelNorm* norm,
+                      uint64_t seed, int utterance0, int iters, float preemphasis_k, float* audio_host, long long audio_stride) {
+    if (!g) return -1;
+    if (!mel_host || !audio_host || !norm || B < 1 || F < 2 || audio_stride < (long long)g->g.hop * (F - 1))
+        return gl_fail(g, -1, "taco_mel_to_audio: bad argument");
+    for (int b = 0; b < B; ++b) {
+        const int fb = n_frames_host ? n_frames_host[b] : F;
+        if (fb > F || (long long)g->g.hop * (fb - 1) <= N / 2)
+            return gl_fail(g, -1, "taco_mel_to_audio: every utterance needs hop * (frames - 1) > n_fft / 2 and frames <= F");
+    }
+    GL_CUDA(cudaSetDevice(g->device));
+    float *mel = nullptr, *mag = nullptr, *audio = nullptr;
+    int32_t* nf = nullptr;
+    const size_t n_mel = (size_t)B * F * g->n_mels, n_mag = (size_t)B * F * NB, n_audio = (size_t)B * audio_stride;
+    int rc = 0;
+    cudaError_t e = cudaMalloc(&mel, n_mel * sizeof(float));
+    if (e == cudaSuccess) e = cudaMalloc(&mag, n_mag * sizeof(float));
+    if (e == cudaSuccess) e = cudaMalloc(&audio, n_audio * sizeof(float));
+    if (e == cudaSuccess && n_frames_host) e = cudaMalloc(&nf, B * sizeof(int32_t));
+    if (e == cudaSuccess) e = cudaMemcpy(mel, mel_host, n_mel * sizeof(float), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess && nf) e = cudaMemcpy(nf, n_frames_host, B * sizeof(int32_t), cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) rc = gl_fail(g, e == cudaErrorMemoryAllocation ? -2 : -3, "taco_mel_to_audio: staging", e);
+    if (!rc) rc = taco_gl_mel_to_mag(g, mel, nf, B, F, norm, mag, nullptr);
+    if (!rc) rc = taco_gl_griffin_lim(g, mag, nullptr, nf, seed, utterance0, B, F, iters, preemphasis_k, audio, audio_stride, nullptr);
+    if (!rc) {
+        e = cudaMemcpy(audio_host, audio, n_audio * sizeof(float), cudaMemcpyDeviceToHost);
+        if (e != cudaSuccess) rc = gl_fail(g, -3, "taco_mel_to_audio: read back", e);
+    }
+    cudaFree(mel);
+    cudaFree(mag);
+    cudaFree(audio);
+    cudaFree(nf);
+    return rc;
+}
+
+}  // extern "C"

@@ -188,6 +188,18 @@ def default_hparams():
         clip_mels_length=True,
         max_mel_frames=1000,
         hop_size=275,
+        n_fft=2048,
+        win_size=1024,
+        frame_shift_ms=None,
+        fmin=25,
+        fmax=7600,
+        min_level_db=-100,
+        ref_level_db=20,
+        power=1.2,
+        griffin_lim_iters=60,
+        signal_normalization=True,
+        allow_clipping_in_normalization=True,
+        use_lws=False,
         preemphasize=False,
         preemphasis=0.97,
         gin_channels=-1,
