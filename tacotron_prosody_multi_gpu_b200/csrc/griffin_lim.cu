@@ -7,7 +7,8 @@
 //   1. gathers the overlap-added, window-sum-normalised signal under its two windows from the previous iteration's
 //      windowed frames (each sample: <= ceil(win/hop) frames, fixed order => deterministic, no atomics),
 //   2. packs frame 0 into the real and frame 1 into the imaginary part of one 2048-point complex FFT held in shared
-//      memory (Stockham autosort, radix 4,4,4,4,4,2, twiddles from a shared table computed in double precision),
+//      memory (Stockham autosort, radix 8,8,8,4 in registers, padded against bank conflicts, twiddles from an L1-resident
+//      table computed in double precision),
 //   3. splits the two Hermitian spectra, replaces the moduli by the target magnitudes (phase kept),
 //   4. packs the two projected spectra into one inverse FFT, windows the two real outputs and writes them as the next
 //      iteration's frames.
@@ -34,51 +35,79 @@ constexpr uint32_t GLIM_TAG = 0x474C494D;
 
 __device__ __forceinline__ float2 cmul(float2 a, float2 b) { return make_float2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x); }
 
-// One Stockham pass of radix R over N points: in -> out.  tw[m] = exp(-2 pi i m / N); INV conjugates it.
-template <int R, bool INV>
-__device__ __forceinline__ void fft_pass(const float2* __restrict__ in, float2* __restrict__ out, const float2* __restrict__ tw, int Ns) {
+// Shared-memory index of FFT point i: one pad slot per 16 points keeps the radix-8 scatter of the first pass conflict-free.
+__device__ __forceinline__ int pad(int i) { return i + (i >> 4); }
+constexpr int NP = N + N / 16;
+// Twiddle table (global, L1-resident): pass p with radix R and Ns = product of the earlier radices holds
+// exp(-2 pi i r k / (Ns R)) at TW_OFF_p + k (R - 1) + (r - 1); the first pass (Ns = 1) needs none.
+constexpr int TW_OFF1 = 0, TW_OFF2 = TW_OFF1 + 8 * 7, TW_OFF3 = TW_OFF2 + 64 * 7, TW_TOTAL = TW_OFF3 + 512 * 3;
+
+template <bool INV>
+__device__ __forceinline__ void dft4(float2& x0, float2& x1, float2& x2, float2& x3) {
+    const float2 a0 = make_float2(x0.x + x2.x, x0.y + x2.y);
+    const float2 a1 = make_float2(x0.x - x2.x, x0.y - x2.y);
+    const float2 a2 = make_float2(x1.x + x3.x, x1.y + x3.y);
+    const float2 d = make_float2(x1.x - x3.x, x1.y - x3.y);
+    const float2 a3 = INV ? make_float2(-d.y, d.x) : make_float2(d.y, -d.x);   // * (+i) / (-i)
+    x0 = make_float2(a0.x + a2.x, a0.y + a2.y);
+    x1 = make_float2(a1.x + a3.x, a1.y + a3.y);
+    x2 = make_float2(a0.x - a2.x, a0.y - a2.y);
+    x3 = make_float2(a1.x - a3.x, a1.y - a3.y);
+}
+
+// 8-point DFT in registers, natural order out: X[2m] = DFT4(v[n] + v[n+4]), X[2m+1] = DFT4((v[n] - v[n+4]) W8^n)
+template <bool INV>
+__device__ __forceinline__ void dft8(float2 (&v)[8]) {
+    constexpr float S = 0.70710678118654752f;
+    float2 e0 = make_float2(v[0].x + v[4].x, v[0].y + v[4].y), o0 = make_float2(v[0].x - v[4].x, v[0].y - v[4].y);
+    float2 e1 = make_float2(v[1].x + v[5].x, v[1].y + v[5].y), d1 = make_float2(v[1].x - v[5].x, v[1].y - v[5].y);
+    float2 e2 = make_float2(v[2].x + v[6].x, v[2].y + v[6].y), d2 = make_float2(v[2].x - v[6].x, v[2].y - v[6].y);
+    float2 e3 = make_float2(v[3].x + v[7].x, v[3].y + v[7].y), d3 = make_float2(v[3].x - v[7].x, v[3].y - v[7].y);
+    float2 o1 = INV ? make_float2(S * (d1.x - d1.y), S * (d1.x + d1.y)) : make_float2(S * (d1.x + d1.y), S * (d1.y - d1.x));
+    float2 o2 = INV ? make_float2(-d2.y, d2.x) : make_float2(d2.y, -d2.x);
+    float2 o3 = INV ? make_float2(-S * (d3.x + d3.y), S * (d3.x - d3.y)) : make_float2(S * (d3.y - d3.x), -S * (d3.x + d3.y));
+    dft4<INV>(e0, e1, e2, e3);
+    dft4<INV>(o0, o1, o2, o3);
+    v[0] = e0; v[1] = o0; v[2] = e1; v[3] = o1; v[4] = e2; v[5] = o2; v[6] = e3; v[7] = o3;
+}
+
+// One Stockham autosort pass of radix R (Ns = product of the earlier radices): in -> out, both padded.
+template <int R, int Ns, bool INV>
+__device__ __forceinline__ void fft_pass(const float2* __restrict__ in, float2* __restrict__ out, const float2* __restrict__ twp) {
     constexpr int T = N / R;
-    const int tstride = N / (Ns * R);
+#pragma unroll
     for (int j = threadIdx.x; j < T; j += GL_THREADS) {
-        const int k = j & (Ns - 1);
+        const int k = j & (Ns - 1), pj = pad(j);
         float2 v[R];
 #pragma unroll
-        for (int r = 0; r < R; ++r) {
-            v[r] = in[j + r * T];
-            if (r > 0) {
-                float2 w = tw[(r * k * tstride) & (N - 1)];
+        for (int r = 0; r < R; ++r) v[r] = in[pj + r * (T + T / 16)];       // pad(j + r T): T is a multiple of 16
+        if (Ns > 1) {
+#pragma unroll
+            for (int r = 1; r < R; ++r) {
+                float2 w = __ldg(twp + k * (R - 1) + (r - 1));
                 if (INV) w.y = -w.y;
                 v[r] = cmul(v[r], w);
             }
         }
-        const int j0 = (j - k) * R + k;
-        if (R == 4) {
-            const float2 a0 = make_float2(v[0].x + v[2].x, v[0].y + v[2].y);
-            const float2 a1 = make_float2(v[0].x - v[2].x, v[0].y - v[2].y);
-            const float2 a2 = make_float2(v[1].x + v[3].x, v[1].y + v[3].y);
-            const float2 d = make_float2(v[1].x - v[3].x, v[1].y - v[3].y);
-            const float2 a3 = INV ? make_float2(-d.y, d.x) : make_float2(d.y, -d.x);   // * (+i) / (-i)
-            out[j0] = make_float2(a0.x + a2.x, a0.y + a2.y);
-            out[j0 + Ns] = make_float2(a1.x + a3.x, a1.y + a3.y);
-            out[j0 + 2 * Ns] = make_float2(a0.x - a2.x, a0.y - a2.y);
-            out[j0 + 3 * Ns] = make_float2(a1.x - a3.x, a1.y - a3.y);
+        const int pj0 = pad((j - k) * R + k);
+        if constexpr (R == 8) {
+            dft8<INV>(v);
         } else {
-            out[j0] = make_float2(v[0].x + v[1].x, v[0].y + v[1].y);
-            out[j0 + Ns] = make_float2(v[0].x - v[1].x, v[0].y - v[1].y);
+            dft4<INV>(v[0], v[1], v[2], v[3]);
         }
+#pragma unroll
+        for (int r = 0; r < R; ++r) out[pj0 + r * Ns + ((r * Ns) >> 4)] = v[r];   // pad(j0 + r Ns): no carry out of the low 4 bits
     }
     __syncthreads();
 }
 
-// 2048-point FFT, a -> a (b is scratch): six passes, the data ends in the buffer it started in.
+// 2048-point FFT, a -> a (b is scratch): radix 8, 8, 8, 4 -- the data ends in the buffer it started in.
 template <bool INV>
 __device__ __forceinline__ void fft2048(float2* a, float2* b, const float2* tw) {
-    fft_pass<4, INV>(a, b, tw, 1);
-    fft_pass<4, INV>(b, a, tw, 4);
-    fft_pass<4, INV>(a, b, tw, 16);
-    fft_pass<4, INV>(b, a, tw, 64);
-    fft_pass<4, INV>(a, b, tw, 256);
-    fft_pass<2, INV>(b, a, tw, 1024);
+    fft_pass<8, 1, INV>(a, b, tw);
+    fft_pass<8, 8, INV>(b, a, tw + TW_OFF1);
+    fft_pass<8, 64, INV>(a, b, tw + TW_OFF2);
+    fft_pass<4, 512, INV>(b, a, tw + TW_OFF3);
 }
 
 struct GlGeom {
@@ -128,8 +157,9 @@ struct GlArgs {
     float* yf_out;           // [B,F,win]
     float* dist_acc;         // [B,2] (GL_MEASURE)
     const int32_t* n_frames; // [B] or null
-    const float2* tw;        // [N]
+    const float2* tw;        // [TW_TOTAL] per-pass twiddles
     const float* w;          // [win]
+    const float* wsum;       // [win + hop] window sum of squares under an interior frame pair
     GlGeom g;
     int F;
     uint64_t seed;
@@ -140,26 +170,41 @@ template <int MODE>
 __global__ void __launch_bounds__(GL_THREADS) gl_kernel(const GlArgs a) {
     extern __shared__ float2 gl_smem[];
     float2* A = gl_smem;
-    float2* Bf = gl_smem + N;
-    float2* tw = gl_smem + 2 * N;
+    float2* Bf = gl_smem + NP;
+    const float2* tw = a.tw;
     const int b = blockIdx.y, t0 = blockIdx.x * 2, tid = threadIdx.x;
     const int Fb = a.n_frames ? a.n_frames[b] : a.F;
     if (t0 >= Fb) return;
     const bool has1 = t0 + 1 < Fb;
     const GlGeom g = a.g;
     const float* mag0 = a.mag + ((size_t)b * a.F + t0) * NB;
-    for (int i = tid; i < N; i += GL_THREADS) tw[i] = a.tw[i];
 
     if (MODE != GL_FIRST) {
         float* seg = reinterpret_cast<float*>(Bf);
         const int L = g.hop * (Fb - 1);
         const float* yf = a.yf_in ? a.yf_in + (size_t)b * a.F * g.win : nullptr;
-        for (int i = tid; i < g.win + g.hop; i += GL_THREADS) {
-            int n = t0 * g.hop + g.lpad + i - N / 2;
-            if (n < 0) n = -n;                       // np.pad(mode='reflect')
-            if (n >= L) n = 2 * (L - 1) - n;
-            n = min(max(n, 0), L - 1);
-            seg[i] = MODE == GL_MEASURE ? a.sig[(size_t)b * a.sig_stride + n] : ola_sample(yf, a.w, g, Fb, n);
+        const int SEG = g.win + g.hop;
+        const int n0 = t0 * g.hop + g.lpad - N / 2;              // signal sample under the first tap of frame t0
+        const int d_lo = -((g.win - 1) / g.hop), d_hi = (SEG - 1) / g.hop;
+        if (MODE == GL_ITER && n0 >= 0 && n0 + SEG <= L && t0 + d_lo >= 0 && t0 + d_hi <= Fb - 1) {
+            // interior: no reflection, every covering frame exists => the window sum depends on the offset only (a.wsum)
+            const float* base = yf + (size_t)t0 * g.win;
+            for (int i = tid; i < SEG; i += GL_THREADS) {
+                float acc = 0.f;
+                for (int d = d_lo; d <= d_hi; ++d) {
+                    const int j = i - d * g.hop;
+                    if (j >= 0 && j < g.win) acc += base[d * g.win + j];
+                }
+                seg[i] = acc / __ldg(a.wsum + i);
+            }
+        } else {
+            for (int i = tid; i < SEG; i += GL_THREADS) {
+                int n = n0 + i;
+                if (n < 0) n = -n;                       // np.pad(mode='reflect')
+                if (n >= L) n = 2 * (L - 1) - n;
+                n = min(max(n, 0), L - 1);
+                seg[i] = MODE == GL_MEASURE ? a.sig[(size_t)b * a.sig_stride + n] : ola_sample(yf, a.w, g, Fb, n);
+            }
         }
         __syncthreads();
         for (int j = tid; j < N; j += GL_THREADS) {
@@ -170,12 +215,10 @@ __global__ void __launch_bounds__(GL_THREADS) gl_kernel(const GlArgs a) {
                 z.x = wj * seg[jj];
                 z.y = has1 ? wj * seg[jj + g.hop] : 0.f;
             }
-            A[j] = z;
+            A[pad(j)] = z;
         }
         __syncthreads();
         fft2048<false>(A, Bf, tw);
-    } else {
-        __syncthreads();
     }
 
     float err = 0.f, ref = 0.f;
@@ -199,22 +242,23 @@ __global__ void __launch_bounds__(GL_THREADS) gl_kernel(const GlArgs a) {
             sincospif(2.f * u1, &s, &c);
             P1 = make_float2(m1 * c, m1 * s);
         } else {
-            const float2 Zk = A[k], Zn = A[(N - k) & (N - 1)];
+            const float2 Zk = A[pad(k)], Zn = A[pad((N - k) & (N - 1))];
             const float2 X0 = make_float2(0.5f * (Zk.x + Zn.x), 0.5f * (Zk.y - Zn.y));   // (Z[k] + conj Z[N-k]) / 2
             const float2 X1 = make_float2(0.5f * (Zk.y + Zn.y), 0.5f * (Zn.x - Zk.x));   // (Z[k] - conj Z[N-k]) / 2i
-            const float r0 = sqrtf(X0.x * X0.x + X0.y * X0.y), r1 = sqrtf(X1.x * X1.x + X1.y * X1.y);
+            const float q0 = X0.x * X0.x + X0.y * X0.y, q1 = X1.x * X1.x + X1.y * X1.y;
             if (MODE == GL_MEASURE) {
+                const float r0 = sqrtf(q0), r1 = sqrtf(q1);
                 err += (r0 - m0) * (r0 - m0) + (has1 ? (r1 - m1) * (r1 - m1) : 0.f);
                 ref += m0 * m0 + m1 * m1;
                 continue;
             }
-            const float s0 = r0 > 0.f ? m0 / r0 : 0.f, s1 = r1 > 0.f ? m1 / r1 : 0.f;   // exp(i angle(X)); angle(0) = 0
-            P0 = r0 > 0.f ? make_float2(X0.x * s0, X0.y * s0) : make_float2(m0, 0.f);
-            P1 = r1 > 0.f ? make_float2(X1.x * s1, X1.y * s1) : make_float2(m1, 0.f);
+            const float s0 = m0 * rsqrtf(q0), s1 = m1 * rsqrtf(q1);                     // m exp(i angle(X)); angle(0) = 0
+            P0 = q0 > 0.f ? make_float2(X0.x * s0, X0.y * s0) : make_float2(m0, 0.f);
+            P1 = q1 > 0.f ? make_float2(X1.x * s1, X1.y * s1) : make_float2(m1, 0.f);
         }
         if (k == 0 || k == N / 2) P0.y = P1.y = 0.f;       // irfft ignores the imaginary part of DC / Nyquist
-        Bf[k] = make_float2(P0.x - P1.y, P0.y + P1.x);      // P0 + i P1
-        if (k > 0 && k < N / 2) Bf[N - k] = make_float2(P0.x + P1.y, P1.x - P0.y);   // conj P0 + i conj P1
+        Bf[pad(k)] = make_float2(P0.x - P1.y, P0.y + P1.x);      // P0 + i P1
+        if (k > 0 && k < N / 2) Bf[pad(N - k)] = make_float2(P0.x + P1.y, P1.x - P0.y);   // conj P0 + i conj P1
     }
     if (MODE == GL_MEASURE) {
         __shared__ float red[2][GL_THREADS / 32];
@@ -237,7 +281,7 @@ __global__ void __launch_bounds__(GL_THREADS) gl_kernel(const GlArgs a) {
     float* out0 = a.yf_out + ((size_t)b * a.F + t0) * g.win;
     for (int j = tid; j < g.win; j += GL_THREADS) {
         const float wj = __ldg(a.w + j) * (1.0f / N);
-        const float2 z = Bf[g.lpad + j];
+        const float2 z = Bf[pad(g.lpad + j)];
         out0[j] = wj * z.x;
         if (has1) out0[g.win + j] = wj * z.y;
     }
@@ -337,8 +381,9 @@ struct TacoGl {
     int device = 0;
     GlGeom g{};
     int n_mels = 0;
-    float2* tw = nullptr;      // [N]
+    float2* tw = nullptr;      // [TW_TOTAL]
     float* w = nullptr;        // [win]
+    float* wsum = nullptr;     // [win + hop]
     float* invT = nullptr;     // [n_mels][NB]
     float* yf[2] = {nullptr, nullptr};
     size_t yf_floats = 0;
@@ -349,7 +394,7 @@ struct TacoGl {
 
 namespace {
 
-constexpr size_t GL_SMEM = 3 * N * sizeof(float2);
+constexpr size_t GL_SMEM = 2 * NP * sizeof(float2);
 
 int gl_fail(TacoGl* g, int code, const char* what, cudaError_t e = cudaSuccess) {
     if (g) {
@@ -417,21 +462,37 @@ int taco_gl_create(int device, int n_fft, int hop, int win, int n_mels, const fl
     g->g.lpad = (N - win) / 2;
     g->g.cover = (win + hop - 1) / hop;
     g->n_mels = n_mels;
-    std::vector<float2> tw(N);
-    for (int m = 0; m < N; ++m) {
-        const double ang = -2.0 * 3.14159265358979323846 * m / N;
-        tw[m] = make_float2((float)cos(ang), (float)sin(ang));
+    std::vector<float2> tw(TW_TOTAL);
+    {
+        const int radix[3] = {8, 8, 4}, ns[3] = {8, 64, 512}, off[3] = {TW_OFF1, TW_OFF2, TW_OFF3};
+        for (int p = 0; p < 3; ++p)
+            for (int k = 0; k < ns[p]; ++k)
+                for (int r = 1; r < radix[p]; ++r) {
+                    const double ang = -2.0 * 3.14159265358979323846 * r * k / ((double)ns[p] * radix[p]);
+                    tw[off[p] + k * (radix[p] - 1) + (r - 1)] = make_float2((float)cos(ang), (float)sin(ang));
+                }
     }
     std::vector<float> w(win);
     for (int j = 0; j < win; ++j) w[j] = (float)(0.5 - 0.5 * cos(2.0 * 3.14159265358979323846 * j / win));   // periodic Hann
+    std::vector<float> wsum(win + hop);
+    for (int i = 0; i < win + hop; ++i) {
+        float ws = 0.f;
+        for (int d = -((win - 1) / hop); d <= (win + hop - 1) / hop; ++d) {
+            const int j = i - d * hop;
+            if (j >= 0 && j < win) ws = fmaf(w[j], w[j], ws);
+        }
+        wsum[i] = ws > 1.17549435e-38f ? ws : 1.f;
+    }
     std::vector<float> invT((size_t)n_mels * NB);
     for (int k = 0; k < NB; ++k)
         for (int m = 0; m < n_mels; ++m) invT[(size_t)m * NB + k] = inv_mel_basis[(size_t)k * n_mels + m];
     cudaError_t e = cudaSetDevice(device);
-    if (e == cudaSuccess) e = cudaMalloc(&g->tw, N * sizeof(float2));
+    if (e == cudaSuccess) e = cudaMalloc(&g->tw, TW_TOTAL * sizeof(float2));
     if (e == cudaSuccess) e = cudaMalloc(&g->w, win * sizeof(float));
     if (e == cudaSuccess) e = cudaMalloc(&g->invT, invT.size() * sizeof(float));
-    if (e == cudaSuccess) e = cudaMemcpy(g->tw, tw.data(), N * sizeof(float2), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMalloc(&g->wsum, wsum.size() * sizeof(float));
+    if (e == cudaSuccess) e = cudaMemcpy(g->wsum, wsum.data(), wsum.size() * sizeof(float), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(g->tw, tw.data(), TW_TOTAL * sizeof(float2), cudaMemcpyHostToDevice);
     if (e == cudaSuccess) e = cudaMemcpy(g->w, w.data(), win * sizeof(float), cudaMemcpyHostToDevice);
     if (e == cudaSuccess) e = cudaMemcpy(g->invT, invT.data(), invT.size() * sizeof(float), cudaMemcpyHostToDevice);
     if (e != cudaSuccess) {
@@ -447,6 +508,7 @@ void taco_gl_destroy(TacoGl* g) {
     cudaFree(g->tw);
     cudaFree(g->w);
     cudaFree(g->invT);
+    cudaFree(g->wsum);
     cudaFree(g->yf[0]);
     cudaFree(g->yf[1]);
     cudaFree(g->dist_acc);
@@ -484,6 +546,7 @@ int taco_gl_griffin_lim(TacoGl* g, const float* mag_dev, const float* turns_dev,
     a.n_frames = n_frames_dev;
     a.tw = g->tw;
     a.w = g->w;
+    a.wsum = g->wsum;
     a.g = g->g;
     a.F = F;
     a.seed = seed;
@@ -522,6 +585,7 @@ int taco_gl_spectral_distance(TacoGl* g, const float* audio_dev, long long audio
     a.n_frames = n_frames_dev;
     a.tw = g->tw;
     a.w = g->w;
+    a.wsum = g->wsum;
     a.g = g->g;
     a.F = F;
     if (int rc = gl_launch<GL_MEASURE>(g, a, B, st)) return rc;
