@@ -292,18 +292,30 @@ __device__ __forceinline__ void att3_step(const Dec3Params& p, float (&preR)[8][
         float c[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
         if (tg < TG) {
             const uint4* vp = reinterpret_cast<const uint4*>(p.values + (size_t)b * p.T * MEM) + d8;
-#pragma unroll 8
-            for (int t = tg; t < len; t += TG) {
-                const uint4 v = ldg_stream_v4(vp + (size_t)t * D8);
-                const float a = SMF(SO_ES)[t];
-                c[0] = fmaf(a, bf_lo(v.x), c[0]);
-                c[1] = fmaf(a, bf_hi(v.x), c[1]);
-                c[2] = fmaf(a, bf_lo(v.y), c[2]);
-                c[3] = fmaf(a, bf_hi(v.y), c[3]);
-                c[4] = fmaf(a, bf_lo(v.z), c[4]);
-                c[5] = fmaf(a, bf_hi(v.z), c[5]);
-                c[6] = fmaf(a, bf_lo(v.w), c[6]);
-                c[7] = fmaf(a, bf_hi(v.w), c[7]);
+            // fixed-size predicated batches: every load of a batch is in flight before the first FMA needs one (a plain
+            // unrolled loop leaves a remainder loop that pays one L2 latency per position)
+            constexpr int UB = 12;
+            for (int t0 = tg; t0 < len; t0 += TG * UB) {
+                uint4 v[UB];
+                float a[UB];
+#pragma unroll
+                for (int u = 0; u < UB; ++u) {
+                    const int t = t0 + u * TG;
+                    const bool ok = t < len;
+                    v[u] = ok ? ldg_stream_v4(vp + (size_t)t * D8) : make_uint4(0u, 0u, 0u, 0u);
+                    a[u] = ok ? SMF(SO_ES)[t] : 0.f;
+                }
+#pragma unroll
+                for (int u = 0; u < UB; ++u) {
+                    c[0] = fmaf(a[u], bf_lo(v[u].x), c[0]);
+                    c[1] = fmaf(a[u], bf_hi(v[u].x), c[1]);
+                    c[2] = fmaf(a[u], bf_lo(v[u].y), c[2]);
+                    c[3] = fmaf(a[u], bf_hi(v[u].y), c[3]);
+                    c[4] = fmaf(a[u], bf_lo(v[u].z), c[4]);
+                    c[5] = fmaf(a[u], bf_hi(v[u].z), c[5]);
+                    c[6] = fmaf(a[u], bf_lo(v[u].w), c[6]);
+                    c[7] = fmaf(a[u], bf_hi(v[u].w), c[7]);
+                }
             }
             float4* dst = reinterpret_cast<float4*>(scr + (size_t)tg * MEM + d8 * 8);
             dst[0] = make_float4(c[0], c[1], c[2], c[3]);
