@@ -448,8 +448,9 @@ int pack_decoder3(TacoHandle* h) {
         for (int ks = 0; ks < 64; ++ks)   // frame / stop projection of [LSTM output ; context] (Decoder.py:273-279)
             pack_tile(p + ks * 128, [&](int k, int m) {
                 const int kk = ks * 16 + k;
-                if (c < 10) return kf->host[(size_t)kk * 160 + 16 * c + m];
-                if (c == 10 && m < 2) return kst->host[(size_t)kk * 2 + m];
+                const int slot = dec3_proj_slot(c);
+                if (slot >= 0 && slot < 10) return kf->host[(size_t)kk * 160 + 16 * slot + m];
+                if (slot == 10 && m < 2) return kst->host[(size_t)kk * 2 + m];
                 return 0.f;
             });
         p += 64 * 128;
@@ -472,7 +473,8 @@ int pack_decoder3(TacoHandle* h) {
         for (int u = 0; u < 16; ++u) {
             bias[128 + u] = bp1->host[16 * c + u];
             bias[144 + u] = bp2->host[16 * c + u];
-            bias[160 + u] = c < 10 ? bf->host[16 * c + u] : ((c == 10 && u < 2) ? bst->host[u] : 0.f);
+            const int slot = dec3_proj_slot(c);
+            bias[160 + u] = (slot >= 0 && slot < 10) ? bf->host[16 * slot + u] : ((slot == 10 && u < 2) ? bst->host[u] : 0.f);
         }
         uint32_t* q = str.data() + (size_t)c * SW;
         // streamed sets [4 mt][16 ks]: 0 LSTM-1 prenet rows [0,256); 1 LSTM-2 h1 rows [0,256); 2 LSTM-1 h1 rows [1024,1280);

@@ -339,7 +339,7 @@ __device__ __forceinline__ void att3_step(const Dec3Params& p, float (&preR)[8][
         // multicast this row's 48 x 32-byte chunks into every CTA's context buffer
         for (int i = tid; i < CS * KS_CTX * 2; i += NT) {
             const int slot = i / (KS_CTX * 2), v = i - slot * (KS_CTX * 2);
-            const int dst = slot < 5 ? slot + 5 : (slot < 10 ? slot - 5 : slot);   // feedback-frame producers (ranks 5..9) first
+            const int dst = slot < 5 ? slot + 11 : slot - 5;   // feedback-frame producers (ranks 11..15) first
             const int ks = v >> 1, half = v & 1;
             const uint4 val = *reinterpret_cast<const uint4*>(SMU(SO_STG_C) + ks * 8 + half * 4);
             st_remote_v4(mapa_rank(smem_addr(SMU(SO_CTX) + ks * TILE_W + ((rank >> 3) << 6) + ((rank & 7) << 3) + half * 4), dst), val);

@@ -28,6 +28,7 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
     cg::cluster_group cluster = cg::this_cluster();
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int rank = (int)cluster.block_rank();
+    const int slot = dec3_proj_slot(rank);
     const int cid = blockIdx.x / CS;
     const int row0 = cid * p.R;
     const int R = min(p.R, p.B - row0);
@@ -359,7 +360,10 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
         prefetch4(aW1C, sW1C, kg, lane);   // in flight while the projection waits for the slowest context row
         D3_STAMP(10)
         // ================= PROJ: frame + stop projection, outputs, feedback (Decoder.py:273-279; Helpers.py:36-59) =================
-        if (rank <= 10) {
+        // projection slot of this rank: slots 0..4 (first frame of the step) on ranks 0..4, slots 5..9 (last frame = the
+        // feedback input) on ranks 11..15, which own no attention row when a cluster has <= 10 rows and therefore start
+        // as soon as the last context row lands; slot 10 (stop token) on rank 10
+        if (slot >= 0) {
             float accO[2][4] = {};
             gemm_smem4(accO, SMU(SO_WO), SMU(SO_H2R), KS_H, warp, 16, lane, g);
             gemm_smem4(accO, SMU(SO_WO) + KS_H * TILE_W, SMU(SO_CTX), KS_CTX, warp, 16, lane, g);
@@ -372,10 +376,10 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
                 float y = bias[160 + eu];
 #pragma unroll
                 for (int k = 0; k < 16; ++k) y += red[(k * 16 + eu) * 17 + er];
-                if (rank < 10) {
-                    const int col = 16 * rank + eu;   // 0..159: frame col / 80, mel col % 80
+                if (slot < 10) {
+                    const int col = 16 * slot + eu;   // 0..159: frame col / 80, mel col % 80
                     if (evalid) p.frames[((size_t)eb * p.S_cap * 2 + (size_t)s * 2 + (col >= MEL ? 1 : 0)) * MEL + (col >= MEL ? col - MEL : col)] = y;
-                    if (rank >= 5) {
+                    if (slot >= 5) {
                         // TacoTestHelper.next_inputs: next input = last frame of this step (Helpers.py:56)
                         const float x = evalid ? y : 0.f;
                         if (evalid) p.x_state[(size_t)eb * MEL + col - MEL] = x;
@@ -390,18 +394,18 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
                     }
                 }
             }
-            if (rank == 10) {
+            if (slot == 10) {
                 if (free_run) {
                     const int cnt = __syncthreads_count(fin ? 1 : 0);
                     if (tid == 0) stg_relaxed(reinterpret_cast<uint32_t*>(p.flags) + (size_t)s * p.NCL + cid, (p.stop_at_any ? cnt > 0 : cnt == 2 * R) ? 2u : 1u);
                 }
-            } else if (rank >= 5 && free_run) {
+            } else if (slot >= 5 && free_run) {
                 __syncthreads();
                 const int dst = tid >> 5, v = tid & 31;
                 const int row = ((v >> 4) << 3) + ((v & 15) >> 1);
                 if (row < R) {
                     const uint4 val = *reinterpret_cast<const uint4*>(SMU(SO_STG_R) + (v << 2));
-                    st_remote_v4(mapa_rank(smem_addr(SMU(SO_X) + (rank - 5) * TILE_W + (v << 2)), dst), val);
+                    st_remote_v4(mapa_rank(smem_addr(SMU(SO_X) + (slot - 5) * TILE_W + (v << 2)), dst), val);
                 }
             }
         }

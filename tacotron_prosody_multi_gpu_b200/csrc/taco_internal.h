@@ -95,6 +95,14 @@ cudaError_t taco_launch_f32_to_bf16(const float* in, void* out, size_t n, cudaSt
 #define TACO_DEC3_TMAX 512
 #define TACO_DEC3_RES_WORDS (221 * 128 + 176)
 #define TACO_DEC3_STREAM_TILES 320
+// decoder3: which 16-column slot of the frame/stop projection a cluster rank computes (-1: none).  Slots 0..4 = first
+// frame of the step, 5..9 = last frame (fed back as the next input), 10 = stop token.  Shared by the host packing
+// (api.cu pack_decoder3) and the kernel.
+#ifdef __CUDACC__
+__host__ __device__
+#endif
+inline int dec3_proj_slot(int rank) { return rank < 5 ? rank : (rank == 10 ? 10 : (rank >= 11 ? rank - 6 : -1)); }
+
 struct Dec3Params {
     int B, T, NCL, R;       // NCL clusters; cluster i owns batch rows [i*R, min(B, i*R + R))
     int S_max, S_cap, t0, mode;
