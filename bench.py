@@ -11,12 +11,15 @@ batch-global stop never fires), r = 2 -> 92 160 mel frames per step per GPU.
   torchrun ... bench.py --gpus N ...                              (N>1: one rank per GPU, weak scaling)
   python bench.py --impl reference ...                            (CPU restatement of the reference)
 
-`value`      device-resident inputs, CUDA-event time of the K steps (max over ranks).
+`value`      device-resident inputs, CUDA-event time of the K steps (max over ranks), `--in-flight` (default 2)
+             independent batches in flight per GPU (engine.EnginePool): the decoder kernel of one batch overlaps
+             the encoder / postnet / copies of the next; `stages_ms.one_batch_in_flight_ms_per_step` is the
+             latency of a single batch.
 `e2e`        same metric through the reference-facing API (Tacotron.initialize on HOST arrays):
              pinned-host -> device copies of ids/lengths and device -> host reads of
              mel_outputs, alignments and stop tokens inside the timed region.
 `roofline`   dominant kernel = the persistent decoder kernel, timed live by CUDA events recorded
-             around its launch inside the library (taco_stage_ms).
+             around its launch inside the library (taco_stage_ms), in a pass with ONE batch in flight.
 `cpu_baseline` the oracle (CPU restatement of the reference; TF 1.9 is not installable) on the
              box's host cores, rank 0, N=1 only.
 """
@@ -211,18 +214,22 @@ def run_b200(args):
 
     hp = default_hparams()
     w = weights.set_stop_bias(weights.init_weights(hp, perturb=0.05), -10.0)
-    eng = TacoEngine(hp, w, device=local_rank, precision=args.precision)
+    from tacotron_prosody_multi_gpu_b200.engine import EnginePool
+    pool = EnginePool(hp, w, device=local_rank, precision=args.precision, in_flight=args.in_flight)
+    eng = pool.engines[0]
     ids, lens, gw = workload(hp, rank)
     B, T = ids.shape
     S = args.decoder_steps
     r = hp.outputs_per_step
     frames_per_step = B * S * r
     seed = hp.tacotron_random_seed
-
+    torch.cuda.set_device(dev)
     ids_d = torch.from_numpy(ids).to(dev)
     lens_d = torch.from_numpy(lens).to(dev)
     gw_d = torch.from_numpy(gw).to(dev)
-    flush = torch.empty(512 * 1024 * 1024 // 4, dtype=torch.float32, device=dev)  # 512 MB > 126 MB L2
+    # one 512 MB (> 126 MB L2) flush buffer per engine: written on the engine's stream before each of its steps
+    flush = [torch.empty(512 * 1024 * 1024 // 4, dtype=torch.float32, device=dev) for _ in range(len(pool))]
+    fidx = {id(e): i for i, e in enumerate(pool.engines)}
 
     def barrier():
         torch.cuda.synchronize()
@@ -237,53 +244,66 @@ def run_b200(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    def device_step():
-        out = eng.forward(ids_d, lens_d, gst_weights=gw_d, max_iters=S, philox_seed=seed)
-        return out
+    def device_step(e, _):
+        flush[fidx[id(e)]].add_(1.0)
+        return e.forward(ids_d, lens_d, gst_weights=gw_d, max_iters=S, philox_seed=seed)["steps"]
+
+    def e2e_step(e, _):
+        flush[fidx[id(e)]].add_(1.0)
+        o = e.forward_host(ids, lens, gst_weights=gw, max_iters=S, philox_seed=seed)
+        return o["steps"], int(o["h2d_bytes"]), int(o["d2h_bytes"])
 
     def timed(fn, n):
-        """n steps, each bracketed by CUDA events on the launching stream; L2 flushed (untimed)
-        between steps.  Returns (sum of per-step device ms, per-step decoder-kernel ms list, last out)."""
-        tot = 0.0
-        dec = []
-        out = None
-        for _ in range(n):
-            flush.add_(1.0)
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            torch.cuda.synchronize()
-            e0.record()
-            out = fn()
-            e1.record()
-            torch.cuda.synchronize()
-            tot += e0.elapsed_time(e1)
-            dec.append(eng.stage_ms(_lib.TACO_STAGE_DECODER_KERNEL))
-        return tot, dec, out
+        """EXACTLY n steps, `in_flight` of them at a time (one engine + stream + host thread each); ONE pair of CUDA events
+        on the default stream brackets the region: every engine stream waits for the first, the second is recorded after all
+        of them were joined.  The L2 flush of each step runs on the step's own stream, inside the timed region."""
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        res = pool.map(fn, range(n), after=e0)
+        for st in pool.streams:
+            torch.cuda.current_stream().wait_stream(st)
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1), res
 
     # ---- device-resident arm ---------------------------------------------------------------
-    timed(device_step, args.warmup)
+    timed(device_step, max(args.warmup, len(pool)))
     barrier()
     sampler = ClockSampler(local_rank) if rank == 0 else None
-    l0 = eng.launch_count
-    ms_total, dec_ms, out = timed(device_step, args.steps)
-    launches = eng.launch_count - l0
+    l0 = pool.launch_count
+    ms_total, steps_seen = timed(device_step, args.steps)
+    launches = pool.launch_count - l0
     barrier()
-    assert out["steps"] == S, "stop fired in a throughput run"
+    assert all(x == S for x in steps_seen), "stop fired in a throughput run"
     ms_total = max_over_ranks(ms_total)
-    stage = {"encode_ms": eng.stage_ms(_lib.TACO_STAGE_ENCODE), "decoder_kernel_ms": float(np.mean(dec_ms)),
-             "postnet_ms": eng.stage_ms(_lib.TACO_STAGE_POSTNET)}
 
     # ---- end-to-end arm: host buffers in, host buffers out -----------------------------------
-    def e2e_step():
-        return eng.forward_host(ids, lens, gst_weights=gw, max_iters=S, philox_seed=seed)
-
-    timed(e2e_step, max(1, min(args.warmup, 2)))
+    timed(e2e_step, max(min(args.warmup, 2), len(pool)))
     barrier()
-    e2e_ms, _, eo = timed(e2e_step, args.steps)
+    e2e_ms, eo = timed(e2e_step, args.steps)
     barrier()
     e2e_ms = max_over_ranks(e2e_ms)
+    h2d, d2h = eo[-1][1], eo[-1][2]
+
+    # ---- one batch at a time: per-stage and decoder-kernel durations for the roofline (CUDA events around each kernel
+    #      inside the library; with several batches in flight they would include the wait for free SMs) ----
+    dec_ms = []
+    seq_ms = 0.0
+    for _ in range(3):
+        flush[0].add_(1.0)
+        torch.cuda.synchronize()
+        q0, q1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        q0.record()
+        eng.forward(ids_d, lens_d, gst_weights=gw_d, max_iters=S, philox_seed=seed)
+        q1.record()
+        torch.cuda.synchronize()
+        seq_ms = q0.elapsed_time(q1)
+        dec_ms.append(eng.stage_ms(_lib.TACO_STAGE_DECODER_KERNEL))
+    dec_ms = dec_ms[1:]
+    stage = {"encode_ms": eng.stage_ms(_lib.TACO_STAGE_ENCODE), "decoder_kernel_ms": float(np.mean(dec_ms)),
+             "postnet_ms": eng.stage_ms(_lib.TACO_STAGE_POSTNET), "one_batch_in_flight_ms_per_step": seq_ms}
     clocks = sampler.stop() if sampler is not None else None
-    h2d = int(eo["h2d_bytes"])
-    d2h = int(eo["d2h_bytes"])
 
     if rank != 0:
         if world > 1:
@@ -304,7 +324,11 @@ def run_b200(args):
         "config": {"workload": "C2 free-running inference, B=64/GPU, sentences.txt token lengths x4 (T=111), "
                                "S=%d decoder steps (max_iters, stop bias -10), r=2, random-init seed 45454" % S,
                    "batch_per_gpu": B, "T": T, "decoder_steps": S, "frames_counted": "all B*2S frames (no stop fires)",
-                   "l2": "512 MB flush write between timed steps", "parallelism": "independent batches per GPU, no collective"},
+                   "l2": "512 MB flush write before every step, on the step's stream, inside the timed region",
+                   "in_flight": args.in_flight,
+                   "parallelism": "independent batches per GPU, no collective; %d batches in flight per GPU (one engine handle, CUDA "
+                                  "stream and host thread each): the encoder / postnet / copies of one batch overlap the persistent "
+                                  "decoder kernel of another" % args.in_flight},
         "decoder_step_us": 1e6 * dec_s / S,
         "stages_ms": stage,
         "roofline": {"bound": "hbm", "kernel": "decoder3_kernel (cluster persistent decoder)" if args.precision == "bf16" else "decoder_persistent_kernel", "achieved": achieved, "peak": peak,
@@ -340,6 +364,7 @@ def main():
     ap.add_argument("--ref-steps", type=int, default=0, help="--impl reference: decoder steps per pass (0 = auto)")
     ap.add_argument("--ref-budget-s", type=float, default=240.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--in-flight", type=int, default=2, help="independent batches in flight per GPU (engine.EnginePool)")
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"],
                     help="bf16: tensor-core (tcgen05) contractions with bf16 operands, fp32 accumulate; fp32: SIMT everywhere")
     args = ap.parse_args()

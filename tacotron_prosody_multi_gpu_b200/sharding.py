@@ -52,7 +52,8 @@ def synthesize_batches(engine, hp, seqs, rank=0, world=1, batch_size=64, gst_wei
                        fetch=("mel_outputs", "stop")):
     """Runs this rank's share of ``seqs`` (list of int token arrays).  Returns {utterance index: dict(mel [len,80],
     steps)} for the utterances this rank owns; outputs are trimmed at the first rounded stop token and clipped like
-    Synthesizer.synthesize.  ``engine`` is a TacoEngine bound to this rank's GPU."""
+    Synthesizer.synthesize.  ``engine`` is a TacoEngine bound to this rank's GPU, or an EnginePool on it (several batches
+    in flight, same results)."""
     from .Utils.Tacotron_feeder import _get_output_lengths, _prepare_inputs
     from .synthetic import gst_random_weights
     lengths = [len(s) for s in seqs]
@@ -60,14 +61,21 @@ def synthesize_batches(engine, hp, seqs, rank=0, world=1, batch_size=64, gst_wei
     gw = gst_random_weights(hp) if gst_weights is None else gst_weights
     seed = hp.tacotron_random_seed if philox_seed is None else philox_seed
     lo, hi = (-hp.max_abs_value, hp.max_abs_value) if hp.symmetric_mels else (0, hp.max_abs_value)
-    out = {}
-    for b, idx in enumerate(batches):
-        if owner[b] != rank:
-            continue
+    mine = [(b, idx) for b, idx in enumerate(batches) if owner[b] == rank]
+
+    def run(eng, job):
+        b, idx = job
         ids, _ = _prepare_inputs([np.asarray(seqs[i], np.int32) for i in idx])
         lens = np.asarray([lengths[i] for i in idx], np.int32)
-        res = engine.forward_host(ids.astype(np.int32), lens, gst_weights=gw, max_iters=max_iters, philox_seed=seed, fetch=fetch)
+        res = eng.forward_host(ids.astype(np.int32), lens, gst_weights=gw, max_iters=max_iters, philox_seed=seed, fetch=fetch)
         keep = _get_output_lengths(res["stop"])
-        for j, i in enumerate(idx):
-            out[int(i)] = dict(mel=np.clip(res["mel_outputs"][j, :keep[j]], lo, hi).copy(), steps=res["steps"], batch=b)
+        # copies: the host arrays are views of the engine's pinned buffers, reused by its next batch
+        return {int(i): dict(mel=np.clip(res["mel_outputs"][j, :keep[j]], lo, hi).copy(), steps=res["steps"], batch=b)
+                for j, i in enumerate(idx)}
+
+    # an EnginePool keeps several batches in flight on this GPU (engine.EnginePool); a single TacoEngine runs them in turn
+    parts = engine.map(run, mine) if hasattr(engine, "map") else [run(engine, job) for job in mine]
+    out = {}
+    for part in parts:
+        out.update(part)
     return out

@@ -158,6 +158,28 @@ def test_sharded_synthesis_equals_unsharded(rt):
         assert np.array_equal(one[i]["mel"], merged[i]["mel"])      # same batch composition -> bit-identical
 
 
+def test_engine_pool_in_flight_batches_equal_sequential(rt):
+    """Several batches in flight on one GPU (engine.EnginePool: one handle + stream + host thread each) give the same
+    bits as one batch at a time, in the order of the jobs."""
+    from tacotron_prosody_multi_gpu_b200.engine import EnginePool
+    hp, w = rt
+    eng = runtime.engine(hp)
+    seqs = [synthetic.token_batch(hp, [n], seed=300 + n)[0][0] for n in (5, 9, 7, 12, 6, 10, 8, 11, 4, 13, 6)]
+    gw = synthetic.gst_random_weights(hp)
+    one = sharding.synthesize_batches(eng, hp, seqs, 0, 1, batch_size=2, gst_weights=gw, max_iters=6)
+    pool = EnginePool(hp, w, device=0, precision=eng.precision if hasattr(eng, "precision") else "fp32", in_flight=3)
+    try:
+        many = sharding.synthesize_batches(pool, hp, seqs, 0, 1, batch_size=2, gst_weights=gw, max_iters=6)
+        assert pool.map(lambda e, x: x * 2, [1, 2, 3, 4, 5]) == [2, 4, 6, 8, 10]
+        with pytest.raises(ZeroDivisionError):
+            pool.map(lambda e, x: 1 // x, [1, 0, 2])
+    finally:
+        pool.close()
+    assert sorted(many) == sorted(one) == list(range(11))
+    for i in range(11):
+        assert np.array_equal(one[i]["mel"], many[i]["mel"])
+
+
 def test_tacotron_training_surface_two_towers(rt):
     """initialize(is_training=True) -> add_loss -> add_optimizer -> optimize() through the reference's class surface
     (Tacotron.py:46-48,351-540) with 2 towers packed along the time axis (split_infos), against the training oracle:
