@@ -74,7 +74,8 @@ constexpr int SO_VA = SO_QS + ATT;
 constexpr int SO_BC = SO_VA + ATT;
 constexpr int SO_FLAG = SO_BC + ATT;              // [16]: 0 = stop decision, 8.. = prefetched stop words of the clusters
 constexpr int SO_TACC = SO_FLAG + 16;              // 24 x int64 stage timers
-constexpr int SMEM3_WORDS = SO_TACC + 48;
+constexpr int SO_OWN = SO_TACC + 48;             // [16]: cluster rank that owns the attention of cluster row i
+constexpr int SMEM3_WORDS = SO_OWN + 16;
 static_assert(RES_WORDS == TACO_DEC3_RES_WORDS, "resident blob size");
 static_assert(SMEM3_WORDS * 4 <= 227 * 1024, "shared memory budget");
 static_assert(SO_X % 4 == 0 && SO_RED % 4 == 0 && SO_QRECV % 4 == 0 && SO_STG_R % 4 == 0 && SO_STG_C % 4 == 0 && SO_ES % 4 == 0 &&

@@ -145,7 +145,7 @@ __device__ __forceinline__ void att3_location(const Dec3Params& p, float (&preR)
     }
 }
 
-// One attention step of cluster row `rank` (global row b): q from the 16 partials, energies, masked softmax, cumulate,
+// One attention step of cluster row `rank` (global row b; the CTA that runs it is chosen by row length, SO_OWN): q from the 16 partials, energies, masked softmax, cumulate,
 // alignment history, context (bf16 values, fp32 accumulate), multicast of the context row, next step's location term.
 __device__ __forceinline__ void att3_step(const Dec3Params& p, float (&preR)[8][4], float* pre_scr, int b, int len, int rank, int s,
                                           int tid, int warp, int lane, Guard3& g, long long* tacc, long long& tprev, bool timing) {

@@ -69,9 +69,26 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
         c2s = p.c2[(size_t)eb * DEC + 16 * rank + eu];
         h2s = p.h2z[(size_t)eb * DEC + 16 * rank + eu];
     }
-    // attention work item: cluster row `rank`
-    const bool att = rank < R;
-    const int ab = row0 + (att ? rank : 0);
+    // attention work items: one cluster row per CTA.  The rows are dealt by length: the 5 longest to ranks 5..9, which
+    // compute no projection slot (dec3_proj_slot) -- the owner of the longest row is the last CTA to leave the attention
+    // phase and must not carry extra work into the next step -- the next 5 to ranks 0..4, the rest to ranks 10..15.
+    if (tid < 16) {
+        int pos = 0;
+        if (tid < R) {
+            const int mylen = p.lens[row0 + tid];
+            for (int r2 = 0; r2 < R; ++r2) {
+                const int l2 = p.lens[row0 + r2];
+                pos += (l2 > mylen || (l2 == mylen && r2 < tid)) ? 1 : 0;
+            }
+        }
+        SMU(SO_OWN)[tid] = tid < R ? (pos < 5 ? pos + 5 : (pos < 10 ? pos - 5 : pos)) : 0xFFFFu;
+    }
+    __syncthreads();
+    int arow = -1;
+    for (int r2 = 0; r2 < R; ++r2)
+        if ((int)SMU(SO_OWN)[r2] == rank) arow = r2;
+    const bool att = arow >= 0;
+    const int ab = row0 + (att ? arow : 0);
     const int alen = att ? p.lens[ab] : 0;
     float* pre_scr = p.pre_scratch + (size_t)ab * p.T * ATT;   // [T][128]: working copy when !pre_reg, saved state otherwise
     float preR[8][4];
@@ -335,7 +352,7 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
                 const int row = tid >> 5, v = tid & 31;
                 if (row < R) {
                     const uint4 val = *reinterpret_cast<const uint4*>(red + row * ATT + (v << 2));
-                    st_remote_v4(mapa_rank(smem_addr(SMU(SO_QRECV) + rank * ATT + (v << 2)), row), val);
+                    st_remote_v4(mapa_rank(smem_addr(SMU(SO_QRECV) + rank * ATT + (v << 2)), SMU(SO_OWN)[row]), val);
                 }
             }
             multicast_block(SMU(SO_STG_R), SMU(SO_H2R), rank, R, tid);
@@ -350,7 +367,7 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
         D3_STAMP(9)
         // ================= ATT: location-sensitive attention of cluster row `rank` =================
         if (att) {
-            att3_step(p, preR, pre_scr, ab, alen, rank, s, tid, warp, lane, g, tacc, tprev, timing);
+            att3_step(p, preR, pre_scr, ab, alen, arow, s, tid, warp, lane, g, tacc, tprev, timing);
             // next step's location term: off the critical path of every CTA but the one that owns the slowest row
             __syncthreads();
             att3_next(p, preR, pre_scr, ab, alen, tid, warp, lane);
