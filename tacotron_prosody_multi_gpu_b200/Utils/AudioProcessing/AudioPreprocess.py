@@ -187,16 +187,19 @@ class GriffinLim:
         B = len(mels)
         lens = np.asarray([m.shape[0] for m in mels], np.int32)
         F = int(lens.max())
-        batch = np.zeros((B, F, self.n_mels), np.float32)
-        for b, m in enumerate(mels):
-            batch[b, :lens[b]] = m
+        if B > 1 and all(n == F for n in lens):
+            batch = np.ascontiguousarray(np.stack(mels), np.float32)
+        else:
+            batch = np.zeros((B, F, self.n_mels), np.float32)
+            for b, m in enumerate(mels):
+                batch[b, :lens[b]] = m
         stride = self.hop * (F - 1)
         audio = np.empty((B, stride), np.float32)
         k = self.hp.preemphasis if self.hp.preemphasize else 0.0
         self._check(_L().taco_mel_to_audio(self._h, batch.ctypes.data, lens.ctypes.data, B, F, C.byref(self.norm), int(seed),
                                            utterance0, self.hp.griffin_lim_iters if iters is None else iters, float(k),
                                            audio.ctypes.data, stride), "taco_mel_to_audio")
-        return [audio[b, :self.hop * (lens[b] - 1)].copy() for b in range(B)]
+        return [audio[b, :self.hop * (lens[b] - 1)] for b in range(B)]   # views of this call's own buffer
 
 
 _plans = {}

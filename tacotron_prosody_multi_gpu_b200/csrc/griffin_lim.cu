@@ -389,6 +389,11 @@ struct TacoGl {
     size_t yf_floats = 0;
     float* dist_acc = nullptr;
     size_t dist_cap = 0;
+    // grow-only staging of the host-buffer entry point: device mel / mag / audio / n_frames, pinned bounce buffer
+    void* stage[4] = {nullptr, nullptr, nullptr, nullptr};
+    size_t stage_bytes[4] = {0, 0, 0, 0};
+    void* pinned = nullptr;
+    size_t pinned_bytes = 0;
     std::string err;
 };
 
@@ -512,6 +517,8 @@ void taco_gl_destroy(TacoGl* g) {
     cudaFree(g->yf[0]);
     cudaFree(g->yf[1]);
     cudaFree(g->dist_acc);
+    for (int i = 0; i < 4; ++i) cudaFree(g->stage[i]);
+    if (g->pinned) cudaFreeHost(g->pinned);
     delete g;
 }
 
@@ -605,27 +612,78 @@ int taco_mel_to_audio(TacoGl* g, const float* mel_host, const int32_t* n_frames_
             return gl_fail(g, -1, "taco_mel_to_audio: every utterance needs hop * (frames - 1) > n_fft / 2 and frames <= F");
     }
     GL_CUDA(cudaSetDevice(g->device));
-    float *mel = nullptr, *mag = nullptr, *audio = nullptr;
-    int32_t* nf = nullptr;
     const size_t n_mel = (size_t)B * F * g->n_mels, n_mag = (size_t)B * F * NB, n_audio = (size_t)B * audio_stride;
-    int rc = 0;
-    cudaError_t e = cudaMalloc(&mel, n_mel * sizeof(float));
-    if (e == cudaSuccess) e = cudaMalloc(&mag, n_mag * sizeof(float));
-    if (e == cudaSuccess) e = cudaMalloc(&audio, n_audio * sizeof(float));
-    if (e == cudaSuccess && n_frames_host) e = cudaMalloc(&nf, B * sizeof(int32_t));
-    if (e == cudaSuccess) e = cudaMemcpy(mel, mel_host, n_mel * sizeof(float), cudaMemcpyHostToDevice);
-    if (e == cudaSuccess && nf) e = cudaMemcpy(nf, n_frames_host, B * sizeof(int32_t), cudaMemcpyHostToDevice);
-    if (e != cudaSuccess) rc = gl_fail(g, e == cudaErrorMemoryAllocation ? -2 : -3, "taco_mel_to_audio: staging", e);
-    if (!rc) rc = taco_gl_mel_to_mag(g, mel, nf, B, F, norm, mag, nullptr);
-    if (!rc) rc = taco_gl_griffin_lim(g, mag, nullptr, nf, seed, utterance0, B, F, iters, preemphasis_k, audio, audio_stride, nullptr);
-    if (!rc) {
-        e = cudaMemcpy(audio_host, audio, n_audio * sizeof(float), cudaMemcpyDeviceToHost);
-        if (e != cudaSuccess) rc = gl_fail(g, -3, "taco_mel_to_audio: read back", e);
+    const size_t need[4] = {n_mel * sizeof(float), n_mag * sizeof(float), n_audio * sizeof(float), (size_t)B * sizeof(int32_t)};
+    for (int i = 0; i < 4; ++i)
+        if (need[i] > g->stage_bytes[i]) {
+            cudaFree(g->stage[i]);
+            g->stage[i] = nullptr;
+            g->stage_bytes[i] = 0;
+            GL_CUDA(cudaMalloc(&g->stage[i], need[i]));
+            g->stage_bytes[i] = need[i];
+        }
+    // pinned bounce buffer: the copies run at full PCIe rate and in chunks that overlap the host memcpy of the next chunk
+    const size_t CHUNK = (size_t)16 << 20;
+    if (g->pinned_bytes < 2 * CHUNK) {
+        if (g->pinned) cudaFreeHost(g->pinned);
+        g->pinned = nullptr;
+        g->pinned_bytes = 0;
+        GL_CUDA(cudaHostAlloc(&g->pinned, 2 * CHUNK, cudaHostAllocDefault));
+        g->pinned_bytes = 2 * CHUNK;
     }
-    cudaFree(mel);
-    cudaFree(mag);
-    cudaFree(audio);
-    cudaFree(nf);
+    float* mel = static_cast<float*>(g->stage[0]);
+    float* mag = static_cast<float*>(g->stage[1]);
+    float* audio = static_cast<float*>(g->stage[2]);
+    int32_t* nf = n_frames_host ? static_cast<int32_t*>(g->stage[3]) : nullptr;
+    cudaStream_t st = nullptr;
+    cudaEvent_t ev[2];
+    GL_CUDA(cudaEventCreateWithFlags(&ev[0], cudaEventDisableTiming));
+    GL_CUDA(cudaEventCreateWithFlags(&ev[1], cudaEventDisableTiming));
+    int rc = 0;
+    auto fail_cuda = [&](const char* what, cudaError_t e) { if (!rc) rc = gl_fail(g, -3, what, e); };
+    {   // host -> device through the two halves of the bounce buffer
+        const char* src = reinterpret_cast<const char*>(mel_host);
+        size_t off = 0;
+        for (int k = 0; off < need[0] && !rc; ++k, off += CHUNK) {
+            const size_t n = need[0] - off < CHUNK ? need[0] - off : CHUNK;
+            char* half = static_cast<char*>(g->pinned) + (k & 1) * CHUNK;
+            cudaError_t e = k >= 2 ? cudaEventSynchronize(ev[k & 1]) : cudaSuccess;
+            if (e != cudaSuccess) { fail_cuda("taco_mel_to_audio: staging", e); break; }
+            memcpy(half, src + off, n);
+            e = cudaMemcpyAsync(reinterpret_cast<char*>(mel) + off, half, n, cudaMemcpyHostToDevice, st);
+            if (e == cudaSuccess) e = cudaEventRecord(ev[k & 1], st);
+            if (e != cudaSuccess) fail_cuda("taco_mel_to_audio: staging", e);
+        }
+        if (!rc && nf) {
+            cudaError_t e = cudaMemcpyAsync(nf, n_frames_host, need[3], cudaMemcpyHostToDevice, st);
+            if (e != cudaSuccess) fail_cuda("taco_mel_to_audio: staging", e);
+        }
+    }
+    if (!rc) rc = taco_gl_mel_to_mag(g, mel, nf, B, F, norm, mag, st);
+    if (!rc) rc = taco_gl_griffin_lim(g, mag, nullptr, nf, seed, utterance0, B, F, iters, preemphasis_k, audio, audio_stride, st);
+    if (!rc) {   // device -> host, chunk k copied out of the bounce buffer while chunk k + 1 is in flight
+        char* dst = reinterpret_cast<char*>(audio_host);
+        const size_t total = need[2];
+        const size_t nchunks = (total + CHUNK - 1) / CHUNK;
+        for (size_t k = 0; k <= nchunks && !rc; ++k) {
+            if (k < nchunks) {
+                const size_t off = k * CHUNK, n = total - off < CHUNK ? total - off : CHUNK;
+                cudaError_t e = cudaMemcpyAsync(static_cast<char*>(g->pinned) + (k & 1) * CHUNK, reinterpret_cast<char*>(audio) + off, n,
+                                                cudaMemcpyDeviceToHost, st);
+                if (e == cudaSuccess) e = cudaEventRecord(ev[k & 1], st);
+                if (e != cudaSuccess) { fail_cuda("taco_mel_to_audio: read back", e); break; }
+            }
+            if (k >= 1) {
+                const size_t j = k - 1, off = j * CHUNK, n = total - off < CHUNK ? total - off : CHUNK;
+                cudaError_t e = cudaEventSynchronize(ev[j & 1]);
+                if (e != cudaSuccess) { fail_cuda("taco_mel_to_audio: read back", e); break; }
+                memcpy(dst + off, static_cast<char*>(g->pinned) + (j & 1) * CHUNK, n);
+            }
+        }
+    }
+    cudaStreamSynchronize(st);
+    cudaEventDestroy(ev[0]);
+    cudaEventDestroy(ev[1]);
     return rc;
 }
 
