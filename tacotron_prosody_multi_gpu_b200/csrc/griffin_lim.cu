@@ -72,15 +72,21 @@ __device__ __forceinline__ void dft8(float2 (&v)[8]) {
 }
 
 // One Stockham autosort pass of radix R (Ns = product of the earlier radices): in -> out, both padded.
-template <int R, int Ns, bool INV>
+// ZIN: the input is known to be zero outside [N/4, 3N/4) (a window of at most N/2 taps centred in the frame): the first
+// radix-8 pass reads only the 4 of its 8 inputs that can be non-zero.  HOUT: only outputs in [N/4, 3N/4) are used (the
+// windowed part of the inverse transform): the last radix-4 pass stores 2 of its 4 outputs.
+template <int R, int Ns, bool INV, bool ZIN = false, bool HOUT = false>
 __device__ __forceinline__ void fft_pass(const float2* __restrict__ in, float2* __restrict__ out, const float2* __restrict__ twp) {
+    static_assert(!ZIN || (R == 8 && Ns == 1), "ZIN is a property of the first pass");
+    static_assert(!HOUT || (R == 4 && Ns == N / 4), "HOUT is a property of the last pass");
     constexpr int T = N / R;
 #pragma unroll
     for (int j = threadIdx.x; j < T; j += GL_THREADS) {
         const int k = j & (Ns - 1), pj = pad(j);
         float2 v[R];
 #pragma unroll
-        for (int r = 0; r < R; ++r) v[r] = in[pj + r * (T + T / 16)];       // pad(j + r T): T is a multiple of 16
+        for (int r = 0; r < R; ++r)                                        // pad(j + r T): T is a multiple of 16
+            v[r] = (ZIN && (r < R / 4 || r >= 3 * R / 4)) ? make_float2(0.f, 0.f) : in[pj + r * (T + T / 16)];
         if (Ns > 1) {
 #pragma unroll
             for (int r = 1; r < R; ++r) {
@@ -96,18 +102,19 @@ __device__ __forceinline__ void fft_pass(const float2* __restrict__ in, float2* 
             dft4<INV>(v[0], v[1], v[2], v[3]);
         }
 #pragma unroll
-        for (int r = 0; r < R; ++r) out[pj0 + r * Ns + ((r * Ns) >> 4)] = v[r];   // pad(j0 + r Ns): no carry out of the low 4 bits
+        for (int r = 0; r < R; ++r)                                        // pad(j0 + r Ns): no carry out of the low 4 bits
+            if (!HOUT || r == 1 || r == 2) out[pj0 + r * Ns + ((r * Ns) >> 4)] = v[r];
     }
     __syncthreads();
 }
 
 // 2048-point FFT, a -> a (b is scratch): radix 8, 8, 8, 4 -- the data ends in the buffer it started in.
-template <bool INV>
+template <bool INV, bool ZIN = false, bool HOUT = false>
 __device__ __forceinline__ void fft2048(float2* a, float2* b, const float2* tw) {
-    fft_pass<8, 1, INV>(a, b, tw);
+    fft_pass<8, 1, INV, ZIN>(a, b, tw);
     fft_pass<8, 8, INV>(b, a, tw + TW_OFF1);
     fft_pass<8, 64, INV>(a, b, tw + TW_OFF2);
-    fft_pass<4, 512, INV>(b, a, tw + TW_OFF3);
+    fft_pass<4, 512, INV, false, HOUT>(b, a, tw + TW_OFF3);
 }
 
 struct GlGeom {
@@ -166,7 +173,7 @@ struct GlArgs {
     int utt0;
 };
 
-template <int MODE>
+template <int MODE, bool CENTRED>
 __global__ void __launch_bounds__(GL_THREADS) gl_kernel(const GlArgs a) {
     extern __shared__ float2 gl_smem[];
     float2* A = gl_smem;
@@ -207,7 +214,8 @@ __global__ void __launch_bounds__(GL_THREADS) gl_kernel(const GlArgs a) {
             }
         }
         __syncthreads();
-        for (int j = tid; j < N; j += GL_THREADS) {
+        // CENTRED: window inside [N/4, 3N/4): skip the known-zero half of the transforms
+        for (int j = CENTRED ? N / 4 + tid : tid; j < (CENTRED ? 3 * N / 4 : N); j += GL_THREADS) {
             const int jj = j - g.lpad;
             float2 z = make_float2(0.f, 0.f);
             if (jj >= 0 && jj < g.win) {
@@ -218,7 +226,7 @@ __global__ void __launch_bounds__(GL_THREADS) gl_kernel(const GlArgs a) {
             A[pad(j)] = z;
         }
         __syncthreads();
-        fft2048<false>(A, Bf, tw);
+        fft2048<false, CENTRED, false>(A, Bf, tw);
     }
 
     float err = 0.f, ref = 0.f;
@@ -277,7 +285,7 @@ __global__ void __launch_bounds__(GL_THREADS) gl_kernel(const GlArgs a) {
         return;
     }
     __syncthreads();
-    fft2048<true>(Bf, A, tw);
+    fft2048<true, false, CENTRED>(Bf, A, tw);
     float* out0 = a.yf_out + ((size_t)b * a.F + t0) * g.win;
     for (int j = tid; j < g.win; j += GL_THREADS) {
         const float wj = __ldg(a.w + j) * (1.0f / N);
@@ -437,17 +445,21 @@ int gl_reserve(TacoGl* g, int B, int F) {
     return 0;
 }
 
-template <int MODE>
-int gl_launch(TacoGl* g, const GlArgs& a, int B, cudaStream_t st) {
+template <int MODE, bool CENTRED>
+int gl_launch2(TacoGl* g, const GlArgs& a, int B, cudaStream_t st) {
     static bool attr_done = false;
     if (!attr_done) {
-        GL_CUDA(cudaFuncSetAttribute(gl_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GL_SMEM));
+        GL_CUDA(cudaFuncSetAttribute(gl_kernel<MODE, CENTRED>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GL_SMEM));
         attr_done = true;
     }
     dim3 grid((a.F + 1) / 2, B);
-    gl_kernel<MODE><<<grid, GL_THREADS, GL_SMEM, st>>>(a);
+    gl_kernel<MODE, CENTRED><<<grid, GL_THREADS, GL_SMEM, st>>>(a);
     GL_CUDA(cudaGetLastError());
     return 0;
+}
+template <int MODE>
+int gl_launch(TacoGl* g, const GlArgs& a, int B, cudaStream_t st) {
+    return 2 * a.g.win <= N ? gl_launch2<MODE, true>(g, a, B, st) : gl_launch2<MODE, false>(g, a, B, st);
 }
 
 }  // namespace
