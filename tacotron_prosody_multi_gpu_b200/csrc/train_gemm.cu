@@ -58,6 +58,18 @@ struct AConvWgrad {
     }
 };
 
+// conv2d(3x3, stride 2, SAME) weight gradient as an implicit GEMM: m = (tap = 3 kh + kw, ci), k = output position (b, ho, wo),
+// A(m, k) = X[b, 2 ho + kh - pt, 2 wo + kw - pl, ci] (NHWC, zero outside); B = dY [positions][Co]; C = dW [3,3,Ci,Co]
+struct AConv2dWgrad {
+    const float* x; int H, W, Ci, Ho, Wo, pt, pl, k_contig;
+    __device__ __forceinline__ float operator()(int m, int k) const {
+        const int tap = m / Ci, ci = m - tap * Ci, kh = tap / 3, kw = tap - 3 * kh;
+        const int r = k / Wo, wo = k - r * Wo, b = r / Ho, ho = r - b * Ho;
+        const int hi = 2 * ho + kh - pt, wi = 2 * wo + kw - pl;
+        return (hi >= 0 && hi < H && wi >= 0 && wi < W) ? x[(((long long)b * H + hi) * W + wi) * Ci + ci] : 0.f;
+    }
+};
+
 template <int BM, int BN, int BK, int TM, int TN, class AL, class BL>
 __global__ void __launch_bounds__((BM / TM) * (BN / TN))
 gemm_kernel(AL A, BL Bm, float* __restrict__ C, long long ldc, int M, int N, int K, float beta, const float* __restrict__ bias,
@@ -561,6 +573,31 @@ int launch_skinny_acc(AL A, BPlain Bm, float* C, long long ldc, float* C2, long 
         }
     }
     gemm_kernel<32, 32, 32, 2, 2, AL, BPlain><<<grid, 256, 0, st>>>(A, Bm, C, ldc, M, N, K, 1.f, nullptr, kchunk, C2, ldc2, N1);
+    return cudaGetLastError() == cudaSuccess ? 0 : -3;
+}
+
+// Reference-encoder conv2d weight gradient as a split-K implicit GEMM (called from train_misc.cu): every (tap, ci) x co tile
+// reads its share of X and dY once, instead of one CTA per (tap, ci) row re-reading all of dY.  Returns 1 when the shape
+// does not qualify (the caller then runs its own kernel), 0 on success, < 0 on error.
+int taco_train_conv2d_wgrad_gemm(const float* x, const float* dy, float* dw, int B, int H, int W, int Ci, int Co, int Ho, int Wo,
+                                 int pt, int pl, cudaStream_t st) {
+    const long long npos = (long long)B * Ho * Wo;
+    const int M = 9 * Ci;
+    if (Ci < 8 || npos < 256 || npos >= (1LL << 31) - 65536) return 1;
+    if (cudaMemsetAsync(dw, 0, sizeof(float) * (size_t)M * Co, st) != cudaSuccess) return -3;
+    const AConv2dWgrad A{x, H, W, Ci, Ho, Wo, pt, pl, 0};
+    const BPlain Bm{dy, Co, 1, 1};
+    const bool big = Co >= 64 && M >= 256;
+    const int tile = big ? 64 : 32;
+    dim3 grid((Co + tile - 1) / tile, (M + tile - 1) / tile, 1);
+    const int ctas = grid.x * grid.y;
+    int splits = (592 + ctas - 1) / ctas;
+    if (splits > (int)(npos / 256)) splits = (int)(npos / 256);
+    if (splits < 1) splits = 1;
+    const int kchunk = (int)(((npos + splits - 1) / splits + 31) / 32 * 32);
+    grid.z = (unsigned)((npos + kchunk - 1) / kchunk);
+    if (big) gemm_kernel<64, 64, 16, 4, 4, AConv2dWgrad, BPlain><<<grid, 256, 0, st>>>(A, Bm, dw, Co, M, Co, (int)npos, 0.f, nullptr, kchunk);
+    else gemm_kernel<32, 32, 32, 2, 2, AConv2dWgrad, BPlain><<<grid, 256, 0, st>>>(A, Bm, dw, Co, M, Co, (int)npos, 0.f, nullptr, kchunk);
     return cudaGetLastError() == cudaSuccess ? 0 : -3;
 }
 

@@ -7,6 +7,9 @@
 #include "../../include/taco_b200_train.h"
 #include "common.cuh"
 
+int taco_train_conv2d_wgrad_gemm(const float* x, const float* dy, float* dw, int B, int H, int W, int Ci, int Co, int Ho, int Wo,
+                                 int pt, int pl, cudaStream_t st);   // train_gemm.cu
+
 namespace {
 
 __host__ __device__ inline int pad_before(int n) {   // SAME padding of a 3-tap stride-2 window
@@ -198,6 +201,10 @@ int taco_op_conv2d_wgrad(const float* x, const float* dy, float* dw, int B, int 
     if (!x || !dy || !dw) return -1;
     if (Co < 1 || Co > 256 || 256 % Co != 0) return -1;
     const int Ho = (H + 1) / 2, Wo = (W + 1) / 2;
+    {   // Ci >= 8: split-K implicit GEMM of train_gemm.cu (fp32); the first layer (Ci = 1) keeps the row-per-CTA kernel below
+        const int rc = taco_train_conv2d_wgrad_gemm(x, dy, dw, B, H, W, Ci, Co, Ho, Wo, pad_before(H), pad_before(W), ST);
+        if (rc <= 0) return rc;
+    }
     if (cudaMemsetAsync(dw, 0, sizeof(float) * 9 * (size_t)Ci * Co, ST) != cudaSuccess) return -3;
     const long long npos = (long long)B * Ho * Wo;
     if (npos >= (1LL << 31) - 65536) return -1;
