@@ -61,7 +61,10 @@ class TacotronOracle(object):
         hoisted input projection of the encoder LSTMs; their recurrent contraction stays fp32).
         ``dec_bf16``: same for the decoder step's contractions (prenet, both LSTM layers, query
         layer, frame/stop projection), the memory-layer keys and the attention values of the context reduction; recurrent
-        state, gate non-linearities, energies, softmax and cumulative alignments stay fp32."""
+        state, gate non-linearities, energies, softmax and cumulative alignments stay fp32.  In this mirror mode the
+        free-running feedback (Helpers.py:56 -> Decoder.py:346) is contracted the way the cluster decoder does it: the last
+        frame's projection and prenet dense_1 precomposed into one [1024 x 256] kernel (see ``_folded_dense1``) -- in exact
+        arithmetic the same function; the plain fp32 oracle keeps the reference's two separate contractions."""
         self.hp = hp
         self.dtype = dtype
         self.conv_bf16 = conv_bf16
@@ -297,12 +300,13 @@ class TacotronOracle(object):
         v_a = self.w[W_LSA + "/attention_variable"]
         b_a = self.w[W_LSA + "/attention_bias"]
         energy = torch.sum(v_a * torch.tanh(keys + q.unsqueeze(1) + loc + b_a), dim=2)        # [B, T]
+        # TF 1.9 _BaseAttentionMechanism wraps EVERY probability_fn as probability_fn(_maybe_mask_score(score, lengths, -inf)):
+        # the -inf mask is applied before the smoothing normalisation too (sigmoid(-inf) = 0)
+        energy = torch.where(mask, energy, torch.full_like(energy, -math.inf))
         if self.hp.smoothing:
-            # Attention.py:405-425 (_smoothing_normalization); NB masking is not applied on this branch in TF
-            sg = torch.sigmoid(energy)
+            sg = torch.sigmoid(energy)                      # Attention.py:405-425 (_smoothing_normalization)
             align = sg / sg.sum(dim=-1, keepdim=True)
         else:
-            energy = torch.where(mask, energy, torch.full_like(energy, -math.inf))
             align = torch.softmax(energy, dim=-1)
         next_cum = align + cum if self.hp.cumulative_weights else align
         vals = _round_bf16(values) if self.dec_bf16 else values
@@ -310,11 +314,28 @@ class TacotronOracle(object):
         return context, align, next_cum
 
     # ------------------------------------------------------------------ decoder
-    def prenet(self, x, keep_masks):
-        """Prenet.__call__ (Decoder.py:342-352): dense+ReLU+dropout(0.5, ALWAYS on). keep_masks: [B, L, units]."""
+    def _folded_dense1(self):
+        """bf16 mirror only: (Wo[:, -M:] . Wp1, bo[-M:] . Wp1 + bp1) composed in float64, as csrc/api.cu pack_decoder3 does."""
+        if getattr(self, "_fold", None) is None:
+            M = self.hp.num_mels
+            wo = self.w[W_FRAME + "/kernel"].double()[:, -M:]
+            bo = self.w[W_FRAME + "/bias"].double()[-M:]
+            wp = self.w[(W_PRENET % 1) + "/kernel"].double()
+            bp = self.w[(W_PRENET % 1) + "/bias"].double()
+            self._fold = ((wo @ wp).float().to(self.dtype), (bo @ wp + bp).float().to(self.dtype))
+        return self._fold
+
+    def prenet(self, x, keep_masks, fold_in=None):
+        """Prenet.__call__ (Decoder.py:342-352): dense+ReLU+dropout(0.5, ALWAYS on). keep_masks: [B, L, units].
+        ``fold_in`` (bf16 mirror, free-running steps > 0): the previous step's projection input [h2raw ; context]; dense_1 is
+        then evaluated through the precomposed kernel instead of from ``x``."""
         keep = 1.0 - self.hp.dropout_rate
         for i in range(len(self.hp.prenet_layers)):
-            x = torch.relu(self._dmm(x, self.w[(W_PRENET % (i + 1)) + "/kernel"]) + self.w[(W_PRENET % (i + 1)) + "/bias"])
+            if i == 0 and fold_in is not None:
+                a, b = self._folded_dense1()
+                x = torch.relu(_round_bf16(fold_in) @ _round_bf16(a) + b)
+            else:
+                x = torch.relu(self._dmm(x, self.w[(W_PRENET % (i + 1)) + "/kernel"]) + self.w[(W_PRENET % (i + 1)) + "/bias"])
             x = x * keep_masks[:, i].to(x.dtype) / keep
         return x
 
@@ -325,9 +346,9 @@ class TacotronOracle(object):
         z = lambda n: torch.zeros(B, n, dtype=self.dtype)
         return DecoderState(z(D), z(D), z(D), z(D), z(mem), z(T), 0)
 
-    def decoder_step(self, x, state, values, keys, mask, keep_masks, is_training=False, zo_masks=None):
+    def decoder_step(self, x, state, values, keys, mask, keep_masks, is_training=False, zo_masks=None, fold_in=None):
         """TacotronDecoderCell.__call__ (Decoder.py:246-292). Returns (frames [B,160], stop [B,2] (logits), state)."""
-        p = self.prenet(x, keep_masks)
+        p = self.prenet(x, keep_masks, fold_in)
         lstm_in = torch.cat([p, state.attention], dim=-1)
         k1, b1 = self.w[(W_DEC_LSTM % (0, 1)) + "/kernel"], self.w[(W_DEC_LSTM % (0, 1)) + "/bias"]
         k2, b2 = self.w[(W_DEC_LSTM % (1, 2)) + "/kernel"], self.w[(W_DEC_LSTM % (1, 2)) + "/bias"]
@@ -338,6 +359,7 @@ class TacotronOracle(object):
         h2raw, c2, h2 = self.zoneout_lstm(h1raw, state.c2, state.h2, k2, b2, is_training, m2, self.dec_bf16)
         context, align, cum = self.attention_step(h2raw, state.alignments, values, keys, mask)
         proj_in = torch.cat([h2raw, context], dim=-1)
+        self._last_proj_in = proj_in
         frames = self._dmm(proj_in, self.w[W_FRAME + "/kernel"]) + self.w[W_FRAME + "/bias"]
         stop_logits = self._dmm(proj_in, self.w[W_STOP + "/kernel"]) + self.w[W_STOP + "/bias"]
         nxt = DecoderState(c1, h1, c2, h2, context, cum, state.time + 1)
@@ -376,7 +398,8 @@ class TacotronOracle(object):
             else:
                 raise ValueError("prenet dropout is always on: pass explicit masks or a philox seed")
             zm = None if zo_masks is None else zo_masks[t]
-            frames, stop_logits, align, state = self.decoder_step(x, state, values, keys, mask, km, is_training, zm)
+            fold_in = self._last_proj_in if (self.dec_bf16 and not teacher and t > 0) else None
+            frames, stop_logits, align, state = self.decoder_step(x, state, values, keys, mask, km, is_training, zm, fold_in)
             stop = stop_logits if is_training else torch.sigmoid(stop_logits)   # Decoder.py:408-410
             frames_l.append(frames)
             stop_l.append(stop)

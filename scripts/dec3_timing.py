@@ -27,14 +27,14 @@ for _ in range(2):
 print("B=%d T=%d S=%d steps=%d kernel %.3f ms -> %.2f us/step" % (B, ids.shape[1], S, d["steps"], eng.stage_ms(1), 1e3 * eng.stage_ms(1) / S))
 buf = np.zeros((128, 24), np.int64)
 eng._check(eng.L.taco_debug_read_workspace(eng._h, b"dec2_timing", buf.ctypes.data_as(C.c_void_p), buf.nbytes), "debug_read")
-names = ["P1.mma", "P1.epi", "P2.mma", "P2.epi", "L1.mma", "L1.epi", "L2.mma", "L2.epi", "E1.qwait", "h2shadow", "E3.softmax", "PROJ.mma", "PROJ.epi", "W1C", "E6loc", "E5.mcast", "E2.energy", "E5.ctx", "sm.load", "sm.max", "sm.exp", "sm.sum", "sm.store", "-"]
+names = ["P1.mma", "P1.epi", "P2.mma", "P2.epi", "L1.mma", "L1.epi", "L2.mma", "L2.epi", "E1.qwait", "zshadow", "E3.softmax", "W1C", "stop", "-", "E6loc", "E5.mcast", "E2.energy", "E5.ctx", "sm.load", "sm.max", "sm.exp", "sm.sum", "sm.store", "-"]
 us = buf / 1e3 / S
-for cls, sel in (("cluster0 rank 0", slice(0, 1)), ("cluster0 rank 5 (x)", slice(5, 6)), ("cluster0 rank 10 (stop)", slice(10, 11)), ("cluster0 rank 15", slice(15, 16)),
-                 ("cluster0 mean", slice(0, 16)), ("cluster1 rank 5 (row 15)", slice(21, 22)), ("cluster1 rank 0", slice(16, 17)), ("cluster1 rank 12", slice(28, 29))):
+for cls, sel in (("cluster0 rank 0 (longest)", slice(0, 1)), ("cluster0 rank 5", slice(5, 6)), ("cluster0 rank 10 (stop)", slice(10, 11)), ("cluster0 rank 15", slice(15, 16)),
+                 ("cluster0 mean", slice(0, 16)), ("cluster1 rank 0 (T=111)", slice(16, 17)), ("cluster1 rank 9", slice(25, 26)), ("cluster1 rank 12", slice(28, 29))):
     m = us[sel].mean(0)
     print("%-24s " % cls + "  ".join("%s %.2f" % (n, v) for n, v in zip(names, m) if n != "-") + "  | sum %.2f us" % m.sum())
 
-# the straggler of every cluster: the CTA that waits least for the feedback frame
+# the straggler of every cluster: the CTA that waits least for the context rows
 for c in range(8):
     blk = us[16 * c:16 * c + 16]
     if blk.sum() == 0:

@@ -77,6 +77,10 @@ struct TacoHandle {
     // cluster decoder (decoder3.cu): per-rank resident A-fragment tiles + L2-streamed tiles
     uint32_t* dec3_res = nullptr;
     uint32_t* dec3_stream = nullptr;
+    uint32_t* dec3_stop_tiles = nullptr;   // [64][128] A-fragment tiles of the stop projection
+    uint32_t* dec3_wo_t = nullptr;         // frame projection kernel, bf16 pairs along k: [160][512]
+    float* dec3_bo = nullptr;              // frame projection bias [160]
+    float dec3_stop_bias[2] = {0.f, 0.f};
     int dec3_max_clusters = -1;  // cudaOccupancyMaxActiveClusters of decoder3_kernel (queried once)
     int dec_kind = 0;            // which decoder kernel owns the running state (1 = decoder.cu, 2 = decoder2.cu)
     float* bilstm_blob[2] = {};  // same two configs, [2 dir][GN][256*4U]
@@ -441,18 +445,26 @@ int pack_decoder3(TacoHandle* h) {
             }
         }
     };
+    // Folded feedback: x(s+1) = [h2raw;ctx].Wo[:,80:160] + bo[80:160] (TacoTestHelper.next_inputs, Helpers.py:56) feeds prenet
+    // dense_1 (Decoder.py:346) => A = Wo[:,80:160].Wp1 [1024 x 256], bfold = bo[80:160].Wp1 + bp1, composed in double.
+    std::vector<float> fold((size_t)1024 * 256), bfold(256);
+    for (int k = 0; k < 1024; ++k)
+        for (int n = 0; n < 256; ++n) {
+            double a = 0.0;
+            for (int m = 0; m < 80; ++m) a += (double)kf->host[(size_t)k * 160 + 80 + m] * (double)kp1->host[(size_t)m * 256 + n];
+            fold[(size_t)k * 256 + n] = (float)a;
+        }
+    for (int n = 0; n < 256; ++n) {
+        double a = bp1->host[n];
+        for (int m = 0; m < 80; ++m) a += (double)bf->host[80 + m] * (double)kp1->host[(size_t)m * 256 + n];
+        bfold[n] = (float)a;
+    }
     const int RW = TACO_DEC3_RES_WORDS, SW = TACO_DEC3_STREAM_TILES * 128;
     std::vector<uint32_t> res((size_t)16 * RW, 0u), str((size_t)16 * SW, 0u);
     for (int c = 0; c < 16; ++c) {
         uint32_t* p = res.data() + (size_t)c * RW;
-        for (int ks = 0; ks < 64; ++ks)   // frame / stop projection of [LSTM output ; context] (Decoder.py:273-279)
-            pack_tile(p + ks * 128, [&](int k, int m) {
-                const int kk = ks * 16 + k;
-                const int slot = dec3_proj_slot(c);
-                if (slot >= 0 && slot < 10) return kf->host[(size_t)kk * 160 + 16 * slot + m];
-                if (slot == 10 && m < 2) return kst->host[(size_t)kk * 2 + m];
-                return 0.f;
-            });
+        for (int ks = 0; ks < 64; ++ks)   // folded dense_1 of [LSTM output ; context]
+            pack_tile(p + ks * 128, [&](int k, int m) { return fold[(size_t)(ks * 16 + k) * 256 + 16 * c + m]; });
         p += 64 * 128;
         for (int ks = 0; ks < 5; ++ks) pack_tile(p + ks * 128, [&](int k, int m) { return kp1->host[(size_t)(ks * 16 + k) * 256 + 16 * c + m]; });
         p += 5 * 128;
@@ -473,8 +485,7 @@ int pack_decoder3(TacoHandle* h) {
         for (int u = 0; u < 16; ++u) {
             bias[128 + u] = bp1->host[16 * c + u];
             bias[144 + u] = bp2->host[16 * c + u];
-            const int slot = dec3_proj_slot(c);
-            bias[160 + u] = (slot >= 0 && slot < 10) ? bf->host[16 * slot + u] : ((slot == 10 && u < 2) ? bst->host[u] : 0.f);
+            bias[160 + u] = bfold[16 * c + u];
         }
         uint32_t* q = str.data() + (size_t)c * SW;
         // streamed sets [4 mt][16 ks]: 0 LSTM-1 prenet rows [0,256); 1 LSTM-2 h1 rows [0,256); 2 LSTM-1 h1 rows [1024,1280);
@@ -489,7 +500,20 @@ int pack_decoder3(TacoHandle* h) {
                 pack_tile(q + (256 + mt * 16 + ks) * 128, [&](int k, int m) { return k1->host[(size_t)(768 + ks * 16 + k) * 1024 + col(m)]; });
             }
     }
+    // stop projection (Decoder.py:404): one m16 tile per k-step, rows 0..1 = the two stop units
+    std::vector<uint32_t> stp((size_t)64 * 128, 0u);
+    for (int ks = 0; ks < 64; ++ks)
+        pack_tile(stp.data() + ks * 128, [&](int k, int m) { return m < 2 ? kst->host[(size_t)(ks * 16 + k) * 2 + m] : 0.f; });
+    h->dec3_stop_bias[0] = bst->host[0];
+    h->dec3_stop_bias[1] = bst->host[1];
+    // frame projection for the post-launch contraction (frame_proj.cu): Wo^T as bf16 pairs along k
+    std::vector<uint32_t> wot((size_t)160 * 512);
+    for (int n = 0; n < 160; ++n)
+        for (int kk = 0; kk < 512; ++kk) wot[(size_t)n * 512 + kk] = pack2(kf->host[(size_t)(2 * kk) * 160 + n], kf->host[(size_t)(2 * kk + 1) * 160 + n]);
     if ((rc = upload_words(h, res, &h->dec3_res))) return rc;
+    if ((rc = upload_words(h, stp, &h->dec3_stop_tiles))) return rc;
+    if ((rc = upload_words(h, wot, &h->dec3_wo_t))) return rc;
+    if ((rc = upload(h, bf->host, &h->dec3_bo))) return rc;
     return upload_words(h, str, &h->dec3_stream);
 }
 
@@ -671,6 +695,11 @@ int decode_v3(TacoHandle* h, int mode, const float* memory, const int32_t* lens,
     if (ncl > h->dec3_max_clusters) ncl = h->dec3_max_clusters;
     if (ncl < (B + 15) / 16) FAIL(TACO_ERR_UNSUPPORTED, "taco_decode: batch needs more co-resident 16-CTA clusters than this device schedules");
     if (ncl < 1) ncl = 1;
+    // the alignment rows of a cluster live in every one of its CTAs: rows per cluster * round_up(T, 4) <= TACO_DEC3_ACAP words
+    p.TP = (T + 3) & ~3;
+    while (ncl < h->dec3_max_clusters && ((B + ncl - 1) / ncl) * p.TP > TACO_DEC3_ACAP) ++ncl;
+    if (((B + ncl - 1) / ncl) * p.TP > TACO_DEC3_ACAP)
+        FAIL(TACO_ERR_UNSUPPORTED, "taco_decode: B x T too large for the cluster decoder (rows per cluster x T exceeds its alignment buffer)");
     p.R = (B + ncl - 1) / ncl;
     p.NCL = (B + p.R - 1) / p.R;
     p.S_max = S_max; p.S_cap = S_max; p.mode = mode;
@@ -681,6 +710,8 @@ int decode_v3(TacoHandle* h, int mode, const float* memory, const int32_t* lens,
     p.keep_scale = 1.0f / (1.0f - hp.dropout_rate);
     p.res_blobs = h->dec3_res;
     p.stream_blobs = reinterpret_cast<const uint4*>(h->dec3_stream);
+    p.stop_tiles = reinterpret_cast<const uint4*>(h->dec3_stop_tiles);
+    p.stop_bias[0] = h->dec3_stop_bias[0]; p.stop_bias[1] = h->dec3_stop_bias[1];
     p.g_hi = h->dec2_ghi; p.g_lo = h->dec2_glo;
     p.va = dev_w(h, std::string(LSA) + "/attention_variable");
     p.bconst = h->dec2_bconst;
@@ -706,8 +737,8 @@ int decode_v3(TacoHandle* h, int mode, const float* memory, const int32_t* lens,
     }
     p.keys = keys;
     p.values = vals;
-    // recurrent state (fp32 row-major): c1 h1z c2 h2z [B][256], ctx [B][768], x [B][80], cum [B][T]
-    const size_t n_state = (size_t)B * (4 * 256 + 768 + 80 + T);
+    // recurrent state (fp32 row-major): c1 h1z c2 h2z [B][256], ctx [B][768], (unused [B][80]), cum [B][T]; h2raw [B][256] after it
+    const size_t n_state = (size_t)B * (4 * 256 + 768 + 80 + T + 256);
     WS(state, float, "dec2_state", n_state)
     if (reset_state) {
         CK(cudaMemsetAsync(state, 0, n_state * sizeof(float), st));
@@ -719,8 +750,11 @@ int decode_v3(TacoHandle* h, int mode, const float* memory, const int32_t* lens,
     p.c2 = s; s += (size_t)B * 256;
     p.h2z = s; s += (size_t)B * 256;
     p.ctx_state = s; s += (size_t)B * 768;
-    p.x_state = s; s += (size_t)B * 80;
-    p.cum = s;
+    s += (size_t)B * 80;
+    p.cum = s; s += (size_t)B * T;
+    p.h2raw = s;
+    WS(act, uint32_t, "dec3_act_hist", (size_t)S_max * B * 512)
+    p.act_hist = act;
     WS(pre, float, "dec3_pre", (size_t)B * T * 128)
     p.pre_scratch = pre;
     p.cont = reset_state ? 0 : 1;
@@ -728,7 +762,7 @@ int decode_v3(TacoHandle* h, int mode, const float* memory, const int32_t* lens,
     p.t0 = h->dec_t;
     p.targets = mel_targets; p.F_tgt = F_tgt;
     p.masks = prenet_masks; p.seed = philox_seed;
-    p.frames = frames; p.stop = stop; p.hist = align_hist; p.steps_out = steps_out;
+    p.stop = stop; p.hist = align_hist; p.steps_out = steps_out;
     const size_t n_flags = (size_t)S_max * p.NCL + 8;
     WS(flags, int, "dec3_flags", n_flags)
     CK(cudaMemsetAsync(flags, 0, n_flags * sizeof(int), st));
@@ -741,6 +775,9 @@ int decode_v3(TacoHandle* h, int mode, const float* memory, const int32_t* lens,
     }
     CK(cudaEventRecord(h->ev[TACO_STAGE_DECODER_KERNEL][0], st));
     CK(taco_launch_decoder3(p, st));
+    // frame projection of all executed steps (hoisted out of the recurrence: nothing in the loop reads the frames)
+    CK(taco_launch_frame_projection(act, h->dec3_wo_t, h->dec3_bo, steps_out, S_max, B, S_max, frames, st));
+    h->launches++;
     CK(cudaEventRecord(h->ev[TACO_STAGE_DECODER_KERNEL][1], st));
     h->ev_valid[TACO_STAGE_DECODER_KERNEL] = true;
     h->launches++;
@@ -1103,7 +1140,9 @@ int taco_decode(TacoHandle* h, int mode, const float* memory, const int32_t* len
         h->dec3_max_clusters = n > TACO_DEC3_MAX_CLUSTERS ? TACO_DEC3_MAX_CLUSTERS : n;
     }
     const char* force = getenv("TACO_DECODER");   // "2": dataflow kernel through L2 (decoder2.cu), kept for comparison
-    if (h->precision == TACO_PRECISION_BF16 && T <= TACO_DEC3_TMAX && h->dec3_max_clusters * 16 >= B && !(force && force[0] == '2'))
+    const bool dec3_fits = h->dec3_max_clusters > 0 && T <= TACO_DEC3_TMAX && h->dec3_max_clusters * 16 >= B &&
+                           ((B + h->dec3_max_clusters - 1) / h->dec3_max_clusters) * ((T + 3) & ~3) <= TACO_DEC3_ACAP;
+    if (h->precision == TACO_PRECISION_BF16 && dec3_fits && !(force && force[0] == '2'))
         return decode_v3(h, mode, memory, lens, B, T, mel_targets, F_tgt, S_max, prenet_masks, philox_seed, reset_state, logits_only,
                          frames, stop, align_hist, steps_out, st);
     if (h->precision == TACO_PRECISION_BF16 && T <= TACO_DEC2_TMAX)

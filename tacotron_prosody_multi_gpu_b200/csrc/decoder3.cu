@@ -43,16 +43,15 @@ constexpr int KS_X = 5, KS_H = 16, KS_CTX = 48;
 constexpr int TILE_W = 128;             // words of one A tile (32 lanes x uint4) and of one B k-step block (2 n-tiles x 32 lanes x uint2)
 
 // ---- shared-memory map (32-bit word offsets) ----
-constexpr int SO_WO = 0;                          // [64 ks] frame/stop projection tiles (ks 0..15: h2raw, 16..63: context)
-constexpr int SO_WP1 = SO_WO + 64 * TILE_W;       // [5]
+constexpr int SO_WF = 0;                          // [64 ks] folded feedback projection . prenet dense_1 (ks 0..15: h2raw, 16..63: context)
+constexpr int SO_WP1 = SO_WF + 64 * TILE_W;       // [5]  prenet dense_1 itself (teacher-forced steps)
 constexpr int SO_WP2 = SO_WP1 + 5 * TILE_W;       // [16]
 constexpr int W1C_RES = 32;                       // k-steps of the LSTM-1 context rows kept in shared memory (of 48)
 constexpr int SO_W1C = SO_WP2 + 16 * TILE_W;      // [4 mt][32 ks]  LSTM-1, context rows [256, 256 + 512)
 constexpr int SO_WQ = SO_W1C + 4 * W1C_RES * TILE_W;  // [8 mt]     query kernel rows of this CTA's 16 units
-constexpr int SO_BIAS = SO_WQ + 8 * TILE_W;       // b1[64] b2[64] bp1[16] bp2[16] bo[16]
+constexpr int SO_BIAS = SO_WQ + 8 * TILE_W;       // b1[64] b2[64] bp1[16] bp2[16] bfold[16]
 constexpr int RES_WORDS = SO_BIAS + 176;          // resident blob words per rank
-constexpr int SO_X = RES_WORDS;                   // activation buffers (B-fragment order, one 128-word block per k-step)
-constexpr int SO_P1 = SO_X + KS_X * TILE_W;
+constexpr int SO_P1 = RES_WORDS;                  // activation buffers (B-fragment order, one 128-word block per k-step)
 constexpr int SO_P2 = SO_P1 + KS_H * TILE_W;
 constexpr int SO_H1R = SO_P2 + KS_H * TILE_W;
 constexpr int SO_H1Z = SO_H1R + KS_H * TILE_W;
@@ -64,8 +63,8 @@ constexpr int RED_WORDS = 16 * 16 * 17;
 constexpr int SO_QRECV = SO_RED + RED_WORDS;      // [16 src][128] fp32 query partials of this CTA's attention row
 constexpr int SO_STG_R = SO_QRECV + 16 * ATT;     // staging: raw block, zoned block, context row
 constexpr int SO_STG_Z = SO_STG_R + TILE_W;
-constexpr int SO_STG_C = SO_STG_Z + TILE_W;       // [48 ks][8 words]
-constexpr int SO_ES = SO_STG_C + KS_CTX * 8;      // [T_MAX3]
+constexpr int SO_STG_C = SO_STG_Z + TILE_W;       // [3 k-steps][128 words]: this CTA's context slice, B-fragment order
+constexpr int SO_ES = SO_STG_C + 3 * TILE_W;      // [T_MAX3]
 constexpr int SO_CPAD = SO_ES + T_MAX3;           // [T_MAX3 + 48]  cpad[i] = cum[i - 15]
 constexpr int PW3 = (T_MAX3 + 48) / 2;
 constexpr int SO_P = SO_CPAD + T_MAX3 + 48;       // 4 x [PW3] pair arrays P0hi, P1hi, P0lo, P1lo
@@ -75,11 +74,15 @@ constexpr int SO_BC = SO_VA + ATT;
 constexpr int SO_FLAG = SO_BC + ATT;              // [16]: 0 = stop decision, 8.. = prefetched stop words of the clusters
 constexpr int SO_TACC = SO_FLAG + 16;              // 24 x int64 stage timers
 constexpr int SO_OWN = SO_TACC + 48;             // [16]: cluster rank that owns the attention of cluster row i
-constexpr int SMEM3_WORDS = SO_OWN + 16;
+constexpr int SO_LEN = SO_OWN + 16;              // [16]: memory length of cluster row i
+constexpr int SO_GRP = SO_LEN + 16;              // [16][2]: first thread group / number of groups of row i in the context-slice reduction
+constexpr int SO_AALL = SO_GRP + 32;             // [R][TP] alignment rows of every cluster row, multicast by their owners
+constexpr int A_CAP = TACO_DEC3_ACAP;            // words: R * TP <= A_CAP (the host picks the cluster count accordingly)
+constexpr int SMEM3_WORDS = SO_AALL + A_CAP;
 static_assert(RES_WORDS == TACO_DEC3_RES_WORDS, "resident blob size");
 static_assert(SMEM3_WORDS * 4 <= 227 * 1024, "shared memory budget");
-static_assert(SO_X % 4 == 0 && SO_RED % 4 == 0 && SO_QRECV % 4 == 0 && SO_STG_R % 4 == 0 && SO_STG_C % 4 == 0 && SO_ES % 4 == 0 &&
-              SO_QS % 4 == 0 && SO_TACC % 2 == 0, "smem alignment");
+static_assert(SO_P1 % 4 == 0 && SO_RED % 4 == 0 && SO_QRECV % 4 == 0 && SO_STG_R % 4 == 0 && SO_STG_C % 4 == 0 && SO_ES % 4 == 0 &&
+              SO_QS % 4 == 0 && SO_TACC % 2 == 0 && SO_AALL % 4 == 0, "smem alignment");
 
 extern __shared__ __align__(16) uint32_t smem3[];
 #define SMU(off) (smem3 + (off))

@@ -145,10 +145,20 @@ __device__ __forceinline__ void att3_location(const Dec3Params& p, float (&preR)
     }
 }
 
-// One attention step of cluster row `rank` (global row b; the CTA that runs it is chosen by row length, SO_OWN): q from the 16 partials, energies, masked softmax, cumulate,
-// alignment history, context (bf16 values, fp32 accumulate), multicast of the context row, next step's location term.
-__device__ __forceinline__ void att3_step(const Dec3Params& p, float (&preR)[8][4], float* pre_scr, int b, int len, int rank, int s,
-                                          int tid, int warp, int lane, Guard3& g, long long* tacc, long long& tprev, bool timing) {
+// thread -> (row, position slot, 16-byte column chunk) of the column-sliced context reduction (att3_context_slice), packed:
+// bits 0..3 cluster row, 4..11 first position (slot), 12..19 number of slots of the row (0: no work), 20..31 row length;
+// the thread takes positions slot, slot + nslot, ... of columns [48 rank + 8 chunk, + 8), chunk = tid % 6, group = tid / 6
+constexpr int CTX_GROUPS = 85;   // 85 groups x 6 chunks of 8 columns = 510 threads
+constexpr int CTX_BASE = CTX_GROUPS - CS;   // groups dealt in proportion to the row lengths; + 1 per row
+
+// groups of row r = floor(CTX_BASE * len_r / sum(len)) + 1  (sum <= CTX_GROUPS for <= 16 rows)
+__device__ __forceinline__ int ctx_groups_of(int len, int total) { return (CTX_BASE * len) / total + 1; }
+
+// Owner part of one attention step of cluster row `arow` (global row b; the CTA that runs it is chosen by row length, SO_OWN):
+// q from the 16 partials, energies, masked softmax, cumulate, alignment history, and the multicast of the alignment row to
+// every CTA of the cluster (each of which reduces a 48-column slice of the context, att3_context_slice).
+__device__ __forceinline__ void att3_owner(const Dec3Params& p, float (&preR)[8][4], float* pre_scr, int b, int len, int arow, int s,
+                                           int tid, int warp, int lane, Guard3& g, long long* tacc, long long& tprev, bool timing) {
     float* scr = SMF(SO_RED);
 #define A3_STAMP(i)                                                     \
     if (timing) { /* whole warp 0, uniform: a divergent stamp would push the following collectives onto their slow path */ \
@@ -196,13 +206,6 @@ __device__ __forceinline__ void att3_step(const Dec3Params& p, float (&preR)[8][
                 }
             }
         }
-        __syncthreads();
-        if (tid < len) {
-            float e = 0.f;
-#pragma unroll
-            for (int w = 0; w < 16; ++w) e += scr[w * PRE_REG_T + tid];
-            SMF(SO_ES)[tid] = e;
-        }
     } else {
         const int tl = lane & 7, qd = lane >> 3;
         const float4* q4 = reinterpret_cast<const float4*>(SMF(SO_QS) + qd * 32);
@@ -230,19 +233,22 @@ __device__ __forceinline__ void att3_step(const Dec3Params& p, float (&preR)[8][
     A3_STAMP(16)
     // E3: masked softmax over t < len (exact zeros beyond: -inf mask), Attention.py:203-206
     if (warp == 0) {
-        if (len <= 128) {
-            // whole row in registers: 4 positions per lane
+        if (p.pre_reg) {
+            // whole row in registers: 4 positions per lane, each the sum of the 16 per-warp partials
             float e[4];
             float m = -INFINITY;
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
                 const int t = lane + 32 * i;
-                e[i] = t < len ? SMF(SO_ES)[t] : -INFINITY;
+                float x = 0.f;
+                if (t < len) {
+#pragma unroll
+                    for (int w = 0; w < 16; ++w) x += scr[w * PRE_REG_T + t];
+                }
+                e[i] = t < len ? x : -INFINITY;
                 m = fmaxf(m, e[i]);
             }
-            A3_STAMP(18)
             m = p.smoothing ? 0.f : warp_max(m);
-            A3_STAMP(19)
             float sum = 0.f;
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
@@ -250,16 +256,13 @@ __device__ __forceinline__ void att3_step(const Dec3Params& p, float (&preR)[8][
                 e[i] = t < len ? (p.smoothing ? sigmoidf_(e[i]) : __expf(e[i] - m)) : 0.f;
                 sum += e[i];
             }
-            A3_STAMP(20)
             sum = warp_sum(sum);
-            A3_STAMP(21)
             const float inv = __fdividef(1.0f, sum);
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
                 const int t = lane + 32 * i;
-                if (t < len) SMF(SO_ES)[t] = e[i] * inv;
+                if (t < PRE_REG_T) SMF(SO_ES)[t] = e[i] * inv;   // exact zeros beyond the length
             }
-            A3_STAMP(22)
         } else {
             float m = -INFINITY;
             if (!p.smoothing) {
@@ -279,80 +282,147 @@ __device__ __forceinline__ void att3_step(const Dec3Params& p, float (&preR)[8][
     }
     __syncthreads();
     A3_STAMP(10)
+    // multicast the alignment row to every CTA of the cluster (positions < len; the context slices never read beyond)
+    {
+        const int nv = (len + 3) >> 2;
+        const int TP = p.TP;
+        for (int i = tid; i < CS * nv; i += NT) {
+            const int slot = i / nv, v = i - slot * nv;
+            const int dst = (slot + arow) & (CS - 1);
+            const uint4 val = *reinterpret_cast<const uint4*>(SMU(SO_ES) + (v << 2));
+            st_remote_v4(mapa_rank(smem_addr(SMU(SO_AALL) + arow * TP + (v << 2)), dst), val);
+        }
+    }
     // E4: cumulate + alignment history
     for (int t = tid; t < p.T; t += NT) {
         const float a = t < len ? SMF(SO_ES)[t] : 0.f;
         SMF(SO_CPAD)[15 + t] = p.cumulative ? SMF(SO_CPAD)[15 + t] + a : a;
         p.hist[((size_t)s * p.B + b) * p.T + t] = a;
     }
-    // E5: context = sum_t a[t] values[b][t][:]   (_compute_attention, Attention.py:345-366)
-    {
-        constexpr int D8 = MEM / 8, TG = 5;
-        const int d8 = tid % D8, tg = tid / D8;
-        float c[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-        if (tg < TG) {
-            const uint4* vp = reinterpret_cast<const uint4*>(p.values + (size_t)b * p.T * MEM) + d8;
-            // fixed-size predicated batches: every load of a batch is in flight before the first FMA needs one (a plain
-            // unrolled loop leaves a remainder loop that pays one L2 latency per position)
-            constexpr int UB = 12;
-            for (int t0 = tg; t0 < len; t0 += TG * UB) {
-                uint4 v[UB];
-                float a[UB];
-#pragma unroll
-                for (int u = 0; u < UB; ++u) {
-                    const int t = t0 + u * TG;
-                    const bool ok = t < len;
-                    v[u] = ok ? ldg_stream_v4(vp + (size_t)t * D8) : make_uint4(0u, 0u, 0u, 0u);
-                    a[u] = ok ? SMF(SO_ES)[t] : 0.f;
-                }
-#pragma unroll
-                for (int u = 0; u < UB; ++u) {
-                    c[0] = fmaf(a[u], bf_lo(v[u].x), c[0]);
-                    c[1] = fmaf(a[u], bf_hi(v[u].x), c[1]);
-                    c[2] = fmaf(a[u], bf_lo(v[u].y), c[2]);
-                    c[3] = fmaf(a[u], bf_hi(v[u].y), c[3]);
-                    c[4] = fmaf(a[u], bf_lo(v[u].z), c[4]);
-                    c[5] = fmaf(a[u], bf_hi(v[u].z), c[5]);
-                    c[6] = fmaf(a[u], bf_lo(v[u].w), c[6]);
-                    c[7] = fmaf(a[u], bf_hi(v[u].w), c[7]);
-                }
-            }
-            float4* dst = reinterpret_cast<float4*>(scr + (size_t)tg * MEM + d8 * 8);
-            dst[0] = make_float4(c[0], c[1], c[2], c[3]);
-            dst[1] = make_float4(c[4], c[5], c[6], c[7]);
-        }
-        __syncthreads();
-        if (tid < MEM / 2) {
-            float x0 = 0.f, x1 = 0.f;
-#pragma unroll
-            for (int q = 0; q < TG; ++q) {
-                const float2 v = *reinterpret_cast<const float2*>(scr + (size_t)q * MEM + 2 * tid);
-                x0 += v.x;
-                x1 += v.y;
-            }
-            const int ks = tid >> 3, j = tid & 7;
-            SMU(SO_STG_C)[ks * 8 + ((j & 3) << 1) + (j >> 2)] = pack_bf16x2(x0, x1);
-            *reinterpret_cast<float2*>(p.ctx_state + (size_t)b * MEM + 2 * tid) = make_float2(x0, x1);
-        }
-        __syncthreads();
-        A3_STAMP(17)
-        // multicast this row's 48 x 32-byte chunks into every CTA's context buffer
-        for (int i = tid; i < CS * KS_CTX * 2; i += NT) {
-            const int slot = i / (KS_CTX * 2), v = i - slot * (KS_CTX * 2);
-            const int dst = slot < 5 ? slot + 11 : slot - 5;   // feedback-frame producers (ranks 11..15) first
-            const int ks = v >> 1, half = v & 1;
-            const uint4 val = *reinterpret_cast<const uint4*>(SMU(SO_STG_C) + ks * 8 + half * 4);
-            st_remote_v4(mapa_rank(smem_addr(SMU(SO_CTX) + ks * TILE_W + ((rank >> 3) << 6) + ((rank & 7) << 3) + half * 4), dst), val);
-        }
-    }
+    if (!p.cumulative) __syncthreads();
+    // pair arrays of the new alignments for the location term of the next step (att3_loc_chunk, in the shadow of later exchanges)
+    att3_build_pairs(p.T, tid, p.cumulative != 0, len);
     A3_STAMP(15)
 }
 
-// E6 (off the critical path, after the projection): location pre-activations of the NEXT step from the new cumulative alignments
-__device__ __forceinline__ void att3_next(const Dec3Params& p, float (&preR)[8][4], float* pre_scr, int b, int len, int tid, int warp, int lane) {
-    att3_build_pairs(p.T, tid, p.cumulative != 0, len);
+// Context of ALL rows of the cluster, columns [48 rank, 48 rank + 48): ctx[r][c] = sum_t a[r][t] values[r][t][c]
+// (_compute_attention, Attention.py:345-366; bf16 values, fp32 accumulate).  Every CTA reduces its slice from the alignment rows
+// the owners multicast, then multicasts its three k-step blocks (B-fragment order) to the whole cluster: the reduction is spread
+// over 16 SMs' L2 ports instead of one per row, and nobody waits for the CTA that owns the longest row.
+__device__ __forceinline__ void att3_context_slice(const Dec3Params& p, uint32_t cmw, int row0, int R, int rank, int s, int tid,
+                                                   Guard3& g) {
+    float* scr = SMF(SO_RED);
+    const int TP = p.TP;
+    __syncthreads();   // the K-split partials / query slices of this step (same scratch) have been read
+    const int nslot = (cmw >> 12) & 255;
+    if (nslot) {
+        const int crow = cmw & 15, cslot = (cmw >> 4) & 255, len = cmw >> 20;
+        const int b = row0 + crow;
+        const int gidx = tid / 6, chunk = tid - gidx * 6;
+        const uint4* vp = reinterpret_cast<const uint4*>(p.values) + (size_t)b * p.T * (MEM / 8) + 6 * rank + chunk;
+        const uint32_t* al = SMU(SO_AALL) + crow * TP;
+        float c[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        constexpr int UB = 5;
+        for (int t0 = cslot; t0 < len; t0 += nslot * UB) {
+            uint4 v[UB];
+            float a[UB];
+#pragma unroll
+            for (int u = 0; u < UB; ++u) {
+                const int t = t0 + u * nslot;
+                v[u] = t < len ? ldg_stream_v4(vp + (size_t)t * (MEM / 8)) : make_uint4(0u, 0u, 0u, 0u);
+            }
+#pragma unroll
+            for (int u = 0; u < UB; ++u) {
+                const int t = t0 + u * nslot;
+                uint32_t w = 0u;
+                if (t < len) {
+                    w = *reinterpret_cast<const volatile uint32_t*>(al + t);
+                    int spins = 0;
+                    while (w == SENT && !spin_check3(g, spins)) w = *reinterpret_cast<const volatile uint32_t*>(al + t);
+                    if (g.dead) w = 0u;
+                }
+                a[u] = __uint_as_float(w);
+            }
+#pragma unroll
+            for (int u = 0; u < UB; ++u) {
+                c[0] = fmaf(a[u], bf_lo(v[u].x), c[0]);
+                c[1] = fmaf(a[u], bf_hi(v[u].x), c[1]);
+                c[2] = fmaf(a[u], bf_lo(v[u].y), c[2]);
+                c[3] = fmaf(a[u], bf_hi(v[u].y), c[3]);
+                c[4] = fmaf(a[u], bf_lo(v[u].z), c[4]);
+                c[5] = fmaf(a[u], bf_hi(v[u].z), c[5]);
+                c[6] = fmaf(a[u], bf_lo(v[u].w), c[6]);
+                c[7] = fmaf(a[u], bf_hi(v[u].w), c[7]);
+            }
+        }
+        float4* dst = reinterpret_cast<float4*>(scr + gidx * 48 + chunk * 8);
+        dst[0] = make_float4(c[0], c[1], c[2], c[3]);
+        dst[1] = make_float4(c[4], c[5], c[6], c[7]);
+    }
+    g.dead = __syncthreads_or(g.dead ? 1 : 0) != 0;
+    // every alignment row has been consumed: re-arm (valid rows only; rows >= R are never written)
+    for (int i = tid; i < (R * TP) >> 2; i += NT) reinterpret_cast<uint4*>(SMU(SO_AALL))[i] = make_uint4(SENT, SENT, SENT, SENT);
+    if (tid < R * 24) {
+        const int r = tid / 24, cp = tid - r * 24;
+        const int g0 = (int)SMU(SO_GRP)[2 * r], ng = (int)SMU(SO_GRP)[2 * r + 1];   // groups of row r: [g0, g0 + ng)
+        float x0 = 0.f, x1 = 0.f;
+        for (int q = 0; q < ng; ++q) {
+            const float2 v = *reinterpret_cast<const float2*>(scr + (g0 + q) * 48 + 2 * cp);
+            x0 += v.x;
+            x1 += v.y;
+        }
+        const int b = row0 + r;
+        const uint32_t cw = pack_bf16x2(x0, x1);
+        const int k = cp >> 3, j = cp & 7;
+        SMU(SO_STG_C)[k * TILE_W + bword(r, j)] = cw;
+        *reinterpret_cast<float2*>(p.ctx_state + (size_t)b * MEM + 48 * rank + 2 * cp) = make_float2(x0, x1);
+        p.act_hist[((size_t)s * p.B + b) * 512 + 128 + 24 * rank + cp] = cw;   // projection input row of this step, columns 256..1023
+    }
     __syncthreads();
-    att3_location(p, preR, pre_scr, b, len, warp, lane, p.cumulative != 0);
+    // multicast this CTA's three k-step blocks (3 rank .. 3 rank + 2) to every CTA of the cluster
+    {
+        const int dst = tid >> 5, v = tid & 31;
+        const int row = ((v >> 4) << 3) + ((v & 15) >> 1);
+        if (row < R) {
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                const uint4 val = *reinterpret_cast<const uint4*>(SMU(SO_STG_C) + k * TILE_W + (v << 2));
+                st_remote_v4(mapa_rank(smem_addr(SMU(SO_CTX) + (3 * rank + k) * TILE_W + (v << 2)), dst), val);
+            }
+        }
+    }
+}
+
+// Location pre-activations of the NEXT step from the new alignments (pair arrays built by att3_owner), tiles [i0, i1) of the
+// in-register path; the scratch path (T > 128) runs all its tiles in the first call.  Warp-local: no block synchronisation,
+// so the chunks can sit in the shadow of the dense_2 / LSTM-1 exchanges.
+__device__ __forceinline__ void att3_loc_chunk(const Dec3Params& p, float (&preR)[8][4], float* pre_scr, int b, int len, int warp, int lane,
+                                               int i0, int i1) {
+    if (!p.cumulative) {   // not incremental: pre = keys + location(a) + const, every step
+        if (i0 == 0) att3_location(p, preR, pre_scr, b, len, warp, lane, false);
+        return;
+    }
+    if (!p.pre_reg) {
+        if (i0 == 0) att3_location(p, preR, pre_scr, b, len, warp, lane, true);
+        return;
+    }
+    uint2 ghi[2], glo[2];
+#pragma unroll
+    for (int ks = 0; ks < 2; ++ks) {
+        ghi[ks] = __ldg(reinterpret_cast<const uint2*>(p.g_hi) + (ks * 16 + warp) * 32 + lane);
+        glo[ks] = __ldg(reinterpret_cast<const uint2*>(p.g_lo) + (ks * 16 + warp) * 32 + lane);
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        if (i >= i0 && i < i1 && 16 * i < len) {
+            float acc[4];
+            att3_loc_tile(acc, 16 * i, lane, ghi, glo);
+            preR[i][0] += acc[0];
+            preR[i][1] += acc[1];
+            preR[i][2] += acc[2];
+            preR[i][3] += acc[3];
+        }
+    }
 }
 
 }  // namespace

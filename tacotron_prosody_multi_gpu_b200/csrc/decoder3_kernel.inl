@@ -4,6 +4,8 @@
 namespace {
 
 constexpr int STOP_LAG = 8;
+constexpr int STOP_RANK = 10;   // cluster rank that computes the stop-token projection
+constexpr int ACT_W = 1024;     // projection input row: [h2raw 256 | context 768] (Decoder.py:272)
 
 #define D3_STAMP(i)                                                     \
     if (timing) { /* whole warp 0, uniform: a divergent stamp would push the following collectives onto their slow path */ \
@@ -12,6 +14,43 @@ constexpr int STOP_LAG = 8;
         if (lane == 0) tacc[i] += now_ - tprev;                         \
         tprev = now_;                                                   \
     }
+
+// Stop-token projection of launch step s_idx for the rows of this cluster (StopProjection, Decoder.py:404-410; the batch-global
+// decision of TacoTestHelper.next_inputs, Helpers.py:36-59): [h2raw ; context] . Ws[1024 x 2] as 64 k-steps of one m16 tile whose
+// rows 0..1 are the two stop units.  Runs on ONE rank per cluster, off the critical path; its tiles stream from L2.
+__device__ __noinline__ void dec3_stop_token(const Dec3Params& p, int s_idx, int row0, int R, int cid, bool free_run, float* red, int tid,
+                                             int warp, int lane, Guard3& g) {
+    float acc[2][4] = {};
+    uint4 a[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) a[i] = ldg_stream_v4(p.stop_tiles + (size_t)(warp + 16 * i) * 32 + lane);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const uint32_t* blk = i == 0 ? SMU(SO_H2R) + warp * TILE_W : SMU(SO_CTX) + (warp + 16 * (i - 1)) * TILE_W;
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+            const uint2 b = load_b(blk, j, lane, g);
+            mma16816(acc[j], a[i], b);
+        }
+    }
+    store_red3(red, acc, warp, lane, 2);
+    __syncthreads();
+    bool fin = false;
+    if (tid < 256) {
+        const int eu = tid & 15, er = tid >> 4;
+        if (eu < 2 && er < R) {
+            float y = p.stop_bias[eu];
+#pragma unroll
+            for (int k = 0; k < 16; ++k) y += red[(k * 16 + eu) * 17 + er];
+            const float sg = sigmoidf_(y);
+            p.stop[(size_t)(row0 + er) * p.S_cap * 2 + (size_t)s_idx * 2 + eu] = p.stop_sigmoid ? sg : y;
+            fin = sg > 0.5f;   // tf.round(sigmoid) == 1 <=> sigmoid > 0.5 (half-to-even; Helpers.py:40)
+        }
+    }
+    const int cnt = __syncthreads_count(fin ? 1 : 0);
+    if (free_run && tid == 0)
+        stg_relaxed(reinterpret_cast<uint32_t*>(p.flags) + (size_t)s_idx * p.NCL + cid, (p.stop_at_any ? cnt > 0 : cnt == 2 * R) ? 2u : 1u);
+}
 
 // fill one activation buffer from a row-major fp32 state array [B][width] (rows row0 .. row0+R-1 of this cluster)
 __device__ __forceinline__ void fill_from_state(uint32_t* buf, const float* state, int width, int row0, int R, int tid) {
@@ -28,7 +67,6 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
     cg::cluster_group cluster = cg::this_cluster();
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int rank = (int)cluster.block_rank();
-    const int slot = dec3_proj_slot(rank);
     const int cid = blockIdx.x / CS;
     const int row0 = cid * p.R;
     const int R = min(p.R, p.B - row0);
@@ -47,7 +85,7 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
         }
         for (int i = tid; i < T_MAX3 + 48; i += NT) SMF(SO_CPAD)[i] = 0.f;
         if (tid < 16 + 48) SMU(SO_FLAG)[tid] = 0;
-        rearm(SMU(SO_X), KS_X + 6 * KS_H + KS_CTX, R, tid);   // all activation buffers are contiguous
+        rearm(SMU(SO_P1), 6 * KS_H + KS_CTX, R, tid);   // all activation buffers are contiguous
         for (int i = tid; i < CS * ATT; i += NT) SMU(SO_QRECV)[i] = SENT;
     }
     __syncthreads();
@@ -55,23 +93,24 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
     fill_from_state(SMU(SO_CTX), p.ctx_state, MEM, row0, R, tid);
     fill_from_state(SMU(SO_H1Z), p.h1z, DEC, row0, R, tid);
     fill_from_state(SMU(SO_H2Z), p.h2z, DEC, row0, R, tid);
-    if (free_run) fill_from_state(SMU(SO_X), p.x_state, MEL, row0, R, tid);
+    // folded prenet dense_1 of the first step of a continuation launch reads the raw LSTM-2 output of step t0-1
+    if (free_run && p.t0 > 0) fill_from_state(SMU(SO_H2R), p.h2raw, DEC, row0, R, tid);
 
     // epilogue threads: (unit eu = tid & 15 of this CTA's 16 units, cluster row er = tid >> 4); fp32 recurrent state in registers
     const int eu = tid & 15, er = tid >> 4;
     const bool ept = tid < 256;
     const bool evalid = ept && er < R;
     const int eb = row0 + er;
-    float c1s = 0.f, h1s = 0.f, c2s = 0.f, h2s = 0.f;
+    float c1s = 0.f, h1s = 0.f, c2s = 0.f, h2s = 0.f, h2r_last = 0.f;
     if (evalid) {
+        h2r_last = p.h2raw[(size_t)eb * DEC + 16 * rank + eu];
         c1s = p.c1[(size_t)eb * DEC + 16 * rank + eu];
         h1s = p.h1z[(size_t)eb * DEC + 16 * rank + eu];
         c2s = p.c2[(size_t)eb * DEC + 16 * rank + eu];
         h2s = p.h2z[(size_t)eb * DEC + 16 * rank + eu];
     }
-    // attention work items: one cluster row per CTA.  The rows are dealt by length: the 5 longest to ranks 5..9, which
-    // compute no projection slot (dec3_proj_slot) -- the owner of the longest row is the last CTA to leave the attention
-    // phase and must not carry extra work into the next step -- the next 5 to ranks 0..4, the rest to ranks 10..15.
+    // attention work items: one cluster row per CTA, dealt by length to ranks 0..9, 11..15 and last to rank 10, which
+    // also computes the stop-token projection of the cluster (a cluster of <= 15 rows leaves it without a row).
     if (tid < 16) {
         int pos = 0;
         if (tid < R) {
@@ -81,9 +120,30 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
                 pos += (l2 > mylen || (l2 == mylen && r2 < tid)) ? 1 : 0;
             }
         }
-        SMU(SO_OWN)[tid] = tid < R ? (pos < 5 ? pos + 5 : (pos < 10 ? pos - 5 : pos)) : 0xFFFFu;
+        SMU(SO_OWN)[tid] = tid < R ? (pos < STOP_RANK ? pos : (pos < CS - 1 ? pos + 1 : STOP_RANK)) : 0xFFFFu;
+        SMU(SO_LEN)[tid] = tid < R ? (uint32_t)p.lens[row0 + tid] : 0u;
+    }
+    for (int i = tid; i < (R * p.TP) >> 2; i += NT) reinterpret_cast<uint4*>(SMU(SO_AALL))[i] = make_uint4(SENT, SENT, SENT, SENT);
+    __syncthreads();
+    if (tid == 0) {   // thread groups of the context-slice reduction, dealt in proportion to the row lengths
+        int total = 0, g0 = 0;
+        for (int r2 = 0; r2 < R; ++r2) total += (int)SMU(SO_LEN)[r2];
+        for (int r2 = 0; r2 < R; ++r2) {
+            const int ng = ctx_groups_of((int)SMU(SO_LEN)[r2], total);
+            SMU(SO_GRP)[2 * r2] = g0;
+            SMU(SO_GRP)[2 * r2 + 1] = ng;
+            g0 += ng;
+        }
     }
     __syncthreads();
+    uint32_t cmw = 0u;
+    if (tid < 6 * CTX_GROUPS) {
+        const int gidx = tid / 6;
+        for (int r2 = 0; r2 < R; ++r2) {
+            const int g0 = (int)SMU(SO_GRP)[2 * r2], ng = (int)SMU(SO_GRP)[2 * r2 + 1];
+            if (gidx >= g0 && gidx < g0 + ng) cmw = (uint32_t)r2 | ((uint32_t)(gidx - g0) << 4) | ((uint32_t)ng << 12) | (SMU(SO_LEN)[r2] << 20);
+        }
+    }
     int arow = -1;
     for (int r2 = 0; r2 < R; ++r2)
         if ((int)SMU(SO_OWN)[r2] == rank) arow = r2;
@@ -149,11 +209,7 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
         gemm_regs(acc1, t1, SMU(SO_H1Z), kg, lane, g);
         gemm_regs(acc2, t2, SMU(SO_H2Z), kg, lane, g);
     }
-    __syncthreads();
-    rearm(SMU(SO_H1Z), KS_H, R, tid);
-    rearm(SMU(SO_H2Z), KS_H, R, tid);
-    rearm(SMU(SO_CTX), KS_CTX, R, tid);
-    __syncthreads();
+    __syncthreads();   // (the blocks are re-armed after dense_1 of the first step, which reads the context and h2raw blocks again)
 
     long long* tacc = reinterpret_cast<long long*>(smem3 + SO_TACC);
     long long tprev = 0;
@@ -161,11 +217,15 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
     if (timing) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tprev));
     int s_done = 0;
     bool stopped = false;
+    // prenet dropout bits (always on, Decoder.py:350-351) of the step about to run; those of step s + 1 are drawn while step s
+    // waits for its attention
+    bool keep0 = evalid && keep_bit3(p, p.t0, eb, 0, 16 * rank + eu);
+    bool keep1 = evalid && keep_bit3(p, p.t0, eb, 1, 16 * rank + eu);
 
     for (int s = 0; s < p.S_max; ++s) {
         const int step = p.t0 + s;
         // ---- batch-global stop (Helpers.py:51-52), evaluated STOP_LAG steps late so that clusters never wait for each other; speculative steps are discarded ----
-        // Warp 15 is idle during P1 (warps 0..4 contract the 5 k-steps of the frame): lane i handles the word of cluster i.
+        // Warp 15, lane i handles the word of cluster i.
         if (free_run && warp == 15 && !(p.dbg & 1)) {
             if (s >= STOP_LAG) {
                 cp_async_wait_all();   // words of step s - STOP_LAG, requested one step ago
@@ -179,35 +239,37 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
             }
             if (s >= STOP_LAG - 1 && lane < p.NCL) cp_async_4(SMU(SO_FLAG) + 8 + lane, p.flags + (size_t)(s - (STOP_LAG - 1)) * p.NCL + lane);
         }
-        uint4 aW1P[4];
-        prefetch4(aW1P, sW1P, kg, lane);   // used two exchanges later (L1)
-        // prenet dropout bits of this step (always on, Decoder.py:350-351): computed while the feedback frame is in flight
-        const bool keep0 = evalid && keep_bit3(p, step, eb, 0, 16 * rank + eu);
-        const bool keep1 = evalid && keep_bit3(p, step, eb, 1, 16 * rank + eu);
+        uint4 aW1C[4];
+        prefetch4(aW1C, sW1C, kg, lane);   // used right after dense_1 (context rows of step s-1 -> LSTM-1 gates)
         // ================= P1: prenet dense_1 (Decoder.py:346-351) =================
+        // Free-running steps > 0 (TacoTestHelper.next_inputs, Helpers.py:56: x = last frame of the previous step): the frame
+        // projection of that frame and dense_1 are ONE precomposed contraction of [h2raw ; context] (K = 1024):
+        //   relu(([h2raw;ctx].Wo[:,80:160] + bo[80:160]).Wp1 + bp1) = relu([h2raw;ctx].(Wo[:,80:160].Wp1) + (bo[80:160].Wp1 + bp1))
+        // -- the feedback frame is never materialised, so the step has no projection phase and no frame exchange.
+        const bool folded = free_run && step > 0;
         {
             float acc[2][4] = {};
-            if (warp < KS_X) {
-                if (free_run) {
-                    gemm_smem4(acc, SMU(SO_WP1), SMU(SO_X), KS_X, warp, 16, lane, g);
-                } else {
-                    // TacoTrainingHelper.next_inputs (Helpers.py:121-124, ratio 1.0): x(step) = targets[:, r*step - 1]
-                    const int fidx = step * 2 - 1;
-                    const int gq = lane >> 2, tq = lane & 3;
-                    const uint4 a = *reinterpret_cast<const uint4*>(SMU(SO_WP1) + warp * TILE_W + (lane << 2));
+            if (folded) {
+                gemm_smem4(acc, SMU(SO_WF), SMU(SO_H2R), KS_H, warp, 16, lane, g);
+                gemm_smem4(acc, SMU(SO_WF) + KS_H * TILE_W, SMU(SO_CTX), KS_CTX, warp, 16, lane, g);
+                store_red3(red, acc, warp, lane, 2);
+            } else if (!free_run && warp < KS_X) {
+                // TacoTrainingHelper.next_inputs (Helpers.py:121-124, ratio 1.0): x(step) = targets[:, r*step - 1]
+                const int fidx = step * 2 - 1;
+                const int gq = lane >> 2, tq = lane & 3;
+                const uint4 a = *reinterpret_cast<const uint4*>(SMU(SO_WP1) + warp * TILE_W + (lane << 2));
 #pragma unroll
-                    for (int j = 0; j < 2; ++j) {
-                        uint2 bfrag = make_uint2(0u, 0u);
-                        const int r = 8 * j + gq;
-                        if (fidx >= 0 && fidx < p.F_tgt && r < R) {
-                            const float* src = p.targets + ((size_t)(row0 + r) * p.F_tgt + fidx) * MEL + warp * 16 + 2 * tq;
-                            const float2 v0 = __ldg(reinterpret_cast<const float2*>(src));
-                            const float2 v1 = __ldg(reinterpret_cast<const float2*>(src + 8));
-                            bfrag.x = pack_bf16x2(v0.x, v0.y);
-                            bfrag.y = pack_bf16x2(v1.x, v1.y);
-                        }
-                        mma16816(acc[j], a, bfrag);
+                for (int j = 0; j < 2; ++j) {
+                    uint2 bfrag = make_uint2(0u, 0u);
+                    const int r = 8 * j + gq;
+                    if (fidx >= 0 && fidx < p.F_tgt && r < R) {
+                        const float* src = p.targets + ((size_t)(row0 + r) * p.F_tgt + fidx) * MEL + warp * 16 + 2 * tq;
+                        const float2 v0 = __ldg(reinterpret_cast<const float2*>(src));
+                        const float2 v1 = __ldg(reinterpret_cast<const float2*>(src + 8));
+                        bfrag.x = pack_bf16x2(v0.x, v0.y);
+                        bfrag.y = pack_bf16x2(v1.x, v1.y);
                     }
+                    mma16816(acc[j], a, bfrag);
                 }
                 store_red3(red, acc, warp, lane, 2);
             }
@@ -218,23 +280,42 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
                 break;   // CTA- and cluster-uniform: every CTA reads the same flag words
             }
             if (ept) {
-                float z = bias[128 + eu];
+                float z;
+                if (folded) {
+                    z = bias[160 + eu];
 #pragma unroll
-                for (int k = 0; k < KS_X; ++k) z += red[(k * 16 + eu) * 17 + er];
+                    for (int k = 0; k < 16; ++k) z += red[(k * 16 + eu) * 17 + er];
+                } else {
+                    z = bias[128 + eu];   // <GO> frame of zeros (Helpers.py:131-133): dense_1 = bias
+                    if (!free_run) {
+#pragma unroll
+                        for (int k = 0; k < KS_X; ++k) z += red[(k * 16 + eu) * 17 + er];
+                    }
+                }
                 z = fmaxf(z, 0.f);
                 z = keep0 ? z * p.keep_scale : 0.f;
                 const float zn = __shfl_down_sync(0xffffffffu, z, 1);
                 if (!(eu & 1)) SMU(SO_STG_R)[bword(er, eu >> 1)] = pack_bf16x2(z, zn);
             }
-            if (free_run) rearm(SMU(SO_X), KS_X, R, tid);
-            if (s > 0) {   // buffers whose last readers ran before this phase's barrier
-                rearm(SMU(SO_CTX), KS_CTX, R, tid);
-                rearm(SMU(SO_H1Z), 3 * KS_H, R, tid);   // H1Z, H2R, H2Z are contiguous
-            }
             __syncthreads();
             multicast_block(SMU(SO_STG_R), SMU(SO_P1), rank, R, tid);
             D3_STAMP(1)
         }
+        // ---- shadow of the dense_1 exchange: what step s-1 left behind ----
+        if (s > 0) {
+            // context of step s-1 -> LSTM-1 gates of this step
+            gemm_smem4(acc1, rW1C, SMU(SO_CTX), W1C_RES, kg, 4, lane, g);
+            gemm_regs(acc1, aW1C, SMU(SO_CTX) + W1C_RES * TILE_W, kg, lane, g);
+            D3_STAMP(11)
+            // stop token of step s-1 (Decoder.py:404-410; Helpers.py:36-59)
+            if (rank == STOP_RANK) dec3_stop_token(p, s - 1, row0, R, cid, free_run, red, tid, warp, lane, g);
+            D3_STAMP(12)
+        }
+        uint4 aW1P[4];
+        prefetch4(aW1P, sW1P, kg, lane);   // used two exchanges later (L1)
+        __syncthreads();   // every reader of the context / h2raw blocks of step s-1 is done
+        rearm(SMU(SO_CTX), KS_CTX, R, tid);
+        rearm(SMU(SO_H1Z), 3 * KS_H, R, tid);   // H1Z, H2R, H2Z are contiguous
         // ================= P2: prenet dense_2 =================
         {
             float acc[2][4] = {};
@@ -255,6 +336,11 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
             __syncthreads();
             multicast_block(SMU(SO_STG_R), SMU(SO_P2), rank, R, tid);
             D3_STAMP(3)
+        }
+        // ---- shadow of the dense_2 exchange: first half of the location term of this step (alignments of step s-1) ----
+        if (att && s > 0) {
+            att3_loc_chunk(p, preR, pre_scr, ab, alen, warp, lane, 0, 4);
+            D3_STAMP(13)
         }
         // ================= L1: decoder LSTM layer 1 (Decoder.py:256; Encoder.py:118-142) =================
         {
@@ -295,6 +381,11 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
             multicast_block(SMU(SO_STG_R), SMU(SO_H1R), rank, R, tid);
             multicast_block(SMU(SO_STG_Z), SMU(SO_H1Z), rank, R, tid);
             D3_STAMP(5)
+            // ---- shadow of the h1 exchange: second half of the location term ----
+            if (att && s > 0) {
+                att3_loc_chunk(p, preR, pre_scr, ab, alen, warp, lane, 4, 8);
+                D3_STAMP(14)
+            }
         // ================= L2: decoder LSTM layer 2 =================
             gemm_regs(acc2, aW2H, SMU(SO_H1R), kg, lane, g);
         }
@@ -319,14 +410,18 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
                 if (evalid) {
                     c2s = (1.f - zo) * c_new + zo * c2s;
                     h2s = (1.f - zo) * h_new + zo * h2s;
+                    h2r_last = h_new;
                 } else {
                     h_new = 0.f;
                 }
                 const float hn1 = __shfl_down_sync(0xffffffffu, h_new, 1);
                 const float hz1 = __shfl_down_sync(0xffffffffu, h2s, 1);
                 if (!(eu & 1)) {
-                    SMU(SO_STG_R)[bword(er, eu >> 1)] = pack_bf16x2(h_new, hn1);
+                    const uint32_t hw = pack_bf16x2(h_new, hn1);
+                    SMU(SO_STG_R)[bword(er, eu >> 1)] = hw;
                     SMU(SO_STG_Z)[bword(er, eu >> 1)] = pack_bf16x2(h2s, hz1);
+                    // projection input row of this step, first 256 columns (the frame projection runs after the launch)
+                    if (evalid) p.act_hist[((size_t)s * p.B + eb) * (ACT_W / 2) + 8 * rank + (eu >> 1)] = hw;
                 }
             }
             rearm(SMU(SO_H1R), KS_H, R, tid);
@@ -359,80 +454,28 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
             multicast_block(SMU(SO_STG_Z), SMU(SO_H2Z), rank, R, tid);
             D3_STAMP(7)
         }
-        // ---- h2-dependent halves of the next LSTM-2 gates and of the projection (their operands arrive with the query partials) ----
         uint4 aW2Z[4];
         prefetch4(aW2Z, sW2Z, kg, lane);
-        gemm_regs(acc1, aW1H, SMU(SO_H1Z), kg, lane, g);   // zoned h1 of this step -> LSTM-1 gates of the next step
-        gemm_regs(acc2, aW2Z, SMU(SO_H2Z), kg, lane, g);   // zoned h2 of this step -> LSTM-2 gates of the next step
+        // dropout bits of the next step
+        keep0 = evalid && keep_bit3(p, step + 1, eb, 0, 16 * rank + eu);
+        keep1 = evalid && keep_bit3(p, step + 1, eb, 1, 16 * rank + eu);
+        // ---- zoned states of this step -> gates of the next step (in the shadow of the query exchange) ----
+        gemm_regs(acc1, aW1H, SMU(SO_H1Z), kg, lane, g);
+        gemm_regs(acc2, aW2Z, SMU(SO_H2Z), kg, lane, g);
         D3_STAMP(9)
-        // ================= ATT: location-sensitive attention of cluster row `rank` =================
-        if (att) {
-            att3_step(p, preR, pre_scr, ab, alen, arow, s, tid, warp, lane, g, tacc, tprev, timing);
-            // next step's location term: off the critical path of every CTA but the one that owns the slowest row
-            __syncthreads();
-            att3_next(p, preR, pre_scr, ab, alen, tid, warp, lane);
-            D3_STAMP(14)
-        }
-        uint4 aW1C[4];
-        prefetch4(aW1C, sW1C, kg, lane);   // in flight while the projection waits for the slowest context row
-        D3_STAMP(10)
-        // ================= PROJ: frame + stop projection, outputs, feedback (Decoder.py:273-279; Helpers.py:36-59) =================
-        // projection slot of this rank: slots 0..4 (first frame of the step) on ranks 0..4, slots 5..9 (last frame = the
-        // feedback input) on ranks 11..15, which own no attention row when a cluster has <= 10 rows and therefore start
-        // as soon as the last context row lands; slot 10 (stop token) on rank 10
-        if (slot >= 0) {
-            float accO[2][4] = {};
-            gemm_smem4(accO, SMU(SO_WO), SMU(SO_H2R), KS_H, warp, 16, lane, g);
-            gemm_smem4(accO, SMU(SO_WO) + KS_H * TILE_W, SMU(SO_CTX), KS_CTX, warp, 16, lane, g);
-            __syncthreads();   // attention scratch (aliases red) is no longer read
-            store_red3(red, accO, warp, lane, 2);
-            D3_STAMP(11)
-            __syncthreads();
-            bool fin = false;
-            if (ept) {
-                float y = bias[160 + eu];
-#pragma unroll
-                for (int k = 0; k < 16; ++k) y += red[(k * 16 + eu) * 17 + er];
-                if (slot < 10) {
-                    const int col = 16 * slot + eu;   // 0..159: frame col / 80, mel col % 80
-                    if (evalid) p.frames[((size_t)eb * p.S_cap * 2 + (size_t)s * 2 + (col >= MEL ? 1 : 0)) * MEL + (col >= MEL ? col - MEL : col)] = y;
-                    if (slot >= 5) {
-                        // TacoTestHelper.next_inputs: next input = last frame of this step (Helpers.py:56)
-                        const float x = evalid ? y : 0.f;
-                        if (evalid) p.x_state[(size_t)eb * MEL + col - MEL] = x;
-                        const float xn = __shfl_down_sync(0xffffffffu, x, 1);
-                        if (!(eu & 1)) SMU(SO_STG_R)[bword(er, eu >> 1)] = pack_bf16x2(x, xn);
-                    }
-                } else if (eu < 2) {
-                    const float sg = sigmoidf_(y);
-                    if (evalid) {
-                        p.stop[(size_t)eb * p.S_cap * 2 + (size_t)s * 2 + eu] = p.stop_sigmoid ? sg : y;
-                        fin = sg > 0.5f;   // tf.round(sigmoid) == 1 <=> sigmoid > 0.5 (half-to-even; Helpers.py:40)
-                    }
-                }
-            }
-            if (slot == 10) {
-                if (free_run) {
-                    const int cnt = __syncthreads_count(fin ? 1 : 0);
-                    if (tid == 0) stg_relaxed(reinterpret_cast<uint32_t*>(p.flags) + (size_t)s * p.NCL + cid, (p.stop_at_any ? cnt > 0 : cnt == 2 * R) ? 2u : 1u);
-                }
-            } else if (slot >= 5 && free_run) {
-                __syncthreads();
-                const int dst = tid >> 5, v = tid & 31;
-                const int row = ((v >> 4) << 3) + ((v & 15) >> 1);
-                if (row < R) {
-                    const uint4 val = *reinterpret_cast<const uint4*>(SMU(SO_STG_R) + (v << 2));
-                    st_remote_v4(mapa_rank(smem_addr(SMU(SO_X) + (slot - 5) * TILE_W + (v << 2)), dst), val);
-                }
-            }
-        }
-        D3_STAMP(12)
-        // ---- shadow of the feedback exchange: context-dependent part of the next LSTM-1 gates ----
-        gemm_smem4(acc1, rW1C, SMU(SO_CTX), W1C_RES, kg, 4, lane, g);
-        gemm_regs(acc1, aW1C, SMU(SO_CTX) + W1C_RES * TILE_W, kg, lane, g);
-        D3_STAMP(13)
+        // ================= ATT: location-sensitive attention =================
+        // owner of a cluster row: query, energies, softmax, alignment row -> every CTA; then every CTA: its 48 context columns
+        if (att) att3_owner(p, preR, pre_scr, ab, alen, arow, s, tid, warp, lane, g, tacc, tprev, timing);
+        att3_context_slice(p, cmw, row0, R, rank, s, tid, g);
+        D3_STAMP(17)
         __syncthreads();   // red / staging readers of this step are done before the next step's writers
         s_done = s + 1;
+    }
+    // what the next iteration would have done for the last executed step: its stop token (the context and h2raw blocks are
+    // still in place) and the location term of the following step (saved below for a continuation launch)
+    if (!stopped && s_done > 0) {
+        if (rank == STOP_RANK) dec3_stop_token(p, s_done - 1, row0, R, cid, free_run, red, tid, warp, lane, g);
+        if (att) att3_loc_chunk(p, preR, pre_scr, ab, alen, warp, lane, 0, 8);
     }
 
     if (timing && lane == 0)
@@ -443,6 +486,7 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
         p.h1z[(size_t)eb * DEC + 16 * rank + eu] = h1s;
         p.c2[(size_t)eb * DEC + 16 * rank + eu] = c2s;
         p.h2z[(size_t)eb * DEC + 16 * rank + eu] = h2s;
+        p.h2raw[(size_t)eb * DEC + 16 * rank + eu] = h2r_last;
     }
     if (att) {
         for (int t = tid; t < p.T; t += NT) p.cum[(size_t)ab * p.T + t] = SMF(SO_CPAD)[15 + t];

@@ -95,16 +95,11 @@ cudaError_t taco_launch_f32_to_bf16(const float* in, void* out, size_t n, cudaSt
 #define TACO_DEC3_TMAX 512
 #define TACO_DEC3_RES_WORDS (221 * 128 + 176)
 #define TACO_DEC3_STREAM_TILES 320
-// decoder3: which 16-column slot of the frame/stop projection a cluster rank computes (-1: none).  Slots 0..4 = first
-// frame of the step, 5..9 = last frame (fed back as the next input), 10 = stop token.  Shared by the host packing
-// (api.cu pack_decoder3) and the kernel.
-#ifdef __CUDACC__
-__host__ __device__
-#endif
-inline int dec3_proj_slot(int rank) { return rank < 5 ? rank : (rank == 10 ? 10 : (rank >= 11 ? rank - 6 : -1)); }
+#define TACO_DEC3_ACAP 1472   // shared-memory words for the alignment rows of one cluster: rows per cluster * round_up(T, 4) <= this
 
 struct Dec3Params {
     int B, T, NCL, R;       // NCL clusters; cluster i owns batch rows [i*R, min(B, i*R + R))
+    int TP;                 // round_up(T, 4): row stride of the per-cluster alignment rows (R * TP <= TACO_DEC3_ACAP)
     int S_max, S_cap, t0, mode;
     int stop_at_any, cumulative, smoothing, stop_sigmoid;
     int pre_reg;            // T <= 128: location pre-activations live in registers (else in pre_scratch)
@@ -113,6 +108,8 @@ struct Dec3Params {
     float zoneout, keep_scale;
     const uint32_t* res_blobs;   // [16 ranks][TACO_DEC3_RES_WORDS] A-fragment tiles resident in shared memory + fp32 biases
     const uint4* stream_blobs;   // [16 ranks][320 tiles][32 lanes] A-fragment tiles streamed from L2: W1c [4][48], W1h [4][16], W2z [4][16]
+    const uint4* stop_tiles;     // [64 k-steps][32 lanes] A-fragment tiles of the stop projection (rows 0..1 of the m16 tile)
+    float stop_bias[2];
     const uint32_t *g_hi, *g_lo; // G = conv31 . Wl, B-fragment-major [2 ks][16 nt][32 lanes][2], hi / lo bf16 split
     const float *va, *bconst;    // [128] attention_variable; attention_bias + conv_bias . Wl
     const uint16_t* values;      // bf16 [B][T][768]
@@ -122,19 +119,23 @@ struct Dec3Params {
     float *c1, *h1z, *c2, *h2z;  // [B][256]
     float* ctx_state;            // [B][768]
     float* cum;                  // [B][T]
-    float* x_state;              // [B][80] next decoder input (free-running)
+    float* h2raw;                // [B][256] raw LSTM-2 output of the last step (input of the folded prenet dense_1)
     float* pre_scratch;          // [B][T][128] location pre-activations: working copy (!pre_reg) / state saved between launches
     const float* targets;
     int F_tgt;
     const uint8_t* masks;
     uint64_t seed;
-    float *frames, *stop, *hist;
+    uint32_t* act_hist;          // [S_max][B][512] bf16 pairs: projection input rows [h2raw | context] of every step
+    float *stop, *hist;
     int* steps_out;
     int* flags;       // [S_max][NCL]: 0 not ready, 1 continue, 2 stop (free-running)
     int* abort_flag;
     long long* timing;  // optional [grid][16] per-CTA stage nanoseconds (thread 0), or null
 };
 size_t taco_decoder3_smem_bytes();
+// frames[b][2s + f][m] = act_hist[s][b][:] . Wo[:, 80 f + m] + bo  for s < *steps (FrameProjection, Decoder.py:371-380)
+cudaError_t taco_launch_frame_projection(const uint32_t* act_hist, const uint32_t* wo_t, const float* bo, const int* steps, int S_max, int B,
+                                         int S_cap, float* frames, cudaStream_t stream);
 cudaError_t taco_decoder3_max_clusters(int* out);
 cudaError_t taco_launch_decoder3(const Dec3Params& p, cudaStream_t stream);
 
