@@ -20,22 +20,45 @@ from .AudioProcessing.AudioPreprocess import inv_preemphasis, mel_to_audio_serie
 from .Tacotron_feeder import _get_output_lengths, _prepare_inputs, _prepare_targets
 
 
-def _default_text_to_sequence(text, hparams):
-    """Korean G2P front end of the reference (HangulUtils.hangul_to_sequence; pure Python, unchanged, SURVEY
-    8f row f4) when it is importable; otherwise a deterministic byte-hash tokenisation so that the path can
-    be driven without the text assets (ids in [2, n_symbols), EOS = 1 appended)."""
+class TextFrontEndUnavailable(RuntimeError):
+    """The reference's Korean G2P (Utils/TextProcessing, pure Python) is not importable."""
+
+
+def _import_reference_g2p():
+    from Utils.TextProcessing.HangulUtils import hangul_to_sequence  # the reference's own module, when its root is on sys.path
+    return hangul_to_sequence
+
+
+def _default_text_to_sequence(text, hparams, _import=_import_reference_g2p):
+    """Korean G2P front end of the reference (HangulUtils.hangul_to_sequence:49-65 -> KoG2P; pure Python, used UNCHANGED when the
+    reference's root is on sys.path).  There is no substitute tokeniser on this path: without the front end a text input raises
+    ``TextFrontEndUnavailable`` (pass token-id arrays instead, or opt in to ``synthetic_text_to_sequence`` explicitly with
+    ``Synthesizer(synthetic_tokens=True)`` / ``TACO_SYNTHETIC_TOKENS=1``)."""
     try:
-        from Utils.TextProcessing.HangulUtils import hangul_to_sequence  # the reference's own module, if on sys.path
-        return np.asarray(hangul_to_sequence(dir=hparams.base_dir, hangul_text=text, hangul_type=hparams.hangul_type))
-    except Exception:
-        from ..hparams import num_symbols
-        n = num_symbols(hparams)
-        ids = [2 + (b * 31 + i) % (n - 2) for i, b in enumerate(text.encode("utf-8")) if not chr(b).isspace()]
-        return np.asarray(ids + [1], np.int32)
+        hangul_to_sequence = _import()
+    except ImportError as e:
+        raise TextFrontEndUnavailable(
+            "text input needs the reference's Utils/TextProcessing package on sys.path (%s); pass token-id arrays, or request "
+            "synthetic tokens explicitly (Synthesizer(synthetic_tokens=True) or TACO_SYNTHETIC_TOKENS=1)" % e) from e
+    return np.asarray(hangul_to_sequence(dir=hparams.base_dir, hangul_text=text, hangul_type=hparams.hangul_type))
+
+
+def synthetic_text_to_sequence(text, hparams):
+    """Explicit opt-in stand-in for benchmarking without the text assets: one deterministic id in [2, n_symbols) per non-blank
+    byte, EOS = 1 appended.  NOT a tokeniser of the reference; never selected implicitly."""
+    from ..hparams import num_symbols
+    n = num_symbols(hparams)
+    ids = [2 + (b * 31 + i) % (n - 2) for i, b in enumerate(text.encode("utf-8")) if not chr(b).isspace()]
+    return np.asarray(ids + [1], np.int32)
 
 
 class Synthesizer(object):
-    text_to_sequence = staticmethod(_default_text_to_sequence)
+    def __init__(self, synthetic_tokens=None):
+        if synthetic_tokens is None:
+            synthetic_tokens = os.environ.get("TACO_SYNTHETIC_TOKENS", "0") == "1"
+        self.text_to_sequence = synthetic_text_to_sequence if synthetic_tokens else _default_text_to_sequence
+        if synthetic_tokens:
+            log('synthetic token ids requested explicitly: text is NOT passed through the G2P front end')
 
     def load(self, checkpoint_path, hparams, GTA=False, reference_mel=None, model_name='Tacotron'):
         from .. import runtime, weights
@@ -44,11 +67,14 @@ class Synthesizer(object):
         self.GTA = GTA
         self.hparams = hparams
         self.reference_mel = None if reference_mel is None else np.asarray(reference_mel, np.float32).reshape(1, -1, hparams.num_mels)
-        if checkpoint_path is not None and os.path.isfile(str(checkpoint_path)):
+        if checkpoint_path is not None:
+            # saver.restore of a missing checkpoint fails in the reference (:49-50); so does this
+            if not os.path.isfile(str(checkpoint_path)):
+                raise FileNotFoundError('weight container %r does not exist (pass checkpoint_path=None for random-init weights)' % (checkpoint_path,))
             log('Loading checkpoint: %s' % checkpoint_path)
             runtime.set_weights(weights.load(checkpoint_path))
         else:
-            log('No weight container at %r: random-init weights, seed %d' % (checkpoint_path, hparams.tacotron_random_seed))
+            log('checkpoint_path=None: random-init weights, seed %d' % hparams.tacotron_random_seed)
         runtime.engine(hparams)   # builds the handle, uploads + packs the weights (fails loudly without a GPU / .so)
         return self
 

@@ -329,7 +329,7 @@ __device__ __forceinline__ void att3_context_slice(const Dec3Params& p, uint32_t
 #pragma unroll
             for (int u = 0; u < UB; ++u) {
                 const int t = t0 + u * nslot;
-                v[u] = t < len ? ldg_stream_v4(vp + (size_t)t * (MEM / 8)) : make_uint4(0u, 0u, 0u, 0u);
+                v[u] = (t < len && !(p.dbg & 32)) ? ldg_stream_v4(vp + (size_t)t * (MEM / 8)) : make_uint4(0u, 0u, 0u, 0u);
             }
 #pragma unroll
             for (int u = 0; u < UB; ++u) {

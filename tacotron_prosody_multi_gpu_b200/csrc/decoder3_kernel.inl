@@ -251,7 +251,7 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
             float acc[2][4] = {};
             if (folded) {
                 gemm_smem4(acc, SMU(SO_WF), SMU(SO_H2R), KS_H, warp, 16, lane, g);
-                gemm_smem4(acc, SMU(SO_WF) + KS_H * TILE_W, SMU(SO_CTX), KS_CTX, warp, 16, lane, g);
+                if (!(p.dbg & 64)) gemm_smem4(acc, SMU(SO_WF) + KS_H * TILE_W, SMU(SO_CTX), KS_CTX, warp, 16, lane, g);
                 store_red3(red, acc, warp, lane, 2);
             } else if (!free_run && warp < KS_X) {
                 // TacoTrainingHelper.next_inputs (Helpers.py:121-124, ratio 1.0): x(step) = targets[:, r*step - 1]
@@ -304,11 +304,13 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
         // ---- shadow of the dense_1 exchange: what step s-1 left behind ----
         if (s > 0) {
             // context of step s-1 -> LSTM-1 gates of this step
+            if (!(p.dbg & 2)) {
             gemm_smem4(acc1, rW1C, SMU(SO_CTX), W1C_RES, kg, 4, lane, g);
             gemm_regs(acc1, aW1C, SMU(SO_CTX) + W1C_RES * TILE_W, kg, lane, g);
+            }
             D3_STAMP(11)
             // stop token of step s-1 (Decoder.py:404-410; Helpers.py:36-59)
-            if (rank == STOP_RANK) dec3_stop_token(p, s - 1, row0, R, cid, free_run, red, tid, warp, lane, g);
+            if (rank == STOP_RANK && !(p.dbg & 4)) dec3_stop_token(p, s - 1, row0, R, cid, free_run, red, tid, warp, lane, g);
             D3_STAMP(12)
         }
         uint4 aW1P[4];
@@ -338,7 +340,7 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
             D3_STAMP(3)
         }
         // ---- shadow of the dense_2 exchange: first half of the location term of this step (alignments of step s-1) ----
-        if (att && s > 0) {
+        if (att && s > 0 && !(p.dbg & 8)) {
             att3_loc_chunk(p, preR, pre_scr, ab, alen, warp, lane, 0, 4);
             D3_STAMP(13)
         }
@@ -382,7 +384,7 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
             multicast_block(SMU(SO_STG_Z), SMU(SO_H1Z), rank, R, tid);
             D3_STAMP(5)
             // ---- shadow of the h1 exchange: second half of the location term ----
-            if (att && s > 0) {
+            if (att && s > 0 && !(p.dbg & 8)) {
                 att3_loc_chunk(p, preR, pre_scr, ab, alen, warp, lane, 4, 8);
                 D3_STAMP(14)
             }
@@ -460,8 +462,10 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
         keep0 = evalid && keep_bit3(p, step + 1, eb, 0, 16 * rank + eu);
         keep1 = evalid && keep_bit3(p, step + 1, eb, 1, 16 * rank + eu);
         // ---- zoned states of this step -> gates of the next step (in the shadow of the query exchange) ----
+        if (!(p.dbg & 16)) {
         gemm_regs(acc1, aW1H, SMU(SO_H1Z), kg, lane, g);
         gemm_regs(acc2, aW2Z, SMU(SO_H2Z), kg, lane, g);
+        }
         D3_STAMP(9)
         // ================= ATT: location-sensitive attention =================
         // owner of a cluster row: query, energies, softmax, alignment row -> every CTA; then every CTA: its 48 context columns
