@@ -45,6 +45,18 @@ B_PER_GPU = 64
 S_STEPS = 720
 
 
+def config_dict(S, in_flight, batch=B_PER_GPU, T=111):
+    """The workload description BOTH arms print (the driver compares the two `config` objects)."""
+    return {"workload": "C2 free-running inference, B=%d/GPU, sentences.txt token lengths x4 (T=%d), S=%d decoder steps "
+                        "(max_iters, stop bias -10), r=2, random-init seed 45454" % (batch, T, S),
+            "batch_per_gpu": batch, "T": T, "decoder_steps": S, "frames_counted": "all B*2S frames (no stop fires)",
+            "l2": "512 MB flush write before every step, on the step's stream, inside the timed region",
+            "in_flight": in_flight,
+            "parallelism": "independent batches per GPU, no collective; %d batches in flight per GPU (one engine handle, CUDA "
+                           "stream and host thread each): the encoder / postnet / copies of one batch overlap the persistent "
+                           "decoder kernel of another" % in_flight}
+
+
 def load_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -184,14 +196,163 @@ def run_reference(args):
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / len(times),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "C2 free-running B=64 T=111 S=720 (sentences.txt lengths x4), CPU restatement of the "
-                               "reference (TF 1.9 unavailable)", "sample_decoder_steps": S},
+        "config": config_dict(S_STEPS, args.in_flight),
+        "reference_arm": "CPU restatement of the reference (oracle/; TensorFlow 1.9 is not installable here), %d host threads, "
+                         "%d of %d decoder steps per pass" % (cores, S, S_STEPS),
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
     print(json.dumps(line))
     return 0
+
+
+C5_LENGTHS = [300, 287, 300, 251, 199, 300, 123, 64, 300, 18, 277, 300, 150, 290, 300, 42]
+
+
+def _event_ms(fn, n):
+    import torch
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(n):
+        out = fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / n, out
+
+
+def c3_stop_bias(eng, hp, ids, lens, gw, S_cap, seed, scale=8.0):
+    """C3 stop behaviour with random-init weights: the stop kernel is scaled x8 and the bias is placed, from ONE
+    calibration batch decoded to S_cap steps without stopping (raw logits, bias -30), in the widest gap between the running
+    maximum of the per-step max logit and a later step that exceeds it, in the second half of the sequence.  Every other
+    batch then stops wherever ITS logits first cross that threshold (batch-global stop, Helpers.py:51-52)."""
+    import torch
+    mem = eng.encode(torch.from_numpy(ids), torch.from_numpy(lens), gst_weights=gw)
+    d = eng.decode(mem, torch.from_numpy(lens), max_iters=S_cap, philox_seed=seed, logits_only=True)
+    logit = d["stop"].double().cpu().numpy() + 30.0
+    m = logit.reshape(logit.shape[0], S_cap, -1).max(axis=(0, 2))
+    best = None
+    run = m[: S_cap // 2].max()
+    for s in range(S_cap // 2, S_cap - 1):
+        if m[s] > run and (best is None or m[s] - run > best[0]):
+            best = (m[s] - run, s, -(m[s] + run) / 2.0)
+        run = max(run, m[s])
+    if best is None:
+        return -float(m.max()) + 1e-3, S_cap
+    return float(best[2]), best[1] + 1
+
+
+def extra_configs(args, hp, w, dev, rank, world, dist):
+    """The other configurations of BASELINE.json beside the headline: C2 B=1 step latency, C5 long-form,
+    C3 = 4096 utterances sharded over the ranks with stop-driven lengths (strong scaling, valid frames), fp32-mode C2."""
+    import torch
+    from tacotron_prosody_multi_gpu_b200 import _lib, sharding, synthetic, weights
+    from tacotron_prosody_multi_gpu_b200.engine import EnginePool, TacoEngine
+    local = dev.index
+    out = {}
+    gw = synthetic.gst_random_weights(hp)
+    seed = hp.tacotron_random_seed
+    if rank == 0:
+        # ---- C2, batch 1 (synthesize.py --mode=inference runs one sentence at a time): decoder step latency ----
+        c2 = {}
+        for prec in ("bf16", "fp32"):
+            eng = TacoEngine(hp, w, device=local, precision=prec)
+            for T1, S1 in ((42, 277), (111, 720)):
+                ids, lens = synthetic.token_batch(hp, [T1])
+                a = (torch.from_numpy(ids).to(dev), torch.from_numpy(lens).to(dev))
+                for _ in range(2):
+                    eng.forward(*a, gst_weights=gw, max_iters=S1, philox_seed=seed)
+                ms, o = _event_ms(lambda: eng.forward(*a, gst_weights=gw, max_iters=S1, philox_seed=seed), 3)
+                assert o["steps"] == S1
+                dk = eng.stage_ms(_lib.TACO_STAGE_DECODER_KERNEL)
+                c2["%s_T%d_S%d" % (prec, T1, S1)] = {"decoder_step_us": 1e3 * dk / S1, "utterance_ms": ms, "mel_frames_per_sec": 2 * S1 / (ms * 1e-3)}
+            if prec == "fp32":
+                # ---- the headline batch in fp32 mode (exact-parity kernels), one batch in flight ----
+                ids, lens, _ = workload(hp, rank)
+                a = (torch.from_numpy(ids).to(dev), torch.from_numpy(lens).to(dev))
+                S = args.decoder_steps
+                eng.forward(*a, gst_weights=gw, max_iters=S, philox_seed=seed)
+                ms, o = _event_ms(lambda: eng.forward(*a, gst_weights=gw, max_iters=S, philox_seed=seed), 2)
+                dk = eng.stage_ms(_lib.TACO_STAGE_DECODER_KERNEL)
+                out["c2_b64_fp32"] = {"value": ids.shape[0] * 2 * S / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms, "decoder_step_us": 1e3 * dk / S,
+                                      "dtype": "f32", "in_flight": 1}
+            eng.close()
+        out["c2_b1"] = c2
+        # ---- C5 long form: B=16, T=300, reference encoder on [16, 2000, 80], 1000 free-running steps ----
+        eng = TacoEngine(hp, w, device=local, precision="bf16")
+        ids, lens = synthetic.token_batch(hp, C5_LENGTHS)
+        rm = torch.from_numpy(synthetic.reference_mel(hp, len(C5_LENGTHS), 2000)).to(dev)
+        a = (torch.from_numpy(ids).to(dev), torch.from_numpy(lens).to(dev))
+        for _ in range(2):
+            eng.forward(*a, reference_mel=rm, max_iters=1000, philox_seed=5)
+        ms, o = _event_ms(lambda: eng.forward(*a, reference_mel=rm, max_iters=1000, philox_seed=5), 3)
+        assert o["steps"] == 1000
+        dk = eng.stage_ms(_lib.TACO_STAGE_DECODER_KERNEL)
+        out["c5"] = {"workload": "B=16, T=300, reference mel [16,2000,80] through the reference encoder + GST, S=1000 free-running steps",
+                     "mel_frames_per_sec": 16 * 2000 / (ms * 1e-3), "ms_per_batch": ms, "decoder_step_us": 1e3 * dk / 1000,
+                     "encode_ms": eng.stage_ms(_lib.TACO_STAGE_ENCODE), "postnet_ms": eng.stage_ms(_lib.TACO_STAGE_POSTNET), "dtype": "bf16"}
+        eng.close()
+    # ---- C3: 4096 utterances, 64 batches of 64 sorted by length, LPT-assigned to the ranks, stop-driven S per batch ----
+    n_utt, S_cap = args.c3_utterances, args.decoder_steps
+    ulens = synthetic.utterance_set(hp, n_utt)
+    rng = np.random.Generator(np.random.PCG64(hp.tacotron_data_random_state + 7))
+    seqs = [np.concatenate([rng.integers(2, 66, size=int(n) - 1), [1]]).astype(np.int32) for n in ulens]
+    bias_t = torch.zeros(1, dtype=torch.float64, device=dev)
+    if rank == 0:
+        cal = TacoEngine(hp, weights.scale_stop_projection(w, 8.0, -30.0), device=local, precision="bf16")
+        batches = sharding.plan_batches([len(x) for x in seqs], 64)
+        from tacotron_prosody_multi_gpu_b200.Utils.Tacotron_feeder import _prepare_inputs
+        idx = batches[len(batches) // 2]
+        cids, _ = _prepare_inputs([seqs[i] for i in idx])
+        bias, s_cal = c3_stop_bias(cal, hp, cids.astype(np.int32), np.asarray([len(seqs[i]) for i in idx], np.int32), gw, S_cap, seed)
+        cal.close()
+        bias_t[0] = bias
+    if world > 1:
+        dist.broadcast(bias_t, 0)
+    bias = float(bias_t.item())
+    pool = EnginePool(hp, weights.scale_stop_projection(w, 8.0, bias), device=local, precision="bf16", in_flight=args.in_flight)
+    sharding.synthesize_batches(pool, hp, seqs[:128], 0, 1, 64, gw, S_cap, seed)   # warm-up: two batches on every rank
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.perf_counter()
+    e0.record()
+    res = sharding.synthesize_batches(pool, hp, seqs, rank, world, 64, gw, S_cap, seed)
+    for st in pool.streams:
+        torch.cuda.current_stream().wait_stream(st)
+    e1.record()
+    torch.cuda.synchronize()
+    busy_ms = e0.elapsed_time(e1)
+    wall_ms = 1e3 * (time.perf_counter() - t0)
+    valid = sum(int(v["mel"].shape[0]) for v in res.values())
+    steps_by_batch = {}
+    for v in res.values():
+        steps_by_batch[v["batch"]] = v["steps"]
+    padded = sum(64 * 2 * sN for sN in steps_by_batch.values())
+    stat = torch.tensor([busy_ms, float(valid), float(padded), float(len(res)), float(sum(steps_by_batch.values())), wall_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        allst = [torch.zeros_like(stat) for _ in range(world)]
+        dist.all_gather(allst, stat)
+    else:
+        allst = [stat]
+    pool.close()
+    if rank == 0:
+        a = np.stack([x.cpu().numpy() for x in allst])
+        job_ms = float(a[:, 0].max())
+        steps_list = sorted(steps_by_batch.values())
+        out["c3"] = {"workload": "%d utterances (256 x the sentences.txt lengths, shuffled seed 1324), sorted into batches of 64, LPT-assigned to "
+                                 "%d rank(s), no collective; stop kernel x8, bias %.3f calibrated on one batch: every batch stops at its own "
+                                 "first any-row crossing (cap %d steps); host token arrays in, trimmed host mels out" % (n_utt, world, bias, S_cap),
+                     "scaling": "strong", "utterances": int(a[:, 3].sum()), "valid_mel_frames_per_sec": float(a[:, 1].sum()) / (job_ms * 1e-3),
+                     "padded_mel_frames_per_sec": float(a[:, 2].sum()) / (job_ms * 1e-3), "job_ms": job_ms,
+                     "rank_busy_ms": [float(x) for x in a[:, 0]], "rank_decoder_steps": [int(x) for x in a[:, 4]],
+                     "imbalance_max_over_mean": float(a[:, 0].max() / a[:, 0].mean()),
+                     "valid_frames": int(a[:, 1].sum()), "padded_frames": int(a[:, 2].sum()),
+                     "rank0_batch_steps_min_median_max": [int(steps_list[0]), int(steps_list[len(steps_list) // 2]), int(steps_list[-1])],
+                     "in_flight": args.in_flight}
+    return out
 
 
 def run_b200(args):
@@ -304,6 +465,10 @@ def run_b200(args):
     stage = {"encode_ms": eng.stage_ms(_lib.TACO_STAGE_ENCODE), "decoder_kernel_ms": float(np.mean(dec_ms)),
              "postnet_ms": eng.stage_ms(_lib.TACO_STAGE_POSTNET), "one_batch_in_flight_ms_per_step": seq_ms}
     clocks = sampler.stop() if sampler is not None else None
+    pool.close()
+    del flush
+    torch.cuda.empty_cache()
+    extras = None if args.no_extra else extra_configs(args, hp, w, dev, rank, world, dist)
 
     if rank != 0:
         if world > 1:
@@ -321,14 +486,7 @@ def run_b200(args):
         "dtype": "bf16" if args.precision == "bf16" else "f32", "data": "synthetic",
         "precision": ("bf16 operands + fp32 accumulation in every contraction (tcgen05 in the postnet, mma.sync in the decoder step); "
                       "attention values streamed as bf16; recurrent state, softmax, location term and all outputs fp32") if args.precision == "bf16" else "fp32 everywhere",
-        "config": {"workload": "C2 free-running inference, B=64/GPU, sentences.txt token lengths x4 (T=111), "
-                               "S=%d decoder steps (max_iters, stop bias -10), r=2, random-init seed 45454" % S,
-                   "batch_per_gpu": B, "T": T, "decoder_steps": S, "frames_counted": "all B*2S frames (no stop fires)",
-                   "l2": "512 MB flush write before every step, on the step's stream, inside the timed region",
-                   "in_flight": args.in_flight,
-                   "parallelism": "independent batches per GPU, no collective; %d batches in flight per GPU (one engine handle, CUDA "
-                                  "stream and host thread each): the encoder / postnet / copies of one batch overlap the persistent "
-                                  "decoder kernel of another" % args.in_flight},
+        "config": config_dict(S, args.in_flight, B, T),
         "decoder_step_us": 1e6 * dec_s / S,
         "stages_ms": stage,
         "roofline": {"bound": "hbm", "kernel": "decoder3_kernel (cluster persistent decoder)" if args.precision == "bf16" else "decoder_persistent_kernel", "achieved": achieved, "peak": peak,
@@ -340,6 +498,8 @@ def run_b200(args):
         "gpu_launches": int(launches),
         "clocks": clocks,
     }
+    if extras is not None:
+        line["configs"] = extras
     if world == 1 and not args.no_cpu_baseline:
         cores = os.cpu_count() or 1
         Sc = args.cpu_steps
@@ -364,12 +524,22 @@ def main():
     ap.add_argument("--ref-steps", type=int, default=0, help="--impl reference: decoder steps per pass (0 = auto)")
     ap.add_argument("--ref-budget-s", type=float, default=240.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extra", action="store_true", help="skip the `configs` record (C2 B=1, C3, C5, fp32 mode)")
+    ap.add_argument("--c3-utterances", type=int, default=4096)
+    ap.add_argument("--workload", default="c2", choices=["c2", "c4"],
+                    help="c2: the headline (free-running synthesis, B=64/GPU); c4: the data-parallel training step (scripts/bench_train.py)")
     ap.add_argument("--in-flight", type=int, default=2, help="independent batches in flight per GPU (engine.EnginePool)")
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"],
                     help="bf16: tensor-core (tcgen05) contractions with bf16 operands, fp32 accumulate; fp32: SIMT everywhere")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "b200":
         args.warmup = 3
+    if args.workload == "c4":
+        sys.argv = [os.path.join(ROOT, "scripts", "bench_train.py"), "--steps", str(args.steps), "--warmup", str(args.warmup)] + (
+            ["--impl", "reference"] if args.impl == "reference" else [])
+        sys.path.insert(0, os.path.join(ROOT, "scripts"))
+        import bench_train
+        return bench_train.main()
     if args.impl == "reference":
         return run_reference(args)
     return run_b200(args)

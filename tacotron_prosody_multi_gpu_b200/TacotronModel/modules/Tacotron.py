@@ -157,9 +157,14 @@ class Tacotron(object):
         o = tr.ops
         batch_size = self.tower_inputs[0].shape[0]
         stop_np = np.asarray(stop_token_targets.cpu() if hasattr(stop_token_targets, "cpu") else stop_token_targets, np.float32)
+        if split_infos.shape[1] > 2 and split_infos[:, 2].any() and not np.array_equal(split_infos[:, 2], split_infos[:, 1]):
+            # the stop loss pairs one target with every mel frame (Tacotron.py:394-396): the reference's feeder pads len(mel) - 1
+            # stop tokens to round_up(max + 1, r), which equals the mel width; anything else would mis-index the labels
+            raise ValueError("split_infos: stop-token width %s != mel width %s" % (split_infos[:, 2].tolist(), split_infos[:, 1].tolist()))
         p_stop = split_func(stop_np, split_infos[:, 2] if split_infos.shape[1] > 2 and split_infos[:, 2].any() else split_infos[:, 1])
         self.tower_stop_token_targets = [np.ascontiguousarray(p_stop[i].reshape(batch_size, -1)) for i in range(G)]
         seed = (hp.tacotron_random_seed + 7919 * int(global_step or 0)) if philox_seed is None else philox_seed
+        seed += 104729 * G * tr.rank          # every tower of every rank draws its own dropout / zoneout masks
         self._trainer, self._tapes, self._tower_losses = tr, [], []
         self.tower_decoder_output, self.tower_alignments = [], []
         self.tower_stop_token_prediction, self.tower_mel_outputs = [], []
@@ -211,8 +216,13 @@ class Tacotron(object):
 
         def optimize():
             acc = None
-            for tape in self._tapes:
-                st.backward(tape)
+            for k, tape in enumerate(self._tapes):
+                # the early exchange half may only start when the LAST tower's gradients are in the buffer
+                hook, st.on_tail_ready = st.on_tail_ready, (st.on_tail_ready if len(self._tapes) == 1 else None)
+                try:
+                    st.backward(tape)
+                finally:
+                    st.on_tail_ready = hook
                 if len(self._tapes) > 1:
                     if acc is None:
                         acc = st.store.g.clone()
@@ -221,7 +231,7 @@ class Tacotron(object):
             if acc is not None:
                 st.store.g.copy_(acc)
             towers = len(self._tapes) * tr.world
-            st.apply(step_no, world=towers, all_reduce=tr._all_reduce if tr.world > 1 else None)
+            st.apply(step_no, world=towers, all_reduce=tr._all_reduce if tr.world > 1 else None, ranks=tr.world)
             self._tapes = []
             return step_no + 1
 

@@ -773,6 +773,12 @@ int decode_v3(TacoHandle* h, int mode, const float* memory, const int32_t* lens,
         CK(cudaMemsetAsync(timing, 0, (size_t)TACO_DEC3_CLUSTER * TACO_DEC3_MAX_CLUSTERS * 24 * sizeof(long long), st));
         p.timing = timing;
     }
+    if (getenv("TACO_DEC3_TRACE")) {
+        WS(trace, long long, "dec3_trace", (size_t)TACO_DEC3_CLUSTER * TACO_DEC3_MAX_CLUSTERS * 128)
+        CK(cudaMemsetAsync(trace, 0, (size_t)TACO_DEC3_CLUSTER * TACO_DEC3_MAX_CLUSTERS * 128 * sizeof(long long), st));
+        p.trace = trace;
+        p.trace_step = atoi(getenv("TACO_DEC3_TRACE"));
+    }
     CK(cudaEventRecord(h->ev[TACO_STAGE_DECODER_KERNEL][0], st));
     CK(taco_launch_decoder3(p, st));
     // frame projection of all executed steps (hoisted out of the recurrence: nothing in the loop reads the frames)

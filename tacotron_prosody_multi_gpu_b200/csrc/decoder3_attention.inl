@@ -158,8 +158,15 @@ __device__ __forceinline__ int ctx_groups_of(int len, int total) { return (CTX_B
 // q from the 16 partials, energies, masked softmax, cumulate, alignment history, and the multicast of the alignment row to
 // every CTA of the cluster (each of which reduces a 48-column slice of the context, att3_context_slice).
 __device__ __forceinline__ void att3_owner(const Dec3Params& p, float (&preR)[8][4], float* pre_scr, int b, int len, int arow, int s,
-                                           int tid, int warp, int lane, Guard3& g, long long* tacc, long long& tprev, bool timing) {
+                                           int tid, int warp, int lane, Guard3& g, long long* tacc, long long& tprev, bool timing, bool tracing) {
     float* scr = SMF(SO_RED);
+#define A3_TR(i)                                                        \
+    if (tracing && tid == 0) {                                          \
+        long long gt_;                                                  \
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt_));         \
+        p.trace[((size_t)blockIdx.x * 64 + (i)) * 2] = clock64();       \
+        p.trace[((size_t)blockIdx.x * 64 + (i)) * 2 + 1] = gt_;         \
+    }
 #define A3_STAMP(i)                                                     \
     if (timing) { /* whole warp 0, uniform: a divergent stamp would push the following collectives onto their slow path */ \
         long long now_;                                                 \
@@ -184,8 +191,10 @@ __device__ __forceinline__ void att3_owner(const Dec3Params& p, float (&preR)[8]
         q += __shfl_xor_sync(0xffffffffu, q, 2);
         if (part == 0) SMF(SO_QS)[d] = g.dead ? 0.f : q;
     }
+    A3_TR(34)
     __syncthreads();
     A3_STAMP(8)
+    A3_TR(35)
     for (int i = tid; i < CS * ATT; i += NT) SMU(SO_QRECV)[i] = SENT;  // re-arm for the next step
     // E2: energies e[t] = sum_d v_a[d] tanh(pre[t][d] + q[d])   (Attention.py:401)
     if (p.pre_reg) {
@@ -231,6 +240,7 @@ __device__ __forceinline__ void att3_owner(const Dec3Params& p, float (&preR)[8]
     }
     __syncthreads();
     A3_STAMP(16)
+    A3_TR(36)
     // E3: masked softmax over t < len (exact zeros beyond: -inf mask), Attention.py:203-206
     if (warp == 0) {
         if (p.pre_reg) {
@@ -282,6 +292,7 @@ __device__ __forceinline__ void att3_owner(const Dec3Params& p, float (&preR)[8]
     }
     __syncthreads();
     A3_STAMP(10)
+    A3_TR(37)
     // multicast the alignment row to every CTA of the cluster (positions < len; the context slices never read beyond)
     {
         const int nv = (len + 3) >> 2;
@@ -293,6 +304,7 @@ __device__ __forceinline__ void att3_owner(const Dec3Params& p, float (&preR)[8]
             st_remote_v4(mapa_rank(smem_addr(SMU(SO_AALL) + arow * TP + (v << 2)), dst), val);
         }
     }
+    A3_TR(38)
     // E4: cumulate + alignment history
     for (int t = tid; t < p.T; t += NT) {
         const float a = t < len ? SMF(SO_ES)[t] : 0.f;
@@ -303,6 +315,7 @@ __device__ __forceinline__ void att3_owner(const Dec3Params& p, float (&preR)[8]
     // pair arrays of the new alignments for the location term of the next step (att3_loc_chunk, in the shadow of later exchanges)
     att3_build_pairs(p.T, tid, p.cumulative != 0, len);
     A3_STAMP(15)
+    A3_TR(39)
 }
 
 // Context of ALL rows of the cluster, columns [48 rank, 48 rank + 48): ctx[r][c] = sum_t a[r][t] values[r][t][c]
@@ -310,10 +323,23 @@ __device__ __forceinline__ void att3_owner(const Dec3Params& p, float (&preR)[8]
 // the owners multicast, then multicasts its three k-step blocks (B-fragment order) to the whole cluster: the reduction is spread
 // over 16 SMs' L2 ports instead of one per row, and nobody waits for the CTA that owns the longest row.
 __device__ __forceinline__ void att3_context_slice(const Dec3Params& p, uint32_t cmw, int row0, int R, int rank, int s, int tid,
-                                                   Guard3& g) {
+                                                   Guard3& g, bool tracing) {
     float* scr = SMF(SO_RED);
     const int TP = p.TP;
     __syncthreads();   // the K-split partials / query slices of this step (same scratch) have been read
+    A3_TR(40)
+    if (tracing) {   // trace mode only: all alignment rows present before the loads start
+        for (int r2 = 0; r2 < R; ++r2) {
+            const int l2 = (int)SMU(SO_LEN)[r2];
+            for (int t = tid; t < l2; t += NT) {
+                int spins = 0;
+                while (*reinterpret_cast<const volatile uint32_t*>(SMU(SO_AALL) + r2 * TP + t) == SENT && !spin_check3(g, spins)) {
+                }
+            }
+        }
+        __syncthreads();
+    }
+    A3_TR(41)
     const int nslot = (cmw >> 12) & 255;
     if (nslot) {
         const int crow = cmw & 15, cslot = (cmw >> 4) & 255, len = cmw >> 20;
@@ -359,7 +385,9 @@ __device__ __forceinline__ void att3_context_slice(const Dec3Params& p, uint32_t
         dst[0] = make_float4(c[0], c[1], c[2], c[3]);
         dst[1] = make_float4(c[4], c[5], c[6], c[7]);
     }
+    A3_TR(42)
     g.dead = __syncthreads_or(g.dead ? 1 : 0) != 0;
+    A3_TR(43)
     // every alignment row has been consumed: re-arm (valid rows only; rows >= R are never written)
     for (int i = tid; i < (R * TP) >> 2; i += NT) reinterpret_cast<uint4*>(SMU(SO_AALL))[i] = make_uint4(SENT, SENT, SENT, SENT);
     if (tid < R * 24) {
@@ -378,7 +406,9 @@ __device__ __forceinline__ void att3_context_slice(const Dec3Params& p, uint32_t
         *reinterpret_cast<float2*>(p.ctx_state + (size_t)b * MEM + 48 * rank + 2 * cp) = make_float2(x0, x1);
         p.act_hist[((size_t)s * p.B + b) * 512 + 128 + 24 * rank + cp] = cw;   // projection input row of this step, columns 256..1023
     }
+    A3_TR(44)
     __syncthreads();
+    A3_TR(45)
     // multicast this CTA's three k-step blocks (3 rank .. 3 rank + 2) to every CTA of the cluster
     {
         const int dst = tid >> 5, v = tid & 31;
@@ -391,6 +421,7 @@ __device__ __forceinline__ void att3_context_slice(const Dec3Params& p, uint32_t
             }
         }
     }
+    A3_TR(46)
 }
 
 // Location pre-activations of the NEXT step from the new alignments (pair arrays built by att3_owner), tiles [i0, i1) of the

@@ -15,6 +15,22 @@ constexpr int ACT_W = 1024;     // projection input row: [h2raw 256 | context 76
         tprev = now_;                                                   \
     }
 
+// one-step trace (TACO_DEC3_TRACE=<step>): warp 0 lane 0 stamps (clock64, globaltimer) at point i of step trace_step
+#define D3_TR(i)                                                        \
+    if (tracing && tid == 0) {                                          \
+        long long gt_;                                                  \
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt_));         \
+        p.trace[((size_t)blockIdx.x * 64 + (i)) * 2] = clock64();       \
+        p.trace[((size_t)blockIdx.x * 64 + (i)) * 2 + 1] = gt_;         \
+    }
+// trace mode only: wait (all threads) until every valid row of the blocks [buf, buf + KS blocks) has arrived, so that the
+// stamp that follows separates "waiting for the exchange" from "computing"
+#define D3_PREPOLL(buf, KS)                                             \
+    if (tracing) {                                                      \
+        prepoll3(buf, KS, R, tid, g);                                   \
+        __syncthreads();                                                \
+    }
+
 // Stop-token projection of launch step s_idx for the rows of this cluster (StopProjection, Decoder.py:404-410; the batch-global
 // decision of TacoTestHelper.next_inputs, Helpers.py:36-59): [h2raw ; context] . Ws[1024 x 2] as 64 k-steps of one m16 tile whose
 // rows 0..1 are the two stop units.  Runs on ONE rank per cluster, off the critical path; its tiles stream from L2.
@@ -50,6 +66,20 @@ __device__ __noinline__ void dec3_stop_token(const Dec3Params& p, int s_idx, int
     const int cnt = __syncthreads_count(fin ? 1 : 0);
     if (free_run && tid == 0)
         stg_relaxed(reinterpret_cast<uint32_t*>(p.flags) + (size_t)s_idx * p.NCL + cid, (p.stop_at_any ? cnt > 0 : cnt == 2 * R) ? 2u : 1u);
+}
+
+__device__ __noinline__ void prepoll3(const uint32_t* buf, int KS, int R, int tid, Guard3& g) {
+    for (int i = tid; i < KS * (TILE_W / 4); i += NT) {
+        const int v = i & 31;
+        const int row = ((v >> 4) << 3) + ((v & 15) >> 1);
+        if (row >= R) continue;
+        int spins = 0;
+        while (true) {
+            const uint4 w = lds_poll_v4(buf + 4 * i);
+            if (!(w.x == SENT || w.y == SENT || w.z == SENT || w.w == SENT)) break;
+            if (spin_check3(g, spins)) break;
+        }
+    }
 }
 
 // fill one activation buffer from a row-major fp32 state array [B][width] (rows row0 .. row0+R-1 of this cluster)
@@ -224,6 +254,8 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
 
     for (int s = 0; s < p.S_max; ++s) {
         const int step = p.t0 + s;
+        const bool tracing = p.trace != nullptr && s == p.trace_step;
+        D3_TR(0)
         // ---- batch-global stop (Helpers.py:51-52), evaluated STOP_LAG steps late so that clusters never wait for each other; speculative steps are discarded ----
         // Warp 15, lane i handles the word of cluster i.
         if (free_run && warp == 15 && !(p.dbg & 1)) {
@@ -250,6 +282,9 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
         {
             float acc[2][4] = {};
             if (folded) {
+                D3_PREPOLL(SMU(SO_H2R), KS_H)
+                D3_PREPOLL(SMU(SO_CTX), KS_CTX)
+                D3_TR(1)
                 gemm_smem4(acc, SMU(SO_WF), SMU(SO_H2R), KS_H, warp, 16, lane, g);
                 if (!(p.dbg & 64)) gemm_smem4(acc, SMU(SO_WF) + KS_H * TILE_W, SMU(SO_CTX), KS_CTX, warp, 16, lane, g);
                 store_red3(red, acc, warp, lane, 2);
@@ -274,7 +309,9 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
                 store_red3(red, acc, warp, lane, 2);
             }
             D3_STAMP(0)
+            D3_TR(2)
             __syncthreads();
+            D3_TR(3)
             if (free_run && s >= STOP_LAG && SMU(SO_FLAG)[0] == 2u) {
                 stopped = true;
                 break;   // CTA- and cluster-uniform: every CTA reads the same flag words
@@ -297,9 +334,12 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
                 const float zn = __shfl_down_sync(0xffffffffu, z, 1);
                 if (!(eu & 1)) SMU(SO_STG_R)[bword(er, eu >> 1)] = pack_bf16x2(z, zn);
             }
+            D3_TR(4)
             __syncthreads();
+            D3_TR(5)
             multicast_block(SMU(SO_STG_R), SMU(SO_P1), rank, R, tid);
             D3_STAMP(1)
+            D3_TR(6)
         }
         // ---- shadow of the dense_1 exchange: what step s-1 left behind ----
         if (s > 0) {
@@ -309,22 +349,30 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
             gemm_regs(acc1, aW1C, SMU(SO_CTX) + W1C_RES * TILE_W, kg, lane, g);
             }
             D3_STAMP(11)
+            D3_TR(7)
             // stop token of step s-1 (Decoder.py:404-410; Helpers.py:36-59)
             if (rank == STOP_RANK && !(p.dbg & 4)) dec3_stop_token(p, s - 1, row0, R, cid, free_run, red, tid, warp, lane, g);
+            if (rank == STOP_RANK && (p.dbg & 4) && free_run && tid == 0) stg_relaxed(reinterpret_cast<uint32_t*>(p.flags) + (size_t)(s - 1) * p.NCL + cid, 1u);
             D3_STAMP(12)
+            D3_TR(8)
         }
         uint4 aW1P[4];
         prefetch4(aW1P, sW1P, kg, lane);   // used two exchanges later (L1)
         __syncthreads();   // every reader of the context / h2raw blocks of step s-1 is done
         rearm(SMU(SO_CTX), KS_CTX, R, tid);
         rearm(SMU(SO_H1Z), 3 * KS_H, R, tid);   // H1Z, H2R, H2Z are contiguous
+        D3_TR(9)
+        D3_PREPOLL(SMU(SO_P1), KS_H)
+        D3_TR(10)
         // ================= P2: prenet dense_2 =================
         {
             float acc[2][4] = {};
             gemm_smem4(acc, SMU(SO_WP2), SMU(SO_P1), KS_H, warp, 16, lane, g);
             store_red3(red, acc, warp, lane, 2);
             D3_STAMP(2)
+            D3_TR(11)
             __syncthreads();
+            D3_TR(12)
             if (ept) {
                 float z = bias[144 + eu];
 #pragma unroll
@@ -335,15 +383,21 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
                 if (!(eu & 1)) SMU(SO_STG_R)[bword(er, eu >> 1)] = pack_bf16x2(z, zn);
             }
             rearm(SMU(SO_P1), KS_H, R, tid);
+            D3_TR(13)
             __syncthreads();
+            D3_TR(14)
             multicast_block(SMU(SO_STG_R), SMU(SO_P2), rank, R, tid);
             D3_STAMP(3)
+            D3_TR(15)
         }
         // ---- shadow of the dense_2 exchange: first half of the location term of this step (alignments of step s-1) ----
         if (att && s > 0 && !(p.dbg & 8)) {
             att3_loc_chunk(p, preR, pre_scr, ab, alen, warp, lane, 0, 4);
             D3_STAMP(13)
         }
+        D3_TR(16)
+        D3_PREPOLL(SMU(SO_P2), KS_H)
+        D3_TR(17)
         // ================= L1: decoder LSTM layer 1 (Decoder.py:256; Encoder.py:118-142) =================
         {
             gemm_regs(acc1, aW1P, SMU(SO_P2), kg, lane, g);
@@ -353,7 +407,9 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
 #pragma unroll
             for (int j = 0; j < 2; ++j) acc1[j][0] = acc1[j][1] = acc1[j][2] = acc1[j][3] = 0.f;
             D3_STAMP(4)
+            D3_TR(18)
             __syncthreads();
+            D3_TR(19)
             if (ept) {
                 float z[4];
 #pragma unroll
@@ -379,15 +435,21 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
                 }
             }
             rearm(SMU(SO_P2), KS_H, R, tid);
+            D3_TR(20)
             __syncthreads();
+            D3_TR(21)
             multicast_block(SMU(SO_STG_R), SMU(SO_H1R), rank, R, tid);
             multicast_block(SMU(SO_STG_Z), SMU(SO_H1Z), rank, R, tid);
             D3_STAMP(5)
+            D3_TR(22)
             // ---- shadow of the h1 exchange: second half of the location term ----
             if (att && s > 0 && !(p.dbg & 8)) {
                 att3_loc_chunk(p, preR, pre_scr, ab, alen, warp, lane, 4, 8);
                 D3_STAMP(14)
             }
+            D3_TR(23)
+            D3_PREPOLL(SMU(SO_H1R), KS_H)
+            D3_TR(24)
         // ================= L2: decoder LSTM layer 2 =================
             gemm_regs(acc2, aW2H, SMU(SO_H1R), kg, lane, g);
         }
@@ -398,7 +460,9 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
 #pragma unroll
             for (int j = 0; j < 2; ++j) acc2[j][0] = acc2[j][1] = acc2[j][2] = acc2[j][3] = 0.f;
             D3_STAMP(6)
+            D3_TR(25)
             __syncthreads();
+            D3_TR(26)
             if (ept) {
                 float z[4];
 #pragma unroll
@@ -427,7 +491,9 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
                 }
             }
             rearm(SMU(SO_H1R), KS_H, R, tid);
+            D3_TR(27)
             __syncthreads();
+            D3_TR(28)
             // K-slice of the query projection: qpart[row][d] = sum_{u in my 16 units} h2raw[row][u] Wq[u][d]
             if (warp < 8) {
                 float accq[2][4] = {};
@@ -444,7 +510,9 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
                     q0[ATT + 8] = accq[j][3];
                 }
             }
+            D3_TR(29)
             __syncthreads();
+            D3_TR(30)
             {
                 const int row = tid >> 5, v = tid & 31;
                 if (row < R) {
@@ -455,6 +523,7 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
             multicast_block(SMU(SO_STG_R), SMU(SO_H2R), rank, R, tid);
             multicast_block(SMU(SO_STG_Z), SMU(SO_H2Z), rank, R, tid);
             D3_STAMP(7)
+            D3_TR(31)
         }
         uint4 aW2Z[4];
         prefetch4(aW2Z, sW2Z, kg, lane);
@@ -462,17 +531,22 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
         keep0 = evalid && keep_bit3(p, step + 1, eb, 0, 16 * rank + eu);
         keep1 = evalid && keep_bit3(p, step + 1, eb, 1, 16 * rank + eu);
         // ---- zoned states of this step -> gates of the next step (in the shadow of the query exchange) ----
+        D3_PREPOLL(SMU(SO_H1Z), KS_H)
+        D3_PREPOLL(SMU(SO_H2Z), KS_H)
+        D3_TR(32)
         if (!(p.dbg & 16)) {
         gemm_regs(acc1, aW1H, SMU(SO_H1Z), kg, lane, g);
         gemm_regs(acc2, aW2Z, SMU(SO_H2Z), kg, lane, g);
         }
         D3_STAMP(9)
+        D3_TR(33)
         // ================= ATT: location-sensitive attention =================
         // owner of a cluster row: query, energies, softmax, alignment row -> every CTA; then every CTA: its 48 context columns
-        if (att) att3_owner(p, preR, pre_scr, ab, alen, arow, s, tid, warp, lane, g, tacc, tprev, timing);
-        att3_context_slice(p, cmw, row0, R, rank, s, tid, g);
+        if (att) att3_owner(p, preR, pre_scr, ab, alen, arow, s, tid, warp, lane, g, tacc, tprev, timing, tracing);
+        att3_context_slice(p, cmw, row0, R, rank, s, tid, g, tracing);
         D3_STAMP(17)
-        __syncthreads();   // red / staging readers of this step are done before the next step's writers
+        __syncthreads();
+        D3_TR(47)   // red / staging readers of this step are done before the next step's writers
         s_done = s + 1;
     }
     // what the next iteration would have done for the last executed step: its stop token (the context and h2raw blocks are

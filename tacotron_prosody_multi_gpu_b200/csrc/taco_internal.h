@@ -131,6 +131,8 @@ struct Dec3Params {
     int* flags;       // [S_max][NCL]: 0 not ready, 1 continue, 2 stop (free-running)
     int* abort_flag;
     long long* timing;  // optional [grid][16] per-CTA stage nanoseconds (thread 0), or null
+    long long* trace;   // optional [grid][64][2] (clock64, globaltimer) stamps of step trace_step (TACO_DEC3_TRACE), or null
+    int trace_step;
 };
 size_t taco_decoder3_smem_bytes();
 // frames[b][2s + f][m] = act_hist[s][b][:] . Wo[:, 80 f + m] + bo  for s < *steps (FrameProjection, Decoder.py:371-380)

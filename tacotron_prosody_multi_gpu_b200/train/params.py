@@ -14,6 +14,10 @@ import numpy as np
 NOT_TRAINABLE = ("moving_mean", "moving_variance")
 # Tacotron.py:419-422: variables whose NAME contains one of these are not L2-regularised
 REG_EXCLUDE = ("bias", "Bias", "_projection", "inputs_embedding", "RNN", "LSTM")
+# variable scopes whose gradients are complete when the decoder BPTT ends (train/step.py backward): the early exchange half
+TAIL_SCOPES = ("decoder/", "postnet_convolutions/", "postnet_projection/")
+# Tacotron.py:478-480: with tacotron_fine_tuning only variables NOT matching these are updated
+FINE_TUNE_FROZEN = ("inputs_embedding", "encoder_")
 
 
 def is_trainable(name):
@@ -44,15 +48,27 @@ class ParamStore(object):
                 regw[o:o + sz] = reg_weight
         self.p = ops.to_device(flat)
         self.regw = ops.to_device(regw)
-        self.g = ops.zeros(off)
         self.m = ops.zeros(off)
         self.v = ops.zeros(off)
         self.P = self._views(self.p)
-        self.G = self._views(self.g)
-        # BN moving statistics: one flat buffer too (averaged across ranks by the data-parallel trainer)
+        # ONE exchange bucket per step: [BN moving statistics | gradients].  The statistics sit in front so that
+        # the bucket splits into two contiguous halves by the time their contents are final in backward():
+        #   late  = bucket[: ns + tail_start]  statistics + encoder / style gradients (final at the end of backward)
+        #   early = bucket[ns + tail_start :]  decoder + postnet gradients (final once the decoder BPTT is done)
         snames = [name for name in weights if not is_trainable(name)]
         sflat = np.concatenate([np.asarray(weights[n], np.float32).reshape(-1) for n in snames]) if snames else np.zeros(0, np.float32)
-        self.s = ops.to_device(sflat)
+        self.ns = int(sflat.size)
+        self.bucket = ops.zeros(self.ns + off)
+        self.s = self.bucket[:self.ns]
+        if self.ns:
+            self.s.copy_(ops.to_device(sflat))
+        self.g = self.bucket[self.ns:]
+        self.G = self._views(self.g)
+        names = list(self.layout.keys())
+        k = len(names)
+        while k > 0 and names[k - 1].startswith(TAIL_SCOPES):
+            k -= 1
+        self.tail_start = self.layout[names[k]][0] if k < len(names) else off   # first gradient of the early half
         self.stats = OrderedDict()
         off = 0
         for name in snames:
@@ -66,6 +82,40 @@ class ParamStore(object):
             sz = int(np.prod(shp)) if len(shp) else 1
             out[name] = flat[o:o + sz].view(*shp) if len(shp) else flat[o:o + 1]
         return out
+
+    # ---- resumable state (tf.train.Saver keeps the Adam slots and global_step in the checkpoint, train.py:60) ----
+    def save_state(self, path, global_step):
+        """Variables, BN moving statistics, Adam moments and the update count in one .npz; ``load_state`` resumes the
+        schedule (lr decay, Adam bias correction) exactly where it stopped."""
+        out = {k.replace("/", "|"): v for k, v in self.export().items()}
+        out["__adam_m__"] = self.m.detach().cpu().numpy()
+        out["__adam_v__"] = self.v.detach().cpu().numpy()
+        out["__global_step__"] = np.asarray(int(global_step), np.int64)
+        np.savez(path, **out)
+
+    def load_state(self, path):
+        """-> global_step.  Raises if the container does not hold exactly this store's variables."""
+        z = np.load(path)
+        names = {k.replace("|", "/"): k for k in z.files if not k.startswith("__")}
+        missing = [n for n in list(self.layout) + list(self.stats) if n not in names]
+        if missing:
+            raise KeyError("training state %r lacks %d variables, e.g. %s" % (path, len(missing), missing[:3]))
+        flat = np.empty(self.n, np.float32)
+        for name, (o, shp) in self.layout.items():
+            a = np.asarray(z[names[name]], np.float32)
+            if tuple(a.shape) != tuple(shp):
+                raise ValueError("training state %r: %s has shape %s, expected %s" % (path, name, a.shape, shp))
+            flat[o:o + a.size] = a.reshape(-1)
+        self.p.copy_(self.ops.to_device(flat))
+        for name, t in self.stats.items():
+            t.copy_(self.ops.to_device(np.asarray(z[names[name]], np.float32).reshape(-1)))
+        if "__adam_m__" in z.files:
+            self.m.copy_(self.ops.to_device(np.asarray(z["__adam_m__"], np.float32)))
+            self.v.copy_(self.ops.to_device(np.asarray(z["__adam_v__"], np.float32)))
+            return int(z["__global_step__"])
+        self.m.zero_()
+        self.v.zero_()
+        return 0
 
     def export(self):
         """name -> float32 ndarray (the weight-container format of weights.py), moving statistics included."""

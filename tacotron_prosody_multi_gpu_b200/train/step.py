@@ -41,7 +41,33 @@ class TrainStep(object):
         reg = hp.tacotron_reg_weight
         if hp.tacotron_scale_regularization:
             reg *= 1.0 / (2 * hp.max_abs_value) if hp.symmetric_mels else 1.0 / hp.max_abs_value
+        # hparams that change the reference's TRAINING graph and are not built here fail loudly (the inference path raises
+        # FusedStageError for the same settings) instead of silently training a different model
+        if str(getattr(hp, "tacotron_teacher_forcing_mode", "constant")) != "constant":
+            raise NotImplementedError("tacotron_teacher_forcing_mode=%r (scheduled teacher forcing, Helpers.py:100-124) is not built: "
+                                      "only 'constant' with ratio 1.0" % hp.tacotron_teacher_forcing_mode)
+        if float(getattr(hp, "tacotron_teacher_forcing_ratio", 1.0)) != 1.0:
+            raise NotImplementedError("tacotron_teacher_forcing_ratio=%r: only 1.0 (pure teacher forcing, Helpers.py:118-124) is built"
+                                      % hp.tacotron_teacher_forcing_ratio)
+        if bool(getattr(hp, "predict_linear", False)):
+            raise NotImplementedError("predict_linear=True (CBHG post-processing net, Tacotron.py:319-337) is out of scope")
         self.store = ParamStore(ops, weights, reg)
+        # tacotron_fine_tuning (Tacotron.py:478-480): variables whose name contains 'inputs_embedding' or 'encoder_' are
+        # excluded from the update; here a 0/1 mask over the flat gradient, applied before the global norm
+        self.update_mask = None
+        self.regw_grad = self.store.regw
+        if bool(getattr(hp, "tacotron_fine_tuning", False)):
+            import numpy as _np
+            from .params import FINE_TUNE_FROZEN
+            mask = _np.ones(self.store.n, _np.float32)
+            for name, (o_, shp) in self.store.layout.items():
+                if any(f in name for f in FINE_TUNE_FROZEN):
+                    mask[o_:o_ + (int(_np.prod(shp)) if len(shp) else 1)] = 0.0
+            self.update_mask = ops.to_device(mask)
+            # compute_gradients(var_list=update_vars): the frozen variables get no L2 gradient either (the LOSS keeps their term)
+            self.regw_grad = ops.to_device(mask)
+            ops.ew("mul", self.regw_grad, self.regw_grad, self.store.regw)
+        self.on_tail_ready = None     # set by the data-parallel trainer: called in backward() when store.g[tail_start:] is final
         self.losses = None
         self.update_moving_stats = True
         lo = (-hp.max_abs_value if hp.symmetric_mels else 0.0) - hp.lower_bound_decay
@@ -106,10 +132,23 @@ class TrainStep(object):
             o.gemm(dy2, P[kernel_name], dx2, tb=True, beta=beta)
 
     # ------------------------------------------------------------------ forward
+    def _check_shapes(self, ids, lens, mel_targets, stop_targets):
+        B = ids.shape[0]
+        if mel_targets.dim() != 3 or mel_targets.shape[0] != B or mel_targets.shape[2] != self.hp.num_mels:
+            raise ValueError("mel_targets must be [B=%d, F, %d], got %s" % (B, self.hp.num_mels, tuple(mel_targets.shape)))
+        if mel_targets.shape[1] % self.hp.outputs_per_step != 0:
+            raise ValueError("mel_targets frames (%d) must be a multiple of outputs_per_step" % mel_targets.shape[1])
+        if tuple(stop_targets.shape) != (B, mel_targets.shape[1]):
+            raise ValueError("stop_token_targets must be [B, F] = %s (one per mel frame), got %s"
+                             % ((B, mel_targets.shape[1]), tuple(stop_targets.shape)))
+        if ids.dim() != 2 or tuple(lens.shape) != (B,):
+            raise ValueError("inputs must be [B, T] with input_lengths [B], got %s / %s" % (tuple(ids.shape), tuple(lens.shape)))
+
     def forward(self, ids, lens, mel_targets, stop_targets, seed):
         """ids int32 [B,T], lens int32 [B], mel_targets fp32 [B,F,80], stop_targets fp32 [B,F] (device
         tensors).  Returns the tower outputs + losses of ``initialize(is_training=True)`` / ``add_loss``."""
         hp, o, P = self.hp, self.ops, self.store.P
+        self._check_shapes(ids, lens, mel_targets, stop_targets)
         B, T = ids.shape
         F = mel_targets.shape[1]
         r, M = hp.outputs_per_step, hp.num_mels
@@ -417,6 +456,10 @@ class TrainStep(object):
         if hp.mask_encoder:
             o.mask_rows(dvalues, t["lens"])
         dmemory = dvalues
+        # every decoder / postnet gradient (store.g[tail_start:]) is final from here on: the data-parallel trainer starts
+        # the exchange of that half now, under the style / encoder backward that follows
+        if self.on_tail_ready is not None:
+            self.on_tail_ready()
 
         # ---- style embedding: GST attention -> reference encoder (Attention.py:243-341; Tacotron.py:12-29)
         nh = hp.num_heads
@@ -512,15 +555,22 @@ class TrainStep(object):
             (global_step - hp.tacotron_start_decay) / float(hp.tacotron_decay_steps))
         return min(max(lr, hp.tacotron_final_learning_rate), hp.tacotron_initial_learning_rate)
 
-    def apply(self, global_step, world=1, all_reduce=None):
+    def apply(self, global_step, world=1, all_reduce=None, ranks=None):
         """Average the tower gradients (one all-reduce of the flat buffer replaces Tacotron.py:484-501), add the
         L2 term, clip by global norm 1.0 (:507), Adam update (:470-471; TF formulation, eps outside the bias
         correction).  ``global_step`` counts completed updates (0 for the first)."""
         hp, o, st = self.hp, self.ops, self.store
         if all_reduce is not None and world > 1:
-            all_reduce(st.g)                                          # SUM over ranks
+            # SUM over ranks of the ONE flat bucket [BN moving statistics | gradients]; a trainer that already started the
+            # early half (decoder + postnet gradients) passes a reducer that finishes the rest and joins both
+            all_reduce(st.bucket)
+            if st.ns:
+                # mean over the RANKS that were summed (``world`` also counts the in-process towers of one rank)
+                o.ew("scale", st.s, st.s, None, 1.0 / (world if ranks is None else ranks))
+        if self.update_mask is not None:
+            o.ew("mul", st.g, st.g, self.update_mask)                # tacotron_fine_tuning (Tacotron.py:478-480)
         sumsq = o.zeros(1)
-        o.grad_finalize(st.g, st.p, st.regw, 1.0 / world, sumsq)
+        o.grad_finalize(st.g, st.p, self.regw_grad, 1.0 / world, sumsq)
         tstep = global_step + 1
         b1, b2 = hp.tacotron_adam_beta1, hp.tacotron_adam_beta2
         lr_t = self.learning_rate(global_step) * np.sqrt(1.0 - b2 ** tstep) / (1.0 - b1 ** tstep)

@@ -6,9 +6,12 @@ owns one tower (batch shard) and the exchange is a single ``all_reduce(SUM)`` of
 buffer (20 425 491 elements, 81.7 MB) over NCCL / NVLink; the division by the world size, the L2 term,
 the global-norm clip and the Adam update are one fused pass over the reduced buffer on every rank
 (identical inputs -> identical weights, no broadcast needed).  Batch-norm moving statistics are
-per-rank batch estimates; they are averaged across ranks in the same step (the reference applies every
-tower's UPDATE_OPS to the same CPU variables, Tacotron.py:513 -- a momentum update per tower; the mean
-of the per-rank updates is the order-independent equivalent).
+per-rank batch estimates; they travel in the SAME flat bucket ([statistics | gradients], train/params.py) and are
+averaged across ranks (the reference applies every tower's UPDATE_OPS to the same CPU variables,
+Tacotron.py:513 -- a momentum update per tower; the mean of the per-rank updates is the order-independent
+equivalent).  The bucket is exchanged in two contiguous halves: the decoder + postnet gradients (70 % of the bytes)
+are final when the decoder BPTT ends, so their all-reduce starts there on a side stream and runs under the style /
+encoder backward; the rest follows when backward() returns.
 """
 from __future__ import annotations
 
@@ -29,8 +32,48 @@ class DataParallelTrainer(object):
         self.dist = torch.distributed if (torch.distributed.is_available() and torch.distributed.is_initialized()) else None
         self.world = self.dist.get_world_size() if self.dist else 1
         self.rank = self.dist.get_rank() if self.dist else 0
+        self.overlap = True
+        self._early = None            # (work handle | None, side-stream event) of the early half started in backward()
+        self._side = None
+        if self.world > 1:
+            self.step_fn.on_tail_ready = self._start_early_half
+
+    # ---- the exchange step ----
+    def _on_cuda(self):
+        return self.step_fn.store.bucket.is_cuda
+
+    def _start_early_half(self):
+        """Called inside backward() once store.g[tail_start:] is final: all-reduce that half on a side stream."""
+        if not self.overlap or self.world == 1:
+            return
+        st = self.step_fn.store
+        early = st.bucket[st.ns + st.tail_start:]
+        if not self._on_cuda():                       # gloo / CPU twin (tests): no streams, reduce in place right away
+            self.dist.all_reduce(early, op=self.dist.ReduceOp.SUM)
+            self._early = (None, None)
+            return
+        if self._side is None:
+            self._side = torch.cuda.Stream(device=st.bucket.device)
+        ready = torch.cuda.Event()
+        ready.record()
+        with torch.cuda.stream(self._side):
+            self._side.wait_event(ready)
+            self.dist.all_reduce(early, op=self.dist.ReduceOp.SUM)
+            done = torch.cuda.Event()
+            done.record()
+        self._early = (None, done)
 
     def _all_reduce(self, t):
+        """Reducer handed to TrainStep.apply: SUM of the flat bucket over the ranks.  If the early half is already in flight
+        only the late half [statistics | encoder / style gradients] is reduced here, then both are joined."""
+        st = self.step_fn.store
+        if t is st.bucket and self._early is not None:
+            _, done = self._early
+            self._early = None
+            self.dist.all_reduce(st.bucket[:st.ns + st.tail_start], op=self.dist.ReduceOp.SUM)
+            if done is not None:
+                torch.cuda.current_stream().wait_event(done)
+            return
         self.dist.all_reduce(t, op=self.dist.ReduceOp.SUM)
 
     def step(self, ids, lens, mel_targets, stop_targets, seed=None):
@@ -41,9 +84,6 @@ class DataParallelTrainer(object):
         out = st.forward(ids, lens, mel_targets, stop_targets, seed)
         st.backward()
         st.apply(self.global_step, world=self.world, all_reduce=self._all_reduce if self.world > 1 else None)
-        if self.world > 1 and st.store.s.numel():
-            self._all_reduce(st.store.s)
-            self.ops.ew("scale", st.store.s, st.store.s, None, 1.0 / self.world)
         self.global_step += 1
         ls = out["losses"]
         self.ops.ew("add", ls[4:5], ls[0:1], ls[1:2])
@@ -53,3 +93,11 @@ class DataParallelTrainer(object):
 
     def export(self):
         return self.step_fn.store.export()
+
+    # ---- checkpoint / resume (the reference's tf.train.Saver keeps variables, Adam slots and global_step, train.py:60) ----
+    def save(self, path):
+        self.step_fn.store.save_state(path, self.global_step)
+
+    def load(self, path):
+        self.global_step = self.step_fn.store.load_state(path)
+        return self.global_step

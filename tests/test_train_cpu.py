@@ -93,3 +93,70 @@ def test_apply_matches_reference_optimizer(problem):
     # moving statistics moved towards the batch statistics (UPDATE_OPS, Tacotron.py:513)
     k = "postnet_convolutions/conv_layer_1_postnet_convolutions/batch_normalization/moving_mean"
     assert np.abs(new[k] - np.asarray(w[k])).max() > 0
+
+
+def test_unsupported_training_hparams_raise():
+    """Settings that change the reference's training graph and are not built must fail loudly (Helpers.py:100-124)."""
+    w = weights.init_weights(default_hparams(), perturb=0.05)
+    for field, value in (("tacotron_teacher_forcing_mode", "scheduled"), ("tacotron_teacher_forcing_ratio", 0.5), ("predict_linear", True)):
+        hp = default_hparams()
+        setattr(hp, field, value)
+        with pytest.raises(NotImplementedError):
+            TrainStep(hp, TorchOps(), w)
+
+
+def test_forward_rejects_mismatched_stop_targets(problem):
+    hp, w, data, _, _ = problem
+    ids, lens, mel, stop, seed = data
+    step = TrainStep(hp, TorchOps(), w)
+    wide = np.concatenate([stop, np.ones((stop.shape[0], 2), np.float32)], axis=1)      # F + 2 columns
+    with pytest.raises(ValueError):
+        step.forward(torch.from_numpy(ids), torch.from_numpy(lens), torch.from_numpy(mel), torch.from_numpy(wide), seed)
+
+
+def test_fine_tuning_freezes_embedding_and_encoder(problem):
+    """tacotron_fine_tuning (Tacotron.py:478-480): variables named *inputs_embedding* / *encoder_* keep their values."""
+    hp0, w, data, _, _ = problem
+    hp = default_hparams()
+    hp.tacotron_fine_tuning = True
+    step, _ = _run(hp, w, data)
+    step.apply(global_step=0)
+    new = step.store.export()
+    frozen = [n for n in step.store.layout if "inputs_embedding" in n or "encoder_" in n]
+    assert "inputs_embedding" in frozen and any(n.startswith("encoder_LSTM/") for n in frozen) and len(frozen) == 17
+    assert not any(n.startswith("ref_encoder/") for n in frozen)     # 'ref_encoder/...' does not contain 'encoder_'
+    for n in frozen:
+        assert np.array_equal(new[n], np.asarray(w[n], np.float32)), n
+    moved = "decoder/decoder_prenet/dense_2/kernel"
+    assert np.abs(new[moved] - np.asarray(w[moved])).max() > 0
+
+
+def test_training_state_round_trip_resumes_adam_and_schedule(problem, tmp_path):
+    """Checkpoint = variables + BN statistics + Adam moments + global_step (tf.train.Saver, train.py:60): two updates in one
+    run equal one update, save, load into a fresh store, second update."""
+    hp, w, data, _, _ = problem
+    ids, lens, mel, stop, seed = data
+    args = tuple(torch.from_numpy(a) for a in (ids, lens, mel, stop))
+
+    def update(step, k):
+        step.forward(*args, seed + k)
+        step.backward()
+        step.apply(global_step=k)
+
+    a = TrainStep(hp, TorchOps(), w)
+    update(a, 0)
+    path = str(tmp_path / "state.npz")
+    a.store.save_state(path, 1)
+    update(a, 1)
+    b = TrainStep(hp, TorchOps(), weights.init_weights(hp, perturb=0.0))       # different initial values: everything must come from the file
+    assert b.store.load_state(path) == 1
+    update(b, 1)
+    ea, eb = a.store.export(), b.store.export()
+    for n in ea:
+        assert np.array_equal(ea[n], eb[n]), n
+    assert torch.equal(a.store.m, b.store.m) and torch.equal(a.store.v, b.store.v)
+    # a plain weight container (no Adam slots) loads with zero moments and step 0
+    plain = str(tmp_path / "weights.npz")
+    weights.save(plain, ea)
+    c = TrainStep(hp, TorchOps(), w)
+    assert c.store.load_state(plain) == 0 and float(c.store.m.abs().max()) == 0.0
