@@ -18,6 +18,11 @@ w = weights.set_stop_bias(weights.init_weights(hp, perturb=0.05), -10.0)
 eng = TacoEngine(hp, w, precision="bf16")
 ids, lens = synthetic.token_batch(hp, synthetic.cycle_lengths(B))
 mem = eng.encode(torch.from_numpy(ids), torch.from_numpy(lens), gst_weights=synthetic.gst_random_weights(hp))
+steps = -1
 for _ in range(3):
-    d = eng.decode(mem, torch.from_numpy(lens), max_iters=S, philox_seed=1)
-print("B=%d T=%d S=%d steps=%d decoder stage %.3f ms -> %.2f us/step" % (B, ids.shape[1], S, d["steps"], eng.stage_ms(1), 1e3 * eng.stage_ms(1) / S))
+    try:
+        d = eng.decode(mem, torch.from_numpy(lens), max_iters=S, philox_seed=1)
+        steps = d["steps"]
+    except Exception as e:   # ablation runs (TACO_DEC3_DBG) may abort by design; the stage timer is still valid
+        steps = -1
+print("B=%d T=%d S=%d steps=%d decoder stage %.3f ms -> %.2f us/step" % (B, ids.shape[1], S, steps, eng.stage_ms(1), 1e3 * eng.stage_ms(1) / S))

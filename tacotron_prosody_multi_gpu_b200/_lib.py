@@ -6,7 +6,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libtaco_b200.so")
+LIB_PATH = os.environ.get("TACO_B200_LIB") or os.path.join(HERE, "libtaco_b200.so")   # env: A/B builds of the same library (development)
 
 TACO_OK = 0
 TACO_MODE_FREE = 0

@@ -76,13 +76,15 @@ constexpr int SO_TACC = SO_FLAG + 16;              // 24 x int64 stage timers
 constexpr int SO_OWN = SO_TACC + 48;             // [16]: cluster rank that owns the attention of cluster row i
 constexpr int SO_LEN = SO_OWN + 16;              // [16]: memory length of cluster row i
 constexpr int SO_GRP = SO_LEN + 16;              // [16][2]: first thread group / number of groups of row i in the context-slice reduction
-constexpr int SO_AALL = SO_GRP + 32;             // [R][TP] alignment rows of every cluster row, multicast by their owners
+constexpr int SO_MBAR = SO_GRP + 32;             // 9 mbarriers (64-bit each): one per exchange buffer, one phase per decoder step
+constexpr int MB_P1 = 0, MB_P2 = 1, MB_H1R = 2, MB_H1Z = 3, MB_H2R = 4, MB_H2Z = 5, MB_CTX = 6, MB_Q = 7, MB_A = 8, N_MB = 9;
+constexpr int SO_AALL = SO_MBAR + 2 * N_MB + 2;  // [R][TP] alignment rows of every cluster row, multicast by their owners
 constexpr int A_CAP = TACO_DEC3_ACAP;            // words: R * TP <= A_CAP (the host picks the cluster count accordingly)
 constexpr int SMEM3_WORDS = SO_AALL + A_CAP;
 static_assert(RES_WORDS == TACO_DEC3_RES_WORDS, "resident blob size");
 static_assert(SMEM3_WORDS * 4 <= 227 * 1024, "shared memory budget");
 static_assert(SO_P1 % 4 == 0 && SO_RED % 4 == 0 && SO_QRECV % 4 == 0 && SO_STG_R % 4 == 0 && SO_STG_C % 4 == 0 && SO_ES % 4 == 0 &&
-              SO_QS % 4 == 0 && SO_TACC % 2 == 0 && SO_AALL % 4 == 0, "smem alignment");
+              SO_QS % 4 == 0 && SO_TACC % 2 == 0 && SO_AALL % 4 == 0 && SO_MBAR % 2 == 0, "smem alignment");
 
 extern __shared__ __align__(16) uint32_t smem3[];
 #define SMU(off) (smem3 + (off))
@@ -101,6 +103,28 @@ __device__ __forceinline__ uint32_t mapa_rank(uint32_t addr, uint32_t rank) {
 }
 __device__ __forceinline__ void st_remote_v4(uint32_t addr, const uint4& v) {
     asm volatile("st.shared::cluster.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+// ---- exchange synchronisation: every remote store is a st.async that completes bytes on the DESTINATION's mbarrier of that
+// buffer; one mbarrier phase per decoder step (expected byte count armed by the consumer), consumers sleep in try_wait -- no
+// sentinel values, no polling loads, no re-arming of the buffers.
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ void st_async_v4(uint32_t addr, const uint4& v, uint32_t bar) {
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v4.b32 [%0], {%1,%2,%3,%4}, [%5];"
+                 ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w), "r"(bar) : "memory");
 }
 __device__ __forceinline__ uint2 lds_poll_v2(const uint32_t* p) {
     uint2 v;
@@ -169,17 +193,20 @@ __device__ __forceinline__ float tanh_f(float x) { return 1.0f - __fdividef(2.0f
 // word offset, inside a 128-word B block, of the bf16 pair (row r, k-pair j = 0..7 of the k-step)
 __device__ __forceinline__ int bword(int r, int j) { return ((r >> 3) << 6) + ((((r & 7) << 2) | (j & 3)) << 1) + (j >> 2); }
 
-// B fragment of (k-step block, n-tile j) for this lane, polling while a producer has not written it yet
-__device__ __forceinline__ uint2 load_b(const uint32_t* blk, int j, int lane, Guard3& g) {
-    const uint32_t* p = blk + (j << 6) + (lane << 1);
-    uint2 b = lds_poll_v2(p);
+// wait (bounded) until the mbarrier phase `parity` of exchange buffer `mb` has completed: all of its bytes have arrived
+__device__ __forceinline__ void mbar_wait(int mb, uint32_t parity, Guard3& g) {
+    const uint32_t bar = smem_addr(SMU(SO_MBAR) + 2 * mb);
     int spins = 0;
-    while (!g.dead && __any_sync(0xffffffffu, b.x == SENT || b.y == SENT)) {
+    while (!g.dead && !mbar_try_wait(bar, parity)) {
         if (spin_check3(g, spins)) break;
-        b = lds_poll_v2(p);
     }
-    g.dead = __any_sync(0xffffffffu, g.dead);
-    return b;
+}
+// ... and, by ONE thread after its own wait returned, arm the next phase with the bytes one decoder step delivers
+__device__ __forceinline__ void mbar_rearm(int mb, uint32_t bytes) { mbar_expect_tx(smem_addr(SMU(SO_MBAR) + 2 * mb), bytes); }
+
+// B fragment of (k-step block, n-tile j) for this lane (the caller has waited for the buffer's mbarrier phase)
+__device__ __forceinline__ uint2 load_b(const uint32_t* blk, int j, int lane, Guard3&) {
+    return *reinterpret_cast<const uint2*>(blk + (j << 6) + (lane << 1));
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -201,25 +228,15 @@ __device__ __forceinline__ void prefetch4(uint4 (&a)[4], const uint4* set_mt, in
 #pragma unroll
     for (int i = 0; i < 4; ++i) a[i] = ldg_stream_v4(set_mt + (size_t)(kg + 4 * i) * 32 + lane);
 }
-// the 8 B fragments (4 k-steps x 2 n-tiles) of blocks ks0, ks0 + kstride, ...: all loads in flight together, ONE vote per round
-__device__ __forceinline__ void load_b4(uint2 (&b)[4][2], const uint32_t* bbuf, int ks0, int kstride, int nks, int lane, Guard3& g) {
-    int spins = 0;
-    while (true) {
-        bool bad = false;
+// the 8 B fragments (4 k-steps x 2 n-tiles) of blocks ks0, ks0 + kstride, ...
+__device__ __forceinline__ void load_b4(uint2 (&b)[4][2], const uint32_t* bbuf, int ks0, int kstride, int nks, int lane, Guard3&) {
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            if (i < nks) {
+    for (int i = 0; i < 4; ++i) {
+        if (i < nks) {
 #pragma unroll
-                for (int j = 0; j < 2; ++j) {
-                    b[i][j] = lds_poll_v2(bbuf + (ks0 + i * kstride) * TILE_W + (j << 6) + (lane << 1));
-                    bad = bad || b[i][j].x == SENT || b[i][j].y == SENT;
-                }
-            }
+            for (int j = 0; j < 2; ++j) b[i][j] = *reinterpret_cast<const uint2*>(bbuf + (ks0 + i * kstride) * TILE_W + (j << 6) + (lane << 1));
         }
-        if (!__any_sync(0xffffffffu, bad)) break;
-        if (g.dead || spin_check3(g, spins)) break;
     }
-    g.dead = __any_sync(0xffffffffu, g.dead);
 }
 // acc[j] += A(regs i) . B(block kg + 4 i, n-tile j)
 __device__ __forceinline__ AccV gemm_regs_core(AccV acc, A4 a, const uint32_t* bbuf, int kg, int lane, int* abort_flag) {
@@ -312,24 +329,20 @@ __device__ __forceinline__ void store_red3(float* red, const float (&acc)[2][4],
     store_red3_core(red, x, slot, lane);
 }
 
-// re-arm a consumed activation buffer: valid rows -> sentinel, padding rows -> 0 (they have no producer)
-__device__ __forceinline__ void rearm(uint32_t* buf, int KS, int R, int tid) {
+// zero the activation buffers once: padding rows (>= R) have no producer and must read as 0
+__device__ __forceinline__ void zero_blocks(uint32_t* buf, int KS, int tid) {
     uint4* b4 = reinterpret_cast<uint4*>(buf);
-    for (int i = tid; i < KS * (TILE_W / 4); i += NT) {
-        const int v = i & 31;   // uint4 index inside the block: 4 words = 2 lanes of one row
-        const int row = ((v >> 4) << 3) + ((v & 15) >> 1);
-        const uint32_t x = row < R ? SENT : 0u;
-        b4[i] = make_uint4(x, x, x, x);
-    }
+    for (int i = tid; i < KS * (TILE_W / 4); i += NT) b4[i] = make_uint4(0u, 0u, 0u, 0u);
 }
 
 // multicast one staged 128-word block (B-fragment order, k-step = this CTA's rank) to every CTA of the cluster
-__device__ __forceinline__ void multicast_block(const uint32_t* stage, uint32_t* dst_buf, int rank, int R, int tid) {
+// (st.async: the 16 bytes complete on the destination's mbarrier `mb`; R rows x 32 bytes per source and block)
+__device__ __forceinline__ void multicast_block(const uint32_t* stage, uint32_t* dst_buf, int mb, int rank, int R, int tid) {
     const int dst = tid >> 5, v = tid & 31;
     const int row = ((v >> 4) << 3) + ((v & 15) >> 1);
     if (row < R) {
         const uint4 val = *reinterpret_cast<const uint4*>(stage + (v << 2));
-        st_remote_v4(mapa_rank(smem_addr(dst_buf + rank * TILE_W + (v << 2)), dst), val);
+        st_async_v4(mapa_rank(smem_addr(dst_buf + rank * TILE_W + (v << 2)), dst), val, mapa_rank(smem_addr(SMU(SO_MBAR) + 2 * mb), dst));
     }
 }
 

@@ -158,8 +158,10 @@ __device__ __forceinline__ int ctx_groups_of(int len, int total) { return (CTX_B
 // q from the 16 partials, energies, masked softmax, cumulate, alignment history, and the multicast of the alignment row to
 // every CTA of the cluster (each of which reduces a 48-column slice of the context, att3_context_slice).
 __device__ __forceinline__ void att3_owner(const Dec3Params& p, float (&preR)[8][4], float* pre_scr, int b, int len, int arow, int s,
-                                           int tid, int warp, int lane, Guard3& g, long long* tacc, long long& tprev, bool timing, bool tracing) {
+                                           int tid, int warp, int lane, Guard3& g, long long* tacc, long long& tprev, bool timing, bool tracing,
+                                           uint32_t q_bytes) {
     float* scr = SMF(SO_RED);
+#ifdef TACO_DEC3_TRACE_BUILD
 #define A3_TR(i)                                                        \
     if (tracing && tid == 0) {                                          \
         long long gt_;                                                  \
@@ -167,6 +169,9 @@ __device__ __forceinline__ void att3_owner(const Dec3Params& p, float (&preR)[8]
         p.trace[((size_t)blockIdx.x * 64 + (i)) * 2] = clock64();       \
         p.trace[((size_t)blockIdx.x * 64 + (i)) * 2 + 1] = gt_;         \
     }
+#else
+#define A3_TR(i)
+#endif
 #define A3_STAMP(i)                                                     \
     if (timing) { /* whole warp 0, uniform: a divergent stamp would push the following collectives onto their slow path */ \
         long long now_;                                                 \
@@ -178,15 +183,11 @@ __device__ __forceinline__ void att3_owner(const Dec3Params& p, float (&preR)[8]
     {
         // 4 threads per d, 4 sources each
         const int d = tid >> 2, part = tid & 3;
+        mbar_wait(MB_Q, (uint32_t)(s & 1), g);
+        if (tid == 0 && !g.dead) mbar_rearm(MB_Q, q_bytes);
         float q = 0.f;
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            const uint32_t* a = SMU(SO_QRECV) + (part * 4 + i) * ATT + d;
-            uint32_t w = *reinterpret_cast<const volatile uint32_t*>(a);
-            int spins = 0;
-            while (w == SENT && !spin_check3(g, spins)) w = *reinterpret_cast<const volatile uint32_t*>(a);
-            q += __uint_as_float(w);
-        }
+        for (int i = 0; i < 4; ++i) q += SMF(SO_QRECV)[(part * 4 + i) * ATT + d];
         q += __shfl_xor_sync(0xffffffffu, q, 1);
         q += __shfl_xor_sync(0xffffffffu, q, 2);
         if (part == 0) SMF(SO_QS)[d] = g.dead ? 0.f : q;
@@ -195,7 +196,6 @@ __device__ __forceinline__ void att3_owner(const Dec3Params& p, float (&preR)[8]
     __syncthreads();
     A3_STAMP(8)
     A3_TR(35)
-    for (int i = tid; i < CS * ATT; i += NT) SMU(SO_QRECV)[i] = SENT;  // re-arm for the next step
     // E2: energies e[t] = sum_d v_a[d] tanh(pre[t][d] + q[d])   (Attention.py:401)
     if (p.pre_reg) {
         const int gq = lane >> 2, tq = lane & 3, d0 = warp * 8 + 2 * tq;
@@ -241,6 +241,7 @@ __device__ __forceinline__ void att3_owner(const Dec3Params& p, float (&preR)[8]
     __syncthreads();
     A3_STAMP(16)
     A3_TR(36)
+#ifdef D3_OLD_SOFTMAX
     // E3: masked softmax over t < len (exact zeros beyond: -inf mask), Attention.py:203-206
     if (warp == 0) {
         if (p.pre_reg) {
@@ -290,6 +291,66 @@ __device__ __forceinline__ void att3_owner(const Dec3Params& p, float (&preR)[8]
             for (int t = lane; t < len; t += 32) SMF(SO_ES)[t] *= inv;
         }
     }
+#else
+    // E3: masked softmax over t < len (exact zeros beyond: -inf mask), Attention.py:203-206
+    if (p.pre_reg) {
+        // all 512 threads: thread (position t = tid >> 2, quarter = tid & 3) adds 4 of the 16 per-warp partials of e[t]; a warp
+        // covers 8 positions, so the row maximum and the normaliser are two warp reductions + one 16-entry exchange each
+        float* wred = SMF(SO_QS);   // q has been consumed by E2: [0,16) warp maxima, [16,32) warp sums
+        const int t = tid >> 2, part = tid & 3;
+        float x = 0.f;
+        if (t < len) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) x += scr[(part * 4 + i) * PRE_REG_T + t];
+        }
+        x += __shfl_xor_sync(0xffffffffu, x, 1);
+        x += __shfl_xor_sync(0xffffffffu, x, 2);
+        const float e = t < len ? x : -INFINITY;
+        float m = 0.f;
+        if (!p.smoothing) {
+            m = e;
+            m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 4));
+            m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 8));
+            m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 16));
+            if (lane == 0) wred[warp] = m;
+            __syncthreads();
+            const float4 a0 = *reinterpret_cast<const float4*>(wred), a1 = *reinterpret_cast<const float4*>(wred + 4);
+            const float4 a2 = *reinterpret_cast<const float4*>(wred + 8), a3 = *reinterpret_cast<const float4*>(wred + 12);
+            m = fmaxf(fmaxf(fmaxf(fmaxf(a0.x, a0.y), fmaxf(a0.z, a0.w)), fmaxf(fmaxf(a1.x, a1.y), fmaxf(a1.z, a1.w))),
+                      fmaxf(fmaxf(fmaxf(a2.x, a2.y), fmaxf(a2.z, a2.w)), fmaxf(fmaxf(a3.x, a3.y), fmaxf(a3.z, a3.w))));
+        }
+        const float v = t < len ? (p.smoothing ? sigmoidf_(e) : __expf(e - m)) : 0.f;
+        float sm = v;
+        sm += __shfl_xor_sync(0xffffffffu, sm, 4);
+        sm += __shfl_xor_sync(0xffffffffu, sm, 8);
+        sm += __shfl_xor_sync(0xffffffffu, sm, 16);
+        if (lane == 0) wred[16 + warp] = sm;
+        __syncthreads();
+        float sum = 0.f;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const float4 a = *reinterpret_cast<const float4*>(wred + 16 + 4 * i);
+            sum += (a.x + a.y) + (a.z + a.w);
+        }
+        const float inv = __fdividef(1.0f, sum);
+        if (part == 0) SMF(SO_ES)[t] = v * inv;   // t < PRE_REG_T always; exact zeros beyond the length
+    } else if (warp == 0) {
+        float m = -INFINITY;
+        if (!p.smoothing) {
+            for (int t = lane; t < len; t += 32) m = fmaxf(m, SMF(SO_ES)[t]);
+            m = warp_max(m);
+        }
+        float sum = 0.f;
+        for (int t = lane; t < len; t += 32) {
+            const float v = p.smoothing ? sigmoidf_(SMF(SO_ES)[t]) : __expf(SMF(SO_ES)[t] - m);
+            SMF(SO_ES)[t] = v;
+            sum += v;
+        }
+        sum = warp_sum(sum);
+        const float inv = 1.0f / sum;
+        for (int t = lane; t < len; t += 32) SMF(SO_ES)[t] *= inv;
+    }
+#endif
     __syncthreads();
     A3_STAMP(10)
     A3_TR(37)
@@ -301,7 +362,7 @@ __device__ __forceinline__ void att3_owner(const Dec3Params& p, float (&preR)[8]
             const int slot = i / nv, v = i - slot * nv;
             const int dst = (slot + arow) & (CS - 1);
             const uint4 val = *reinterpret_cast<const uint4*>(SMU(SO_ES) + (v << 2));
-            st_remote_v4(mapa_rank(smem_addr(SMU(SO_AALL) + arow * TP + (v << 2)), dst), val);
+            st_async_v4(mapa_rank(smem_addr(SMU(SO_AALL) + arow * TP + (v << 2)), dst), val, mapa_rank(smem_addr(SMU(SO_MBAR) + 2 * MB_A), dst));
         }
     }
     A3_TR(38)
@@ -323,22 +384,11 @@ __device__ __forceinline__ void att3_owner(const Dec3Params& p, float (&preR)[8]
 // the owners multicast, then multicasts its three k-step blocks (B-fragment order) to the whole cluster: the reduction is spread
 // over 16 SMs' L2 ports instead of one per row, and nobody waits for the CTA that owns the longest row.
 __device__ __forceinline__ void att3_context_slice(const Dec3Params& p, uint32_t cmw, int row0, int R, int rank, int s, int tid,
-                                                   Guard3& g, bool tracing) {
+                                                   Guard3& g, bool tracing, uint32_t a_bytes) {
     float* scr = SMF(SO_RED);
     const int TP = p.TP;
     __syncthreads();   // the K-split partials / query slices of this step (same scratch) have been read
     A3_TR(40)
-    if (tracing) {   // trace mode only: all alignment rows present before the loads start
-        for (int r2 = 0; r2 < R; ++r2) {
-            const int l2 = (int)SMU(SO_LEN)[r2];
-            for (int t = tid; t < l2; t += NT) {
-                int spins = 0;
-                while (*reinterpret_cast<const volatile uint32_t*>(SMU(SO_AALL) + r2 * TP + t) == SENT && !spin_check3(g, spins)) {
-                }
-            }
-        }
-        __syncthreads();
-    }
     A3_TR(41)
     const int nslot = (cmw >> 12) & 255;
     if (nslot) {
@@ -348,7 +398,10 @@ __device__ __forceinline__ void att3_context_slice(const Dec3Params& p, uint32_t
         const uint4* vp = reinterpret_cast<const uint4*>(p.values) + (size_t)b * p.T * (MEM / 8) + 6 * rank + chunk;
         const uint32_t* al = SMU(SO_AALL) + crow * TP;
         float c[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-        constexpr int UB = 5;
+#ifndef D3_UB
+#define D3_UB 5
+#endif
+        constexpr int UB = D3_UB;   // one round of loads for rows up to 8 x nslot positions (T = 111: nslot >= 14)
         for (int t0 = cslot; t0 < len; t0 += nslot * UB) {
             uint4 v[UB];
             float a[UB];
@@ -357,17 +410,11 @@ __device__ __forceinline__ void att3_context_slice(const Dec3Params& p, uint32_t
                 const int t = t0 + u * nslot;
                 v[u] = (t < len && !(p.dbg & 32)) ? ldg_stream_v4(vp + (size_t)t * (MEM / 8)) : make_uint4(0u, 0u, 0u, 0u);
             }
+            if (t0 == cslot) mbar_wait(MB_A, (uint32_t)(s & 1), g);   // after the value loads of the first batch are in flight
 #pragma unroll
             for (int u = 0; u < UB; ++u) {
                 const int t = t0 + u * nslot;
-                uint32_t w = 0u;
-                if (t < len) {
-                    w = *reinterpret_cast<const volatile uint32_t*>(al + t);
-                    int spins = 0;
-                    while (w == SENT && !spin_check3(g, spins)) w = *reinterpret_cast<const volatile uint32_t*>(al + t);
-                    if (g.dead) w = 0u;
-                }
-                a[u] = __uint_as_float(w);
+                a[u] = t < len ? __uint_as_float(al[t]) : 0.f;
             }
 #pragma unroll
             for (int u = 0; u < UB; ++u) {
@@ -388,8 +435,10 @@ __device__ __forceinline__ void att3_context_slice(const Dec3Params& p, uint32_t
     A3_TR(42)
     g.dead = __syncthreads_or(g.dead ? 1 : 0) != 0;
     A3_TR(43)
-    // every alignment row has been consumed: re-arm (valid rows only; rows >= R are never written)
-    for (int i = tid; i < (R * TP) >> 2; i += NT) reinterpret_cast<uint4*>(SMU(SO_AALL))[i] = make_uint4(SENT, SENT, SENT, SENT);
+    if (tid == 0 && !g.dead) {   // (thread 0 has work whenever the cluster has a row: its wait above has returned)
+        mbar_wait(MB_A, (uint32_t)(s & 1), g);
+        mbar_rearm(MB_A, a_bytes);
+    }
     if (tid < R * 24) {
         const int r = tid / 24, cp = tid - r * 24;
         const int g0 = (int)SMU(SO_GRP)[2 * r], ng = (int)SMU(SO_GRP)[2 * r + 1];   // groups of row r: [g0, g0 + ng)
@@ -417,7 +466,7 @@ __device__ __forceinline__ void att3_context_slice(const Dec3Params& p, uint32_t
 #pragma unroll
             for (int k = 0; k < 3; ++k) {
                 const uint4 val = *reinterpret_cast<const uint4*>(SMU(SO_STG_C) + k * TILE_W + (v << 2));
-                st_remote_v4(mapa_rank(smem_addr(SMU(SO_CTX) + (3 * rank + k) * TILE_W + (v << 2)), dst), val);
+                st_async_v4(mapa_rank(smem_addr(SMU(SO_CTX) + (3 * rank + k) * TILE_W + (v << 2)), dst), val, mapa_rank(smem_addr(SMU(SO_MBAR) + 2 * MB_CTX), dst));
             }
         }
     }

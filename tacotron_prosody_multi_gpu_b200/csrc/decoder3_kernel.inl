@@ -15,7 +15,9 @@ constexpr int ACT_W = 1024;     // projection input row: [h2raw 256 | context 76
         tprev = now_;                                                   \
     }
 
-// one-step trace (TACO_DEC3_TRACE=<step>): warp 0 lane 0 stamps (clock64, globaltimer) at point i of step trace_step
+// one-step trace (build with -DTACO_DEC3_TRACE_BUILD, run with TACO_DEC3_TRACE=<step>): warp 0 lane 0 stamps (clock64, globaltimer)
+// at point i of step trace_step.  Compiled out of the product build: the extra code costs 2 us per step even when it never runs.
+#ifdef TACO_DEC3_TRACE_BUILD
 #define D3_TR(i)                                                        \
     if (tracing && tid == 0) {                                          \
         long long gt_;                                                  \
@@ -23,14 +25,69 @@ constexpr int ACT_W = 1024;     // projection input row: [h2raw 256 | context 76
         p.trace[((size_t)blockIdx.x * 64 + (i)) * 2] = clock64();       \
         p.trace[((size_t)blockIdx.x * 64 + (i)) * 2 + 1] = gt_;         \
     }
-// trace mode only: wait (all threads) until every valid row of the blocks [buf, buf + KS blocks) has arrived, so that the
-// stamp that follows separates "waiting for the exchange" from "computing"
-#define D3_PREPOLL(buf, KS)                                             \
-    if (tracing) {                                                      \
-        prepoll3(buf, KS, R, tid, g);                                   \
-        __syncthreads();                                                \
-    }
+// wait (all threads) until every valid row of the blocks [buf, buf + KS blocks) has arrived, so that the stamp that follows
+// separates "waiting for the exchange" from "computing"
+#define D3_PREPOLL(buf, KS)
+#else
+#define D3_TR(i)
+#define D3_PREPOLL(buf, KS)
+#endif
 
+// Stop-token projection (StopProjection, Decoder.py:404-410; batch-global decision of TacoTestHelper.next_inputs, Helpers.py:36-59):
+// y = [h2raw ; context] . Ws[1024 x 2] + bs, K-split over the cluster so that no CTA carries it on the critical path.
+// Part 1 (one warp of EVERY CTA, in the shadow of the dense_1 exchange of the following step): the 4 k-steps this CTA produced itself
+// (its 16 h2raw units, its 48 context columns) as one m16 tile whose rows 0..1 are the two stop units -> 32 partial sums
+// [unit][cluster row] stored to the global exchange slot of (cluster, step parity, rank).
+__device__ __forceinline__ void dec3_stop_partial(const Dec3Params& p, int s_idx, int cid, int rank, int lane, Guard3& g) {
+    float acc[2][4] = {};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int ks = i == 0 ? rank : 16 + 3 * rank + (i - 1);
+        const uint4 a = __ldg(p.stop_tiles + (size_t)ks * 32 + lane);
+        const uint32_t* blk = i == 0 ? SMU(SO_H2R) + rank * TILE_W : SMU(SO_CTX) + (3 * rank + i - 1) * TILE_W;
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+            const uint2 b = load_b(blk, j, lane, g);
+            mma16816(acc[j], a, b);
+        }
+    }
+    const int gq = lane >> 2, tq = lane & 3;
+    if (gq < 2) {
+        float* dst = p.stop_part + ((((size_t)cid * 2 + (s_idx & 1)) * CS + rank) * 32) + gq * 16 + 2 * tq;
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+            stg_relaxed(reinterpret_cast<uint32_t*>(dst + 8 * j), __float_as_uint(acc[j][0]));
+            stg_relaxed(reinterpret_cast<uint32_t*>(dst + 8 * j + 1), __float_as_uint(acc[j][1]));
+        }
+    }
+}
+// Part 2 (warp 0 of the stop rank, one step later: the partials have long arrived): lane = 2 * cluster row + unit sums the 16
+// partials in rank order, applies the sigmoid, writes the stop token and publishes the cluster's stop bit of that step.
+__device__ __forceinline__ void dec3_stop_finish(const Dec3Params& p, int s_idx, int row0, int R, int cid, bool free_run, int lane, Guard3& g) {
+    const int er = lane >> 1, eu = lane & 1;
+    uint32_t* src = reinterpret_cast<uint32_t*>(p.stop_part) + (((size_t)cid * 2 + (s_idx & 1)) * CS) * 32 + eu * 16 + er;
+    float y = p.stop_bias[eu];
+    bool fin = false;
+    if (er < R) {
+#pragma unroll 4
+        for (int k = 0; k < CS; ++k) {
+            uint32_t w = ldg_relaxed(src + k * 32);
+            int spins = 0;
+            while (w == SENT && !spin_check3(g, spins)) w = ldg_relaxed(src + k * 32);
+            y += __uint_as_float(w);
+        }
+        const float sg = sigmoidf_(y);
+        p.stop[(size_t)(row0 + er) * p.S_cap * 2 + (size_t)s_idx * 2 + eu] = p.stop_sigmoid ? sg : y;
+        fin = sg > 0.5f;   // tf.round(sigmoid) == 1 <=> sigmoid > 0.5 (half-to-even; Helpers.py:40)
+    }
+#pragma unroll 4
+    for (int k = 0; k < CS; ++k) stg_relaxed(src + k * 32, SENT);   // re-arm the slot for step s_idx + 2 (rows >= R too: harmless)
+    const int cnt = __popc(__ballot_sync(0xffffffffu, fin));
+    if (free_run && lane == 0)
+        stg_relaxed(reinterpret_cast<uint32_t*>(p.flags) + (size_t)s_idx * p.NCL + cid, (p.stop_at_any ? cnt > 0 : cnt == 2 * R) ? 2u : 1u);
+}
+
+#ifndef D3_DIST_STOP
 // Stop-token projection of launch step s_idx for the rows of this cluster (StopProjection, Decoder.py:404-410; the batch-global
 // decision of TacoTestHelper.next_inputs, Helpers.py:36-59): [h2raw ; context] . Ws[1024 x 2] as 64 k-steps of one m16 tile whose
 // rows 0..1 are the two stop units.  Runs on ONE rank per cluster, off the critical path; its tiles stream from L2.
@@ -68,20 +125,7 @@ __device__ __noinline__ void dec3_stop_token(const Dec3Params& p, int s_idx, int
         stg_relaxed(reinterpret_cast<uint32_t*>(p.flags) + (size_t)s_idx * p.NCL + cid, (p.stop_at_any ? cnt > 0 : cnt == 2 * R) ? 2u : 1u);
 }
 
-__device__ __noinline__ void prepoll3(const uint32_t* buf, int KS, int R, int tid, Guard3& g) {
-    for (int i = tid; i < KS * (TILE_W / 4); i += NT) {
-        const int v = i & 31;
-        const int row = ((v >> 4) << 3) + ((v & 15) >> 1);
-        if (row >= R) continue;
-        int spins = 0;
-        while (true) {
-            const uint4 w = lds_poll_v4(buf + 4 * i);
-            if (!(w.x == SENT || w.y == SENT || w.z == SENT || w.w == SENT)) break;
-            if (spin_check3(g, spins)) break;
-        }
-    }
-}
-
+#endif
 // fill one activation buffer from a row-major fp32 state array [B][width] (rows row0 .. row0+R-1 of this cluster)
 __device__ __forceinline__ void fill_from_state(uint32_t* buf, const float* state, int width, int row0, int R, int tid) {
     const int pairs = width >> 1;
@@ -100,7 +144,7 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
     const int cid = blockIdx.x / CS;
     const int row0 = cid * p.R;
     const int R = min(p.R, p.B - row0);
-    Guard3 g{p.abort_flag, false};
+    Guard3 g{p.abort_flag, (p.dbg & 512) != 0};   // dbg 512: no CTA ever waits (pure local instruction time per step; results are garbage)
     const bool free_run = p.mode == TACO_MODE_FREE;
     const float zo = p.zoneout;
 
@@ -115,8 +159,8 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
         }
         for (int i = tid; i < T_MAX3 + 48; i += NT) SMF(SO_CPAD)[i] = 0.f;
         if (tid < 16 + 48) SMU(SO_FLAG)[tid] = 0;
-        rearm(SMU(SO_P1), 6 * KS_H + KS_CTX, R, tid);   // all activation buffers are contiguous
-        for (int i = tid; i < CS * ATT; i += NT) SMU(SO_QRECV)[i] = SENT;
+        zero_blocks(SMU(SO_P1), 6 * KS_H + KS_CTX, tid);   // all activation buffers are contiguous
+        if (tid < N_MB) mbar_init(smem_addr(SMU(SO_MBAR) + 2 * tid), 1);
     }
     __syncthreads();
     // recurrent state of step t0-1 (zeros after reset): context, zoned h1 / h2, next decoder input
@@ -153,7 +197,6 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
         SMU(SO_OWN)[tid] = tid < R ? (pos < STOP_RANK ? pos : (pos < CS - 1 ? pos + 1 : STOP_RANK)) : 0xFFFFu;
         SMU(SO_LEN)[tid] = tid < R ? (uint32_t)p.lens[row0 + tid] : 0u;
     }
-    for (int i = tid; i < (R * p.TP) >> 2; i += NT) reinterpret_cast<uint4*>(SMU(SO_AALL))[i] = make_uint4(SENT, SENT, SENT, SENT);
     __syncthreads();
     if (tid == 0) {   // thread groups of the context-slice reduction, dealt in proportion to the row lengths
         int total = 0, g0 = 0;
@@ -164,8 +207,15 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
             SMU(SO_GRP)[2 * r2 + 1] = ng;
             g0 += ng;
         }
+        // bytes one decoder step delivers into this CTA's alignment rows: every owner multicasts ceil(len / 4) 16-byte pieces
+        uint32_t ab_ = 0u;
+        for (int r2 = 0; r2 < R; ++r2) ab_ += ((SMU(SO_LEN)[r2] + 3u) >> 2) * 16u;
+        SMU(SO_MBAR)[2 * N_MB] = ab_;
     }
     __syncthreads();
+    // expected bytes per step and exchange buffer (st.async completes them on the buffer's mbarrier)
+    const uint32_t BLK_BYTES = (uint32_t)CS * R * 32u, CTX_BYTES = 3u * BLK_BYTES, Q_BYTES = (uint32_t)CS * ATT * 4u;
+    const uint32_t A_BYTES = SMU(SO_MBAR)[2 * N_MB];
     uint32_t cmw = 0u;
     if (tid < 6 * CTX_GROUPS) {
         const int gidx = tid / 6;
@@ -212,6 +262,13 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
             }
         }
     }
+    if (tid == 0) {   // arm the first phase of every exchange buffer
+        for (int mb = MB_P1; mb <= MB_H2Z; ++mb) mbar_rearm(mb, BLK_BYTES);
+        mbar_rearm(MB_CTX, CTX_BYTES);
+        if (att) mbar_rearm(MB_Q, Q_BYTES);
+        mbar_rearm(MB_A, A_BYTES);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
     // every CTA of the cluster has armed its buffers before any peer may write into them
     cluster.sync();
 
@@ -254,7 +311,11 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
 
     for (int s = 0; s < p.S_max; ++s) {
         const int step = p.t0 + s;
+#ifdef TACO_DEC3_TRACE_BUILD
         const bool tracing = p.trace != nullptr && s == p.trace_step;
+#else
+        constexpr bool tracing = false;
+#endif
         D3_TR(0)
         // ---- batch-global stop (Helpers.py:51-52), evaluated STOP_LAG steps late so that clusters never wait for each other; speculative steps are discarded ----
         // Warp 15, lane i handles the word of cluster i.
@@ -279,6 +340,15 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
         //   relu(([h2raw;ctx].Wo[:,80:160] + bo[80:160]).Wp1 + bp1) = relu([h2raw;ctx].(Wo[:,80:160].Wp1) + (bo[80:160].Wp1 + bp1))
         // -- the feedback frame is never materialised, so the step has no projection phase and no frame exchange.
         const bool folded = free_run && step > 0;
+        const uint32_t par = (uint32_t)(s & 1), par_prev = par ^ 1u;
+        if (s > 0) {   // raw LSTM-2 output and context of step s-1 (every mode: the stop token and the next gates read them)
+            mbar_wait(MB_H2R, par_prev, g);
+            mbar_wait(MB_CTX, par_prev, g);
+            if (tid == 0 && !g.dead) {
+                mbar_rearm(MB_H2R, BLK_BYTES);
+                mbar_rearm(MB_CTX, CTX_BYTES);
+            }
+        }
         {
             float acc[2][4] = {};
             if (folded) {
@@ -337,7 +407,7 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
             D3_TR(4)
             __syncthreads();
             D3_TR(5)
-            multicast_block(SMU(SO_STG_R), SMU(SO_P1), rank, R, tid);
+            multicast_block(SMU(SO_STG_R), SMU(SO_P1), MB_P1, rank, R, tid);
             D3_STAMP(1)
             D3_TR(6)
         }
@@ -350,23 +420,31 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
             }
             D3_STAMP(11)
             D3_TR(7)
-            // stop token of step s-1 (Decoder.py:404-410; Helpers.py:36-59)
-            if (rank == STOP_RANK && !(p.dbg & 4)) dec3_stop_token(p, s - 1, row0, R, cid, free_run, red, tid, warp, lane, g);
-            if (rank == STOP_RANK && (p.dbg & 4) && free_run && tid == 0) stg_relaxed(reinterpret_cast<uint32_t*>(p.flags) + (size_t)(s - 1) * p.NCL + cid, 1u);
+            // stop token (Decoder.py:404-410; Helpers.py:36-59): this CTA's K-slice of step s-1; the stop rank finishes step s-2
+#ifndef D3_DIST_STOP
+            if (rank == STOP_RANK) dec3_stop_token(p, s - 1, row0, R, cid, free_run, red, tid, warp, lane, g);
+#else
+            if (!(p.dbg & 4)) {
+                if (warp == 15) dec3_stop_partial(p, s - 1, cid, rank, lane, g);
+                if (rank == STOP_RANK && warp == 0 && s >= 2) dec3_stop_finish(p, s - 2, row0, R, cid, free_run, lane, g);
+            } else if (rank == STOP_RANK && free_run && tid == 0 && s >= 2) {
+                stg_relaxed(reinterpret_cast<uint32_t*>(p.flags) + (size_t)(s - 2) * p.NCL + cid, 1u);
+            }
+#endif
             D3_STAMP(12)
             D3_TR(8)
         }
         uint4 aW1P[4];
         prefetch4(aW1P, sW1P, kg, lane);   // used two exchanges later (L1)
         __syncthreads();   // every reader of the context / h2raw blocks of step s-1 is done
-        rearm(SMU(SO_CTX), KS_CTX, R, tid);
-        rearm(SMU(SO_H1Z), 3 * KS_H, R, tid);   // H1Z, H2R, H2Z are contiguous
         D3_TR(9)
         D3_PREPOLL(SMU(SO_P1), KS_H)
         D3_TR(10)
         // ================= P2: prenet dense_2 =================
         {
             float acc[2][4] = {};
+            mbar_wait(MB_P1, par, g);
+            if (tid == 0 && !g.dead) mbar_rearm(MB_P1, BLK_BYTES);
             gemm_smem4(acc, SMU(SO_WP2), SMU(SO_P1), KS_H, warp, 16, lane, g);
             store_red3(red, acc, warp, lane, 2);
             D3_STAMP(2)
@@ -382,11 +460,10 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
                 const float zn = __shfl_down_sync(0xffffffffu, z, 1);
                 if (!(eu & 1)) SMU(SO_STG_R)[bword(er, eu >> 1)] = pack_bf16x2(z, zn);
             }
-            rearm(SMU(SO_P1), KS_H, R, tid);
             D3_TR(13)
             __syncthreads();
             D3_TR(14)
-            multicast_block(SMU(SO_STG_R), SMU(SO_P2), rank, R, tid);
+            multicast_block(SMU(SO_STG_R), SMU(SO_P2), MB_P2, rank, R, tid);
             D3_STAMP(3)
             D3_TR(15)
         }
@@ -400,6 +477,8 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
         D3_TR(17)
         // ================= L1: decoder LSTM layer 1 (Decoder.py:256; Encoder.py:118-142) =================
         {
+            mbar_wait(MB_P2, par, g);
+            if (tid == 0 && !g.dead) mbar_rearm(MB_P2, BLK_BYTES);
             gemm_regs(acc1, aW1P, SMU(SO_P2), kg, lane, g);
             uint4 aW2H[4];
             prefetch4(aW2H, sW2H, kg, lane);   // in flight during the LSTM-1 epilogue and the h1 exchange
@@ -434,12 +513,11 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
                     SMU(SO_STG_Z)[bword(er, eu >> 1)] = pack_bf16x2(h1s, hz1);
                 }
             }
-            rearm(SMU(SO_P2), KS_H, R, tid);
             D3_TR(20)
             __syncthreads();
             D3_TR(21)
-            multicast_block(SMU(SO_STG_R), SMU(SO_H1R), rank, R, tid);
-            multicast_block(SMU(SO_STG_Z), SMU(SO_H1Z), rank, R, tid);
+            multicast_block(SMU(SO_STG_R), SMU(SO_H1R), MB_H1R, rank, R, tid);
+            multicast_block(SMU(SO_STG_Z), SMU(SO_H1Z), MB_H1Z, rank, R, tid);
             D3_STAMP(5)
             D3_TR(22)
             // ---- shadow of the h1 exchange: second half of the location term ----
@@ -451,6 +529,8 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
             D3_PREPOLL(SMU(SO_H1R), KS_H)
             D3_TR(24)
         // ================= L2: decoder LSTM layer 2 =================
+            mbar_wait(MB_H1R, par, g);
+            if (tid == 0 && !g.dead) mbar_rearm(MB_H1R, BLK_BYTES);
             gemm_regs(acc2, aW2H, SMU(SO_H1R), kg, lane, g);
         }
         uint4 aW1H[4];
@@ -490,7 +570,6 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
                     if (evalid) p.act_hist[((size_t)s * p.B + eb) * (ACT_W / 2) + 8 * rank + (eu >> 1)] = hw;
                 }
             }
-            rearm(SMU(SO_H1R), KS_H, R, tid);
             D3_TR(27)
             __syncthreads();
             D3_TR(28)
@@ -517,11 +596,12 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
                 const int row = tid >> 5, v = tid & 31;
                 if (row < R) {
                     const uint4 val = *reinterpret_cast<const uint4*>(red + row * ATT + (v << 2));
-                    st_remote_v4(mapa_rank(smem_addr(SMU(SO_QRECV) + rank * ATT + (v << 2)), SMU(SO_OWN)[row]), val);
+                    const uint32_t own = SMU(SO_OWN)[row];
+                    st_async_v4(mapa_rank(smem_addr(SMU(SO_QRECV) + rank * ATT + (v << 2)), own), val, mapa_rank(smem_addr(SMU(SO_MBAR) + 2 * MB_Q), own));
                 }
             }
-            multicast_block(SMU(SO_STG_R), SMU(SO_H2R), rank, R, tid);
-            multicast_block(SMU(SO_STG_Z), SMU(SO_H2Z), rank, R, tid);
+            multicast_block(SMU(SO_STG_R), SMU(SO_H2R), MB_H2R, rank, R, tid);
+            multicast_block(SMU(SO_STG_Z), SMU(SO_H2Z), MB_H2Z, rank, R, tid);
             D3_STAMP(7)
             D3_TR(31)
         }
@@ -534,6 +614,12 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
         D3_PREPOLL(SMU(SO_H1Z), KS_H)
         D3_PREPOLL(SMU(SO_H2Z), KS_H)
         D3_TR(32)
+        mbar_wait(MB_H1Z, par, g);
+        mbar_wait(MB_H2Z, par, g);
+        if (tid == 0 && !g.dead) {
+            mbar_rearm(MB_H1Z, BLK_BYTES);
+            mbar_rearm(MB_H2Z, BLK_BYTES);
+        }
         if (!(p.dbg & 16)) {
         gemm_regs(acc1, aW1H, SMU(SO_H1Z), kg, lane, g);
         gemm_regs(acc2, aW2Z, SMU(SO_H2Z), kg, lane, g);
@@ -542,8 +628,8 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
         D3_TR(33)
         // ================= ATT: location-sensitive attention =================
         // owner of a cluster row: query, energies, softmax, alignment row -> every CTA; then every CTA: its 48 context columns
-        if (att) att3_owner(p, preR, pre_scr, ab, alen, arow, s, tid, warp, lane, g, tacc, tprev, timing, tracing);
-        att3_context_slice(p, cmw, row0, R, rank, s, tid, g, tracing);
+        if (att) att3_owner(p, preR, pre_scr, ab, alen, arow, s, tid, warp, lane, g, tacc, tprev, timing, tracing, Q_BYTES);
+        att3_context_slice(p, cmw, row0, R, rank, s, tid, g, tracing, A_BYTES);
         D3_STAMP(17)
         __syncthreads();
         D3_TR(47)   // red / staging readers of this step are done before the next step's writers
@@ -552,7 +638,15 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
     // what the next iteration would have done for the last executed step: its stop token (the context and h2raw blocks are
     // still in place) and the location term of the following step (saved below for a continuation launch)
     if (!stopped && s_done > 0) {
+#ifndef D3_DIST_STOP
         if (rank == STOP_RANK) dec3_stop_token(p, s_done - 1, row0, R, cid, free_run, red, tid, warp, lane, g);
+#else
+        if (warp == 15) dec3_stop_partial(p, s_done - 1, cid, rank, lane, g);
+        if (rank == STOP_RANK && warp == 0) {
+            if (s_done >= 2) dec3_stop_finish(p, s_done - 2, row0, R, cid, free_run, lane, g);
+            dec3_stop_finish(p, s_done - 1, row0, R, cid, free_run, lane, g);   // polls for the partials sent just above
+        }
+#endif
         if (att) att3_loc_chunk(p, preR, pre_scr, ab, alen, warp, lane, 0, 8);
     }
 

@@ -95,7 +95,7 @@ cudaError_t taco_launch_f32_to_bf16(const float* in, void* out, size_t n, cudaSt
 #define TACO_DEC3_TMAX 512
 #define TACO_DEC3_RES_WORDS (221 * 128 + 176)
 #define TACO_DEC3_STREAM_TILES 320
-#define TACO_DEC3_ACAP 1472   // shared-memory words for the alignment rows of one cluster: rows per cluster * round_up(T, 4) <= this
+#define TACO_DEC3_ACAP 1440   // shared-memory words for the alignment rows of one cluster: rows per cluster * round_up(T, 4) <= this
 
 struct Dec3Params {
     int B, T, NCL, R;       // NCL clusters; cluster i owns batch rows [i*R, min(B, i*R + R))
@@ -109,6 +109,7 @@ struct Dec3Params {
     const uint32_t* res_blobs;   // [16 ranks][TACO_DEC3_RES_WORDS] A-fragment tiles resident in shared memory + fp32 biases
     const uint4* stream_blobs;   // [16 ranks][320 tiles][32 lanes] A-fragment tiles streamed from L2: W1c [4][48], W1h [4][16], W2z [4][16]
     const uint4* stop_tiles;     // [64 k-steps][32 lanes] A-fragment tiles of the stop projection (rows 0..1 of the m16 tile)
+    float* stop_part;            // [NCL][2 step parities][16 ranks][2 units x 16 rows] K-split partial sums of the stop projection (all-ones bits = empty)
     float stop_bias[2];
     const uint32_t *g_hi, *g_lo; // G = conv31 . Wl, B-fragment-major [2 ks][16 nt][32 lanes][2], hi / lo bf16 split
     const float *va, *bconst;    // [128] attention_variable; attention_bias + conv_bias . Wl
