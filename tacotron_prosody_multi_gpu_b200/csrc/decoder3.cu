@@ -78,7 +78,8 @@ constexpr int SO_LEN = SO_OWN + 16;              // [16]: memory length of clust
 constexpr int SO_GRP = SO_LEN + 16;              // [16][2]: first thread group / number of groups of row i in the context-slice reduction
 constexpr int SO_MBAR = SO_GRP + 32;             // 9 mbarriers (64-bit each): one per exchange buffer, one phase per decoder step
 constexpr int MB_P1 = 0, MB_P2 = 1, MB_H1R = 2, MB_H1Z = 3, MB_H2R = 4, MB_H2Z = 5, MB_CTX = 6, MB_Q = 7, MB_A = 8, N_MB = 9;
-constexpr int SO_AALL = SO_MBAR + 2 * N_MB + 2;  // [R][TP] alignment rows of every cluster row, multicast by their owners
+constexpr int SO_KEEP = SO_MBAR + 2 * N_MB + 2;  // [2 prenet layers][16 rows]: 16 dropout keep bits (this CTA's units) of the step about to run
+constexpr int SO_AALL = SO_KEEP + 32;  // [R][TP] alignment rows of every cluster row, multicast by their owners
 constexpr int A_CAP = TACO_DEC3_ACAP;            // words: R * TP <= A_CAP (the host picks the cluster count accordingly)
 constexpr int SMEM3_WORDS = SO_AALL + A_CAP;
 static_assert(RES_WORDS == TACO_DEC3_RES_WORDS, "resident blob size");
@@ -347,6 +348,21 @@ __device__ __forceinline__ void multicast_block(const uint32_t* stage, uint32_t*
 }
 
 // Philox4x32-10 as in common.cuh (same counter / key layout, restated in oracle/philox.py), rolled and out of line
+// one Philox block = the keep bits of 128 consecutive units of (step, row, layer)
+__device__ __forceinline__ uint4 philox_block3(uint64_t seed, uint32_t step, uint32_t row, uint32_t layer, uint32_t blk) {
+    const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
+    uint4 c = make_uint4(step, row, layer, blk);
+    uint2 k = make_uint2((uint32_t)seed, (uint32_t)(seed >> 32));
+#pragma unroll 1
+    for (int i = 0; i < 10; ++i) {
+        const uint32_t hi0 = __umulhi(M0, c.x), lo0 = M0 * c.x;
+        const uint32_t hi1 = __umulhi(M1, c.z), lo1 = M1 * c.z;
+        c = make_uint4(hi1 ^ c.y ^ k.x, lo1, hi0 ^ c.w ^ k.y, lo0);
+        k.x += W0;
+        k.y += W1;
+    }
+    return c;
+}
 __device__ __forceinline__ bool philox_keep3(uint64_t seed, uint32_t step, uint32_t row, uint32_t layer, uint32_t unit) {
     const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
     uint4 c = make_uint4(step, row, layer, unit >> 7);

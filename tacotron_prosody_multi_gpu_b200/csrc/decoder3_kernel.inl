@@ -126,6 +126,17 @@ __device__ __noinline__ void dec3_stop_token(const Dec3Params& p, int s_idx, int
 }
 
 #endif
+// Prenet dropout bits (always on, Decoder.py:350-351) of `step` for this CTA's 16 units of both layers and every cluster row:
+// ONE Philox block per (row, layer) -- thread i < 2R: row i >> 1, layer i & 1 -- instead of one per (row, layer, unit).
+__device__ __forceinline__ void keep_bits_step(const Dec3Params& p, int step, int row0, int R, int rank, int tid) {
+    if (p.masks || tid >= 2 * R) return;
+    const int row = tid >> 1, layer = tid & 1;
+    const uint4 c = philox_block3(p.seed, (uint32_t)step, (uint32_t)(row0 + row), (uint32_t)layer, (uint32_t)(rank >> 3));
+    const int wi = (rank & 7) >> 1;
+    const uint32_t w = wi == 0 ? c.x : (wi == 1 ? c.y : (wi == 2 ? c.z : c.w));
+    SMU(SO_KEEP)[layer * 16 + row] = (w >> (16 * (rank & 1))) & 0xFFFFu;
+}
+
 // fill one activation buffer from a row-major fp32 state array [B][width] (rows row0 .. row0+R-1 of this cluster)
 __device__ __forceinline__ void fill_from_state(uint32_t* buf, const float* state, int width, int row0, int R, int tid) {
     const int pairs = width >> 1;
@@ -306,8 +317,13 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
     bool stopped = false;
     // prenet dropout bits (always on, Decoder.py:350-351) of the step about to run; those of step s + 1 are drawn while step s
     // waits for its attention
-    bool keep0 = evalid && keep_bit3(p, p.t0, eb, 0, 16 * rank + eu);
-    bool keep1 = evalid && keep_bit3(p, p.t0, eb, 1, 16 * rank + eu);
+    bool keep0 = false, keep1 = false;
+    if (p.masks) {
+        keep0 = evalid && keep_bit3(p, p.t0, eb, 0, 16 * rank + eu);
+        keep1 = evalid && keep_bit3(p, p.t0, eb, 1, 16 * rank + eu);
+    } else {
+        keep_bits_step(p, p.t0, row0, R, rank, tid);   // read after the barrier that precedes the first epilogue
+    }
 
     for (int s = 0; s < p.S_max; ++s) {
         const int step = p.t0 + s;
@@ -400,6 +416,10 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
                     }
                 }
                 z = fmaxf(z, 0.f);
+                if (!p.masks) {
+                    keep0 = evalid && ((SMU(SO_KEEP)[er] >> eu) & 1u);
+                    keep1 = evalid && ((SMU(SO_KEEP)[16 + er] >> eu) & 1u);
+                }
                 z = keep0 ? z * p.keep_scale : 0.f;
                 const float zn = __shfl_down_sync(0xffffffffu, z, 1);
                 if (!(eu & 1)) SMU(SO_STG_R)[bword(er, eu >> 1)] = pack_bf16x2(z, zn);
@@ -436,7 +456,9 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
         }
         uint4 aW1P[4];
         prefetch4(aW1P, sW1P, kg, lane);   // used two exchanges later (L1)
-        __syncthreads();   // every reader of the context / h2raw blocks of step s-1 is done
+#ifndef D3_DIST_STOP
+        if (rank == STOP_RANK && s > 0) __syncthreads();   // the stop token's reduction scratch is reused by dense_2 (CTA-uniform branch)
+#endif
         D3_TR(9)
         D3_PREPOLL(SMU(SO_P1), KS_H)
         D3_TR(10)
@@ -608,8 +630,16 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
         uint4 aW2Z[4];
         prefetch4(aW2Z, sW2Z, kg, lane);
         // dropout bits of the next step
-        keep0 = evalid && keep_bit3(p, step + 1, eb, 0, 16 * rank + eu);
-        keep1 = evalid && keep_bit3(p, step + 1, eb, 1, 16 * rank + eu);
+        if (p.masks) {
+            keep0 = evalid && keep_bit3(p, step + 1, eb, 0, 16 * rank + eu);
+            keep1 = evalid && keep_bit3(p, step + 1, eb, 1, 16 * rank + eu);
+        } else {
+            keep_bits_step(p, step + 1, row0, R, rank, tid);   // both layers' bits of this step were read in the dense_1 epilogue
+        }
+#ifdef D3_OWNER_FIRST
+        // the owners' alignment rows are what every other CTA waits for: before the zoned-state contributions
+        if (att) att3_owner(p, preR, pre_scr, ab, alen, arow, s, tid, warp, lane, g, tacc, tprev, timing, tracing, Q_BYTES);
+#endif
         // ---- zoned states of this step -> gates of the next step (in the shadow of the query exchange) ----
         D3_PREPOLL(SMU(SO_H1Z), KS_H)
         D3_PREPOLL(SMU(SO_H2Z), KS_H)
@@ -628,11 +658,12 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
         D3_TR(33)
         // ================= ATT: location-sensitive attention =================
         // owner of a cluster row: query, energies, softmax, alignment row -> every CTA; then every CTA: its 48 context columns
+#ifndef D3_OWNER_FIRST
         if (att) att3_owner(p, preR, pre_scr, ab, alen, arow, s, tid, warp, lane, g, tacc, tprev, timing, tracing, Q_BYTES);
+#endif
         att3_context_slice(p, cmw, row0, R, rank, s, tid, g, tracing, A_BYTES);
         D3_STAMP(17)
-        __syncthreads();
-        D3_TR(47)   // red / staging readers of this step are done before the next step's writers
+        D3_TR(47)
         s_done = s + 1;
     }
     // what the next iteration would have done for the last executed step: its stop token (the context and h2raw blocks are

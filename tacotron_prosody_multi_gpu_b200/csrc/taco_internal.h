@@ -95,7 +95,7 @@ cudaError_t taco_launch_f32_to_bf16(const float* in, void* out, size_t n, cudaSt
 #define TACO_DEC3_TMAX 512
 #define TACO_DEC3_RES_WORDS (221 * 128 + 176)
 #define TACO_DEC3_STREAM_TILES 320
-#define TACO_DEC3_ACAP 1440   // shared-memory words for the alignment rows of one cluster: rows per cluster * round_up(T, 4) <= this
+#define TACO_DEC3_ACAP 1408   // shared-memory words for the alignment rows of one cluster: rows per cluster * round_up(T, 4) <= this
 
 struct Dec3Params {
     int B, T, NCL, R;       // NCL clusters; cluster i owns batch rows [i*R, min(B, i*R + R))
