@@ -71,8 +71,9 @@ struct TacoHandle {
     void* enc_xw_wt[2] = {};   // LSTM input projection kernel[0:C] of fw / bw, bf16 K-major
     void* keys_wt = nullptr;    // memory_layer kernel, bf16 K-major [128][768]
     float* dec_blob[2] = {};     // U = 2 (GN 128), U = 4 (GN 64)
-    // dataflow decoder (decoder2.cu): fragment-major bf16 shards and fused location kernel
-    uint32_t *dec2_blob = nullptr, *dec2_wq = nullptr, *dec2_ghi = nullptr, *dec2_glo = nullptr;
+    // fused location matrix of the cluster decoder (hi / lo bf16, B-fragment order)
+    uint32_t *dec2_ghi = nullptr, *dec2_glo = nullptr;
+    bool warned_dec_fallback = false;
     float* dec2_bconst = nullptr;
     // cluster decoder (decoder3.cu): per-rank resident A-fragment tiles + L2-streamed tiles
     uint32_t* dec3_res = nullptr;
@@ -82,7 +83,7 @@ struct TacoHandle {
     float* dec3_bo = nullptr;              // frame projection bias [160]
     float dec3_stop_bias[2] = {0.f, 0.f};
     int dec3_max_clusters = -1;  // cudaOccupancyMaxActiveClusters of decoder3_kernel (queried once)
-    int dec_kind = 0;            // which decoder kernel owns the running state (1 = decoder.cu, 2 = decoder2.cu)
+    int dec_kind = 0;            // which decoder kernel owns the running state (1 = decoder.cu fp32, 3 = decoder3.cu bf16 cluster kernel)
     float* bilstm_blob[2] = {};  // same two configs, [2 dir][GN][256*4U]
     // decoder running state
     int dec_t = 0, dec_B = 0, dec_T = 0, dec_RBP = 0, dec_GB = 0;
@@ -312,74 +313,18 @@ inline float bf16_round(float f) {
     return r;
 }
 
-// Shards for decoder2.cu: per CTA c (units 2c, 2c+1) the mma.sync m16n8k16 B-fragments of its 8 gate
-// columns / 2 prenet / 2 projection columns: word [ks][lane=4g+t][j] = bf16 pair
-// (W[16ks + 2t + 8j][n=g], W[16ks + 2t + 8j + 1][g]).
-int pack_decoder2(TacoHandle* h) {
-    const Weight *k1, *b1, *k2, *b2, *kp1, *bp1, *kp2, *bp2, *kq, *kf, *bf, *kst, *bst, *cw, *cb, *wl, *ba;
+// Fused location term of the cluster decoder (Attention.py:193-197): conv1d(k=31, 32 filters) followed by Dense(128, no bias) is
+// one [31 x 128] matrix G, split into hi/lo bf16 parts in mma B-fragment order; bconst = attention_bias + conv_bias . Wl.
+int pack_location(TacoHandle* h) {
+    const Weight *cw, *cb, *wl, *ba;
     int rc;
 #define NEED(var, name, ...) \
     if ((rc = need(h, name, {__VA_ARGS__}, &var))) return rc;
-    NEED(k1, std::string(DEC_LSTM1) + "/kernel", 1280, 1024)
-    NEED(b1, std::string(DEC_LSTM1) + "/bias", 1024)
-    NEED(k2, std::string(DEC_LSTM2) + "/kernel", 512, 1024)
-    NEED(b2, std::string(DEC_LSTM2) + "/bias", 1024)
-    NEED(kp1, fmt(PRENET, 1) + "/kernel", 80, 256)
-    NEED(bp1, fmt(PRENET, 1) + "/bias", 256)
-    NEED(kp2, fmt(PRENET, 2) + "/kernel", 256, 256)
-    NEED(bp2, fmt(PRENET, 2) + "/bias", 256)
-    NEED(kq, std::string(LSA) + "/query_layer/kernel", 256, 128)
-    NEED(kf, std::string(FRAME_PROJ) + "/kernel", 1024, 160)
-    NEED(bf, std::string(FRAME_PROJ) + "/bias", 160)
-    NEED(kst, std::string(STOP_PROJ) + "/kernel", 1024, 2)
-    NEED(bst, std::string(STOP_PROJ) + "/bias", 2)
     NEED(cw, std::string(LSA) + "/location_features_convolution/kernel", 31, 1, 32)
     NEED(cb, std::string(LSA) + "/location_features_convolution/bias", 32)
     NEED(wl, std::string(LSA) + "/location_features_layer/kernel", 32, 128)
     NEED(ba, std::string(LSA) + "/attention_bias", 128)
 #undef NEED
-    const int BW = TACO_DEC2_BLOB_WORDS;
-    std::vector<uint32_t> blob((size_t)TACO_DEC2_CTAS * BW, 0u);
-    // generic fragment packer: get(k, n) -> weight
-    auto pack_frag = [](uint32_t* dst, int KS, auto get) {
-        for (int ks = 0; ks < KS; ++ks)
-            for (int lane = 0; lane < 32; ++lane) {
-                const int g = lane >> 2, t = lane & 3;
-                for (int j = 0; j < 2; ++j) {
-                    const int k = ks * 16 + 2 * t + 8 * j;
-                    dst[(ks * 32 + lane) * 2 + j] = pack2(get(k, g), get(k + 1, g));
-                }
-            }
-    };
-    for (int c = 0; c < TACO_DEC2_CTAS; ++c) {
-        uint32_t* p = blob.data() + (size_t)c * BW;
-        auto gate_col = [c](int n) { return (n >> 1) * 256 + 2 * c + (n & 1); };  // n = gate*2 + unit
-        pack_frag(p, 80, [&](int k, int n) { return k1->host[(size_t)k * 1024 + gate_col(n)]; });
-        pack_frag(p + 80 * 64, 32, [&](int k, int n) { return k2->host[(size_t)k * 1024 + gate_col(n)]; });
-        pack_frag(p + 112 * 64, 5, [&](int k, int n) { return n < 2 ? kp1->host[(size_t)k * 256 + 2 * c + n] : 0.f; });
-        pack_frag(p + 117 * 64, 16, [&](int k, int n) { return n < 2 ? kp2->host[(size_t)k * 256 + 2 * c + n] : 0.f; });
-        pack_frag(p + 133 * 64, 64, [&](int k, int n) {
-            const int oc = 2 * c + n;
-            if (n >= 2 || oc >= 162) return 0.f;
-            return oc < 160 ? kf->host[(size_t)k * 160 + oc] : kst->host[(size_t)k * 2 + (oc - 160)];
-        });
-        float* bias = reinterpret_cast<float*>(p + 197 * 64);
-        for (int n = 0; n < 8; ++n) {
-            bias[n] = b1->host[gate_col(n)];
-            bias[8 + n] = b2->host[gate_col(n)];
-        }
-        for (int n = 0; n < 2; ++n) {
-            bias[16 + n] = bp1->host[2 * c + n];
-            bias[18 + n] = bp2->host[2 * c + n];
-            const int oc = 2 * c + n;
-            bias[20 + n] = oc < 160 ? bf->host[oc] : (oc < 162 ? bst->host[oc - 160] : 0.f);
-        }
-    }
-    if ((rc = upload_words(h, blob, &h->dec2_blob))) return rc;
-    std::vector<uint32_t> wq((size_t)256 * 64);
-    for (int k = 0; k < 256; ++k)
-        for (int j = 0; j < 64; ++j) wq[(size_t)k * 64 + j] = pack2(kq->host[(size_t)k * 128 + 2 * j], kq->host[(size_t)k * 128 + 2 * j + 1]);
-    if ((rc = upload_words(h, wq, &h->dec2_wq))) return rc;
     // G[k][d] = sum_c conv[k][c] Wl[c][d] (k < 31; row 31 = 0), hi/lo bf16 split, B-fragment-major [ks][nt][lane][2]
     std::vector<double> G((size_t)32 * 128, 0.0);
     for (int k = 0; k < 31; ++k)
@@ -574,110 +519,6 @@ int keys_tc(TacoHandle* h, const void* vals_bf16, float* keys, int B, int T, cud
     c.y_f32 = keys; c.out_f32_only = 1;
     CK(taco_launch_conv_tc(c, h->n_sm, st));
     h->launches++;
-    return TACO_OK;
-}
-
-// taco_decode through the dataflow kernel (decoder2.cu) -- TACO_PRECISION_BF16
-int decode_v2(TacoHandle* h, int mode, const float* memory, const int32_t* lens, int B, int T, const float* mel_targets,
-              int F_tgt, int S_max, const uint8_t* prenet_masks, uint64_t philox_seed, int reset_state, int logits_only,
-              float* frames, float* stop, float* align_hist, int32_t* steps_out, cudaStream_t st) {
-    const TacoHParams& hp = h->hp;
-    Dec2Params p;
-    memset(&p, 0, sizeof p);
-    p.B = B; p.T = T;
-    p.MT = B <= 16 ? 1 : (B <= 32 ? 2 : 4);
-    p.KG = 16 / p.MT;
-    static const int ns_opts[] = {96, 48, 32, 24, 16, 12, 8, 6, 4, 3, 2, 1};
-    p.NS = 1;
-    for (int ns : ns_opts)
-        if (B * ns <= TACO_DEC2_CTAS) { p.NS = ns; break; }
-    p.S_max = S_max; p.S_cap = S_max; p.mode = mode;
-    p.stop_at_any = hp.stop_at_any; p.cumulative = hp.cumulative_weights; p.smoothing = hp.smoothing;
-    p.stop_sigmoid = logits_only ? 0 : 1;
-    p.zoneout = hp.zoneout_rate;
-    p.keep_scale = 1.0f / (1.0f - hp.dropout_rate);
-    p.blobs = h->dec2_blob; p.wq = h->dec2_wq; p.g_hi = h->dec2_ghi; p.g_lo = h->dec2_glo;
-    p.va = dev_w(h, std::string(LSA) + "/attention_variable");
-    p.bconst = h->dec2_bconst;
-    if (!reset_state && (h->dec_kind != 2 || h->dec_B != B || h->dec_T != T))
-        FAIL(TACO_ERR_STATE, "taco_decode: continuing with a different batch shape or precision");
-    WS(lens_eff, int32_t, "dec_lens", B)
-    if (hp.mask_encoder) {
-        CK(cudaMemcpyAsync(lens_eff, lens, B * sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
-    } else {
-        std::vector<int32_t> full(B, T);
-        CK(cudaMemcpyAsync(lens_eff, full.data(), B * sizeof(int32_t), cudaMemcpyHostToDevice, st));
-        CK(cudaStreamSynchronize(st));
-    }
-    p.lens = lens_eff;
-    WS(keys, float, "dec_keys", (size_t)B * T * 128)
-    WS(vals, uint16_t, "dec2_values", (size_t)B * T * 768)
-    if (reset_state) {
-        // values as bf16 (the per-step stream), keys = values . W_mem on tcgen05 from the same bf16 copy
-        CK(taco_launch_f32_to_bf16(memory, vals, (size_t)B * T * 768, st));
-        h->launches++;
-        int rc = keys_tc(h, vals, keys, B, T, st);
-        if (rc) return rc;
-    }
-    p.keys = keys;
-    p.values = vals;
-    // rings
-    const size_t unit = (size_t)p.MT * 128 * 4;  // words per k-step, 4 slots
-    const size_t n_x = unit * 5, n_h = unit * 16, n_c = unit * 48;
-    WS(rings, uint32_t, "dec2_rings", n_x + 6 * n_h + n_c)
-    uint32_t* r = rings;
-    p.ring_x = r; r += n_x;
-    p.ring_p1 = r; r += n_h;
-    p.ring_p2 = r; r += n_h;
-    p.ring_h1raw = r; r += n_h;
-    p.ring_h1z = r; r += n_h;
-    p.ring_h2raw = r; r += n_h;
-    p.ring_h2z = r; r += n_h;
-    p.ring_ctx = r;
-    // recurrent state (fp32 row-major): c1 h1z c2 h2z [B][256], ctx [B][768], x [B][80], cum [B][T]
-    const size_t n_state = (size_t)B * (4 * 256 + 768 + 80 + T);
-    WS(state, float, "dec2_state", n_state)
-    if (reset_state) {
-        CK(cudaMemsetAsync(state, 0, n_state * sizeof(float), st));
-        h->dec_t = 0;
-    }
-    float* s = state;
-    p.c1 = s; s += (size_t)B * 256;
-    p.h1z = s; s += (size_t)B * 256;
-    p.c2 = s; s += (size_t)B * 256;
-    p.h2z = s; s += (size_t)B * 256;
-    p.ctx_state = s; s += (size_t)B * 768;
-    p.x_state = s; s += (size_t)B * 80;
-    p.cum = s;
-    int pre_in_smem = 0;
-    taco_decoder2_smem_bytes(T, &pre_in_smem);
-    p.pre_in_smem = pre_in_smem;
-    if (!pre_in_smem) {
-        WS(pre, float, "dec2_pre", (size_t)TACO_DEC2_CTAS * T * 128)
-        p.pre_scratch = pre;
-    }
-    p.t0 = h->dec_t;
-    p.targets = mel_targets; p.F_tgt = F_tgt;
-    p.masks = prenet_masks; p.seed = philox_seed;
-    p.frames = frames; p.stop = stop; p.hist = align_hist; p.steps_out = steps_out;
-    WS(flags, int, "dec2_flags", (size_t)S_max + 8)
-    CK(cudaMemsetAsync(flags, 0, ((size_t)S_max + 8) * sizeof(int), st));
-    p.flags = flags;
-    p.abort_flag = flags + S_max + 4;
-    if (getenv("TACO_DEC2_DBG")) p.dbg = atoi(getenv("TACO_DEC2_DBG"));
-    if (getenv("TACO_DEC2_TIMING")) {
-        WS(timing, long long, "dec2_timing", (size_t)TACO_DEC2_CTAS * 16)
-        p.timing = timing;
-    }
-    CK(taco_launch_decoder2_init(p, st));
-    h->launches++;
-    CK(cudaEventRecord(h->ev[TACO_STAGE_DECODER_KERNEL][0], st));
-    CK(taco_launch_decoder2(p, st));
-    CK(cudaEventRecord(h->ev[TACO_STAGE_DECODER_KERNEL][1], st));
-    h->ev_valid[TACO_STAGE_DECODER_KERNEL] = true;
-    h->launches++;
-    h->dec_t += S_max;
-    h->dec_B = B; h->dec_T = T; h->dec_kind = 2;
     return TACO_OK;
 }
 
@@ -916,7 +757,7 @@ int taco_finalize_weights(TacoHandle* h) {
     for (int i = 0; i < h->hp.n_reference_filters; ++i)
         if ((rc = fold_bn(h, fmt(REF_CONV, i), "conv2d", eps, &h->ref_scale[i], &h->ref_shift[i]))) return rc;
     if ((rc = pack_decoder_blobs(h))) return rc;
-    if ((rc = pack_decoder2(h))) return rc;
+    if ((rc = pack_location(h))) return rc;
     if ((rc = pack_decoder3(h))) return rc;
     const char* required[] = {"inputs_embedding", "style_tokens"};
     for (const char* r : required)
@@ -1148,15 +989,19 @@ int taco_decode(TacoHandle* h, int mode, const float* memory, const int32_t* len
         }
         h->dec3_max_clusters = n > TACO_DEC3_MAX_CLUSTERS ? TACO_DEC3_MAX_CLUSTERS : n;
     }
-    const char* force = getenv("TACO_DECODER");   // "2": dataflow kernel through L2 (decoder2.cu), kept for comparison
     const bool dec3_fits = h->dec3_max_clusters > 0 && T <= TACO_DEC3_TMAX && h->dec3_max_clusters * 16 >= B &&
                            ((B + h->dec3_max_clusters - 1) / h->dec3_max_clusters) * ((T + 3) & ~3) <= TACO_DEC3_ACAP;
-    if (h->precision == TACO_PRECISION_BF16 && dec3_fits && !(force && force[0] == '2'))
+    if (h->precision == TACO_PRECISION_BF16 && dec3_fits)
         return decode_v3(h, mode, memory, lens, B, T, mel_targets, F_tgt, S_max, prenet_masks, philox_seed, reset_state, logits_only,
                          frames, stop, align_hist, steps_out, st);
-    if (h->precision == TACO_PRECISION_BF16 && T <= TACO_DEC2_TMAX)
-        return decode_v2(h, mode, memory, lens, B, T, mel_targets, F_tgt, S_max, prenet_masks, philox_seed, reset_state, logits_only,
-                         frames, stop, align_hist, steps_out, st);
+    if (h->precision == TACO_PRECISION_BF16 && !h->warned_dec_fallback) {
+        // never silent: the bf16 cluster decoder holds the alignment rows of a cluster in shared memory (rows x T <= TACO_DEC3_ACAP
+        // words, T <= TACO_DEC3_TMAX, 16-CTA clusters schedulable); beyond that the exact fp32 kernel below decodes this batch
+        fprintf(stderr, "[taco_b200] taco_decode: B=%d T=%d does not fit the bf16 cluster decoder (T <= %d, rows per cluster x T <= %d, "
+                        "%d clusters): this batch runs on the fp32 persistent kernel (3x slower per step)\n",
+                B, T, TACO_DEC3_TMAX, TACO_DEC3_ACAP, h->dec3_max_clusters);
+        h->warned_dec_fallback = true;
+    }
 
     DecParams p;
     memset(&p, 0, sizeof p);
@@ -1365,7 +1210,7 @@ int taco_get_decoder_state(TacoHandle* h, int B, int T, float* c1, float* h1, fl
     if (h->dec_B != B || h->dec_T != T) FAIL(TACO_ERR_STATE, "taco_get_decoder_state: no decoder state of that shape");
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     CK(cudaSetDevice(h->device));
-    if (h->dec_kind == 2 || h->dec_kind == 3) {
+    if (h->dec_kind == 3) {
         auto it2 = h->ws.find("dec2_state");
         if (it2 == h->ws.end()) FAIL(TACO_ERR_STATE, "no decoder state");
         const float* s = reinterpret_cast<const float*>(it2->second.p);

@@ -3,7 +3,7 @@
 //
 // Computes TacotronDecoderCell.__call__ for every decoder step (reference Decoder.py:246-292;
 // CustomDecoder.step / helpers, Decoder.py:117-146, Utils/Helpers.py:36-59,115-128;
-// LocationSensitiveAttention, Attention.py:169-210,345-401) like decoder2.cu, but decomposed by what
+// LocationSensitiveAttention, Attention.py:169-210,345-401), decomposed by what
 // the measurements in tools/microbench_hop.cu say bounds a step on B200:
 //   one L2 hop (st.relaxed.gpu -> polled ld.relaxed.gpu)   0.45 us,  128-CTA all-gather through L2 1.6-2.2 us
 //   one DSMEM hop (st.shared::cluster -> local smem poll)   0.19 us,  16-CTA all-gather through DSMEM 0.5 us

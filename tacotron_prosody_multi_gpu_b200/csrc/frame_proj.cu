@@ -120,3 +120,19 @@ cudaError_t taco_launch_frame_projection(const uint32_t* act_hist, const uint32_
     frame_projection_kernel<<<(M + FP_BM - 1) / FP_BM, FP_THREADS, smem, stream>>>(act_hist, wo_t, bo, steps, S_max, B, S_cap, frames);
     return cudaGetLastError();
 }
+
+// fp32 -> bf16 copy of the attention values (the per-step stream of the cluster decoder), 4 elements per thread
+__global__ void f32_to_bf16_kernel(const float* __restrict__ in, uint2* __restrict__ out, size_t n4) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n4) return;
+    const float4 v = reinterpret_cast<const float4*>(in)[i];
+    __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
+    out[i] = make_uint2(*reinterpret_cast<uint32_t*>(&lo), *reinterpret_cast<uint32_t*>(&hi));
+}
+
+cudaError_t taco_launch_f32_to_bf16(const float* in, void* out, size_t n, cudaStream_t stream) {
+    if (n % 4 != 0) return cudaErrorInvalidValue;
+    const size_t n4 = n / 4;
+    f32_to_bf16_kernel<<<(unsigned)((n4 + 255) / 256), 256, 0, stream>>>(in, reinterpret_cast<uint2*>(out), n4);
+    return cudaGetLastError();
+}

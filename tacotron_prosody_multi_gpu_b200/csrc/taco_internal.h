@@ -45,49 +45,6 @@ cudaError_t taco_launch_decoder(const DecParams& p, cudaStream_t stream);
 cudaError_t taco_launch_transpose_alignments(const float* hist, float* out, int S, int B, int T, cudaStream_t stream);
 
 // ---------------------------------------------------------------------------------------------
-// decoder2.cu : dataflow persistent decoder (bf16 mma.sync contractions, sentinel rings in L2)
-// ---------------------------------------------------------------------------------------------
-#define TACO_DEC2_CTAS 128
-#define TACO_DEC2_TMAX 512
-#define TACO_DEC2_BLOB_WORDS (197 * 64 + 24)
-struct Dec2Params {
-    int B, T, MT, KG, NS;   // MT = M-tiles of 16 batch rows (1,2,4); KG = 16/MT; NS = context slices per row
-    int S_max, S_cap, t0, mode;
-    int stop_at_any, cumulative, smoothing, stop_sigmoid;
-    int pre_in_smem;        // pre[t][128] of this CTA's row lives in shared memory (else pre_scratch)
-    float zoneout, keep_scale;
-    const uint32_t* blobs;  // [128][TACO_DEC2_BLOB_WORDS] fragment-major bf16 weights + fp32 biases
-    const uint32_t* wq;     // query_layer kernel, bf16 pairs along d: [256][64]
-    const uint32_t *g_hi, *g_lo;  // G = conv31 . Wl, B-fragment-major [2 ks][16 nt][32 lanes][2], hi / lo bf16 split
-    const float *va, *bconst;     // [128] attention_variable; attention_bias + conv_bias . Wl
-    const uint16_t* values;       // bf16 [B][T][768]
-    const float* keys;            // fp32 [B][T][128]
-    const int* lens;
-    // rings: 4 slots x (16*MT rows x K) bf16 in A-fragment-major order
-    uint32_t *ring_x, *ring_p1, *ring_p2, *ring_h1raw, *ring_h1z, *ring_h2raw, *ring_h2z, *ring_ctx;
-    // recurrent state, fp32 row-major (TacotronDecoderCellState, Decoder.py:419-438)
-    float *c1, *h1z, *c2, *h2z;  // [B][256]
-    float* ctx_state;            // [B][768]
-    float* cum;                  // [B][T]
-    float* x_state;              // [B][80] next decoder input (free-running)
-    float* pre_scratch;          // [B*NS][T][128] when !pre_in_smem
-    const float* targets;
-    int F_tgt;
-    const uint8_t* masks;
-    uint64_t seed;
-    float *frames, *stop, *hist;
-    int* steps_out;
-    int* flags;       // [S_max + 1]: 0 not ready, 1 continue, 2 stop (free-running)
-    int* abort_flag;
-    int dbg;            // experiment bitmask (TACO_DEC2_DBG): 1 = no producer fence, 2 = nanosleep back-off in polls
-    long long* timing;  // optional [128][8] per-CTA stage nanoseconds (thread 0), or null
-};
-size_t taco_decoder2_smem_bytes(int T, int* pre_in_smem);
-cudaError_t taco_launch_decoder2_init(const Dec2Params& p, cudaStream_t stream);
-cudaError_t taco_launch_decoder2(const Dec2Params& p, cudaStream_t stream);
-cudaError_t taco_launch_f32_to_bf16(const float* in, void* out, size_t n, cudaStream_t stream);
-
-// ---------------------------------------------------------------------------------------------
 // decoder3.cu : cluster persistent decoder (16-CTA clusters, DSMEM exchanges, bf16 mma.sync contractions)
 // ---------------------------------------------------------------------------------------------
 #define TACO_DEC3_CLUSTER 16
@@ -140,6 +97,7 @@ size_t taco_decoder3_smem_bytes();
 cudaError_t taco_launch_frame_projection(const uint32_t* act_hist, const uint32_t* wo_t, const float* bo, const int* steps, int S_max, int B,
                                          int S_cap, float* frames, cudaStream_t stream);
 cudaError_t taco_decoder3_max_clusters(int* out);
+cudaError_t taco_launch_f32_to_bf16(const float* in, void* out, size_t n, cudaStream_t stream);   // frame_proj.cu; n % 4 == 0
 cudaError_t taco_launch_decoder3(const Dec3Params& p, cudaStream_t stream);
 
 // ---------------------------------------------------------------------------------------------

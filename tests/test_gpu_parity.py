@@ -214,7 +214,7 @@ def test_postnet_tcgen05_parity(ctx, B, F):
     eng.close()
 
 
-# ------------------------------------------------------------------ dataflow decoder (bf16 tensor-core contractions)
+# ------------------------------------------------------------------ cluster decoder, decoder3.cu (bf16 tensor-core contractions)
 # Tolerances of TACO_PRECISION_BF16 against the oracle that rounds the SAME operands to bf16 (dec_bf16=True):
 # remaining differences are fp32 accumulation order, tanh.approx in the energies (|err| <= 2^-10.99 per PTX ISA),
 # the hi/lo-split fused location contraction (~2^-16 relative) and bf16 re-rounding of near-tie activations.
@@ -235,7 +235,7 @@ def ctx2():
 
 
 @pytest.mark.parametrize("lengths", [[13], [20, 11, 16], [9] * 6 + [14] * 5, [10, 25] * 10, [12, 30, 7, 22] * 16])
-def test_decoder2_teacher_forced_parity(ctx2, lengths):
+def test_cluster_decoder_teacher_forced_parity(ctx2, lengths):
     """Covers MT = 1 / 1 / 1 / 2 / 4 M-tiles and NS = 96 / 32 / 8 / 6 / 2 context slices."""
     hp, w, eng, mir, orc = ctx2
     B = len(lengths)
@@ -253,7 +253,7 @@ def test_decoder2_teacher_forced_parity(ctx2, lengths):
                    prenet_masks=masks)
     assert d["steps"] == ref["steps"] == S
     al = _t(eng.alignments(d["align_hist"], S))
-    print("decoder2 B=%d: |frames-mirror|=%.2e |frames-fp32|=%.2e |mirror-fp32|=%.2e |align-mirror|=%.2e" % (
+    print("cluster decoder B=%d: |frames-mirror|=%.2e |frames-fp32|=%.2e |mirror-fp32|=%.2e |align-mirror|=%.2e" % (
         B, np.abs(_t(d["frames"]) - ref["frames_raw"].numpy()).max(), np.abs(_t(d["frames"]) - ref32["frames_raw"].numpy()).max(),
         np.abs(ref["frames_raw"].numpy() - ref32["frames_raw"].numpy()).max(), np.abs(al - ref["alignments"].numpy()).max()))
     np.testing.assert_allclose(_t(d["frames"]), ref["frames_raw"].numpy(), atol=ATOL_D2_FRAMES)
@@ -272,7 +272,7 @@ def test_decoder2_teacher_forced_parity(ctx2, lengths):
     np.testing.assert_allclose(_t(st["alignments"]), fs.alignments.numpy(), atol=5e-2)
 
 
-def test_decoder2_philox_equals_explicit_masks(ctx2):
+def test_cluster_decoder_philox_equals_explicit_masks(ctx2):
     hp, w, eng, _, _ = ctx2
     ids, lens = synthetic.token_batch(hp, [10, 8, 12])
     rng = np.random.default_rng(5)
@@ -284,7 +284,7 @@ def test_decoder2_philox_equals_explicit_masks(ctx2):
     assert torch.equal(a["frames"], b["frames"]) and torch.equal(a["align_hist"], b["align_hist"])
 
 
-def test_decoder2_cell_stepping_matches_one_launch(ctx2):
+def test_cluster_decoder_cell_stepping_matches_one_launch(ctx2):
     hp, w, eng, _, _ = ctx2
     ids, lens = synthetic.token_batch(hp, [10, 8])
     rng = np.random.default_rng(8)
@@ -298,7 +298,7 @@ def test_decoder2_cell_stepping_matches_one_launch(ctx2):
     assert torch.equal(torch.cat(frames, 1), whole["frames"])
 
 
-def test_decoder2_free_running_stop_step_bit_exact(ctx2):
+def test_cluster_decoder_free_running_stop_step_bit_exact(ctx2):
     """Batch-global stop: S and output lengths equal the bf16-mirroring oracle's exactly."""
     hp, _, _, _, _ = ctx2
     from tacotron_prosody_multi_gpu_b200.engine import TacoEngine
@@ -310,7 +310,7 @@ def test_decoder2_free_running_stop_step_bit_exact(ctx2):
     ref = mir.forward(ids, lens, gst_weights=gw, max_iters=40, philox_seed=99)
     eng = TacoEngine(hp, w, precision="bf16")
     out = eng.forward(torch.from_numpy(ids), torch.from_numpy(lens), gst_weights=gw, max_iters=40, philox_seed=99)
-    print("decoder2 free-run: S gpu=%d mirror=%d fp32-oracle=%d margin=%.3f" % (out["steps"], ref["steps"], S, margin))
+    print("cluster decoder free-run: S gpu=%d mirror=%d fp32-oracle=%d margin=%.3f" % (out["steps"], ref["steps"], S, margin))
     assert out["steps"] == ref["steps"]
     assert out["mel_outputs"].shape == (4, 2 * ref["steps"], 80)
     np.testing.assert_allclose(_t(out["mel_outputs"]), ref["mel_outputs"].numpy(), atol=5e-2)
@@ -383,3 +383,53 @@ def test_c5_long_form_reference_encoder(ctx2):
     assert mo.min() >= -4.1 - 1e-6 and mo.max() <= 4.0 + 1e-6
     out2 = eng.forward(torch.from_numpy(ids), torch.from_numpy(lens), reference_mel=torch.from_numpy(rm), max_iters=1000, philox_seed=5)
     assert torch.equal(out["frames_raw"], out2["frames_raw"])
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_smoothing_normalisation_ragged_batch(precision):
+    """hparams.smoothing=True (Attention.py:405-425): sigmoid(e) / sum sigmoid(e) with the TF 1.9 length mask applied BEFORE the
+    normalisation (_maybe_mask_score wraps every probability_fn): padded positions get exactly 0 on a ragged batch."""
+    from tacotron_prosody_multi_gpu_b200.engine import TacoEngine
+    hp = default_hparams()
+    hp.smoothing = True
+    w = weights.set_stop_bias(weights.init_weights(hp, perturb=0.05), -10.0)
+    lengths = [21, 9, 14, 21, 5, 17, 12, 3, 19, 11, 8]
+    ids, lens = synthetic.token_batch(hp, lengths)
+    B, T = ids.shape
+    memory = (np.random.default_rng(7).standard_normal((B, T, 768)) * 0.5).astype(np.float32)
+    mel, _, _ = synthetic.mel_targets(hp, np.full(B, T, np.int32), frames_per_token=2, max_frames=40)
+    S = mel.shape[1] // 2
+    bf = precision == "bf16"
+    with torch.no_grad():
+        ref = TacotronOracle(hp, w, conv_bf16=bf, dec_bf16=bf).decode(torch.from_numpy(memory), lens, mel_targets=mel, philox_seed=4)
+    eng = TacoEngine(hp, w, precision=precision)
+    d = eng.decode(torch.from_numpy(memory).cuda(), torch.from_numpy(lens), mel_targets=torch.from_numpy(mel), philox_seed=4)
+    assert d["steps"] == ref["steps"] == S
+    al = _t(eng.alignments(d["align_hist"], S))
+    np.testing.assert_allclose(al, ref["alignments"].numpy(), atol=ATOL_D2_ALIGN if bf else ATOL_ALIGN)
+    np.testing.assert_allclose(_t(d["frames"]), ref["frames_raw"].numpy(), atol=ATOL_D2_FRAMES if bf else ATOL_F32)
+    for b, n in enumerate(lens):
+        assert al[b, n:].max(initial=0.0) == 0.0
+    np.testing.assert_allclose(al.sum(1), 1.0, atol=1e-5)
+    eng.close()
+
+
+def test_bf16_mode_beyond_cluster_decoder_limits_is_exact_and_announced(capfd):
+    """T > 512 does not fit the bf16 cluster decoder: the batch is decoded by the fp32 persistent kernel (fp32 tolerances hold)
+    and the library says so on stderr -- never a silent change of kernel."""
+    from tacotron_prosody_multi_gpu_b200.engine import TacoEngine
+    hp = default_hparams()
+    w = weights.set_stop_bias(weights.init_weights(hp, perturb=0.05), -10.0)
+    ids, lens = synthetic.token_batch(hp, [530, 64])
+    B, T = ids.shape
+    memory = (np.random.default_rng(9).standard_normal((B, T, 768)) * 0.5).astype(np.float32)
+    S = 6
+    with torch.no_grad():
+        ref = TacotronOracle(hp, w).decode(torch.from_numpy(memory), lens, max_iters=S, philox_seed=4)
+    eng = TacoEngine(hp, w, precision="bf16")
+    d = eng.decode(torch.from_numpy(memory).cuda(), torch.from_numpy(lens), max_iters=S, philox_seed=4)
+    assert d["steps"] == S
+    np.testing.assert_allclose(_t(d["frames"]), ref["frames_raw"].numpy(), atol=ATOL_F32)
+    err = capfd.readouterr().err
+    assert "does not fit the bf16 cluster decoder" in err
+    eng.close()
