@@ -312,7 +312,8 @@ def extra_configs(args, hp, w, dev, rank, world, dist):
         dist.broadcast(bias_t, 0)
     bias = float(bias_t.item())
     pool = EnginePool(hp, weights.scale_stop_projection(w, 8.0, bias), device=local, precision="bf16", in_flight=args.in_flight)
-    sharding.synthesize_batches(pool, hp, seqs[:128], 0, 1, 64, gw, S_cap, seed)   # warm-up: two batches on every rank
+    longest = sorted(range(n_utt), key=lambda i: -len(seqs[i]))[:64 * max(2, args.in_flight)]
+    sharding.synthesize_batches(pool, hp, [seqs[i] for i in longest], 0, 1, 64, gw, S_cap, seed)   # warm-up: the largest batches on every engine
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()

@@ -36,8 +36,28 @@ class LocationSensitiveAttention(object):
     initial_state = initial_alignments
 
     def __call__(self, query, state):
-        raise FusedStageError("LocationSensitiveAttention.__call__ is fused into the persistent decoder kernel: "
-                              "call TacotronDecoderCell(...)(inputs, state) or dynamic decoding via Tacotron.initialize")
+        """Attention.py:169-210: (alignments [B, T], next_state) for query = LSTM output [B, 256] and state = previous
+        (cumulative) alignments.  Standalone form on the device primitives (``taco_op_attn_fwd``); inside decoding the same step
+        is part of the persistent kernel.  The context of ``_compute_attention`` (:345-366) is kept in ``self.last_context``."""
+        from . import _standalone as S
+        if getattr(self, "_keys", None) is None:
+            self._values, self._keys, self._lens = S.memory_keys(self.hparams, self.values, self.memory_sequence_length, self.mask_encoder)
+        hp = self.hparams
+        if bool(hp.smoothing) != bool(self.smoothing) or bool(hp.cumulative_weights) != bool(self._cumulate):
+            raise FusedStageError("smoothing / cumulate_weights must equal the hparams the device kernels were configured with")
+        if bool(self.smoothing):
+            raise FusedStageError("smoothing=True is implemented in the fused decoder kernels only (taco_decode)")
+        align, nxt, ctx = S.location_sensitive_attention(hp, query, state, self._values, self._keys, self._lens)
+        self.last_context = ctx
+        return align, nxt
+
+    keys = property(lambda self: self._ensure()[1])
+
+    def _ensure(self):
+        from . import _standalone as S
+        if getattr(self, "_keys", None) is None:
+            self._values, self._keys, self._lens = S.memory_keys(self.hparams, self.values, self.memory_sequence_length, self.mask_encoder)
+        return self._values, self._keys, self._lens
 
 
 class MultiheadAttention(object):
@@ -51,6 +71,12 @@ class MultiheadAttention(object):
         if attention_type != 'mlp_attention':
             raise FusedStageError("only mlp_attention (the reference default, Hyperparams.py:12) is on the B200 path")
 
-    def multi_head_attention(self):
-        raise FusedStageError("GST multi-head attention runs inside taco_encode (gst_attention_kernel): "
-                              "pass reference_mel to EncoderCell / Tacotron.initialize")
+    def multi_head_attention(self, hparams=None):
+        """Attention.py:243-260: style embedding [B, 1, num_units * ...] = multi-head MLP attention of the query (reference
+        encoder output [B, 1, 128] or [B, 128]) over value = tanh(style tokens).  Standalone form on ``taco_op_gst_fwd`` with
+        the installed GST weights; inside synthesis the same computation is part of ``taco_encode``."""
+        from ...Utils.Hyperparams import hparams as default_hp
+        from . import _standalone as S
+        hp = default_hp if hparams is None else hparams
+        style, self.attention_weights = S.gst_multi_head_attention(hp, self.query, self.num_heads)
+        return style

@@ -43,9 +43,13 @@ class Prenet(object):
         self.is_training = is_training
         self.scope = 'prenet' if scope is None else scope
 
-    def __call__(self, inputs):
-        raise FusedStageError("Prenet (2 x Dense+ReLU+always-on dropout, Decoder.py:342-352) is phase A/B of the "
-                              "persistent decoder kernel: call TacotronDecoderCell(...)(inputs, state)")
+    def __call__(self, inputs, philox_seed=None, step=0):
+        """Decoder.py:342-352 standalone (device primitives): the dropout bits are the decoder's Philox stream for
+        (seed, step), so the result equals the fused kernel's prenet output of that step."""
+        from . import _standalone as S
+        if list(self.layers_sizes) != list(hparams.prenet_layers) or self.drop_rate != hparams.dropout_rate:
+            raise FusedStageError("Prenet layers / drop_rate must equal the hparams the weights were created with")
+        return S.prenet(hparams, inputs, hparams.tacotron_random_seed if philox_seed is None else philox_seed, step)
 
 
 class DecoderRNN(object):
@@ -59,7 +63,11 @@ class DecoderRNN(object):
         self.scope = scope
 
     def __call__(self, input, states):
-        raise FusedStageError("DecoderRNN is phase C/D of the persistent decoder kernel")
+        """Decoder.py:319-321 standalone, inference mode: (raw LSTM-2 output, ((c1, h1), (c2, h2)) zoned)."""
+        from . import _standalone as S
+        if self.is_training:
+            raise FusedStageError("training-mode DecoderRNN (sampled zoneout masks) runs inside train/step.py")
+        return S.decoder_rnn(hparams, input, states, self.zoneout)
 
 
 class FrameProjection(object):
@@ -69,7 +77,10 @@ class FrameProjection(object):
         self.scope = 'Linear_projection' if scope is None else scope
 
     def __call__(self, inputs):
-        raise FusedStageError("FrameProjection is phase F of the persistent decoder kernel")
+        """Decoder.py:371-380 standalone: Dense(num_mels * r) of [LSTM output ; context] [B, 1024]."""
+        from ... import weights as W
+        from . import _standalone as S
+        return S.dense(hparams, inputs, W.FRAME_PROJ)
 
 
 class StopProjection(object):
@@ -80,7 +91,12 @@ class StopProjection(object):
         self.scope = 'stop_token_projection' if scope is None else scope
 
     def __call__(self, inputs):
-        raise FusedStageError("StopProjection is phase F of the persistent decoder kernel")
+        """Decoder.py:404-410 standalone: Dense(r) then sigmoid unless is_training (logits feed the loss)."""
+        import torch
+        from ... import weights as W
+        from . import _standalone as S
+        y = S.dense(hparams, inputs, W.STOP_PROJ)
+        return y if self.is_training else torch.sigmoid(y)
 
 
 class TacotronDecoderCell(object):

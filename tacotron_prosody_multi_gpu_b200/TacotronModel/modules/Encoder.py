@@ -34,15 +34,31 @@ class ZoneoutLSTMCell(object):
     state_size = property(lambda self: (self._num_units, self._num_units))
     output_size = property(lambda self: self._num_units)
 
+    _SCOPES = {"encoder_fw_LSTM": "ENC_LSTM_FW", "encoder_bw_LSTM": "ENC_LSTM_BW",
+               "decoder_LSTM_1": ("DEC_LSTM", (0, 1)), "decoder_LSTM_2": ("DEC_LSTM", (1, 2))}
+
     def __call__(self, inputs, state, scope=None):
-        raise FusedStageError("ZoneoutLSTMCell runs inside bilstm_persistent_kernel / the decoder kernel: "
-                              "use EncoderCell(...)(ids, lengths) or TacotronDecoderCell(...)(inputs, state)")
+        """Encoder.py:118-142 standalone, inference mode: (raw h, (zoned c, zoned h)).  The cell's weights are found by its
+        reference name (``encoder_fw_LSTM`` / ``encoder_bw_LSTM`` / ``decoder_LSTM_1`` / ``decoder_LSTM_2``)."""
+        from ... import weights as W
+        from ...Utils.Hyperparams import hparams
+        from . import _standalone as S
+        if self.is_training:
+            raise FusedStageError("training-mode zoneout (sampled masks) runs inside train/step.py")
+        ref = self._SCOPES.get(self.name)
+        if ref is None:
+            raise FusedStageError("ZoneoutLSTMCell(name=%r): no weights of that name (one of %s)" % (self.name, sorted(self._SCOPES)))
+        wscope = getattr(W, ref) if isinstance(ref, str) else getattr(W, ref[0]) % ref[1]
+        if self._zoneout_cell != self._zoneout_outputs:
+            raise FusedStageError("the device cell applies one zoneout factor to c and h (the reference always passes equal factors)")
+        return S.zoneout_lstm(hparams, inputs, state, wscope, self._zoneout_cell)
 
 
 class EncoderConvolution(object):
     def __init__(self, is_training, hparams, activation='relu', scope='encoder_convolutions'):
         if is_training:
-            raise FusedStageError("training-mode encoder (dropout + batch statistics) is SURVEY 8f row f1")
+            raise FusedStageError("training-mode encoder convolutions (dropout + batch statistics) run inside train/step.py "
+                                  "(Tacotron.initialize(is_training=True)); the standalone stage is inference-mode")
         self.is_training = is_training
         self.activation = activation
         self.scope = scope
@@ -53,7 +69,9 @@ class EncoderConvolution(object):
         self.hparams = hparams
 
     def __call__(self, inputs):
-        raise FusedStageError("EncoderConvolution is fused into taco_encode: call EncoderCell(conv, lstm)(ids, lengths)")
+        """Encoder.py:40-46 standalone on embedded inputs [B, T, 512] (inference: moving statistics, no dropout)."""
+        from . import _standalone as S
+        return S.encoder_convolution(self.hparams, inputs)
 
 
 class EncoderLSTM(object):
@@ -66,7 +84,12 @@ class EncoderLSTM(object):
         self.bw_cell = ZoneoutLSTMCell(size, is_training, zoneout, zoneout, name='encoder_bw_LSTM')
 
     def __call__(self, inputs, input_lengths):
-        raise FusedStageError("EncoderLSTM is fused into taco_encode: call EncoderCell(conv, lstm)(ids, lengths)")
+        """Encoder.py:68-77 standalone on conv outputs [B, T, 512] (inference-mode zoneout): [B, T, 2 * size]."""
+        from ...Utils.Hyperparams import hparams
+        from . import _standalone as S
+        if self.is_training:
+            raise FusedStageError("training-mode EncoderLSTM (sampled zoneout masks) runs inside train/step.py")
+        return S.encoder_lstm(hparams, inputs, input_lengths, self.zoneout)
 
 
 class EncoderCell(object):
@@ -86,7 +109,13 @@ class EncoderCell(object):
         hp = self.convolution_network.hparams
         ids = torch.as_tensor(np.asarray(inputs) if not isinstance(inputs, torch.Tensor) else inputs)
         if ids.dtype.is_floating_point:
-            raise FusedStageError("EncoderCell takes token ids [B, T]; embedded float inputs have no C-ABI entry")
+            # the reference's call shape (Encoder.py:11-20): embedded inputs [B, T, 512] -> conv stack -> BiLSTM, composed from
+            # the standalone stages (device primitives); token ids take the fused taco_encode path below
+            conv_output = self.convolution_network(ids)
+            self.conv_output_shape = tuple(conv_output.shape)
+            if input_lengths is None:
+                input_lengths = np.full(ids.shape[0], ids.shape[1], np.int32)
+            return self.lstm_network(conv_output, input_lengths)
         if input_lengths is None:
             input_lengths = np.full(ids.shape[0], ids.shape[1], np.int32)
         lens = torch.as_tensor(np.asarray(input_lengths) if not isinstance(input_lengths, torch.Tensor) else input_lengths)

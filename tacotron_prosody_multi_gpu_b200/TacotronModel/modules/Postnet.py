@@ -8,7 +8,7 @@ from .Encoder import FusedStageError
 class Postnet(object):
     def __init__(self, is_training, hparams, activation='tanh', scope=None):
         if is_training:
-            raise FusedStageError("training-mode postnet (dropout + batch statistics) is SURVEY 8f row f1")
+            raise FusedStageError("training-mode postnet (dropout + batch statistics) runs inside train/step.py (Tacotron.initialize(is_training=True))")
         self.is_training = is_training
         self.kernel_size = hparams.postnet_kernel_size
         self.channels = hparams.postnet_channels + hparams.style_embed_depth   # Postnet.py:22

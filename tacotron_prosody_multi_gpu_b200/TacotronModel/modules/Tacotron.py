@@ -25,9 +25,13 @@ from .Encoder import FusedStageError
 
 
 def reference_encoder(inputs, hparams, is_training=True, activation='relu'):
-    """Tacotron.py:12-29 (6 x conv2d 3x3 s2 + BN + ReLU -> GRU(128) -> Dense tanh).  Executed inside
-    ``taco_encode`` when a reference mel is given; kept here as the named entry of the reference."""
-    raise FusedStageError("reference_encoder runs inside taco_encode: pass reference_mel to Tacotron.initialize")
+    """Tacotron.py:12-29 (6 x conv2d 3x3 s2 + BN + ReLU -> GRU(128) -> Dense tanh): mel [B, Tm, 80] -> [B, 128].  Standalone
+    form on the device primitives, inference mode (moving statistics); inside synthesis it is part of ``taco_encode``, in training
+    (batch statistics) part of train/step.py."""
+    if is_training:
+        raise FusedStageError("training-mode reference_encoder (batch statistics) runs inside train/step.py")
+    from . import _standalone as S
+    return S.reference_encoder(hparams, inputs)
 
 
 class Tacotron(object):

@@ -62,6 +62,8 @@ def synthesize_batches(engine, hp, seqs, rank=0, world=1, batch_size=64, gst_wei
     seed = hp.tacotron_random_seed if philox_seed is None else philox_seed
     lo, hi = (-hp.max_abs_value, hp.max_abs_value) if hp.symmetric_mels else (0, hp.max_abs_value)
     mine = [(b, idx) for b, idx in enumerate(batches) if owner[b] == rank]
+    # longest batches first: the library's workspaces are grow-only, so they are sized once by the first (largest) batch
+    mine.sort(key=lambda job: -max(lengths[i] for i in job[1]))
 
     def run(eng, job):
         b, idx = job
@@ -69,9 +71,10 @@ def synthesize_batches(engine, hp, seqs, rank=0, world=1, batch_size=64, gst_wei
         lens = np.asarray([lengths[i] for i in idx], np.int32)
         res = eng.forward_host(ids.astype(np.int32), lens, gst_weights=gw, max_iters=max_iters, philox_seed=seed, fetch=fetch)
         keep = _get_output_lengths(res["stop"])
-        # copies: the host arrays are views of the engine's pinned buffers, reused by its next batch
-        return {int(i): dict(mel=np.clip(res["mel_outputs"][j, :keep[j]], lo, hi).copy(), steps=res["steps"], batch=b)
-                for j, i in enumerate(idx)}
+        # ONE clip of the whole batch into a fresh array (the pinned buffers are reused by the engine's next batch); the per-utterance
+        # results are views of it trimmed at the first rounded stop token -- the host cost per batch stays a single vector pass
+        mel = np.clip(res["mel_outputs"], lo, hi)
+        return {int(i): dict(mel=mel[j, :keep[j]], steps=res["steps"], batch=b) for j, i in enumerate(idx)}
 
     # an EnginePool keeps several batches in flight on this GPU (engine.EnginePool); a single TacoEngine runs them in turn
     parts = engine.map(run, mine) if hasattr(engine, "map") else [run(engine, job) for job in mine]
