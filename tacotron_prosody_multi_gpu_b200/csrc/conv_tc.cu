@@ -9,11 +9,13 @@
 // coordinate f0 + j - pad -- TMA zero-fills the out-of-range frames, which IS the 'same' padding,
 // per batch item.  Weights are pre-transposed at load time to K-major [Cout][taps*Cin] bf16.
 //
-// One persistent CTA per SM, 6 warps:
+// One persistent CTA per SM, 10 warps:
 //   warp 0      TMA producer (one elected lane), 4-stage mbarrier ring of {A 128x64, B BNx64} tiles
 //   warp 1      TMEM allocator + single-thread tcgen05.mma issuer (M=128, N=BN, K=16 per instruction)
-//   warps 2..5  epilogue: tcgen05.ld of the fp32 accumulator (one TMEM lane quarter per warp),
-//               folded BN scale/shift + activation (+ residual + clip), vector stores
+//   warps 2..9  epilogue: tcgen05.ld of the fp32 accumulator (TMEM lane quarter warp & 3, column half (warp - 2) >> 2),
+//               folded BN scale/shift + tanh.approx | relu (+ residual + clip), vector stores.  The epilogue of a tile must
+//               finish inside the MMA time of the next one (30.7 k cycles at K = 3840): with 4 warps, scalar scale / shift
+//               loads and tanhf it took 54-61 k cycles per tile and bounded the kernel (profiles/r02e_conv_tc_*).
 // Two accumulators (2 x 256 TMEM columns) so the epilogue of tile i overlaps the MMAs of tile i+1.
 #include <cuda.h>
 #include <cuda_bf16.h>
@@ -25,7 +27,8 @@ namespace {
 constexpr int BM = 128;      // rows (frames of one batch item) per tile = UMMA M
 constexpr int BK = 64;       // bf16 elements per stage along K = one 128-byte swizzle row
 constexpr int STAGES = 4;
-constexpr int TC_THREADS = 192;
+constexpr int EPI_WARPS = 8;   // two warps per TMEM lane quarter, each takes half of the accumulator columns
+constexpr int TC_THREADS = 64 + 32 * EPI_WARPS;
 constexpr int ACC_COLS = 256;  // TMEM column stride between the two accumulators
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -151,7 +154,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         }
         for (int i = 0; i < 2; ++i) {
             mbar_init(&tmem_full[i], 1);
-            mbar_init(&tmem_empty[i], 4);
+            mbar_init(&tmem_empty[i], EPI_WARPS);
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -170,8 +173,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             int stage = 0;
             uint32_t phase = 0;
             for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
-                const int nt = t / (p.B * p.tiles_f);
-                const int mt = t - nt * (p.B * p.tiles_f);
+                const int mt = t / p.tiles_n, nt = t - mt * p.tiles_n;   // column tiles of one row tile run together: A is read from DRAM once
                 const int b = mt / p.tiles_f, f0 = (mt - b * p.tiles_f) * BM;
                 for (int kb = 0; kb < KB; ++kb) {
                     const int tap = kb / kchunks, cc = kb - tap * kchunks;
@@ -216,13 +218,15 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         }
     } else {
         // ===================== epilogue warps =====================
-        const int q = warp & 3;  // TMEM lane quarter this warp may access
+        const int q = warp & 3;             // TMEM lane quarter this warp may access
+        const int half = (warp - 2) >> 2;   // which half of the accumulator columns
+        constexpr int CHUNKS = BN / 16;
+        const int ch0 = half == 0 ? 0 : (CHUNKS + 1) / 2, ch1 = half == 0 ? (CHUNKS + 1) / 2 : CHUNKS;
         int it = 0;
         for (int t = blockIdx.x; t < n_tiles; t += gridDim.x, ++it) {
             const int acc = it & 1;
             const uint32_t acc_phase = (it >> 1) & 1;
-            const int nt = t / (p.B * p.tiles_f);
-            const int mt = t - nt * (p.B * p.tiles_f);
+            const int mt = t / p.tiles_n, nt = t - mt * p.tiles_n;
             const int b = mt / p.tiles_f, f0 = (mt - b * p.tiles_f) * BM;
             const int f = f0 + q * 32 + lane;
             const bool valid = f < p.F;
@@ -231,21 +235,29 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             tc_fence_after();
             const uint32_t taddr = tmem_base + acc * ACC_COLS + ((uint32_t)(q * 32) << 16);
 #pragma unroll 1
-            for (int c0 = 0; c0 < BN; c0 += 16) {
+            for (int ch = ch0; ch < ch1; ++ch) {
+                const int c0 = ch * 16;
                 uint32_t v[16];
                 __syncwarp();
                 tmem_ld16(taddr + c0, v);
-                tmem_ld_wait();
                 const int n = nt * BN + c0;
+                // folded BN scale / shift of these 16 output channels (same addresses in every lane: broadcast 16-byte loads),
+                // in flight while the accumulator load completes
+                float sc[16], sh[16];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const float4 a = p.scale ? __ldg(reinterpret_cast<const float4*>(p.scale + n) + j) : make_float4(1.f, 1.f, 1.f, 1.f);
+                    const float4 d = p.shift ? __ldg(reinterpret_cast<const float4*>(p.shift + n) + j) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    sc[4 * j] = a.x; sc[4 * j + 1] = a.y; sc[4 * j + 2] = a.z; sc[4 * j + 3] = a.w;
+                    sh[4 * j] = d.x; sh[4 * j + 1] = d.y; sh[4 * j + 2] = d.z; sh[4 * j + 3] = d.w;
+                }
+                tmem_ld_wait();
                 float o[16];
 #pragma unroll
                 for (int j = 0; j < 16; ++j) {
-                    float x = __uint_as_float(v[j]);
-                    const float sc = p.scale ? __ldg(p.scale + n + j) : 1.f;
-                    const float sh = p.shift ? __ldg(p.shift + n + j) : 0.f;
-                    x = fmaf(x, sc, sh);
+                    float x = fmaf(__uint_as_float(v[j]), sc[j], sh[j]);
                     if (p.act == ACT_RELU) x = fmaxf(x, 0.f);
-                    else if (p.act == ACT_TANH) x = tanhf(x);
+                    else if (p.act == ACT_TANH) asm("tanh.approx.f32 %0, %0;" : "+f"(x));   // |err| <= 2^-10.99, then rounded to bf16
                     o[j] = x;
                 }
                 if (!valid) {
