@@ -270,9 +270,11 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                         __nv_bfloat162 h = __floats2bfloat162_rn(o[2 * j], o[2 * j + 1]);
                         pk[j] = *reinterpret_cast<uint32_t*>(&h);
                     }
-                    uint4* dst = reinterpret_cast<uint4*>(p.y_bf16 + row * p.y_stride + n);
-                    dst[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-                    dst[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+                    if (p.y_bf16) {
+                        uint4* dst = reinterpret_cast<uint4*>(p.y_bf16 + row * p.y_stride + n);
+                        dst[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                        dst[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+                    }
                     if (p.y_f32) {
                         float4* d32 = reinterpret_cast<float4*>(p.y_f32 + row * p.Cout + n);
 #pragma unroll

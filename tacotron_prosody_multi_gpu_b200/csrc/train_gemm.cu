@@ -8,9 +8,14 @@
 // Tiles: BM x BN x BK with a TM x TN register micro-tile per thread, shared-memory double buffering.
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <cuda_bf16.h>
 #include <cstdint>
 
 #include "../../include/taco_b200_train.h"
+#include "taco_internal.h"   // conv_tc.cu: the tcgen05 implicit-GEMM convolution shared with the synthesis path
 
 namespace {
 
@@ -520,6 +525,90 @@ inline bool use_mma(int M, int N, int K) {
     return g_train_precision == TACO_TRAIN_BF16 && (long long)M * N >= 64LL * 64 * 64 && (long long)M * N * K >= (1LL << 24);
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// conv1d forward / data gradient on the tcgen05 kernel of the synthesis path (conv_tc.cu) in the bf16 precision mode:
+// operands are packed to bf16 per call (activations channel-padded to a multiple of 64, weights K-major [Cout][taps * Cin_pad];
+// the data gradient is the same convolution of dY with the tap-reversed, channel-transposed kernel), fp32 output.
+// Scratch buffers are process-wide and grow-only.
+// ---------------------------------------------------------------------------------------------
+struct TcScratch {
+    void* p = nullptr;
+    size_t bytes = 0;
+};
+TcScratch g_tc_x, g_tc_w, g_tc_b;
+bool g_conv_tc = getenv("TACO_TRAIN_CONV_TC") ? atoi(getenv("TACO_TRAIN_CONV_TC")) != 0 : true;   // 0: keep the mma.sync kernels (A/B)
+int g_tc_sms = 0;
+
+bool tc_reserve(TcScratch& s, size_t bytes) {
+    if (s.bytes >= bytes) return true;
+    if (s.p) cudaFree(s.p);
+    s.p = nullptr;
+    s.bytes = 0;
+    if (cudaMalloc(&s.p, bytes) != cudaSuccess) return false;
+    s.bytes = bytes;
+    return true;
+}
+
+// w [k][Ci][Co] fp32 -> out [N][k * Kpad] bf16.  fwd: N = Co, channel c = ci, out[co][tap][ci] = w[tap][ci][co];
+// dgrad: N = Ci, channel c = co, out[ci][tap][co] = w[k - 1 - tap][ci][co].
+__global__ void pack_conv_w_kernel(const float* __restrict__ w, __nv_bfloat16* __restrict__ out, int k, int Ci, int Co, int Kpad, int dgrad) {
+    const int N = dgrad ? Ci : Co, C = dgrad ? Co : Ci;
+    const long long total = (long long)N * k * Kpad;
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= total) return;
+    const int c = (int)(i % Kpad);
+    const int tap = (int)((i / Kpad) % k);
+    const int n = (int)(i / ((long long)Kpad * k));
+    float v = 0.f;
+    if (c < C) v = dgrad ? w[((size_t)(k - 1 - tap) * Ci + n) * Co + c] : w[((size_t)tap * Ci + c) * Co + n];
+    out[i] = __float2bfloat16_rn(v);
+}
+
+// returns 1 if the tcgen05 kernel took the call, 0 if the shape is not covered, < 0 on error
+int conv_tc_train(const float* x, const float* w, const float* bias, float* y, int B, int T, int Cin, int Cout, int k, int dgrad,
+                  cudaStream_t st) {
+    static int dbg = getenv("TACO_TRAIN_CONV_DBG") ? 8 : 0;
+    if (dbg > 0) {
+        --dbg;
+        fprintf(stderr, "[conv_tc_train] prec %d B %d T %d Cin %d Cout %d k %d dgrad %d bias %p\n", g_train_precision, B, T, Cin, Cout, k, dgrad, (const void*)bias);
+    }
+    if (g_train_precision != TACO_TRAIN_BF16) return 0;
+    if (!(Cout % 256 == 0 || Cout == 80 || Cout == 128) || (long long)B * T < 4096) return 0;
+    const int Cpad = (Cin + 63) / 64 * 64;
+    if (!g_tc_sms) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&g_tc_sms, cudaDevAttrMultiProcessorCount, dev);
+    }
+    if (!tc_reserve(g_tc_x, (size_t)B * T * Cpad * 2) || !tc_reserve(g_tc_w, (size_t)Cout * k * Cpad * 2)) return -3;
+    if (taco_launch_prep_bf16(x, nullptr, g_tc_x.p, B, T, (long long)T * Cin, Cin, Cpad, 0.f, 0.f, 0, st) != cudaSuccess) return -3;
+    const long long nw = (long long)Cout * k * Cpad;
+    // fwd: w is [k][Ci = Cin][Co = Cout]; dgrad: the caller's kernel is [k][Ci = Cout][Co = Cin]
+    pack_conv_w_kernel<<<(unsigned)((nw + 255) / 256), 256, 0, st>>>(w, reinterpret_cast<__nv_bfloat16*>(g_tc_w.p), k, dgrad ? Cout : Cin,
+                                                                     dgrad ? Cin : Cout, Cpad, dgrad);
+    // the epilogue reads the bias with 16-byte loads; parameter views of the flat training buffer are only 4-byte aligned
+    const float* bias_al = nullptr;
+    if (bias) {
+        if (!tc_reserve(g_tc_b, 4096 * sizeof(float)) || Cout > 4096) return -3;
+        if (cudaMemcpyAsync(g_tc_b.p, bias, (size_t)Cout * sizeof(float), cudaMemcpyDeviceToDevice, st) != cudaSuccess) return -3;
+        bias_al = reinterpret_cast<const float*>(g_tc_b.p);
+    }
+    ConvTcParams c;
+    memset(&c, 0, sizeof c);
+    c.x = g_tc_x.p; c.wt = g_tc_w.p;
+    c.B = B; c.F = T; c.Cin = Cpad; c.taps = k; c.Cout = Cout;
+    c.scale = nullptr; c.shift = bias_al; c.act = ACT_NONE;
+    c.y_bf16 = nullptr; c.y_stride = 0; c.y_f32 = y;
+    c.out_f32_only = (Cout % 256 != 0) ? 1 : 0;
+    c.residual = nullptr; c.clip = 0;
+    if (taco_launch_conv_tc(c, g_tc_sms, st) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;   // e.g. the driver entry point for tensor maps is unavailable: the mma.sync kernel takes the call
+    }
+    return 1;
+}
+
 template <class AL, class BL>
 int launch_gemm(AL A, BL Bm, float* C, long long ldc, int M, int N, int K, float beta, const float* bias, cudaStream_t st) {
     if (M <= 0 || N <= 0) return 0;
@@ -639,6 +728,10 @@ int taco_op_gemm(const float* A, long long lda, const float* B, long long ldb, f
 
 int taco_op_conv1d_fwd(const float* x, const float* w, const float* bias, float* y, int B, int T, int Ci, int Co, int k, void* stream) {
     if (!x || !w || !y) return -1;
+    if (g_conv_tc) {
+        const int r = conv_tc_train(x, w, bias, y, B, T, Ci, Co, k, 0, (cudaStream_t)stream);
+        if (r != 0) return r < 0 ? r : 0;
+    }
     if (use_mma(B * T, Co, k * Ci) && Ci % 8 == 0 && Co % 8 == 0)
         return launch_gemm_mma2(VAConvFwd{x, T, Ci, (k - 1) / 2}, VBPlainN{w, Co}, y, Co, B * T, Co, k * Ci, 0.f, bias, (cudaStream_t)stream);
     AConvFwd a{x, T, Ci, (k - 1) / 2, 1};
@@ -648,6 +741,10 @@ int taco_op_conv1d_fwd(const float* x, const float* w, const float* bias, float*
 
 int taco_op_conv1d_dgrad(const float* dy, const float* w, float* dx, int B, int T, int Ci, int Co, int k, void* stream) {
     if (!dy || !w || !dx) return -1;
+    if (g_conv_tc) {
+        const int r = conv_tc_train(dy, w, nullptr, dx, B, T, Co, Ci, k, 1, (cudaStream_t)stream);
+        if (r != 0) return r < 0 ? r : 0;
+    }
     if (use_mma(B * T, Ci, k * Co) && Ci % 8 == 0 && Co % 8 == 0)
         return launch_gemm_mma2(VAConvDgrad{dy, T, Co, (k - 1) / 2}, VBConvDgrad{w, Ci, Co}, dx, Ci, B * T, Ci, k * Co, 0.f, nullptr,
                                 (cudaStream_t)stream);
