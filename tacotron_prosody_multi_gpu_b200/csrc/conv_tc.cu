@@ -20,6 +20,8 @@
 #include <cuda.h>
 #include <cuda_bf16.h>
 
+#include <cstring>
+
 #include "taco_internal.h"
 
 namespace {
@@ -122,6 +124,9 @@ struct TcParams {
     const float* residual;            // [B][F][Cout] (EPI 1)
     int clip;
     float lo, hi;
+    int rows_pad;                     // wgrad: (taps - 1) / 2 of the convolution
+    int wgrad;                        // weight-gradient mode: the "batch" index is the tap, its shift applies to the K coordinate
+    int rows_valid;                   // wgrad: output rows per tap (Cin of the convolution); rows beyond are padding
 };
 
 template <int BN, int EPI>
@@ -180,8 +185,15 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                     mbar_wait(&empty[stage], phase ^ 1);
                     uint8_t* sa = smem + stage * STAGE_BYTES;
                     mbar_expect_tx(&full[stage], A_BYTES + B_BYTES);
-                    tma_load_3d(sa, &tmA, &full[stage], cc * BK, f0 + tap - pad, b);
-                    tma_load_2d(sa + A_BYTES, &tmB, &full[stage], tap * p.Cin + cc * BK, nt * BN);
+                    if (p.wgrad) {
+                        // dW[tap b][ci][co] = sum_k xT[b][ci][k] dyT[co][k]: both operands K-major over k = (item, frame); xT[b] is
+                        // x shifted by the tap (materialised by transpose_bf16_kernel)
+                        tma_load_3d(sa, &tmA, &full[stage], cc * BK, f0, b);
+                        tma_load_2d(sa + A_BYTES, &tmB, &full[stage], cc * BK, nt * BN);
+                    } else {
+                        tma_load_3d(sa, &tmA, &full[stage], cc * BK, f0 + tap - pad, b);
+                        tma_load_2d(sa + A_BYTES, &tmB, &full[stage], tap * p.Cin + cc * BK, nt * BN);
+                    }
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
             }
@@ -229,8 +241,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             const int mt = t / p.tiles_n, nt = t - mt * p.tiles_n;
             const int b = mt / p.tiles_f, f0 = (mt - b * p.tiles_f) * BM;
             const int f = f0 + q * 32 + lane;
-            const bool valid = f < p.F;
-            const size_t row = (size_t)b * p.F + f;
+            const bool valid = p.wgrad ? f < p.rows_valid : f < p.F;
+            const size_t row = p.wgrad ? (size_t)b * p.rows_valid + f : (size_t)b * p.F + f;
             mbar_wait(&tmem_full[acc], acc_phase);
             tc_fence_after();
             const uint32_t taddr = tmem_base + acc * ACC_COLS + ((uint32_t)(q * 32) << 16);
@@ -410,10 +422,79 @@ cudaError_t taco_launch_conv_tc(const ConvTcParams& c, int n_sm, cudaStream_t st
     p.y_stride = c.y_stride;
     p.residual = c.residual;
     p.clip = c.clip; p.lo = c.clip_lo; p.hi = c.clip_hi;
+    p.wgrad = 0; p.rows_valid = 0; p.rows_pad = 0;
     if (c.out_f32_only) {
         if (c.Cout == 80) return launch<80, 1>(tmA, tmB, p, n_sm, st);
         if (c.Cout == 128) return launch<128, 1>(tmA, tmB, p, n_sm, st);
         return cudaErrorInvalidValue;
     }
+    return launch<256, 0>(tmA, tmB, p, n_sm, st);
+}
+
+// fp32 [B][T][C] -> bf16 transposed, K-major operands of the weight-gradient contraction: out[s][c][b * Tp + tp] =
+// in[b][tp - margin + s - shift0][c] (0 outside [0, T)) for s < nshift.  nshift = 1, shift0 = 0: the plain transpose with `margin`
+// zero frames in front of every item; nshift = taps, shift0 = pad: one copy per tap, shifted in time -- TMA cannot start a box at an
+// inner coordinate that is not a multiple of 16 bytes, so the tap shift is materialised here.  32-frame x 32-channel tiles (+ halo).
+__global__ void transpose_bf16_kernel(const float* __restrict__ in, __nv_bfloat16* __restrict__ out, int B, int T, int C, int Cpad, int Tp,
+                                      int margin, int nshift, int shift0) {
+    __shared__ float tile[32 + 8][33];
+    const int b = blockIdx.z;
+    const int t0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
+    const int tx = threadIdx.x, ty = threadIdx.y;   // 32 x 8
+    for (int i = ty; i < 32 + nshift - 1; i += 8) {
+        const int t = t0 + i - margin - shift0, c = c0 + tx;
+        tile[i][tx] = (t >= 0 && t < T && c < C) ? in[((size_t)b * T + t) * C + c] : 0.f;
+    }
+    __syncthreads();
+    const size_t K = (size_t)B * Tp;
+    for (int s = 0; s < nshift; ++s)
+        for (int i = ty; i < 32; i += 8) {
+            const int c = c0 + i, tp = t0 + tx;
+            if (c < Cpad && tp < Tp) out[((size_t)s * Cpad + c) * K + (size_t)b * Tp + tp] = __float2bfloat16_rn(tile[tx + s][i]);
+        }
+}
+
+cudaError_t taco_launch_transpose_bf16(const float* in, void* out, int B, int T, int C, int Cpad, int Tp, int margin, int nshift, int shift0,
+                                       cudaStream_t st) {
+    if (nshift < 1 || nshift > 9) return cudaErrorInvalidValue;
+    dim3 grid((Tp + 31) / 32, (Cpad + 31) / 32, B);
+    transpose_bf16_kernel<<<grid, dim3(32, 8), 0, st>>>(in, reinterpret_cast<__nv_bfloat16*>(out), B, T, C, Cpad, Tp, margin, nshift, shift0);
+    return cudaGetLastError();
+}
+
+// dW [taps][Ci][Co] (fp32) = conv1d weight gradient from xT bf16 [taps][Ci_pad][K] (one time-shifted copy per tap), dyT bf16 [Co][K], K = B * Tp (multiple of 64), Ci_pad
+// a multiple of 128, Co a multiple of 256: one tile per (tap, 128 input channels, 256 output channels), K-loop over all frames.
+cudaError_t taco_launch_conv_wgrad_tc(const void* xT, const void* dyT, float* dw, int K, int Ci, int Ci_pad, int Co, int taps, int n_sm,
+                                      cudaStream_t st) {
+    EncodeTiledFn enc = encode_fn();
+    if (!enc) return cudaErrorNotSupported;
+    if (K % BK != 0 || Ci_pad % BM != 0 || Co % 256 != 0) return cudaErrorInvalidValue;
+    CUtensorMap tmA, tmB;
+    {
+        cuuint64_t dims[3] = {(cuuint64_t)K, (cuuint64_t)Ci_pad, (cuuint64_t)taps};
+        cuuint64_t strides[2] = {(cuuint64_t)K * 2, (cuuint64_t)K * Ci_pad * 2};
+        cuuint32_t box[3] = {(cuuint32_t)BK, (cuuint32_t)BM, 1};
+        cuuint32_t es[3] = {1, 1, 1};
+        if (enc(&tmA, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(xT), dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+            return cudaErrorInvalidValue;
+    }
+    {
+        cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)Co};
+        cuuint64_t strides[1] = {(cuuint64_t)K * 2};
+        cuuint32_t box[2] = {(cuuint32_t)BK, 256};
+        cuuint32_t es[2] = {1, 1};
+        if (enc(&tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(dyT), dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+            return cudaErrorInvalidValue;
+    }
+    TcParams p;
+    memset(&p, 0, sizeof p);
+    p.B = taps; p.F = Ci_pad; p.Cin = K; p.taps = 1; p.Cout = Co;
+    p.tiles_f = Ci_pad / BM;
+    p.tiles_n = Co / 256;
+    p.act = ACT_NONE;
+    p.y_f32 = dw; p.y_bf16 = nullptr;
+    p.wgrad = 1; p.rows_valid = Ci; p.rows_pad = (taps - 1) / 2;
     return launch<256, 0>(tmA, tmB, p, n_sm, st);
 }

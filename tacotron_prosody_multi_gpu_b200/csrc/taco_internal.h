@@ -141,6 +141,10 @@ struct ConvTcParams {
     float clip_lo, clip_hi;
 };
 cudaError_t taco_launch_conv_tc(const ConvTcParams& p, int n_sm, cudaStream_t stream);
+cudaError_t taco_launch_transpose_bf16(const float* in, void* out, int B, int T, int C, int Cpad, int Tp, int margin, int nshift, int shift0,
+                                       cudaStream_t st);
+cudaError_t taco_launch_conv_wgrad_tc(const void* xT, const void* dyT, float* dw, int K, int Ci, int Ci_pad, int Co, int taps, int n_sm,
+                                      cudaStream_t st);
 cudaError_t taco_launch_prep_bf16(const float* in, float* out32, void* out16, int B, int F, long long in_bstride, int C,
                                   int Cpad, float lo, float hi, int clip, cudaStream_t stream);
 

@@ -536,7 +536,7 @@ struct TcScratch {
     void* p = nullptr;
     size_t bytes = 0;
 };
-TcScratch g_tc_x, g_tc_w, g_tc_b;
+TcScratch g_tc_x, g_tc_w, g_tc_b, g_tc_xt, g_tc_dyt, g_tc_dw;
 bool g_conv_tc = getenv("TACO_TRAIN_CONV_TC") ? atoi(getenv("TACO_TRAIN_CONV_TC")) != 0 : true;   // 0: keep the mma.sync kernels (A/B)
 int g_tc_sms = 0;
 
@@ -599,6 +599,7 @@ int conv_tc_train(const float* x, const float* w, const float* bias, float* y, i
     c.x = g_tc_x.p; c.wt = g_tc_w.p;
     c.B = B; c.F = T; c.Cin = Cpad; c.taps = k; c.Cout = Cout;
     c.scale = nullptr; c.shift = bias_al; c.act = ACT_NONE;
+    if (reinterpret_cast<uintptr_t>(y) & 15) return 0;   // 16-byte stores in the epilogue
     c.y_bf16 = nullptr; c.y_stride = 0; c.y_f32 = y;
     c.out_f32_only = (Cout % 256 != 0) ? 1 : 0;
     c.residual = nullptr; c.clip = 0;
@@ -606,6 +607,44 @@ int conv_tc_train(const float* x, const float* w, const float* bias, float* y, i
         cudaGetLastError();
         return 0;   // e.g. the driver entry point for tensor maps is unavailable: the mma.sync kernel takes the call
     }
+    return 1;
+}
+
+// conv1d weight gradient on the same kernel (wgrad mode): dW[tap][ci][co] = sum_(b,t) x[b, t + tap - pad, ci] dY[b, t, co] with both
+// operands transposed to K-major bf16 [channels][B * Tp] (zero margins of `pad` frames around every item).  1 = done, 0 = not covered.
+int conv_wgrad_tc_train(const float* x, const float* dy, float* dw, int B, int T, int Ci, int Co, int k, cudaStream_t st) {
+    if (g_train_precision != TACO_TRAIN_BF16 || Co % 256 != 0 || (long long)B * T < 4096) return 0;
+    const int pad = (k - 1) / 2;
+    const int Tp = (T + 2 * pad + 63) / 64 * 64;
+    const int Ci_pad = (Ci + 127) / 128 * 128;
+    const long long K = (long long)B * Tp;
+    if (!g_tc_sms) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&g_tc_sms, cudaDevAttrMultiProcessorCount, dev);
+    }
+    cudaError_t e;
+#define TC_TRY(what, expr)                                                                          \
+    if ((e = (expr)) != cudaSuccess) {                                                               \
+        fprintf(stderr, "[taco_b200] conv wgrad (tcgen05): %s: %s\n", what, cudaGetErrorString(e)); \
+        return -3;                                                                                   \
+    }
+    TC_TRY("scratch", (tc_reserve(g_tc_xt, (size_t)k * Ci_pad * K * 2) && tc_reserve(g_tc_dyt, (size_t)Co * K * 2)) ? cudaSuccess : cudaErrorMemoryAllocation)
+    TC_TRY("transpose x", taco_launch_transpose_bf16(x, g_tc_xt.p, B, T, Ci, Ci_pad, Tp, pad, k, pad, st))
+    TC_TRY("transpose dy", taco_launch_transpose_bf16(dy, g_tc_dyt.p, B, T, Co, Co, Tp, pad, 1, 0, st))
+#undef TC_TRY
+    // the epilogue stores 16 bytes at a time; gradient views of the flat training buffer are only 4-byte aligned
+    float* out = dw;
+    const size_t dw_bytes = (size_t)k * Ci * Co * sizeof(float);
+    if (reinterpret_cast<uintptr_t>(dw) & 15) {
+        if (!tc_reserve(g_tc_dw, dw_bytes)) return -3;
+        out = reinterpret_cast<float*>(g_tc_dw.p);
+    }
+    if (taco_launch_conv_wgrad_tc(g_tc_xt.p, g_tc_dyt.p, out, (int)K, Ci, Ci_pad, Co, k, g_tc_sms, st) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    if (out != dw && cudaMemcpyAsync(dw, out, dw_bytes, cudaMemcpyDeviceToDevice, st) != cudaSuccess) return -3;
     return 1;
 }
 
@@ -755,6 +794,10 @@ int taco_op_conv1d_dgrad(const float* dy, const float* w, float* dx, int B, int 
 
 int taco_op_conv1d_wgrad(const float* x, const float* dy, float* dw, int B, int T, int Ci, int Co, int k, void* stream) {
     if (!x || !dy || !dw) return -1;
+    if (g_conv_tc) {
+        const int r = conv_wgrad_tc_train(x, dy, dw, B, T, Ci, Co, k, (cudaStream_t)stream);
+        if (r != 0) return r < 0 ? r : 0;
+    }
     if (use_mma(k * Ci, Co, B * T) && Ci % 8 == 0 && Co % 8 == 0 && (B * T) % 8 == 0)
         return launch_gemm_mma2(VAConvWgrad{x, T, Ci, (k - 1) / 2}, VBPlainN{dy, Co}, dw, Co, k * Ci, Co, B * T, 0.f, nullptr,
                                 (cudaStream_t)stream);

@@ -309,3 +309,44 @@ def test_training_step_bf16_mode_close_to_fp32_oracle(ops):
         worst = max(worst, (name, err), key=lambda z: z[1])
         assert err < 6e-2, "%s: relative L2 error %.3e" % (name, err)
     print("bf16 mode worst gradient (relative L2):", worst)
+
+
+@pytest.mark.parametrize("Ci,Co,T", [(768, 768, 200), (80, 768, 199), (512, 512, 130)])
+def test_conv1d_tcgen05_training_paths_match_bf16_reference(Ci, Co, T):
+    """bf16 training mode: conv1d forward, data gradient and weight gradient run on the tcgen05 kernel of the synthesis path
+    (conv_tc.cu; operands packed / transposed to bf16 per call) when B*T >= 4096 rows.  Reference: float64 convolutions of the
+    same bf16-rounded operands; tolerance = fp32 accumulation order over K <= 6400 (relative 2e-4 of the output scale)."""
+    from tacotron_prosody_multi_gpu_b200.train.ops import CudaOps
+    o = CudaOps(0)
+    o.set_precision("bf16")
+    try:
+        B, k = 32, 5
+        g = torch.Generator(device="cuda").manual_seed(Ci + T)
+        x = torch.randn(B, T, Ci, device="cuda", generator=g)
+        w = torch.randn(k, Ci, Co, device="cuda", generator=g) * 0.05
+        b = torch.randn(Co, device="cuda", generator=g)
+        dy = torch.randn(B, T, Co, device="cuda", generator=g) * 0.1
+        # views at an odd float offset, like the parameter / gradient views of the flat training buffer
+        flat = torch.zeros(k * Ci * Co + Co + 3, device="cuda")
+        wv = flat[1:1 + k * Ci * Co].view(k, Ci, Co)
+        wv.copy_(w)
+        bv = flat[1 + k * Ci * Co:1 + k * Ci * Co + Co]
+        bv.copy_(b)
+        gflat = torch.zeros(k * Ci * Co + 3, device="cuda")
+        dw = gflat[3:3 + k * Ci * Co].view(k, Ci, Co)
+        y, dx = o.empty(B, T, Co), o.empty(B, T, Ci)
+        o.conv1d_fwd(x, wv, bv, y)
+        o.conv1d_dgrad(dy, wv, dx)
+        o.conv1d_wgrad(x, dy, dw)
+        xr, wr, dyr = x.bfloat16().double(), w.bfloat16().double(), dy.bfloat16().double()
+        ref_y = torch.nn.functional.conv1d(xr.transpose(1, 2), wr.permute(2, 1, 0), b.double(), padding=2).transpose(1, 2)
+        ref_dx = torch.nn.functional.conv_transpose1d(dyr.transpose(1, 2), wr.permute(2, 1, 0), padding=2).transpose(1, 2)
+        xp = torch.nn.functional.pad(xr, (0, 0, 2, 2))
+        ref_dw = torch.stack([torch.einsum("btc,bto->co", xp[:, tap:tap + T], dyr) for tap in range(k)])
+        for name, got, ref in (("fwd", y, ref_y), ("dgrad", dx, ref_dx), ("wgrad", dw, ref_dw)):
+            err = float((got.double() - ref).abs().max())
+            scale = float(ref.abs().max())
+            print("%s Ci=%d Co=%d: max err %.2e of %.2e" % (name, Ci, Co, err, scale))
+            assert err <= 2e-4 * scale, (name, err, scale)
+    finally:
+        o.set_precision("fp32")
