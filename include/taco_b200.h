@@ -134,6 +134,12 @@ int taco_postnet(TacoHandle* h, const float* frames, int B, int F, int F_stride,
 /* Number of kernels launched by this handle since creation (bench.py's gpu_launches). */
 int64_t taco_launch_count(const TacoHandle* h);
 
+/* Grid of the persistent BiLSTM kernel of taco_encode (EncoderLSTM, Encoder.py:68-77).  0 (default): the lowest-latency grid
+ * (128 CTAs at B = 64, cooperative launch -- cannot start while a cluster decoder of another handle occupies 112 SMs);
+ * max_ctas > 0: at most that many CTAs (32 at B = 64: 16 units per CTA, ~2x the latency, but it runs on the 36 SMs a running
+ * decoder leaves free, so handles that keep several batches in flight overlap the whole encoder with the decoder). */
+int taco_set_encoder_ctas(TacoHandle* h, int max_ctas);
+
 /* Device time of the most recent run of a stage, from CUDA events recorded on the caller's stream
  * around it (blocks until the stage has finished).  TACO_STAGE_DECODER_KERNEL brackets only the
  * persistent decoder kernel launch -- the figure bench.py's roofline uses. */

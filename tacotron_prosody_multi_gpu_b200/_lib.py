@@ -22,7 +22,7 @@ ERROR_NAMES = {-1: "TACO_ERR_INVALID", -2: "TACO_ERR_UNSUPPORTED", -3: "TACO_ERR
 # every symbol include/taco_b200.h declares
 EXPORTED_SYMBOLS = [
     "taco_create", "taco_destroy", "taco_last_error", "taco_version", "taco_set_weight",
-    "taco_finalize_weights", "taco_set_precision", "taco_encode", "taco_decode",
+    "taco_finalize_weights", "taco_set_precision", "taco_set_encoder_ctas", "taco_encode", "taco_decode",
     "taco_transpose_alignments", "taco_postnet", "taco_launch_count", "taco_get_decoder_state",
     "taco_stage_ms", "taco_debug_read_workspace",
 ]
@@ -77,6 +77,8 @@ def lib():
     L.taco_finalize_weights.restype = i32
     L.taco_set_precision.argtypes = [vp, i32]
     L.taco_set_precision.restype = i32
+    L.taco_set_encoder_ctas.argtypes = [vp, i32]
+    L.taco_set_encoder_ctas.restype = i32
     L.taco_encode.argtypes = [vp, vp, vp, i32, i32, vp, i32, vp, vp, vp]
     L.taco_encode.restype = i32
     L.taco_decode.argtypes = [vp, i32, vp, vp, i32, i32, vp, i32, i32, vp, u64, i32, i32, vp, vp, vp, vp, vp]

@@ -84,7 +84,8 @@ struct TacoHandle {
     float dec3_stop_bias[2] = {0.f, 0.f};
     int dec3_max_clusters = -1;  // cudaOccupancyMaxActiveClusters of decoder3_kernel (queried once)
     int dec_kind = 0;            // which decoder kernel owns the running state (1 = decoder.cu fp32, 3 = decoder3.cu bf16 cluster kernel)
-    float* bilstm_blob[2] = {};  // same two configs, [2 dir][GN][256*4U]
+    float* bilstm_blob[3] = {};  // U = 2, 4, 16 units per CTA, [2 dir][GN][256*4U]
+    int encoder_max_ctas = 0;    // 0: lowest-latency BiLSTM grid; > 0: at most this many CTAs (taco_set_encoder_ctas)
     // decoder running state
     int dec_t = 0, dec_B = 0, dec_T = 0, dec_RBP = 0, dec_GB = 0;
     // CUDA events bracketing each stage on the caller's stream (taco_stage_ms)
@@ -275,8 +276,8 @@ int pack_decoder_blobs(TacoHandle* h) {
     NEED(kbw, std::string(ENC_BW) + "/kernel", 768, 1024)
     NEED(bfw, std::string(ENC_FW) + "/bias", 1024)
     NEED(bbw, std::string(ENC_BW) + "/bias", 1024)
-    for (int cfg = 0; cfg < 2; ++cfg) {
-        const int U = cfg == 0 ? 2 : 4, GN = 256 / U, NCL = 4 * U;
+    for (int cfg = 0; cfg < 3; ++cfg) {
+        const int U = cfg == 0 ? 2 : (cfg == 1 ? 4 : 16), GN = 256 / U, NCL = 4 * U;
         const int bf_ = taco_bilstm_blob_floats(U);
         std::vector<float> blob((size_t)2 * GN * bf_, 0.f);
         for (int d = 0; d < 2; ++d) {
@@ -892,8 +893,9 @@ int taco_encode(TacoHandle* h, const int32_t* ids, const int32_t* lens, int B, i
         p.B = B; p.T = T;
         p.RBP = B <= 4 ? 4 : (B <= 8 ? 8 : (B <= 16 ? 16 : 32));
         p.GB = (B + p.RBP - 1) / p.RBP;
-        const int cfg = p.GB == 1 ? 0 : 1;
-        p.U = cfg == 0 ? 2 : 4;
+        int cfg = p.GB == 1 ? 0 : 1;
+        if (h->encoder_max_ctas > 0 && p.RBP == 32 && p.GB * (256 / (cfg == 0 ? 2 : 4)) > h->encoder_max_ctas) cfg = 2;   // 16 units per CTA
+        p.U = cfg == 0 ? 2 : (cfg == 1 ? 4 : 16);
         p.GN = 256 / p.U;
         p.blobs = h->bilstm_blob[cfg];
         p.blob_floats = taco_bilstm_blob_floats(p.U);
@@ -1201,6 +1203,12 @@ int taco_stage_ms(TacoHandle* h, int stage, float* ms_out) {
     CK(cudaSetDevice(h->device));
     CK(cudaEventSynchronize(h->ev[stage][1]));
     CK(cudaEventElapsedTime(ms_out, h->ev[stage][0], h->ev[stage][1]));
+    return TACO_OK;
+}
+
+int taco_set_encoder_ctas(TacoHandle* h, int max_ctas) {
+    if (!h || max_ctas < 0) return TACO_ERR_INVALID;
+    h->encoder_max_ctas = max_ctas;
     return TACO_OK;
 }
 

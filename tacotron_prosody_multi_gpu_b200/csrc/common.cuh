@@ -155,6 +155,16 @@ __device__ __forceinline__ void dense_xt(const XSeg* segs, int nseg, const float
     __syncthreads();
     // reduction: nOut = tiles*16 outputs, KS = 16*G partials each (G = TACO_THREADS / nOut)
     const int nOut = tiles * 16;
+    if (nOut > TACO_THREADS) {   // wide tiles (32 rows x 64 columns): KS = TACO_THREADS / tiles partials per output, several outputs per thread
+        for (int o2 = tid; o2 < nOut; o2 += TACO_THREADS) {
+            float sum2 = 0.f;
+            for (int q = 0; q < KS; ++q) sum2 += part[(size_t)q * nOut + o2];
+            const int t = o2 >> 4, i = (o2 >> 2) & 3, j = o2 & 3;
+            res[((t / tiles_c) * 4 + i) * NC + (t % tiles_c) * 4 + j] = sum2;
+        }
+        __syncthreads();
+        return;
+    }
     const int G = TACO_THREADS / nOut;  // >= 1 because tiles <= 32
     const int o = tid % nOut;
     const int g = tid / nOut;

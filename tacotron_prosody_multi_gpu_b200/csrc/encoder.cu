@@ -16,7 +16,8 @@ __global__ void embedding_kernel(const int32_t* __restrict__ ids, const float* _
     reinterpret_cast<float4*>(out)[i] = reinterpret_cast<const float4*>(table)[(size_t)id * dim4 + d];
 }
 
-// One CTA = (batch tile bt, unit tile nt), both directions.  Recurrent kernels [256][4U] of both
+// One CTA = (batch tile bt, unit tile nt), both directions.  U units per CTA: 2 / 4 (lowest latency: 128 CTAs at B = 64) or 16
+// (32 CTAs at B = 64: fits beside a running cluster decoder, which leaves 36 SMs free -- engine.EnginePool selects it).  Recurrent kernels [256][4U] of both
 // directions resident in shared memory for all T steps; h exchanged through L2 (XT layout,
 // ping-pong), c private.  The input half of the gate pre-activation (x.W_x + b) is hoisted out
 // of the loop into one GEMM over all tokens (xw).
@@ -29,14 +30,14 @@ __global__ void __launch_bounds__(TACO_THREADS, 1) bilstm_persistent_kernel(BiLs
     const int H = 256;
     float* Wh[2] = {smem, smem + H * NCL};
     float* part = smem + 2 * H * NCL;
-    float* res = part + TACO_THREADS * 16;
-    float* cst = res + 32 * 16;  // [2][RBP][U]
+    float* res = part + TACO_THREADS * 16;   // [RBP][NCL]
+    float* cst = res + 32 * NCL;             // [2][32][U]
     for (int d = 0; d < 2; ++d) {
         const float4* src = reinterpret_cast<const float4*>(p.blobs + ((size_t)d * GN + nt) * p.blob_floats);
         float4* dst = reinterpret_cast<float4*>(Wh[d]);
         for (int i = tid; i < H * NCL / 4; i += TACO_THREADS) dst[i] = src[i];
     }
-    for (int i = tid; i < 2 * 32 * 4; i += TACO_THREADS) cst[i] = 0.f;
+    for (int i = tid; i < 2 * 32 * U; i += TACO_THREADS) cst[i] = 0.f;
     __syncthreads();
 
     GridBarrier gb{p.barrier, 0u, gridDim.x};
@@ -68,7 +69,7 @@ __global__ void __launch_bounds__(TACO_THREADS, 1) bilstm_persistent_kernel(BiLs
                         float zj = z[1 * U + ul] + xw[1 * H + u];
                         float zf = z[2 * U + ul] + xw[2 * H + u];
                         float zo_ = z[3 * U + ul] + xw[3 * H + u];
-                        float* cp = cst + (d * 32 + r) * 4 + ul;
+                        float* cp = cst + (d * 32 + r) * U + ul;
                         float c_prev = *cp;
                         float c_new = sigmoidf_(zf + 1.0f) * c_prev + sigmoidf_(zi) * tanhf(zj);
                         float h_new = sigmoidf_(zo_) * tanhf(c_new);
@@ -106,7 +107,7 @@ cudaError_t taco_launch_embedding(const int32_t* ids, const float* table, float*
 }
 
 cudaError_t taco_launch_bilstm(const BiLstmParams& p, cudaStream_t stream) {
-    size_t smem = (size_t)(2 * 256 * 4 * p.U + TACO_THREADS * 16 + 32 * 16 + 2 * 32 * 4) * sizeof(float);
+    size_t smem = (size_t)(2 * 256 * 4 * p.U + TACO_THREADS * 16 + 32 * 4 * p.U + 2 * 32 * p.U) * sizeof(float);
     cudaError_t e = cudaFuncSetAttribute(bilstm_persistent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     BiLstmParams pl = p;

@@ -79,6 +79,11 @@ class TacoEngine(object):
         self._check(self.L.taco_set_precision(self._h, code), "taco_set_precision")
         self.precision = precision
 
+    def set_encoder_ctas(self, max_ctas):
+        """Grid bound of the persistent BiLSTM (include/taco_b200.h taco_set_encoder_ctas): 0 = lowest latency, 32 = fits beside a
+        running cluster decoder."""
+        self._check(self.L.taco_set_encoder_ctas(self._h, int(max_ctas)), "taco_set_encoder_ctas")
+
     @property
     def launch_count(self):
         return int(self.L.taco_launch_count(self._h))
@@ -262,6 +267,11 @@ class EnginePool:
             raise ValueError("in_flight must be >= 1")
         self.device = device
         self.engines = [TacoEngine(hp, weights, device=device, precision=precision) for _ in range(in_flight)]
+        if in_flight > 1:
+            # the cluster decoder of one batch leaves 36 SMs free: a BiLSTM of <= 32 CTAs (instead of 128) runs on them, so the
+            # whole encoder of the next batch overlaps the decoder instead of waiting for it
+            for e in self.engines:
+                e.set_encoder_ctas(32)
         self.streams = [torch.cuda.Stream(device=device) for _ in range(in_flight)]
 
     def __len__(self):

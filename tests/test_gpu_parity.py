@@ -433,3 +433,22 @@ def test_bf16_mode_beyond_cluster_decoder_limits_is_exact_and_announced(capfd):
     err = capfd.readouterr().err
     assert "does not fit the bf16 cluster decoder" in err
     eng.close()
+
+
+def test_encoder_bilstm_32_cta_grid_equals_default(ctx):
+    """taco_set_encoder_ctas(32): the BiLSTM with 16 units per CTA (the grid that fits beside a running decoder) against the oracle
+    and against the default 128-CTA grid at B = 64."""
+    hp, w, eng, orc = ctx
+    ids, lens = synthetic.token_batch(hp, synthetic.cycle_lengths(64)[:40] + [7, 3] * 12)
+    gw = synthetic.gst_random_weights(hp)
+    a = _t(eng.encode(torch.from_numpy(ids), torch.from_numpy(lens), gst_weights=gw))
+    eng.set_encoder_ctas(32)
+    try:
+        b = _t(eng.encode(torch.from_numpy(ids), torch.from_numpy(lens), gst_weights=gw))
+    finally:
+        eng.set_encoder_ctas(0)
+    ref = orc.encode(ids, lens, gst_weights=gw).numpy()
+    np.testing.assert_allclose(b, ref, atol=1e-4)
+    np.testing.assert_allclose(b, a, atol=2e-5)
+    for i, n in enumerate(lens):
+        assert float(np.abs(b[i, n:, :512]).max(initial=0.0)) == 0.0
