@@ -383,8 +383,30 @@ __device__ __forceinline__ void att3_owner(const Dec3Params& p, float (&preR)[8]
 // (_compute_attention, Attention.py:345-366; bf16 values, fp32 accumulate).  Every CTA reduces its slice from the alignment rows
 // the owners multicast, then multicasts its three k-step blocks (B-fragment order) to the whole cluster: the reduction is spread
 // over 16 SMs' L2 ports instead of one per row, and nobody waits for the CTA that owns the longest row.
+#ifndef D3_UB
+#define D3_UB 5
+#endif
+// first batch of value rows of this thread's context-slice work (att3_context_slice): issued BEFORE the attention of the owners, so
+// that the L2 latency is behind the energies / softmax instead of in front of the context reduction
+struct CtxPre {
+    uint4 v[D3_UB];
+};
+__device__ __forceinline__ CtxPre att3_context_prefetch(const Dec3Params& p, uint32_t cmw, int row0, int rank, int tid) {
+    CtxPre r;
+    const int nslot = (cmw >> 12) & 255;
+    const int crow = cmw & 15, cslot = (cmw >> 4) & 255, len = cmw >> 20;
+    const int gidx = tid / 6, chunk = tid - gidx * 6;
+    const uint4* vp = reinterpret_cast<const uint4*>(p.values) + (size_t)(row0 + crow) * p.T * (MEM / 8) + 6 * rank + chunk;
+#pragma unroll
+    for (int u = 0; u < D3_UB; ++u) {
+        const int t = cslot + u * nslot;
+        r.v[u] = (nslot && t < len) ? ldg_stream_v4(vp + (size_t)t * (MEM / 8)) : make_uint4(0u, 0u, 0u, 0u);
+    }
+    return r;
+}
+
 __device__ __forceinline__ void att3_context_slice(const Dec3Params& p, uint32_t cmw, int row0, int R, int rank, int s, int tid,
-                                                   Guard3& g, bool tracing, uint32_t a_bytes) {
+                                                   Guard3& g, bool tracing, uint32_t a_bytes, const CtxPre& pre) {
     float* scr = SMF(SO_RED);
     const int TP = p.TP;
     __syncthreads();   // the K-split partials / query slices of this step (same scratch) have been read
@@ -398,9 +420,6 @@ __device__ __forceinline__ void att3_context_slice(const Dec3Params& p, uint32_t
         const uint4* vp = reinterpret_cast<const uint4*>(p.values) + (size_t)b * p.T * (MEM / 8) + 6 * rank + chunk;
         const uint32_t* al = SMU(SO_AALL) + crow * TP;
         float c[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-#ifndef D3_UB
-#define D3_UB 5
-#endif
         constexpr int UB = D3_UB;   // one round of loads for rows up to 8 x nslot positions (T = 111: nslot >= 14)
         for (int t0 = cslot; t0 < len; t0 += nslot * UB) {
             uint4 v[UB];
@@ -408,6 +427,10 @@ __device__ __forceinline__ void att3_context_slice(const Dec3Params& p, uint32_t
 #pragma unroll
             for (int u = 0; u < UB; ++u) {
                 const int t = t0 + u * nslot;
+#ifdef D3_CTX_PREFETCH
+                if (t0 == cslot) v[u] = pre.v[u];
+                else
+#endif
                 v[u] = (t < len && !(p.dbg & 32)) ? ldg_stream_v4(vp + (size_t)t * (MEM / 8)) : make_uint4(0u, 0u, 0u, 0u);
             }
             if (t0 == cslot) mbar_wait(MB_A, (uint32_t)(s & 1), g);   // after the value loads of the first batch are in flight

@@ -658,10 +658,15 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
         D3_TR(33)
         // ================= ATT: location-sensitive attention =================
         // owner of a cluster row: query, energies, softmax, alignment row -> every CTA; then every CTA: its 48 context columns
+#ifdef D3_CTX_PREFETCH
+        const CtxPre cpre = att3_context_prefetch(p, cmw, row0, rank, tid);
+#else
+        CtxPre cpre;
+#endif
 #ifndef D3_OWNER_FIRST
         if (att) att3_owner(p, preR, pre_scr, ab, alen, arow, s, tid, warp, lane, g, tacc, tprev, timing, tracing, Q_BYTES);
 #endif
-        att3_context_slice(p, cmw, row0, R, rank, s, tid, g, tracing, A_BYTES);
+        att3_context_slice(p, cmw, row0, R, rank, s, tid, g, tracing, A_BYTES, cpre);
         D3_STAMP(17)
         D3_TR(47)
         s_done = s + 1;
