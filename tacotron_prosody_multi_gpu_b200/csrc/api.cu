@@ -539,15 +539,29 @@ int decode_v3(TacoHandle* h, int mode, const float* memory, const int32_t* lens,
     if (ncl < 1) ncl = 1;
     // the alignment rows of a cluster live in every one of its CTAs: rows per cluster * round_up(T, 4) <= TACO_DEC3_ACAP words
     p.TP = (T + 3) & ~3;
-    while (ncl < h->dec3_max_clusters && ((B + ncl - 1) / ncl) * p.TP > TACO_DEC3_ACAP) ++ncl;
-    if (((B + ncl - 1) / ncl) * p.TP > TACO_DEC3_ACAP)
-        FAIL(TACO_ERR_UNSUPPORTED, "taco_decode: B x T too large for the cluster decoder (rows per cluster x T exceeds its alignment buffer)");
+    // T > 128: a row is split into position slices of 128, one attention work item (CTA) each, so that the location
+    // pre-activations stay in registers; rows per cluster * slices <= 16 CTAs.  (Not with cumulative_weights = False: the
+    // non-incremental location term needs the whole row in one CTA -- that case keeps the global scratch path.)
+    int parts = (T > 128 && hp.cumulative_weights && !getenv("TACO_DEC3_NO_PARTS")) ? (T + 127) / 128 : 1;
+    auto rows_of = [&](int n) { return (B + n - 1) / n; };
+    auto fits = [&](int n, int pp) { return rows_of(n) * p.TP <= TACO_DEC3_ACAP && rows_of(n) * pp <= TACO_DEC3_CLUSTER; };
+    int n2 = ncl;
+    while (n2 < h->dec3_max_clusters && !fits(n2, parts)) ++n2;
+    if (!fits(n2, parts)) {
+        parts = 1;
+        n2 = ncl;
+        while (n2 < h->dec3_max_clusters && !fits(n2, 1)) ++n2;
+        if (!fits(n2, 1))
+            FAIL(TACO_ERR_UNSUPPORTED, "taco_decode: B x T too large for the cluster decoder (rows per cluster x T exceeds its alignment buffer)");
+    }
+    ncl = n2;
+    p.parts = parts;
     p.R = (B + ncl - 1) / ncl;
     p.NCL = (B + p.R - 1) / p.R;
     p.S_max = S_max; p.S_cap = S_max; p.mode = mode;
     p.stop_at_any = hp.stop_at_any; p.cumulative = hp.cumulative_weights; p.smoothing = hp.smoothing;
     p.stop_sigmoid = logits_only ? 0 : 1;
-    p.pre_reg = T <= 128 ? 1 : 0;
+    p.pre_reg = (T <= 128 || p.parts > 1) ? 1 : 0;
     p.zoneout = hp.zoneout_rate;
     p.keep_scale = 1.0f / (1.0f - hp.dropout_rate);
     p.res_blobs = h->dec3_res;

@@ -76,10 +76,13 @@ constexpr int SO_TACC = SO_FLAG + 16;              // 24 x int64 stage timers
 constexpr int SO_OWN = SO_TACC + 48;             // [16]: cluster rank that owns the attention of cluster row i
 constexpr int SO_LEN = SO_OWN + 16;              // [16]: memory length of cluster row i
 constexpr int SO_GRP = SO_LEN + 16;              // [16][2]: first thread group / number of groups of row i in the context-slice reduction
-constexpr int SO_MBAR = SO_GRP + 32;             // 9 mbarriers (64-bit each): one per exchange buffer, one phase per decoder step
-constexpr int MB_P1 = 0, MB_P2 = 1, MB_H1R = 2, MB_H1Z = 3, MB_H2R = 4, MB_H2Z = 5, MB_CTX = 6, MB_Q = 7, MB_A = 8, N_MB = 9;
-constexpr int SO_KEEP = SO_MBAR + 2 * N_MB + 2;  // [2 prenet layers][16 rows]: 16 dropout keep bits (this CTA's units) of the step about to run
-constexpr int SO_AALL = SO_KEEP + 32;  // [R][TP] alignment rows of every cluster row, multicast by their owners
+constexpr int SO_MBAR = SO_GRP + 32;             // 10 mbarriers (64-bit each): one per exchange buffer, one phase per decoder step
+constexpr int MB_P1 = 0, MB_P2 = 1, MB_H1R = 2, MB_H1Z = 3, MB_H2R = 4, MB_H2Z = 5, MB_CTX = 6, MB_Q = 7, MB_A = 8, MB_PART = 9, N_MB = 10;
+constexpr int PART_T = 128;                      // positions per attention work item when a row is split (T > 128)
+constexpr int PART_MAX = 4;                      // T <= 512
+constexpr int SO_KEEP = SO_MBAR + 2 * N_MB + 4;  // [2 prenet layers][16 rows]: 16 dropout keep bits (this CTA's units) of the step about to run
+constexpr int SO_PART = SO_KEEP + 32;             // [PART_MAX][2]: (local maximum, local sum of exp) of every position slice of this CTA's row
+constexpr int SO_AALL = SO_PART + 2 * PART_MAX;  // [R][TP] alignment rows of every cluster row, multicast by their owners
 constexpr int A_CAP = TACO_DEC3_ACAP;            // words: R * TP <= A_CAP (the host picks the cluster count accordingly)
 constexpr int SMEM3_WORDS = SO_AALL + A_CAP;
 static_assert(RES_WORDS == TACO_DEC3_RES_WORDS, "resident blob size");

@@ -26,6 +26,27 @@ __device__ __forceinline__ void att3_build_pairs(int T, int tid, bool from_es = 
     }
 }
 
+// ... the same from the window [t0 - 15, t0 + Tl + 15) of a complete alignment row (position slices: the halo belongs to the
+// neighbouring slices); positions outside [0, rowlen) are 0
+__device__ __forceinline__ void att3_build_pairs_row(const float* row, int t0, int rowlen, int Tl, int tid) {
+    uint32_t* P = SMU(SO_P);
+    const int n = (Tl + 46) / 2 + 1;
+    auto val = [&](int i) -> float {
+        const int t = t0 + i - 15;
+        return (t >= 0 && t < rowlen) ? row[t] : 0.f;
+    };
+    for (int i = tid; i < n && i < PW3; i += NT) {
+        const float c0 = val(2 * i), c1 = val(2 * i + 1), c2 = val(2 * i + 2);
+        const float h0 = __bfloat162float(__float2bfloat16_rn(c0));
+        const float h1 = __bfloat162float(__float2bfloat16_rn(c1));
+        const float h2 = __bfloat162float(__float2bfloat16_rn(c2));
+        P[i] = pack_bf16x2(h0, h1);
+        P[PW3 + i] = pack_bf16x2(h1, h2);
+        P[2 * PW3 + i] = pack_bf16x2(c0 - h0, c1 - h1);
+        P[3 * PW3 + i] = pack_bf16x2(c1 - h1, c2 - h2);
+    }
+}
+
 // One 16-row tile of the location term: acc[t][d] = sum_k cum[t + k - 15] G[k][d], d = 8*warp + 2*tq (+1), rows t0+gq, t0+gq+8
 // (Attention.py:193-197 fused: conv1d(k=31, 32 filters) then Dense(128, no bias)); hi/lo bf16 split, 3 MMAs per k-step.
 struct G4 {
@@ -72,7 +93,7 @@ __device__ __forceinline__ void att3_loc_tile(float (&acc)[4], int t0, int lane,
 // incremental: the pair arrays hold the NEW alignments and the (linear) location term is accumulated: pre += T(a).G
 // -- no key reload from L2 (cumulative attention only).
 __device__ __forceinline__ void att3_location(const Dec3Params& p, float (&preR)[8][4], float* pre_scr, int b, int len, int warp, int lane,
-                                              bool incremental = false) {
+                                              bool incremental = false, int t_off = 0) {
     const int gq = lane >> 2, tq = lane & 3;
     uint2 ghi[2], glo[2];
 #pragma unroll
@@ -121,8 +142,8 @@ __device__ __forceinline__ void att3_location(const Dec3Params& p, float (&preR)
             if (t0 < len) {
                 const int ta = t0 + gq, tb = ta + 8;
                 float2 ka = make_float2(0.f, 0.f), kb = make_float2(0.f, 0.f);
-                if (ta < len) ka = __ldg(reinterpret_cast<const float2*>(p.keys + ((size_t)b * p.T + ta) * ATT + d0));
-                if (tb < len) kb = __ldg(reinterpret_cast<const float2*>(p.keys + ((size_t)b * p.T + tb) * ATT + d0));
+                if (ta < len) ka = __ldg(reinterpret_cast<const float2*>(p.keys + ((size_t)b * p.T + t_off + ta) * ATT + d0));
+                if (tb < len) kb = __ldg(reinterpret_cast<const float2*>(p.keys + ((size_t)b * p.T + t_off + tb) * ATT + d0));
                 float acc[4];
                 att3_loc_tile(acc, t0, lane, ghi, glo);
                 preR[i][0] = acc[0] + ka.x + bc0;
@@ -159,7 +180,7 @@ __device__ __forceinline__ int ctx_groups_of(int len, int total) { return (CTX_B
 // every CTA of the cluster (each of which reduces a 48-column slice of the context, att3_context_slice).
 __device__ __forceinline__ void att3_owner(const Dec3Params& p, float (&preR)[8][4], float* pre_scr, int b, int len, int arow, int s,
                                            int tid, int warp, int lane, Guard3& g, long long* tacc, long long& tprev, bool timing, bool tracing,
-                                           uint32_t q_bytes) {
+                                           uint32_t q_bytes, int apart, int tb0, int Tl) {
     float* scr = SMF(SO_RED);
 #ifdef TACO_DEC3_TRACE_BUILD
 #define A3_TR(i)                                                        \
@@ -332,7 +353,31 @@ __device__ __forceinline__ void att3_owner(const Dec3Params& p, float (&preR)[8]
             const float4 a = *reinterpret_cast<const float4*>(wred + 16 + 4 * i);
             sum += (a.x + a.y) + (a.z + a.w);
         }
-        const float inv = __fdividef(1.0f, sum);
+        float inv = __fdividef(1.0f, sum);
+        if (p.parts > 1) {
+            // position slices of one row: every slice sends (its maximum, its sum of exp) to the others; the row's softmax is
+            // exp(e - m_j) * exp(m_j - M) / sum_j s_j exp(m_j - M), M = max_j m_j
+            const int P = p.parts;
+            if (tid == 0) {
+                SMF(SO_PART)[2 * apart] = m;
+                SMF(SO_PART)[2 * apart + 1] = sum;
+            }
+            if (tid < P && tid != apart) {
+                const uint32_t peer = SMU(SO_OWN)[arow * P + tid];
+                asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v2.b32 [%0], {%1,%2}, [%3];"
+                             ::"r"(mapa_rank(smem_addr(SMU(SO_PART) + 2 * apart), peer)), "r"(__float_as_uint(m)), "r"(__float_as_uint(sum)),
+                               "r"(mapa_rank(smem_addr(SMU(SO_MBAR) + 2 * MB_PART), peer)) : "memory");
+            }
+            mbar_wait(MB_PART, (uint32_t)(s & 1), g);
+            __syncthreads();   // thread 0's own slot
+            float M = -INFINITY;
+            for (int j = 0; j < P; ++j) M = fmaxf(M, SMF(SO_PART)[2 * j]);
+            float Z = 0.f;
+            for (int j = 0; j < P; ++j) Z += SMF(SO_PART)[2 * j + 1] * __expf(SMF(SO_PART)[2 * j] - M);
+            inv = __expf(m - M) * __fdividef(1.0f, Z);   // an empty slice has m = -inf: factor 0
+            __syncthreads();   // every thread has read the slots before thread 0 re-arms the exchange for the next step
+            if (tid == 0 && !g.dead) mbar_rearm(MB_PART, (uint32_t)(P - 1) * 8u);
+        }
         if (part == 0) SMF(SO_ES)[t] = v * inv;   // t < PRE_REG_T always; exact zeros beyond the length
     } else if (warp == 0) {
         float m = -INFINITY;
@@ -362,19 +407,20 @@ __device__ __forceinline__ void att3_owner(const Dec3Params& p, float (&preR)[8]
             const int slot = i / nv, v = i - slot * nv;
             const int dst = (slot + arow) & (CS - 1);
             const uint4 val = *reinterpret_cast<const uint4*>(SMU(SO_ES) + (v << 2));
-            st_async_v4(mapa_rank(smem_addr(SMU(SO_AALL) + arow * TP + (v << 2)), dst), val, mapa_rank(smem_addr(SMU(SO_MBAR) + 2 * MB_A), dst));
+            st_async_v4(mapa_rank(smem_addr(SMU(SO_AALL) + arow * TP + tb0 + (v << 2)), dst), val, mapa_rank(smem_addr(SMU(SO_MBAR) + 2 * MB_A), dst));
         }
     }
     A3_TR(38)
     // E4: cumulate + alignment history
-    for (int t = tid; t < p.T; t += NT) {
+    for (int t = tid; t < Tl; t += NT) {
         const float a = t < len ? SMF(SO_ES)[t] : 0.f;
         SMF(SO_CPAD)[15 + t] = p.cumulative ? SMF(SO_CPAD)[15 + t] + a : a;
-        p.hist[((size_t)s * p.B + b) * p.T + t] = a;
+        p.hist[((size_t)s * p.B + b) * p.T + tb0 + t] = a;
     }
     if (!p.cumulative) __syncthreads();
-    // pair arrays of the new alignments for the location term of the next step (att3_loc_chunk, in the shadow of later exchanges)
-    att3_build_pairs(p.T, tid, p.cumulative != 0, len);
+    // pair arrays of the new alignments for the location term of the next step (att3_loc_chunk, in the shadow of later exchanges);
+    // position slices build them after the alignment exchange, from the complete row (att3_build_pairs_row)
+    if (p.parts == 1) att3_build_pairs(Tl, tid, p.cumulative != 0, len);
     A3_STAMP(15)
     A3_TR(39)
 }

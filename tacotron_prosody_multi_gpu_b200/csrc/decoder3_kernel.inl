@@ -194,18 +194,26 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
         c2s = p.c2[(size_t)eb * DEC + 16 * rank + eu];
         h2s = p.h2z[(size_t)eb * DEC + 16 * rank + eu];
     }
-    // attention work items: one cluster row per CTA, dealt by length to ranks 0..9, 11..15 and last to rank 10, which
-    // also computes the stop-token projection of the cluster (a cluster of <= 15 rows leaves it without a row).
+    // attention work items: item = row * P + part (P = 1: the whole row; P > 1: position slice [128 part, 128 part + 128) of the
+    // row, so that a long row (T > 128) is spread over P CTAs and keeps its pre-activations in registers), one item per CTA,
+    // dealt by (local) length to ranks 0..9, 11..15 and last to rank 10, which also computes the stop-token projection of the
+    // cluster (<= 15 items leave it without one).  The host guarantees R * P <= 16.
+    const int P = p.parts;
+    auto item_len = [&](int item) -> int {
+        const int l = p.lens[row0 + item / P];
+        return P == 1 ? l : max(0, min(PART_T, l - PART_T * (item % P)));
+    };
     if (tid < 16) {
         int pos = 0;
-        if (tid < R) {
-            const int mylen = p.lens[row0 + tid];
-            for (int r2 = 0; r2 < R; ++r2) {
-                const int l2 = p.lens[row0 + r2];
+        const int items = R * P;
+        if (tid < items) {
+            const int mylen = item_len(tid);
+            for (int r2 = 0; r2 < items; ++r2) {
+                const int l2 = item_len(r2);
                 pos += (l2 > mylen || (l2 == mylen && r2 < tid)) ? 1 : 0;
             }
         }
-        SMU(SO_OWN)[tid] = tid < R ? (pos < STOP_RANK ? pos : (pos < CS - 1 ? pos + 1 : STOP_RANK)) : 0xFFFFu;
+        SMU(SO_OWN)[tid] = tid < items ? (pos < STOP_RANK ? pos : (pos < CS - 1 ? pos + 1 : STOP_RANK)) : 0xFFFFu;
         SMU(SO_LEN)[tid] = tid < R ? (uint32_t)p.lens[row0 + tid] : 0u;
     }
     __syncthreads();
@@ -235,24 +243,30 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
             if (gidx >= g0 && gidx < g0 + ng) cmw = (uint32_t)r2 | ((uint32_t)(gidx - g0) << 4) | ((uint32_t)ng << 12) | (SMU(SO_LEN)[r2] << 20);
         }
     }
-    int arow = -1;
-    for (int r2 = 0; r2 < R; ++r2)
-        if ((int)SMU(SO_OWN)[r2] == rank) arow = r2;
-    const bool att = arow >= 0;
+    int aitem = -1;
+    for (int r2 = 0; r2 < R * P; ++r2)
+        if ((int)SMU(SO_OWN)[r2] == rank) aitem = r2;
+    const bool att = aitem >= 0;
+    const int arow = att ? aitem / P : -1, apart = att ? aitem % P : 0;
     const int ab = row0 + (att ? arow : 0);
-    const int alen = att ? p.lens[ab] : 0;
-    float* pre_scr = p.pre_scratch + (size_t)ab * p.T * ATT;   // [T][128]: working copy when !pre_reg, saved state otherwise
+    const int tb0 = P == 1 ? 0 : PART_T * apart;                 // first position of this item
+    const int Tl = P == 1 ? p.T : max(0, min(PART_T, p.T - tb0));   // positions it covers (valid ones: alen)
+    const int alen = att ? item_len(aitem) : 0;
+    float* pre_scr = p.pre_scratch + ((size_t)ab * p.T + tb0) * ATT;   // [T][128]: working copy when !pre_reg, saved state otherwise
     float preR[8][4];
 #pragma unroll
     for (int i = 0; i < 8; ++i) preR[i][0] = preR[i][1] = preR[i][2] = preR[i][3] = 0.f;
     __syncthreads();
     if (att) {
-        for (int t = tid; t < p.T; t += NT) SMF(SO_CPAD)[15 + t] = p.cum[(size_t)ab * p.T + t];
+        for (int i = tid; i < Tl + 30; i += NT) {   // cumulative alignments of the item's window, 15 positions of halo on both sides
+            const int t = tb0 + i - 15;
+            SMF(SO_CPAD)[i] = (t >= 0 && t < p.T) ? p.cum[(size_t)ab * p.T + t] : 0.f;
+        }
         __syncthreads();
-        att3_build_pairs(p.T, tid);
+        att3_build_pairs(Tl, tid);
         __syncthreads();
         if (!p.cont || !p.cumulative) {
-            att3_location(p, preR, pre_scr, ab, alen, warp, lane);
+            att3_location(p, preR, pre_scr, ab, alen, warp, lane, false, tb0);
         } else if (p.pre_reg) {
             // continuation launch: the accumulated pre-activations were saved by the previous launch (keeps cell stepping
             // bit-identical to one multi-step launch)
@@ -277,6 +291,7 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
         for (int mb = MB_P1; mb <= MB_H2Z; ++mb) mbar_rearm(mb, BLK_BYTES);
         mbar_rearm(MB_CTX, CTX_BYTES);
         if (att) mbar_rearm(MB_Q, Q_BYTES);
+        if (att && P > 1) mbar_rearm(MB_PART, (uint32_t)(P - 1) * 8u);
         mbar_rearm(MB_A, A_BYTES);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -618,8 +633,10 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
                 const int row = tid >> 5, v = tid & 31;
                 if (row < R) {
                     const uint4 val = *reinterpret_cast<const uint4*>(red + row * ATT + (v << 2));
-                    const uint32_t own = SMU(SO_OWN)[row];
-                    st_async_v4(mapa_rank(smem_addr(SMU(SO_QRECV) + rank * ATT + (v << 2)), own), val, mapa_rank(smem_addr(SMU(SO_MBAR) + 2 * MB_Q), own));
+                    for (int j = 0; j < P; ++j) {   // every position slice of the row needs the query
+                        const uint32_t own = SMU(SO_OWN)[row * P + j];
+                        st_async_v4(mapa_rank(smem_addr(SMU(SO_QRECV) + rank * ATT + (v << 2)), own), val, mapa_rank(smem_addr(SMU(SO_MBAR) + 2 * MB_Q), own));
+                    }
                 }
             }
             multicast_block(SMU(SO_STG_R), SMU(SO_H2R), MB_H2R, rank, R, tid);
@@ -638,7 +655,7 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
         }
 #ifdef D3_OWNER_FIRST
         // the owners' alignment rows are what every other CTA waits for: before the zoned-state contributions
-        if (att) att3_owner(p, preR, pre_scr, ab, alen, arow, s, tid, warp, lane, g, tacc, tprev, timing, tracing, Q_BYTES);
+        if (att) att3_owner(p, preR, pre_scr, ab, alen, arow, s, tid, warp, lane, g, tacc, tprev, timing, tracing, Q_BYTES, apart, tb0, Tl);
 #endif
         // ---- zoned states of this step -> gates of the next step (in the shadow of the query exchange) ----
         D3_PREPOLL(SMU(SO_H1Z), KS_H)
@@ -664,9 +681,12 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
         CtxPre cpre;
 #endif
 #ifndef D3_OWNER_FIRST
-        if (att) att3_owner(p, preR, pre_scr, ab, alen, arow, s, tid, warp, lane, g, tacc, tprev, timing, tracing, Q_BYTES);
+        if (att) att3_owner(p, preR, pre_scr, ab, alen, arow, s, tid, warp, lane, g, tacc, tprev, timing, tracing, Q_BYTES, apart, tb0, Tl);
 #endif
         att3_context_slice(p, cmw, row0, R, rank, s, tid, g, tracing, A_BYTES, cpre);
+        // a position slice needs the alignments of its neighbours (15 positions of halo) for the location term of the next step:
+        // pair arrays from the complete row every CTA holds after the alignment exchange
+        if (att && P > 1) att3_build_pairs_row(SMF(SO_AALL) + arow * p.TP, tb0, (int)SMU(SO_LEN)[arow], Tl, tid);
         D3_STAMP(17)
         D3_TR(47)
         s_done = s + 1;
@@ -697,7 +717,7 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
         p.h2raw[(size_t)eb * DEC + 16 * rank + eu] = h2r_last;
     }
     if (att) {
-        for (int t = tid; t < p.T; t += NT) p.cum[(size_t)ab * p.T + t] = SMF(SO_CPAD)[15 + t];
+        for (int t = tid; t < Tl; t += NT) p.cum[(size_t)ab * p.T + tb0 + t] = SMF(SO_CPAD)[15 + t];
         if (p.pre_reg) {
             const int gq = lane >> 2, tq = lane & 3, d0 = warp * 8 + 2 * tq;
 #pragma unroll

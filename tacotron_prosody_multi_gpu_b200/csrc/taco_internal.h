@@ -52,14 +52,15 @@ cudaError_t taco_launch_transpose_alignments(const float* hist, float* out, int 
 #define TACO_DEC3_TMAX 512
 #define TACO_DEC3_RES_WORDS (221 * 128 + 176)
 #define TACO_DEC3_STREAM_TILES 320
-#define TACO_DEC3_ACAP 1408   // shared-memory words for the alignment rows of one cluster: rows per cluster * round_up(T, 4) <= this
+#define TACO_DEC3_ACAP 1392   // shared-memory words for the alignment rows of one cluster: rows per cluster * round_up(T, 4) <= this
 
 struct Dec3Params {
     int B, T, NCL, R;       // NCL clusters; cluster i owns batch rows [i*R, min(B, i*R + R))
     int TP;                 // round_up(T, 4): row stride of the per-cluster alignment rows (R * TP <= TACO_DEC3_ACAP)
     int S_max, S_cap, t0, mode;
     int stop_at_any, cumulative, smoothing, stop_sigmoid;
-    int pre_reg;            // T <= 128: location pre-activations live in registers (else in pre_scratch)
+    int pre_reg;            // location pre-activations live in registers (T <= 128, or any T split into parts) -- else in pre_scratch
+    int parts;              // attention work items per row: 1, or ceil(T / 128) position slices of 128 owned by different CTAs
     int dbg;                // experiment bitmask (TACO_DEC3_DBG): 1 = never consume the stop flags
     int cont;               // continuation launch (reset_state == 0): pre-activations are loaded from pre_scratch
     float zoneout, keep_scale;
