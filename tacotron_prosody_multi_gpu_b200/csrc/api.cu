@@ -624,9 +624,6 @@ int decode_v3(TacoHandle* h, int mode, const float* memory, const int32_t* lens,
     CK(cudaMemsetAsync(flags, 0, n_flags * sizeof(int), st));
     p.flags = flags;
     p.abort_flag = flags + (size_t)S_max * p.NCL + 4;
-    WS(stop_part, float, "dec3_stop_part", (size_t)TACO_DEC3_MAX_CLUSTERS * 2 * TACO_DEC3_CLUSTER * 32)
-    CK(cudaMemsetAsync(stop_part, 0xFF, (size_t)TACO_DEC3_MAX_CLUSTERS * 2 * TACO_DEC3_CLUSTER * 32 * sizeof(float), st));
-    p.stop_part = stop_part;
     if (getenv("TACO_DEC2_TIMING")) {
         WS(timing, long long, "dec2_timing", (size_t)TACO_DEC3_CLUSTER * TACO_DEC3_MAX_CLUSTERS * 24)
         CK(cudaMemsetAsync(timing, 0, (size_t)TACO_DEC3_CLUSTER * TACO_DEC3_MAX_CLUSTERS * 24 * sizeof(long long), st));

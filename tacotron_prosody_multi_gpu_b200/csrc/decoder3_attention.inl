@@ -262,57 +262,6 @@ __device__ __forceinline__ void att3_owner(const Dec3Params& p, float (&preR)[8]
     __syncthreads();
     A3_STAMP(16)
     A3_TR(36)
-#ifdef D3_OLD_SOFTMAX
-    // E3: masked softmax over t < len (exact zeros beyond: -inf mask), Attention.py:203-206
-    if (warp == 0) {
-        if (p.pre_reg) {
-            // whole row in registers: 4 positions per lane, each the sum of the 16 per-warp partials
-            float e[4];
-            float m = -INFINITY;
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const int t = lane + 32 * i;
-                float x = 0.f;
-                if (t < len) {
-#pragma unroll
-                    for (int w = 0; w < 16; ++w) x += scr[w * PRE_REG_T + t];
-                }
-                e[i] = t < len ? x : -INFINITY;
-                m = fmaxf(m, e[i]);
-            }
-            m = p.smoothing ? 0.f : warp_max(m);
-            float sum = 0.f;
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const int t = lane + 32 * i;
-                e[i] = t < len ? (p.smoothing ? sigmoidf_(e[i]) : __expf(e[i] - m)) : 0.f;
-                sum += e[i];
-            }
-            sum = warp_sum(sum);
-            const float inv = __fdividef(1.0f, sum);
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const int t = lane + 32 * i;
-                if (t < PRE_REG_T) SMF(SO_ES)[t] = e[i] * inv;   // exact zeros beyond the length
-            }
-        } else {
-            float m = -INFINITY;
-            if (!p.smoothing) {
-                for (int t = lane; t < len; t += 32) m = fmaxf(m, SMF(SO_ES)[t]);
-                m = warp_max(m);
-            }
-            float sum = 0.f;
-            for (int t = lane; t < len; t += 32) {
-                const float v = p.smoothing ? sigmoidf_(SMF(SO_ES)[t]) : __expf(SMF(SO_ES)[t] - m);
-                SMF(SO_ES)[t] = v;
-                sum += v;
-            }
-            sum = warp_sum(sum);
-            const float inv = 1.0f / sum;
-            for (int t = lane; t < len; t += 32) SMF(SO_ES)[t] *= inv;
-        }
-    }
-#else
     // E3: masked softmax over t < len (exact zeros beyond: -inf mask), Attention.py:203-206
     if (p.pre_reg) {
         // all 512 threads: thread (position t = tid >> 2, quarter = tid & 3) adds 4 of the 16 per-warp partials of e[t]; a warp
@@ -395,7 +344,6 @@ __device__ __forceinline__ void att3_owner(const Dec3Params& p, float (&preR)[8]
         const float inv = 1.0f / sum;
         for (int t = lane; t < len; t += 32) SMF(SO_ES)[t] *= inv;
     }
-#endif
     __syncthreads();
     A3_STAMP(10)
     A3_TR(37)
@@ -432,27 +380,8 @@ __device__ __forceinline__ void att3_owner(const Dec3Params& p, float (&preR)[8]
 #ifndef D3_UB
 #define D3_UB 5
 #endif
-// first batch of value rows of this thread's context-slice work (att3_context_slice): issued BEFORE the attention of the owners, so
-// that the L2 latency is behind the energies / softmax instead of in front of the context reduction
-struct CtxPre {
-    uint4 v[D3_UB];
-};
-__device__ __forceinline__ CtxPre att3_context_prefetch(const Dec3Params& p, uint32_t cmw, int row0, int rank, int tid) {
-    CtxPre r;
-    const int nslot = (cmw >> 12) & 255;
-    const int crow = cmw & 15, cslot = (cmw >> 4) & 255, len = cmw >> 20;
-    const int gidx = tid / 6, chunk = tid - gidx * 6;
-    const uint4* vp = reinterpret_cast<const uint4*>(p.values) + (size_t)(row0 + crow) * p.T * (MEM / 8) + 6 * rank + chunk;
-#pragma unroll
-    for (int u = 0; u < D3_UB; ++u) {
-        const int t = cslot + u * nslot;
-        r.v[u] = (nslot && t < len) ? ldg_stream_v4(vp + (size_t)t * (MEM / 8)) : make_uint4(0u, 0u, 0u, 0u);
-    }
-    return r;
-}
-
 __device__ __forceinline__ void att3_context_slice(const Dec3Params& p, uint32_t cmw, int row0, int R, int rank, int s, int tid,
-                                                   Guard3& g, bool tracing, uint32_t a_bytes, const CtxPre& pre) {
+                                                   Guard3& g, bool tracing, uint32_t a_bytes) {
     float* scr = SMF(SO_RED);
     const int TP = p.TP;
     __syncthreads();   // the K-split partials / query slices of this step (same scratch) have been read
@@ -466,17 +395,13 @@ __device__ __forceinline__ void att3_context_slice(const Dec3Params& p, uint32_t
         const uint4* vp = reinterpret_cast<const uint4*>(p.values) + (size_t)b * p.T * (MEM / 8) + 6 * rank + chunk;
         const uint32_t* al = SMU(SO_AALL) + crow * TP;
         float c[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-        constexpr int UB = D3_UB;   // one round of loads for rows up to 8 x nslot positions (T = 111: nslot >= 14)
+        constexpr int UB = D3_UB;   // value rows in flight per thread and round (8 measured slower: registers)
         for (int t0 = cslot; t0 < len; t0 += nslot * UB) {
             uint4 v[UB];
             float a[UB];
 #pragma unroll
             for (int u = 0; u < UB; ++u) {
                 const int t = t0 + u * nslot;
-#ifdef D3_CTX_PREFETCH
-                if (t0 == cslot) v[u] = pre.v[u];
-                else
-#endif
                 v[u] = (t < len && !(p.dbg & 32)) ? ldg_stream_v4(vp + (size_t)t * (MEM / 8)) : make_uint4(0u, 0u, 0u, 0u);
             }
             if (t0 == cslot) mbar_wait(MB_A, (uint32_t)(s & 1), g);   // after the value loads of the first batch are in flight

@@ -33,61 +33,6 @@ constexpr int ACT_W = 1024;     // projection input row: [h2raw 256 | context 76
 #define D3_PREPOLL(buf, KS)
 #endif
 
-// Stop-token projection (StopProjection, Decoder.py:404-410; batch-global decision of TacoTestHelper.next_inputs, Helpers.py:36-59):
-// y = [h2raw ; context] . Ws[1024 x 2] + bs, K-split over the cluster so that no CTA carries it on the critical path.
-// Part 1 (one warp of EVERY CTA, in the shadow of the dense_1 exchange of the following step): the 4 k-steps this CTA produced itself
-// (its 16 h2raw units, its 48 context columns) as one m16 tile whose rows 0..1 are the two stop units -> 32 partial sums
-// [unit][cluster row] stored to the global exchange slot of (cluster, step parity, rank).
-__device__ __forceinline__ void dec3_stop_partial(const Dec3Params& p, int s_idx, int cid, int rank, int lane, Guard3& g) {
-    float acc[2][4] = {};
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        const int ks = i == 0 ? rank : 16 + 3 * rank + (i - 1);
-        const uint4 a = __ldg(p.stop_tiles + (size_t)ks * 32 + lane);
-        const uint32_t* blk = i == 0 ? SMU(SO_H2R) + rank * TILE_W : SMU(SO_CTX) + (3 * rank + i - 1) * TILE_W;
-#pragma unroll
-        for (int j = 0; j < 2; ++j) {
-            const uint2 b = load_b(blk, j, lane, g);
-            mma16816(acc[j], a, b);
-        }
-    }
-    const int gq = lane >> 2, tq = lane & 3;
-    if (gq < 2) {
-        float* dst = p.stop_part + ((((size_t)cid * 2 + (s_idx & 1)) * CS + rank) * 32) + gq * 16 + 2 * tq;
-#pragma unroll
-        for (int j = 0; j < 2; ++j) {
-            stg_relaxed(reinterpret_cast<uint32_t*>(dst + 8 * j), __float_as_uint(acc[j][0]));
-            stg_relaxed(reinterpret_cast<uint32_t*>(dst + 8 * j + 1), __float_as_uint(acc[j][1]));
-        }
-    }
-}
-// Part 2 (warp 0 of the stop rank, one step later: the partials have long arrived): lane = 2 * cluster row + unit sums the 16
-// partials in rank order, applies the sigmoid, writes the stop token and publishes the cluster's stop bit of that step.
-__device__ __forceinline__ void dec3_stop_finish(const Dec3Params& p, int s_idx, int row0, int R, int cid, bool free_run, int lane, Guard3& g) {
-    const int er = lane >> 1, eu = lane & 1;
-    uint32_t* src = reinterpret_cast<uint32_t*>(p.stop_part) + (((size_t)cid * 2 + (s_idx & 1)) * CS) * 32 + eu * 16 + er;
-    float y = p.stop_bias[eu];
-    bool fin = false;
-    if (er < R) {
-#pragma unroll 4
-        for (int k = 0; k < CS; ++k) {
-            uint32_t w = ldg_relaxed(src + k * 32);
-            int spins = 0;
-            while (w == SENT && !spin_check3(g, spins)) w = ldg_relaxed(src + k * 32);
-            y += __uint_as_float(w);
-        }
-        const float sg = sigmoidf_(y);
-        p.stop[(size_t)(row0 + er) * p.S_cap * 2 + (size_t)s_idx * 2 + eu] = p.stop_sigmoid ? sg : y;
-        fin = sg > 0.5f;   // tf.round(sigmoid) == 1 <=> sigmoid > 0.5 (half-to-even; Helpers.py:40)
-    }
-#pragma unroll 4
-    for (int k = 0; k < CS; ++k) stg_relaxed(src + k * 32, SENT);   // re-arm the slot for step s_idx + 2 (rows >= R too: harmless)
-    const int cnt = __popc(__ballot_sync(0xffffffffu, fin));
-    if (free_run && lane == 0)
-        stg_relaxed(reinterpret_cast<uint32_t*>(p.flags) + (size_t)s_idx * p.NCL + cid, (p.stop_at_any ? cnt > 0 : cnt == 2 * R) ? 2u : 1u);
-}
-
-#ifndef D3_DIST_STOP
 // Stop-token projection of launch step s_idx for the rows of this cluster (StopProjection, Decoder.py:404-410; the batch-global
 // decision of TacoTestHelper.next_inputs, Helpers.py:36-59): [h2raw ; context] . Ws[1024 x 2] as 64 k-steps of one m16 tile whose
 // rows 0..1 are the two stop units.  Runs on ONE rank per cluster, off the critical path; its tiles stream from L2.
@@ -125,7 +70,6 @@ __device__ __noinline__ void dec3_stop_token(const Dec3Params& p, int s_idx, int
         stg_relaxed(reinterpret_cast<uint32_t*>(p.flags) + (size_t)s_idx * p.NCL + cid, (p.stop_at_any ? cnt > 0 : cnt == 2 * R) ? 2u : 1u);
 }
 
-#endif
 // Prenet dropout bits (always on, Decoder.py:350-351) of `step` for this CTA's 16 units of both layers and every cluster row:
 // ONE Philox block per (row, layer) -- thread i < 2R: row i >> 1, layer i & 1 -- instead of one per (row, layer, unit).
 __device__ __forceinline__ void keep_bits_step(const Dec3Params& p, int step, int row0, int R, int rank, int tid) {
@@ -455,25 +399,14 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
             }
             D3_STAMP(11)
             D3_TR(7)
-            // stop token (Decoder.py:404-410; Helpers.py:36-59): this CTA's K-slice of step s-1; the stop rank finishes step s-2
-#ifndef D3_DIST_STOP
+            // stop token of step s-1 (Decoder.py:404-410; Helpers.py:36-59), on the one rank that owns no long attention item
             if (rank == STOP_RANK) dec3_stop_token(p, s - 1, row0, R, cid, free_run, red, tid, warp, lane, g);
-#else
-            if (!(p.dbg & 4)) {
-                if (warp == 15) dec3_stop_partial(p, s - 1, cid, rank, lane, g);
-                if (rank == STOP_RANK && warp == 0 && s >= 2) dec3_stop_finish(p, s - 2, row0, R, cid, free_run, lane, g);
-            } else if (rank == STOP_RANK && free_run && tid == 0 && s >= 2) {
-                stg_relaxed(reinterpret_cast<uint32_t*>(p.flags) + (size_t)(s - 2) * p.NCL + cid, 1u);
-            }
-#endif
             D3_STAMP(12)
             D3_TR(8)
         }
         uint4 aW1P[4];
         prefetch4(aW1P, sW1P, kg, lane);   // used two exchanges later (L1)
-#ifndef D3_DIST_STOP
         if (rank == STOP_RANK && s > 0) __syncthreads();   // the stop token's reduction scratch is reused by dense_2 (CTA-uniform branch)
-#endif
         D3_TR(9)
         D3_PREPOLL(SMU(SO_P1), KS_H)
         D3_TR(10)
@@ -653,10 +586,6 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
         } else {
             keep_bits_step(p, step + 1, row0, R, rank, tid);   // both layers' bits of this step were read in the dense_1 epilogue
         }
-#ifdef D3_OWNER_FIRST
-        // the owners' alignment rows are what every other CTA waits for: before the zoned-state contributions
-        if (att) att3_owner(p, preR, pre_scr, ab, alen, arow, s, tid, warp, lane, g, tacc, tprev, timing, tracing, Q_BYTES, apart, tb0, Tl);
-#endif
         // ---- zoned states of this step -> gates of the next step (in the shadow of the query exchange) ----
         D3_PREPOLL(SMU(SO_H1Z), KS_H)
         D3_PREPOLL(SMU(SO_H2Z), KS_H)
@@ -675,15 +604,8 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
         D3_TR(33)
         // ================= ATT: location-sensitive attention =================
         // owner of a cluster row: query, energies, softmax, alignment row -> every CTA; then every CTA: its 48 context columns
-#ifdef D3_CTX_PREFETCH
-        const CtxPre cpre = att3_context_prefetch(p, cmw, row0, rank, tid);
-#else
-        CtxPre cpre;
-#endif
-#ifndef D3_OWNER_FIRST
         if (att) att3_owner(p, preR, pre_scr, ab, alen, arow, s, tid, warp, lane, g, tacc, tprev, timing, tracing, Q_BYTES, apart, tb0, Tl);
-#endif
-        att3_context_slice(p, cmw, row0, R, rank, s, tid, g, tracing, A_BYTES, cpre);
+        att3_context_slice(p, cmw, row0, R, rank, s, tid, g, tracing, A_BYTES);
         // a position slice needs the alignments of its neighbours (15 positions of halo) for the location term of the next step:
         // pair arrays from the complete row every CTA holds after the alignment exchange
         if (att && P > 1) att3_build_pairs_row(SMF(SO_AALL) + arow * p.TP, tb0, (int)SMU(SO_LEN)[arow], Tl, tid);
@@ -694,15 +616,7 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
     // what the next iteration would have done for the last executed step: its stop token (the context and h2raw blocks are
     // still in place) and the location term of the following step (saved below for a continuation launch)
     if (!stopped && s_done > 0) {
-#ifndef D3_DIST_STOP
         if (rank == STOP_RANK) dec3_stop_token(p, s_done - 1, row0, R, cid, free_run, red, tid, warp, lane, g);
-#else
-        if (warp == 15) dec3_stop_partial(p, s_done - 1, cid, rank, lane, g);
-        if (rank == STOP_RANK && warp == 0) {
-            if (s_done >= 2) dec3_stop_finish(p, s_done - 2, row0, R, cid, free_run, lane, g);
-            dec3_stop_finish(p, s_done - 1, row0, R, cid, free_run, lane, g);   // polls for the partials sent just above
-        }
-#endif
         if (att) att3_loc_chunk(p, preR, pre_scr, ab, alen, warp, lane, 0, 8);
     }
 

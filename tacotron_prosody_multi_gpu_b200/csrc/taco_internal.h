@@ -67,7 +67,6 @@ struct Dec3Params {
     const uint32_t* res_blobs;   // [16 ranks][TACO_DEC3_RES_WORDS] A-fragment tiles resident in shared memory + fp32 biases
     const uint4* stream_blobs;   // [16 ranks][320 tiles][32 lanes] A-fragment tiles streamed from L2: W1c [4][48], W1h [4][16], W2z [4][16]
     const uint4* stop_tiles;     // [64 k-steps][32 lanes] A-fragment tiles of the stop projection (rows 0..1 of the m16 tile)
-    float* stop_part;            // [NCL][2 step parities][16 ranks][2 units x 16 rows] K-split partial sums of the stop projection (all-ones bits = empty)
     float stop_bias[2];
     const uint32_t *g_hi, *g_lo; // G = conv31 . Wl, B-fragment-major [2 ks][16 nt][32 lanes][2], hi / lo bf16 split
     const float *va, *bconst;    // [128] attention_variable; attention_bias + conv_bias . Wl
