@@ -320,7 +320,10 @@ def extra_configs(args, hp, w, dev, rank, world, dist):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t0 = time.perf_counter()
     e0.record()
-    res = sharding.synthesize_batches(pool, hp, seqs, rank, world, 64, gw, S_cap, seed)
+    store = None
+    if world > 1 and not args.c3_static:
+        store = dist.distributed_c10d._get_default_store()   # control plane only: a shared "next batch" counter
+    res = sharding.synthesize_batches(pool, hp, seqs, rank, world, 64, gw, S_cap, seed, store=store, store_key="taco_b200/c3/%d" % args.steps)
     for st in pool.streams:
         torch.cuda.current_stream().wait_stream(st)
     e1.record()
@@ -343,9 +346,10 @@ def extra_configs(args, hp, w, dev, rank, world, dist):
         a = np.stack([x.cpu().numpy() for x in allst])
         job_ms = float(a[:, 0].max())
         steps_list = sorted(steps_by_batch.values())
-        out["c3"] = {"workload": "%d utterances (256 x the sentences.txt lengths, shuffled seed 1324), sorted into batches of 64, LPT-assigned to "
-                                 "%d rank(s), no collective; stop kernel x8, bias %.3f calibrated on one batch: every batch stops at its own "
-                                 "first any-row crossing (cap %d steps); host token arrays in, trimmed host mels out" % (n_utt, world, bias, S_cap),
+        plan = "static LPT plan by estimated cost" if (world == 1 or args.c3_static) else "claimed dynamically from a shared counter in the rendezvous store"
+        out["c3"] = {"workload": "%d utterances (256 x the sentences.txt lengths, shuffled seed 1324), sorted into batches of 64, assigned to "
+                                 "%d rank(s) (%s), no collective; stop kernel x8, bias %.3f calibrated on one batch: every batch stops at its own "
+                                 "first any-row crossing (cap %d steps); host token arrays in, trimmed host mels out" % (n_utt, world, plan, bias, S_cap),
                      "scaling": "strong", "utterances": int(a[:, 3].sum()), "valid_mel_frames_per_sec": float(a[:, 1].sum()) / (job_ms * 1e-3),
                      "padded_mel_frames_per_sec": float(a[:, 2].sum()) / (job_ms * 1e-3), "job_ms": job_ms,
                      "rank_busy_ms": [float(x) for x in a[:, 0]], "rank_decoder_steps": [int(x) for x in a[:, 4]],
@@ -531,6 +535,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extra", action="store_true", help="skip the `configs` record (C2 B=1, C3, C5, fp32 mode)")
     ap.add_argument("--c3-utterances", type=int, default=4096)
+    ap.add_argument("--c3-static", action="store_true", help="C3 at N > 1: static LPT plan instead of dynamic claiming")
     ap.add_argument("--workload", default="c2", choices=["c2", "c4"],
                     help="c2: the headline (free-running synthesis, B=64/GPU); c4: the data-parallel training step (scripts/bench_train.py)")
     ap.add_argument("--in-flight", type=int, default=2, help="independent batches in flight per GPU (engine.EnginePool)")

@@ -48,12 +48,26 @@ def shard(lengths, world, batch_size=64, frames_per_token=13.0, r=2, measured_st
     return batches, assign_batches(costs, world)
 
 
+class _Ticket(object):
+    """Dynamic batch assignment: a shared counter in the job's rendezvous store (control plane only -- no tensor ever crosses
+    ranks).  Every call hands out the next batch index of the common, cost-sorted order; the reference's batch-global stop makes
+    the cost of a batch data dependent (Helpers.py:51-52), which a static plan cannot see."""
+
+    def __init__(self, store, key):
+        self.store, self.key = store, key
+
+    def next(self):
+        return int(self.store.add(self.key, 1)) - 1
+
+
 def synthesize_batches(engine, hp, seqs, rank=0, world=1, batch_size=64, gst_weights=None, max_iters=None, philox_seed=None,
-                       fetch=("mel_outputs", "stop")):
+                       fetch=("mel_outputs", "stop"), store=None, store_key="taco_b200/next_batch"):
     """Runs this rank's share of ``seqs`` (list of int token arrays).  Returns {utterance index: dict(mel [len,80],
     steps)} for the utterances this rank owns; outputs are trimmed at the first rounded stop token and clipped like
     Synthesizer.synthesize.  ``engine`` is a TacoEngine bound to this rank's GPU, or an EnginePool on it (several batches
-    in flight, same results)."""
+    in flight, same results).  ``store`` (a torch.distributed Store shared by the ranks, e.g. the default process-group store):
+    batches are then claimed dynamically from one cost-sorted list instead of the static LPT plan -- same batch composition,
+    same outputs, better balance when the stop-driven lengths differ."""
     from .Utils.Tacotron_feeder import _get_output_lengths, _prepare_inputs
     from .synthetic import gst_random_weights
     lengths = [len(s) for s in seqs]
@@ -76,6 +90,36 @@ def synthesize_batches(engine, hp, seqs, rank=0, world=1, batch_size=64, gst_wei
         mel = np.clip(res["mel_outputs"], lo, hi)
         return {int(i): dict(mel=mel[j, :keep[j]], steps=res["steps"], batch=b) for j, i in enumerate(idx)}
 
+    if store is not None and world > 1:
+        order = sorted(range(len(batches)), key=lambda b: (-batch_cost(lengths, batches[b], r=hp.outputs_per_step), b))
+        ticket = _Ticket(store, store_key)
+
+        def claimed():
+            while True:
+                k = ticket.next()
+                if k >= len(order):
+                    return
+                yield (order[k], batches[order[k]])
+
+        import threading
+        lock = threading.Lock()
+        it = claimed()
+
+        def run_claimed(eng, _):
+            out_ = {}
+            while True:
+                with lock:
+                    job = next(it, None)
+                if job is None:
+                    return out_
+                out_.update(run(eng, job))
+
+        n_workers = len(engine) if hasattr(engine, "map") else 1
+        parts = engine.map(run_claimed, range(n_workers)) if hasattr(engine, "map") else [run_claimed(engine, 0)]
+        out = {}
+        for part in parts:
+            out.update(part)
+        return out
     # an EnginePool keeps several batches in flight on this GPU (engine.EnginePool); a single TacoEngine runs them in turn
     parts = engine.map(run, mine) if hasattr(engine, "map") else [run(engine, job) for job in mine]
     out = {}

@@ -114,3 +114,54 @@ def test_two_rank_data_parallel_training_step_gloo(tmp_path):
     import json
     d = json.loads([l for l in r.stdout.splitlines() if l.startswith("{")][-1])
     assert d["world"] == 2 and d["same"] and d["max_err"] < 5e-5
+
+
+CLAIM_WORKER = textwrap.dedent("""
+    import os, sys, json
+    sys.path.insert(0, %r)
+    import numpy as np, torch.distributed as dist
+    from tacotron_prosody_multi_gpu_b200 import sharding
+    from tacotron_prosody_multi_gpu_b200.hparams import default_hparams
+    dist.init_process_group("gloo")
+    rank, world = dist.get_rank(), dist.get_world_size()
+    hp = default_hparams()
+    rng = np.random.default_rng(5)
+    seqs = [np.arange(2, 2 + n).astype(np.int32) for n in rng.integers(3, 40, size=70)]
+    class FakeEngine:                       # stands in for TacoEngine.forward_host: one frame per token, no GPU
+        def forward_host(self, ids, lens, **kw):
+            B, T = ids.shape
+            mel = np.repeat(ids[:, :, None].astype(np.float32), 80, axis=2) * 0.01
+            stop = np.zeros((B, T), np.float32)
+            for b, n in enumerate(lens):
+                stop[b, n - 1:] = 1.0
+            return dict(mel_outputs=mel, stop=stop, steps=T)
+    store = dist.distributed_c10d._get_default_store()
+    mine = sharding.synthesize_batches(FakeEngine(), hp, seqs, rank, world, batch_size=8, gst_weights=np.zeros((4, 10), np.float32),
+                                       max_iters=50, philox_seed=1, store=store, store_key="t/claim")
+    got = [None] * world
+    dist.all_gather_object(got, {k: (v["mel"].shape[0], float(v["mel"].sum())) for k, v in mine.items()})
+    if rank == 0:
+        merged = {}
+        for g in got:
+            assert not (set(g) & set(merged)), "an utterance was synthesised twice"
+            merged.update(g)
+        ref = sharding.synthesize_batches(FakeEngine(), hp, seqs, 0, 1, batch_size=8, gst_weights=np.zeros((4, 10), np.float32), max_iters=50, philox_seed=1)
+        ok = set(merged) == set(ref) and all(merged[k] == (ref[k]["mel"].shape[0], float(ref[k]["mel"].sum())) for k in ref)
+        print(json.dumps({"ok": bool(ok), "n": len(merged), "per_rank": [len(g) for g in got]}))
+        assert ok
+    dist.destroy_process_group()
+""") % (ROOT,)
+
+
+def test_dynamic_batch_claiming_covers_every_utterance_once_gloo(tmp_path):
+    """N > 1 synthesis with batches claimed from a shared store counter: every utterance exactly once, outputs equal to the
+    single-rank run (same batch composition), no data-path collective."""
+    script = tmp_path / "claim_worker.py"
+    script.write_text(CLAIM_WORKER)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+           "--master-port", str(_free_port()), str(script)]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, (r.stdout[-1500:], r.stderr[-2500:])
+    import json
+    d = json.loads([l for l in r.stdout.splitlines() if l.startswith("{")][-1])
+    assert d["ok"] and d["n"] == 70 and sum(d["per_rank"]) == 70
