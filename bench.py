@@ -372,7 +372,7 @@ def run_b200(args):
     world = int(os.environ.get("WORLD_SIZE", "1"))
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device -- the B200 path has no CPU fallback (use --impl reference)")
-    if os.environ.get("TACO_BLOCKING_SYNC", "0") == "1":
+    if os.environ.get("TACO_BLOCKING_SYNC", "1" if world > 1 else "0") == "1":
         # host threads that wait for the GPU sleep instead of spinning (N ranks x (in_flight + 1) threads share the host cores)
         import ctypes
         ctypes.CDLL("libcudart.so").cudaSetDeviceFlags(4)   # cudaDeviceScheduleBlockingSync, before the context exists
