@@ -96,6 +96,25 @@ int taco_op_attn_bwd(const float* dctx, const float* dcum, const float* q, const
                      float* p_conv_w, float* p_conv_b, float* p_Wl, float* p_va, float* p_ba, float* scratch /* >= B*T*NF floats */,
                      int B, int T, int A, int V, int NF, int KW, void* stream);
 
+/* The same attention step for the time loops, fused (csrc/train_attn_fused.cu): the location convolution and the location dense
+ * layer folded into one filter bank U [KW,A] (+ c0 [A]) once per training step; forward = ONE launch per decoder step (query
+ * projection q = h2raw . Wq, energies, masked softmax, cumulative update, context) that also saves tanh(pre) [B,T,A]; backward
+ * = TWO launches per step that produce only what the recurrence needs (d(q) and d(h2raw) += d(q) Wq^T, d(cum_{t-1}), the total
+ * d(ctx_t) = dctx + carry written back to dctx, and the saved d(energy) [B,T]); d(keys) and the weight gradients of all S steps
+ * come from ONE pass after the loop (taco_op_attn_bwd_hoisted; results are ADDED to g_* and dkeys; work >= B*(KW+2)*A floats).
+ * taco_op_attn_fused_supported: 1 when these kernels hold the shape (A = 128, NF = 32, KW = 31, T <= 256-ish), else 0. */
+int taco_op_attn_fused_supported(int T, int D, int A, int V, int NF, int KW);
+int taco_op_attn_fold(const float* conv_w, const float* conv_b, const float* Wl, float* U, float* c0, void* stream);
+int taco_op_attn_fwd_fused(const float* h2raw, const float* Wq, const float* U, const float* c0, const float* ba, const float* va,
+                           const float* cum_prev, const float* keys, const float* values, const int32_t* lens, float* q, float* th,
+                           float* align, float* cum, float* ctx, int B, int T, int D, int V, void* stream);
+int taco_op_attn_bwd_fused(float* dctx, const float* carry, const float* dcum, const float* align, const float* th, const float* values,
+                           const int32_t* lens, const float* U, const float* va, const float* Wq, float* de, float* dq, float* dh2,
+                           float* dcum_prev, float* scratch /* >= B*T floats */, int B, int T, int D, int V, void* stream);
+int taco_op_attn_bwd_hoisted(const float* de, const float* th, const float* cum, const int32_t* lens, const float* conv_w,
+                             const float* conv_b, const float* Wl, const float* va, float* dkeys, float* g_conv_w, float* g_conv_b,
+                             float* g_Wl, float* g_va, float* g_ba, float* work, int S, int B, int T, void* stream);
+
 /* GRUCell (Tacotron.py:201; reset before the candidate matmul) pointwise parts and gradients. */
 int taco_op_gru_pre(float* g, const float* h, float* rh, int B, int R, void* stream);
 int taco_op_gru_out(float* cpre, const float* ru, const float* h, float* hnew, int B, int R, void* stream);
@@ -158,6 +177,10 @@ typedef struct TacoDecLoop {
     float* dkeys;                            /* [B,T,A] accumulated (caller zeroes) */
     float *p_conv_w, *p_conv_b, *p_Wl, *p_va, *p_ba;   /* per-row partials of the attention weight gradients (caller zeroes) */
     float* work;                             /* scratch, >= B*(8*D + 2*T + T*NF) + S*B*D + (S+1)*B*MD floats */
+    /* fused attention path (taco_op_attn_*_fused; used when all three are set and taco_op_attn_fused_supported): */
+    float* th;                               /* [S,B,T,A] tanh(pre) saved by the forward loop */
+    float* de;                               /* [S,B,T] d(energy) saved by the backward loop */
+    float* attn_work;                        /* >= (KW+1)*A + B*(KW+2)*A floats: folded filter bank | hoisted accumulators */
 } TacoDecLoop;
 int taco_op_decoder_loop_fwd(const TacoDecLoop* p, void* stream);
 int taco_op_decoder_loop_bwd(const TacoDecLoop* p, void* stream);

@@ -16,7 +16,8 @@ S = int(sys.argv[2]) if len(sys.argv) > 2 else 100
 hp = default_hparams()
 w = weights.set_stop_bias(weights.init_weights(hp, perturb=0.05), -10.0)
 eng = TacoEngine(hp, w, precision="bf16")
-ids, lens = synthetic.token_batch(hp, synthetic.cycle_lengths(B))
+MAXLEN = int(sys.argv[3]) if len(sys.argv) > 3 else 1000
+ids, lens = synthetic.token_batch(hp, [min(n, MAXLEN) for n in synthetic.cycle_lengths(B)])
 mem = eng.encode(torch.from_numpy(ids), torch.from_numpy(lens), gst_weights=synthetic.gst_random_weights(hp))
 steps = -1
 for _ in range(3):

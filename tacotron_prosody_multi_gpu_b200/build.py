@@ -16,7 +16,7 @@ CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(CSRC, "build")
 LIB = os.path.join(HERE, "libtaco_b200.so")
 SOURCES = ["api.cu", "decoder.cu", "decoder3.cu", "frame_proj.cu", "conv.cu", "conv_tc.cu", "encoder.cu", "refenc.cu",
-           "train_gemm.cu", "train_ops.cu", "train_attn.cu", "train_misc.cu", "train_loops.cu", "griffin_lim.cu"]
+           "train_gemm.cu", "train_ops.cu", "train_attn.cu", "train_attn_fused.cu", "train_misc.cu", "train_loops.cu", "griffin_lim.cu"]
 NVCC_FLAGS = ["-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
               "-Xcompiler", "-fPIC", "-Xptxas", "-v"]
 

@@ -38,7 +38,11 @@ constexpr int NT = TACO_THREADS;       // 512 threads = 16 warps
 constexpr int MEL = 80, PRE = 256, DEC = 256, MEM = 768, ATT = 128;
 constexpr uint32_t SENT = 0xFFFFFFFFu;
 constexpr int T_MAX3 = TACO_DEC3_TMAX;  // 512
-constexpr int PRE_REG_T = 128;          // T <= 128: location pre-activations live in registers
+#ifndef D3_NPT
+#define D3_NPT 8
+#endif
+constexpr int NPT = D3_NPT;             // 16-position tiles of location pre-activations an attention work item keeps in registers
+constexpr int PRE_REG_T = 16 * NPT;     // positions per work item
 constexpr int KS_X = 5, KS_H = 16, KS_CTX = 48;
 constexpr int TILE_W = 128;             // words of one A tile (32 lanes x uint4) and of one B k-step block (2 n-tiles x 32 lanes x uint2)
 
@@ -78,7 +82,7 @@ constexpr int SO_LEN = SO_OWN + 16;              // [16]: memory length of clust
 constexpr int SO_GRP = SO_LEN + 16;              // [16][2]: first thread group / number of groups of row i in the context-slice reduction
 constexpr int SO_MBAR = SO_GRP + 32;             // 10 mbarriers (64-bit each): one per exchange buffer, one phase per decoder step
 constexpr int MB_P1 = 0, MB_P2 = 1, MB_H1R = 2, MB_H1Z = 3, MB_H2R = 4, MB_H2Z = 5, MB_CTX = 6, MB_Q = 7, MB_A = 8, MB_PART = 9, N_MB = 10;
-constexpr int PART_T = 128;                      // positions per attention work item when a row is split (T > 128)
+constexpr int PART_T = PRE_REG_T;                // positions per attention work item when a row is split
 constexpr int PART_MAX = 4;                      // T <= 512
 constexpr int SO_KEEP = SO_MBAR + 2 * N_MB + 4;  // [2 prenet layers][16 rows]: 16 dropout keep bits (this CTA's units) of the step about to run
 constexpr int SO_PART = SO_KEEP + 32;             // [PART_MAX][2]: (local maximum, local sum of exp) of every position slice of this CTA's row

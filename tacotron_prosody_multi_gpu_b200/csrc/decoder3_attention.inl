@@ -92,7 +92,7 @@ __device__ __forceinline__ void att3_loc_tile(float (&acc)[4], int t0, int lane,
 // otherwise written to the row's global scratch [T][128].
 // incremental: the pair arrays hold the NEW alignments and the (linear) location term is accumulated: pre += T(a).G
 // -- no key reload from L2 (cumulative attention only).
-__device__ __forceinline__ void att3_location(const Dec3Params& p, float (&preR)[8][4], float* pre_scr, int b, int len, int warp, int lane,
+__device__ __forceinline__ void att3_location(const Dec3Params& p, float (&preR)[NPT][4], float* pre_scr, int b, int len, int warp, int lane,
                                               bool incremental = false, int t_off = 0) {
     const int gq = lane >> 2, tq = lane & 3;
     uint2 ghi[2], glo[2];
@@ -106,7 +106,7 @@ __device__ __forceinline__ void att3_location(const Dec3Params& p, float (&preR)
     if (incremental) {
         if (p.pre_reg) {
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
+            for (int i = 0; i < NPT; ++i) {
                 if (16 * i < len) {
                     float acc[4];
                     att3_loc_tile(acc, 16 * i, lane, ghi, glo);
@@ -137,7 +137,7 @@ __device__ __forceinline__ void att3_location(const Dec3Params& p, float (&preR)
     }
     if (p.pre_reg) {
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
+        for (int i = 0; i < NPT; ++i) {
             const int t0 = 16 * i;
             if (t0 < len) {
                 const int ta = t0 + gq, tb = ta + 8;
@@ -178,7 +178,7 @@ __device__ __forceinline__ int ctx_groups_of(int len, int total) { return (CTX_B
 // Owner part of one attention step of cluster row `arow` (global row b; the CTA that runs it is chosen by row length, SO_OWN):
 // q from the 16 partials, energies, masked softmax, cumulate, alignment history, and the multicast of the alignment row to
 // every CTA of the cluster (each of which reduces a 48-column slice of the context, att3_context_slice).
-__device__ __forceinline__ void att3_owner(const Dec3Params& p, float (&preR)[8][4], float* pre_scr, int b, int len, int arow, int s,
+__device__ __forceinline__ void att3_owner(const Dec3Params& p, float (&preR)[NPT][4], float* pre_scr, int b, int len, int arow, int s,
                                            int tid, int warp, int lane, Guard3& g, long long* tacc, long long& tprev, bool timing, bool tracing,
                                            uint32_t q_bytes, int apart, int tb0, int Tl) {
     float* scr = SMF(SO_RED);
@@ -222,7 +222,7 @@ __device__ __forceinline__ void att3_owner(const Dec3Params& p, float (&preR)[8]
         const int gq = lane >> 2, tq = lane & 3, d0 = warp * 8 + 2 * tq;
         const float q0 = SMF(SO_QS)[d0], q1 = SMF(SO_QS)[d0 + 1], v0 = SMF(SO_VA)[d0], v1 = SMF(SO_VA)[d0 + 1];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
+        for (int i = 0; i < NPT; ++i) {
             if (16 * i < len) {
                 float ea = v0 * tanh_apx(preR[i][0] + q0) + v1 * tanh_apx(preR[i][1] + q1);
                 float eb = v0 * tanh_apx(preR[i][2] + q0) + v1 * tanh_apx(preR[i][3] + q1);
@@ -246,7 +246,7 @@ __device__ __forceinline__ void att3_owner(const Dec3Params& p, float (&preR)[8]
             if (t < len) {
                 const float4* p4 = reinterpret_cast<const float4*>(pre_scr + (size_t)t * ATT + qd * 32);
 #pragma unroll
-                for (int i = 0; i < 8; ++i) {
+                for (int i = 0; i < NPT; ++i) {
                     const float4 x = p4[i], qq = q4[i], vv = v4[i];
                     e = fmaf(vv.x, tanh_apx(x.x + qq.x), e);
                     e = fmaf(vv.y, tanh_apx(x.y + qq.y), e);
@@ -470,7 +470,7 @@ __device__ __forceinline__ void att3_context_slice(const Dec3Params& p, uint32_t
 // Location pre-activations of the NEXT step from the new alignments (pair arrays built by att3_owner), tiles [i0, i1) of the
 // in-register path; the scratch path (T > 128) runs all its tiles in the first call.  Warp-local: no block synchronisation,
 // so the chunks can sit in the shadow of the dense_2 / LSTM-1 exchanges.
-__device__ __forceinline__ void att3_loc_chunk(const Dec3Params& p, float (&preR)[8][4], float* pre_scr, int b, int len, int warp, int lane,
+__device__ __forceinline__ void att3_loc_chunk(const Dec3Params& p, float (&preR)[NPT][4], float* pre_scr, int b, int len, int warp, int lane,
                                                int i0, int i1) {
     if (!p.cumulative) {   // not incremental: pre = keys + location(a) + const, every step
         if (i0 == 0) att3_location(p, preR, pre_scr, b, len, warp, lane, false);
@@ -487,7 +487,7 @@ __device__ __forceinline__ void att3_loc_chunk(const Dec3Params& p, float (&preR
         glo[ks] = __ldg(reinterpret_cast<const uint2*>(p.g_lo) + (ks * 16 + warp) * 32 + lane);
     }
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
+    for (int i = 0; i < NPT; ++i) {
         if (i >= i0 && i < i1 && 16 * i < len) {
             float acc[4];
             att3_loc_tile(acc, 16 * i, lane, ghi, glo);

@@ -197,9 +197,9 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
     const int Tl = P == 1 ? p.T : max(0, min(PART_T, p.T - tb0));   // positions it covers (valid ones: alen)
     const int alen = att ? item_len(aitem) : 0;
     float* pre_scr = p.pre_scratch + ((size_t)ab * p.T + tb0) * ATT;   // [T][128]: working copy when !pre_reg, saved state otherwise
-    float preR[8][4];
+    float preR[NPT][4];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) preR[i][0] = preR[i][1] = preR[i][2] = preR[i][3] = 0.f;
+    for (int i = 0; i < NPT; ++i) preR[i][0] = preR[i][1] = preR[i][2] = preR[i][3] = 0.f;
     __syncthreads();
     if (att) {
         for (int i = tid; i < Tl + 30; i += NT) {   // cumulative alignments of the item's window, 15 positions of halo on both sides
@@ -216,7 +216,7 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
             // bit-identical to one multi-step launch)
             const int gq = lane >> 2, tq = lane & 3, d0 = warp * 8 + 2 * tq;
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
+            for (int i = 0; i < NPT; ++i) {
                 const int ta = 16 * i + gq, tb = ta + 8;
                 if (ta < alen) {
                     const float2 v = *reinterpret_cast<const float2*>(pre_scr + (size_t)ta * ATT + d0);
@@ -439,7 +439,7 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
         }
         // ---- shadow of the dense_2 exchange: first half of the location term of this step (alignments of step s-1) ----
         if (att && s > 0 && !(p.dbg & 8)) {
-            att3_loc_chunk(p, preR, pre_scr, ab, alen, warp, lane, 0, 4);
+            att3_loc_chunk(p, preR, pre_scr, ab, alen, warp, lane, 0, NPT / 2);
             D3_STAMP(13)
         }
         D3_TR(16)
@@ -492,7 +492,7 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
             D3_TR(22)
             // ---- shadow of the h1 exchange: second half of the location term ----
             if (att && s > 0 && !(p.dbg & 8)) {
-                att3_loc_chunk(p, preR, pre_scr, ab, alen, warp, lane, 4, 8);
+                att3_loc_chunk(p, preR, pre_scr, ab, alen, warp, lane, NPT / 2, NPT);
                 D3_STAMP(14)
             }
             D3_TR(23)
@@ -617,7 +617,7 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
     // still in place) and the location term of the following step (saved below for a continuation launch)
     if (!stopped && s_done > 0) {
         if (rank == STOP_RANK) dec3_stop_token(p, s_done - 1, row0, R, cid, free_run, red, tid, warp, lane, g);
-        if (att) att3_loc_chunk(p, preR, pre_scr, ab, alen, warp, lane, 0, 8);
+        if (att) att3_loc_chunk(p, preR, pre_scr, ab, alen, warp, lane, 0, NPT);
     }
 
     if (timing && lane == 0)
@@ -635,7 +635,7 @@ __global__ void __launch_bounds__(NT, 1) decoder3_kernel(const __grid_constant__
         if (p.pre_reg) {
             const int gq = lane >> 2, tq = lane & 3, d0 = warp * 8 + 2 * tq;
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
+            for (int i = 0; i < NPT; ++i) {
                 const int ta = 16 * i + gq, tb = ta + 8;
                 if (ta < alen) *reinterpret_cast<float2*>(pre_scr + (size_t)ta * ATT + d0) = make_float2(preR[i][0], preR[i][1]);
                 if (tb < alen) *reinterpret_cast<float2*>(pre_scr + (size_t)tb * ATT + d0) = make_float2(preR[i][2], preR[i][3]);

@@ -1,0 +1,504 @@
+// train_attn_fused.cu -- the LocationSensitiveAttention step of the training recurrence (Attention.py:169-210,345-401) as
+// ONE launch forward and TWO launches backward per decoder step, with everything that does not feed the recurrence hoisted
+// out of the BPTT loop (train_attn.cu keeps the op-by-op kernels: they remain the path for kernel sizes != 31 / T > 256).
+//
+//   fold     U[j,d] = sum_f conv_w[j,f] Wl[f,d], c0[d] = sum_f conv_b[f] Wl[f,d]: the location convolution and the location
+//            dense layer are one 31-tap filter bank [31,128] (no nonlinearity between them), folded once per training step
+//   forward  grid (4 value-column slices, B rows), 512 threads: q = h2raw . Wq, tanh pre-activations of all positions of the
+//            row (kept in registers as a sliding 31-tap window per thread; every CTA of a row computes them, the 4 CTAs
+//            share the stores of tanh(pre) [T,128], which the backward pass reads instead of recomputing it), masked
+//            softmax, cumulative update, and this CTA's 192 columns of the context
+//   backward d(align) grid (T/8, B): values . (d(ctx) + carry) + d(cum)
+//            row kernel grid (B): softmax gradient, d(pre), d(q) -> d(h2raw) += d(q) Wq^T, d(cum_{t-1}) through the folded
+//            filter bank (4x4 register tiles over the shared-memory d(pre) tile); saves d(energy) [T] per step
+//   hoisted  after the loop, grid (T/8, B) looping over all S steps: d(keys), d(U), d(c0), d(v_a) from the saved d(energy)
+//            and tanh(pre); then d(conv_w), d(conv_b), d(Wl), d(b_a) from d(U), d(c0) by the chain rule of the fold
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdint.h>
+
+#include "../../include/taco_b200_train.h"
+#include "common.cuh"
+
+namespace {
+
+constexpr int AD = 128, NF = 32, KW = 31, LEFT = 15;   // attention dim, location filters, taps
+constexpr int FT = 512;                                // threads of the forward / row kernels
+constexpr int CS = 4;                                  // value-column slices (CTAs per row) of the forward kernel
+constexpr int RS = AD + 4;                             // shared-memory row stride of [.,128] tiles (16-byte aligned, +4 banks per row)
+constexpr int GS = 33;                                 // row stride of the [T,31] tap-gradient tile
+
+__global__ void __launch_bounds__(AD) attn_fold_kernel(const float* __restrict__ cw, const float* __restrict__ cb,
+                                                       const float* __restrict__ Wl, float* __restrict__ U, float* __restrict__ c0) {
+    const int j = blockIdx.x, d = threadIdx.x;
+    float a = 0.f;
+    for (int f = 0; f < NF; ++f) a = fmaf(j < KW ? cw[j * NF + f] : cb[f], Wl[f * AD + d], a);
+    if (j < KW) U[j * AD + d] = a; else c0[d] = a;
+}
+
+__device__ __forceinline__ float block_reduce(float v, float* red, bool is_max) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    v = is_max ? warp_max(v) : warp_sum(v);
+    __syncthreads();                     // red may still be read from a previous reduction
+    if (lane == 0) red[warp] = v;
+    __syncthreads();
+    float r = red[0];
+    for (int w = 1; w < nw; ++w) r = is_max ? fmaxf(r, red[w]) : r + red[w];
+    return r;
+}
+
+// ------------------------------------------------------------------------------------------------ forward
+__global__ void __launch_bounds__(FT) attn_fwd_fused_kernel(
+    const float* __restrict__ h2raw, const float* __restrict__ Wq, const float* __restrict__ U, const float* __restrict__ c0,
+    const float* __restrict__ ba, const float* __restrict__ va, const float* __restrict__ cum_prev, const float* __restrict__ keys,
+    const float* __restrict__ values, const int32_t* __restrict__ lens, float* __restrict__ q_out, float* __restrict__ th_out,
+    float* __restrict__ align, float* __restrict__ cum, float* __restrict__ ctx, int T, int D, int V) {
+    extern __shared__ __align__(16) float smem[];
+    const int Tp = (T + 3) & ~3;
+    float* s_cum = smem;                       // [Tp + 32]: cum_prev[t - LEFT], zero padded
+    float* s_e = s_cum + Tp + 32;              // [Tp][4] partial energies (one per warp of a 128-thread group) -> [Tp] alignments
+    float* s_q = s_e + Tp * 4;                 // [AD]
+    float* s_qp = s_q + AD;                    // [4][AD] K-split partials of q
+    float* s_h = s_qp + 4 * AD;                // [D]
+    float* s_red = s_h + D;                    // [32]
+    float4* s_part = reinterpret_cast<float4*>(s_red + 32);   // [ntg][nq] context partials
+    const int cs = blockIdx.x, b = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int len = min(lens[b], T);
+    const int d = tid & (AD - 1), g = tid >> 7;
+
+    float Ur[KW];
+#pragma unroll
+    for (int j = 0; j < KW; ++j) Ur[j] = U[j * AD + d];
+    for (int i = tid; i < Tp + 32; i += FT) {
+        const int t = i - LEFT;
+        s_cum[i] = (t >= 0 && t < T) ? cum_prev[(long long)b * T + t] : 0.f;
+    }
+    for (int i = tid; i < D; i += FT) s_h[i] = h2raw[(long long)b * D + i];
+    __syncthreads();
+    {   // q = h2raw . Wq, K split over the 4 thread groups
+        const int k0 = g * (D / 4), k1 = (g == 3) ? D : k0 + D / 4;
+        float a = 0.f;
+#pragma unroll 8
+        for (int k = k0; k < k1; ++k) a = fmaf(s_h[k], Wq[(long long)k * AD + d], a);
+        s_qp[g * AD + d] = a;
+    }
+    __syncthreads();
+    if (tid < AD) {
+        const float qv = s_qp[tid] + s_qp[AD + tid] + s_qp[2 * AD + tid] + s_qp[3 * AD + tid];
+        if (cs == 0) q_out[(long long)b * AD + tid] = qv;
+        s_q[tid] = qv + ba[tid] + c0[tid];
+    }
+    __syncthreads();
+    const float qd = s_q[d], vad = va[d];
+    const int nblk = (len + 3) >> 2;
+    for (int blk = g; blk < nblk; blk += 4) {
+        const int t0 = blk * 4;
+        float kv[4];
+#pragma unroll
+        for (int p = 0; p < 4; ++p) kv[p] = (t0 + p < len) ? keys[((long long)b * T + t0 + p) * AD + d] : 0.f;
+        float w[36];
+#pragma unroll
+        for (int k = 0; k < 9; ++k) {
+            const float4 x = *reinterpret_cast<const float4*>(s_cum + t0 + 4 * k);
+            w[4 * k] = x.x; w[4 * k + 1] = x.y; w[4 * k + 2] = x.z; w[4 * k + 3] = x.w;
+        }
+        float acc[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+        for (int j = 0; j < KW; ++j)
+#pragma unroll
+            for (int p = 0; p < 4; ++p) acc[p] = fmaf(Ur[j], w[p + j], acc[p]);
+        const bool writer = (blk & (CS - 1)) == cs;
+#pragma unroll
+        for (int p = 0; p < 4; ++p) {
+            const int t = t0 + p;
+            float e = 0.f;
+            if (t < len) {
+                const float th = tanhf(acc[p] + qd + kv[p]);
+                if (writer) th_out[((long long)b * T + t) * AD + d] = th;
+                e = vad * th;
+            }
+            e = warp_sum(e);
+            if (lane == 0) s_e[t * 4 + (warp & 3)] = e;
+        }
+    }
+    __syncthreads();
+    // masked softmax over t < len (alignments beyond the length are exact zeros), cumulative update
+    float mx = -INFINITY;
+    for (int t = tid; t < len; t += FT) mx = fmaxf(mx, s_e[t * 4] + s_e[t * 4 + 1] + s_e[t * 4 + 2] + s_e[t * 4 + 3]);
+    mx = block_reduce(mx, s_red, true);
+    float sum = 0.f;
+    for (int t = tid; t < len; t += FT) sum += expf(s_e[t * 4] + s_e[t * 4 + 1] + s_e[t * 4 + 2] + s_e[t * 4 + 3] - mx);
+    sum = block_reduce(sum, s_red, false);
+    const float inv = 1.0f / sum;
+    float av[4];                                      // up to 4 positions per thread (T <= 2048)
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const int t = tid + k * FT;
+        av[k] = (t < len) ? expf(s_e[t * 4] + s_e[t * 4 + 1] + s_e[t * 4 + 2] + s_e[t * 4 + 3] - mx) * inv : 0.f;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const int t = tid + k * FT;
+        if (t < T) {
+            s_e[t] = av[k];
+            if (cs == 0) {
+                align[(long long)b * T + t] = av[k];
+                cum[(long long)b * T + t] = s_cum[t + LEFT] + av[k];
+            }
+        }
+    }
+    __syncthreads();
+    // context columns of this slice: thread = (column quad, position group)
+    const int V4 = V >> 2, nq = (V4 + CS - 1) / CS, ntg = FT / nq;
+    const int cq = tid % nq, tg = tid / nq, c4 = cs * nq + cq;
+    if (tg < ntg) {
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (c4 < V4) {
+            const float4* vp = reinterpret_cast<const float4*>(values) + (long long)b * T * V4 + c4;
+#pragma unroll 4
+            for (int t = tg; t < len; t += ntg) {
+                const float a = s_e[t];
+                const float4 v = vp[(long long)t * V4];
+                acc.x = fmaf(a, v.x, acc.x); acc.y = fmaf(a, v.y, acc.y); acc.z = fmaf(a, v.z, acc.z); acc.w = fmaf(a, v.w, acc.w);
+            }
+        }
+        s_part[tg * nq + cq] = acc;
+    }
+    __syncthreads();
+    if (tid < nq && c4 < V4) {
+        float4 acc = s_part[tid];
+        for (int k = 1; k < ntg; ++k) { const float4 o = s_part[k * nq + tid]; acc.x += o.x; acc.y += o.y; acc.z += o.z; acc.w += o.w; }
+        reinterpret_cast<float4*>(ctx)[(long long)b * V4 + c4] = acc;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ backward, in the loop
+// d(align)[t] = values[t,:] . (d(ctx) + carry) + d(cum_t)[t]; one warp per position
+__global__ void __launch_bounds__(256) attn_bwd_dalign_fused_kernel(const float* __restrict__ dctx, const float* __restrict__ carry,
+                                                                    const float* __restrict__ dcum, const float* __restrict__ values,
+                                                                    const int32_t* __restrict__ lens, float* __restrict__ da, int T, int V) {
+    extern __shared__ __align__(16) float s_dctx[];
+    const int b = blockIdx.y, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int t = blockIdx.x * 8 + warp;
+    const int len = min(lens[b], T);
+    if (blockIdx.x * 8 >= len) {
+        if (t < T && lane == 0) da[(long long)b * T + t] = 0.f;
+        return;
+    }
+    float4 v[6];                                   // the first 768 columns of the value row in flight before the smem fill
+    const float4* vp = reinterpret_cast<const float4*>(values + ((long long)b * T + min(t, len - 1)) * V);
+    const int V4 = V >> 2;
+#pragma unroll
+    for (int k = 0; k < 6; ++k) v[k] = (lane + 32 * k < V4) ? vp[lane + 32 * k] : make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int i = threadIdx.x; i < V; i += blockDim.x) s_dctx[i] = dctx[(long long)b * V + i] + carry[(long long)b * V + i];
+    __syncthreads();
+    if (t >= T) return;
+    float acc = 0.f;
+    if (t < len) {
+#pragma unroll
+        for (int k = 0; k < 6; ++k) {
+            const int c = (lane + 32 * k) * 4;
+            if (c < V) {
+                acc = fmaf(v[k].x, s_dctx[c], acc); acc = fmaf(v[k].y, s_dctx[c + 1], acc);
+                acc = fmaf(v[k].z, s_dctx[c + 2], acc); acc = fmaf(v[k].w, s_dctx[c + 3], acc);
+            }
+        }
+        for (int c4 = lane + 192; c4 < V4; c4 += 32) {
+            const float4 x = vp[c4];
+            acc = fmaf(x.x, s_dctx[4 * c4], acc); acc = fmaf(x.y, s_dctx[4 * c4 + 1], acc);
+            acc = fmaf(x.z, s_dctx[4 * c4 + 2], acc); acc = fmaf(x.w, s_dctx[4 * c4 + 3], acc);
+        }
+        acc = warp_sum(acc) + dcum[(long long)b * T + t];
+    }
+    if (lane == 0) da[(long long)b * T + t] = t < len ? acc : 0.f;
+}
+
+// everything of the attention gradient that feeds the recurrence, one CTA per row
+__global__ void __launch_bounds__(FT) attn_bwd_row_kernel(
+    float* __restrict__ dctx, const float* __restrict__ carry, const float* __restrict__ dcum, const float* __restrict__ da,
+    const float* __restrict__ align, const float* __restrict__ th, const int32_t* __restrict__ lens, const float* __restrict__ U,
+    const float* __restrict__ va, const float* __restrict__ Wq, float* __restrict__ de_out, float* __restrict__ dq_out,
+    float* __restrict__ dh2, float* __restrict__ dcum_prev, int T, int D, int V) {
+    extern __shared__ __align__(16) float smem[];
+    const int Tp = (T + 3) & ~3;
+    float* s_dpre = smem;                       // [Tp][RS]
+    float* s_U = s_dpre + (size_t)Tp * RS;      // [32][RS], row 31 = 0
+    float* s_G = s_U + 32 * RS;                 // [Tp][GS]: G[t][j] = sum_d dpre[t,d] U[j,d]
+    float* s_de = s_G + (size_t)Tp * GS;        // [Tp]
+    float* s_dq = s_de + Tp;                    // [4][AD] partials -> [AD]
+    float* s_red = s_dq + 4 * AD;               // [32]
+    const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int len = min(lens[b], T);
+    const int lenp = (len + 3) & ~3;
+    for (int i = tid; i < V; i += FT) dctx[(long long)b * V + i] += carry[(long long)b * V + i];      // total d(ctx_t), kept for d(values)
+    for (int i = tid; i < 32 * AD; i += FT) s_U[(i >> 7) * RS + (i & 127)] = (i >> 7) < KW ? U[i] : 0.f;
+    for (int i = tid; i < lenp * GS; i += FT) s_G[i] = 0.f;
+    float dot = 0.f;
+    for (int t = tid; t < len; t += FT) dot = fmaf(align[(long long)b * T + t], da[(long long)b * T + t], dot);
+    dot = block_reduce(dot, s_red, false);
+    for (int t = tid; t < Tp; t += FT) {
+        const float v = t < len ? align[(long long)b * T + t] * (da[(long long)b * T + t] - dot) : 0.f;
+        s_de[t] = v;
+        if (t < T) de_out[(long long)b * T + t] = v;
+    }
+    __syncthreads();
+    {   // d(pre)[t,d] = d(e)[t] v_a[d] (1 - tanh^2); column sums -> d(q)
+        const int d = tid & (AD - 1), g = tid >> 7;
+        const float vad = va[d];
+        float cs = 0.f;
+        for (int t = g; t < lenp; t += 4) {
+            float dp = 0.f;
+            if (t < len) {
+                const float x = th[((long long)b * T + t) * AD + d];
+                dp = s_de[t] * vad * (1.f - x * x);
+            }
+            s_dpre[t * RS + d] = dp;
+            cs += dp;
+        }
+        s_dq[g * AD + d] = cs;
+    }
+    __syncthreads();
+    if (tid < AD) {
+        const float v = s_dq[tid] + s_dq[AD + tid] + s_dq[2 * AD + tid] + s_dq[3 * AD + tid];
+        dq_out[(long long)b * AD + tid] = v;
+        s_dq[tid] = v;
+    }
+    // G tiles: 4 positions x 4 taps (taps jt, jt+8, jt+16, jt+24) x half of d per work item
+    const int ntt = lenp >> 2, nitems = ntt * 16;
+    for (int it = tid; it < nitems; it += FT) {
+        const int jt = it & 7, hf = (it >> 3) & 1, tt = it >> 4;
+        const float* pr = s_dpre + (size_t)(tt * 4) * RS + hf * 64;
+        const float* ur = s_U + (size_t)jt * RS + hf * 64;
+        float acc[4][4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+            for (int k = 0; k < 4; ++k) acc[i][k] = 0.f;
+#pragma unroll 4
+        for (int d4 = 0; d4 < 16; ++d4) {
+            float4 p[4], u[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) p[i] = *reinterpret_cast<const float4*>(pr + i * RS + 4 * d4);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) u[k] = *reinterpret_cast<const float4*>(ur + (size_t)(8 * k) * RS + 4 * d4);
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    acc[i][k] = fmaf(p[i].x, u[k].x, acc[i][k]); acc[i][k] = fmaf(p[i].y, u[k].y, acc[i][k]);
+                    acc[i][k] = fmaf(p[i].z, u[k].z, acc[i][k]); acc[i][k] = fmaf(p[i].w, u[k].w, acc[i][k]);
+                }
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+            for (int k = 0; k < 4; ++k) atomicAdd(s_G + (size_t)(tt * 4 + i) * GS + jt + 8 * k, acc[i][k]);
+    }
+    __syncthreads();
+    // d(cum_{t-1})[tp] = d(cum_t)[tp] + sum_j G[tp - j + LEFT][j]   (pre[t] reads cum[t + j - LEFT])
+    for (int tp = tid; tp < T; tp += FT) {
+        float a = dcum[(long long)b * T + tp];
+#pragma unroll
+        for (int j = 0; j < KW; ++j) {
+            const int t = tp - j + LEFT;
+            if (t >= 0 && t < len) a += s_G[t * GS + j];
+        }
+        dcum_prev[(long long)b * T + tp] = a;
+    }
+    // d(h2raw)[k] += sum_d d(q)[d] Wq[k,d]: one warp per k (Wq is a view into the flat parameter buffer: 4-byte aligned only)
+    float dqr[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) dqr[i] = s_dq[lane + 32 * i];
+    for (int k0 = warp * 4; k0 < D; k0 += (FT / 32) * 4) {
+        float wv[4][4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+            for (int c = 0; c < 4; ++c) wv[i][c] = (k0 + i < D) ? Wq[(long long)(k0 + i) * AD + lane + 32 * c] : 0.f;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            float a = wv[i][0] * dqr[0] + wv[i][1] * dqr[1] + wv[i][2] * dqr[2] + wv[i][3] * dqr[3];
+            a = warp_sum(a);
+            if (lane == 0 && k0 + i < D) dh2[(long long)b * D + k0 + i] += a;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ backward, hoisted
+// All S steps of a tile of 8 positions of one row: d(keys)[b,t,:] += sum_s d(pre), and this CTA's partial sums of
+// d(U)[j,d] = sum cum_{s-1}[t + j - LEFT] d(pre)[t,d], d(c0)[d] = sum d(pre), d(v_a)[d] = sum d(e) tanh(pre) -> acc[b][...]
+constexpr int HP = 8, HSB = 4;      // positions per CTA, steps per shared-memory refill
+constexpr int ACC_N = KW * AD + 2 * AD;   // d(U) | d(c0) | d(v_a)
+__global__ void __launch_bounds__(256) attn_bwd_hoisted_kernel(const float* __restrict__ de, const float* __restrict__ th,
+                                                               const float* __restrict__ cum, const int32_t* __restrict__ lens,
+                                                               const float* __restrict__ va, float* __restrict__ dkeys,
+                                                               float* __restrict__ acc_out, int S, int B, int T) {
+    __shared__ __align__(16) float s_cum[HSB][HP + 32];   // cum[t0 - LEFT ..]
+    __shared__ float s_de[HSB][HP];
+    __shared__ float s_x[2][ACC_N / 2 + AD];              // cross-half reduction scratch
+    const int b = blockIdx.y, t0 = blockIdx.x * HP, tid = threadIdx.x, d = tid & (AD - 1), hf = tid >> 7;
+    const int len = min(lens[b], T);
+    if (t0 >= len) return;
+    const float vad = va[d];
+    float dU[KW], dk[4] = {0.f, 0.f, 0.f, 0.f}, dc0 = 0.f, dva = 0.f;
+#pragma unroll
+    for (int j = 0; j < KW; ++j) dU[j] = 0.f;
+    const int tb = t0 + hf * 4;               // this thread's 4 positions
+    for (int s0 = 0; s0 < S; s0 += HSB) {
+        const int ns = min(HSB, S - s0);
+        float x[HSB][4];
+#pragma unroll
+        for (int k = 0; k < HSB; ++k)
+#pragma unroll
+            for (int p = 0; p < 4; ++p)
+                x[k][p] = (k < ns && tb + p < len) ? th[(((long long)(s0 + k) * B + b) * T + tb + p) * AD + d] : 0.f;
+        __syncthreads();
+        for (int i = tid; i < HSB * (HP + 32); i += 256) {
+            const int k = i / (HP + 32), o = i - k * (HP + 32), t = t0 + o - LEFT;
+            s_cum[k][o] = (k < ns && t >= 0 && t < T) ? cum[((long long)(s0 + k) * B + b) * T + t] : 0.f;
+        }
+        if (tid < HSB * HP) {
+            const int k = tid / HP, o = tid - k * HP;
+            s_de[k][o] = (k < ns && t0 + o < len) ? de[((long long)(s0 + k) * B + b) * T + t0 + o] : 0.f;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < HSB; ++k) {
+            float dp[4];
+#pragma unroll
+            for (int p = 0; p < 4; ++p) {
+                const float dev = s_de[k][hf * 4 + p];
+                dva = fmaf(dev, x[k][p], dva);
+                dp[p] = dev * vad * (1.f - x[k][p] * x[k][p]);
+                dk[p] += dp[p];
+                dc0 += dp[p];
+            }
+            float w[36];
+#pragma unroll
+            for (int i = 0; i < 9; ++i) {
+                const float4 c = *reinterpret_cast<const float4*>(&s_cum[k][hf * 4 + 4 * i]);
+                w[4 * i] = c.x; w[4 * i + 1] = c.y; w[4 * i + 2] = c.z; w[4 * i + 3] = c.w;
+            }
+#pragma unroll
+            for (int j = 0; j < KW; ++j)
+#pragma unroll
+                for (int p = 0; p < 4; ++p) dU[j] = fmaf(w[p + j], dp[p], dU[j]);
+        }
+    }
+#pragma unroll
+    for (int p = 0; p < 4; ++p)
+        if (tb + p < len) dkeys[((long long)b * T + tb + p) * AD + d] += dk[p];
+    // the two position halves of the CTA combine in shared memory; one atomic per element and CTA into the row's accumulator
+    __syncthreads();
+    float* sx = &s_x[0][0];
+    if (hf == 1) {
+#pragma unroll
+        for (int j = 0; j < KW; ++j) sx[j * AD + d] = dU[j];
+        sx[KW * AD + d] = dc0; sx[(KW + 1) * AD + d] = dva;
+    }
+    __syncthreads();
+    if (hf == 0) {
+        float* out = acc_out + (long long)b * ACC_N;
+#pragma unroll
+        for (int j = 0; j < KW; ++j) atomicAdd(out + j * AD + d, dU[j] + sx[j * AD + d]);
+        atomicAdd(out + KW * AD + d, dc0 + sx[KW * AD + d]);
+        atomicAdd(out + (KW + 1) * AD + d, dva + sx[(KW + 1) * AD + d]);
+    }
+}
+
+// chain rule of the fold: block j < KW: d(conv_w)[j,:]; block KW + f: d(Wl)[f,:]; block KW + NF: d(conv_b), d(v_a), d(b_a).
+// acc [B][ACC_N] is summed over the rows on the fly; results are ADDED to the outputs.
+__global__ void __launch_bounds__(AD) attn_fold_bwd_kernel(const float* __restrict__ acc, const float* __restrict__ cw,
+                                                           const float* __restrict__ cb, const float* __restrict__ Wl,
+                                                           float* __restrict__ g_cw, float* __restrict__ g_cb, float* __restrict__ g_Wl,
+                                                           float* __restrict__ g_va, float* __restrict__ g_ba, int B) {
+    __shared__ float s_v[AD];
+    const int blk = blockIdx.x, d = threadIdx.x, lane = d & 31, warp = d >> 5;
+    auto rowsum = [&](int off) { float a = 0.f; for (int b = 0; b < B; ++b) a += acc[(long long)b * ACC_N + off + d]; return a; };
+    if (blk < KW || blk == KW + NF) {                 // d(conv_w)[j,f] = sum_d dU[j,d] Wl[f,d]; d(conv_b)[f] = sum_d dc0[d] Wl[f,d]
+        const float v = rowsum(blk < KW ? blk * AD : KW * AD);
+        s_v[d] = v;
+        __syncthreads();
+        for (int f = warp; f < NF; f += AD / 32) {
+            float a = 0.f;
+            for (int k = lane; k < AD; k += 32) a = fmaf(s_v[k], Wl[f * AD + k], a);
+            a = warp_sum(a);
+            if (lane == 0) { if (blk < KW) g_cw[blk * NF + f] += a; else g_cb[f] += a; }
+        }
+        if (blk == KW + NF) { g_ba[d] += v; g_va[d] += rowsum((KW + 1) * AD); }
+    } else {                                          // d(Wl)[f,d] = sum_j cw[j,f] dU[j,d] + cb[f] dc0[d]
+        const int f = blk - KW;
+        float a = cb[f] * rowsum(KW * AD);
+        for (int j = 0; j < KW; ++j) a = fmaf(cw[j * NF + f], rowsum(j * AD), a);
+        g_Wl[f * AD + d] += a;
+    }
+}
+
+template <class K>
+inline bool ensure_smem(K kernel, size_t bytes) {
+    return bytes <= 48 * 1024 || cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes) == cudaSuccess;
+}
+inline size_t fwd_smem(int T, int D, int V) {
+    const int Tp = (T + 3) & ~3, nq = ((V >> 2) + CS - 1) / CS, ntg = FT / nq;
+    return sizeof(float) * ((size_t)Tp + 32 + (size_t)Tp * 4 + AD + 4 * AD + D + 32) + sizeof(float4) * (size_t)ntg * nq;
+}
+inline size_t row_smem(int T) {
+    const int Tp = (T + 3) & ~3;
+    return sizeof(float) * ((size_t)Tp * RS + 32 * RS + (size_t)Tp * GS + Tp + 4 * AD + 32);
+}
+
+}  // namespace
+
+extern "C" {
+
+int taco_op_attn_fused_supported(int T, int D, int A, int V, int NFf, int KWf) {
+    return A == AD && NFf == NF && KWf == KW && T >= 1 && T <= 2048 && D >= 4 && D % 4 == 0 && V % 4 == 0 &&
+           ((V >> 2) + CS - 1) / CS <= FT && row_smem(T) <= 200 * 1024 && fwd_smem(T, D, V) <= 200 * 1024;
+}
+
+int taco_op_attn_fold(const float* conv_w, const float* conv_b, const float* Wl, float* U, float* c0, void* stream) {
+    if (!conv_w || !conv_b || !Wl || !U || !c0) return -1;
+    attn_fold_kernel<<<KW + 1, AD, 0, (cudaStream_t)stream>>>(conv_w, conv_b, Wl, U, c0);
+    return cudaGetLastError() == cudaSuccess ? 0 : -3;
+}
+
+int taco_op_attn_fwd_fused(const float* h2raw, const float* Wq, const float* U, const float* c0, const float* ba, const float* va,
+                           const float* cum_prev, const float* keys, const float* values, const int32_t* lens, float* q, float* th,
+                           float* align, float* cum, float* ctx, int B, int T, int D, int V, void* stream) {
+    if (!h2raw || !Wq || !U || !c0 || !ba || !va || !cum_prev || !keys || !values || !lens || !q || !th || !align || !cum || !ctx) return -1;
+    if (B < 1 || !taco_op_attn_fused_supported(T, D, AD, V, NF, KW)) return -1;
+    const size_t sm = fwd_smem(T, D, V);
+    if (!ensure_smem(attn_fwd_fused_kernel, sm)) return -3;
+    attn_fwd_fused_kernel<<<dim3(CS, B), FT, sm, (cudaStream_t)stream>>>(h2raw, Wq, U, c0, ba, va, cum_prev, keys, values, lens, q, th, align,
+                                                                        cum, ctx, T, D, V);
+    return cudaGetLastError() == cudaSuccess ? 0 : -3;
+}
+
+int taco_op_attn_bwd_fused(float* dctx, const float* carry, const float* dcum, const float* align, const float* th, const float* values,
+                           const int32_t* lens, const float* U, const float* va, const float* Wq, float* de, float* dq, float* dh2,
+                           float* dcum_prev, float* scratch, int B, int T, int D, int V, void* stream) {
+    if (!dctx || !carry || !dcum || !align || !th || !values || !lens || !U || !va || !Wq || !de || !dq || !dh2 || !dcum_prev || !scratch) return -1;
+    if (B < 1 || !taco_op_attn_fused_supported(T, D, AD, V, NF, KW)) return -1;
+    cudaStream_t st = (cudaStream_t)stream;
+    attn_bwd_dalign_fused_kernel<<<dim3((T + 7) / 8, B), 256, sizeof(float) * V, st>>>(dctx, carry, dcum, values, lens, scratch, T, V);
+    const size_t sm = row_smem(T);
+    if (!ensure_smem(attn_bwd_row_kernel, sm)) return -3;
+    attn_bwd_row_kernel<<<B, FT, sm, st>>>(dctx, carry, dcum, scratch, align, th, lens, U, va, Wq, de, dq, dh2, dcum_prev, T, D, V);
+    return cudaGetLastError() == cudaSuccess ? 0 : -3;
+}
+
+int taco_op_attn_bwd_hoisted(const float* de, const float* th, const float* cum, const int32_t* lens, const float* conv_w,
+                             const float* conv_b, const float* Wl, const float* va, float* dkeys, float* g_conv_w, float* g_conv_b,
+                             float* g_Wl, float* g_va, float* g_ba, float* work, int S, int B, int T, void* stream) {
+    if (!de || !th || !cum || !lens || !conv_w || !conv_b || !Wl || !va || !dkeys || !g_conv_w || !g_conv_b || !g_Wl || !g_va || !g_ba || !work)
+        return -1;
+    if (S < 1 || B < 1 || T < 1) return -1;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (cudaMemsetAsync(work, 0, sizeof(float) * (size_t)B * ACC_N, st) != cudaSuccess) return -3;
+    attn_bwd_hoisted_kernel<<<dim3((T + HP - 1) / HP, B), 256, 0, st>>>(de, th, cum, lens, va, dkeys, work, S, B, T);
+    attn_fold_bwd_kernel<<<KW + NF + 1, AD, 0, st>>>(work, conv_w, conv_b, Wl, g_conv_w, g_conv_b, g_Wl, g_va, g_ba, B);
+    return cudaGetLastError() == cudaSuccess ? 0 : -3;
+}
+
+}  // extern "C"

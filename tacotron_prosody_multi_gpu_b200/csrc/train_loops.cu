@@ -24,6 +24,11 @@ int taco_op_decoder_loop_fwd(const TacoDecLoop* p, void* st) {
         cudaMemsetAsync(p->acts2, 0, sizeof(float) * (size_t)S * B * G, cs) != cudaSuccess ||
         cudaMemsetAsync(p->q, 0, sizeof(float) * (size_t)S * B * A, cs) != cudaSuccess)
         return -3;
+    // fused attention (train_attn_fused.cu): query projection + attention step in one launch, tanh(pre) saved for the backward pass
+    const bool fused = p->th && p->attn_work && taco_op_attn_fused_supported(T, D, A, MD, p->NF, p->KW);
+    float* Uf = p->attn_work;
+    float* c0 = Uf ? Uf + (size_t)p->KW * A : nullptr;
+    if (fused) OK(taco_op_attn_fold(p->conv_w, p->conv_b, p->Wl, Uf, c0, st));
     for (int s = 0; s < S; ++s) {
         const size_t oD = (size_t)s * B * D, oG = (size_t)s * B * G, nD = oD + (size_t)B * D;
         float* a1 = p->acts1 + oG;
@@ -35,6 +40,12 @@ int taco_op_decoder_loop_fwd(const TacoDecLoop* p, void* st) {
         OK(taco_op_lstm_fwd(a2, nullptr, p->b2, p->c2z + oD, p->h2z + oD, nullptr, 0, p->zoneout, 1, p->zo_keep_thresh, p->seed,
                             p->stream2, p->stream2 + 1, s * B, p->c2new + oD, p->c2z + nD, p->h2raw + oD, p->h2z + nD, B, D, st));
         float* q = p->q + (size_t)s * B * A;
+        if (fused) {
+            OK(taco_op_attn_fwd_fused(p->h2raw + oD, p->Wq, Uf, c0, p->ba, p->va, p->cum + (size_t)s * B * T, p->keys, p->values, p->lens,
+                                      q, p->th + (size_t)s * B * T * A, p->align + (size_t)s * B * T, p->cum + (size_t)(s + 1) * B * T,
+                                      p->ctx + (size_t)(s + 1) * B * MD, B, T, D, MD, st));
+            continue;
+        }
         OK(taco_op_gemm(p->h2raw + oD, D, p->Wq, A, q, A, B, A, D, 0, 0, 1.f, nullptr, st));
         OK(taco_op_attn_fwd(q, p->cum + (size_t)s * B * T, p->keys, p->values, p->lens, p->conv_w, p->conv_b, p->Wl, p->va, p->ba,
                             p->align + (size_t)s * B * T, p->cum + (size_t)(s + 1) * B * T, p->ctx + (size_t)(s + 1) * B * MD, B, T, A, MD,
@@ -62,20 +73,27 @@ int taco_op_decoder_loop_bwd(const TacoDecLoop* p, void* st) {
     float* attn_scratch = dcum_n + (size_t)B * T;      // [B][T][NF]
     float* dh1raw_all = attn_scratch + (size_t)B * T * p->NF;
     float* dcarry_all = dh1raw_all + (size_t)S * B * D;   // slot s+1 = carry INTO step s (slot S = 0)
+    const bool fused = p->th && p->de && p->attn_work && taco_op_attn_fused_supported(T, D, A, MD, p->NF, p->KW);
+    float* Uf = p->attn_work;               // folded by the forward loop of this step
     for (int s = S - 1; s >= 0; --s) {
         const size_t oD = (size_t)s * B * D, oG = (size_t)s * B * G;
         float* dctx = p->dCtx + (size_t)s * B * MD;
         float* dh1raw = dh1raw_all + (size_t)s * B * D;
         const float* dctx_carry = dcarry_all + (size_t)(s + 1) * B * MD;
         float* dctx_carry_out = dcarry_all + (size_t)s * B * MD;
-        OK(taco_op_ew(TACO_EW_ADD, dctx, dctx, dctx_carry, 1.f, (long long)B * MD, st));
         float* dq = p->dQ + (size_t)s * B * A;
-        OK(taco_op_attn_bwd(dctx, dcum, p->q + (size_t)s * B * A, p->cum + (size_t)s * B * T, p->align + (size_t)s * B * T, p->keys,
-                            p->values, p->lens, p->conv_w, p->conv_b, p->Wl, p->va, p->ba, dq, dcum_n, p->dkeys, p->p_conv_w,
-                            p->p_conv_b, p->p_Wl, p->p_va, p->p_ba, attn_scratch, B, T, A, MD, p->NF, p->KW, st));
-        { float* t_ = dcum; dcum = dcum_n; dcum_n = t_; }
         float* dh2 = p->dH2 + oD;
-        OK(taco_op_gemm(dq, A, p->Wq, A, dh2, D, B, D, A, 0, 1, 1.f, nullptr, st));
+        if (fused) {
+            OK(taco_op_attn_bwd_fused(dctx, dctx_carry, dcum, p->align + (size_t)s * B * T, p->th + (size_t)s * B * T * A, p->values, p->lens,
+                                      Uf, p->va, p->Wq, p->de + (size_t)s * B * T, dq, dh2, dcum_n, attn_scratch, B, T, D, MD, st));
+        } else {
+            OK(taco_op_ew(TACO_EW_ADD, dctx, dctx, dctx_carry, 1.f, (long long)B * MD, st));
+            OK(taco_op_attn_bwd(dctx, dcum, p->q + (size_t)s * B * A, p->cum + (size_t)s * B * T, p->align + (size_t)s * B * T, p->keys,
+                                p->values, p->lens, p->conv_w, p->conv_b, p->Wl, p->va, p->ba, dq, dcum_n, p->dkeys, p->p_conv_w,
+                                p->p_conv_b, p->p_Wl, p->p_va, p->p_ba, attn_scratch, B, T, A, MD, p->NF, p->KW, st));
+            OK(taco_op_gemm(dq, A, p->Wq, A, dh2, D, B, D, A, 0, 1, 1.f, nullptr, st));
+        }
+        { float* t_ = dcum; dcum = dcum_n; dcum_n = t_; }
         OK(taco_op_lstm_bwd(p->acts2 + oG, p->c2z + oD, p->h2z + oD, p->c2new + oD, nullptr, 0, p->zoneout, 1, p->zo_keep_thresh, p->seed,
                             p->stream2, p->stream2 + 1, s * B, dh2, dc2, dh2z, p->dG2 + oG, dc2n, dh2zn, B, D, st));
         OK(taco_op_gemm_nt_split_acc(p->dG2 + oG, G, p->W2, G, dh1raw, D, D, dh2zn, D, D, B, G, st));
@@ -88,6 +106,10 @@ int taco_op_decoder_loop_bwd(const TacoDecLoop* p, void* st) {
         t_ = dc2; dc2 = dc2n; dc2n = t_;
         t_ = dh2z; dh2z = dh2zn; dh2zn = t_;
     }
+    // d(keys) and the attention weight gradients of all S steps in one pass (row 0 of the per-row partial buffers)
+    if (fused)
+        OK(taco_op_attn_bwd_hoisted(p->de, p->th, p->cum, p->lens, p->conv_w, p->conv_b, p->Wl, p->va, p->dkeys, p->p_conv_w, p->p_conv_b,
+                                    p->p_Wl, p->p_va, p->p_ba, Uf + (size_t)(p->KW + 1) * A, S, B, T, st));
     return 0;
 }
 

@@ -34,6 +34,10 @@ _SIGS = {
     "taco_op_scatter_rows": [_P, _P, _I, _I, _P, _LL, _LL, _I, _I, _P],
     "taco_op_attn_fwd": [_P] * 13 + [_I] * 6 + [_P],
     "taco_op_attn_bwd": [_P] * 22 + [_I] * 6 + [_P],
+    "taco_op_attn_fold": [_P] * 5 + [_P],
+    "taco_op_attn_fwd_fused": [_P] * 15 + [_I] * 4 + [_P],
+    "taco_op_attn_bwd_fused": [_P] * 15 + [_I] * 4 + [_P],
+    "taco_op_attn_bwd_hoisted": [_P] * 15 + [_I] * 3 + [_P],
     "taco_op_gru_pre": [_P, _P, _P, _I, _I, _P],
     "taco_op_gru_out": [_P, _P, _P, _P, _I, _I, _P],
     "taco_op_gru_out_bwd": [_P, _P, _P, _P, _P, _P, _P, _I, _I, _P],
@@ -206,6 +210,30 @@ class CudaOps(object):
                    _c(conv_b), _c(Wl), _c(va), _c(ba), _c(dq), _c(dcum_prev), _c(dkeys), _c(p_conv_w), _c(p_conv_b), _c(p_Wl),
                    _c(p_va), _c(p_ba), _c(self.empty(B * T * conv_w.shape[2])), B, T, A, values.shape[2], conv_w.shape[2], conv_w.shape[0])
 
+    # fused attention of the time loops (train_attn_fused.cu)
+    def attn_fused_supported(self, T, D, A, V, NF, KW):
+        fn = self.L.taco_op_attn_fused_supported
+        fn.argtypes, fn.restype = [C.c_int] * 6, C.c_int
+        return bool(fn(T, D, A, V, NF, KW))
+
+    def attn_fold(self, conv_w, conv_b, Wl, U, c0):
+        self._call("taco_op_attn_fold", _c(conv_w), _c(conv_b), _c(Wl), _c(U), _c(c0))
+
+    def attn_fwd_fused(self, h2raw, Wq, U, c0, ba, va, cum_prev, keys, values, lens, q, th, align, cum, ctx):
+        B, T, _ = keys.shape
+        self._call("taco_op_attn_fwd_fused", _c(h2raw), _c(Wq), _c(U), _c(c0), _c(ba), _c(va), _c(cum_prev), _c(keys), _c(values), _c(lens),
+                   _c(q), _c(th), _c(align), _c(cum), _c(ctx), B, T, h2raw.shape[1], values.shape[2])
+
+    def attn_bwd_fused(self, dctx, carry, dcum, align, th, values, lens, U, va, Wq, de, dq, dh2, dcum_prev):
+        B, T, V = values.shape
+        self._call("taco_op_attn_bwd_fused", _c(dctx), _c(carry), _c(dcum), _c(align), _c(th), _c(values), _c(lens), _c(U), _c(va), _c(Wq),
+                   _c(de), _c(dq), _c(dh2), _c(dcum_prev), _c(self.empty(B * T)), B, T, dh2.shape[1], V)
+
+    def attn_bwd_hoisted(self, de, th, cum, lens, conv_w, conv_b, Wl, va, dkeys, g_conv_w, g_conv_b, g_Wl, g_va, g_ba):
+        S, B, T = de.shape
+        self._call("taco_op_attn_bwd_hoisted", _c(de), _c(th), _c(cum), _c(lens), _c(conv_w), _c(conv_b), _c(Wl), _c(va), _c(dkeys),
+                   _c(g_conv_w), _c(g_conv_b), _c(g_Wl), _c(g_va), _c(g_ba), _c(self.empty(B * (conv_w.shape[0] + 2) * Wl.shape[1])), S, B, T)
+
     # ------------------------------------------------------------------ GRU / GST
     def gru_pre(self, g, h, rh):
         self._call("taco_op_gru_pre", _c(g), _c(h), _c(rh), h.shape[0], h.shape[1])
@@ -291,7 +319,7 @@ class TacoDecLoop(C.Structure):
                 [(n, C.c_void_p) for n in ("W1", "W2", "b2", "Wq", "conv_w", "conv_b", "Wl", "va", "ba", "keys", "values", "lens", "G1x",
                                            "acts1", "acts2", "c1new", "c2new", "h1raw", "h2raw", "c1z", "h1z", "c2z", "h2z", "ctx", "cum",
                                            "align", "q", "dH2", "dCtx", "dG1", "dG2", "dQ", "dkeys", "p_conv_w", "p_conv_b", "p_Wl",
-                                           "p_va", "p_ba", "work")])
+                                           "p_va", "p_ba", "work", "th", "de", "attn_work")])
 
 
 class TacoLstmLoop(C.Structure):
@@ -329,7 +357,9 @@ def _loop_call(self, name, struct, n_launch):
 def _decoder_loop(self, bwd, dims, zoneout, seed, stream1, stream2, **t):
     s = _fill(TacoDecLoop(), dict(dims, zoneout=float(zoneout), zo_keep_thresh=keep_threshold(1.0 - zoneout), seed=seed,
                                    stream1=stream1, stream2=stream2), t)
-    _loop_call(self, "taco_op_decoder_loop_bwd" if bwd else "taco_op_decoder_loop_fwd", s, dims["S"] * (9 if bwd else 8))
+    fused = t.get("th") is not None and t.get("attn_work") is not None
+    per_step = ((6 if fused else 12) if bwd else (5 if fused else 8))
+    _loop_call(self, "taco_op_decoder_loop_bwd" if bwd else "taco_op_decoder_loop_fwd", s, dims["S"] * per_step)
 
 
 def _lstm_loop(self, bwd, dims, zoneout, seed, stream_c, stream_h, out, **t):
@@ -342,7 +372,7 @@ def _lstm_loop(self, bwd, dims, zoneout, seed, stream_c, stream_h, out, **t):
 
 CudaOps.decoder_loop = _decoder_loop
 CudaOps.lstm_loop = _lstm_loop
-TRAIN_SYMBOLS = tuple(_SIGS.keys()) + LOOP_SYMBOLS + ("taco_op_set_precision", "taco_op_gemm_pair_acc", "taco_op_gemm_nt_split_acc")
+TRAIN_SYMBOLS = tuple(_SIGS.keys()) + LOOP_SYMBOLS + ("taco_op_set_precision", "taco_op_gemm_pair_acc", "taco_op_gemm_nt_split_acc", "taco_op_attn_fused_supported")
 
 
 def _set_precision(self, precision):

@@ -273,8 +273,12 @@ class TrainStep(object):
         s1, s2 = STREAM_DEC_LSTM, STREAM_DEC_LSTM + 2
         dims = dict(B=B, T=T, S=S, D=D, MD=MD, A=A, U2=U2, NF=att_w[0].shape[2], KW=att_w[0].shape[0])
         fast = hasattr(o, "decoder_loop")           # the same loop sequenced in C (train_loops.cu)
+        th = attn_work = None
+        if fast and o.attn_fused_supported(T, D, A, MD, dims["NF"], dims["KW"]):
+            # fused attention of the loops (csrc/train_attn_fused.cu): tanh(pre) of every step is kept for the backward pass
+            th, attn_work = o.empty(S, B, T, A), o.empty((dims["KW"] + 1) * A + B * (dims["KW"] + 2) * A)
         if fast:
-            o.decoder_loop(False, dims, zo, seed, s1, s2, W1=W1, W2=W2, b2=b2, Wq=Wq, conv_w=att_w[0], conv_b=att_w[1], Wl=att_w[2],
+            o.decoder_loop(False, dims, zo, seed, s1, s2, th=th, attn_work=attn_work, W1=W1, W2=W2, b2=b2, Wq=Wq, conv_w=att_w[0], conv_b=att_w[1], Wl=att_w[2],
                            va=att_w[3], ba=att_w[4], keys=keys, values=values, lens=lens_eff, G1x=G1x, acts1=acts1, acts2=acts2,
                            c1new=c1new, c2new=c2new, h1raw=h1raw, h2raw=h2raw, c1z=c1z, h1z=h1z, c2z=c2z, h2z=h2z, ctx=ctx, cum=cum,
                            align=align, q=q)
@@ -289,7 +293,7 @@ class TrainStep(object):
                        c2new[s], c2z[s + 1], h2raw[s], h2z[s + 1])
             o.gemm(h2raw[s], Wq, q[s])
             o.attn_fwd(q[s], cum[s], keys, values, lens_eff, *att_w, align[s], cum[s + 1], ctx[s + 1])
-        t.update(dec_dims=dims, G1x=G1x, Xin=Xin, P1=P1, P2=P2, acts1=acts1, acts2=acts2, c1new=c1new, c2new=c2new, h1raw=h1raw, h2raw=h2raw,
+        t.update(th=th, attn_work=attn_work, dec_dims=dims, G1x=G1x, Xin=Xin, P1=P1, P2=P2, acts1=acts1, acts2=acts2, c1new=c1new, c2new=c2new, h1raw=h1raw, h2raw=h2raw,
                  c1z=c1z, h1z=h1z, c2z=c2z, h2z=h2z, ctx=ctx, cum=cum, align=align, q=q)
         # frame / stop projections on [LSTM_output, context] for all steps at once (Decoder.py:355-410)
         Wf, Ws = P[W.FRAME_PROJ + "/kernel"], P[W.STOP_PROJ + "/kernel"]
@@ -406,7 +410,8 @@ class TrainStep(object):
         s1, s2 = STREAM_DEC_LSTM, STREAM_DEC_LSTM + 2
         fast = hasattr(o, "decoder_loop")
         if fast:
-            o.decoder_loop(True, t["dec_dims"], zo, seed, s1, s2, W1=W1, W2=W2, Wq=Wq, conv_w=att_w[0], conv_b=att_w[1], Wl=att_w[2],
+            o.decoder_loop(True, t["dec_dims"], zo, seed, s1, s2, th=t["th"], attn_work=t["attn_work"],
+                           de=o.empty(S, B, T) if t["th"] is not None else None, W1=W1, W2=W2, Wq=Wq, conv_w=att_w[0], conv_b=att_w[1], Wl=att_w[2],
                            va=att_w[3], ba=att_w[4], keys=keys, values=values, lens=lens_eff, acts1=t["acts1"], acts2=t["acts2"],
                            c1new=t["c1new"], c2new=t["c2new"], c1z=t["c1z"], h1z=t["h1z"], c2z=t["c2z"], h2z=t["h2z"], cum=t["cum"],
                            align=t["align"], q=t["q"], dH2=dH2, dCtx=dCtx, dG1=dG1, dG2=dG2, dQ=dQ, dkeys=dkeys, p_conv_w=parts[0],

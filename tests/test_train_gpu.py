@@ -150,6 +150,63 @@ def test_attention_step_fwd_bwd(ops, T):
         np.testing.assert_allclose(a_gpu[i].sum(0).cpu().numpy(), a_cpu[i].sum(0).numpy(), atol=2e-4, rtol=1e-4, err_msg="attn_bwd partial %d" % i)
 
 
+@pytest.mark.parametrize("T,D", [(9, 256), (111, 256), (230, 64)])
+def test_fused_attention_of_the_time_loops_matches_the_op_by_op_kernels(ops, T, D):
+    """train_attn_fused.cu (one launch forward, two backward per decoder step, weight / key gradients hoisted out of the BPTT loop)
+    against the op-by-op kernels checked above, over a 3-step chain: the carried cumulative alignments forward, the carried
+    d(cum) backward; the hoisted gradients against the per-step accumulation.  Same fp32 arithmetic, different summation
+    order (folded 31-tap filter bank): 2e-5 absolute on O(1) values, 1e-4 relative on the accumulated gradients."""
+    cu, _ = ops
+    S, B, A, V = 3, 4, 128, 768
+    lens = torch.tensor([T, max(1, T // 2), max(1, T - 3), 1], dtype=torch.int32).cuda()
+    keys, values = R(B, T, A).cuda(), R(B, T, V).cuda()
+    cw, cb, Wl, va, ba = (x.cuda() for x in (R(31, 1, 32, scale=0.3), R(32, scale=0.1), R(32, A, scale=0.2), R(A, scale=0.3), R(A, scale=0.1)))
+    Wq, h2 = R(D, A, scale=0.1).cuda(), R(S, B, D, seed=4).cuda()
+    z = lambda *sh: torch.zeros(*sh, device="cuda")
+    # forward, op by op
+    q0, al0, cum0, ctx0 = z(S, B, A), z(S, B, T), z(S + 1, B, T), z(S, B, V)
+    for s in range(S):
+        q0[s] = h2[s] @ Wq
+        cu.attn_fwd(q0[s], cum0[s], keys, values, lens, cw, cb, Wl, va, ba, al0[s], cum0[s + 1], ctx0[s])
+    # forward, fused
+    U, c0 = z(31, A), z(A)
+    cu.attn_fold(cw, cb, Wl, U, c0)
+    q1, al1, cum1, ctx1, th = z(S, B, A), z(S, B, T), z(S + 1, B, T), z(S, B, V), torch.full((S, B, T, A), float("nan"), device="cuda")
+    for s in range(S):
+        cu.attn_fwd_fused(h2[s], Wq, U, c0, ba, va, cum1[s], keys, values, lens, q1[s], th[s], al1[s], cum1[s + 1], ctx1[s])
+    for name, a, b in (("q", q1, q0), ("align", al1, al0), ("cum", cum1, cum0), ("ctx", ctx1, ctx0)):
+        np.testing.assert_allclose(a.cpu().numpy(), b.cpu().numpy(), atol=2e-5, rtol=1e-5, err_msg=name)
+    assert float(al1[:, 1, max(1, T // 2):].abs().sum()) == 0.0          # exact zeros beyond the length
+    # backward chain, op by op
+    dctx_in, carry = R(S, B, V, seed=2).cuda(), R(S, B, V, seed=6).cuda() * 0.5
+    parts = [z(B, 31, 1, 32), z(B, 32), z(B, 32, A), z(B, A), z(B, A)]
+    dkeys0, dq0, dh20 = z(B, T, A), z(S, B, A), R(S, B, D, seed=8).cuda()
+    dh2_init = dh20.clone()
+    tot0 = dctx_in + carry
+    dcum, dcum_n = R(B, T, seed=3).cuda(), z(B, T)
+    dcum_init = dcum.clone()
+    for s in range(S - 1, -1, -1):
+        cu.attn_bwd(tot0[s], dcum, q0[s], cum0[s], al0[s], keys, values, lens, cw, cb, Wl, va, ba, dq0[s], dcum_n, dkeys0, *parts)
+        dh20[s] += dq0[s] @ Wq.t()
+        dcum, dcum_n = dcum_n, dcum
+    dcum_end0 = dcum.clone()
+    # backward chain, fused + hoisted
+    tot1, de, dq1, dh21 = dctx_in.clone(), z(S, B, T), z(S, B, A), dh2_init.clone()
+    dcum, dcum_n = dcum_init.clone(), z(B, T)
+    for s in range(S - 1, -1, -1):
+        cu.attn_bwd_fused(tot1[s], carry[s], dcum, al1[s], th[s], values, lens, U, va, Wq, de[s], dq1[s], dh21[s], dcum_n)
+        dcum, dcum_n = dcum_n, dcum
+    g = [z(31, 1, 32), z(32), z(32, A), z(A), z(A)]
+    dkeys1 = z(B, T, A)
+    cu.attn_bwd_hoisted(de, th, cum1[:S].contiguous(), lens, cw, cb, Wl, va, dkeys1, *g)
+    torch.cuda.synchronize()
+    for name, a, b in (("total dctx", tot1, tot0), ("dq", dq1, dq0), ("dh2", dh21, dh20), ("dcum", dcum, dcum_end0), ("dkeys", dkeys1, dkeys0)):
+        np.testing.assert_allclose(a.cpu().numpy(), b.cpu().numpy(), atol=3e-5, rtol=1e-4, err_msg=name)
+    for name, a, b in zip(("d conv_w", "d conv_b", "d Wl", "d va", "d ba"), g, parts):
+        ref = b.sum(0).cpu().numpy()
+        np.testing.assert_allclose(a.cpu().numpy(), ref, atol=1e-4 * max(1.0, float(np.abs(ref).max())), rtol=1e-4, err_msg=name)
+
+
 def test_gru_gst_pointwise(ops):
     B, Rr = 6, 128
     g, h = R(B, 2 * Rr), R(B, Rr, seed=1)
