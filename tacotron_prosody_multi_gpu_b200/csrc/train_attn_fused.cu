@@ -4,21 +4,26 @@
 //
 //   fold     U[j,d] = sum_f conv_w[j,f] Wl[f,d], c0[d] = sum_f conv_b[f] Wl[f,d]: the location convolution and the location
 //            dense layer are one 31-tap filter bank [31,128] (no nonlinearity between them), folded once per training step
-//   forward  grid (4 value-column slices, B rows), 512 threads: q = h2raw . Wq, tanh pre-activations of all positions of the
-//            row (kept in registers as a sliding 31-tap window per thread; every CTA of a row computes them, the 4 CTAs
-//            share the stores of tanh(pre) [T,128], which the backward pass reads instead of recomputing it), masked
-//            softmax, cumulative update, and this CTA's 192 columns of the context
+//   forward  grid (4, B rows) in clusters of the 4 CTAs of a row, 512 threads: q = h2raw . Wq, tanh pre-activations (a 31-tap
+//            window of the cumulative alignments per thread in registers) of this CTA's quarter of the positions, stored as
+//            tanh(pre) [T,128] for the backward pass; the partial energies go to all 4 CTAs through distributed shared
+//            memory; then every CTA does the masked softmax + cumulative update and its 192 columns of the context
 //   backward d(align) grid (T/8, B): values . (d(ctx) + carry) + d(cum)
-//            row kernel grid (B): softmax gradient, d(pre), d(q) -> d(h2raw) += d(q) Wq^T, d(cum_{t-1}) through the folded
-//            filter bank (4x4 register tiles over the shared-memory d(pre) tile); saves d(energy) [T] per step
+//            row kernel grid (4, B), clusters of the 4 CTAs of a row: softmax gradient, d(pre) and the tap gradients of a
+//            quarter of the positions (4x4 register tiles over the shared-memory d(pre) tile), d(q) -> d(h2raw) += d(q) Wq^T,
+//            d(cum_{t-1}) through the folded filter bank (halo rows read from the neighbours' shared memory); saves
+//            d(energy) [T] per step
 //   hoisted  after the loop, grid (T/8, B) looping over all S steps: d(keys), d(U), d(c0), d(v_a) from the saved d(energy)
 //            and tanh(pre); then d(conv_w), d(conv_b), d(Wl), d(b_a) from d(U), d(c0) by the chain rule of the fold
+#include <cooperative_groups.h>
 #include <cuda_runtime.h>
 #include <math.h>
 #include <stdint.h>
 
 #include "../../include/taco_b200_train.h"
 #include "common.cuh"
+
+namespace cg = cooperative_groups;
 
 namespace {
 
@@ -48,12 +53,13 @@ __device__ __forceinline__ float block_reduce(float v, float* red, bool is_max) 
 }
 
 // ------------------------------------------------------------------------------------------------ forward
-__global__ void __launch_bounds__(FT) attn_fwd_fused_kernel(
+__global__ void __cluster_dims__(CS, 1, 1) __launch_bounds__(FT, 1) attn_fwd_fused_kernel(
     const float* __restrict__ h2raw, const float* __restrict__ Wq, const float* __restrict__ U, const float* __restrict__ c0,
     const float* __restrict__ ba, const float* __restrict__ va, const float* __restrict__ cum_prev, const float* __restrict__ keys,
     const float* __restrict__ values, const int32_t* __restrict__ lens, float* __restrict__ q_out, float* __restrict__ th_out,
     float* __restrict__ align, float* __restrict__ cum, float* __restrict__ ctx, int T, int D, int V) {
     extern __shared__ __align__(16) float smem[];
+    cg::cluster_group cl = cg::this_cluster();
     const int Tp = (T + 3) & ~3;
     float* s_cum = smem;                       // [Tp + 32]: cum_prev[t - LEFT], zero padded
     float* s_e = s_cum + Tp + 32;              // [Tp][4] partial energies (one per warp of a 128-thread group) -> [Tp] alignments
@@ -65,24 +71,38 @@ __global__ void __launch_bounds__(FT) attn_fwd_fused_kernel(
     const int cs = blockIdx.x, b = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int len = min(lens[b], T);
     const int d = tid & (AD - 1), g = tid >> 7;
+    const int nblk = (len + 3) >> 2;
+    // the 4 CTAs of a row (one cluster) split the 4-position blocks of the row: CTA cs, thread group g takes blocks
+    // cs + 4 g, cs + 4 g + 16, ...; the keys of the first block are in flight before anything else
+    int blk = cs + CS * g;
+    float kv[4];
+#pragma unroll
+    for (int p = 0; p < 4; ++p) kv[p] = (blk < nblk && blk * 4 + p < len) ? keys[((long long)b * T + blk * 4 + p) * AD + d] : 0.f;
 
-    float Ur[KW];
+    float Ur[KW], wq0[32];                      // filter-bank column and the first 32 rows of this thread's Wq column: in flight
 #pragma unroll
     for (int j = 0; j < KW; ++j) Ur[j] = U[j * AD + d];
+    {
+        const int k0 = g * (D / 4), k1 = (g == 3) ? D : k0 + D / 4;
+#pragma unroll
+        for (int k = 0; k < 32; ++k) wq0[k] = k0 + k < k1 ? Wq[(long long)(k0 + k) * AD + d] : 0.f;
+    }
     for (int i = tid; i < Tp + 32; i += FT) {
         const int t = i - LEFT;
         s_cum[i] = (t >= 0 && t < T) ? cum_prev[(long long)b * T + t] : 0.f;
     }
     for (int i = tid; i < D; i += FT) s_h[i] = h2raw[(long long)b * D + i];
     __syncthreads();
-    {   // q = h2raw . Wq, K split over the 4 thread groups
+    {   // q = h2raw . Wq, K split over the 4 thread groups (every CTA of the row computes it)
         const int k0 = g * (D / 4), k1 = (g == 3) ? D : k0 + D / 4;
         float a = 0.f;
-#pragma unroll 8
-        for (int k = k0; k < k1; ++k) a = fmaf(s_h[k], Wq[(long long)k * AD + d], a);
+#pragma unroll
+        for (int k = 0; k < 32; ++k) a = fmaf(k0 + k < k1 ? s_h[k0 + k] : 0.f, wq0[k], a);
+#pragma unroll 32
+        for (int k = k0 + 32; k < k1; ++k) a = fmaf(s_h[k], Wq[(long long)k * AD + d], a);
         s_qp[g * AD + d] = a;
     }
-    __syncthreads();
+    cl.sync();                                 // q partials visible; every CTA of the cluster runs (remote stores below are safe)
     if (tid < AD) {
         const float qv = s_qp[tid] + s_qp[AD + tid] + s_qp[2 * AD + tid] + s_qp[3 * AD + tid];
         if (cs == 0) q_out[(long long)b * AD + tid] = qv;
@@ -90,12 +110,12 @@ __global__ void __launch_bounds__(FT) attn_fwd_fused_kernel(
     }
     __syncthreads();
     const float qd = s_q[d], vad = va[d];
-    const int nblk = (len + 3) >> 2;
-    for (int blk = g; blk < nblk; blk += 4) {
-        const int t0 = blk * 4;
-        float kv[4];
+    float* s_e_rem = cl.map_shared_rank(s_e, lane & (CS - 1));     // lanes 0..3 forward a partial energy to the 4 CTAs of the row
+    for (; blk < nblk; blk += CS * 4) {
+        const int t0 = blk * 4, nxt = blk + CS * 4;
+        float kn[4];
 #pragma unroll
-        for (int p = 0; p < 4; ++p) kv[p] = (t0 + p < len) ? keys[((long long)b * T + t0 + p) * AD + d] : 0.f;
+        for (int p = 0; p < 4; ++p) kn[p] = (nxt < nblk && nxt * 4 + p < len) ? keys[((long long)b * T + nxt * 4 + p) * AD + d] : 0.f;
         float w[36];
 #pragma unroll
         for (int k = 0; k < 9; ++k) {
@@ -107,38 +127,40 @@ __global__ void __launch_bounds__(FT) attn_fwd_fused_kernel(
         for (int j = 0; j < KW; ++j)
 #pragma unroll
             for (int p = 0; p < 4; ++p) acc[p] = fmaf(Ur[j], w[p + j], acc[p]);
-        const bool writer = (blk & (CS - 1)) == cs;
 #pragma unroll
         for (int p = 0; p < 4; ++p) {
             const int t = t0 + p;
             float e = 0.f;
             if (t < len) {
                 const float th = tanhf(acc[p] + qd + kv[p]);
-                if (writer) th_out[((long long)b * T + t) * AD + d] = th;
+                th_out[((long long)b * T + t) * AD + d] = th;
                 e = vad * th;
             }
             e = warp_sum(e);
-            if (lane == 0) s_e[t * 4 + (warp & 3)] = e;
+            if (lane < CS) s_e_rem[t * 4 + (warp & 3)] = e;
+            kv[p] = kn[p];
         }
     }
+    cl.sync();
     __syncthreads();
-    // masked softmax over t < len (alignments beyond the length are exact zeros), cumulative update
+    // masked softmax over t < len (alignments beyond the length are exact zeros), cumulative update.  Every warp reduces the
+    // whole row by itself (shuffles only): no block barriers.
     float mx = -INFINITY;
-    for (int t = tid; t < len; t += FT) mx = fmaxf(mx, s_e[t * 4] + s_e[t * 4 + 1] + s_e[t * 4 + 2] + s_e[t * 4 + 3]);
-    mx = block_reduce(mx, s_red, true);
+    for (int t = lane; t < len; t += 32) mx = fmaxf(mx, s_e[t * 4] + s_e[t * 4 + 1] + s_e[t * 4 + 2] + s_e[t * 4 + 3]);
+    mx = warp_max(mx);
     float sum = 0.f;
-    for (int t = tid; t < len; t += FT) sum += expf(s_e[t * 4] + s_e[t * 4 + 1] + s_e[t * 4 + 2] + s_e[t * 4 + 3] - mx);
-    sum = block_reduce(sum, s_red, false);
+    for (int t = lane; t < len; t += 32) sum += expf(s_e[t * 4] + s_e[t * 4 + 1] + s_e[t * 4 + 2] + s_e[t * 4 + 3] - mx);
+    sum = warp_sum(sum);
     const float inv = 1.0f / sum;
-    float av[4];                                      // up to 4 positions per thread (T <= 2048)
+    float av[2];                                      // up to 2 positions per thread (T <= 1024)
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
+    for (int k = 0; k < 2; ++k) {
         const int t = tid + k * FT;
         av[k] = (t < len) ? expf(s_e[t * 4] + s_e[t * 4 + 1] + s_e[t * 4 + 2] + s_e[t * 4 + 3] - mx) * inv : 0.f;
     }
     __syncthreads();
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
+    for (int k = 0; k < 2; ++k) {
         const int t = tid + k * FT;
         if (t < T) {
             s_e[t] = av[k];
@@ -156,11 +178,15 @@ __global__ void __launch_bounds__(FT) attn_fwd_fused_kernel(
         float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
         if (c4 < V4) {
             const float4* vp = reinterpret_cast<const float4*>(values) + (long long)b * T * V4 + c4;
-#pragma unroll 4
-            for (int t = tg; t < len; t += ntg) {
-                const float a = s_e[t];
-                const float4 v = vp[(long long)t * V4];
-                acc.x = fmaf(a, v.x, acc.x); acc.y = fmaf(a, v.y, acc.y); acc.z = fmaf(a, v.z, acc.z); acc.w = fmaf(a, v.w, acc.w);
+            float4 v[12];                              // 12 value rows in flight per thread (one batch at T <= 120)
+            for (int tb = tg; tb < len; tb += 12 * ntg) {
+#pragma unroll
+                for (int i = 0; i < 12; ++i) v[i] = (tb + i * ntg < len) ? vp[(long long)(tb + i * ntg) * V4] : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+                for (int i = 0; i < 12; ++i) {
+                    const float a = (tb + i * ntg < len) ? s_e[tb + i * ntg] : 0.f;
+                    acc.x = fmaf(a, v[i].x, acc.x); acc.y = fmaf(a, v[i].y, acc.y); acc.z = fmaf(a, v[i].z, acc.z); acc.w = fmaf(a, v[i].w, acc.w);
+                }
             }
         }
         s_part[tg * nq + cq] = acc;
@@ -214,58 +240,107 @@ __global__ void __launch_bounds__(256) attn_bwd_dalign_fused_kernel(const float*
     if (lane == 0) da[(long long)b * T + t] = t < len ? acc : 0.f;
 }
 
-// everything of the attention gradient that feeds the recurrence, one CTA per row
-__global__ void __launch_bounds__(FT) attn_bwd_row_kernel(
+// everything of the attention gradient that feeds the recurrence: the 4 CTAs of a row (one cluster) split its positions into
+// contiguous quarters (d(pre) rows, tap gradients G) and the units of d(h2raw); d(q) partial sums and the G rows of the
+// neighbouring quarters (the 31-tap halo of d(cum_{t-1})) cross the cluster through distributed shared memory
+constexpr int XT = 32;    // tanh(pre) values a thread of the row kernel keeps in flight (positions g, g+4, ... of its quarter)
+__global__ void __cluster_dims__(CS, 1, 1) __launch_bounds__(FT, 1) attn_bwd_row_kernel(
     float* __restrict__ dctx, const float* __restrict__ carry, const float* __restrict__ dcum, const float* __restrict__ da,
     const float* __restrict__ align, const float* __restrict__ th, const int32_t* __restrict__ lens, const float* __restrict__ U,
     const float* __restrict__ va, const float* __restrict__ Wq, float* __restrict__ de_out, float* __restrict__ dq_out,
-    float* __restrict__ dh2, float* __restrict__ dcum_prev, int T, int D, int V) {
+    float* __restrict__ dh2, float* __restrict__ dcum_prev, int T, int D, int V, int Qmax) {
     extern __shared__ __align__(16) float smem[];
+    cg::cluster_group cl = cg::this_cluster();
     const int Tp = (T + 3) & ~3;
-    float* s_dpre = smem;                       // [Tp][RS]
-    float* s_U = s_dpre + (size_t)Tp * RS;      // [32][RS], row 31 = 0
-    float* s_G = s_U + 32 * RS;                 // [Tp][GS]: G[t][j] = sum_d dpre[t,d] U[j,d]
-    float* s_de = s_G + (size_t)Tp * GS;        // [Tp]
-    float* s_dq = s_de + Tp;                    // [4][AD] partials -> [AD]
-    float* s_red = s_dq + 4 * AD;               // [32]
-    const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    float* s_dpre = smem;                         // [Qmax][RS]   d(pre) rows of this quarter
+    float* s_U = s_dpre + (size_t)Qmax * RS;      // [32][RS], row 31 = 0
+    float* s_G = s_U + 32 * RS;                   // [Qmax][GS]: G[t][j] = sum_d dpre[t,d] U[j,d]
+    float* s_de = s_G + (size_t)Qmax * GS;        // [Tp]
+    float* s_dq = s_de + Tp;                      // [4][AD] partials of this CTA -> [AD] total
+    float* s_dqx = s_dq + 4 * AD;                 // [CS][AD] partial d(q) of every CTA of the row
+    float* s_red = s_dqx + CS * AD;               // [32]
+    const int cs = blockIdx.x, b = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int len = min(lens[b], T);
     const int lenp = (len + 3) & ~3;
-    for (int i = tid; i < V; i += FT) dctx[(long long)b * V + i] += carry[(long long)b * V + i];      // total d(ctx_t), kept for d(values)
+    const int Q = (((lenp >> 2) + CS - 1) / CS) * 4;               // positions per CTA (whole 4-position blocks), <= Qmax
+    const int t_lo = cs * Q, nq = max(0, min(lenp, t_lo + Q) - t_lo);   // this CTA's rows: t_lo .. t_lo + nq - 1
+    const int d = tid & (AD - 1), g = tid >> 7;
+    // tanh(pre) of this thread's positions (rows g, g+4, ... of the quarter) in flight first: the longest chain waits for them
+    const int nvalid = min(nq, len - t_lo);                        // rows of this quarter inside the length
+    const int ni = nvalid > g ? (nvalid - g + 3) >> 2 : 0;
+    const float* thp = th + ((long long)b * T + t_lo + g) * AD + d;
+    float x[XT];
+#pragma unroll
+    for (int i = 0; i < XT; ++i) x[i] = i < ni ? thp[(long long)i * 4 * AD] : 0.f;
+    cl.sync();                                   // every CTA of the row runs: remote stores below are safe
+    if (cs == 0)
+        for (int i = tid; i < V; i += FT) dctx[(long long)b * V + i] += carry[(long long)b * V + i];      // total d(ctx_t), kept for d(values)
     for (int i = tid; i < 32 * AD; i += FT) s_U[(i >> 7) * RS + (i & 127)] = (i >> 7) < KW ? U[i] : 0.f;
-    for (int i = tid; i < lenp * GS; i += FT) s_G[i] = 0.f;
+    for (int i = tid; i < nq * GS; i += FT) s_G[i] = 0.f;
+    float al_r[2], da_r[2];                      // T <= 1024: the row's alignments and d(align) stay in registers between the passes
     float dot = 0.f;
-    for (int t = tid; t < len; t += FT) dot = fmaf(align[(long long)b * T + t], da[(long long)b * T + t], dot);
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+        const int t = tid + k * FT;
+        al_r[k] = t < len ? align[(long long)b * T + t] : 0.f;
+        da_r[k] = t < len ? da[(long long)b * T + t] : 0.f;
+        dot = fmaf(al_r[k], da_r[k], dot);
+    }
     dot = block_reduce(dot, s_red, false);
-    for (int t = tid; t < Tp; t += FT) {
-        const float v = t < len ? align[(long long)b * T + t] * (da[(long long)b * T + t] - dot) : 0.f;
-        s_de[t] = v;
-        if (t < T) de_out[(long long)b * T + t] = v;
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+        const int t = tid + k * FT;
+        const float v = al_r[k] * (da_r[k] - dot);                 // 0 beyond the length
+        if (t < Tp) s_de[t] = v;
+        if (cs == 0 && t < T) de_out[(long long)b * T + t] = v;
     }
     __syncthreads();
-    {   // d(pre)[t,d] = d(e)[t] v_a[d] (1 - tanh^2); column sums -> d(q)
-        const int d = tid & (AD - 1), g = tid >> 7;
+    {   // d(pre)[t,d] = d(e)[t] v_a[d] (1 - tanh^2); column sums -> partial d(q)
         const float vad = va[d];
-        float cs = 0.f;
-        for (int t = g; t < lenp; t += 4) {
-            float dp = 0.f;
-            if (t < len) {
-                const float x = th[((long long)b * T + t) * AD + d];
-                dp = s_de[t] * vad * (1.f - x * x);
+        float csum = 0.f;
+#pragma unroll
+        for (int i = 0; i < XT; ++i) {
+            const int r = g + 4 * i;
+            if (r < nq) {
+                const float dp = s_de[t_lo + r] * vad * (1.f - x[i] * x[i]);     // 0 beyond the length: s_de = 0
+                s_dpre[r * RS + d] = dp;
+                csum += dp;
             }
-            s_dpre[t * RS + d] = dp;
-            cs += dp;
         }
-        s_dq[g * AD + d] = cs;
+        for (int r = g + 4 * XT; r < nq; r += 4) {                               // quarters longer than 128 positions
+            const int t = t_lo + r;
+            float dp = 0.f;
+            if (t < len) { const float xv = th[((long long)b * T + t) * AD + d]; dp = s_de[t] * vad * (1.f - xv * xv); }
+            s_dpre[r * RS + d] = dp;
+            csum += dp;
+        }
+        s_dq[g * AD + d] = csum;
     }
     __syncthreads();
     if (tid < AD) {
         const float v = s_dq[tid] + s_dq[AD + tid] + s_dq[2 * AD + tid] + s_dq[3 * AD + tid];
-        dq_out[(long long)b * AD + tid] = v;
-        s_dq[tid] = v;
+#pragma unroll
+        for (int r = 0; r < CS; ++r) cl.map_shared_rank(s_dqx, r)[cs * AD + tid] = v;
     }
-    // G tiles: 4 positions x 4 taps (taps jt, jt+8, jt+16, jt+24) x half of d per work item
-    const int ntt = lenp >> 2, nitems = ntt * 16;
+    cl.sync();                                   // partial d(q) of all 4 CTAs have arrived
+    if (tid < AD) {
+        float v = 0.f;
+#pragma unroll
+        for (int r = 0; r < CS; ++r) v += s_dqx[r * AD + tid];
+        s_dq[tid] = v;
+        if (cs == 0) dq_out[(long long)b * AD + tid] = v;
+    }
+    // d(h2raw)[k] += sum_d d(q)[d] Wq[k,d] for this CTA's quarter of the units, one warp per k (Wq is a view into the flat
+    // parameter buffer: 4-byte aligned only).  The loads are issued here; the products are finished after the G tiles.
+    const int kq = (D + CS - 1) / CS, k_end = min(D, (cs + 1) * kq), k0w = cs * kq + warp * 4;
+    float wv[4][4], dh_old = 0.f;
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int c = 0; c < 4; ++c) wv[i][c] = (k0w + i < k_end) ? Wq[(long long)(k0w + i) * AD + lane + 32 * c] : 0.f;
+    if (lane < 4 && k0w + lane < k_end) dh_old = dh2[(long long)b * D + k0w + lane];
+    // G tiles of this quarter: 4 positions x 4 taps (taps jt, jt+8, jt+16, jt+24) x half of d per work item
+    const int nitems = (nq >> 2) * 16;
     for (int it = tid; it < nitems; it += FT) {
         const int jt = it & 7, hf = (it >> 3) & 1, tt = it >> 4;
         const float* pr = s_dpre + (size_t)(tt * 4) * RS + hf * 64;
@@ -295,34 +370,51 @@ __global__ void __launch_bounds__(FT) attn_bwd_row_kernel(
 #pragma unroll
             for (int k = 0; k < 4; ++k) atomicAdd(s_G + (size_t)(tt * 4 + i) * GS + jt + 8 * k, acc[i][k]);
     }
-    __syncthreads();
-    // d(cum_{t-1})[tp] = d(cum_t)[tp] + sum_j G[tp - j + LEFT][j]   (pre[t] reads cum[t + j - LEFT])
-    for (int tp = tid; tp < T; tp += FT) {
-        float a = dcum[(long long)b * T + tp];
+    {   // finish d(h2raw) (s_dq was written before the G tiles by the first 128 threads: the barrier below orders it)
+        __syncthreads();
+        float dqr[4];
 #pragma unroll
-        for (int j = 0; j < KW; ++j) {
-            const int t = tp - j + LEFT;
-            if (t >= 0 && t < len) a += s_G[t * GS + j];
-        }
-        dcum_prev[(long long)b * T + tp] = a;
-    }
-    // d(h2raw)[k] += sum_d d(q)[d] Wq[k,d]: one warp per k (Wq is a view into the flat parameter buffer: 4-byte aligned only)
-    float dqr[4];
-#pragma unroll
-    for (int i = 0; i < 4; ++i) dqr[i] = s_dq[lane + 32 * i];
-    for (int k0 = warp * 4; k0 < D; k0 += (FT / 32) * 4) {
-        float wv[4][4];
-#pragma unroll
-        for (int i = 0; i < 4; ++i)
-#pragma unroll
-            for (int c = 0; c < 4; ++c) wv[i][c] = (k0 + i < D) ? Wq[(long long)(k0 + i) * AD + lane + 32 * c] : 0.f;
+        for (int i = 0; i < 4; ++i) dqr[i] = s_dq[lane + 32 * i];
+        float mine = 0.f;
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
             float a = wv[i][0] * dqr[0] + wv[i][1] * dqr[1] + wv[i][2] * dqr[2] + wv[i][3] * dqr[3];
             a = warp_sum(a);
-            if (lane == 0 && k0 + i < D) dh2[(long long)b * D + k0 + i] += a;
+            if (lane == i) mine = a;
+        }
+        if (lane < 4 && k0w + lane < k_end) dh2[(long long)b * D + k0w + lane] = dh_old + mine;
+        for (int k0 = k0w + (FT / 32) * 4; k0 < k_end; k0 += (FT / 32) * 4) {       // D > 256
+            for (int i = 0; i < 4 && k0 + i < k_end; ++i) {
+                float a = 0.f;
+#pragma unroll
+                for (int c = 0; c < 4; ++c) a = fmaf(Wq[(long long)(k0 + i) * AD + lane + 32 * c], dqr[c], a);
+                a = warp_sum(a);
+                if (lane == 0) dh2[(long long)b * D + k0 + i] += a;
+            }
         }
     }
+    cl.sync();                                   // all G rows of the row are complete
+    // d(cum_{t-1})[tp] = d(cum_t)[tp] + sum_j G[tp - j + LEFT][j]   (pre[t] reads cum[t + j - LEFT]); the G row of position t
+    // lives in the CTA that owns t.  CTA cs takes the tp of its quarter, the last one also everything beyond 4 Q; one warp per
+    // tp, lane = tap: one (possibly remote) shared-memory load per lane, then a warp sum.
+    {
+        const int tp_hi = (cs == CS - 1) ? T : min(T, t_lo + Q);
+        const float* Gr[CS];
+#pragma unroll
+        for (int r = 0; r < CS; ++r) Gr[r] = cl.map_shared_rank(s_G, r);
+        for (int tp = t_lo + warp; tp < tp_hi; tp += FT / 32) {
+            const int t = tp - lane + LEFT;
+            float a = 0.f;
+            if (lane < KW && t >= 0 && t < len) {
+                const int o = t / Q, r = t - o * Q;
+                const float* Go = o == 0 ? Gr[0] : o == 1 ? Gr[1] : o == 2 ? Gr[2] : Gr[3];
+                a = Go[r * GS + lane];
+            }
+            a = warp_sum(a);
+            if (lane == 0) dcum_prev[(long long)b * T + tp] = a + dcum[(long long)b * T + tp];
+        }
+    }
+    cl.sync();                                   // no CTA leaves while a neighbour may still read its G rows
 }
 
 // ------------------------------------------------------------------------------------------------ backward, hoisted
@@ -443,9 +535,10 @@ inline size_t fwd_smem(int T, int D, int V) {
     const int Tp = (T + 3) & ~3, nq = ((V >> 2) + CS - 1) / CS, ntg = FT / nq;
     return sizeof(float) * ((size_t)Tp + 32 + (size_t)Tp * 4 + AD + 4 * AD + D + 32) + sizeof(float4) * (size_t)ntg * nq;
 }
+inline int row_qmax(int T) { return ((((T + 3) >> 2) + CS - 1) / CS) * 4; }     // positions per CTA of the row kernel at len = T
 inline size_t row_smem(int T) {
-    const int Tp = (T + 3) & ~3;
-    return sizeof(float) * ((size_t)Tp * RS + 32 * RS + (size_t)Tp * GS + Tp + 4 * AD + 32);
+    const int Tp = (T + 3) & ~3, Q = row_qmax(T);
+    return sizeof(float) * ((size_t)Q * RS + 32 * RS + (size_t)Q * GS + Tp + 4 * AD + CS * AD + 32);
 }
 
 }  // namespace
@@ -453,7 +546,7 @@ inline size_t row_smem(int T) {
 extern "C" {
 
 int taco_op_attn_fused_supported(int T, int D, int A, int V, int NFf, int KWf) {
-    return A == AD && NFf == NF && KWf == KW && T >= 1 && T <= 2048 && D >= 4 && D % 4 == 0 && V % 4 == 0 &&
+    return A == AD && NFf == NF && KWf == KW && T >= 1 && T <= 1024 && D >= 4 && D % 4 == 0 && V % 4 == 0 &&
            ((V >> 2) + CS - 1) / CS <= FT && row_smem(T) <= 200 * 1024 && fwd_smem(T, D, V) <= 200 * 1024;
 }
 
@@ -484,7 +577,8 @@ int taco_op_attn_bwd_fused(float* dctx, const float* carry, const float* dcum, c
     attn_bwd_dalign_fused_kernel<<<dim3((T + 7) / 8, B), 256, sizeof(float) * V, st>>>(dctx, carry, dcum, values, lens, scratch, T, V);
     const size_t sm = row_smem(T);
     if (!ensure_smem(attn_bwd_row_kernel, sm)) return -3;
-    attn_bwd_row_kernel<<<B, FT, sm, st>>>(dctx, carry, dcum, scratch, align, th, lens, U, va, Wq, de, dq, dh2, dcum_prev, T, D, V);
+    attn_bwd_row_kernel<<<dim3(CS, B), FT, sm, st>>>(dctx, carry, dcum, scratch, align, th, lens, U, va, Wq, de, dq, dh2, dcum_prev, T, D, V,
+                                                     row_qmax(T));
     return cudaGetLastError() == cudaSuccess ? 0 : -3;
 }
 

@@ -685,9 +685,78 @@ int launch_gemm(AL A, BL Bm, float* C, long long ldc, int M, int N, int K, float
 
 }  // namespace
 
+// The per-step (M = batch <= 32 rows) contractions of the recurrences are latency-bound, not throughput-bound: a CTA of the
+// general kernel walks its K range in 32-wide stages, one global-load round trip per stage.  This kernel takes a 32 x 32 output
+// tile and a K chunk of KC, issues ALL loads of both operand chunks at once (2 x KC/4 per thread in flight), stages them in shared
+// memory with one barrier, contracts from there (2 x 4 outputs per thread) and accumulates with atomics (split-K over blockIdx.z).
+template <int KC, class AL>
+__global__ void __launch_bounds__(128) skinny_acc_kernel(AL A, BPlain Bm, float* __restrict__ C, long long ldc, float* __restrict__ C2,
+                                                         long long ldc2, int N1, int M, int N, int K) {
+    constexpr int NT = 128, PER = 32 * KC / NT;
+    __shared__ float As[KC][33];
+    __shared__ __align__(16) float Bs[KC][36];
+    const int tid = threadIdx.x, m0 = blockIdx.y * 32, n0 = blockIdx.x * 32, k0 = blockIdx.z * KC;
+    float ra[PER], rb[PER];
+#pragma unroll
+    for (int i = 0; i < PER; ++i) {              // A is k-contiguous in both uses (activations [M, K])
+        const int e = tid + i * NT, kk = e % KC, mm = e / KC;
+        ra[i] = (m0 + mm < M && k0 + kk < K) ? A(m0 + mm, k0 + kk) : 0.f;
+    }
+#pragma unroll
+    for (int i = 0; i < PER; ++i) {
+        const int e = tid + i * NT;
+        int nn, kk;
+        if (Bm.n_contig) { nn = e & 31; kk = e >> 5; } else { kk = e % KC; nn = e / KC; }
+        rb[i] = (n0 + nn < N && k0 + kk < K) ? Bm(k0 + kk, n0 + nn) : 0.f;
+    }
+#pragma unroll
+    for (int i = 0; i < PER; ++i) {
+        const int e = tid + i * NT;
+        As[e % KC][e / KC] = ra[i];
+        if (Bm.n_contig) Bs[e >> 5][e & 31] = rb[i]; else Bs[e % KC][e / KC] = rb[i];
+    }
+    __syncthreads();
+    const int ty = tid >> 3, tx = tid & 7;       // rows 2 ty, 2 ty + 1; columns 4 tx .. 4 tx + 3
+    float acc[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
+#pragma unroll 16
+    for (int k = 0; k < KC; ++k) {
+        const float a0 = As[k][2 * ty], a1 = As[k][2 * ty + 1];
+        const float4 b = *reinterpret_cast<const float4*>(&Bs[k][4 * tx]);
+        acc[0][0] = fmaf(a0, b.x, acc[0][0]); acc[0][1] = fmaf(a0, b.y, acc[0][1]); acc[0][2] = fmaf(a0, b.z, acc[0][2]); acc[0][3] = fmaf(a0, b.w, acc[0][3]);
+        acc[1][0] = fmaf(a1, b.x, acc[1][0]); acc[1][1] = fmaf(a1, b.y, acc[1][1]); acc[1][2] = fmaf(a1, b.z, acc[1][2]); acc[1][3] = fmaf(a1, b.w, acc[1][3]);
+    }
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+        const int m = m0 + 2 * ty + i;
+        if (m >= M) continue;
+        const int nb = n0 + 4 * tx;
+        float* c4 = (C2 && nb >= N1) ? C2 + (long long)m * ldc2 + (nb - N1) : C + (long long)m * ldc + nb;
+        if (nb + 3 < N && (!C2 || nb + 3 < N1 || nb >= N1) && (reinterpret_cast<uintptr_t>(c4) & 15) == 0) {
+            atomicAdd(reinterpret_cast<float4*>(c4), make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]));   // one 16-byte reduction
+            continue;
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int n = nb + j;
+            if (n >= N) continue;
+            atomicAdd((C2 && n >= N1) ? C2 + (long long)m * ldc2 + (n - N1) : C + (long long)m * ldc + n, acc[i][j]);
+        }
+    }
+}
+
 // skinny (M = batch) contraction with a two-block A and/or a two-block C, always accumulating (beta = 1), split-K
 template <class AL>
 int launch_skinny_acc(AL A, BPlain Bm, float* C, long long ldc, float* C2, long long ldc2, int N1, int M, int N, int K, cudaStream_t st) {
+    static const bool one_shot = !getenv("TACO_TRAIN_SKINNY_OLD");
+    if (one_shot && K >= 128) {
+        const int tiles = ((N + 31) / 32) * ((M + 31) / 32);
+        if (tiles * ((K + 127) / 128) >= 200) {
+            skinny_acc_kernel<128, AL><<<dim3((N + 31) / 32, (M + 31) / 32, (K + 127) / 128), 128, 0, st>>>(A, Bm, C, ldc, C2, ldc2, N1, M, N, K);
+        } else {
+            skinny_acc_kernel<64, AL><<<dim3((N + 31) / 32, (M + 31) / 32, (K + 63) / 64), 128, 0, st>>>(A, Bm, C, ldc, C2, ldc2, N1, M, N, K);
+        }
+        return cudaGetLastError() == cudaSuccess ? 0 : -3;
+    }
     dim3 grid((N + 31) / 32, (M + 31) / 32, 1);
     int kchunk = K;
     const int ctas = grid.x * grid.y;
