@@ -3,6 +3,7 @@
 // Small tensors (< 2 GFLOP per step in total): direct kernels, one thread per output element.
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
 
 #include "../../include/taco_b200_train.h"
 #include "common.cuh"
@@ -104,6 +105,76 @@ __global__ void conv2d_wgrad_kernel(const float* __restrict__ x, const float* __
     }
 }
 
+// ---- im2col / col2im: the three conv2d contractions as plain GEMMs on taco_op_gemm (bf16 tensor cores in the bf16 mode) ----
+// col[m = (b,ho,wo)][k = (kh*3+kw)*Ci + ci] = x[b, 2 ho + kh - pt, 2 wo + kw - pl, ci]   (0 outside the image)
+template <int VEC>
+__global__ void im2col_s2_kernel(const float* __restrict__ x, float* __restrict__ col, int H, int W, int Ci, int Ho, int Wo, int pt,
+                                 int pl, long long n /* M * 9 * Ci / VEC */) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int cv = Ci / VEC;
+    const int c = (int)(i % cv);
+    long long r = i / cv;
+    const int tap = (int)(r % 9); r /= 9;
+    const int wo = (int)(r % Wo); r /= Wo;
+    const int ho = (int)(r % Ho);
+    const int b = (int)(r / Ho);
+    const int h = 2 * ho + tap / 3 - pt, w = 2 * wo + tap % 3 - pl;
+    const bool ok = h >= 0 && h < H && w >= 0 && w < W;
+    const float* src = x + (((long long)b * H + h) * W + w) * Ci + c * VEC;
+    if (VEC == 4) reinterpret_cast<float4*>(col)[i] = ok ? *reinterpret_cast<const float4*>(src) : make_float4(0.f, 0.f, 0.f, 0.f);
+    else col[i] = ok ? *src : 0.f;
+}
+// dx[b,h,w,ci] = sum over the taps that reach (h,w): dcol[(b,ho,wo)][(kh*3+kw)*Ci + ci]
+template <int VEC>
+__global__ void col2im_s2_kernel(const float* __restrict__ dcol, float* __restrict__ dx, int H, int W, int Ci, int Ho, int Wo, int pt,
+                                 int pl, long long n /* B*H*W*Ci / VEC */) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int cv = Ci / VEC;
+    const int c = (int)(i % cv);
+    long long r = i / cv;
+    const int w = (int)(r % W); r /= W;
+    const int h = (int)(r % H);
+    const int b = (int)(r / H);
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int kh = 0; kh < 3; ++kh) {
+        const int hh = h + pt - kh;
+        if (hh < 0 || (hh & 1) || (hh >> 1) >= Ho) continue;
+#pragma unroll
+        for (int kw = 0; kw < 3; ++kw) {
+            const int ww = w + pl - kw;
+            if (ww < 0 || (ww & 1) || (ww >> 1) >= Wo) continue;
+            const float* src = dcol + ((((long long)b * Ho + (hh >> 1)) * Wo + (ww >> 1)) * 9 + kh * 3 + kw) * Ci + c * VEC;
+            if (VEC == 4) { const float4 v = *reinterpret_cast<const float4*>(src); acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w; }
+            else acc.x += *src;
+        }
+    }
+    if (VEC == 4) reinterpret_cast<float4*>(dx)[i] = acc; else dx[i] = acc.x;
+}
+
+struct Scratch { float* p = nullptr; size_t n = 0; };
+Scratch g_col;     // process-wide, grow-only (cudaMalloc: 16-byte aligned)
+float* col_scratch(size_t n) {
+    if (g_col.n < n) {
+        if (g_col.p) { cudaDeviceSynchronize(); cudaFree(g_col.p); }
+        g_col.p = nullptr; g_col.n = 0;
+        if (cudaMalloc(&g_col.p, n * sizeof(float)) != cudaSuccess) return nullptr;
+        g_col.n = n;
+    }
+    return g_col.p;
+}
+const bool g_conv2d_gemm = !getenv("TACO_TRAIN_CONV2D_DIRECT");
+
+int im2col(const float* x, float* col, int B, int H, int W, int Ci, int Ho, int Wo, cudaStream_t st) {
+    const bool v4 = Ci % 4 == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0;
+    const long long n = (long long)B * Ho * Wo * 9 * Ci / (v4 ? 4 : 1);
+    if (v4) im2col_s2_kernel<4><<<(unsigned)((n + 255) / 256), 256, 0, st>>>(x, col, H, W, Ci, Ho, Wo, pad_before(H), pad_before(W), n);
+    else im2col_s2_kernel<1><<<(unsigned)((n + 255) / 256), 256, 0, st>>>(x, col, H, W, Ci, Ho, Wo, pad_before(H), pad_before(W), n);
+    return cudaGetLastError() == cudaSuccess ? 0 : -3;
+}
+
 // ------------------------------------------------------------------------------------------------ GST attention
 // block per batch row, one warp per head (head width U/nh == 32 lanes); N <= 32 tokens
 __global__ void gst_fwd_kernel(const float* __restrict__ q, const float* __restrict__ k, const float* __restrict__ v,
@@ -187,6 +258,13 @@ int taco_op_conv2d_fwd(const float* x, const float* w, const float* bias, float*
     if (!x || !w || !y || B < 1 || H < 1 || W < 1) return -1;
     const int Ho = (H + 1) / 2, Wo = (W + 1) / 2;
     long long n = (long long)B * Ho * Wo * Co;
+    if (g_conv2d_gemm && Ci >= 8 && n / Co < (1LL << 31) / (9 * Ci)) {       // y = im2col(x) . w + bias
+        const int M = B * Ho * Wo, K = 9 * Ci;
+        float* col = col_scratch((size_t)M * K);
+        if (!col) return -3;
+        int rc = im2col(x, col, B, H, W, Ci, Ho, Wo, ST);
+        return rc ? rc : taco_op_gemm(col, K, w, Co, y, Co, M, Co, K, 0, 0, 0.f, bias, stream);
+    }
     conv2d_fwd_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ST>>>(x, w, bias, y, B, H, W, Ci, Co, Ho, Wo, pad_before(H), pad_before(W));
     return rcm();
 }
@@ -194,6 +272,18 @@ int taco_op_conv2d_dgrad(const float* dy, const float* w, float* dx, int B, int 
     if (!dy || !w || !dx) return -1;
     const int Ho = (H + 1) / 2, Wo = (W + 1) / 2;
     long long n = (long long)B * H * W * Ci;
+    if (g_conv2d_gemm && Ci >= 8 && (long long)B * Ho * Wo < (1LL << 31) / (9 * Ci)) {   // d(col) = dy . w^T, then col2im
+        const int M = B * Ho * Wo, K = 9 * Ci;
+        float* col = col_scratch((size_t)M * K);
+        if (!col) return -3;
+        int rc = taco_op_gemm(dy, Co, w, Co, col, K, M, K, Co, 0, 1, 0.f, nullptr, stream);
+        if (rc) return rc;
+        const bool v4 = Ci % 4 == 0 && (reinterpret_cast<uintptr_t>(dx) & 15) == 0;
+        const long long nv = n / (v4 ? 4 : 1);
+        if (v4) col2im_s2_kernel<4><<<(unsigned)((nv + 255) / 256), 256, 0, ST>>>(col, dx, H, W, Ci, Ho, Wo, pad_before(H), pad_before(W), nv);
+        else col2im_s2_kernel<1><<<(unsigned)((nv + 255) / 256), 256, 0, ST>>>(col, dx, H, W, Ci, Ho, Wo, pad_before(H), pad_before(W), nv);
+        return rcm();
+    }
     conv2d_dgrad_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ST>>>(dy, w, dx, B, H, W, Ci, Co, Ho, Wo, pad_before(H), pad_before(W));
     return rcm();
 }
@@ -201,6 +291,13 @@ int taco_op_conv2d_wgrad(const float* x, const float* dy, float* dw, int B, int 
     if (!x || !dy || !dw) return -1;
     if (Co < 1 || Co > 256 || 256 % Co != 0) return -1;
     const int Ho = (H + 1) / 2, Wo = (W + 1) / 2;
+    if (g_conv2d_gemm && Ci >= 8 && (long long)B * Ho * Wo < (1LL << 31) / (9 * Ci)) {   // d(w) = im2col(x)^T . dy
+        const int M = B * Ho * Wo, K = 9 * Ci;
+        float* col = col_scratch((size_t)M * K);
+        if (!col) return -3;
+        int rc = im2col(x, col, B, H, W, Ci, Ho, Wo, ST);
+        return rc ? rc : taco_op_gemm(col, K, dy, Co, dw, Co, K, Co, M, 1, 0, 0.f, nullptr, stream);
+    }
     {   // Ci >= 8: split-K implicit GEMM of train_gemm.cu (fp32); the first layer (Ci = 1) keeps the row-per-CTA kernel below
         const int rc = taco_train_conv2d_wgrad_gemm(x, dy, dw, B, H, W, Ci, Co, Ho, Wo, pad_before(H), pad_before(W), ST);
         if (rc <= 0) return rc;

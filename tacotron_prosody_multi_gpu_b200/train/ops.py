@@ -82,6 +82,26 @@ def _c(t):
     return t.data_ptr()
 
 
+class _Side(object):
+    def __init__(self, ops, i):
+        self.ops, self.i = ops, i
+
+    def __enter__(self):
+        o = self.ops
+        if self.i not in o._sides:
+            o._sides[self.i] = torch.cuda.Stream(device=o.device)
+        s = o._sides[self.i]
+        s.wait_stream(torch.cuda.current_stream(o.device))
+        self.cm = torch.cuda.stream(s)
+        self.cm.__enter__()
+        if s not in o._pending:
+            o._pending.append(s)
+        return s
+
+    def __exit__(self, *exc):
+        return self.cm.__exit__(*exc)
+
+
 class CudaOps(object):
     def __init__(self, device=0):
         if not torch.cuda.is_available():
@@ -93,6 +113,7 @@ class CudaOps(object):
             fn.argtypes = sig
             fn.restype = C.c_int
         self.launches = 0
+        self._sides, self._pending = {}, []
 
     # ------------------------------------------------------------------ plumbing
     def empty(self, *shape, dtype=torch.float32):
@@ -115,6 +136,19 @@ class CudaOps(object):
         self.launches += 1
         if rc != 0:
             raise _lib.TacoError("%s failed with code %d (%s)" % (name, rc, "bad argument" if rc == -1 else "CUDA error"))
+
+    # ------------------------------------------------------------------ independent branches of the step on side streams
+    def side(self, i):
+        """Context manager: the enclosed launches go to side stream ``i``, ordered after everything already queued on the
+        current stream.  The text encoder's two LSTM directions and the reference encoder are independent chains of small,
+        latency-bound launches; ``join()`` makes the current stream wait for all of them."""
+        return _Side(self, i)
+
+    def join(self):
+        cur = torch.cuda.current_stream(self.device)
+        for s in self._pending:
+            cur.wait_stream(s)
+        self._pending = []
 
     # ------------------------------------------------------------------ contractions
     def gemm(self, A, B, Cm, ta=False, tb=False, beta=0.0, bias=None):

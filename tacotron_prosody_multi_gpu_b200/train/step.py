@@ -19,6 +19,8 @@ them) -- the injected stand-in for TF's stateful RNG.
 """
 from __future__ import annotations
 
+import contextlib
+
 import numpy as np
 
 from .. import weights as W
@@ -122,6 +124,14 @@ class TrainStep(object):
                 o.conv1d_dgrad(dz, w, dx)
         return dx
 
+    def _side(self, i):
+        """Launches of an independent branch of the step go to side stream i (CudaOps.side); a no-op for the CPU twin."""
+        return self.ops.side(i) if hasattr(self.ops, "side") else contextlib.nullcontext()
+
+    def _join(self):
+        if hasattr(self.ops, "join"):
+            self.ops.join()
+
     def _dense_bwd(self, x2, dy2, kernel_name, bias_name, dx2=None, beta=0.0):
         """dW = x^T dy, db = colsum(dy), optionally dx (+)= dy W^T."""
         o, P, G = self.ops, self.store.P, self.store.G
@@ -183,19 +193,22 @@ class TrainStep(object):
             pre = o.empty(B, 4 * H)
             sc, sh = STREAM_ENC_LSTM + 2 * d, STREAM_ENC_LSTM + 2 * d + 1
             fast = hasattr(o, "lstm_loop")         # the same loop sequenced in C (train_loops.cu)
-            if fast:
-                o.lstm_loop(False, dict(B=B, T=T, H=H, C=C, reverse=int(rev)), zo, seed, sc, sh, enc_out[:, :, d * H:(d + 1) * H],
-                            K=K, lens=lens, xw=xw, acts=acts, cnew=cnew, cz=cz, hz=hz, work=o.empty(B * 9 * H))
-            for s in range(0 if not fast else T, T):
-                o.gather_rows(xw, lens, s, rev, pre)
-                o.gemm(hz[s], K[C:], acts[s])
-                o.lstm_fwd(acts[s], pre, None, cz[s], hz[s], lens, s, zo, True, seed, sc, sh, s * B,
-                           cnew[s], cz[s + 1], hraw[s], hz[s + 1])
-                o.scatter_rows(hraw[s], lens, s, rev, enc_out[:, :, d * H:(d + 1) * H])
+            with self._side(d):                    # the two directions are independent chains: one side stream each
+                if fast:
+                    o.lstm_loop(False, dict(B=B, T=T, H=H, C=C, reverse=int(rev)), zo, seed, sc, sh, enc_out[:, :, d * H:(d + 1) * H],
+                                K=K, lens=lens, xw=xw, acts=acts, cnew=cnew, cz=cz, hz=hz, work=o.empty(B * 9 * H))
+                for s in range(0 if not fast else T, T):
+                    o.gather_rows(xw, lens, s, rev, pre)
+                    o.gemm(hz[s], K[C:], acts[s])
+                    o.lstm_fwd(acts[s], pre, None, cz[s], hz[s], lens, s, zo, True, seed, sc, sh, s * B,
+                               cnew[s], cz[s + 1], hraw[s], hz[s + 1])
+                    o.scatter_rows(hraw[s], lens, s, rev, enc_out[:, :, d * H:(d + 1) * H])
             t["bilstm"].append(dict(scope=scope, rev=rev, acts=acts, cnew=cnew, cz=cz, hz=hz, sc=sc, sh=sh))
         t["x3"] = x3
 
         # ---- reference encoder on the mel targets (Tacotron.py:12-29,191-193) -> GST attention (Attention.py:243-341)
+        ref_side = self._side(2)                   # independent of the text encoder: its own side stream
+        ref_side.__enter__()
         t["ref_conv"] = []
         xr = mel_targets.view(B, F, M, 1)
         for i in range(len(hp.reference_filters)):
@@ -229,6 +242,8 @@ class TrainStep(object):
         wts, style = o.empty(B, nh, tok.shape[0]), o.empty(B, nh * tok.shape[1])
         o.gst_fwd(gq, gk, P[W.MHA + "/attention_v"], P[W.MHA + "/attention_g"], P[W.MHA + "/attention_b"], tt, nh, wts, style)
         t.update(tt=tt, gq=gq, gk=gk, wts=wts)
+        ref_side.__exit__(None, None, None)
+        self._join()                               # both LSTM directions and the style embedding are ready
         SD = style.shape[1]
         MD = 2 * H + SD
         memory = o.empty(B, T, MD)
@@ -470,6 +485,8 @@ class TrainStep(object):
         nh = hp.num_heads
         tt, ref, Tp, In = t["tt"], t["ref"], t["Tp"], t["In"]
         R = hp.reference_depth
+        ref_side = self._side(2)                   # reference-encoder gradient chain beside the BiLSTM BPTT
+        ref_side.__enter__()
         dstyle = o.empty(B, MD - 2 * H)
         o.sum_style(dmemory, 2 * H, dstyle)
         dq, dk, dtt = o.empty(*t["gq"].shape), o.empty(*t["gk"].shape), o.empty(*tt.shape)
@@ -512,35 +529,41 @@ class TrainStep(object):
         dy.view(B, Tp, In).copy_(dXt.transpose(0, 1))
         for i in range(len(t["ref_conv"]) - 1, -1, -1):
             dy = self._conv_block_bwd(dy, t["ref_conv"][i], seed, need_dx=i > 0)
+        ref_side.__exit__(None, None, None)
 
         # ---- encoder BiLSTM BPTT over the valid lengths
         lens = t["lens"]
         x3 = t["x3"]
         C = x3.shape[1]
         dx3 = o.empty(B * T, C)
-        d_hraw = o.empty(B, H)
+        dxws = []
         for d, rec in enumerate(t["bilstm"]):
             K = P[rec["scope"] + "/kernel"]
             GK = G[rec["scope"] + "/kernel"]
-            dxw = o.zeros(B, T, 4 * H)
-            dg = o.empty(T, B, 4 * H)
-            dc, dhz, dcn, dhn = o.zeros(B, H), o.zeros(B, H), o.empty(B, H), o.empty(B, H)
             src = dmemory[:, :, d * H:(d + 1) * H]
-            fast = hasattr(o, "lstm_loop")
-            if fast:
-                o.lstm_loop(True, dict(B=B, T=T, H=H, C=C, reverse=int(rec["rev"])), zo, seed, rec["sc"], rec["sh"], src, K=K, lens=lens,
-                            acts=rec["acts"], cnew=rec["cnew"], cz=rec["cz"], hz=rec["hz"], dxw=dxw, dg=dg, work=o.empty(B * 9 * H))
-            for s in range(T - 1 if not fast else -1, -1, -1):
-                o.gather_rows(src, lens, s, rec["rev"], d_hraw)
-                o.lstm_bwd(rec["acts"][s], rec["cz"][s], rec["hz"][s], rec["cnew"][s], lens, s, zo, True, seed, rec["sc"], rec["sh"],
-                           s * B, d_hraw, dc, dhz, dg[s], dcn, dhn)
-                o.gemm(dg[s], K[C:], dhn, tb=True, beta=1.0)
-                o.scatter_rows(dg[s], lens, s, rec["rev"], dxw)
-                dc, dcn, dhz, dhn = dcn, dc, dhn, dhz
-            o.gemm(rec["hz"][:T].view(T * B, H), dg.view(T * B, 4 * H), GK[C:], ta=True)
-            dxw2 = dxw.view(B * T, 4 * H)
-            o.gemm(x3, dxw2, GK[:C], ta=True)
-            o.colsum(dxw2, G[rec["scope"] + "/bias"])
+            with self._side(d):                    # the two directions are independent chains: one side stream each
+                dxw = o.zeros(B, T, 4 * H)
+                dg = o.empty(T, B, 4 * H)
+                dc, dhz, dcn, dhn = o.zeros(B, H), o.zeros(B, H), o.empty(B, H), o.empty(B, H)
+                d_hraw = o.empty(B, H)
+                fast = hasattr(o, "lstm_loop")
+                if fast:
+                    o.lstm_loop(True, dict(B=B, T=T, H=H, C=C, reverse=int(rec["rev"])), zo, seed, rec["sc"], rec["sh"], src, K=K, lens=lens,
+                                acts=rec["acts"], cnew=rec["cnew"], cz=rec["cz"], hz=rec["hz"], dxw=dxw, dg=dg, work=o.empty(B * 9 * H))
+                for s in range(T - 1 if not fast else -1, -1, -1):
+                    o.gather_rows(src, lens, s, rec["rev"], d_hraw)
+                    o.lstm_bwd(rec["acts"][s], rec["cz"][s], rec["hz"][s], rec["cnew"][s], lens, s, zo, True, seed, rec["sc"], rec["sh"],
+                               s * B, d_hraw, dc, dhz, dg[s], dcn, dhn)
+                    o.gemm(dg[s], K[C:], dhn, tb=True, beta=1.0)
+                    o.scatter_rows(dg[s], lens, s, rec["rev"], dxw)
+                    dc, dcn, dhz, dhn = dcn, dc, dhn, dhz
+                o.gemm(rec["hz"][:T].view(T * B, H), dg.view(T * B, 4 * H), GK[C:], ta=True)
+                dxw2 = dxw.view(B * T, 4 * H)
+                o.gemm(x3, dxw2, GK[:C], ta=True)
+                o.colsum(dxw2, G[rec["scope"] + "/bias"])
+            dxws.append((dxw2, K))
+        self._join()                               # both directions and the reference-encoder chain
+        for d, (dxw2, K) in enumerate(dxws):
             o.gemm(dxw2, K[:C], dx3, tb=True, beta=0.0 if d == 0 else 1.0)
 
         # ---- encoder convolutions + embedding
