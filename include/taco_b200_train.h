@@ -99,7 +99,7 @@ int taco_op_attn_bwd(const float* dctx, const float* dcum, const float* q, const
 /* The same attention step for the time loops, fused (csrc/train_attn_fused.cu): the location convolution and the location dense
  * layer folded into one filter bank U [KW,A] (+ c0 [A]) once per training step; forward = ONE launch per decoder step (query
  * projection q = h2raw . Wq, energies, masked softmax, cumulative update, context) that also saves tanh(pre) [B,T,A]; backward
- * = TWO launches per step that produce only what the recurrence needs (d(q) and d(h2raw) += d(q) Wq^T, d(cum_{t-1}), the total
+ * = ONE launch per step that produces only what the recurrence needs (d(q) and d(h2raw) += d(q) Wq^T, d(cum_{t-1}), the total
  * d(ctx_t) = dctx + carry written back to dctx, and the saved d(energy) [B,T]); d(keys) and the weight gradients of all S steps
  * come from ONE pass after the loop (taco_op_attn_bwd_hoisted; results are ADDED to g_* and dkeys; work >= B*(KW+2)*A floats).
  * taco_op_attn_fused_supported: 1 when these kernels hold the shape (A = 128, NF = 32, KW = 31, T <= 256-ish), else 0. */

@@ -1,5 +1,5 @@
 // train_attn_fused.cu -- the LocationSensitiveAttention step of the training recurrence (Attention.py:169-210,345-401) as
-// ONE launch forward and TWO launches backward per decoder step, with everything that does not feed the recurrence hoisted
+// ONE launch forward and ONE launch backward per decoder step, with everything that does not feed the recurrence hoisted
 // out of the BPTT loop (train_attn.cu keeps the op-by-op kernels: they remain the path for kernel sizes != 31 / T > 256).
 //
 //   fold     U[j,d] = sum_f conv_w[j,f] Wl[f,d], c0[d] = sum_f conv_b[f] Wl[f,d]: the location convolution and the location
@@ -8,8 +8,9 @@
 //            window of the cumulative alignments per thread in registers) of this CTA's quarter of the positions, stored as
 //            tanh(pre) [T,128] for the backward pass; the partial energies go to all 4 CTAs through distributed shared
 //            memory; then every CTA does the masked softmax + cumulative update and its 192 columns of the context
-//   backward d(align) grid (T/8, B): values . (d(ctx) + carry) + d(cum)
-//            row kernel grid (4, B), clusters of the 4 CTAs of a row: softmax gradient, d(pre) and the tap gradients of a
+//   backward ONE launch, grid (4, B), clusters of the 4 CTAs of a row: d(align) = values . (d(ctx) + carry) + d(cum) of a
+//            quarter of the positions (partial sums of the softmax gradient exchanged through distributed shared memory),
+//            d(pre) and the tap gradients of that
 //            quarter of the positions (4x4 register tiles over the shared-memory d(pre) tile), d(q) -> d(h2raw) += d(q) Wq^T,
 //            d(cum_{t-1}) through the folded filter bank (halo rows read from the neighbours' shared memory); saves
 //            d(energy) [T] per step
@@ -200,52 +201,12 @@ __global__ void __cluster_dims__(CS, 1, 1) __launch_bounds__(FT, 1) attn_fwd_fus
 }
 
 // ------------------------------------------------------------------------------------------------ backward, in the loop
-// d(align)[t] = values[t,:] . (d(ctx) + carry) + d(cum_t)[t]; one warp per position
-__global__ void __launch_bounds__(256) attn_bwd_dalign_fused_kernel(const float* __restrict__ dctx, const float* __restrict__ carry,
-                                                                    const float* __restrict__ dcum, const float* __restrict__ values,
-                                                                    const int32_t* __restrict__ lens, float* __restrict__ da, int T, int V) {
-    extern __shared__ __align__(16) float s_dctx[];
-    const int b = blockIdx.y, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int t = blockIdx.x * 8 + warp;
-    const int len = min(lens[b], T);
-    if (blockIdx.x * 8 >= len) {
-        if (t < T && lane == 0) da[(long long)b * T + t] = 0.f;
-        return;
-    }
-    float4 v[6];                                   // the first 768 columns of the value row in flight before the smem fill
-    const float4* vp = reinterpret_cast<const float4*>(values + ((long long)b * T + min(t, len - 1)) * V);
-    const int V4 = V >> 2;
-#pragma unroll
-    for (int k = 0; k < 6; ++k) v[k] = (lane + 32 * k < V4) ? vp[lane + 32 * k] : make_float4(0.f, 0.f, 0.f, 0.f);
-    for (int i = threadIdx.x; i < V; i += blockDim.x) s_dctx[i] = dctx[(long long)b * V + i] + carry[(long long)b * V + i];
-    __syncthreads();
-    if (t >= T) return;
-    float acc = 0.f;
-    if (t < len) {
-#pragma unroll
-        for (int k = 0; k < 6; ++k) {
-            const int c = (lane + 32 * k) * 4;
-            if (c < V) {
-                acc = fmaf(v[k].x, s_dctx[c], acc); acc = fmaf(v[k].y, s_dctx[c + 1], acc);
-                acc = fmaf(v[k].z, s_dctx[c + 2], acc); acc = fmaf(v[k].w, s_dctx[c + 3], acc);
-            }
-        }
-        for (int c4 = lane + 192; c4 < V4; c4 += 32) {
-            const float4 x = vp[c4];
-            acc = fmaf(x.x, s_dctx[4 * c4], acc); acc = fmaf(x.y, s_dctx[4 * c4 + 1], acc);
-            acc = fmaf(x.z, s_dctx[4 * c4 + 2], acc); acc = fmaf(x.w, s_dctx[4 * c4 + 3], acc);
-        }
-        acc = warp_sum(acc) + dcum[(long long)b * T + t];
-    }
-    if (lane == 0) da[(long long)b * T + t] = t < len ? acc : 0.f;
-}
-
 // everything of the attention gradient that feeds the recurrence: the 4 CTAs of a row (one cluster) split its positions into
 // contiguous quarters (d(pre) rows, tap gradients G) and the units of d(h2raw); d(q) partial sums and the G rows of the
 // neighbouring quarters (the 31-tap halo of d(cum_{t-1})) cross the cluster through distributed shared memory
 constexpr int XT = 32;    // tanh(pre) values a thread of the row kernel keeps in flight (positions g, g+4, ... of its quarter)
 __global__ void __cluster_dims__(CS, 1, 1) __launch_bounds__(FT, 1) attn_bwd_row_kernel(
-    float* __restrict__ dctx, const float* __restrict__ carry, const float* __restrict__ dcum, const float* __restrict__ da,
+    float* __restrict__ dctx, const float* __restrict__ carry, const float* __restrict__ dcum, const float* __restrict__ values,
     const float* __restrict__ align, const float* __restrict__ th, const int32_t* __restrict__ lens, const float* __restrict__ U,
     const float* __restrict__ va, const float* __restrict__ Wq, float* __restrict__ de_out, float* __restrict__ dq_out,
     float* __restrict__ dh2, float* __restrict__ dcum_prev, int T, int D, int V, int Qmax) {
@@ -259,6 +220,8 @@ __global__ void __cluster_dims__(CS, 1, 1) __launch_bounds__(FT, 1) attn_bwd_row
     float* s_dq = s_de + Tp;                      // [4][AD] partials of this CTA -> [AD] total
     float* s_dqx = s_dq + 4 * AD;                 // [CS][AD] partial d(q) of every CTA of the row
     float* s_red = s_dqx + CS * AD;               // [32]
+    float* s_dot = s_red + 32;                    // [CS] partial sums of a . d(align)
+    float* s_dctx = s_dot + CS;                   // [V] d(ctx) + carry
     const int cs = blockIdx.x, b = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int len = min(lens[b], T);
     const int lenp = (len + 3) & ~3;
@@ -272,28 +235,56 @@ __global__ void __cluster_dims__(CS, 1, 1) __launch_bounds__(FT, 1) attn_bwd_row
     float x[XT];
 #pragma unroll
     for (int i = 0; i < XT; ++i) x[i] = i < ni ? thp[(long long)i * 4 * AD] : 0.f;
-    cl.sync();                                   // every CTA of the row runs: remote stores below are safe
-    if (cs == 0)
-        for (int i = tid; i < V; i += FT) dctx[(long long)b * V + i] += carry[(long long)b * V + i];      // total d(ctx_t), kept for d(values)
+    // d(align) of this quarter's rows needs the value rows: the first row of every warp is in flight as well
+    const int V4 = V >> 2;
+    const float4* val4 = reinterpret_cast<const float4*>(values) + (long long)b * T * V4;
+    float4 v0[6];
+#pragma unroll
+    for (int k = 0; k < 6; ++k)
+        v0[k] = (warp < nvalid && lane + 32 * k < V4) ? val4[(long long)(t_lo + warp) * V4 + lane + 32 * k] : make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int i = tid; i < V; i += FT) s_dctx[i] = dctx[(long long)b * V + i] + carry[(long long)b * V + i];
     for (int i = tid; i < 32 * AD; i += FT) s_U[(i >> 7) * RS + (i & 127)] = (i >> 7) < KW ? U[i] : 0.f;
-    for (int i = tid; i < nq * GS; i += FT) s_G[i] = 0.f;
-    float al_r[2], da_r[2];                      // T <= 1024: the row's alignments and d(align) stay in registers between the passes
-    float dot = 0.f;
+    cl.sync();                                   // every CTA of the row runs (remote stores below are safe) and has read d(ctx)
+    if (cs == 0)
+        for (int i = tid; i < V; i += FT) dctx[(long long)b * V + i] = s_dctx[i];      // total d(ctx_t), kept for d(values)
+    // d(align)[t] = values[t,:] . d(ctx) + d(cum_t)[t], one warp per row; partial sum_t a[t] d(align)[t] of this quarter
+    float part = 0.f;
+    for (int r = warp; r < nq; r += FT / 32) {
+        const int t = t_lo + r;
+        float acc = 0.f;
+        if (r < nvalid) {
+            const float4* vp = val4 + (long long)t * V4;
 #pragma unroll
-    for (int k = 0; k < 2; ++k) {
-        const int t = tid + k * FT;
-        al_r[k] = t < len ? align[(long long)b * T + t] : 0.f;
-        da_r[k] = t < len ? da[(long long)b * T + t] : 0.f;
-        dot = fmaf(al_r[k], da_r[k], dot);
+            for (int k = 0; k < 6; ++k) {
+                const int c4 = lane + 32 * k;
+                if (c4 < V4) {
+                    const float4 v = (r == warp) ? v0[k] : vp[c4];
+                    const float4 g4 = *reinterpret_cast<const float4*>(s_dctx + 4 * c4);
+                    acc = fmaf(v.x, g4.x, acc); acc = fmaf(v.y, g4.y, acc); acc = fmaf(v.z, g4.z, acc); acc = fmaf(v.w, g4.w, acc);
+                }
+            }
+            for (int c4 = lane + 192; c4 < V4; c4 += 32) {
+                const float4 v = vp[c4];
+                const float4 g4 = *reinterpret_cast<const float4*>(s_dctx + 4 * c4);
+                acc = fmaf(v.x, g4.x, acc); acc = fmaf(v.y, g4.y, acc); acc = fmaf(v.z, g4.z, acc); acc = fmaf(v.w, g4.w, acc);
+            }
+            acc = warp_sum(acc) + dcum[(long long)b * T + t];
+            part = fmaf(align[(long long)b * T + t], acc, part);
+        }
+        if (lane == 0) s_de[t] = acc;            // d(align) for now; 0 on the padding rows
     }
-    dot = block_reduce(dot, s_red, false);
-#pragma unroll
-    for (int k = 0; k < 2; ++k) {
-        const int t = tid + k * FT;
-        const float v = al_r[k] * (da_r[k] - dot);                 // 0 beyond the length
-        if (t < Tp) s_de[t] = v;
-        if (cs == 0 && t < T) de_out[(long long)b * T + t] = v;
+    part = block_reduce(lane == 0 ? part : 0.f, s_red, false);
+    if (tid < CS) cl.map_shared_rank(s_dot, tid)[cs] = part;
+    cl.sync();                                   // the 4 partial sums are everywhere
+    const float dot = s_dot[0] + s_dot[1] + s_dot[2] + s_dot[3];
+    for (int r = tid; r < nq; r += FT) {         // d(energy) = a (d(align) - sum a d(align)); 0 beyond the length
+        const int t = t_lo + r;
+        const float v = r < nvalid ? align[(long long)b * T + t] * (s_de[t] - dot) : 0.f;
+        s_de[t] = v;
+        if (t < T) de_out[(long long)b * T + t] = v;
     }
+    if (cs == CS - 1)
+        for (int t = CS * Q + tid; t < T; t += FT) de_out[(long long)b * T + t] = 0.f;
     __syncthreads();
     {   // d(pre)[t,d] = d(e)[t] v_a[d] (1 - tanh^2); column sums -> partial d(q)
         const float vad = va[d];
@@ -339,24 +330,25 @@ __global__ void __cluster_dims__(CS, 1, 1) __launch_bounds__(FT, 1) attn_bwd_row
 #pragma unroll
         for (int c = 0; c < 4; ++c) wv[i][c] = (k0w + i < k_end) ? Wq[(long long)(k0w + i) * AD + lane + 32 * c] : 0.f;
     if (lane < 4 && k0w + lane < k_end) dh_old = dh2[(long long)b * D + k0w + lane];
-    // G tiles of this quarter: 4 positions x 4 taps (taps jt, jt+8, jt+16, jt+24) x half of d per work item
-    const int nitems = (nq >> 2) * 16;
+    // G tiles of this quarter: 4 positions x 4 taps (taps jt, jt+8, jt+16, jt+24) x one eighth of d per work item; the 8
+    // d-parts of a tile sit in 8 adjacent lanes (interleaved 16-byte columns: conflict-free loads) and combine by shuffles
+    const int nitems = (nq >> 2) * 64;           // a multiple of 64: whole warps in or out
     for (int it = tid; it < nitems; it += FT) {
-        const int jt = it & 7, hf = (it >> 3) & 1, tt = it >> 4;
-        const float* pr = s_dpre + (size_t)(tt * 4) * RS + hf * 64;
-        const float* ur = s_U + (size_t)jt * RS + hf * 64;
+        const int p8 = it & 7, jt = (it >> 3) & 7, tt = it >> 6;
+        const float* pr = s_dpre + (size_t)(tt * 4) * RS + p8 * 4;
+        const float* ur = s_U + (size_t)jt * RS + p8 * 4;
         float acc[4][4];
 #pragma unroll
         for (int i = 0; i < 4; ++i)
 #pragma unroll
             for (int k = 0; k < 4; ++k) acc[i][k] = 0.f;
-#pragma unroll 4
-        for (int d4 = 0; d4 < 16; ++d4) {
+#pragma unroll
+        for (int d4 = 0; d4 < 4; ++d4) {
             float4 p[4], u[4];
 #pragma unroll
-            for (int i = 0; i < 4; ++i) p[i] = *reinterpret_cast<const float4*>(pr + i * RS + 4 * d4);
+            for (int i = 0; i < 4; ++i) p[i] = *reinterpret_cast<const float4*>(pr + i * RS + 32 * d4);
 #pragma unroll
-            for (int k = 0; k < 4; ++k) u[k] = *reinterpret_cast<const float4*>(ur + (size_t)(8 * k) * RS + 4 * d4);
+            for (int k = 0; k < 4; ++k) u[k] = *reinterpret_cast<const float4*>(ur + (size_t)(8 * k) * RS + 32 * d4);
 #pragma unroll
             for (int i = 0; i < 4; ++i)
 #pragma unroll
@@ -368,7 +360,13 @@ __global__ void __cluster_dims__(CS, 1, 1) __launch_bounds__(FT, 1) attn_bwd_row
 #pragma unroll
         for (int i = 0; i < 4; ++i)
 #pragma unroll
-            for (int k = 0; k < 4; ++k) atomicAdd(s_G + (size_t)(tt * 4 + i) * GS + jt + 8 * k, acc[i][k]);
+            for (int k = 0; k < 4; ++k) {
+                float a = acc[i][k];
+                a += __shfl_xor_sync(0xffffffffu, a, 1);
+                a += __shfl_xor_sync(0xffffffffu, a, 2);
+                a += __shfl_xor_sync(0xffffffffu, a, 4);
+                if (p8 == 0) s_G[(size_t)(tt * 4 + i) * GS + jt + 8 * k] = a;
+            }
     }
     {   // finish d(h2raw) (s_dq was written before the G tiles by the first 128 threads: the barrier below orders it)
         __syncthreads();
@@ -536,9 +534,9 @@ inline size_t fwd_smem(int T, int D, int V) {
     return sizeof(float) * ((size_t)Tp + 32 + (size_t)Tp * 4 + AD + 4 * AD + D + 32) + sizeof(float4) * (size_t)ntg * nq;
 }
 inline int row_qmax(int T) { return ((((T + 3) >> 2) + CS - 1) / CS) * 4; }     // positions per CTA of the row kernel at len = T
-inline size_t row_smem(int T) {
+inline size_t row_smem(int T, int V) {
     const int Tp = (T + 3) & ~3, Q = row_qmax(T);
-    return sizeof(float) * ((size_t)Q * RS + 32 * RS + (size_t)Q * GS + Tp + 4 * AD + CS * AD + 32);
+    return sizeof(float) * ((size_t)Q * RS + 32 * RS + (size_t)Q * GS + Tp + 4 * AD + CS * AD + 32 + CS + V);
 }
 
 }  // namespace
@@ -547,7 +545,7 @@ extern "C" {
 
 int taco_op_attn_fused_supported(int T, int D, int A, int V, int NFf, int KWf) {
     return A == AD && NFf == NF && KWf == KW && T >= 1 && T <= 1024 && D >= 4 && D % 4 == 0 && V % 4 == 0 &&
-           ((V >> 2) + CS - 1) / CS <= FT && row_smem(T) <= 200 * 1024 && fwd_smem(T, D, V) <= 200 * 1024;
+           ((V >> 2) + CS - 1) / CS <= FT && row_smem(T, V) <= 200 * 1024 && fwd_smem(T, D, V) <= 200 * 1024;
 }
 
 int taco_op_attn_fold(const float* conv_w, const float* conv_b, const float* Wl, float* U, float* c0, void* stream) {
@@ -574,10 +572,9 @@ int taco_op_attn_bwd_fused(float* dctx, const float* carry, const float* dcum, c
     if (!dctx || !carry || !dcum || !align || !th || !values || !lens || !U || !va || !Wq || !de || !dq || !dh2 || !dcum_prev || !scratch) return -1;
     if (B < 1 || !taco_op_attn_fused_supported(T, D, AD, V, NF, KW)) return -1;
     cudaStream_t st = (cudaStream_t)stream;
-    attn_bwd_dalign_fused_kernel<<<dim3((T + 7) / 8, B), 256, sizeof(float) * V, st>>>(dctx, carry, dcum, values, lens, scratch, T, V);
-    const size_t sm = row_smem(T);
+    const size_t sm = row_smem(T, V);
     if (!ensure_smem(attn_bwd_row_kernel, sm)) return -3;
-    attn_bwd_row_kernel<<<dim3(CS, B), FT, sm, st>>>(dctx, carry, dcum, scratch, align, th, lens, U, va, Wq, de, dq, dh2, dcum_prev, T, D, V,
+    attn_bwd_row_kernel<<<dim3(CS, B), FT, sm, st>>>(dctx, carry, dcum, values, align, th, lens, U, va, Wq, de, dq, dh2, dcum_prev, T, D, V,
                                                      row_qmax(T));
     return cudaGetLastError() == cudaSuccess ? 0 : -3;
 }

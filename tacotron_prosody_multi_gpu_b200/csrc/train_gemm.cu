@@ -750,7 +750,8 @@ int launch_skinny_acc(AL A, BPlain Bm, float* C, long long ldc, float* C2, long 
     static const bool one_shot = !getenv("TACO_TRAIN_SKINNY_OLD");
     if (one_shot && K >= 128) {
         const int tiles = ((N + 31) / 32) * ((M + 31) / 32);
-        if (tiles * ((K + 127) / 128) >= 200) {
+        static const int kc_env = getenv("TACO_SKINNY_KC") ? atoi(getenv("TACO_SKINNY_KC")) : 64;   // measured: 64 beats 128 at K = 1024
+        if (kc_env == 128 && tiles * ((K + 127) / 128) >= 200) {
             skinny_acc_kernel<128, AL><<<dim3((N + 31) / 32, (M + 31) / 32, (K + 127) / 128), 128, 0, st>>>(A, Bm, C, ldc, C2, ldc2, N1, M, N, K);
         } else {
             skinny_acc_kernel<64, AL><<<dim3((N + 31) / 32, (M + 31) / 32, (K + 63) / 64), 128, 0, st>>>(A, Bm, C, ldc, C2, ldc2, N1, M, N, K);

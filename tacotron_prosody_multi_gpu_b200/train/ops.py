@@ -392,7 +392,7 @@ def _decoder_loop(self, bwd, dims, zoneout, seed, stream1, stream2, **t):
     s = _fill(TacoDecLoop(), dict(dims, zoneout=float(zoneout), zo_keep_thresh=keep_threshold(1.0 - zoneout), seed=seed,
                                    stream1=stream1, stream2=stream2), t)
     fused = t.get("th") is not None and t.get("attn_work") is not None
-    per_step = ((6 if fused else 12) if bwd else (5 if fused else 8))
+    per_step = ((5 if fused else 12) if bwd else (5 if fused else 8))
     _loop_call(self, "taco_op_decoder_loop_bwd" if bwd else "taco_op_decoder_loop_fwd", s, dims["S"] * per_step)
 
 
