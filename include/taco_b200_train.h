@@ -43,6 +43,9 @@ int taco_op_gemm_pair_acc(const float* A1, long long lda1, int K1, const float* 
                           float* C, long long ldc, int M, int N, void* stream);
 int taco_op_gemm_nt_split_acc(const float* A, long long lda, const float* B, long long ldb, float* C1, long long ldc1, int N1, float* C2,
                               long long ldc2, int N2, int M, int K, void* stream);
+/* C += A . B (tb = 0: B [K,N]) or C += A . B^T (tb = 1: B [N,K]), M = batch rows: the recurrent contraction of the LSTM loops */
+int taco_op_gemm_acc(const float* A, long long lda, const float* B, long long ldb, float* C, long long ldc, int M, int N, int K, int tb,
+                     void* stream);
 /* tf.layers.conv1d(padding='same') NWC, kernel [k,Ci,Co] (Encoder.py:159-164) and its two gradients. */
 int taco_op_conv1d_fwd(const float* x, const float* w, const float* bias, float* y, int B, int T, int Ci, int Co, int k, void* stream);
 int taco_op_conv1d_dgrad(const float* dy, const float* w, float* dx, int B, int T, int Ci, int Co, int k, void* stream);

@@ -814,6 +814,14 @@ int taco_op_gemm_nt_split_acc(const float* A, long long lda, const float* B, lon
     return launch_skinny_acc(APlain{A, lda, 1, 1}, BPlain{B, 1, ldb, 0}, C1, ldc1, C2, ldc2, N1, M, N1 + N2, K, (cudaStream_t)stream);
 }
 
+/* C += A . B (tb = 0, B [K,N]) or A . B^T (tb = 1, B [N,K]) for M = batch rows: the recurrent contraction of the encoder LSTM loops */
+int taco_op_gemm_acc(const float* A, long long lda, const float* B, long long ldb, float* C, long long ldc, int M, int N, int K, int tb,
+                     void* stream) {
+    if (!A || !B || !C || M < 1 || N < 1 || K < 1) return -1;
+    return launch_skinny_acc(APlain{A, lda, 1, 1}, tb ? BPlain{B, 1, ldb, 0} : BPlain{B, ldb, 1, 1}, C, ldc, nullptr, 0, 0, M, N, K,
+                             (cudaStream_t)stream);
+}
+
 int taco_op_set_precision(int precision) {
     if (precision != TACO_TRAIN_FP32 && precision != TACO_TRAIN_BF16) return -1;
     g_train_precision = precision;

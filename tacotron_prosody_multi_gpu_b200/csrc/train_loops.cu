@@ -124,7 +124,7 @@ int taco_op_lstm_loop_fwd(const TacoLstmLoop* p, void* st) {
         const size_t oH = (size_t)s * B * H, nH = oH + (size_t)B * H;
         float* a = p->acts + (size_t)s * B * G;
         OK(taco_op_gather_rows(p->xw, (long long)T * G, G, p->lens, s, p->reverse, pre, B, G, st));
-        OK(taco_op_gemm(p->hz + oH, H, Kh, G, a, G, B, G, H, 0, 0, 1.f, nullptr, st));
+        OK(taco_op_gemm_acc(p->hz + oH, H, Kh, G, a, G, B, G, H, 0, st));
         OK(taco_op_lstm_fwd(a, pre, nullptr, p->cz + oH, p->hz + oH, p->lens, s, p->zoneout, 1, p->zo_keep_thresh, p->seed, p->stream_c,
                             p->stream_h, s * B, p->cnew + oH, p->cz + nH, hraw, p->hz + nH, B, H, st));
         OK(taco_op_scatter_rows(hraw, p->lens, s, p->reverse, p->out, p->out_sb, p->out_st, B, H, st));
@@ -145,7 +145,7 @@ int taco_op_lstm_loop_bwd(const TacoLstmLoop* p, void* st) {
         OK(taco_op_gather_rows(p->out, p->out_sb, p->out_st, p->lens, s, p->reverse, d_hraw, B, H, st));
         OK(taco_op_lstm_bwd(p->acts + (size_t)s * B * G, p->cz + oH, p->hz + oH, p->cnew + oH, p->lens, s, p->zoneout, 1, p->zo_keep_thresh,
                             p->seed, p->stream_c, p->stream_h, s * B, d_hraw, dc, dh, dg, dcn, dhn, B, H, st));
-        OK(taco_op_gemm(dg, G, Kh, G, dhn, H, B, H, G, 0, 1, 1.f, nullptr, st));
+        OK(taco_op_gemm_acc(dg, G, Kh, G, dhn, H, B, H, G, 1, st));
         OK(taco_op_scatter_rows(dg, p->lens, s, p->reverse, p->dxw, (long long)T * G, G, B, G, st));
         float* t_;
         t_ = dc; dc = dcn; dcn = t_;

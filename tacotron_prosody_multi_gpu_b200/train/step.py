@@ -447,26 +447,6 @@ class TrainStep(object):
             o.gemm(dG1[s], W1[U2 + MD:], dh1zn, tb=True, beta=1.0)
             dc1, dc1n, dh1z, dh1zn = dc1n, dc1, dh1zn, dh1z
             dc2, dc2n, dh2z, dh2zn = dc2n, dc2, dh2zn, dh2z
-        dG1_2, dG2_2, dQ2 = dG1.view(S * B, 4 * D), dG2.view(S * B, 4 * D), dQ.view(S * B, A)
-        GW1, GW2 = G[W.DEC_LSTM % (0, 1) + "/kernel"], G[W.DEC_LSTM % (1, 2) + "/kernel"]
-        o.gemm(t["P2"].view(S * B, U2), dG1_2, GW1[:U2], ta=True)
-        o.gemm(t["ctx"][:S].view(S * B, MD), dG1_2, GW1[U2:U2 + MD], ta=True)
-        o.gemm(t["h1z"][:S].view(S * B, D), dG1_2, GW1[U2 + MD:], ta=True)
-        o.colsum(dG1_2, G[W.DEC_LSTM % (0, 1) + "/bias"])
-        o.gemm(t["h1raw"].view(S * B, D), dG2_2, GW2[:D], ta=True)
-        o.gemm(t["h2z"][:S].view(S * B, D), dG2_2, GW2[D:], ta=True)
-        o.colsum(dG2_2, G[W.DEC_LSTM % (1, 2) + "/bias"])
-        o.gemm(h2all, dQ2, G[W.LSA + "/query_layer/kernel"], ta=True)
-        for n, part in zip(att_names, parts):
-            o.colsum(part.view(B, -1), G[n].view(-1))
-        # prenet (hoisted: all steps at once)
-        dP2, dZ2, dP1, dZ1 = o.empty(S, B, U2), o.empty(S, B, U2), o.empty(S, B, U1), o.empty(S, B, U1)
-        o.gemm(dG1_2, W1[:U2], dP2.view(S * B, U2), tb=True)
-        o.prenet_act_bwd(dP2, t["P2"], 1, seed, 0, keep, dZ2)
-        self._dense_bwd(t["P1"].view(S * B, U1), dZ2.view(S * B, U2), W.PRENET % 2 + "/kernel", W.PRENET % 2 + "/bias",
-                        dP1.view(S * B, U1))
-        o.prenet_act_bwd(dP1, t["P1"], 0, seed, 0, keep, dZ1)
-        self._dense_bwd(t["Xin"].view(S * B, M), dZ1.view(S * B, U1), W.PRENET % 1 + "/kernel", W.PRENET % 1 + "/bias")
         # d(values)[b] = align[:, b, :]^T . d(ctx)[:, b, :]; keys = values . Wmem
         dvalues = o.empty(B, T, MD)
         for b in range(B):
@@ -476,10 +456,6 @@ class TrainStep(object):
         if hp.mask_encoder:
             o.mask_rows(dvalues, t["lens"])
         dmemory = dvalues
-        # every decoder / postnet gradient (store.g[tail_start:]) is final from here on: the data-parallel trainer starts
-        # the exchange of that half now, under the style / encoder backward that follows
-        if self.on_tail_ready is not None:
-            self.on_tail_ready()
 
         # ---- style embedding: GST attention -> reference encoder (Attention.py:243-341; Tacotron.py:12-29)
         nh = hp.num_heads
@@ -562,6 +538,32 @@ class TrainStep(object):
                 o.gemm(x3, dxw2, GK[:C], ta=True)
                 o.colsum(dxw2, G[rec["scope"] + "/bias"])
             dxws.append((dxw2, K))
+        # ---- decoder weight gradients and the prenet, all steps at once: on the main stream while the three encoder-side
+        # chains above run on their side streams
+        dG1_2, dG2_2, dQ2 = dG1.view(S * B, 4 * D), dG2.view(S * B, 4 * D), dQ.view(S * B, A)
+        GW1, GW2 = G[W.DEC_LSTM % (0, 1) + "/kernel"], G[W.DEC_LSTM % (1, 2) + "/kernel"]
+        o.gemm(t["P2"].view(S * B, U2), dG1_2, GW1[:U2], ta=True)
+        o.gemm(t["ctx"][:S].view(S * B, MD), dG1_2, GW1[U2:U2 + MD], ta=True)
+        o.gemm(t["h1z"][:S].view(S * B, D), dG1_2, GW1[U2 + MD:], ta=True)
+        o.colsum(dG1_2, G[W.DEC_LSTM % (0, 1) + "/bias"])
+        o.gemm(t["h1raw"].view(S * B, D), dG2_2, GW2[:D], ta=True)
+        o.gemm(t["h2z"][:S].view(S * B, D), dG2_2, GW2[D:], ta=True)
+        o.colsum(dG2_2, G[W.DEC_LSTM % (1, 2) + "/bias"])
+        o.gemm(h2all, dQ2, G[W.LSA + "/query_layer/kernel"], ta=True)
+        for n, part in zip(att_names, parts):
+            o.colsum(part.view(B, -1), G[n].view(-1))
+        # prenet (hoisted: all steps at once)
+        dP2, dZ2, dP1, dZ1 = o.empty(S, B, U2), o.empty(S, B, U2), o.empty(S, B, U1), o.empty(S, B, U1)
+        o.gemm(dG1_2, W1[:U2], dP2.view(S * B, U2), tb=True)
+        o.prenet_act_bwd(dP2, t["P2"], 1, seed, 0, keep, dZ2)
+        self._dense_bwd(t["P1"].view(S * B, U1), dZ2.view(S * B, U2), W.PRENET % 2 + "/kernel", W.PRENET % 2 + "/bias",
+                        dP1.view(S * B, U1))
+        o.prenet_act_bwd(dP1, t["P1"], 0, seed, 0, keep, dZ1)
+        self._dense_bwd(t["Xin"].view(S * B, M), dZ1.view(S * B, U1), W.PRENET % 1 + "/kernel", W.PRENET % 1 + "/bias")
+        # every decoder / postnet gradient (store.g[tail_start:]) is final from here on: the data-parallel trainer starts
+        # the exchange of that half now, under the rest of the encoder backward
+        if self.on_tail_ready is not None:
+            self.on_tail_ready()
         self._join()                               # both directions and the reference-encoder chain
         for d, (dxw2, K) in enumerate(dxws):
             o.gemm(dxw2, K[:C], dx3, tb=True, beta=0.0 if d == 0 else 1.0)
