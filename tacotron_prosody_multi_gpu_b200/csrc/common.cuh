@@ -67,6 +67,30 @@ __device__ __forceinline__ bool philox_keep(uint64_t seed, uint32_t step, uint32
 
 __device__ __forceinline__ float sigmoidf_(float x) { return 1.0f / (1.0f + expf(-x)); }
 
+// ---------------------------------------------------------------------------------------------
+// Programmatic dependent launch (the time loops of the training step are chains of small dependent kernels): a kernel
+// launched with launch_pdl() may be scheduled while its predecessor on the stream still runs.  It must execute pdl_wait()
+// before it reads anything the predecessor wrote or writes anything at all (before that: index arithmetic, Philox masks,
+// loads of weights and of tensors older than the predecessor); pdl_launch_dependents() after the wait lets the NEXT kernel
+// of the chain start its own prologue under this kernel's body.  Without the launch attribute both are no-ops.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+#ifdef __CUDACC__
+#include <stdlib.h>
+template <class... KArgs, class... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args) {
+    static const bool on = !(getenv("TACO_TRAIN_PDL") && atoi(getenv("TACO_TRAIN_PDL")) == 0);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = on ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+#endif
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

@@ -88,6 +88,8 @@ __global__ void __cluster_dims__(CS, 1, 1) __launch_bounds__(FT, 1) attn_fwd_fus
 #pragma unroll
         for (int k = 0; k < 32; ++k) wq0[k] = k0 + k < k1 ? Wq[(long long)(k0 + k) * AD + d] : 0.f;
     }
+    pdl_wait();                                 // everything above reads weights / keys; below: what the previous kernels wrote
+    pdl_launch_dependents();
     for (int i = tid; i < Tp + 32; i += FT) {
         const int t = i - LEFT;
         s_cum[i] = (t >= 0 && t < T) ? cum_prev[(long long)b * T + t] : 0.f;
@@ -242,8 +244,10 @@ __global__ void __cluster_dims__(CS, 1, 1) __launch_bounds__(FT, 1) attn_bwd_row
 #pragma unroll
     for (int k = 0; k < 6; ++k)
         v0[k] = (warp < nvalid && lane + 32 * k < V4) ? val4[(long long)(t_lo + warp) * V4 + lane + 32 * k] : make_float4(0.f, 0.f, 0.f, 0.f);
-    for (int i = tid; i < V; i += FT) s_dctx[i] = dctx[(long long)b * V + i] + carry[(long long)b * V + i];
     for (int i = tid; i < 32 * AD; i += FT) s_U[(i >> 7) * RS + (i & 127)] = (i >> 7) < KW ? U[i] : 0.f;
+    pdl_wait();                                  // everything above reads tensors of the forward pass; below: this step's gradients
+    pdl_launch_dependents();
+    for (int i = tid; i < V; i += FT) s_dctx[i] = dctx[(long long)b * V + i] + carry[(long long)b * V + i];
     cl.sync();                                   // every CTA of the row runs (remote stores below are safe) and has read d(ctx)
     if (cs == 0)
         for (int i = tid; i < V; i += FT) dctx[(long long)b * V + i] = s_dctx[i];      // total d(ctx_t), kept for d(values)
@@ -561,8 +565,8 @@ int taco_op_attn_fwd_fused(const float* h2raw, const float* Wq, const float* U, 
     if (B < 1 || !taco_op_attn_fused_supported(T, D, AD, V, NF, KW)) return -1;
     const size_t sm = fwd_smem(T, D, V);
     if (!ensure_smem(attn_fwd_fused_kernel, sm)) return -3;
-    attn_fwd_fused_kernel<<<dim3(CS, B), FT, sm, (cudaStream_t)stream>>>(h2raw, Wq, U, c0, ba, va, cum_prev, keys, values, lens, q, th, align,
-                                                                        cum, ctx, T, D, V);
+    launch_pdl(attn_fwd_fused_kernel, dim3(CS, B), dim3(FT), sm, (cudaStream_t)stream, h2raw, Wq, U, c0, ba, va, cum_prev, keys, values, lens, q,
+               th, align, cum, ctx, T, D, V);
     return cudaGetLastError() == cudaSuccess ? 0 : -3;
 }
 
@@ -574,8 +578,8 @@ int taco_op_attn_bwd_fused(float* dctx, const float* carry, const float* dcum, c
     cudaStream_t st = (cudaStream_t)stream;
     const size_t sm = row_smem(T, V);
     if (!ensure_smem(attn_bwd_row_kernel, sm)) return -3;
-    attn_bwd_row_kernel<<<dim3(CS, B), FT, sm, st>>>(dctx, carry, dcum, values, align, th, lens, U, va, Wq, de, dq, dh2, dcum_prev, T, D, V,
-                                                     row_qmax(T));
+    launch_pdl(attn_bwd_row_kernel, dim3(CS, B), dim3(FT), sm, st, dctx, carry, dcum, values, align, th, lens, U, va, Wq, de, dq, dh2, dcum_prev,
+               T, D, V, row_qmax(T));
     return cudaGetLastError() == cudaSuccess ? 0 : -3;
 }
 

@@ -15,6 +15,7 @@
 #include <cstdint>
 
 #include "../../include/taco_b200_train.h"
+#include "common.cuh"
 #include "taco_internal.h"   // conv_tc.cu: the tcgen05 implicit-GEMM convolution shared with the synthesis path
 
 namespace {
@@ -697,17 +698,21 @@ __global__ void __launch_bounds__(128) skinny_acc_kernel(AL A, BPlain Bm, float*
     __shared__ __align__(16) float Bs[KC][36];
     const int tid = threadIdx.x, m0 = blockIdx.y * 32, n0 = blockIdx.x * 32, k0 = blockIdx.z * KC;
     float ra[PER], rb[PER];
-#pragma unroll
-    for (int i = 0; i < PER; ++i) {              // A is k-contiguous in both uses (activations [M, K])
-        const int e = tid + i * NT, kk = e % KC, mm = e / KC;
-        ra[i] = (m0 + mm < M && k0 + kk < K) ? A(m0 + mm, k0 + kk) : 0.f;
-    }
+    // B is the weight operand (constant during a time loop): its loads go out before the programmatic-launch wait, i.e. while
+    // the kernel that produces A may still be running
 #pragma unroll
     for (int i = 0; i < PER; ++i) {
         const int e = tid + i * NT;
         int nn, kk;
         if (Bm.n_contig) { nn = e & 31; kk = e >> 5; } else { kk = e % KC; nn = e / KC; }
         rb[i] = (n0 + nn < N && k0 + kk < K) ? Bm(k0 + kk, n0 + nn) : 0.f;
+    }
+    pdl_wait();
+    pdl_launch_dependents();
+#pragma unroll
+    for (int i = 0; i < PER; ++i) {              // A is k-contiguous in both uses (activations [M, K])
+        const int e = tid + i * NT, kk = e % KC, mm = e / KC;
+        ra[i] = (m0 + mm < M && k0 + kk < K) ? A(m0 + mm, k0 + kk) : 0.f;
     }
 #pragma unroll
     for (int i = 0; i < PER; ++i) {
@@ -752,9 +757,9 @@ int launch_skinny_acc(AL A, BPlain Bm, float* C, long long ldc, float* C2, long 
         const int tiles = ((N + 31) / 32) * ((M + 31) / 32);
         static const int kc_env = getenv("TACO_SKINNY_KC") ? atoi(getenv("TACO_SKINNY_KC")) : 64;   // measured: 64 beats 128 at K = 1024
         if (kc_env == 128 && tiles * ((K + 127) / 128) >= 200) {
-            skinny_acc_kernel<128, AL><<<dim3((N + 31) / 32, (M + 31) / 32, (K + 127) / 128), 128, 0, st>>>(A, Bm, C, ldc, C2, ldc2, N1, M, N, K);
+            launch_pdl(skinny_acc_kernel<128, AL>, dim3((N + 31) / 32, (M + 31) / 32, (K + 127) / 128), dim3(128), 0, st, A, Bm, C, ldc, C2, ldc2, N1, M, N, K);
         } else {
-            skinny_acc_kernel<64, AL><<<dim3((N + 31) / 32, (M + 31) / 32, (K + 63) / 64), 128, 0, st>>>(A, Bm, C, ldc, C2, ldc2, N1, M, N, K);
+            launch_pdl(skinny_acc_kernel<64, AL>, dim3((N + 31) / 32, (M + 31) / 32, (K + 63) / 64), dim3(128), 0, st, A, Bm, C, ldc, C2, ldc2, N1, M, N, K);
         }
         return cudaGetLastError() == cudaSuccess ? 0 : -3;
     }

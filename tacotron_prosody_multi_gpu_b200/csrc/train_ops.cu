@@ -215,6 +215,16 @@ __global__ void lstm_fwd_kernel(float* __restrict__ gates, const float* __restri
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= B * H) return;
     int b = i / H, u = i - b * H;
+    float mc, mh;                                  // zoneout masks: counter-based, computed under the predecessor's tail
+    if (train) {
+        unsigned long long idx = (unsigned long long)(row0 + b) * H + u;
+        mc = train_keep(seed, sc, idx, thresh) ? 1.f : 0.f;
+        mh = train_keep(seed, sh, idx, thresh) ? 1.f : 0.f;
+    } else {
+        mc = mh = 1.f - zoneout;
+    }
+    pdl_wait();
+    pdl_launch_dependents();
     float z[4];
 #pragma unroll
     for (int g = 0; g < 4; ++g) {
@@ -230,14 +240,6 @@ __global__ void lstm_fwd_kernel(float* __restrict__ gates, const float* __restri
     float cp = c_prev[i], hp = h_prev[i];
     float cn = sf * cp + si * tj;
     float hr = so * tanhf(cn);
-    float mc, mh;
-    if (train) {
-        unsigned long long idx = (unsigned long long)(row0 + b) * H + u;
-        mc = train_keep(seed, sc, idx, thresh) ? 1.f : 0.f;
-        mh = train_keep(seed, sh, idx, thresh) ? 1.f : 0.f;
-    } else {
-        mc = mh = 1.f - zoneout;
-    }
     float czv = cp + mc * (cn - cp), hzv = hp + mh * (hr - hp);
     if (lens && s >= lens[b]) { czv = cp; hzv = hp; hr = 0.f; }
     cnew[i] = cn; cz[i] = czv; hraw[i] = hr; hz[i] = hzv;
@@ -252,13 +254,6 @@ __global__ void lstm_bwd_kernel(const float* __restrict__ acts, const float* __r
     if (i >= B * H) return;
     int b = i / H, u = i - b * H;
     long long k0 = (long long)b * 4 * H + u;
-    if (lens && s >= lens[b]) {
-        dgates[k0] = 0.f; dgates[k0 + H] = 0.f; dgates[k0 + 2 * H] = 0.f; dgates[k0 + 3 * H] = 0.f;
-        d_cprev[i] = d_cz[i];
-        d_hprev[i] = d_hz[i];
-        return;
-    }
-    float si = acts[k0], tj = acts[k0 + H], sf = acts[k0 + 2 * H], so = acts[k0 + 3 * H];
     float mc, mh;
     if (train) {
         unsigned long long idx = (unsigned long long)(row0 + b) * H + u;
@@ -267,6 +262,15 @@ __global__ void lstm_bwd_kernel(const float* __restrict__ acts, const float* __r
     } else {
         mc = mh = 1.f - zoneout;
     }
+    pdl_wait();
+    pdl_launch_dependents();
+    if (lens && s >= lens[b]) {
+        dgates[k0] = 0.f; dgates[k0 + H] = 0.f; dgates[k0 + 2 * H] = 0.f; dgates[k0 + 3 * H] = 0.f;
+        d_cprev[i] = d_cz[i];
+        d_hprev[i] = d_hz[i];
+        return;
+    }
+    float si = acts[k0], tj = acts[k0 + H], sf = acts[k0 + 2 * H], so = acts[k0 + 3 * H];
     float tc = tanhf(cnew[i]);
     float dhz = d_hz[i], dcz = d_cz[i];
     float dh_new = d_hraw[i] + mh * dhz;
@@ -284,6 +288,8 @@ __global__ void gather_rows_kernel(const float* __restrict__ src, long long sb, 
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= B * N) return;
     int b = i / N, c = i - b * N, len = lens[b];
+    pdl_wait();
+    pdl_launch_dependents();
     float v = 0.f;
     if (s < len) v = src[(long long)b * sb + (long long)(reverse ? len - 1 - s : s) * st + c];
     out[i] = v;
@@ -293,6 +299,8 @@ __global__ void scatter_rows_kernel(const float* __restrict__ src, const int32_t
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= B * N) return;
     int b = i / N, c = i - b * N, len = lens[b];
+    pdl_wait();
+    pdl_launch_dependents();
     if (s < len) dst[(long long)b * db + (long long)(reverse ? len - 1 - s : s) * dt + c] = src[i];
 }
 
@@ -504,7 +512,7 @@ int taco_op_lstm_fwd(float* gates, const float* pre, const float* bias, const fl
                      const int32_t* lens, int s, float zoneout, int train, uint32_t zo_keep_thresh, uint64_t seed, uint32_t stream_c,
                      uint32_t stream_h, int row0, float* cnew, float* cz, float* hraw, float* hz, int B, int H, void* stream) {
     if (!gates || !c_prev || !h_prev || !cnew || !cz || !hraw || !hz || B < 1 || H < 1) return -1;
-    lstm_fwd_kernel<<<nblk((long long)B * H), 256, 0, ST>>>(gates, pre, bias, c_prev, h_prev, lens, s, zoneout, train, seed, stream_c,
+    launch_pdl(lstm_fwd_kernel, dim3(nblk((long long)B * H)), dim3(256), 0, ST, gates, pre, bias, c_prev, h_prev, lens, s, zoneout, train, seed, stream_c,
                                                             stream_h, row0, zo_keep_thresh, cnew, cz, hraw, hz, B, H);
     return rc();
 }
@@ -513,20 +521,20 @@ int taco_op_lstm_bwd(const float* acts, const float* c_prev, const float* h_prev
                      const float* d_hraw, const float* d_cz, const float* d_hz, float* dgates, float* d_cprev, float* d_hprev,
                      int B, int H, void* stream) {
     if (!acts || !c_prev || !h_prev || !cnew || !d_hraw || !d_cz || !d_hz || !dgates || !d_cprev || !d_hprev) return -1;
-    lstm_bwd_kernel<<<nblk((long long)B * H), 256, 0, ST>>>(acts, c_prev, h_prev, cnew, lens, s, zoneout, train, seed, stream_c, stream_h,
+    launch_pdl(lstm_bwd_kernel, dim3(nblk((long long)B * H)), dim3(256), 0, ST, acts, c_prev, h_prev, cnew, lens, s, zoneout, train, seed, stream_c, stream_h,
                                                             row0, zo_keep_thresh, d_hraw, d_cz, d_hz, dgates, d_cprev, d_hprev, B, H);
     return rc();
 }
 int taco_op_gather_rows(const float* src, long long sb, long long st, const int32_t* lens, int s, int reverse, float* out,
                         int B, int N, void* stream) {
     if (!src || !lens || !out) return -1;
-    gather_rows_kernel<<<nblk((long long)B * N), 256, 0, ST>>>(src, sb, st, lens, s, reverse, out, B, N);
+    launch_pdl(gather_rows_kernel, dim3(nblk((long long)B * N)), dim3(256), 0, ST, src, sb, st, lens, s, reverse, out, B, N);
     return rc();
 }
 int taco_op_scatter_rows(const float* src, const int32_t* lens, int s, int reverse, float* dst, long long db, long long dt,
                          int B, int N, void* stream) {
     if (!src || !lens || !dst) return -1;
-    scatter_rows_kernel<<<nblk((long long)B * N), 256, 0, ST>>>(src, lens, s, reverse, dst, db, dt, B, N);
+    launch_pdl(scatter_rows_kernel, dim3(nblk((long long)B * N)), dim3(256), 0, ST, src, lens, s, reverse, dst, db, dt, B, N);
     return rc();
 }
 int taco_op_gru_pre(float* g, const float* h, float* rh, int B, int R, void* stream) {
