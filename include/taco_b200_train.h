@@ -99,6 +99,23 @@ int taco_op_attn_bwd(const float* dctx, const float* dcum, const float* q, const
                      float* p_conv_w, float* p_conv_b, float* p_Wl, float* p_va, float* p_ba, float* scratch /* >= B*T*NF floats */,
                      int B, int T, int A, int V, int NF, int KW, void* stream);
 
+/* taco_op_attn_bwd for callers that cannot allocate (CUDA graph capture, tight serving / training loops, harnesses that forbid
+ * cudaMalloc).  NO COUNTERPART IN THE REFERENCE.  Same arguments and results as
+ * taco_op_attn_bwd minus the scratch pointer: the d(location features) scratch [B,T,NF] lives in a file-scope
+ * `static __device__ __align__(256)` array of TACO_ATTN_BWD_NOALLOC_MAX_FLOATS floats (4 MiB, held by every GPU that loads the
+ * library until exit), whose device address is resolved with cudaGetSymbolAddress once per device (the device current at the
+ * call).  Calls no cudaMalloc / cudaFree / allocating library routine.  B*T*NF beyond the limit: returns
+ * TACO_OP_ERR_SCRATCH_LIMIT (and says so on stderr) without launching anything.  All calls on a device share the array and it
+ * keeps the last call's contents (every entry a call reads is written by that call first, so nothing has to be cleared): calls
+ * that overlap on the GPU (different streams, or graph branches without an edge between them) RACE -- serialise them. */
+#define TACO_ATTN_BWD_NOALLOC_MAX_FLOATS (1 << 20)
+#define TACO_OP_ERR_SCRATCH_LIMIT (-4)
+int taco_op_attn_bwd_noalloc(const float* dctx, const float* dcum, const float* q, const float* cum_prev, const float* align,
+                             const float* keys, const float* values, const int32_t* lens, const float* conv_w, const float* conv_b,
+                             const float* Wl, const float* va, const float* ba, float* dq, float* dcum_prev, float* dkeys,
+                             float* p_conv_w, float* p_conv_b, float* p_Wl, float* p_va, float* p_ba,
+                             int B, int T, int A, int V, int NF, int KW, void* stream);
+
 /* The same attention step for the time loops, fused (csrc/train_attn_fused.cu): the location convolution and the location dense
  * layer folded into one filter bank U [KW,A] (+ c0 [A]) once per training step; forward = ONE launch per decoder step (query
  * projection q = h2raw . Wq, energies, masked softmax, cumulative update, context) that also saves tanh(pre) [B,T,A]; backward

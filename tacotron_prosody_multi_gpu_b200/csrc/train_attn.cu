@@ -14,6 +14,9 @@
 #include <cuda_runtime.h>
 #include <math.h>
 #include <stdint.h>
+#include <stdio.h>
+
+#include <mutex>
 
 #include "../../include/taco_b200_train.h"
 #include "common.cuh"
@@ -354,6 +357,32 @@ __global__ void __launch_bounds__(512) attn_bwd_conv_kernel(const float* __restr
     }
 }
 
+// Scratch of taco_op_attn_bwd_noalloc: d(location features) [B][T][NF] in a file-scope device array (4 MiB per GPU that loads the
+// library, held until exit).  In host code the name is only a handle: the device address comes from cudaGetSymbolAddress, once per
+// device with that device current (noalloc_scratch()).
+static __device__ __align__(256) float g_attn_bwd_scratch[TACO_ATTN_BWD_NOALLOC_MAX_FLOATS];
+
+constexpr int MAX_DEVICES = 64;
+float* g_scratch_ptr[MAX_DEVICES];       // per device, nullptr until resolved
+std::mutex g_scratch_mu;
+
+int noalloc_scratch(float** out) {
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= MAX_DEVICES) return -3;
+    std::lock_guard<std::mutex> lock(g_scratch_mu);
+    if (!g_scratch_ptr[dev]) {
+        float* ptr = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress((void**)&ptr, g_attn_bwd_scratch);
+        if (e != cudaSuccess || !ptr) {
+            fprintf(stderr, "[taco_b200] taco_op_attn_bwd_noalloc: cudaGetSymbolAddress failed on device %d: %s\n", dev, cudaGetErrorString(e));
+            return -3;
+        }
+        g_scratch_ptr[dev] = ptr;
+    }
+    *out = g_scratch_ptr[dev];
+    return 0;
+}
+
 template <class K>
 inline bool ensure_smem(K kernel, size_t bytes) {
     return bytes <= 48 * 1024 || cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes) == cudaSuccess;
@@ -400,6 +429,28 @@ int taco_op_attn_bwd(const float* dctx, const float* dcum, const float* q, const
     if (!ensure_smem(attn_bwd_conv_kernel, sm2)) return -3;
     attn_bwd_conv_kernel<<<B, 512, sm2, st>>>(dcum, cum_prev, dfl, lens, conv_w, dcum_prev, p_conv_w, p_conv_b, T, KW);
     return cudaGetLastError() == cudaSuccess ? 0 : -3;
+}
+
+int taco_op_attn_bwd_noalloc(const float* dctx, const float* dcum, const float* q, const float* cum_prev, const float* align,
+                             const float* keys, const float* values, const int32_t* lens, const float* conv_w, const float* conv_b,
+                             const float* Wl, const float* va, const float* ba, float* dq, float* dcum_prev, float* dkeys,
+                             float* p_conv_w, float* p_conv_b, float* p_Wl, float* p_va, float* p_ba,
+                             int B, int T, int A, int V, int NFf, int KW, void* stream) {
+    if (B < 1 || T < 1 || NFf < 1) return -1;
+    const long long need = (long long)B * T * NFf;
+    if (need > (long long)TACO_ATTN_BWD_NOALLOC_MAX_FLOATS) {
+        fprintf(stderr, "[taco_b200] taco_op_attn_bwd_noalloc: B*T*NF = %lld floats of scratch exceed the static limit of %d "
+                        "(TACO_ATTN_BWD_NOALLOC_MAX_FLOATS); use taco_op_attn_bwd with caller-provided scratch\n",
+                need, (int)TACO_ATTN_BWD_NOALLOC_MAX_FLOATS);
+        return TACO_OP_ERR_SCRATCH_LIMIT;
+    }
+    float* scratch = nullptr;
+    const int rc = noalloc_scratch(&scratch);
+    if (rc) return rc;
+    // nothing in the scratch has to start at zero: attn_bwd_pre_kernel writes every [b][t < T][f] entry (zeros beyond the
+    // length) before attn_bwd_conv_kernel reads it, so the previous call's contents are never observed
+    return taco_op_attn_bwd(dctx, dcum, q, cum_prev, align, keys, values, lens, conv_w, conv_b, Wl, va, ba, dq, dcum_prev, dkeys,
+                            p_conv_w, p_conv_b, p_Wl, p_va, p_ba, scratch, B, T, A, V, NFf, KW, stream);
 }
 
 }  // extern "C"

@@ -406,7 +406,7 @@ def _lstm_loop(self, bwd, dims, zoneout, seed, stream_c, stream_h, out, **t):
 
 CudaOps.decoder_loop = _decoder_loop
 CudaOps.lstm_loop = _lstm_loop
-TRAIN_SYMBOLS = tuple(_SIGS.keys()) + LOOP_SYMBOLS + ("taco_op_set_precision", "taco_op_gemm_pair_acc", "taco_op_gemm_nt_split_acc", "taco_op_gemm_acc", "taco_op_attn_fused_supported")
+TRAIN_SYMBOLS = tuple(_SIGS.keys()) + LOOP_SYMBOLS + ("taco_op_set_precision", "taco_op_gemm_pair_acc", "taco_op_gemm_nt_split_acc", "taco_op_gemm_acc", "taco_op_attn_fused_supported", "taco_op_attn_bwd_noalloc")
 
 
 def _set_precision(self, precision):
