@@ -45,6 +45,24 @@ B_PER_GPU = 64
 S_STEPS = 720
 
 
+
+def _claim_stdout():
+    """Only the JSON line may reach stdout: libraries write to fd 1 behind Python's back (NCCL prints its version banner there).
+    fd 1 is pointed at stderr for the rest of the process; the returned file is the real stdout."""
+    sys.stdout.flush()
+    saved = os.dup(1)
+    os.dup2(2, 1)
+    return os.fdopen(saved, "w")
+
+
+OUT = None          # the real stdout (set by main)
+
+
+def _emit(line):
+    out = OUT if OUT is not None else sys.stdout
+    print(json.dumps(line), file=out, flush=True)
+
+
 def config_dict(S, in_flight, batch=B_PER_GPU, T=111):
     """The workload description BOTH arms print (the driver compares the two `config` objects)."""
     return {"workload": "C2 free-running inference, B=%d/GPU, sentences.txt token lengths x4 (T=%d), S=%d decoder steps "
@@ -203,7 +221,7 @@ def run_reference(args):
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line))
+    _emit(line)
     return 0
 
 
@@ -516,7 +534,7 @@ def run_b200(args):
         line["cpu_baseline"] = {"value": fr / dt, "unit": UNIT, "cores": cores, "kind": "port",
                                 "sample": "one pass of the same B=64,T=111 batch, %d of %d decoder steps, torch-CPU fp32 "
                                           "restatement of the reference (TF 1.9 unavailable), %.1f s" % (Sc, S, dt)}
-    print(json.dumps(line))
+    _emit(line)
     if world > 1:
         dist.destroy_process_group()
     return 0
@@ -542,6 +560,8 @@ def main():
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"],
                     help="bf16: tensor-core (tcgen05) contractions with bf16 operands, fp32 accumulate; fp32: SIMT everywhere")
     args = ap.parse_args()
+    global OUT
+    OUT = _claim_stdout()
     if args.warmup < 3 and args.impl == "b200":
         args.warmup = 3
     if args.workload == "c4":
@@ -549,6 +569,7 @@ def main():
             ["--impl", "reference"] if args.impl == "reference" else [])
         sys.path.insert(0, os.path.join(ROOT, "scripts"))
         import bench_train
+        bench_train.OUT = OUT
         return bench_train.main()
     if args.impl == "reference":
         return run_reference(args)

@@ -20,6 +20,24 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
 
+
+def _claim_stdout():
+    """Only the JSON line may reach stdout: libraries write to fd 1 behind Python's back (NCCL prints its version banner there).
+    fd 1 is pointed at stderr for the rest of the process; the returned file is the real stdout."""
+    sys.stdout.flush()
+    saved = os.dup(1)
+    os.dup2(2, 1)
+    return os.fdopen(saved, "w")
+
+
+OUT = None          # the real stdout (set by main)
+
+
+def _emit(line):
+    out = OUT if OUT is not None else sys.stdout
+    print(json.dumps(line), file=out, flush=True)
+
+
 def workload(hp, batch, max_frames, rank):
     from tacotron_prosody_multi_gpu_b200 import synthetic
     lengths = synthetic.cycle_lengths(batch)
@@ -63,12 +81,12 @@ def run_reference(args):
     value = fps / (B * F)
     sample = "autograd through the oracle, B=%d, F=%d frames of the same batch per pass; steps/s = sample frames/s / (%d x %d)" % (Bs, Fs, B, F)
     n_grad = 20425491
-    print(json.dumps({"impl": "reference", "metric": METRIC % args.batch, "value": value, "unit": "steps/s", "mel_frames_per_sec": fps,
+    _emit({"impl": "reference", "metric": METRIC % args.batch, "value": value, "unit": "steps/s", "mel_frames_per_sec": fps,
                       "n_gpus": int(os.environ.get("WORLD_SIZE", "1")), "steps": args.steps, "warmup": args.warmup,
                       "ms_per_step": 1e3 / value, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
                       "data": "synthetic", "config": c4_config(B, T, F, n_grad),
                       "cpu_baseline": {"value": value, "unit": "steps/s", "cores": cores, "kind": "port", "sample": sample},
-                      "e2e": {"value": value, "unit": "steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}))
+                      "e2e": {"value": value, "unit": "steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0})
     return 0
 
 
@@ -86,6 +104,9 @@ def main():
     ap.add_argument("--host-inputs", type=int, default=1, help="1: every timed step copies its batch from pinned host memory (e2e form)")
     ap.add_argument("--no-overlap", action="store_true", help="one all-reduce of the whole bucket after backward (no early half)")
     args = ap.parse_args()
+    global OUT
+    if OUT is None:
+        OUT = _claim_stdout()
     if args.impl == "reference":
         return run_reference(args)
     import torch
@@ -205,7 +226,7 @@ def main():
             dt = time.perf_counter() - t0
             line["cpu_baseline"] = {"value": Bs * Fs / dt, "unit": "mel frames/s (training)", "cores": os.cpu_count(), "kind": "port",
                                     "sample": "autograd through the oracle, B=%d, F=%d frames of the same batch, %.1f s" % (Bs, Fs, dt)}
-        print(json.dumps(line))
+        _emit(line)
     if world > 1:
         dist.destroy_process_group()
 
