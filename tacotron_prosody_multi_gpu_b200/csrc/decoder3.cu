@@ -234,7 +234,11 @@ struct A4 {
 // phase are requested from L2 BEFORE the wait that precedes that phase, so their latency hides behind the exchange.
 __device__ __forceinline__ void prefetch4(uint4 (&a)[4], const uint4* set_mt, int kg, int lane) {
 #pragma unroll
+#ifdef D3_NO_STREAM   // ablation build: how much of the step is the L2 stream of the non-resident weight tiles (results are garbage)
+    for (int i = 0; i < 4; ++i) a[i] = make_uint4(0x3c003c00u + lane, 0x3c003c00u + kg, 0x3c003c00u, 0x3c003c00u + i);
+#else
     for (int i = 0; i < 4; ++i) a[i] = ldg_stream_v4(set_mt + (size_t)(kg + 4 * i) * 32 + lane);
+#endif
 }
 // the 8 B fragments (4 k-steps x 2 n-tiles) of blocks ks0, ks0 + kstride, ...
 __device__ __forceinline__ void load_b4(uint2 (&b)[4][2], const uint32_t* bbuf, int ks0, int kstride, int nks, int lane, Guard3&) {
