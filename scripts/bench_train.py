@@ -213,7 +213,7 @@ def main():
                 "exchange": exch,
                 "precision": "bf16 operands + fp32 accumulation in the conv / all-rows contractions (mma.sync); recurrent per-step contractions, "
                              "state, normalisation, losses, optimizer fp32" if args.precision == "bf16" else "fp32 everywhere",
-                "data": "synthetic", "config": c4_config(B, T, F, st.store.n),
+                "data": "synthetic", "config": c4_config(B, T, F, st.store.n_params),
                 "phases_ms": {kk: v / k for kk, v in phases.items()}, "gpu_launches": launches,
                 "losses_first_last": [losses[0], losses[-1]]}
         if world == 1 and args.cpu_sample:

@@ -749,10 +749,93 @@ __global__ void __launch_bounds__(128) skinny_acc_kernel(AL A, BPlain Bm, float*
     }
 }
 
+// The same kernel with 16-byte operand loads for the shapes of the time loops (K % 64 == 0, N % 32 == 0, every row of both operands
+// 16-byte aligned -- train/params.py aligns the variables of the flat parameter buffer for this): 4 + 4 loads per thread instead of
+// 16 + 16, no per-element index arithmetic, 6 LDS.128 per 32 FMA in the contraction.  BT: B is stored [N][K] (k-contiguous).
+__device__ __forceinline__ const float* a_row_ptr(const APlain& A, int m, int k0) { return A.p + (long long)m * A.sm + k0; }
+__device__ __forceinline__ const float* a_row_ptr(const APair& A, int m, int k0) {
+    return k0 < A.K1 ? A.p1 + (long long)m * A.ld1 + k0 : A.p2 + (long long)m * A.ld2 + (k0 - A.K1);
+}
+template <class AL, bool BT>
+__global__ void __launch_bounds__(128) skinny_acc_vec_kernel(AL A, const float* __restrict__ Bp, long long ldb, float* __restrict__ C,
+                                                             long long ldc, float* __restrict__ C2, long long ldc2, int N1, int M) {
+    constexpr int KC = 64, NT = 128, AS = KC + 4;      // row stride of the k-contiguous tiles: 16-byte aligned rows
+    __shared__ __align__(16) float As[32][AS];
+    __shared__ __align__(16) float Bs[BT ? 32 * AS : KC * 36];   // BT: [n][k] (stride AS), else [k][n] (stride 36)
+    const int tid = threadIdx.x, m0 = blockIdx.y * 32, n0 = blockIdx.x * 32, k0 = blockIdx.z * KC;
+    float4 ra[4], rb[4];
+    // the weight operand does not depend on the previous kernel of the chain: requested before the programmatic-launch wait
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int e = tid + i * NT;
+        if (BT) rb[i] = *reinterpret_cast<const float4*>(Bp + (long long)(n0 + (e >> 4)) * ldb + k0 + 4 * (e & 15));
+        else rb[i] = *reinterpret_cast<const float4*>(Bp + (long long)(k0 + (e >> 3)) * ldb + n0 + 4 * (e & 7));
+    }
+    pdl_wait();
+    pdl_launch_dependents();
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int e = tid + i * NT, mm = e >> 4;
+        ra[i] = (m0 + mm < M) ? *reinterpret_cast<const float4*>(a_row_ptr(A, m0 + mm, k0) + 4 * (e & 15)) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int e = tid + i * NT;
+        *reinterpret_cast<float4*>(&As[e >> 4][4 * (e & 15)]) = ra[i];
+        if (BT) *reinterpret_cast<float4*>(&Bs[(((e >> 4) >> 2) + 8 * ((e >> 4) & 3)) * AS + 4 * (e & 15)]) = rb[i];   // row n at (n / 4) + 8 (n % 4): conflict-free reads below
+        else *reinterpret_cast<float4*>(&Bs[(e >> 3) * 36 + 4 * (e & 7)]) = rb[i];
+    }
+    __syncthreads();
+    const int ty = tid >> 3, tx = tid & 7;       // rows 2 ty, 2 ty + 1; columns 4 tx .. 4 tx + 3
+    float acc[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
+#pragma unroll 4
+    for (int k4 = 0; k4 < KC / 4; ++k4) {
+        const float4 a0 = *reinterpret_cast<const float4*>(&As[2 * ty][4 * k4]);
+        const float4 a1 = *reinterpret_cast<const float4*>(&As[2 * ty + 1][4 * k4]);
+        const float a0s[4] = {a0.x, a0.y, a0.z, a0.w}, a1s[4] = {a1.x, a1.y, a1.z, a1.w};
+        if (BT) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const float4 b = *reinterpret_cast<const float4*>(&Bs[(tx + 8 * j) * AS + 4 * k4]);     // column 4 tx + j
+                acc[0][j] = fmaf(a0.x, b.x, acc[0][j]); acc[0][j] = fmaf(a0.y, b.y, acc[0][j]); acc[0][j] = fmaf(a0.z, b.z, acc[0][j]); acc[0][j] = fmaf(a0.w, b.w, acc[0][j]);
+                acc[1][j] = fmaf(a1.x, b.x, acc[1][j]); acc[1][j] = fmaf(a1.y, b.y, acc[1][j]); acc[1][j] = fmaf(a1.z, b.z, acc[1][j]); acc[1][j] = fmaf(a1.w, b.w, acc[1][j]);
+            }
+        } else {
+#pragma unroll
+            for (int kk = 0; kk < 4; ++kk) {
+                const float4 b = *reinterpret_cast<const float4*>(&Bs[(4 * k4 + kk) * 36 + 4 * tx]);
+                acc[0][0] = fmaf(a0s[kk], b.x, acc[0][0]); acc[0][1] = fmaf(a0s[kk], b.y, acc[0][1]); acc[0][2] = fmaf(a0s[kk], b.z, acc[0][2]); acc[0][3] = fmaf(a0s[kk], b.w, acc[0][3]);
+                acc[1][0] = fmaf(a1s[kk], b.x, acc[1][0]); acc[1][1] = fmaf(a1s[kk], b.y, acc[1][1]); acc[1][2] = fmaf(a1s[kk], b.z, acc[1][2]); acc[1][3] = fmaf(a1s[kk], b.w, acc[1][3]);
+            }
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+        const int m = m0 + 2 * ty + i;
+        if (m >= M) continue;
+        const int nb = n0 + 4 * tx;             // N1 % 32 == 0: a thread's 4 columns never straddle the two outputs
+        float* c4 = (C2 && nb >= N1) ? C2 + (long long)m * ldc2 + (nb - N1) : C + (long long)m * ldc + nb;
+        atomicAdd(reinterpret_cast<float4*>(c4), make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]));   // one 16-byte reduction
+    }
+}
+
+inline bool al16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+inline bool vec_ok(const APlain& A, int K) { return A.sk == 1 && A.sm % 4 == 0 && al16(A.p); }
+inline bool vec_ok(const APair& A, int K) { return A.K1 % 64 == 0 && A.ld1 % 4 == 0 && A.ld2 % 4 == 0 && al16(A.p1) && al16(A.p2); }
+
 // skinny (M = batch) contraction with a two-block A and/or a two-block C, always accumulating (beta = 1), split-K
 template <class AL>
 int launch_skinny_acc(AL A, BPlain Bm, float* C, long long ldc, float* C2, long long ldc2, int N1, int M, int N, int K, cudaStream_t st) {
     static const bool one_shot = !getenv("TACO_TRAIN_SKINNY_OLD");
+    static const bool vec = !getenv("TACO_TRAIN_SKINNY_SCALAR");
+    if (one_shot && vec && K >= 128 && K % 64 == 0 && N % 32 == 0 && vec_ok(A, K) && al16(Bm.p) && al16(C) && ldc % 4 == 0 &&
+        (Bm.n_contig ? (Bm.sn == 1 && Bm.sk % 4 == 0) : (Bm.sk == 1 && Bm.sn % 4 == 0)) &&
+        (!C2 || (N1 % 32 == 0 && al16(C2) && ldc2 % 4 == 0))) {
+        const dim3 grid(N / 32, (M + 31) / 32, K / 64);
+        if (Bm.n_contig) launch_pdl(skinny_acc_vec_kernel<AL, false>, grid, dim3(128), 0, st, A, Bm.p, Bm.sk, C, ldc, C2, ldc2, N1, M);
+        else launch_pdl(skinny_acc_vec_kernel<AL, true>, grid, dim3(128), 0, st, A, Bm.p, Bm.sn, C, ldc, C2, ldc2, N1, M);
+        return cudaGetLastError() == cudaSuccess ? 0 : -3;
+    }
     if (one_shot && K >= 128) {
         const int tiles = ((N + 31) / 32) * ((M + 31) / 32);
         static const int kc_env = getenv("TACO_SKINNY_KC") ? atoi(getenv("TACO_SKINNY_KC")) : 64;   // measured: 64 beats 128 at K = 1024

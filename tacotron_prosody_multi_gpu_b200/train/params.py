@@ -15,6 +15,7 @@ NOT_TRAINABLE = ("moving_mean", "moving_variance")
 # Tacotron.py:419-422: variables whose NAME contains one of these are not L2-regularised
 REG_EXCLUDE = ("bias", "Bias", "_projection", "inputs_embedding", "RNN", "LSTM")
 # variable scopes whose gradients are complete when the decoder BPTT ends (train/step.py backward): the early exchange half
+ALIGN = 4          # floats: variables start on 16-byte boundaries of the flat parameter / gradient / Adam buffers
 TAIL_SCOPES = ("decoder/", "postnet_convolutions/", "postnet_projection/")
 # Tacotron.py:478-480: with tacotron_fine_tuning only variables NOT matching these are updated
 FINE_TUNE_FROZEN = ("inputs_embedding", "encoder_")
@@ -32,14 +33,22 @@ class ParamStore(object):
     def __init__(self, ops, weights, reg_weight):
         self.ops = ops
         self.layout = OrderedDict()
+        # every variable starts on a 16-byte boundary of the flat buffers (the kernels use 16-byte loads of weight rows where the
+        # address allows it; the scalar attention_g would otherwise misalign the whole decoder and postnet).  Padding elements are
+        # zero in p, g, m, v and regw: they add nothing to the global norm and Adam leaves them at zero.
         off = 0
+        n_params = 0
         for name, v in weights.items():
             if is_trainable(name):
                 v = np.asarray(v, np.float32)
+                off = (off + ALIGN - 1) // ALIGN * ALIGN
                 self.layout[name] = (off, tuple(v.shape))
                 off += v.size
-        self.n = off
-        flat = np.empty(off, np.float32)
+                n_params += v.size
+        off = (off + ALIGN - 1) // ALIGN * ALIGN
+        self.n = off                      # length of the flat buffers (padding included)
+        self.n_params = n_params          # trainable scalars (20 425 491 with the default hyper-parameters)
+        flat = np.zeros(off, np.float32)
         regw = np.zeros(off, np.float32)
         for name, (o, shp) in self.layout.items():
             sz = int(np.prod(shp)) if len(shp) else 1
@@ -100,7 +109,7 @@ class ParamStore(object):
         missing = [n for n in list(self.layout) + list(self.stats) if n not in names]
         if missing:
             raise KeyError("training state %r lacks %d variables, e.g. %s" % (path, len(missing), missing[:3]))
-        flat = np.empty(self.n, np.float32)
+        flat = np.zeros(self.n, np.float32)
         for name, (o, shp) in self.layout.items():
             a = np.asarray(z[names[name]], np.float32)
             if tuple(a.shape) != tuple(shp):
@@ -110,6 +119,10 @@ class ParamStore(object):
         for name, t in self.stats.items():
             t.copy_(self.ops.to_device(np.asarray(z[names[name]], np.float32).reshape(-1)))
         if "__adam_m__" in z.files:
+            if int(np.asarray(z["__adam_m__"]).size) != self.n:
+                raise ValueError("training state %r holds Adam slots of %d elements, this store's flat layout has %d (written by a "
+                                 "version with a different variable alignment): resume from the variables only"
+                                 % (path, int(np.asarray(z["__adam_m__"]).size), self.n))
             self.m.copy_(self.ops.to_device(np.asarray(z["__adam_m__"], np.float32)))
             self.v.copy_(self.ops.to_device(np.asarray(z["__adam_v__"], np.float32)))
             return int(z["__global_step__"])
