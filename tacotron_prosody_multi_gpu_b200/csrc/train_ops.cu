@@ -3,6 +3,7 @@
 // for the per-channel statistics.  The attention step and the conv2d / GST kernels are in train_attn.cu.
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
 
 #include "../../include/taco_b200_train.h"
 #include "common.cuh"
@@ -193,6 +194,134 @@ __global__ void bn_moving_kernel(const float* mean, const float* rstd, float* mm
         mm[c] = mom * mm[c] + (1.f - mom) * mean[c];
         mv[c] = mom * mv[c] + (1.f - mom) * var;
     }
+}
+
+// ---- 16-byte variants (C % 4 == 0, 16-byte aligned tensors): a thread owns 4 adjacent channels, one Philox block serves its 4
+// dropout bits (train_keep draws element i from word i & 3 of block i >> 2), four rows in flight per thread in the reductions ----
+__device__ __forceinline__ uint4 keep_block4(uint64_t seed, uint32_t stream, unsigned long long i0) {   // i0 % 4 == 0
+    const unsigned long long blk = i0 >> 2;
+    return philox4x32_10(make_uint4((uint32_t)blk, stream, (uint32_t)(blk >> 32), 0x54524E31u), make_uint2((uint32_t)seed, (uint32_t)(seed >> 32)));
+}
+__device__ __forceinline__ float4 ld4(const float* p, long long i4) { return reinterpret_cast<const float4*>(p)[i4]; }
+__device__ __forceinline__ float dz1(float dy, float y, int act, bool kept, float keep) {
+    float da = dy, a = y;
+    if (keep < 1.f) {
+        if (!kept) return 0.f;
+        da = dy / keep;
+        a = y * keep;
+    }
+    if (act == TACO_ACT_RELU) return a > 0.f ? da : 0.f;
+    if (act == TACO_ACT_TANH) return da * (1.f - a * a);
+    return da;
+}
+__device__ __forceinline__ float4 bn_dz4(float4 dy, float4 y, int act, uint32_t thresh, float keep, uint64_t seed, uint32_t stream,
+                                         unsigned long long i0) {
+    uint4 o = make_uint4(0u, 0u, 0u, 0u);
+    if (keep < 1.f) o = keep_block4(seed, stream, i0);
+    return make_float4(dz1(dy.x, y.x, act, o.x < thresh, keep), dz1(dy.y, y.y, act, o.y < thresh, keep),
+                       dz1(dy.z, y.z, act, o.z < thresh, keep), dz1(dy.w, y.w, act, o.w < thresh, keep));
+}
+// block (32, 8): 32 channel quads x 8 row lanes; f(m, c4, a, b) accumulates into two float4
+template <class F>
+__device__ __forceinline__ void col_reduce_v4(int M, int C4, F f, float4& s0, float4& s1) {
+    const int c4 = blockIdx.x * 32 + threadIdx.x;
+    s0 = s1 = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (c4 < C4) {
+#pragma unroll 4
+        for (int m = blockIdx.y * blockDim.y + threadIdx.y; m < M; m += gridDim.y * blockDim.y) f(m, c4, s0, s1);
+    }
+    __shared__ float4 sh0[8][33], sh1[8][33];
+    sh0[threadIdx.y][threadIdx.x] = s0;
+    sh1[threadIdx.y][threadIdx.x] = s1;
+    __syncthreads();
+    if (threadIdx.y == 0) {
+        for (int i = 1; i < 8; ++i) {
+            const float4 a = sh0[i][threadIdx.x], b = sh1[i][threadIdx.x];
+            s0.x += a.x; s0.y += a.y; s0.z += a.z; s0.w += a.w;
+            s1.x += b.x; s1.y += b.y; s1.z += b.z; s1.w += b.w;
+        }
+    }
+}
+__device__ __forceinline__ void atomic_add4(float* p, float4 v) { atomicAdd(p, v.x); atomicAdd(p + 1, v.y); atomicAdd(p + 2, v.z); atomicAdd(p + 3, v.w); }
+
+__global__ void bn_sum_v4_kernel(const float* __restrict__ x, int M, int C4, float* sum) {
+    float4 s0, s1;
+    col_reduce_v4(M, C4, [&](int m, int c4, float4& a, float4&) {
+        const float4 v = ld4(x, (long long)m * C4 + c4);
+        a.x += v.x; a.y += v.y; a.z += v.z; a.w += v.w;
+    }, s0, s1);
+    const int c4 = blockIdx.x * 32 + threadIdx.x;
+    if (threadIdx.y == 0 && c4 < C4) atomic_add4(sum + 4 * c4, s0);
+}
+__global__ void bn_var_v4_kernel(const float* __restrict__ x, int M, int C4, const float* __restrict__ sum, float* sq) {
+    const float invM = 1.0f / (float)M;
+    const int c4q = blockIdx.x * 32 + threadIdx.x;
+    float4 mu = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (c4q < C4) { mu = ld4(sum, c4q); mu.x *= invM; mu.y *= invM; mu.z *= invM; mu.w *= invM; }
+    float4 s0, s1;
+    col_reduce_v4(M, C4, [&](int m, int c4, float4& a, float4&) {
+        const float4 v = ld4(x, (long long)m * C4 + c4);
+        const float d0 = v.x - mu.x, d1 = v.y - mu.y, d2 = v.z - mu.z, d3 = v.w - mu.w;
+        a.x += d0 * d0; a.y += d1 * d1; a.z += d2 * d2; a.w += d3 * d3;
+    }, s0, s1);
+    if (threadIdx.y == 0 && c4q < C4) atomic_add4(sq + 4 * c4q, s0);
+}
+__global__ void bn_apply_v4_kernel(const float* __restrict__ x, const float* __restrict__ gamma, const float* __restrict__ beta,
+                                   const float* __restrict__ mean, const float* __restrict__ rstd, int act, uint32_t thresh, float keep,
+                                   uint64_t seed, uint32_t stream, float* __restrict__ y, long long n4, int C4) {
+    const long long i4 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i4 >= n4) return;
+    const int c4 = (int)(i4 % C4);
+    const float4 v = ld4(x, i4), mu = ld4(mean, c4), rs = ld4(rstd, c4), ga = ld4(gamma, c4), be = ld4(beta, c4);
+    float4 a = make_float4(act_f((v.x - mu.x) * rs.x * ga.x + be.x, act), act_f((v.y - mu.y) * rs.y * ga.y + be.y, act),
+                           act_f((v.z - mu.z) * rs.z * ga.z + be.z, act), act_f((v.w - mu.w) * rs.w * ga.w + be.w, act));
+    if (keep < 1.f) {
+        const uint4 o = keep_block4(seed, stream, (unsigned long long)i4 * 4ull);
+        a.x = o.x < thresh ? a.x / keep : 0.f; a.y = o.y < thresh ? a.y / keep : 0.f;
+        a.z = o.z < thresh ? a.z / keep : 0.f; a.w = o.w < thresh ? a.w / keep : 0.f;
+    }
+    reinterpret_cast<float4*>(y)[i4] = a;
+}
+__global__ void bn_bwd_reduce_v4_kernel(const float* __restrict__ dy, const float* __restrict__ x, const float* __restrict__ y,
+                                        const float* __restrict__ mean, const float* __restrict__ rstd, int act, uint32_t thresh,
+                                        float keep, uint64_t seed, uint32_t stream, float* dgamma, float* dbeta, int M, int C4) {
+    const int c4q = blockIdx.x * 32 + threadIdx.x;
+    float4 mu = make_float4(0.f, 0.f, 0.f, 0.f), rs = mu;
+    if (c4q < C4) { mu = ld4(mean, c4q); rs = ld4(rstd, c4q); }
+    float4 s0, s1;
+    col_reduce_v4(M, C4, [&](int m, int c4, float4& a, float4& b) {
+        const long long i4 = (long long)m * C4 + c4;
+        const float4 xv = ld4(x, i4);
+        const float4 dz = bn_dz4(ld4(dy, i4), ld4(y, i4), act, thresh, keep, seed, stream, (unsigned long long)i4 * 4ull);
+        a.x += dz.x; a.y += dz.y; a.z += dz.z; a.w += dz.w;
+        b.x += dz.x * (xv.x - mu.x) * rs.x; b.y += dz.y * (xv.y - mu.y) * rs.y;
+        b.z += dz.z * (xv.z - mu.z) * rs.z; b.w += dz.w * (xv.w - mu.w) * rs.w;
+    }, s0, s1);
+    if (threadIdx.y == 0 && c4q < C4) { atomic_add4(dbeta + 4 * c4q, s0); atomic_add4(dgamma + 4 * c4q, s1); }
+}
+__global__ void bn_bwd_apply_v4_kernel(const float* __restrict__ dy, const float* __restrict__ x, const float* __restrict__ y,
+                                       const float* __restrict__ mean, const float* __restrict__ rstd, const float* __restrict__ gamma,
+                                       const float* __restrict__ dgamma, const float* __restrict__ dbeta, int act, uint32_t thresh,
+                                       float keep, uint64_t seed, uint32_t stream, float* __restrict__ dx, long long n4, int C4, float invM) {
+    const long long i4 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i4 >= n4) return;
+    const int c4 = (int)(i4 % C4);
+    const float4 dz = bn_dz4(ld4(dy, i4), ld4(y, i4), act, thresh, keep, seed, stream, (unsigned long long)i4 * 4ull);
+    const float4 xv = ld4(x, i4), mu = ld4(mean, c4), rs = ld4(rstd, c4), ga = ld4(gamma, c4), dg = ld4(dgamma, c4), db = ld4(dbeta, c4);
+    float4 o;
+    o.x = ga.x * rs.x * (dz.x - db.x * invM - (xv.x - mu.x) * rs.x * dg.x * invM);
+    o.y = ga.y * rs.y * (dz.y - db.y * invM - (xv.y - mu.y) * rs.y * dg.y * invM);
+    o.z = ga.z * rs.z * (dz.z - db.z * invM - (xv.z - mu.z) * rs.z * dg.z * invM);
+    o.w = ga.w * rs.w * (dz.w - db.w * invM - (xv.w - mu.w) * rs.w * dg.w * invM);
+    reinterpret_cast<float4*>(dx)[i4] = o;
+}
+inline bool al16p(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+const bool g_bn_vec = !getenv("TACO_TRAIN_BN_SCALAR");
+inline dim3 col_grid_v4(int M, int C4) {
+    int gx = (C4 + 31) / 32;
+    int gy = 1;
+    while (gx * gy < 592 && gy * 8 * 16 < M) gy *= 2;
+    return dim3(gx, gy);
 }
 
 inline dim3 col_grid(int M, int C) {
@@ -482,6 +611,15 @@ int taco_op_bn_fwd(const float* x, const float* gamma, const float* beta, int ac
     if (!x || !gamma || !beta || !y || !mean || !rstd || M < 1 || C < 1) return -1;
     ZERO(mean, C);
     ZERO(rstd, C);
+    if (g_bn_vec && C % 4 == 0 && al16p(x) && al16p(y) && al16p(gamma) && al16p(beta) && al16p(mean) && al16p(rstd)) {
+        const dim3 g4 = col_grid_v4(M, C / 4);
+        bn_sum_v4_kernel<<<g4, dim3(32, 8), 0, ST>>>(x, M, C / 4, mean);
+        bn_var_v4_kernel<<<g4, dim3(32, 8), 0, ST>>>(x, M, C / 4, mean, rstd);
+        bn_finish_kernel<<<nblk(C), 256, 0, ST>>>(mean, rstd, M, C);
+        const long long n4 = (long long)M * (C / 4);
+        bn_apply_v4_kernel<<<nblk(n4), 256, 0, ST>>>(x, gamma, beta, mean, rstd, act, keep_thresh, keep, seed, stream_id, y, n4, C / 4);
+        return rc();
+    }
     dim3 g = col_grid(M, C);
     bn_sum_kernel<<<g, dim3(32, 8), 0, ST>>>(x, M, C, mean);
     bn_var_kernel<<<g, dim3(32, 8), 0, ST>>>(x, M, C, mean, rstd);
@@ -496,6 +634,15 @@ int taco_op_bn_bwd(const float* dy, const float* x, const float* y, const float*
     if (!dy || !x || !y || !mean || !rstd || !gamma || !dx || !dgamma || !dbeta || M < 1 || C < 1) return -1;
     ZERO(dgamma, C);
     ZERO(dbeta, C);
+    if (g_bn_vec && C % 4 == 0 && al16p(dy) && al16p(x) && al16p(y) && al16p(dx) && al16p(gamma) && al16p(mean) && al16p(rstd) &&
+        al16p(dgamma) && al16p(dbeta)) {
+        bn_bwd_reduce_v4_kernel<<<col_grid_v4(M, C / 4), dim3(32, 8), 0, ST>>>(dy, x, y, mean, rstd, act, keep_thresh, keep, seed, stream_id,
+                                                                               dgamma, dbeta, M, C / 4);
+        const long long n4 = (long long)M * (C / 4);
+        bn_bwd_apply_v4_kernel<<<nblk(n4), 256, 0, ST>>>(dy, x, y, mean, rstd, gamma, dgamma, dbeta, act, keep_thresh, keep, seed,
+                                                         stream_id, dx, n4, C / 4, 1.0f / (float)M);
+        return rc();
+    }
     bn_bwd_reduce_kernel<<<col_grid(M, C), dim3(32, 8), 0, ST>>>(dy, x, y, mean, rstd, act, keep_thresh, keep, seed, stream_id,
                                                                   dgamma, dbeta, M, C);
     long long n = (long long)M * C;

@@ -82,9 +82,10 @@ def test_conv2d_fwd_dgrad_wgrad(ops, B, H, W, Ci, Co):
     both(ops, "conv2d_wgrad", [x, dy, torch.zeros(3, 3, Ci, Co)], atol=5e-4)
 
 
+@pytest.mark.parametrize("C", [96, 30], ids=["c96_16byte_kernels", "c30_scalar_kernels"])
 @pytest.mark.parametrize("act,keep", [(0, 1.0), (1, 0.5), (2, 0.5), (1, 1.0)])
-def test_bn_fwd_bwd_colsum(ops, act, keep):
-    M, C = 1234, 96
+def test_bn_fwd_bwd_colsum(ops, act, keep, C):
+    M = 1234
     x = R(M, C) * 2 + 0.5
     gamma, beta = R(C) * 0.1 + 1, R(C, seed=9) * 0.1
     ag, ac = both(ops, "bn_fwd", [x, gamma, beta, act, keep, 77, 105, torch.zeros(M, C), torch.zeros(C), torch.zeros(C)], atol=2e-5)
