@@ -131,6 +131,9 @@ int taco_op_attn_fwd_fused(const float* h2raw, const float* Wq, const float* U, 
 int taco_op_attn_bwd_fused(float* dctx, const float* carry, const float* dcum, const float* align, const float* th, const float* values,
                            const int32_t* lens, const float* U, const float* va, const float* Wq, float* de, float* dq, float* dh2,
                            float* dcum_prev, float* scratch /* >= B*T floats */, int B, int T, int D, int V, void* stream);
+/* d(values)[b,t,:] = sum_s align[s,b,t] d(ctx)[s,b,:] for all rows in one launch (align [S,B,T], dctx [S,B,V], dvalues [B,T,V]
+ * overwritten; V % 64 == 0, 16-byte aligned dctx / dvalues) -- the gradient of the context sums of all steps (Attention.py:208-210). */
+int taco_op_attn_dvalues(const float* align, const float* dctx, float* dvalues, int S, int B, int T, int V, void* stream);
 int taco_op_attn_bwd_hoisted(const float* de, const float* th, const float* cum, const int32_t* lens, const float* conv_w,
                              const float* conv_b, const float* Wl, const float* va, float* dkeys, float* g_conv_w, float* g_conv_b,
                              float* g_Wl, float* g_va, float* g_ba, float* work, int S, int B, int T, void* stream);

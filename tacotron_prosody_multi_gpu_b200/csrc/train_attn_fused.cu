@@ -529,6 +529,48 @@ __global__ void __launch_bounds__(AD) attn_fold_bwd_kernel(const float* __restri
     }
 }
 
+// d(values)[b,t,c] = sum_s align[s,b,t] d(ctx)[s,b,c]: one launch for all rows (it was one [T,S] x [S,V] GEMM per batch row).
+// grid (V / 64, ceil(T / 32), B), 256 threads: 32 positions x 64 columns per CTA, 2 x 4 outputs per thread, S in chunks of 32.
+__global__ void __launch_bounds__(256) attn_dvalues_kernel(const float* __restrict__ align, const float* __restrict__ dctx,
+                                                           float* __restrict__ dvalues, int S, int B, int T, int V) {
+    __shared__ float sA[32][33];
+    __shared__ __align__(16) float sB[32][68];
+    const int c0 = blockIdx.x * 64, t0 = blockIdx.y * 32, b = blockIdx.z, tid = threadIdx.x, ty = tid >> 4, tx = tid & 15;
+    float acc[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
+    for (int s0 = 0; s0 < S; s0 += 32) {
+        float ra[4];
+        float4 rb[2];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int e = tid + 256 * i, ss = s0 + (e >> 5), t = t0 + (e & 31);
+            ra[i] = (ss < S && t < T) ? align[((long long)ss * B + b) * T + t] : 0.f;
+        }
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+            const int e = tid + 256 * i, ss = s0 + (e >> 4);
+            rb[i] = ss < S ? *reinterpret_cast<const float4*>(dctx + ((long long)ss * B + b) * V + c0 + 4 * (e & 15)) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        __syncthreads();
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { const int e = tid + 256 * i; sA[e >> 5][e & 31] = ra[i]; }
+#pragma unroll
+        for (int i = 0; i < 2; ++i) { const int e = tid + 256 * i; *reinterpret_cast<float4*>(&sB[e >> 4][4 * (e & 15)]) = rb[i]; }
+        __syncthreads();
+#pragma unroll 8
+        for (int k = 0; k < 32; ++k) {
+            const float a0 = sA[k][2 * ty], a1 = sA[k][2 * ty + 1];
+            const float4 v = *reinterpret_cast<const float4*>(&sB[k][4 * tx]);
+            acc[0][0] = fmaf(a0, v.x, acc[0][0]); acc[0][1] = fmaf(a0, v.y, acc[0][1]); acc[0][2] = fmaf(a0, v.z, acc[0][2]); acc[0][3] = fmaf(a0, v.w, acc[0][3]);
+            acc[1][0] = fmaf(a1, v.x, acc[1][0]); acc[1][1] = fmaf(a1, v.y, acc[1][1]); acc[1][2] = fmaf(a1, v.z, acc[1][2]); acc[1][3] = fmaf(a1, v.w, acc[1][3]);
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+        const int t = t0 + 2 * ty + i;
+        if (t < T) *reinterpret_cast<float4*>(dvalues + ((long long)b * T + t) * V + c0 + 4 * tx) = make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
+    }
+}
+
 template <class K>
 inline bool ensure_smem(K kernel, size_t bytes) {
     return bytes <= 48 * 1024 || cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes) == cudaSuccess;
@@ -580,6 +622,13 @@ int taco_op_attn_bwd_fused(float* dctx, const float* carry, const float* dcum, c
     if (!ensure_smem(attn_bwd_row_kernel, sm)) return -3;
     launch_pdl(attn_bwd_row_kernel, dim3(CS, B), dim3(FT), sm, st, dctx, carry, dcum, values, align, th, lens, U, va, Wq, de, dq, dh2, dcum_prev,
                T, D, V, row_qmax(T));
+    return cudaGetLastError() == cudaSuccess ? 0 : -3;
+}
+
+int taco_op_attn_dvalues(const float* align, const float* dctx, float* dvalues, int S, int B, int T, int V, void* stream) {
+    if (!align || !dctx || !dvalues || S < 1 || B < 1 || T < 1 || V < 64 || V % 64 != 0) return -1;
+    if ((reinterpret_cast<uintptr_t>(dctx) & 15) || (reinterpret_cast<uintptr_t>(dvalues) & 15)) return -1;
+    attn_dvalues_kernel<<<dim3(V / 64, (T + 31) / 32, B), 256, 0, (cudaStream_t)stream>>>(align, dctx, dvalues, S, B, T, V);
     return cudaGetLastError() == cudaSuccess ? 0 : -3;
 }
 

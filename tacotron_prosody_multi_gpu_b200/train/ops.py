@@ -38,6 +38,7 @@ _SIGS = {
     "taco_op_attn_fwd_fused": [_P] * 15 + [_I] * 4 + [_P],
     "taco_op_attn_bwd_fused": [_P] * 15 + [_I] * 4 + [_P],
     "taco_op_attn_bwd_hoisted": [_P] * 15 + [_I] * 3 + [_P],
+    "taco_op_attn_dvalues": [_P] * 3 + [_I] * 4 + [_P],
     "taco_op_gru_pre": [_P, _P, _P, _I, _I, _P],
     "taco_op_gru_out": [_P, _P, _P, _P, _I, _I, _P],
     "taco_op_gru_out_bwd": [_P, _P, _P, _P, _P, _P, _P, _I, _I, _P],
@@ -262,6 +263,10 @@ class CudaOps(object):
         B, T, V = values.shape
         self._call("taco_op_attn_bwd_fused", _c(dctx), _c(carry), _c(dcum), _c(align), _c(th), _c(values), _c(lens), _c(U), _c(va), _c(Wq),
                    _c(de), _c(dq), _c(dh2), _c(dcum_prev), _c(self.empty(B * T)), B, T, dh2.shape[1], V)
+
+    def attn_dvalues(self, align, dctx, dvalues):
+        S, B, T = align.shape
+        self._call("taco_op_attn_dvalues", _c(align), _c(dctx), _c(dvalues), S, B, T, dctx.shape[2])
 
     def attn_bwd_hoisted(self, de, th, cum, lens, conv_w, conv_b, Wl, va, dkeys, g_conv_w, g_conv_b, g_Wl, g_va, g_ba):
         S, B, T = de.shape

@@ -449,8 +449,11 @@ class TrainStep(object):
             dc2, dc2n, dh2z, dh2zn = dc2n, dc2, dh2zn, dh2z
         # d(values)[b] = align[:, b, :]^T . d(ctx)[:, b, :]; keys = values . Wmem
         dvalues = o.empty(B, T, MD)
-        for b in range(B):
-            o.gemm(t["align"][:, b, :], dCtx[:, b, :], dvalues[b], ta=True)
+        if hasattr(o, "attn_dvalues") and MD % 64 == 0:
+            o.attn_dvalues(t["align"], dCtx, dvalues)              # all rows in one launch
+        else:
+            for b in range(B):
+                o.gemm(t["align"][:, b, :], dCtx[:, b, :], dvalues[b], ta=True)
         self._dense_bwd(values.view(B * T, MD), dkeys.view(B * T, A), W.MEMORY_LAYER + "/kernel", None,
                         dvalues.view(B * T, MD), beta=1.0)
         if hp.mask_encoder:

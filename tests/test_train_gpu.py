@@ -208,6 +208,17 @@ def test_fused_attention_of_the_time_loops_matches_the_op_by_op_kernels(ops, T, 
         np.testing.assert_allclose(a.cpu().numpy(), ref, atol=1e-4 * max(1.0, float(np.abs(ref).max())), rtol=1e-4, err_msg=name)
 
 
+@pytest.mark.parametrize("S,B,T,V", [(7, 3, 9, 64), (50, 4, 111, 768), (33, 2, 70, 128)])
+def test_attn_dvalues_matches_einsum(ops, S, B, T, V):
+    """d(values)[b,t,c] = sum_s align[s,b,t] d(ctx)[s,b,c] in one launch vs the fp64 contraction (fp32 accumulation over S)."""
+    cu, _ = ops
+    al, dc = torch.rand(S, B, T, generator=torch.Generator().manual_seed(3)), R(S, B, V, seed=5)
+    out = torch.full((B, T, V), float("nan")).cuda()
+    cu.attn_dvalues(al.cuda(), dc.cuda(), out)
+    ref = torch.einsum("sbt,sbc->btc", al.double(), dc.double()).numpy()
+    np.testing.assert_allclose(out.cpu().numpy(), ref, atol=2e-5 * max(1.0, float(np.abs(ref).max())), rtol=1e-5)
+
+
 def test_gru_gst_pointwise(ops):
     B, Rr = 6, 128
     g, h = R(B, 2 * Rr), R(B, Rr, seed=1)
