@@ -342,6 +342,30 @@ __global__ void prep_bf16_kernel(const float* __restrict__ in, float* __restrict
     out16[i] = __float2bfloat16_rn(v);
 }
 
+// the same with 16-byte loads / 8-byte stores: a thread converts 4 adjacent channels (C, Cpad, in_bstride multiples of 4, aligned
+// pointers, fewer than 2^31 channel quads)
+__global__ void prep_bf16_v4_kernel(const float* __restrict__ in, float* __restrict__ out32, __nv_bfloat16* __restrict__ out16,
+                                    unsigned n4, int F, long long in_bstride, int C4, int Cpad4, float lo, float hi, int clip) {
+    const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n4) return;
+    const unsigned bf = i / (unsigned)Cpad4, c4 = i - bf * (unsigned)Cpad4;
+    const unsigned b = bf / (unsigned)F, f = bf - b * (unsigned)F;
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if ((int)c4 < C4) {
+        v = *reinterpret_cast<const float4*>(in + (size_t)b * in_bstride + ((size_t)f * C4 + c4) * 4);
+        if (clip) {
+            v.x = fminf(fmaxf(v.x, lo), hi); v.y = fminf(fmaxf(v.y, lo), hi);
+            v.z = fminf(fmaxf(v.z, lo), hi); v.w = fminf(fmaxf(v.w, lo), hi);
+        }
+        if (out32) *reinterpret_cast<float4*>(out32 + ((size_t)bf * C4 + c4) * 4) = v;
+    }
+    const __nv_bfloat162 lo2 = __floats2bfloat162_rn(v.x, v.y), hi2 = __floats2bfloat162_rn(v.z, v.w);
+    uint2 w;
+    w.x = *reinterpret_cast<const uint32_t*>(&lo2);
+    w.y = *reinterpret_cast<const uint32_t*>(&hi2);
+    *reinterpret_cast<uint2*>(out16 + (size_t)i * 4) = w;
+}
+
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -379,6 +403,13 @@ cudaError_t launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const TcParam
 cudaError_t taco_launch_prep_bf16(const float* in, float* out32, void* out16, int B, int F, long long in_bstride, int C, int Cpad,
                                   float lo, float hi, int clip, cudaStream_t st) {
     size_t n = (size_t)B * F * Cpad;
+    if (C % 4 == 0 && Cpad % 4 == 0 && in_bstride % 4 == 0 && n / 4 < 0x7fffffffull && (reinterpret_cast<uintptr_t>(in) & 15) == 0 &&
+        (reinterpret_cast<uintptr_t>(out16) & 7) == 0 && (!out32 || (reinterpret_cast<uintptr_t>(out32) & 15) == 0)) {
+        const unsigned n4 = (unsigned)(n / 4);
+        prep_bf16_v4_kernel<<<(n4 + 255) / 256, 256, 0, st>>>(in, out32, reinterpret_cast<__nv_bfloat16*>(out16), n4, F, in_bstride, C / 4,
+                                                              Cpad / 4, lo, hi, clip);
+        return cudaGetLastError();
+    }
     prep_bf16_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(in, out32, reinterpret_cast<__nv_bfloat16*>(out16), B, F, in_bstride, C,
                                                                   Cpad, lo, hi, clip);
     return cudaGetLastError();
