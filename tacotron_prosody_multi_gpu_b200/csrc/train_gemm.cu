@@ -523,7 +523,9 @@ int launch_gemm_mma2(AL A, BL Bm, float* C, long long ldc, int M, int N, int K, 
     return cudaGetLastError() == cudaSuccess ? 0 : -3;
 }
 inline bool use_mma(int M, int N, int K) {
-    return g_train_precision == TACO_TRAIN_BF16 && (long long)M * N >= 64LL * 64 * 64 && (long long)M * N * K >= (1LL << 24);
+    if (g_train_precision != TACO_TRAIN_BF16) return false;
+    if ((long long)M * N >= 64LL * 64 * 64 && (long long)M * N * K >= (1LL << 24)) return true;
+    return M >= 128 && N >= 128 && K >= 4096;      // weight gradients of the narrow layers: few 128 x 128 tiles, split over K
 }
 
 
@@ -668,8 +670,10 @@ int launch_gemm(AL A, BL Bm, float* C, long long ldc, int M, int N, int K, float
         int kchunk = K;
         const int ctas = grid.x * grid.y;
         if ((beta == 0.f || beta == 1.f) && K >= 256 && ctas < 148) {
-            int splits = (296 + ctas - 1) / ctas;
-            if (splits > 8) splits = 8;
+            // weight gradients with few outputs and K = all rows of the batch (up to 160 000): as many K slices as fill the GPU twice
+            int splits = ((K >= 4096 ? 592 : 296) + ctas - 1) / ctas;
+            const int cap = K >= 4096 ? 128 : 8;
+            if (splits > cap) splits = cap;
             if (splits > K / 128) splits = K / 128;
             if (splits > 1) {
                 kchunk = ((K + splits - 1) / splits + 31) / 32 * 32;
@@ -679,6 +683,8 @@ int launch_gemm(AL A, BL Bm, float* C, long long ldc, int M, int N, int K, float
                     return -3;
             }
         }
+        static const bool log_small = getenv("TACO_TRAIN_GEMM_LOG") != nullptr;   // which contractions take the small-tile SIMT path
+        if (log_small) fprintf(stderr, "[taco gemm32] M=%d N=%d K=%d splits=%u\n", M, N, K, grid.z);
         gemm_kernel<32, 32, 32, 2, 2, AL, BL><<<grid, 256, 0, st>>>(A, Bm, C, ldc, M, N, K, beta, bias, kchunk);
     }
     return cudaGetLastError() == cudaSuccess ? 0 : -3;
