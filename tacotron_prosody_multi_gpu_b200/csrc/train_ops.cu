@@ -603,6 +603,10 @@ int taco_op_colsum(const float* x, long long ld, int M, int C, float* out, float
     if (!x || !out || M < 1 || C < 1) return -1;
     if (beta == 0.f) { ZERO(out, C); }
     else if (beta != 1.f) { scale_kernel<<<nblk(C), 256, 0, ST>>>(out, beta, C); }
+    if (g_bn_vec && ld == C && C % 4 == 0 && al16p(x) && al16p(out)) {      // dense rows: the 16-byte column-sum kernel of the batch norm
+        bn_sum_v4_kernel<<<col_grid_v4(M, C / 4), dim3(32, 8), 0, ST>>>(x, M, C / 4, out);
+        return rc();
+    }
     colsum_kernel<<<col_grid(M, C), dim3(32, 8), 0, ST>>>(x, ld, M, C, out);
     return rc();
 }
