@@ -9,11 +9,11 @@
 //            tanh(pre) [T,128] for the backward pass; the partial energies go to all 4 CTAs through distributed shared
 //            memory; then every CTA does the masked softmax + cumulative update and its 192 columns of the context
 //   backward ONE launch, grid (4, B), clusters of the 4 CTAs of a row: d(align) = values . (d(ctx) + carry) + d(cum) of a
-//            quarter of the positions (partial sums of the softmax gradient exchanged through distributed shared memory),
-//            d(pre) and the tap gradients of that
-//            quarter of the positions (4x4 register tiles over the shared-memory d(pre) tile), d(q) -> d(h2raw) += d(q) Wq^T,
-//            d(cum_{t-1}) through the folded filter bank (halo rows read from the neighbours' shared memory); saves
-//            d(energy) [T] per step
+//            quarter of the positions, d(pre) and the tap gradients of that quarter (4x4 register tiles over the shared-memory
+//            d(pre) tile), d(q) -> d(h2raw) += d(q) Wq^T, d(cum_{t-1}) through the folded filter bank; saves d(energy) [T] per
+//            step.  Three cluster barriers: start, ONE exchange of the partial sums of the softmax gradient and of d(q)
+//            (d(q) = v_a (S1 - dot S2) with S1, S2 computable before dot is known), and one after every CTA has PUSHED its
+//            tap-gradient rows into the halo buffers of the CTAs that need them
 //   hoisted  after the loop, grid (T/8, B) looping over all S steps: d(keys), d(U), d(c0), d(v_a) from the saved d(energy)
 //            and tanh(pre); then d(conv_w), d(conv_b), d(Wl), d(b_a) from d(U), d(c0) by the chain rule of the fold
 #include <cooperative_groups.h>
@@ -217,11 +217,12 @@ __global__ void __cluster_dims__(CS, 1, 1) __launch_bounds__(FT, 1) attn_bwd_row
     const int Tp = (T + 3) & ~3;
     float* s_dpre = smem;                         // [Qmax][RS]   d(pre) rows of this quarter
     float* s_U = s_dpre + (size_t)Qmax * RS;      // [32][RS], row 31 = 0
-    float* s_G = s_U + 32 * RS;                   // [Qmax][GS]: G[t][j] = sum_d dpre[t,d] U[j,d]
-    float* s_de = s_G + (size_t)Qmax * GS;        // [Tp]
-    float* s_dq = s_de + Tp;                      // [4][AD] partials of this CTA -> [AD] total
-    float* s_dqx = s_dq + 4 * AD;                 // [CS][AD] partial d(q) of every CTA of the row
-    float* s_red = s_dqx + CS * AD;               // [32]
+    float* s_H = s_U + 32 * RS;                   // [Qmax + 30][GS]: G[t][j] = sum_d dpre[t,d] U[j,d] of positions t_lo - 15 ... (own rows + halo)
+    float* s_de = s_H + (size_t)(Qmax + 32) * GS; // [Tp]   (Qmax + 32 rows: keeps the float4 regions below 16-byte aligned)
+    float* s_al = s_de + Tp;                      // [Tp] alignments of the row
+    float* s_dq = s_al + Tp;                      // [2][4][AD] partial sums S1, S2 of this CTA's thread groups -> [AD] d(q)
+    float* s_dqx = s_dq + 8 * AD;                 // [2][CS][AD] S1, S2 of every CTA of the row
+    float* s_red = s_dqx + 2 * CS * AD;           // [32]
     float* s_dot = s_red + 32;                    // [CS] partial sums of a . d(align)
     float* s_dctx = s_dot + CS;                   // [V] d(ctx) + carry
     const int cs = blockIdx.x, b = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -245,6 +246,7 @@ __global__ void __cluster_dims__(CS, 1, 1) __launch_bounds__(FT, 1) attn_bwd_row
     for (int k = 0; k < 6; ++k)
         v0[k] = (warp < nvalid && lane + 32 * k < V4) ? val4[(long long)(t_lo + warp) * V4 + lane + 32 * k] : make_float4(0.f, 0.f, 0.f, 0.f);
     for (int i = tid; i < 32 * AD; i += FT) s_U[(i >> 7) * RS + (i & 127)] = (i >> 7) < KW ? U[i] : 0.f;
+    for (int t = tid; t < Tp; t += FT) s_al[t] = t < len ? align[(long long)b * T + t] : 0.f;
     pdl_wait();                                  // everything above reads tensors of the forward pass; below: this step's gradients
     pdl_launch_dependents();
     for (int i = tid; i < V; i += FT) s_dctx[i] = dctx[(long long)b * V + i] + carry[(long long)b * V + i];
@@ -273,60 +275,66 @@ __global__ void __cluster_dims__(CS, 1, 1) __launch_bounds__(FT, 1) attn_bwd_row
                 acc = fmaf(v.x, g4.x, acc); acc = fmaf(v.y, g4.y, acc); acc = fmaf(v.z, g4.z, acc); acc = fmaf(v.w, g4.w, acc);
             }
             acc = warp_sum(acc) + dcum[(long long)b * T + t];
-            part = fmaf(align[(long long)b * T + t], acc, part);
+            part = fmaf(s_al[t], acc, part);
         }
         if (lane == 0) s_de[t] = acc;            // d(align) for now; 0 on the padding rows
     }
-    part = block_reduce(lane == 0 ? part : 0.f, s_red, false);
-    if (tid < CS) cl.map_shared_rank(s_dot, tid)[cs] = part;
-    cl.sync();                                   // the 4 partial sums are everywhere
+    part = block_reduce(lane == 0 ? part : 0.f, s_red, false);      // (its barriers also publish s_de = d(align) of the quarter)
+    // ONE exchange for the softmax gradient and d(q):  d(e)[t] = a[t] (d(a)[t] - dot),  dot = sum_t a[t] d(a)[t]  and
+    // d(q)[d] = v_a[d] sum_t d(e)[t] (1 - th[t,d]^2) = v_a[d] (S1[d] - dot S2[d])  with  S1 = sum_t a d(a) (1 - th^2),
+    // S2 = sum_t a (1 - th^2): both sums are available BEFORE dot is known, so the partial (dot, S1, S2) of the 4 CTAs cross the
+    // cluster together
+    const float vad = va[d];
+    {
+        float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+        for (int i = 0; i < XT; ++i) {
+            const int r = g + 4 * i;
+            if (r < nq) {
+                const float w = s_al[t_lo + r] * (1.f - x[i] * x[i]);          // 0 beyond the length: a = 0
+                s2 += w;
+                s1 = fmaf(w, s_de[t_lo + r], s1);
+            }
+        }
+        for (int r = g + 4 * XT; r < nvalid; r += 4) {                          // quarters longer than 128 positions
+            const float xv = th[((long long)b * T + t_lo + r) * AD + d];
+            const float w = s_al[t_lo + r] * (1.f - xv * xv);
+            s2 += w;
+            s1 = fmaf(w, s_de[t_lo + r], s1);
+        }
+        s_dq[g * AD + d] = s1;
+        s_dq[(4 + g) * AD + d] = s2;
+    }
+    __syncthreads();
+    if (tid < 2 * AD) {
+        const int which = tid >> 7, dd = tid & (AD - 1);
+        const float* src = s_dq + which * 4 * AD + dd;
+        const float v = src[0] + src[AD] + src[2 * AD] + src[3 * AD];
+#pragma unroll
+        for (int r = 0; r < CS; ++r) cl.map_shared_rank(s_dqx, r)[(which * CS + cs) * AD + dd] = v;
+    } else if (tid < 2 * AD + CS) {
+        cl.map_shared_rank(s_dot, tid - 2 * AD)[cs] = part;
+    }
+    cl.sync();                                   // the partial sums of all 4 CTAs are everywhere
     const float dot = s_dot[0] + s_dot[1] + s_dot[2] + s_dot[3];
+    if (tid < AD) {
+        float S1 = 0.f, S2 = 0.f;
+#pragma unroll
+        for (int r = 0; r < CS; ++r) { S1 += s_dqx[r * AD + tid]; S2 += s_dqx[(CS + r) * AD + tid]; }
+        const float v = va[tid] * (S1 - dot * S2);
+        s_dq[tid] = v;                           // (the partials in s_dq were consumed before the cluster barrier)
+        if (cs == 0) dq_out[(long long)b * AD + tid] = v;
+    }
     for (int r = tid; r < nq; r += FT) {         // d(energy) = a (d(align) - sum a d(align)); 0 beyond the length
         const int t = t_lo + r;
-        const float v = r < nvalid ? align[(long long)b * T + t] * (s_de[t] - dot) : 0.f;
+        const float v = s_al[t] * (s_de[t] - dot);
         s_de[t] = v;
         if (t < T) de_out[(long long)b * T + t] = v;
     }
     if (cs == CS - 1)
         for (int t = CS * Q + tid; t < T; t += FT) de_out[(long long)b * T + t] = 0.f;
-    __syncthreads();
-    {   // d(pre)[t,d] = d(e)[t] v_a[d] (1 - tanh^2); column sums -> partial d(q)
-        const float vad = va[d];
-        float csum = 0.f;
-#pragma unroll
-        for (int i = 0; i < XT; ++i) {
-            const int r = g + 4 * i;
-            if (r < nq) {
-                const float dp = s_de[t_lo + r] * vad * (1.f - x[i] * x[i]);     // 0 beyond the length: s_de = 0
-                s_dpre[r * RS + d] = dp;
-                csum += dp;
-            }
-        }
-        for (int r = g + 4 * XT; r < nq; r += 4) {                               // quarters longer than 128 positions
-            const int t = t_lo + r;
-            float dp = 0.f;
-            if (t < len) { const float xv = th[((long long)b * T + t) * AD + d]; dp = s_de[t] * vad * (1.f - xv * xv); }
-            s_dpre[r * RS + d] = dp;
-            csum += dp;
-        }
-        s_dq[g * AD + d] = csum;
-    }
-    __syncthreads();
-    if (tid < AD) {
-        const float v = s_dq[tid] + s_dq[AD + tid] + s_dq[2 * AD + tid] + s_dq[3 * AD + tid];
-#pragma unroll
-        for (int r = 0; r < CS; ++r) cl.map_shared_rank(s_dqx, r)[cs * AD + tid] = v;
-    }
-    cl.sync();                                   // partial d(q) of all 4 CTAs have arrived
-    if (tid < AD) {
-        float v = 0.f;
-#pragma unroll
-        for (int r = 0; r < CS; ++r) v += s_dqx[r * AD + tid];
-        s_dq[tid] = v;
-        if (cs == 0) dq_out[(long long)b * AD + tid] = v;
-    }
-    // d(h2raw)[k] += sum_d d(q)[d] Wq[k,d] for this CTA's quarter of the units, one warp per k (Wq is a view into the flat
-    // parameter buffer: 4-byte aligned only).  The loads are issued here; the products are finished after the G tiles.
+    // d(h2raw)[k] += sum_d d(q)[d] Wq[k,d] for this CTA's quarter of the units, one warp per k.  The loads are issued here; the
+    // products are finished after the G tiles.
     const int kq = (D + CS - 1) / CS, k_end = min(D, (cs + 1) * kq), k0w = cs * kq + warp * 4;
     float wv[4][4], dh_old = 0.f;
 #pragma unroll
@@ -334,8 +342,27 @@ __global__ void __cluster_dims__(CS, 1, 1) __launch_bounds__(FT, 1) attn_bwd_row
 #pragma unroll
         for (int c = 0; c < 4; ++c) wv[i][c] = (k0w + i < k_end) ? Wq[(long long)(k0w + i) * AD + lane + 32 * c] : 0.f;
     if (lane < 4 && k0w + lane < k_end) dh_old = dh2[(long long)b * D + k0w + lane];
+    __syncthreads();
+    // d(pre)[t,d] = d(e)[t] v_a[d] (1 - tanh^2)
+#pragma unroll
+    for (int i = 0; i < XT; ++i) {
+        const int r = g + 4 * i;
+        if (r < nq) s_dpre[r * RS + d] = s_de[t_lo + r] * vad * (1.f - x[i] * x[i]);     // 0 beyond the length: s_de = 0
+    }
+    for (int r = g + 4 * XT; r < nq; r += 4) {
+        const int t = t_lo + r;
+        float dp = 0.f;
+        if (t < len) { const float xv = th[((long long)b * T + t) * AD + d]; dp = s_de[t] * vad * (1.f - xv * xv); }
+        s_dpre[r * RS + d] = dp;
+    }
+    __syncthreads();
     // G tiles of this quarter: 4 positions x 4 taps (taps jt, jt+8, jt+16, jt+24) x one eighth of d per work item; the 8
-    // d-parts of a tile sit in 8 adjacent lanes (interleaved 16-byte columns: conflict-free loads) and combine by shuffles
+    // d-parts of a tile sit in 8 adjacent lanes (interleaved 16-byte columns: conflict-free loads) and combine by shuffles.
+    // A finished G row goes to every CTA whose d(cum) positions reach it (its own rows +- 15): pushed, so that nobody reads
+    // remote shared memory after the last cluster barrier.
+    const int hc = tid & (CS - 1);               // lanes 0..3 of a tile's 8 lanes serve CTA 0..3 (p8 = tid & 7 below)
+    float* Hc = cl.map_shared_rank(s_H, hc);
+    const int h_lo = hc * Q - LEFT, h_hi = (hc == CS - 1) ? lenp : min(lenp, hc * Q + Q + LEFT);
     const int nitems = (nq >> 2) * 64;           // a multiple of 64: whole warps in or out
     for (int it = tid; it < nitems; it += FT) {
         const int p8 = it & 7, jt = (it >> 3) & 7, tt = it >> 6;
@@ -362,18 +389,19 @@ __global__ void __cluster_dims__(CS, 1, 1) __launch_bounds__(FT, 1) attn_bwd_row
                 }
         }
 #pragma unroll
-        for (int i = 0; i < 4; ++i)
+        for (int i = 0; i < 4; ++i) {
+            const int t = t_lo + tt * 4 + i;
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
                 float a = acc[i][k];
                 a += __shfl_xor_sync(0xffffffffu, a, 1);
                 a += __shfl_xor_sync(0xffffffffu, a, 2);
                 a += __shfl_xor_sync(0xffffffffu, a, 4);
-                if (p8 == 0) s_G[(size_t)(tt * 4 + i) * GS + jt + 8 * k] = a;
+                if (p8 < CS && t >= h_lo && t < h_hi && jt + 8 * k < KW) Hc[(size_t)(t - h_lo) * GS + jt + 8 * k] = a;
             }
+        }
     }
-    {   // finish d(h2raw) (s_dq was written before the G tiles by the first 128 threads: the barrier below orders it)
-        __syncthreads();
+    {   // finish d(h2raw)
         float dqr[4];
 #pragma unroll
         for (int i = 0; i < 4; ++i) dqr[i] = s_dq[lane + 32 * i];
@@ -395,28 +423,19 @@ __global__ void __cluster_dims__(CS, 1, 1) __launch_bounds__(FT, 1) attn_bwd_row
             }
         }
     }
-    cl.sync();                                   // all G rows of the row are complete
-    // d(cum_{t-1})[tp] = d(cum_t)[tp] + sum_j G[tp - j + LEFT][j]   (pre[t] reads cum[t + j - LEFT]); the G row of position t
-    // lives in the CTA that owns t.  CTA cs takes the tp of its quarter, the last one also everything beyond 4 Q; one warp per
-    // tp, lane = tap: one (possibly remote) shared-memory load per lane, then a warp sum.
+    cl.sync();                                   // all G rows (own and halo) of every CTA are in place; no remote access after this
+    // d(cum_{t-1})[tp] = d(cum_t)[tp] + sum_j G[tp - j + LEFT][j]   (pre[t] reads cum[t + j - LEFT]).  CTA cs takes the tp of its
+    // quarter, the last one also everything beyond 4 Q; one warp per tp, lane = tap, then a warp sum.
     {
         const int tp_hi = (cs == CS - 1) ? T : min(T, t_lo + Q);
-        const float* Gr[CS];
-#pragma unroll
-        for (int r = 0; r < CS; ++r) Gr[r] = cl.map_shared_rank(s_G, r);
         for (int tp = t_lo + warp; tp < tp_hi; tp += FT / 32) {
             const int t = tp - lane + LEFT;
             float a = 0.f;
-            if (lane < KW && t >= 0 && t < len) {
-                const int o = t / Q, r = t - o * Q;
-                const float* Go = o == 0 ? Gr[0] : o == 1 ? Gr[1] : o == 2 ? Gr[2] : Gr[3];
-                a = Go[r * GS + lane];
-            }
+            if (lane < KW && t >= 0 && t < len) a = s_H[(size_t)(t - (t_lo - LEFT)) * GS + lane];
             a = warp_sum(a);
             if (lane == 0) dcum_prev[(long long)b * T + tp] = a + dcum[(long long)b * T + tp];
         }
     }
-    cl.sync();                                   // no CTA leaves while a neighbour may still read its G rows
 }
 
 // ------------------------------------------------------------------------------------------------ backward, hoisted
@@ -582,7 +601,7 @@ inline size_t fwd_smem(int T, int D, int V) {
 inline int row_qmax(int T) { return ((((T + 3) >> 2) + CS - 1) / CS) * 4; }     // positions per CTA of the row kernel at len = T
 inline size_t row_smem(int T, int V) {
     const int Tp = (T + 3) & ~3, Q = row_qmax(T);
-    return sizeof(float) * ((size_t)Q * RS + 32 * RS + (size_t)Q * GS + Tp + 4 * AD + CS * AD + 32 + CS + V);
+    return sizeof(float) * ((size_t)Q * RS + 32 * RS + (size_t)(Q + 32) * GS + 2 * Tp + 8 * AD + 2 * CS * AD + 32 + CS + V);
 }
 
 }  // namespace
