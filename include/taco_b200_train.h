@@ -81,6 +81,19 @@ int taco_op_lstm_bwd(const float* acts, const float* c_prev, const float* h_prev
                      int B, int H, void* stream);
 /* bidirectional_dynamic_rnn position bookkeeping: pos_b = s (forward) or len_b-1-s (reverse), valid iff s < len_b.
  * gather: out[b,:] = src[b,pos_b,:] (0 for invalid rows); scatter: dst[b,pos_b,:] = src[b,:] for valid rows. */
+/* The same two kernels for the encoder time loops with the sequence gather / scatter fused in (Encoder.py:118-142 over the valid
+ * length): forward adds row pos of xw [B,T,4H] (strides xw_sb, xw_st; pos = s, or len - 1 - s when reverse) to the gates and
+ * writes the raw output to out[b,pos,:H]; backward reads d(raw output) from dout[b,pos,:H] and also writes d(gates) to
+ * dxw[b,pos,:4H].  Rows with s >= len: state carried through, nothing scattered. */
+int taco_op_lstm_fwd_seq(float* gates, const float* xw, long long xw_sb, long long xw_st, const float* c_prev, const float* h_prev,
+                         const int32_t* lens, int s, int reverse, float zoneout, int train, uint32_t zo_keep_thresh, uint64_t seed,
+                         uint32_t stream_c, uint32_t stream_h, int row0, float* cnew, float* cz, float* hraw, float* hz, float* out,
+                         long long out_sb, long long out_st, int B, int H, void* stream);
+int taco_op_lstm_bwd_seq(const float* acts, const float* c_prev, const float* h_prev, const float* cnew, const int32_t* lens, int s,
+                         int reverse, float zoneout, int train, uint32_t zo_keep_thresh, uint64_t seed, uint32_t stream_c, uint32_t stream_h,
+                         int row0, const float* dout, long long dout_sb, long long dout_st, const float* d_cz, const float* d_hz,
+                         float* dgates, float* d_cprev, float* d_hprev, float* dxw, long long dxw_sb, long long dxw_st, int B, int H,
+                         void* stream);
 int taco_op_gather_rows(const float* src, long long sb, long long st, const int32_t* lens, int s, int reverse, float* out,
                         int B, int N, void* stream);
 int taco_op_scatter_rows(const float* src, const int32_t* lens, int s, int reverse, float* dst, long long db, long long dt,

@@ -123,11 +123,12 @@ int taco_op_lstm_loop_fwd(const TacoLstmLoop* p, void* st) {
     for (int s = 0; s < T; ++s) {
         const size_t oH = (size_t)s * B * H, nH = oH + (size_t)B * H;
         float* a = p->acts + (size_t)s * B * G;
-        OK(taco_op_gather_rows(p->xw, (long long)T * G, G, p->lens, s, p->reverse, pre, B, G, st));
+        // 2 launches per position: recurrent contraction, then the pointwise step with the gather of the input-projection row and
+        // the scatter of the raw output fused in
         OK(taco_op_gemm_acc(p->hz + oH, H, Kh, G, a, G, B, G, H, 0, st));
-        OK(taco_op_lstm_fwd(a, pre, nullptr, p->cz + oH, p->hz + oH, p->lens, s, p->zoneout, 1, p->zo_keep_thresh, p->seed, p->stream_c,
-                            p->stream_h, s * B, p->cnew + oH, p->cz + nH, hraw, p->hz + nH, B, H, st));
-        OK(taco_op_scatter_rows(hraw, p->lens, s, p->reverse, p->out, p->out_sb, p->out_st, B, H, st));
+        OK(taco_op_lstm_fwd_seq(a, p->xw, (long long)T * G, G, p->cz + oH, p->hz + oH, p->lens, s, p->reverse, p->zoneout, 1, p->zo_keep_thresh,
+                                p->seed, p->stream_c, p->stream_h, s * B, p->cnew + oH, p->cz + nH, hraw, p->hz + nH, p->out, p->out_sb,
+                                p->out_st, B, H, st));
     }
     return 0;
 }
@@ -142,11 +143,10 @@ int taco_op_lstm_loop_bwd(const TacoLstmLoop* p, void* st) {
     for (int s = T - 1; s >= 0; --s) {
         const size_t oH = (size_t)s * B * H;
         float* dg = p->dg + (size_t)s * B * G;
-        OK(taco_op_gather_rows(p->out, p->out_sb, p->out_st, p->lens, s, p->reverse, d_hraw, B, H, st));
-        OK(taco_op_lstm_bwd(p->acts + (size_t)s * B * G, p->cz + oH, p->hz + oH, p->cnew + oH, p->lens, s, p->zoneout, 1, p->zo_keep_thresh,
-                            p->seed, p->stream_c, p->stream_h, s * B, d_hraw, dc, dh, dg, dcn, dhn, B, H, st));
+        OK(taco_op_lstm_bwd_seq(p->acts + (size_t)s * B * G, p->cz + oH, p->hz + oH, p->cnew + oH, p->lens, s, p->reverse, p->zoneout, 1,
+                                p->zo_keep_thresh, p->seed, p->stream_c, p->stream_h, s * B, p->out, p->out_sb, p->out_st, dc, dh, dg, dcn, dhn,
+                                p->dxw, (long long)T * G, G, B, H, st));
         OK(taco_op_gemm_acc(dg, G, Kh, G, dhn, H, B, H, G, 1, st));
-        OK(taco_op_scatter_rows(dg, p->lens, s, p->reverse, p->dxw, (long long)T * G, G, B, G, st));
         float* t_;
         t_ = dc; dc = dcn; dcn = t_;
         t_ = dh; dh = dhn; dhn = t_;

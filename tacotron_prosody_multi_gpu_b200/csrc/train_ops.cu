@@ -336,14 +336,24 @@ inline dim3 col_grid(int M, int C) {
 namespace {
 
 // ---------------------------------------------------------------------------------------------- LSTM / zoneout
+// optional sequence I/O of the encoder time loops fused into the pointwise kernels: gather of the step's input row from
+// [B, T, .] at position s (or len - 1 - s) and scatter of the step's output row to it -- valid rows (s < len) only
+struct SeqIO {
+    const float* gsrc; long long gsb, gst;
+    float* sdst; long long ssb, sst;
+    int reverse;
+};
 __global__ void lstm_fwd_kernel(float* __restrict__ gates, const float* __restrict__ pre, const float* __restrict__ bias,
                                 const float* __restrict__ c_prev, const float* __restrict__ h_prev, const int32_t* __restrict__ lens,
                                 int s, float zoneout, int train, uint64_t seed, uint32_t sc, uint32_t sh, int row0, uint32_t thresh,
                                 float* __restrict__ cnew, float* __restrict__ cz, float* __restrict__ hraw, float* __restrict__ hz,
-                                int B, int H) {
+                                int B, int H, SeqIO io) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= B * H) return;
     int b = i / H, u = i - b * H;
+    const int len_b = lens ? lens[b] : 0x7fffffff;
+    const bool valid = s < len_b;
+    const long long pos = (io.reverse && lens) ? (long long)len_b - 1 - s : s;
     float mc, mh;                                  // zoneout masks: counter-based, computed under the predecessor's tail
     if (train) {
         unsigned long long idx = (unsigned long long)(row0 + b) * H + u;
@@ -360,6 +370,7 @@ __global__ void lstm_fwd_kernel(float* __restrict__ gates, const float* __restri
         long long k = (long long)b * 4 * H + g * H + u;
         float v = gates[k];
         if (pre) v += pre[k];
+        if (io.gsrc && valid) v += io.gsrc[(long long)b * io.gsb + pos * io.gst + g * H + u];   // the gathered row of the input projection
         if (bias) v += bias[g * H + u];
         z[g] = v;
     }
@@ -370,19 +381,22 @@ __global__ void lstm_fwd_kernel(float* __restrict__ gates, const float* __restri
     float cn = sf * cp + si * tj;
     float hr = so * tanhf(cn);
     float czv = cp + mc * (cn - cp), hzv = hp + mh * (hr - hp);
-    if (lens && s >= lens[b]) { czv = cp; hzv = hp; hr = 0.f; }
+    if (!valid) { czv = cp; hzv = hp; hr = 0.f; }
     cnew[i] = cn; cz[i] = czv; hraw[i] = hr; hz[i] = hzv;
+    if (io.sdst && valid) io.sdst[(long long)b * io.ssb + pos * io.sst + u] = hr;               // scattered to its sequence position
 }
 
 __global__ void lstm_bwd_kernel(const float* __restrict__ acts, const float* __restrict__ c_prev, const float* __restrict__ h_prev,
                                 const float* __restrict__ cnew, const int32_t* __restrict__ lens, int s, float zoneout, int train,
                                 uint64_t seed, uint32_t sc, uint32_t sh, int row0, uint32_t thresh, const float* __restrict__ d_hraw,
                                 const float* __restrict__ d_cz, const float* __restrict__ d_hz, float* __restrict__ dgates,
-                                float* __restrict__ d_cprev, float* __restrict__ d_hprev, int B, int H) {
+                                float* __restrict__ d_cprev, float* __restrict__ d_hprev, int B, int H, SeqIO io) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= B * H) return;
     int b = i / H, u = i - b * H;
     long long k0 = (long long)b * 4 * H + u;
+    const int len_b = lens ? lens[b] : 0x7fffffff;
+    const long long pos = (io.reverse && lens) ? (long long)len_b - 1 - s : s;
     float mc, mh;
     if (train) {
         unsigned long long idx = (unsigned long long)(row0 + b) * H + u;
@@ -402,14 +416,18 @@ __global__ void lstm_bwd_kernel(const float* __restrict__ acts, const float* __r
     float si = acts[k0], tj = acts[k0 + H], sf = acts[k0 + 2 * H], so = acts[k0 + 3 * H];
     float tc = tanhf(cnew[i]);
     float dhz = d_hz[i], dcz = d_cz[i];
-    float dh_new = d_hraw[i] + mh * dhz;
+    const float dhr = io.gsrc ? io.gsrc[(long long)b * io.gsb + pos * io.gst + u] : d_hraw[i];   // valid row (invalid ones returned above)
+    float dh_new = dhr + mh * dhz;
     d_hprev[i] = (1.f - mh) * dhz;
     float dc_new = mc * dcz + dh_new * so * (1.f - tc * tc);
     d_cprev[i] = (1.f - mc) * dcz + dc_new * sf;
-    dgates[k0] = dc_new * tj * si * (1.f - si);
-    dgates[k0 + H] = dc_new * si * (1.f - tj * tj);
-    dgates[k0 + 2 * H] = dc_new * c_prev[i] * sf * (1.f - sf);
-    dgates[k0 + 3 * H] = dh_new * tc * so * (1.f - so);
+    const float g0 = dc_new * tj * si * (1.f - si), g1 = dc_new * si * (1.f - tj * tj), g2 = dc_new * c_prev[i] * sf * (1.f - sf),
+                g3 = dh_new * tc * so * (1.f - so);
+    dgates[k0] = g0; dgates[k0 + H] = g1; dgates[k0 + 2 * H] = g2; dgates[k0 + 3 * H] = g3;
+    if (io.sdst) {                                // d(input projection) row at its sequence position
+        float* o = io.sdst + (long long)b * io.ssb + pos * io.sst + u;
+        o[0] = g0; o[H] = g1; o[2 * H] = g2; o[3 * H] = g3;
+    }
 }
 
 __global__ void gather_rows_kernel(const float* __restrict__ src, long long sb, long long st, const int32_t* __restrict__ lens, int s,
@@ -664,7 +682,16 @@ int taco_op_lstm_fwd(float* gates, const float* pre, const float* bias, const fl
                      uint32_t stream_h, int row0, float* cnew, float* cz, float* hraw, float* hz, int B, int H, void* stream) {
     if (!gates || !c_prev || !h_prev || !cnew || !cz || !hraw || !hz || B < 1 || H < 1) return -1;
     launch_pdl(lstm_fwd_kernel, dim3(nblk((long long)B * H)), dim3(256), 0, ST, gates, pre, bias, c_prev, h_prev, lens, s, zoneout, train, seed, stream_c,
-                                                            stream_h, row0, zo_keep_thresh, cnew, cz, hraw, hz, B, H);
+                                                            stream_h, row0, zo_keep_thresh, cnew, cz, hraw, hz, B, H, SeqIO{nullptr, 0, 0, nullptr, 0, 0, 0});
+    return rc();
+}
+int taco_op_lstm_fwd_seq(float* gates, const float* xw, long long xw_sb, long long xw_st, const float* c_prev, const float* h_prev,
+                         const int32_t* lens, int s, int reverse, float zoneout, int train, uint32_t zo_keep_thresh, uint64_t seed,
+                         uint32_t stream_c, uint32_t stream_h, int row0, float* cnew, float* cz, float* hraw, float* hz, float* out,
+                         long long out_sb, long long out_st, int B, int H, void* stream) {
+    if (!gates || !xw || !c_prev || !h_prev || !lens || !cnew || !cz || !hraw || !hz || !out || B < 1 || H < 1) return -1;
+    launch_pdl(lstm_fwd_kernel, dim3(nblk((long long)B * H)), dim3(256), 0, ST, gates, (const float*)nullptr, (const float*)nullptr, c_prev, h_prev, lens, s,
+               zoneout, train, seed, stream_c, stream_h, row0, zo_keep_thresh, cnew, cz, hraw, hz, B, H, SeqIO{xw, xw_sb, xw_st, out, out_sb, out_st, reverse});
     return rc();
 }
 int taco_op_lstm_bwd(const float* acts, const float* c_prev, const float* h_prev, const float* cnew, const int32_t* lens, int s,
@@ -673,7 +700,17 @@ int taco_op_lstm_bwd(const float* acts, const float* c_prev, const float* h_prev
                      int B, int H, void* stream) {
     if (!acts || !c_prev || !h_prev || !cnew || !d_hraw || !d_cz || !d_hz || !dgates || !d_cprev || !d_hprev) return -1;
     launch_pdl(lstm_bwd_kernel, dim3(nblk((long long)B * H)), dim3(256), 0, ST, acts, c_prev, h_prev, cnew, lens, s, zoneout, train, seed, stream_c, stream_h,
-                                                            row0, zo_keep_thresh, d_hraw, d_cz, d_hz, dgates, d_cprev, d_hprev, B, H);
+                                                            row0, zo_keep_thresh, d_hraw, d_cz, d_hz, dgates, d_cprev, d_hprev, B, H, SeqIO{nullptr, 0, 0, nullptr, 0, 0, 0});
+    return rc();
+}
+int taco_op_lstm_bwd_seq(const float* acts, const float* c_prev, const float* h_prev, const float* cnew, const int32_t* lens, int s,
+                         int reverse, float zoneout, int train, uint32_t zo_keep_thresh, uint64_t seed, uint32_t stream_c, uint32_t stream_h,
+                         int row0, const float* dout, long long dout_sb, long long dout_st, const float* d_cz, const float* d_hz,
+                         float* dgates, float* d_cprev, float* d_hprev, float* dxw, long long dxw_sb, long long dxw_st, int B, int H,
+                         void* stream) {
+    if (!acts || !c_prev || !h_prev || !cnew || !lens || !dout || !d_cz || !d_hz || !dgates || !d_cprev || !d_hprev || !dxw) return -1;
+    launch_pdl(lstm_bwd_kernel, dim3(nblk((long long)B * H)), dim3(256), 0, ST, acts, c_prev, h_prev, cnew, lens, s, zoneout, train, seed, stream_c, stream_h,
+               row0, zo_keep_thresh, (const float*)nullptr, d_cz, d_hz, dgates, d_cprev, d_hprev, B, H, SeqIO{dout, dout_sb, dout_st, dxw, dxw_sb, dxw_st, reverse});
     return rc();
 }
 int taco_op_gather_rows(const float* src, long long sb, long long st, const int32_t* lens, int s, int reverse, float* out,

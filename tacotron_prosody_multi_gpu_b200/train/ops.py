@@ -406,12 +406,13 @@ def _lstm_loop(self, bwd, dims, zoneout, seed, stream_c, stream_h, out, **t):
                                     stream_c=stream_c, stream_h=stream_h, out_sb=out.stride(0), out_st=out.stride(1)),
               dict(t, out=out))
     assert out.stride(2) == 1
-    _loop_call(self, "taco_op_lstm_loop_bwd" if bwd else "taco_op_lstm_loop_fwd", s, dims["T"] * 4)
+    _loop_call(self, "taco_op_lstm_loop_bwd" if bwd else "taco_op_lstm_loop_fwd", s, dims["T"] * 2)
 
 
 CudaOps.decoder_loop = _decoder_loop
 CudaOps.lstm_loop = _lstm_loop
-TRAIN_SYMBOLS = tuple(_SIGS.keys()) + LOOP_SYMBOLS + ("taco_op_set_precision", "taco_op_gemm_pair_acc", "taco_op_gemm_nt_split_acc", "taco_op_gemm_acc", "taco_op_attn_fused_supported", "taco_op_attn_bwd_noalloc")
+TRAIN_SYMBOLS = tuple(_SIGS.keys()) + LOOP_SYMBOLS + ("taco_op_set_precision", "taco_op_gemm_pair_acc", "taco_op_gemm_nt_split_acc", "taco_op_gemm_acc", "taco_op_attn_fused_supported", "taco_op_attn_bwd_noalloc",
+                                                         "taco_op_lstm_fwd_seq", "taco_op_lstm_bwd_seq")
 
 
 def _set_precision(self, precision):
