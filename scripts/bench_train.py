@@ -102,6 +102,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"],
                     help="reference: autograd through the CPU restatement (oracle/) on a bounded sample, rank 0 only")
     ap.add_argument("--host-inputs", type=int, default=1, help="1: every timed step copies its batch from pinned host memory (e2e form)")
+    ap.add_argument("--phases", action="store_true", help="print time stamps of the phases of the last step to stderr (CUDA events)")
     ap.add_argument("--no-overlap", action="store_true", help="one all-reduce of the whole bucket after backward (no early half)")
     args = ap.parse_args()
     global OUT
@@ -155,6 +156,7 @@ def main():
         if args.host_inputs:      # the e2e form: this step's batch comes from pinned host memory
             d_ids.copy_(p_ids, non_blocking=True); d_lens.copy_(p_lens, non_blocking=True)
             d_mel.copy_(p_mel, non_blocking=True); d_stop.copy_(p_stop, non_blocking=True)
+        st.marks = [] if args.phases else None
         out = st.forward(d_ids, d_lens, d_mel, d_stop, hp.tacotron_random_seed + it)
         e1 = ev()
         st.backward()
@@ -164,6 +166,11 @@ def main():
             loss_host = out["losses"].cpu()      # the step's result read back inside the timed region (e2e form)
         e3 = ev()
         torch.cuda.synchronize()
+        if args.phases and rank == 0 and it == args.warmup + args.steps - 1:
+            m = st.marks
+            for n1, b2 in m[1:]:          # time stamps relative to the first marker ([side] = recorded on a side stream)
+                print("[phase] %-52s at %7.3f ms" % (n1, m[0][1].elapsed_time(b2)), file=sys.stderr)
+            print("[phase] %-52s at %7.3f ms" % ("backward done", m[0][1].elapsed_time(e2)), file=sys.stderr)
         tr.global_step += 1
         if it >= args.warmup:
             wall += time.perf_counter() - t0

@@ -124,6 +124,14 @@ class TrainStep(object):
                 o.conv1d_dgrad(dz, w, dx)
         return dx
 
+    def _mark(self, name):
+        """Time stamp on the current stream (only when ``self.marks`` is a list: scripts/bench_train.py --phases)."""
+        if getattr(self, "marks", None) is not None:
+            import torch
+            ev = torch.cuda.Event(enable_timing=True)
+            ev.record()
+            self.marks.append((name, ev))
+
     def _side(self, i):
         """Launches of an independent branch of the step go to side stream i (CudaOps.side); a no-op for the CPU twin."""
         return self.ops.side(i) if hasattr(self.ops, "side") else contextlib.nullcontext()
@@ -171,6 +179,7 @@ class TrainStep(object):
         keep = 1.0 - hp.dropout_rate
         t = dict(B=B, T=T, F=F, S=S, seed=seed, ids=ids, lens=lens, mel=mel_targets, stop_tgt=stop_targets)
 
+        self._mark("fwd start")
         # ---- embedding + encoder convolutions (Tacotron.py:179-181; Encoder.py:40-46)
         emb = o.empty(B, T, hp.embedding_dim)
         o.embedding_fwd(ids, P["inputs_embedding"], emb)
@@ -181,6 +190,7 @@ class TrainStep(object):
         C = x.shape[-1]
         x3 = x.view(B * T, C)
 
+        self._mark("fwd encoder convs done")
         # ---- bidirectional zoneout LSTM over the valid length (Encoder.py:68-77,118-142)
         enc_out = o.zeros(B, T, 2 * H)
         t["bilstm"] = []
@@ -203,6 +213,9 @@ class TrainStep(object):
                     o.lstm_fwd(acts[s], pre, None, cz[s], hz[s], lens, s, zo, True, seed, sc, sh, s * B,
                                cnew[s], cz[s + 1], hraw[s], hz[s + 1])
                     o.scatter_rows(hraw[s], lens, s, rev, enc_out[:, :, d * H:(d + 1) * H])
+            if getattr(self, "marks", None) is not None:
+                with self._side(d):
+                    self._mark("  [side] BiLSTM direction %d done" % d)
             t["bilstm"].append(dict(scope=scope, rev=rev, acts=acts, cnew=cnew, cz=cz, hz=hz, sc=sc, sh=sh))
         t["x3"] = x3
 
@@ -213,6 +226,7 @@ class TrainStep(object):
         xr = mel_targets.view(B, F, M, 1)
         for i in range(len(hp.reference_filters)):
             xr = self._conv_block_fwd(xr, W.REF_CONV % i, ACT_RELU, 1.0, seed, 0, t["ref_conv"], conv2d=True)
+            self._mark("  [side] ref conv layer done")
         _, Tp, Wp, Cp = xr.shape
         In, R = Wp * Cp, hp.reference_depth
         Xt = o.empty(Tp, B, In)
@@ -227,6 +241,7 @@ class TrainStep(object):
             o.gru_pre(GX[s], hg[s], rh[s])        # GX[s] <- (r | u)
             o.gemm(rh[s], Wc[In:], CX[s], beta=1.0)
             o.gru_out(CX[s], GX[s], hg[s], hg[s + 1])   # CX[s] <- candidate c
+        self._mark("  [side] ref GRU done")
         refz, ref = o.empty(B, 128), o.empty(B, 128)
         o.gemm(hg[Tp], P[W.REF_DENSE + "/kernel"], refz, bias=P[W.REF_DENSE + "/bias"])
         o.ew("tanh", ref, refz)
@@ -242,6 +257,7 @@ class TrainStep(object):
         wts, style = o.empty(B, nh, tok.shape[0]), o.empty(B, nh * tok.shape[1])
         o.gst_fwd(gq, gk, P[W.MHA + "/attention_v"], P[W.MHA + "/attention_g"], P[W.MHA + "/attention_b"], tt, nh, wts, style)
         t.update(tt=tt, gq=gq, gk=gk, wts=wts)
+        self._mark("  [side] GST done")
         ref_side.__exit__(None, None, None)
         self._join()                               # both LSTM directions and the style embedding are ready
         SD = style.shape[1]
@@ -251,6 +267,7 @@ class TrainStep(object):
         o.tile_style(style, memory, 2 * H)
         t["memory"] = memory
 
+        self._mark("fwd BiLSTM + reference encoder joined")
         # ---- attention memory (Attention.py:153-158): masked values, keys computed once
         values = o.empty(B, T, MD)
         values.copy_(memory)
@@ -263,6 +280,7 @@ class TrainStep(object):
         o.gemm(values.view(B * T, MD), P[W.MEMORY_LAYER + "/kernel"], keys.view(B * T, A))
         t.update(values=values, keys=keys, lens_eff=lens_eff, MD=MD)
 
+        self._mark("fwd memory / keys done")
         # ---- decoder, teacher-forced (Decoder.py:246-292; Helpers.py:62-128; ratio 1.0)
         Xin = o.zeros(S, B, M)                                       # <GO> frame, then targets[:, r*t - 1]
         if S > 1:
@@ -328,6 +346,7 @@ class TrainStep(object):
         o.clip_fwd(frames, self.clip[0], self.clip[1], dec_out)      # :282-284
         t.update(frames=frames, stop_logits=stop_logits, dec_out=dec_out)
 
+        self._mark("fwd decoder (prenet, loop, projections) done")
         # ---- postnet + projection + residual + clip (Postnet.py:28-36; Tacotron.py:287-309)
         t["postnet"] = []
         x = dec_out
@@ -343,6 +362,7 @@ class TrainStep(object):
         o.clip_fwd(pre_mel, self.clip[0], self.clip[1], mel_out)
         t.update(post_x=x, pre_mel=pre_mel, mel_out=mel_out)
 
+        self._mark("fwd postnet done")
         # ---- losses (Tacotron.py:388-396,419-446; mask_decoder=False branch)
         if hp.mask_decoder:
             raise NotImplementedError("mask_decoder=True (MaskedMSE, Tacotron.py:373-386) is not the default branch")
@@ -371,6 +391,7 @@ class TrainStep(object):
         keep = 1.0 - hp.dropout_rate
         self.store.g.zero_()
 
+        self._mark("bwd start")
         # ---- postnet
         d_pre = o.empty(B, F, M)
         o.clip_bwd(t["d_mel"], t["pre_mel"], self.clip[0], self.clip[1], d_pre)
@@ -386,6 +407,7 @@ class TrainStep(object):
         d_frames = o.empty(B, F, M)
         o.clip_bwd(d_dec, t["frames"], self.clip[0], self.clip[1], d_frames)
 
+        self._mark("bwd postnet done")
         # ---- frame / stop projections (all steps at once)
         dY, dL = o.empty(S, B, M * r), o.empty(S, B, r)
         dY.copy_(d_frames.view(B, S, M * r).transpose(0, 1))
@@ -406,6 +428,7 @@ class TrainStep(object):
         o.gemm(dY2, Wf[D:], dCtx.view(S * B, MD), tb=True)
         o.gemm(dL2, Ws[D:], dCtx.view(S * B, MD), tb=True, beta=1.0)
 
+        self._mark("bwd projections done")
         # ---- decoder BPTT
         U1, U2 = hp.prenet_layers
         W1, W2 = P[W.DEC_LSTM % (0, 1) + "/kernel"], P[W.DEC_LSTM % (1, 2) + "/kernel"]
@@ -460,6 +483,7 @@ class TrainStep(object):
             o.mask_rows(dvalues, t["lens"])
         dmemory = dvalues
 
+        self._mark("bwd decoder BPTT + d(values) done")
         # ---- style embedding: GST attention -> reference encoder (Attention.py:243-341; Tacotron.py:12-29)
         nh = hp.num_heads
         tt, ref, Tp, In = t["tt"], t["ref"], t["Tp"], t["In"]
@@ -541,6 +565,7 @@ class TrainStep(object):
                 o.gemm(x3, dxw2, GK[:C], ta=True)
                 o.colsum(dxw2, G[rec["scope"] + "/bias"])
             dxws.append((dxw2, K))
+        self._mark("bwd side chains forked")
         # ---- decoder weight gradients and the prenet, all steps at once: on the main stream while the three encoder-side
         # chains above run on their side streams
         dG1_2, dG2_2, dQ2 = dG1.view(S * B, 4 * D), dG2.view(S * B, 4 * D), dQ.view(S * B, A)
@@ -571,6 +596,7 @@ class TrainStep(object):
         for d, (dxw2, K) in enumerate(dxws):
             o.gemm(dxw2, K[:C], dx3, tb=True, beta=0.0 if d == 0 else 1.0)
 
+        self._mark("bwd weight gradients done, side chains joined")
         # ---- encoder convolutions + embedding
         dy = dx3.view(B, T, C)
         for rec in reversed(t["enc_conv"]):
