@@ -239,6 +239,21 @@ typedef struct TacoLstmLoop {
 int taco_op_lstm_loop_fwd(const TacoLstmLoop* p, void* stream);
 int taco_op_lstm_loop_bwd(const TacoLstmLoop* p, void* stream);
 
+/* The GRU of the reference encoder (Tacotron.py:201, GRUCell over the Tp frames of the convolution stack) sequenced in C:
+ * forward per step  GX[s] += h . Wg[In:], (r|u) = sigmoid, rh = r * h, CX[s] += rh . Wc[In:], h' = u * h + (1 - u) * tanh(CX[s]);
+ * backward the mirrored chain.  GX / CX hold the hoisted input projections (+ bias) on entry and the activations on exit. */
+typedef struct TacoGruLoop {
+    int32_t B, Tp, In, R;                    /* batch, steps, input width, units */
+    const float *Wg, *Wc;                    /* [In+R, 2R], [In+R, R] */
+    float *GX, *CX, *hg, *rh;                /* [Tp,B,2R], [Tp,B,R], [Tp+1,B,R] (slot 0 = initial state), [Tp,B,R] */
+    /* backward only */
+    float *dGX, *dCX;                        /* [Tp,B,2R], [Tp,B,R] out */
+    float *dh;                               /* [B,R]: in = d(final state), out = d(initial state) */
+    float* work;                             /* >= 2*B*R floats */
+} TacoGruLoop;
+int taco_op_gru_loop_fwd(const TacoGruLoop* p, void* stream);
+int taco_op_gru_loop_bwd(const TacoGruLoop* p, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -154,4 +154,46 @@ int taco_op_lstm_loop_bwd(const TacoLstmLoop* p, void* st) {
     return 0;
 }
 
+int taco_op_gru_loop_fwd(const TacoGruLoop* p, void* st) {
+    if (!p || !p->Wg || !p->Wc || !p->GX || !p->CX || !p->hg || !p->rh || p->B < 1 || p->Tp < 1 || p->R < 1) return -1;
+    const int B = p->B, R = p->R;
+    const float* Wgh = p->Wg + (size_t)p->In * 2 * R;
+    const float* Wch = p->Wc + (size_t)p->In * R;
+    for (int s = 0; s < p->Tp; ++s) {
+        float* gx = p->GX + (size_t)s * B * 2 * R;
+        float* cx = p->CX + (size_t)s * B * R;
+        const float* h = p->hg + (size_t)s * B * R;
+        float* rh = p->rh + (size_t)s * B * R;
+        OK(taco_op_gemm_acc(h, R, Wgh, 2 * R, gx, 2 * R, B, 2 * R, R, 0, st));
+        OK(taco_op_gru_pre(gx, h, rh, B, R, st));
+        OK(taco_op_gemm_acc(rh, R, Wch, R, cx, R, B, R, R, 0, st));
+        OK(taco_op_gru_out(cx, gx, h, p->hg + (size_t)(s + 1) * B * R, B, R, st));
+    }
+    return 0;
+}
+
+int taco_op_gru_loop_bwd(const TacoGruLoop* p, void* st) {
+    if (!p || !p->Wg || !p->Wc || !p->GX || !p->CX || !p->hg || !p->dGX || !p->dCX || !p->dh || !p->work) return -1;
+    const int B = p->B, R = p->R;
+    const float* Wgh = p->Wg + (size_t)p->In * 2 * R;
+    const float* Wch = p->Wc + (size_t)p->In * R;
+    float* dh = p->dh;
+    float* dhd = p->work;
+    float* drh = p->work + (size_t)B * R;
+    for (int s = p->Tp - 1; s >= 0; --s) {
+        const float* gx = p->GX + (size_t)s * B * 2 * R;
+        const float* cx = p->CX + (size_t)s * B * R;
+        const float* h = p->hg + (size_t)s * B * R;
+        float* dgx = p->dGX + (size_t)s * B * 2 * R;
+        float* dcx = p->dCX + (size_t)s * B * R;
+        OK(taco_op_gru_out_bwd(dh, gx, h, cx, dcx, dgx, dhd, B, R, st));
+        OK(taco_op_gemm(dcx, R, Wch, R, drh, R, B, R, R, 0, 1, 0.f, nullptr, st));
+        OK(taco_op_gru_pre_bwd(drh, gx, h, dgx, dhd, B, R, st));
+        OK(taco_op_gemm(dgx, 2 * R, Wgh, 2 * R, dhd, R, B, R, 2 * R, 0, 1, 1.f, nullptr, st));
+        float* t_ = dh; dh = dhd; dhd = t_;
+    }
+    if (dh != p->dh && cudaMemcpyAsync(p->dh, dh, sizeof(float) * (size_t)B * R, cudaMemcpyDeviceToDevice, (cudaStream_t)st) != cudaSuccess) return -3;
+    return 0;
+}
+
 }  // extern "C"

@@ -370,7 +370,13 @@ class TacoLstmLoop(C.Structure):
                 [(n, C.c_void_p) for n in ("dxw", "dg", "work")])
 
 
-LOOP_SYMBOLS = ("taco_op_decoder_loop_fwd", "taco_op_decoder_loop_bwd", "taco_op_lstm_loop_fwd", "taco_op_lstm_loop_bwd")
+class TacoGruLoop(C.Structure):
+    _fields_ = ([(n, C.c_int32) for n in ("B", "Tp", "In", "R")] +
+                [(n, C.c_void_p) for n in ("Wg", "Wc", "GX", "CX", "hg", "rh", "dGX", "dCX", "dh", "work")])
+
+
+LOOP_SYMBOLS = ("taco_op_decoder_loop_fwd", "taco_op_decoder_loop_bwd", "taco_op_lstm_loop_fwd", "taco_op_lstm_loop_bwd",
+                "taco_op_gru_loop_fwd", "taco_op_gru_loop_bwd")
 
 
 def _fill(struct, ints, ptrs):
@@ -409,6 +415,12 @@ def _lstm_loop(self, bwd, dims, zoneout, seed, stream_c, stream_h, out, **t):
     _loop_call(self, "taco_op_lstm_loop_bwd" if bwd else "taco_op_lstm_loop_fwd", s, dims["T"] * 2)
 
 
+def _gru_loop(self, bwd, dims, **t):
+    s = _fill(TacoGruLoop(), dims, t)
+    _loop_call(self, "taco_op_gru_loop_bwd" if bwd else "taco_op_gru_loop_fwd", s, dims["Tp"] * 4)
+
+
+CudaOps.gru_loop = _gru_loop
 CudaOps.decoder_loop = _decoder_loop
 CudaOps.lstm_loop = _lstm_loop
 TRAIN_SYMBOLS = tuple(_SIGS.keys()) + LOOP_SYMBOLS + ("taco_op_set_precision", "taco_op_gemm_pair_acc", "taco_op_gemm_nt_split_acc", "taco_op_gemm_acc", "taco_op_attn_fused_supported", "taco_op_attn_bwd_noalloc",

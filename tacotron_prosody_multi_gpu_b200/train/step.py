@@ -236,7 +236,10 @@ class TrainStep(object):
         o.gemm(Xt.view(Tp * B, In), Wg[:In], GX.view(Tp * B, 2 * R), bias=P[W.REF_GRU + "/gates/bias"])
         o.gemm(Xt.view(Tp * B, In), Wc[:In], CX.view(Tp * B, R), bias=P[W.REF_GRU + "/candidate/bias"])
         hg, rh = o.zeros(Tp + 1, B, R), o.empty(Tp, B, R)
-        for s in range(Tp):                       # GRUCell: reset applied before the candidate matmul (App. A.9)
+        gru_fast = hasattr(o, "gru_loop")         # the same loop sequenced in C (train_loops.cu)
+        if gru_fast:
+            o.gru_loop(False, dict(B=B, Tp=Tp, In=In, R=R), Wg=Wg, Wc=Wc, GX=GX, CX=CX, hg=hg, rh=rh)
+        for s in range(0 if not gru_fast else Tp, Tp):   # GRUCell: reset applied before the candidate matmul (App. A.9)
             o.gemm(hg[s], Wg[In:], GX[s], beta=1.0)
             o.gru_pre(GX[s], hg[s], rh[s])        # GX[s] <- (r | u)
             o.gemm(rh[s], Wc[In:], CX[s], beta=1.0)
@@ -510,7 +513,11 @@ class TrainStep(object):
         self._dense_bwd(hg[Tp], drefz, W.REF_DENSE + "/kernel", W.REF_DENSE + "/bias", dh)
         Wg, Wc = P[W.REF_GRU + "/gates/kernel"], P[W.REF_GRU + "/candidate/kernel"]
         dGX, dCX = o.empty(Tp, B, 2 * R), o.empty(Tp, B, R)
-        for s in range(Tp - 1, -1, -1):
+        gru_fast = hasattr(o, "gru_loop")
+        if gru_fast:
+            o.gru_loop(True, dict(B=B, Tp=Tp, In=In, R=R), Wg=Wg, Wc=Wc, GX=GX, CX=CX, hg=hg, rh=rh, dGX=dGX, dCX=dCX, dh=dh,
+                       work=o.empty(2 * B * R))
+        for s in range(Tp - 1 if not gru_fast else -1, -1, -1):
             o.gru_out_bwd(dh, GX[s], hg[s], CX[s], dCX[s], dGX[s], dhd)
             o.gemm(dCX[s], Wc[In:], drh, tb=True)
             o.gru_pre_bwd(drh, GX[s], hg[s], dGX[s], dhd)
